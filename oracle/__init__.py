@@ -1,0 +1,190 @@
+"""TEST INFRASTRUCTURE — not product code.
+
+ctypes/numpy front-end to the two CPU checkers:
+
+* ``oracle.port``  — ``oracle/libstevi_oracle.so``: our plain-C restatement (``oracle/stevi_oracle.c``).
+* ``oracle.ref``   — ``oracle/_ref/libstevi_ref.so``: the UNMODIFIED reference headers compiled from
+  ``/root/reference`` by ``oracle/Makefile`` (``None`` when it was never built).
+
+Both expose the same method names. Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs may import this module; ``libstevi_b200`` never does.
+All arrays are dense C-order numpy arrays.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+# enums (matching_costs.h:38-53, correlation_base.h:31-45, cost_based_refinement.h:30-35)
+CC, NCC, SSD, SAD, ZCC, ZNCC, ZSSD, ZSAD, HAMMING, CENSUS = 0, 1, 2, 3, 4, 5, 6, 7, 10, 11
+COST, SCORE = 0, 1
+L2R, R2L = 0, 1
+EQUIANGULAR, PARABOLA, GAUSSIAN = 0, 1, 2
+TCV_SAME, TCV_REVERSED, TCV_BOTH = 0, 1, 2
+SCORE_FUNCS = (CC, NCC, ZCC, ZNCC)
+
+
+def strategy_of(mf):
+    return SCORE if mf in SCORE_FUNCS else COST
+
+
+def build(ref=True):
+    """(Re)build the checkers. Building the checker is not using it."""
+    targets = ["oracle"] + (["ref"] if ref else [])
+    subprocess.run(["make", "-s", "-C", _HERE] + targets, check=True)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _c(a, dt):
+    return np.ascontiguousarray(a, dtype=dt)
+
+
+class _Checker:
+    def __init__(self, path, prefix):
+        self.lib = ctypes.CDLL(path)
+        self.prefix = prefix
+        self.path = path
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def has(self, name):
+        return hasattr(self.lib, self.prefix + name)
+
+    def set_num_threads(self, n):
+        if self.prefix == "ref_":
+            self.lib.ref_set_num_threads(int(n))
+
+    # --- features -----------------------------------------------------------------
+    def unfold(self, img, hr, vr):
+        h, w = img.shape
+        F = (2 * hr + 1) * (2 * vr + 1)
+        if img.dtype == np.uint8:
+            out = np.empty((h, w, F), np.uint8)
+            self._f("unfold_u8")(_p(_c(img, np.uint8)), h, w, hr, vr, _p(out))
+        else:
+            out = np.empty((h, w, F), np.float32)
+            self._f("unfold_f32")(_p(_c(img, np.float32)), h, w, hr, vr, _p(out))
+        return out
+
+    def census(self, img, hr, vr):
+        h, w = img.shape
+        F = (2 * hr + 1) * (2 * vr + 1)
+        nw = (F - 1) // 32 + 1
+        out = np.zeros((h, w, nw), np.uint32)
+        if img.dtype == np.uint8:
+            self._f("census_u8")(_p(_c(img, np.uint8)), h, w, hr, vr, _p(out))
+        else:
+            self._f("census_f32")(_p(_c(img, np.float32)), h, w, hr, vr, _p(out))
+        return out
+
+    def feature_volume(self, mf, img, hr, vr):
+        h, w = img.shape
+        out = np.empty((h, w, (2 * hr + 1) * (2 * vr + 1)), np.float32)
+        rc = self._f("feature_volume_f32")(mf, _p(_c(img, np.float32)), h, w, hr, vr, _p(out))
+        assert rc == 0
+        return out
+
+    # --- cost volumes ---------------------------------------------------------------
+    def cost_volume(self, mf, left, right, hr, vr, D, direction=R2L):
+        """unfoldBasedCostVolume; returns None where the reference returns an empty array."""
+        h, wl = left.shape
+        h2, wr = right.shape
+        if h != h2:
+            return None
+        ws = wr if direction == R2L else wl
+        if mf == CENSUS:
+            out = np.empty((h, ws, D), np.uint16)
+            if left.dtype == np.uint8:
+                rc = self._f("census_cost_volume_u8")(_p(_c(left, np.uint8)), _p(_c(right, np.uint8)),
+                                                      h, wl, wr, hr, vr, D, direction, _p(out))
+            else:
+                rc = self._f("census_cost_volume_f32")(_p(_c(left, np.float32)), _p(_c(right, np.float32)),
+                                                       h, wl, wr, hr, vr, D, direction, _p(out))
+        else:
+            out = np.empty((h, ws, D), np.float32)
+            rc = self._f("cost_volume_f32")(mf, _p(_c(left, np.float32)), _p(_c(right, np.float32)),
+                                            h, wl, wr, hr, vr, D, direction, _p(out))
+        return out if rc == 0 else None
+
+    def sgm(self, cv, ndir, strategy, P1, P2, Pout=100.0, margins=(0, 0, 0, 0)):
+        h, w, D = cv.shape
+        out = np.empty((h, w, D), np.float32)
+        m = np.asarray(margins, np.int32)
+        f32 = ctypes.c_float
+        if cv.dtype == np.uint16:
+            rc = self._f("sgm_u16")(_p(_c(cv, np.uint16)), h, w, D, ndir, strategy, f32(P1), f32(P2), f32(Pout), _p(m), _p(out))
+        else:
+            rc = self._f("sgm_f32")(_p(_c(cv, np.float32)), h, w, D, ndir, strategy, f32(P1), f32(P2), f32(Pout), _p(m), _p(out))
+        assert rc == 0
+        return out
+
+    def wta(self, vol, strategy):
+        h, w, D = vol.shape
+        out = np.empty((h, w), np.int32)
+        if vol.dtype == np.uint16:
+            self._f("wta_u16")(_p(_c(vol, np.uint16)), h, w, D, strategy, _p(out))
+        else:
+            self._f("wta_f32")(_p(_c(vol, np.float32)), h, w, D, strategy, _p(out))
+        return out
+
+    def index_to_disp(self, idx, direction=R2L, offset=0):
+        h, w = idx.shape
+        out = np.empty((h, w), np.int32)
+        self._f("index_to_disp")(_p(_c(idx, np.int32)), h, w, direction, offset, _p(out))
+        return out
+
+    def selected_cost(self, cv, idx):
+        h, w, D = cv.shape
+        out = np.empty((h, w), np.float32)
+        self._f("selected_cost_f32")(_p(_c(cv, np.float32)), _p(_c(idx, np.int32)), h, w, D, _p(out))
+        return out
+
+    def truncated_cost_volume(self, cv, idx, hr, vr, radius, direction=R2L, tdir=TCV_SAME):
+        h, w, D = cv.shape
+        T = 4 * radius + 1 if tdir == TCV_BOTH else 2 * radius + 1
+        out = np.empty((h, w, T), np.float32)
+        self._f("truncated_cost_volume_f32")(_p(_c(cv, np.float32)), _p(_c(idx, np.int32)), h, w, D,
+                                             hr, vr, radius, direction, tdir, _p(out))
+        return out
+
+    def refine(self, tcv, idx, kernel=PARABOLA):
+        h, w, T = tcv.shape
+        out = np.empty((h, w), np.float32)
+        rc = self._f("refine_disp_cost_interp")(_p(_c(tcv, np.float32)), _p(_c(idx, np.int32)), h, w, T, kernel, _p(out))
+        return out if rc == 0 else None
+
+    def avgpool2(self, img):
+        h, w = img.shape
+        out = np.empty(((h + 1) // 2, (w + 1) // 2), np.float32)
+        self._f("avgpool2_f32")(_p(_c(img, np.float32)), h, w, _p(out))
+        return out
+
+    def hierarchical(self, mf, depth, left, right, hr, vr, D, radius=2, direction=R2L):
+        h, w = left.shape
+        tcv = np.empty((h, w, 2 * radius + 1), np.float32)
+        disp = np.empty((h, w), np.int32)
+        rc = self._f("hierarchical_f32")(mf, depth, _p(_c(left, np.float32)), _p(_c(right, np.float32)), h, w,
+                                         hr, vr, D, radius, direction, _p(tcv), _p(disp))
+        return (tcv, disp) if rc == 0 else None
+
+
+def _load():
+    port_path = os.path.join(_HERE, "libstevi_oracle.so")
+    ref_path = os.path.join(_HERE, "_ref", "libstevi_ref.so")
+    if not os.path.exists(port_path):
+        build(ref=False)
+    p = _Checker(port_path, "orc_")
+    p.lib.orc_refine_cost_triplet.restype = ctypes.c_float
+    p.lib.orc_round_through_float.restype = ctypes.c_uint32
+    r = _Checker(ref_path, "ref_") if os.path.exists(ref_path) else None
+    return p, r
+
+
+port, ref = _load()

@@ -1,0 +1,250 @@
+// TEST INFRASTRUCTURE — not product code. Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline /
+// --impl reference legs may load the library built from this file.
+//
+// Thin extern "C" wrapper over the UNMODIFIED reference headers (included from $STEVI_REF, default
+// /root/reference, never copied into this repo). Built by oracle/Makefile into oracle/_ref/libstevi_ref.so.
+// All buffers are dense C-order (last index fastest); wrappers build Multidim::Array views with explicit
+// strides, call the reference template exactly as test/benchmarks/benchmarkCrossCorrelationAlgorithms.cpp
+// (:93-95, :216-221, :289-293) does, and copy the result out element by element.
+#include <cstdint>
+#include <cstring>
+#include <cmath>
+#include <omp.h>
+
+#include <correlation/cross_correlations.h>
+#include <correlation/sgm.h>
+#include <correlation/hierarchical.h>
+#include <correlation/cost_based_refinement.h>
+#include <correlation/census.h>
+#include <correlation/unfold.h>
+#include <interpolation/downsampling.h>
+
+using namespace StereoVision;
+using namespace StereoVision::Correlation;
+namespace MD = Multidim;
+
+namespace {
+
+template<typename T>
+MD::Array<T, 2> view2(const T* p, int h, int w) {
+	return MD::Array<T, 2>(const_cast<T*>(p), {h, w}, {w, 1}, false);
+}
+template<typename T>
+MD::Array<T, 3> view3(const T* p, int h, int w, int c) {
+	return MD::Array<T, 3>(const_cast<T*>(p), {h, w, c}, {w * c, c, 1}, false);
+}
+template<typename T, typename TO>
+void out3(MD::Array<T, 3> const& a, TO* out) {
+	auto s = a.shape();
+	for (int i = 0; i < s[0]; i++) for (int j = 0; j < s[1]; j++) for (int k = 0; k < s[2]; k++)
+		out[(size_t(i) * s[1] + j) * s[2] + k] = static_cast<TO>(a.valueUnchecked(i, j, k));
+}
+template<typename T, typename TO>
+void out2(MD::Array<T, 2> const& a, TO* out) {
+	auto s = a.shape();
+	for (int i = 0; i < s[0]; i++) for (int j = 0; j < s[1]; j++)
+		out[size_t(i) * s[1] + j] = static_cast<TO>(a.valueUnchecked(i, j));
+}
+
+template<matchingFunctions F, typename TI, typename TCV>
+int cv_dir(const TI* l, const TI* r, int h, int w, int wr, int hr, int vr, int D, int dir, TCV* out) {
+	auto L = view2(l, h, w);
+	auto R = view2(r, h, wr);
+	if (dir == int(dispDirection::RightToLeft)) {
+		auto cv = unfoldBasedCostVolume<F, TI, TI, 2, dispDirection::RightToLeft, TCV>(L, R, hr, vr, D);
+		if (cv.empty()) return 1;
+		out3(cv, out);
+	} else {
+		auto cv = unfoldBasedCostVolume<F, TI, TI, 2, dispDirection::LeftToRight, TCV>(L, R, hr, vr, D);
+		if (cv.empty()) return 1;
+		out3(cv, out);
+	}
+	return 0;
+}
+
+template<dispExtractionStartegy S, typename T>
+int sgm_n(const T* cv, int h, int w, int d, int ndir, float P1, float P2, float Pout, const int* m, float* out) {
+	auto CV = view3(cv, h, w, d);
+	Margins mg(m[0], m[1], m[2], m[3]);
+	if (ndir == 4) out3(sgmCostVolume<4, S>(CV, P1, P2, mg, Pout), out);
+	else if (ndir == 8) out3(sgmCostVolume<8, S>(CV, P1, P2, mg, Pout), out);
+	else if (ndir == 16) out3(sgmCostVolume<16, S>(CV, P1, P2, mg, Pout), out);
+	else return 2;
+	return 0;
+}
+
+template<typename T>
+int wta_t(const T* v, int h, int w, int d, int strategy, int32_t* out) {
+	auto V = view3(v, h, w, d);
+	if (strategy == 0) out2(extractSelectedIndex<dispExtractionStartegy::Cost>(V), out);
+	else out2(extractSelectedIndex<dispExtractionStartegy::Score>(V), out);
+	return 0;
+}
+
+template<matchingFunctions F, int depth>
+int hier_d(const float* l, const float* r, int h, int w, int hr, int vr, int D, int radius, int dir,
+		   float* tcv, int32_t* disp) {
+	auto L = view2(l, h, w);
+	auto R = view2(r, h, w);
+	if (dir == int(dispDirection::RightToLeft)) {
+		auto o = hiearchicalTruncatedCostVolume<F, depth, float, float, 2, dispDirection::RightToLeft, float>(L, R, hr, vr, D, radius);
+		if (o.truncated_cost_volume.empty()) return 1;
+		out3(o.truncated_cost_volume, tcv); out2(o.disp_estimate, disp);
+	} else {
+		auto o = hiearchicalTruncatedCostVolume<F, depth, float, float, 2, dispDirection::LeftToRight, float>(L, R, hr, vr, D, radius);
+		if (o.truncated_cost_volume.empty()) return 1;
+		out3(o.truncated_cost_volume, tcv); out2(o.disp_estimate, disp);
+	}
+	return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int ref_num_threads() { return omp_get_max_threads(); }
+void ref_set_num_threads(int n) { omp_set_num_threads(n); }
+
+// unfold.h:248-291 (2-D image, auto padding). out is (h, w, F) C-order, F=(2hr+1)(2vr+1).
+int ref_unfold_f32(const float* img, int h, int w, int hr, int vr, float* out) {
+	out3(unfold<float, float>(uint8_t(hr), uint8_t(vr), view2(img, h, w)), out); return 0;
+}
+int ref_unfold_u8(const uint8_t* img, int h, int w, int hr, int vr, uint8_t* out) {
+	out3(unfold<uint8_t, uint8_t>(uint8_t(hr), uint8_t(vr), view2(img, h, w)), out); return 0;
+}
+
+// census.h:117-131. out is (h, w, nwords) uint32 C-order, nwords = (F-2)/32+1... i.e. (F-1-1)/32+1 per census.h:79.
+int ref_census_u8(const uint8_t* img, int h, int w, int hr, int vr, uint32_t* out) {
+	out3(censusTransform2D(view2(img, h, w), int8_t(hr), int8_t(vr)), out); return 0;
+}
+int ref_census_f32(const float* img, int h, int w, int hr, int vr, uint32_t* out) {
+	out3(censusTransform2D(view2(img, h, w), int8_t(hr), int8_t(vr)), out); return 0;
+}
+
+// cross_correlations.h:645-722 on the unfolded volume (float images). out (h, w, F) float.
+int ref_feature_volume_f32(int matchfunc, const float* img, int h, int w, int hr, int vr, float* out) {
+	auto fv = unfold<float, float>(uint8_t(hr), uint8_t(vr), view2(img, h, w));
+	switch (matchingFunctions(matchfunc)) {
+	case matchingFunctions::ZNCC: out3(getFeatureVolumeForMatchFunc<matchingFunctions::ZNCC>(fv), out); break;
+	case matchingFunctions::NCC: out3(getFeatureVolumeForMatchFunc<matchingFunctions::NCC>(fv), out); break;
+	case matchingFunctions::ZCC: out3(getFeatureVolumeForMatchFunc<matchingFunctions::ZCC>(fv), out); break;
+	case matchingFunctions::ZSSD: out3(getFeatureVolumeForMatchFunc<matchingFunctions::ZSSD>(fv), out); break;
+	case matchingFunctions::ZSAD: out3(getFeatureVolumeForMatchFunc<matchingFunctions::ZSAD>(fv), out); break;
+	case matchingFunctions::CC: out3(getFeatureVolumeForMatchFunc<matchingFunctions::CC>(fv), out); break;
+	case matchingFunctions::SSD: out3(getFeatureVolumeForMatchFunc<matchingFunctions::SSD>(fv), out); break;
+	case matchingFunctions::SAD: out3(getFeatureVolumeForMatchFunc<matchingFunctions::SAD>(fv), out); break;
+	default: return 2;
+	}
+	return 0;
+}
+
+// cross_correlations.h:740-765, float images, float cost volume. out (h, w, D) C-order.
+// The left image may be wider/narrower than the right one (only heights must match, :751).
+int ref_cost_volume_f32(int matchfunc, const float* l, const float* r, int h, int w, int wr,
+						int hr, int vr, int D, int dir, float* out) {
+	switch (matchingFunctions(matchfunc)) {
+	case matchingFunctions::CC: return cv_dir<matchingFunctions::CC>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::NCC: return cv_dir<matchingFunctions::NCC>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::SSD: return cv_dir<matchingFunctions::SSD>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::SAD: return cv_dir<matchingFunctions::SAD>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::ZCC: return cv_dir<matchingFunctions::ZCC>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::ZNCC: return cv_dir<matchingFunctions::ZNCC>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::ZSSD: return cv_dir<matchingFunctions::ZSSD>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::ZSAD: return cv_dir<matchingFunctions::ZSAD>(l, r, h, w, wr, hr, vr, D, dir, out);
+	default: return 2;
+	}
+}
+
+// census cost volume, hamming_cv_t (uint16) costs, as the C2/C5 configs use it.
+int ref_census_cost_volume_u8(const uint8_t* l, const uint8_t* r, int h, int w, int wr,
+							  int hr, int vr, int D, int dir, uint16_t* out) {
+	return cv_dir<matchingFunctions::CENSUS, uint8_t, uint16_t>(l, r, h, w, wr, hr, vr, D, dir, out);
+}
+int ref_census_cost_volume_f32(const float* l, const float* r, int h, int w, int wr,
+							   int hr, int vr, int D, int dir, uint16_t* out) {
+	return cv_dir<matchingFunctions::CENSUS, float, uint16_t>(l, r, h, w, wr, hr, vr, D, dir, out);
+}
+
+// sgm.h:360-404. margins = {left, top, right, bottom}, the ctor order of utils/margins.h:52.
+int ref_sgm_u16(const uint16_t* cv, int h, int w, int d, int ndir, int strategy,
+				float P1, float P2, float Pout, const int* margins, float* out) {
+	if (strategy == 0) return sgm_n<dispExtractionStartegy::Cost>(cv, h, w, d, ndir, P1, P2, Pout, margins, out);
+	return sgm_n<dispExtractionStartegy::Score>(cv, h, w, d, ndir, P1, P2, Pout, margins, out);
+}
+int ref_sgm_f32(const float* cv, int h, int w, int d, int ndir, int strategy,
+				float P1, float P2, float Pout, const int* margins, float* out) {
+	if (strategy == 0) return sgm_n<dispExtractionStartegy::Cost>(cv, h, w, d, ndir, P1, P2, Pout, margins, out);
+	return sgm_n<dispExtractionStartegy::Score>(cv, h, w, d, ndir, P1, P2, Pout, margins, out);
+}
+
+// correlation_base.h:427-464
+int ref_wta_f32(const float* v, int h, int w, int d, int strategy, int32_t* out) { return wta_t(v, h, w, d, strategy, out); }
+int ref_wta_u16(const uint16_t* v, int h, int w, int d, int strategy, int32_t* out) { return wta_t(v, h, w, d, strategy, out); }
+
+// correlation_base.h:511-532
+int ref_index_to_disp(const int32_t* idx, int h, int w, int dir, int offset, int32_t* out) {
+	auto I = view2(idx, h, w);
+	if (dir == int(dispDirection::RightToLeft)) out2(selectedIndexToDisp<disp_t, dispDirection::RightToLeft>(I, offset), out);
+	else out2(selectedIndexToDisp<disp_t, dispDirection::LeftToRight>(I, offset), out);
+	return 0;
+}
+
+// correlation_base.h:557-577
+int ref_selected_cost_f32(const float* cv, const int32_t* idx, int h, int w, int d, float* out) {
+	out2(selectedCost(view3(cv, h, w, d), view2(idx, h, w)), out); return 0;
+}
+
+// correlation_base.h:579-674; out (h, w, 2*radius+1)
+int ref_truncated_cost_volume_f32(const float* cv, const int32_t* idx, int h, int w, int d,
+								  int hr, int vr, int radius, int dir, int tdir, float* out) {
+	auto CV = view3(cv, h, w, d);
+	auto I = view2(idx, h, w);
+#define TCV_CASE(DD, TD) out3(truncatedCostVolume<float, dispDirection::DD, truncatedCostVolumeDirection::TD>(CV, I, hr, vr, radius), out)
+	bool r2l = dir == int(dispDirection::RightToLeft);
+	if (tdir == 0) { if (r2l) TCV_CASE(RightToLeft, Same); else TCV_CASE(LeftToRight, Same); }
+	else if (tdir == 1) { if (r2l) TCV_CASE(RightToLeft, Reversed); else TCV_CASE(LeftToRight, Reversed); }
+	else { if (r2l) TCV_CASE(RightToLeft, Both); else TCV_CASE(LeftToRight, Both); }
+#undef TCV_CASE
+	return 0;
+}
+
+// cost_based_refinement.h:128-163; returns 1 (and leaves out untouched) when the reference returns an empty array
+int ref_refine_disp_cost_interp(const float* tcv, const int32_t* idx, int h, int w, int t, int kernel, float* out) {
+	auto T = view3(tcv, h, w, t);
+	auto I = view2(idx, h, w);
+	MD::Array<float, 2> r;
+	if (kernel == int(InterpolationKernel::Equiangular)) r = refineDispCostInterpolation<InterpolationKernel::Equiangular>(T, I);
+	else if (kernel == int(InterpolationKernel::Parabola)) r = refineDispCostInterpolation<InterpolationKernel::Parabola>(T, I);
+	else r = refineDispCostInterpolation<InterpolationKernel::Gaussian>(T, I);
+	if (r.empty()) return 1;
+	out2(r, out);
+	return 0;
+}
+
+// interpolation/downsampling.h:67-118; out is (ceil(h/2), ceil(w/2))
+int ref_avgpool2_f32(const float* img, int h, int w, float* out) {
+	out2(Interpolation::averagePoolingDownsample<float, float>(view2(img, h, w), Interpolation::DownSampleWindows(2)), out);
+	return 0;
+}
+
+// hierarchical.h:297-314; tcv (h, w, 2*radius+1) float, disp (h, w) int32
+int ref_hierarchical_f32(int matchfunc, int depth, const float* l, const float* r, int h, int w,
+						 int hr, int vr, int D, int radius, int dir, float* tcv, int32_t* disp) {
+#define HIER(F) \
+	if (depth == 1) return hier_d<matchingFunctions::F, 1>(l, r, h, w, hr, vr, D, radius, dir, tcv, disp); \
+	if (depth == 2) return hier_d<matchingFunctions::F, 2>(l, r, h, w, hr, vr, D, radius, dir, tcv, disp); \
+	if (depth == 3) return hier_d<matchingFunctions::F, 3>(l, r, h, w, hr, vr, D, radius, dir, tcv, disp); \
+	return 2;
+	switch (matchingFunctions(matchfunc)) {
+	case matchingFunctions::ZNCC: HIER(ZNCC)
+	case matchingFunctions::NCC: HIER(NCC)
+	case matchingFunctions::SSD: HIER(SSD)
+	case matchingFunctions::SAD: HIER(SAD)
+	case matchingFunctions::ZSSD: HIER(ZSSD)
+	case matchingFunctions::ZSAD: HIER(ZSAD)
+	default: return 2;
+	}
+#undef HIER
+}
+
+} // extern "C"

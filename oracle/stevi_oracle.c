@@ -1,0 +1,531 @@
+/* TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+ *
+ * Plain-C CPU restatement of the algorithms on LibStevi's dense-stereo hot path, used only as
+ * the checker by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+ * The shipped library (libstevi_b200/csrc) never links, loads or calls anything in this file.
+ *
+ * Parity status: PINNED. Every function here is checked in tests/test_oracle_pinning.py against outputs of the
+ * reference's own headers compiled unmodified (oracle/_ref/libstevi_ref.so, built by oracle/Makefile from
+ * /root/reference) and against golden vectors generated from that library (tests/golden/, generator committed as
+ * tests/golden/make_golden.py), plus Qt-free restatements of the reference's own unit tests.
+ *
+ * All buffers are dense, C-order (last index fastest). File:line citations are relative to /root/reference.
+ * Compiled with -ffp-contract=off: the float operation ORDER below follows the reference's loops.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+
+/* enums mirror correlation/matching_costs.h:38-53, correlation_base.h:31-45, cost_based_refinement.h:30-35 */
+enum { MF_CC = 0, MF_NCC = 1, MF_SSD = 2, MF_SAD = 3, MF_ZCC = 4, MF_ZNCC = 5, MF_ZSSD = 6, MF_ZSAD = 7,
+	   MF_HAMMING = 10, MF_CENSUS = 11 };
+enum { STRAT_COST = 0, STRAT_SCORE = 1 };
+enum { DIR_L2R = 0, DIR_R2L = 1 };
+enum { K_EQUIANGULAR = 0, K_PARABOLA = 1, K_GAUSSIAN = 2 };
+
+static int mf_zero_mean(int mf) { return mf == MF_ZCC || mf == MF_ZNCC || mf == MF_ZSSD || mf == MF_ZSAD; }
+static int mf_normalized(int mf) { return mf == MF_NCC || mf == MF_ZNCC; }
+/* extraction strategy per MatchingFunctionTraits (matching_costs.h:419-685): correlations are scores */
+static int mf_strategy(int mf) { return (mf == MF_CC || mf == MF_NCC || mf == MF_ZCC || mf == MF_ZNCC) ? STRAT_SCORE : STRAT_COST; }
+
+int orc_matchfunc_strategy(int mf) { return mf_strategy(mf); }
+
+/* ---- unfold.h:248-291 (2-D image, auto padding, Rotate0): out(i,j,(2hr+1)*k+l) = img(i-vr+k, j-hr+l), 0 outside */
+#define DEF_UNFOLD(NAME, T) \
+int NAME(const T* img, int h, int w, int hr, int vr, T* out) { \
+	int hs = 2 * hr + 1, vs = 2 * vr + 1, F = hs * vs; \
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) \
+		for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) { \
+			int ii = i - vr + k, jj = j - hr + l; \
+			T v = (ii >= 0 && ii < h && jj >= 0 && jj < w) ? img[(size_t)ii * w + jj] : (T)0; \
+			out[((size_t)i * w + j) * F + hs * k + l] = v; \
+		} \
+	return 0; \
+}
+DEF_UNFOLD(orc_unfold_f32, float)
+DEF_UNFOLD(orc_unfold_u8, uint8_t)
+
+/* ---- census.h:69-115 on an (h,w,F) feature volume: bit b of word n = (feat[0] > feat[1+32n+b]).
+ * Q1: a word is stored only when all 32 bits were filled (census.h:103-108); trailing partial word stays 0
+ * (zero-initialised allocation in the stand-in array type). nwords = (F-1)/32 + 1 (census.h:79). */
+#define DEF_CENSUS_FEATS(NAME, T) \
+static void NAME(const T* fv, int h, int w, int F, uint32_t* out) { \
+	int nw = (F - 1) / 32 + 1; \
+	memset(out, 0, (size_t)h * w * nw * sizeof(uint32_t)); \
+	for (size_t p = 0; p < (size_t)h * w; p++) { \
+		const T* f = fv + p * F; \
+		T ref = f[0]; \
+		uint32_t d = 0; int b = 0, ch = 0; \
+		for (int c = 1; c < F; c++) { \
+			uint32_t g = (ref > f[c]) ? 1u : 0u; \
+			d |= g << b; b++; \
+			if (b >= 32) { out[p * nw + ch] = d; ch++; d = 0; b = 0; } \
+		} \
+	} \
+}
+DEF_CENSUS_FEATS(census_feats_f32, float)
+DEF_CENSUS_FEATS(census_feats_u8, uint8_t)
+
+int orc_census_nwords(int hr, int vr) { int F = (2 * hr + 1) * (2 * vr + 1); return (F - 1) / 32 + 1; }
+
+/* census.h:117-131 censusTransform2D = unfold + censusFeatures */
+int orc_census_u8(const uint8_t* img, int h, int w, int hr, int vr, uint32_t* out) {
+	int F = (2 * hr + 1) * (2 * vr + 1);
+	if (F <= 1) return 1; /* census.h:75-77: empty result */
+	uint8_t* fv = (uint8_t*)malloc((size_t)h * w * F);
+	orc_unfold_u8(img, h, w, hr, vr, fv);
+	census_feats_u8(fv, h, w, F, out);
+	free(fv);
+	return 0;
+}
+int orc_census_f32(const float* img, int h, int w, int hr, int vr, uint32_t* out) {
+	int F = (2 * hr + 1) * (2 * vr + 1);
+	if (F <= 1) return 1;
+	float* fv = (float*)malloc((size_t)h * w * F * sizeof(float));
+	orc_unfold_f32(img, h, w, hr, vr, fv);
+	census_feats_f32(fv, h, w, F, out);
+	free(fv);
+	return 0;
+}
+
+/* ---- cross_correlations.h:645-722 for float images: in place on an (h,w,F) unfolded volume.
+ * mean = (sum_c v) * (1/F)            correlation_base.h:1116-1130
+ * norm = sqrtf(sum_c (v-mean)^2)      cross_correlations.h:61-104   (or sum v^2 for NCC, :149-191)
+ * feat = (v-mean)/norm                cross_correlations.h:452      (no epsilon: flat patch -> NaN, Q6) */
+static void features_inplace(int mf, float* fv, size_t npix, int F) {
+	int zm = mf_zero_mean(mf), nm = mf_normalized(mf);
+	if (!zm && !nm) return;
+	float scale = 1.f / (float)F;
+	for (size_t p = 0; p < npix; p++) {
+		float* f = fv + p * F;
+		float mean = 0.f;
+		if (zm) {
+			for (int c = 0; c < F; c++) mean += f[c];
+			mean *= scale;
+		}
+		if (nm) {
+			float n = 0.f;
+			for (int c = 0; c < F; c++) { float t = zm ? (f[c] - mean) : f[c]; n += t * t; }
+			n = sqrtf(n);
+			for (int c = 0; c < F; c++) f[c] = (zm ? (f[c] - mean) : f[c]) / n;
+		} else {
+			for (int c = 0; c < F; c++) f[c] = f[c] - mean;
+		}
+	}
+}
+
+int orc_feature_volume_f32(int mf, const float* img, int h, int w, int hr, int vr, float* out) {
+	int F = (2 * hr + 1) * (2 * vr + 1);
+	orc_unfold_f32(img, h, w, hr, vr, out);
+	features_inplace(mf, out, (size_t)h * w, F);
+	return 0;
+}
+
+/* ---- matching_costs.h:59-78 / :100-116 / :136-156: sequential accumulation over channels in float */
+static float compare_f32(int mf, const float* s, const float* t, int F) {
+	float acc = 0.f;
+	switch (mf) {
+	case MF_CC: case MF_NCC: case MF_ZCC: case MF_ZNCC:
+		for (int c = 0; c < F; c++) acc += s[c] * t[c];
+		break;
+	case MF_SSD: case MF_ZSSD:
+		for (int c = 0; c < F; c++) { float d = s[c] - t[c]; acc += d * d; }
+		break;
+	default: /* SAD, ZSAD */
+		for (int c = 0; c < F; c++) acc += fabsf(s[c] - t[c]);
+		break;
+	}
+	return acc;
+}
+
+/* ---- cross_correlations.h:194-249 aggregateCost + :740-765 unfoldBasedCostVolume, float images.
+ * RightToLeft: source = right image, target = left image, target column j + d (correlation_base.h:829-852,
+ * cross_correlations.h:204,235); LeftToRight: source = left, target = right, column j - d.
+ * Target features are 0 when the column is outside the TARGET image (valueOrAlt, :235).
+ * out is (h, w_source, D) C-order. Returns 1 (reference returns an empty array) when heights differ (:751). */
+int orc_cost_volume_f32(int mf, const float* l, const float* r, int h, int wl, int wr,
+						int hr, int vr, int D, int dir, float* out) {
+	int F = (2 * hr + 1) * (2 * vr + 1);
+	float* fl = (float*)malloc((size_t)h * wl * F * sizeof(float));
+	float* fr = (float*)malloc((size_t)h * wr * F * sizeof(float));
+	orc_feature_volume_f32(mf, l, h, wl, hr, vr, fl);
+	orc_feature_volume_f32(mf, r, h, wr, hr, vr, fr);
+	const float* src = dir == DIR_R2L ? fr : fl; int ws = dir == DIR_R2L ? wr : wl;
+	const float* tgt = dir == DIR_R2L ? fl : fr; int wt = dir == DIR_R2L ? wl : wr;
+	int sgn = dir == DIR_R2L ? 1 : -1;
+	float* zero = (float*)calloc((size_t)F, sizeof(float));
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) for (int j = 0; j < ws; j++) for (int d = 0; d < D; d++) {
+		int jt = j + sgn * d;
+		const float* t = (jt >= 0 && jt < wt) ? tgt + ((size_t)i * wt + jt) * F : zero;
+		out[((size_t)i * ws + j) * D + d] = compare_f32(mf, src + ((size_t)i * ws + j) * F, t, F);
+	}
+	free(zero); free(fl); free(fr);
+	return 0;
+}
+
+/* Q2 (cross_correlations.h:235-236): every TARGET feature passes through `float t` before being narrowed back
+ * to the feature type. For uint32 census words that is a round-to-nearest-even to 24 significant bits; a word
+ * >= 0xFFFFFF80 rounds to 2^32 whose conversion back is undefined behaviour in C++ — the scalar x86-64 result
+ * (cvttss2si on a 64-bit register, then truncation) is 0, which is what we document and reproduce. */
+uint32_t orc_round_through_float(uint32_t w) {
+	float t = (float)w;
+	if (t >= 4294967296.0f) return 0u;
+	return (uint32_t)t;
+}
+
+static int popc32(uint32_t x) { return __builtin_popcount(x); }
+
+static int census_cv(const uint32_t* cl, const uint32_t* cr, int h, int wl, int wr, int nw, int D, int dir, uint16_t* out) {
+	const uint32_t* src = dir == DIR_R2L ? cr : cl; int ws = dir == DIR_R2L ? wr : wl;
+	const uint32_t* tgt = dir == DIR_R2L ? cl : cr; int wt = dir == DIR_R2L ? wl : wr;
+	int sgn = dir == DIR_R2L ? 1 : -1;
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) for (int j = 0; j < ws; j++) for (int d = 0; d < D; d++) {
+		int jt = j + sgn * d;
+		uint16_t acc = 0; /* hamming_cv_t, matching_costs.h:234,252-263 */
+		for (int n = 0; n < nw; n++) {
+			uint32_t t = (jt >= 0 && jt < wt) ? orc_round_through_float(tgt[((size_t)i * wt + jt) * nw + n]) : 0u;
+			acc = (uint16_t)(acc + popc32(src[((size_t)i * ws + j) * nw + n] ^ t));
+		}
+		out[((size_t)i * ws + j) * D + d] = acc;
+	}
+	return 0;
+}
+
+/* unfoldBasedCostVolume<CENSUS, uint8/float images, hamming_cv_t> */
+int orc_census_cost_volume_u8(const uint8_t* l, const uint8_t* r, int h, int wl, int wr,
+							  int hr, int vr, int D, int dir, uint16_t* out) {
+	int nw = orc_census_nwords(hr, vr);
+	uint32_t* cl = (uint32_t*)malloc((size_t)h * wl * nw * 4);
+	uint32_t* cr = (uint32_t*)malloc((size_t)h * wr * nw * 4);
+	orc_census_u8(l, h, wl, hr, vr, cl);
+	orc_census_u8(r, h, wr, hr, vr, cr);
+	census_cv(cl, cr, h, wl, wr, nw, D, dir, out);
+	free(cl); free(cr);
+	return 0;
+}
+int orc_census_cost_volume_f32(const float* l, const float* r, int h, int wl, int wr,
+							   int hr, int vr, int D, int dir, uint16_t* out) {
+	int nw = orc_census_nwords(hr, vr);
+	uint32_t* cl = (uint32_t*)malloc((size_t)h * wl * nw * 4);
+	uint32_t* cr = (uint32_t*)malloc((size_t)h * wr * nw * 4);
+	orc_census_f32(l, h, wl, hr, vr, cl);
+	orc_census_f32(r, h, wr, hr, vr, cr);
+	census_cv(cl, cr, h, wl, wr, nw, D, dir, out);
+	free(cl); free(cr);
+	return 0;
+}
+
+/* ---- sgm.h:57-155 direction traits: {stepsVertical[2], stepsHorizontal[2]} alternating with the step parity */
+static const int SGM_STEPS[16][4] = {
+	/* Up2Down */ {1, 1, 0, 0}, /* Down2Up */ {-1, -1, 0, 0}, /* Left2Right */ {0, 0, 1, 1}, /* Right2Left */ {0, 0, -1, -1},
+	/* UpLeft2DownRight */ {1, 1, 1, 1}, /* DownRight2UpLeft */ {-1, -1, -1, -1},
+	/* UpRight2DownLeft */ {1, 1, -1, -1}, /* DownLeft2UpRight */ {-1, -1, 1, 1},
+	/* UpLeft2Right */ {0, 1, 1, 1}, /* DownRight2Left */ {0, -1, -1, -1}, /* UpRight2Left */ {0, 1, -1, -1}, /* DownLeft2Right */ {0, -1, 1, 1},
+	/* UpLeft2Down */ {1, 1, 0, 1}, /* DownRight2Up */ {-1, -1, 0, -1}, /* UpRight2Down */ {1, 1, 0, -1}, /* DownLeft2Up */ {-1, -1, 0, 1}};
+/* call order of sgmCostVolume, sgm.h:379-401 */
+static const int SGM_ORDER[16] = {0, 1, 2, 3, 4, 5, 6, 7, 12, 13, 14, 15, 8, 9, 10, 11};
+
+/* sgm.h:186-311 traverseLine. cv (h,w,D) C-order float; sgm (h,w,D) accumulated in place.
+ * The reference's inner O(D^2) loop over od is restated in O(D): subtracting/adding a constant is monotone in
+ * IEEE arithmetic, so max_od (p[od] - P) == (max_od p[od]) - P exactly. Non-finite previous scores are skipped
+ * (`std::isfinite(p_score)` tests at :224,:243,:264,:281). */
+static void sgm_traverse_line(int dirIdx, int strategy, int si, int sj, const float* cv, float* sgm,
+							  int h, int w, int D, float P1, float P2, float Pout, const int* mg) {
+	int left = mg[0], top = mg[1], right = mg[2], bottom = mg[3];
+	const int* st = SGM_STEPS[dirIdx];
+	float* prev = (float*)calloc((size_t)D, sizeof(float));
+	float* act = (float*)malloc((size_t)D * sizeof(float));
+	float* pre = (float*)malloc((size_t)(D + 2) * sizeof(float)); /* prefix extremum over finite p[0..k] */
+	float* suf = (float*)malloc((size_t)(D + 2) * sizeof(float)); /* suffix extremum over finite p[k..D-1] */
+	int c = 0;
+	for (int i = si, j = sj; (i >= top && i < h - bottom) && (j >= left && j < w - right); i += st[c % 2], j += st[2 + c % 2], c++) {
+		const float* cc = cv + ((size_t)i * w + j) * D;
+		if (strategy == STRAT_SCORE) {
+			float max_p = -INFINITY;
+			for (int d = 0; d < D; d++) if (prev[d] > max_p && isfinite(prev[d])) max_p = prev[d];
+			float run = -INFINITY;
+			for (int d = 0; d < D; d++) { if (isfinite(prev[d]) && prev[d] > run) run = prev[d]; pre[d] = run; }
+			run = -INFINITY;
+			for (int d = D - 1; d >= 0; d--) { if (isfinite(prev[d]) && prev[d] > run) run = prev[d]; suf[d] = run; }
+			for (int nd = 0; nd < D; nd++) {
+				float m = -INFINITY, t;
+				/* candidates in the order the reference meets them: od < nd-1 (P2), nd-1 (P1), nd, nd+1 (P1), od > nd+1 (P2) */
+				if (nd - 2 >= 0) { t = pre[nd - 2] - P2; if (t > m && isfinite(t)) m = t; }
+				if (nd - 1 >= 0) { t = prev[nd - 1] - P1; if (t > m && isfinite(t)) m = t; }
+				t = prev[nd]; if (t > m && isfinite(t)) m = t;
+				if (nd + 1 < D) { t = prev[nd + 1] - P1; if (t > m && isfinite(t)) m = t; }
+				if (nd + 2 < D) { t = suf[nd + 2] - P2; if (t > m && isfinite(t)) m = t; }
+				if (j + nd >= w) m -= Pout;
+				act[nd] = cc[nd];
+				if (isfinite(m) && isfinite(max_p)) act[nd] += m - max_p;
+			}
+		} else {
+			float min_p = INFINITY;
+			for (int d = 0; d < D; d++) if (prev[d] < min_p && isfinite(prev[d])) min_p = prev[d];
+			/* Q3 (sgm.h:281-283): the Cost branch assigns min_a_cost = c_score (not p_score) as soon as one
+			 * penalised previous score is finite and below the running value. */
+			int any_finite = 0; /* p_score + P is finite iff p_score is (P1, P2 finite) */
+			for (int od = 0; od < D; od++) if (isfinite(prev[od])) any_finite = 1;
+			for (int nd = 0; nd < D; nd++) {
+				float c_score = cc[nd];
+				/* the od loop can only ever store c_score: the first finite penalised score is < +inf, and
+				 * any later successful test stores c_score again */
+				float min_a = any_finite ? c_score : INFINITY;
+				if (j + nd >= w) min_a += Pout;
+				act[nd] = c_score;
+				if (isfinite(min_a) && isfinite(min_p)) act[nd] += min_a - min_p;
+			}
+		}
+		float* s = sgm + ((size_t)i * w + j) * D;
+		for (int d = 0; d < D; d++) s[d] += act[d] - cc[d];
+		float* tmp = prev; prev = act; act = tmp;
+	}
+	free(prev); free(act); free(pre); free(suf);
+}
+
+/* sgm.h:162-184 + :313-356: start edges. 0 = NoStart, 1 = ZeroPos, 2 = EndPos. */
+static int sgm_start_pos(int s0, int s1) {
+	if (s0 == 0 && s1 == 0) return 0;
+	if (s0 >= 0 && s1 >= 0) return 1;
+	return 2;
+}
+
+static void sgm_add_direction(int dirIdx, int strategy, const float* cv, float* sgm, int h, int w, int D,
+							  float P1, float P2, float Pout, const int* mg) {
+	int left = mg[0], top = mg[1], right = mg[2], bottom = mg[3];
+	const int* st = SGM_STEPS[dirIdx];
+	int colStart = sgm_start_pos(st[0], st[1]); /* from stepsVertical */
+	int rowStart = sgm_start_pos(st[2], st[3]); /* from stepsHorizontal */
+	if (rowStart != 0) { /* lines starting on the left (or, Q4, one past the right) column: sgm.h:329-341 */
+		int sj = (rowStart == 1) ? left : w - right;
+		#pragma omp parallel for
+		for (int si = top; si < h - bottom; si++)
+			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg);
+	}
+	if (colStart != 0) { /* lines starting on the top (or, Q4, one past the bottom) row: sgm.h:343-354 */
+		int si = (colStart == 1) ? top : h - bottom;
+		#pragma omp parallel for
+		for (int sj = left; sj < w - right; sj++)
+			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg);
+	}
+}
+
+/* sgm.h:360-404. margins = {left, top, right, bottom} (utils/margins.h:52). out (h,w,D) float. */
+int orc_sgm_f32(const float* cv, int h, int w, int D, int ndir, int strategy,
+				float P1, float P2, float Pout, const int* margins, float* out) {
+	if (ndir != 4 && ndir != 8 && ndir != 16) return 2;
+	memcpy(out, cv, (size_t)h * w * D * sizeof(float));
+	for (int k = 0; k < ndir; k++)
+		sgm_add_direction(SGM_ORDER[k], strategy, cv, out, h, w, D, P1, P2, Pout, margins);
+	return 0;
+}
+int orc_sgm_u16(const uint16_t* cv, int h, int w, int D, int ndir, int strategy,
+				float P1, float P2, float Pout, const int* margins, float* out) {
+	size_t n = (size_t)h * w * D;
+	float* f = (float*)malloc(n * sizeof(float)); /* static_cast<float>(cv_base.value(...)), sgm.h:233,272 */
+	for (size_t k = 0; k < n; k++) f[k] = (float)cv[k];
+	int r = orc_sgm_f32(f, h, w, D, ndir, strategy, P1, P2, Pout, margins, out);
+	free(f);
+	return r;
+}
+
+/* ---- correlation_base.h:427-464 WTA: `<=` / `>=` so the LAST extremum wins (Q5) */
+#define DEF_WTA(NAME, T) \
+int NAME(const T* v, int h, int w, int D, int strategy, int32_t* out) { \
+	for (size_t p = 0; p < (size_t)h * w; p++) { \
+		const T* c = v + p * D; \
+		T best = c[0]; int32_t bd = 0; \
+		for (int d = 1; d < D; d++) { \
+			if (strategy == STRAT_COST) { if (c[d] <= best) { best = c[d]; bd = d; } } \
+			else { if (c[d] >= best) { best = c[d]; bd = d; } } \
+		} \
+		out[p] = bd; \
+	} \
+	return 0; \
+}
+DEF_WTA(orc_wta_f32, float)
+DEF_WTA(orc_wta_u16, uint16_t)
+
+/* correlation_base.h:511-532 */
+int orc_index_to_disp(const int32_t* idx, int h, int w, int dir, int offset, int32_t* out) {
+	int sgn = dir == DIR_R2L ? 1 : -1;
+	for (size_t p = 0; p < (size_t)h * w; p++) out[p] = sgn * idx[p] + offset;
+	return 0;
+}
+
+/* correlation_base.h:557-577 */
+int orc_selected_cost_f32(const float* cv, const int32_t* idx, int h, int w, int D, float* out) {
+	for (size_t p = 0; p < (size_t)h * w; p++) out[p] = cv[p * D + (uint32_t)idx[p]];
+	return 0;
+}
+
+/* correlation_base.h:579-674. tdir: 0 Same, 1 Reversed, 2 Both. out (h,w,2r+1) or (h,w,4r+1) for Both. */
+int orc_truncated_cost_volume_f32(const float* cv, const int32_t* idx, int h, int w, int D,
+								  int hr, int vr, int r, int dir, int tdir, float* out) {
+	int T = tdir == 2 ? 4 * r + 1 : 2 * r + 1;
+	int sgn = dir == DIR_R2L ? -1 : 1;
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		float* o = out + ((size_t)i * w + j) * T;
+		int vbad = (i < vr) || (i + vr >= h);
+		for (int d = 0; d <= 2 * r; d++) {
+			int p = idx[(size_t)i * w + j] + d - r;
+			int jp = j + sgn * (d - r);
+			int pbad = (p < 0) || (p >= D);
+			int same_bad = pbad || j < hr || j + p + hr >= w || vbad;
+			if (tdir == 0) {
+				o[d] = same_bad ? nanf("") : cv[((size_t)i * w + j) * D + p];
+			} else if (tdir == 1) {
+				int lo = jp < j ? jp : j, hi = jp > j ? jp : j;
+				int bad = pbad || lo < hr || hi + hr >= w || vbad;
+				o[d] = bad ? nanf("") : cv[((size_t)i * w + jp) * D + p];
+			} else {
+				int d_d = 2 * d, d_r = 2 * d + 1;
+				if (d == r) jp = -1;
+				if (d > r) { d_d -= 1; d_r -= 1; }
+				int lo = jp < j ? jp : j, hi = jp > j ? jp : j;
+				int rbad = pbad || lo < hr || hi + hr >= w || vbad;
+				o[d_d] = same_bad ? nanf("") : cv[((size_t)i * w + j) * D + p];
+				o[d_r] = rbad ? nanf("") : cv[((size_t)i * w + jp) * D + p];
+			}
+		}
+	}
+	return 0;
+}
+
+/* cost_based_refinement.h:43-69 */
+float orc_refine_cost_triplet(int kernel, float cm1, float c0, float c1) {
+	if (kernel == K_EQUIANGULAR) {
+		float alpha = copysignf(1.f, c0 - cm1);
+		alpha *= fmaxf(fabsf(c0 - cm1), fabsf(c1 - c0));
+		return (c1 - cm1) / (2 * alpha);
+	} else if (kernel == K_PARABOLA) {
+		return (cm1 - c1) / (2 * (c1 - 2 * c0 + cm1));
+	}
+	return (logf(cm1) - logf(c1)) / (2 * (logf(c1) - 2 * logf(c0) + logf(cm1)));
+}
+
+/* cost_based_refinement.h:128-163. Returns 1 (reference: empty array) if the depth is even or < 3. */
+int orc_refine_disp_cost_interp(const float* tcv, const int32_t* idx, int h, int w, int T, int kernel, float* out) {
+	int r = (T - 1) / 2;
+	if (r < 1 || 2 * r + 1 != T) return 1;
+	for (size_t p = 0; p < (size_t)h * w; p++) {
+		const float* c = tcv + p * T;
+		out[p] = (float)idx[p] + orc_refine_cost_triplet(kernel, c[r - 1], c[r], c[r + 1]);
+	}
+	return 0;
+}
+
+/* interpolation/downsampling.h:67-118 with DownSampleWindows(2): out (ceil(h/2), ceil(w/2)); the mean is over
+ * the in-image part of each 2x2 window (offsets are 0 for window 2: hRem/2 == 0). Accumulates in float, in
+ * row-major window order, then divides by the count. */
+int orc_avgpool2_f32(const float* img, int h, int w, float* out) {
+	int nh = (h + 1) / 2, nw = (w + 1) / 2;
+	for (int i = 0; i < nh; i++) for (int j = 0; j < nw; j++) {
+		float val = 0.f; int count = 0;
+		for (int dv = 0; dv < 2; dv++) for (int dh = 0; dh < 2; dh++) {
+			int pi = 2 * i + dv, pj = 2 * j + dh;
+			if (pi < h && pj < w) { val += img[(size_t)pi * w + pj]; count++; }
+		}
+		val /= count;
+		out[(size_t)i * nw + j] = val;
+	}
+	return 0;
+}
+
+/* ---- hierarchical.h:73-233 computeGuidedCV on float feature volumes (h,w,F) (source width ws, target width wt).
+ * guide is (hg, wg) int32. tcv (h, ws, 2r+1) C-order; disp (h, ws). */
+static void guided_cv(int mf, const float* fl, const float* fr, int h, int wl, int wr, int F,
+					  const int32_t* guide, int hg, int wg, int r, int dir, float* tcv, int32_t* disp) {
+	const float* src = dir == DIR_R2L ? fr : fl; int ws = dir == DIR_R2L ? wr : wl;
+	const float* tgt = dir == DIR_R2L ? fl : fr; int wt = dir == DIR_R2L ? wl : wr;
+	int dirSign = dir == DIR_R2L ? 1 : -1;
+	int T = 2 * r + 1;
+	int cost = mf_strategy(mf) == STRAT_COST;
+	float* zero = (float*)calloc((size_t)F, sizeof(float));
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) {
+		float v_pos = (float)(i * (hg - 1)) / (h - 1); /* Q7: int product, then float division (:116) */
+		int v0 = (int)floorf(v_pos), v1 = (int)ceilf(v_pos);
+		if (v0 == v1) v1 += 1;
+		if (v1 == hg) { v0 -= 1; v1 -= 1; }
+		for (int j = 0; j < ws; j++) {
+			float h_pos = (float)(j * (wg - 1)) / (ws - 1);
+			int h0 = (int)floorf(h_pos), h1 = (int)ceilf(h_pos);
+			if (h0 == h1) h1 += 1;
+			if (h1 == wg) { h0 -= 1; h1 -= 1; }
+			float id = 0.f;
+			id += (v_pos - v0) * (h_pos - h0) * guide[(size_t)v1 * wg + h1];
+			id += (v1 - v_pos) * (h_pos - h0) * guide[(size_t)v0 * wg + h1];
+			id += (v_pos - v0) * (h1 - h_pos) * guide[(size_t)v1 * wg + h0];
+			id += (v1 - v_pos) * (h1 - h_pos) * guide[(size_t)v0 * wg + h0];
+			id *= 2;
+			int d0 = dirSign * (int)roundf(id);
+			const float* s = src + ((size_t)i * ws + j) * F;
+			float* o = tcv + ((size_t)i * ws + j) * T;
+			float score = cost ? INFINITY : -INFINITY;
+			int d_r = d0;
+			for (int dd = -r; dd <= r; dd++) {
+				int jt = j + d0 + dd;
+				const float* t = (jt >= 0 && jt < wt) ? tgt + ((size_t)i * wt + jt) * F : zero;
+				float cmp = compare_f32(mf, s, t, F);
+				if (cost) { if (cmp < score) { score = cmp; d_r = d0 + dd; } } /* strict: FIRST extremum wins (:179,:184) */
+				else { if (cmp > score) { score = cmp; d_r = d0 + dd; } }
+			}
+			disp[(size_t)i * ws + j] = dirSign * d_r;
+			/* after the reference's shift-and-refill (:194-226) cell dd always holds the comparison against
+			 * target column j + d_r + dirSign*(dd - r); each cell is a pure function of the inputs */
+			for (int dd = 0; dd < T; dd++) {
+				int jt = j + d_r + dirSign * (dd - r);
+				const float* t = (jt >= 0 && jt < wt) ? tgt + ((size_t)i * wt + jt) * F : zero;
+				o[dd] = compare_f32(mf, s, t, F);
+			}
+		}
+	}
+	free(zero);
+}
+
+int orc_guided_cv_f32(int mf, const float* l, const float* r, int h, int wl, int wr, int hr, int vr,
+					  const int32_t* guide, int hg, int wg, int radius, int dir, float* tcv, int32_t* disp) {
+	int F = (2 * hr + 1) * (2 * vr + 1);
+	float* fl = (float*)malloc((size_t)h * wl * F * sizeof(float));
+	float* fr = (float*)malloc((size_t)h * wr * F * sizeof(float));
+	orc_feature_volume_f32(mf, l, h, wl, hr, vr, fl);
+	orc_feature_volume_f32(mf, r, h, wr, hr, vr, fr);
+	guided_cv(mf, fl, fr, h, wl, wr, F, guide, hg, wg, radius, dir, tcv, disp);
+	free(fl); free(fr);
+	return 0;
+}
+
+/* ---- hierarchical.h:235-314 (same radii at every level). tcv (h,w,2*radius+1), disp (h,w) at full resolution. */
+static int hier_level(int mf, int depth, const float* l, const float* r, int h, int w, int hr, int vr, int D,
+					  int radius, int dir, float* tcv, int32_t* disp) {
+	int nh = (h + 1) / 2, nw = (w + 1) / 2;
+	float* dl = (float*)malloc((size_t)nh * nw * sizeof(float));
+	float* dr = (float*)malloc((size_t)nh * nw * sizeof(float));
+	int32_t* guide = (int32_t*)malloc((size_t)nh * nw * sizeof(int32_t));
+	orc_avgpool2_f32(l, h, w, dl);
+	orc_avgpool2_f32(r, h, w, dr);
+	int Dn = (D + 1) / 2;
+	if (depth == 1) {
+		float* cv = (float*)malloc((size_t)nh * nw * Dn * sizeof(float));
+		orc_cost_volume_f32(mf, dl, dr, nh, nw, nw, hr, vr, Dn, dir, cv);
+		orc_wta_f32(cv, nh, nw, Dn, mf_strategy(mf), guide);
+		free(cv);
+	} else {
+		float* ptcv = (float*)malloc((size_t)nh * nw * (2 * radius + 1) * sizeof(float));
+		hier_level(mf, depth - 1, dl, dr, nh, nw, hr, vr, Dn, radius, dir, ptcv, guide);
+		free(ptcv);
+	}
+	orc_guided_cv_f32(mf, l, r, h, w, w, hr, vr, guide, nh, nw, radius, dir, tcv, disp);
+	free(dl); free(dr); free(guide);
+	return 0;
+}
+
+int orc_hierarchical_f32(int mf, int depth, const float* l, const float* r, int h, int w,
+						 int hr, int vr, int D, int radius, int dir, float* tcv, int32_t* disp) {
+	if (depth < 1) return 2;
+	return hier_level(mf, depth, l, r, h, w, hr, vr, D, radius, dir, tcv, disp);
+}
