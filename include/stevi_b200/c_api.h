@@ -1,0 +1,150 @@
+/* stevi_b200 — C ABI of the B200-native (sm_100a) dense-stereo hot path of LibStevi.
+ *
+ * This is the drop-in boundary: plain pointers, sizes, enums as int32 — no C++ or torch types. The reference has
+ * no FFI of its own (it is a header-only template library); each entry point below names the
+ * reference template it stands in for (file:line relative to the LibStevi tree). The C++ facade under
+ * include/StereoVision/ re-creates those templates over Multidim::Array and forwards to these functions.
+ *
+ * Conventions
+ *  - every function returns a stevi_status (0 = OK); stevi_last_error(ctx) has the text of the last failure;
+ *  - arrays are described by stevi_array: element strides (not bytes), any order; `mem` says whether `data` is a
+ *    host or a device pointer. Host operands are staged through the ctx workspace (H2D before, D2H after, the
+ *    call returns when the results are in host memory). Device operands are used in place and the call is
+ *    asynchronous on the ctx stream;
+ *  - the library never allocates caller-visible memory: outputs are pre-shaped by the caller;
+ *  - there is NO CPU fallback: without a usable CUDA device stevi_ctx_create fails with STEVI_E_CUDA.
+ *  - `semantics`: STEVI_COMPAT reproduces the reference bit for bit including its quirks,
+ *    STEVI_CORRECTED applies the one-line fixes listed there.
+ */
+#ifndef STEVI_B200_C_API_H
+#define STEVI_B200_C_API_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STEVI_MAX_DIMS 4
+
+typedef enum {
+	STEVI_OK = 0,
+	STEVI_E_SHAPE = 1,       /* the reference returns an empty array in these cases */
+	STEVI_E_DTYPE = 2,
+	STEVI_E_UNSUPPORTED = 3,
+	STEVI_E_CUDA = 4,
+	STEVI_E_NCCL = 5,
+	STEVI_E_ARG = 6
+} stevi_status;
+
+typedef enum { STEVI_U8 = 0, STEVI_U16 = 1, STEVI_I32 = 2, STEVI_U32 = 3, STEVI_F32 = 4 } stevi_dtype;
+typedef enum { STEVI_HOST = 0, STEVI_DEVICE = 1 } stevi_mem;
+typedef enum { STEVI_COMPAT = 0, STEVI_CORRECTED = 1 } stevi_semantics;
+
+/* mirrors StereoVision::Correlation::matchingFunctions, correlation/matching_costs.h:38-53 */
+typedef enum {
+	STEVI_MF_CC = 0, STEVI_MF_NCC = 1, STEVI_MF_SSD = 2, STEVI_MF_SAD = 3, STEVI_MF_ZCC = 4, STEVI_MF_ZNCC = 5,
+	STEVI_MF_ZSSD = 6, STEVI_MF_ZSAD = 7, STEVI_MF_MEDAD = 8, STEVI_MF_ZMEDAD = 9, STEVI_MF_HAMMING = 10,
+	STEVI_MF_CENSUS = 11, STEVI_MF_KERMI = 12
+} stevi_matchfunc;
+/* dispExtractionStartegy (sic), dispDirection, truncatedCostVolumeDirection: correlation/correlation_base.h:31-45 */
+typedef enum { STEVI_COST = 0, STEVI_SCORE = 1 } stevi_strategy;
+typedef enum { STEVI_LEFT_TO_RIGHT = 0, STEVI_RIGHT_TO_LEFT = 1 } stevi_direction;
+typedef enum { STEVI_TCV_SAME = 0, STEVI_TCV_REVERSED = 1, STEVI_TCV_BOTH = 2 } stevi_tcv_direction;
+/* InterpolationKernel: correlation/cost_based_refinement.h:30-35 */
+typedef enum { STEVI_EQUIANGULAR = 0, STEVI_PARABOLA = 1, STEVI_GAUSSIAN = 2 } stevi_interp_kernel;
+
+typedef struct {
+	void* data;
+	int32_t dtype;                    /* stevi_dtype */
+	int32_t ndim;
+	int32_t shape[STEVI_MAX_DIMS];
+	int64_t strides[STEVI_MAX_DIMS];  /* in elements */
+	int32_t mem;                      /* stevi_mem */
+} stevi_array;
+
+/* StereoVision::Margins(left, top, right, bottom), utils/margins.h:24-60 */
+typedef struct { int32_t left, top, right, bottom; } stevi_margins;
+
+typedef struct stevi_ctx stevi_ctx;
+
+/* ---- context: one per host thread / CUDA stream (the reference's functions are stateless and re-entrant; the
+ * ctx only owns the device id, the stream and a grow-only device workspace). `stream` is a cudaStream_t or NULL
+ * to let the ctx create its own non-blocking stream. */
+int32_t stevi_ctx_create(int32_t device, void* stream, stevi_ctx** out);
+int32_t stevi_ctx_destroy(stevi_ctx* ctx);
+int32_t stevi_ctx_set_stream(stevi_ctx* ctx, void* stream);
+void* stevi_ctx_stream(stevi_ctx* ctx);
+int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
+const char* stevi_last_error(stevi_ctx* ctx);
+/* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */
+int64_t stevi_ctx_launch_count(stevi_ctx* ctx);
+/* bytes currently held by the workspace arena */
+int64_t stevi_ctx_workspace_bytes(stevi_ctx* ctx);
+int32_t stevi_device_count(void);
+const char* stevi_version(void);
+
+/* pinned host memory for callers that want DMA-speed staging of host operands */
+int32_t stevi_host_alloc(size_t bytes, void** out);
+int32_t stevi_host_free(void* p);
+
+/* ---- features ------------------------------------------------------------------------------------------- */
+
+/* censusTransform2D (correlation/census.h:117-131) = unfold (unfold.h:248-291) + censusFeatures (census.h:69-115).
+ * img (H,W) u8|f32  ->  out (H,W,nwords) u32, nwords = (F-1)/32+1, F=(2*h_radius+1)*(2*v_radius+1).
+ * COMPAT: only completely filled 32-bit words are written, the trailing word is 0 (Q1). */
+int32_t stevi_census_transform(stevi_ctx* ctx, const stevi_array* img, int32_t h_radius, int32_t v_radius,
+							   int32_t semantics, stevi_array* out);
+
+/* ---- cost volumes ---------------------------------------------------------------------------------------- */
+
+/* unfoldBasedCostVolume<matchFunc, T_L, T_R, 2, dDir, TCV> (correlation/cross_correlations.h:740-765).
+ * img_l (H,Wl), img_r (H,Wr): u8|f32 (same dtype). out (H, Wsource, D) of dtype TCV, Wsource = Wr for
+ * RIGHT_TO_LEFT, Wl for LEFT_TO_RIGHT. CENSUS: out u16|i32|f32 (hamming_cv_t = u16, matching_costs.h:234).
+ * The reference lays the volume out as strides {W*D, 1, W} (cross_correlations.h:220); any strides are accepted.
+ * Returns STEVI_E_SHAPE where the reference returns an empty array (heights differ, :751). */
+int32_t stevi_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+						  int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction,
+						  int32_t semantics, stevi_array* out);
+
+/* aggregateCost<HAMMING|CENSUS> on ready-made census/binary features (correlation/cross_correlations.h:194-249):
+ * feat_l (H,Wl,nw) u32, feat_r (H,Wr,nw) u32 -> out (H,Wsource,D). COMPAT rounds every target word through
+ * float (Q2, :235-236). */
+int32_t stevi_hamming_cost_volume(stevi_ctx* ctx, const stevi_array* feat_l, const stevi_array* feat_r,
+								  int32_t disp_width, int32_t direction, int32_t semantics, stevi_array* out);
+
+/* ---- semi-global matching -------------------------------------------------------------------------------- */
+
+/* sgmCostVolume<nDirections, strategy, T_CV> (correlation/sgm.h:360-404). cv (H,W,D) u16|f32 -> out (H,W,D) f32.
+ * n_directions in {4,8,16}. COMPAT reproduces Q3 (Cost mode ignores P1/P2) and Q4 (dead / half-run / doubled
+ * directions); CORRECTED is the textbook recurrence over all directions. */
+int32_t stevi_sgm(stevi_ctx* ctx, const stevi_array* cv, int32_t n_directions, int32_t strategy,
+				  float P1, float P2, float Pout, const stevi_margins* margins, int32_t semantics, stevi_array* out);
+
+/* ---- winner-take-all and friends -------------------------------------------------------------------------- */
+
+/* extractSelectedIndex<strategy, T_CV> (correlation/correlation_base.h:427-464): vol (H,W,D) u16|i32|f32 ->
+ * out (H,W) i32. `<=` / `>=`: the LAST extremum wins (Q5); a NaN at d=0 sticks. */
+int32_t stevi_wta(stevi_ctx* ctx, const stevi_array* vol, int32_t strategy, stevi_array* out);
+
+/* selectedIndexToDisp<disp_t, dDir> (correlation/correlation_base.h:511-532): disp = +-idx + offset */
+int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, int32_t direction, int32_t offset,
+							stevi_array* out);
+
+/* ---- fused device-resident pipeline ------------------------------------------------------------------------ */
+
+/* census cost volume -> SGM -> WTA -> disparity in one call, the sequence of
+ * test/benchmarks/benchmarkCrossCorrelationAlgorithms.cpp:289-293 with matchFunc = CENSUS and strategy = Cost.
+ * img_l, img_r (H,W) u8|f32; disp (H,W) i32 (required). cv_out (H,W,D) u16 and sgm_out (H,W,D) f32 are optional
+ * (NULL = keep the volume in the ctx workspace / do not materialise it at all when the semantics allow).
+ * Results are bit-identical to calling stevi_cost_volume, stevi_sgm, stevi_wta, stevi_index_to_disp in turn. */
+int32_t stevi_census_sgm_pipeline(stevi_ctx* ctx, const stevi_array* img_l, const stevi_array* img_r,
+								  int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction,
+								  int32_t n_directions, float P1, float P2, float Pout, const stevi_margins* margins,
+								  int32_t semantics, stevi_array* cv_out, stevi_array* sgm_out, stevi_array* disp);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,112 @@
+// Internal plumbing shared by the kernels' host wrappers: context, workspace arena, host-operand staging,
+// launch bookkeeping. Nothing in here touches the CPU oracle; there is no CPU fallback anywhere in csrc/.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdarg>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "../../include/stevi_b200/c_api.h"
+
+struct stevi_ctx {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	bool own_stream = false;
+	std::string err;
+	int64_t launches = 0;
+	int sm_count = 148;
+	// grow-only bump arena; reset at the start of every API call (coalesced into one block when it had to grow)
+	struct Block { char* p; size_t cap; };
+	std::vector<Block> blocks;
+	size_t cur = 0;   // index of the block being bumped
+	size_t off = 0;   // offset inside it
+	size_t high = 0;  // bytes handed out during the current call
+};
+
+namespace stevi {
+
+inline int32_t fail(stevi_ctx* c, int32_t code, const char* fmt, ...) {
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof buf, fmt, ap);
+	va_end(ap);
+	if (c) c->err = buf;
+	return code;
+}
+
+#define STEVI_CUDA(c, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) \
+	return stevi::fail((c), STEVI_E_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); } while (0)
+
+#define STEVI_TRY(expr) do { int32_t s__ = (expr); if (s__ != STEVI_OK) return s__; } while (0)
+
+// kernel<<<grid, block, smem, ctx->stream>>>(args...) with launch counting and error check
+#define STEVI_LAUNCH(c, kern, grid, block, smem, ...) do { \
+	kern<<<(grid), (block), (smem), (c)->stream>>>(__VA_ARGS__); \
+	(c)->launches++; \
+	STEVI_CUDA((c), cudaPeekAtLastError()); } while (0)
+
+inline size_t dtype_size(int dt) {
+	switch (dt) {
+	case STEVI_U8: return 1;
+	case STEVI_U16: return 2;
+	case STEVI_I32: case STEVI_U32: case STEVI_F32: return 4;
+	default: return 0;
+	}
+}
+
+// ---- arena ---------------------------------------------------------------------------------------------------
+int32_t arena_reset(stevi_ctx* c);
+int32_t arena_alloc(stevi_ctx* c, size_t bytes, void** out);
+template<typename T> inline int32_t arena_alloc_t(stevi_ctx* c, size_t n, T** out) {
+	void* p = nullptr;
+	int32_t s = arena_alloc(c, n * sizeof(T), &p);
+	*out = static_cast<T*>(p);
+	return s;
+}
+
+// ---- device view of an operand ----------------------------------------------------------------------------------
+struct View {
+	void* p = nullptr;
+	int dtype = 0, ndim = 0;
+	int shape[STEVI_MAX_DIMS] = {0, 0, 0, 0};
+	int64_t st[STEVI_MAX_DIMS] = {0, 0, 0, 0};
+	template<typename T> T* as() const { return static_cast<T*>(p); }
+	size_t count() const { size_t n = 1; for (int k = 0; k < ndim; k++) n *= (size_t)shape[k]; return n; }
+	size_t span() const { // elements between the first and one past the last addressed element
+		size_t s = 1;
+		for (int k = 0; k < ndim; k++) { if (shape[k] == 0) return 0; s += (size_t)(shape[k] - 1) * (size_t)st[k]; }
+		return s;
+	}
+	bool dense() const { return span() == count(); }
+};
+
+// Brings host operands to the device for the duration of one API call and results back at the end.
+class Stager {
+public:
+	explicit Stager(stevi_ctx* c) : c_(c) {}
+	int32_t in(const stevi_array* a, View& v, const char* name);
+	int32_t out(const stevi_array* a, View& v, const char* name);
+	// issues the D2H copies; synchronises the stream when any operand lived in host memory
+	int32_t finish();
+private:
+	int32_t check(const stevi_array* a, const char* name);
+	struct Back { void* host; void* dev; size_t bytes; };
+	stevi_ctx* c_;
+	std::vector<Back> back_;
+	bool any_host_ = false;
+};
+
+inline int32_t begin_call(stevi_ctx* c) {
+	if (!c) return STEVI_E_ARG;
+	cudaError_t e = cudaSetDevice(c->device);
+	if (e != cudaSuccess) return fail(c, STEVI_E_CUDA, "cudaSetDevice(%d): %s", c->device, cudaGetErrorString(e));
+	return arena_reset(c);
+}
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+} // namespace stevi

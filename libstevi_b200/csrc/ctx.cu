@@ -1,0 +1,188 @@
+// Context, workspace arena and host-operand staging for the C ABI (include/stevi_b200/c_api.h).
+#include "common.cuh"
+
+namespace stevi {
+
+static const size_t ARENA_ALIGN = 256;
+
+int32_t arena_reset(stevi_ctx* c) {
+	if (c->blocks.size() > 1) {
+		// the previous call outgrew the arena: replace the pieces by one block that fits all of it
+		size_t total = 0;
+		for (auto& b : c->blocks) total += b.cap;
+		STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+		for (auto& b : c->blocks) cudaFree(b.p);
+		c->blocks.clear();
+		char* p = nullptr;
+		STEVI_CUDA(c, cudaMalloc(&p, total));
+		c->blocks.push_back({p, total});
+	}
+	c->cur = 0;
+	c->off = 0;
+	c->high = 0;
+	return STEVI_OK;
+}
+
+int32_t arena_alloc(stevi_ctx* c, size_t bytes, void** out) {
+	bytes = (bytes + ARENA_ALIGN - 1) / ARENA_ALIGN * ARENA_ALIGN;
+	if (bytes == 0) bytes = ARENA_ALIGN;
+	while (c->cur < c->blocks.size()) {
+		auto& b = c->blocks[c->cur];
+		if (c->off + bytes <= b.cap) {
+			*out = b.p + c->off;
+			c->off += bytes;
+			c->high += bytes;
+			return STEVI_OK;
+		}
+		c->cur++;
+		c->off = 0;
+	}
+	size_t cap = std::max(bytes, (size_t)(64u << 20));
+	char* p = nullptr;
+	STEVI_CUDA(c, cudaMalloc(&p, cap));
+	c->blocks.push_back({p, cap});
+	c->cur = c->blocks.size() - 1;
+	c->off = bytes;
+	c->high += bytes;
+	*out = p;
+	return STEVI_OK;
+}
+
+int32_t Stager::check(const stevi_array* a, const char* name) {
+	if (!a || !a->data) return fail(c_, STEVI_E_ARG, "%s: null array", name);
+	if (a->ndim < 1 || a->ndim > STEVI_MAX_DIMS) return fail(c_, STEVI_E_ARG, "%s: ndim %d", name, a->ndim);
+	if (dtype_size(a->dtype) == 0) return fail(c_, STEVI_E_DTYPE, "%s: unknown dtype %d", name, a->dtype);
+	for (int k = 0; k < a->ndim; k++) {
+		if (a->shape[k] < 0) return fail(c_, STEVI_E_SHAPE, "%s: negative extent", name);
+		if (a->strides[k] < 0) return fail(c_, STEVI_E_UNSUPPORTED, "%s: negative strides are not supported", name);
+	}
+	return STEVI_OK;
+}
+
+static void fill_view(const stevi_array* a, View& v) {
+	v.p = a->data;
+	v.dtype = a->dtype;
+	v.ndim = a->ndim;
+	for (int k = 0; k < a->ndim; k++) { v.shape[k] = a->shape[k]; v.st[k] = a->strides[k]; }
+}
+
+int32_t Stager::in(const stevi_array* a, View& v, const char* name) {
+	STEVI_TRY(check(a, name));
+	fill_view(a, v);
+	if (a->mem == STEVI_DEVICE) return STEVI_OK;
+	any_host_ = true;
+	size_t bytes = v.span() * dtype_size(v.dtype);
+	void* d = nullptr;
+	STEVI_TRY(arena_alloc(c_, bytes, &d));
+	if (bytes) STEVI_CUDA(c_, cudaMemcpyAsync(d, a->data, bytes, cudaMemcpyHostToDevice, c_->stream));
+	v.p = d;
+	return STEVI_OK;
+}
+
+int32_t Stager::out(const stevi_array* a, View& v, const char* name) {
+	STEVI_TRY(check(a, name));
+	fill_view(a, v);
+	if (a->mem == STEVI_DEVICE) return STEVI_OK;
+	any_host_ = true;
+	size_t bytes = v.span() * dtype_size(v.dtype);
+	void* d = nullptr;
+	STEVI_TRY(arena_alloc(c_, bytes, &d));
+	// a strided result leaves gaps: carry the caller's bytes through so the copy back does not clobber them
+	if (bytes && !v.dense()) STEVI_CUDA(c_, cudaMemcpyAsync(d, a->data, bytes, cudaMemcpyHostToDevice, c_->stream));
+	v.p = d;
+	back_.push_back({a->data, d, bytes});
+	return STEVI_OK;
+}
+
+int32_t Stager::finish() {
+	for (auto& b : back_)
+		if (b.bytes) STEVI_CUDA(c_, cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, c_->stream));
+	back_.clear();
+	if (any_host_) STEVI_CUDA(c_, cudaStreamSynchronize(c_->stream));
+	return STEVI_OK;
+}
+
+} // namespace stevi
+
+using namespace stevi;
+
+extern "C" {
+
+const char* stevi_version(void) { return "stevi_b200 0.1 (sm_100a)"; }
+
+int32_t stevi_device_count(void) {
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+	return n;
+}
+
+int32_t stevi_ctx_create(int32_t device, void* stream, stevi_ctx** out) {
+	if (!out) return STEVI_E_ARG;
+	*out = nullptr;
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) { cudaGetLastError(); return STEVI_E_CUDA; } // no device: fail loudly, no fallback
+	if (device < 0 || device >= n) return STEVI_E_ARG;
+	if (cudaSetDevice(device) != cudaSuccess) return STEVI_E_CUDA;
+	stevi_ctx* c = new stevi_ctx();
+	c->device = device;
+	if (stream) { c->stream = static_cast<cudaStream_t>(stream); c->own_stream = false; }
+	else {
+		if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return STEVI_E_CUDA; }
+		c->own_stream = true;
+	}
+	cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+	*out = c;
+	return STEVI_OK;
+}
+
+int32_t stevi_ctx_destroy(stevi_ctx* c) {
+	if (!c) return STEVI_OK;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	for (auto& b : c->blocks) cudaFree(b.p);
+	if (c->own_stream) cudaStreamDestroy(c->stream);
+	delete c;
+	return STEVI_OK;
+}
+
+int32_t stevi_ctx_set_stream(stevi_ctx* c, void* stream) {
+	if (!c) return STEVI_E_ARG;
+	STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+	if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+	if (stream) c->stream = static_cast<cudaStream_t>(stream);
+	else {
+		STEVI_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+		c->own_stream = true;
+	}
+	return STEVI_OK;
+}
+
+void* stevi_ctx_stream(stevi_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int32_t stevi_ctx_synchronize(stevi_ctx* c) {
+	if (!c) return STEVI_E_ARG;
+	STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+	return STEVI_OK;
+}
+
+const char* stevi_last_error(stevi_ctx* c) { return c ? c->err.c_str() : "null context"; }
+int64_t stevi_ctx_launch_count(stevi_ctx* c) { return c ? c->launches : 0; }
+int64_t stevi_ctx_workspace_bytes(stevi_ctx* c) {
+	if (!c) return 0;
+	size_t t = 0;
+	for (auto& b : c->blocks) t += b.cap;
+	return (int64_t)t;
+}
+
+int32_t stevi_host_alloc(size_t bytes, void** out) {
+	if (!out) return STEVI_E_ARG;
+	if (cudaHostAlloc(out, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return STEVI_E_CUDA; }
+	return STEVI_OK;
+}
+int32_t stevi_host_free(void* p) {
+	if (p && cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return STEVI_E_CUDA; }
+	return STEVI_OK;
+}
+
+} // extern "C"
