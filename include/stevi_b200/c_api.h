@@ -26,6 +26,12 @@
 extern "C" {
 #endif
 
+#if defined(__GNUC__)
+#define STEVI_API __attribute__((visibility("default")))
+#else
+#define STEVI_API
+#endif
+
 #define STEVI_MAX_DIMS 4
 
 typedef enum {
@@ -72,29 +78,29 @@ typedef struct stevi_ctx stevi_ctx;
 /* ---- context: one per host thread / CUDA stream (the reference's functions are stateless and re-entrant; the
  * ctx only owns the device id, the stream and a grow-only device workspace). `stream` is a cudaStream_t or NULL
  * to let the ctx create its own non-blocking stream. */
-int32_t stevi_ctx_create(int32_t device, void* stream, stevi_ctx** out);
-int32_t stevi_ctx_destroy(stevi_ctx* ctx);
-int32_t stevi_ctx_set_stream(stevi_ctx* ctx, void* stream);
-void* stevi_ctx_stream(stevi_ctx* ctx);
-int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
-const char* stevi_last_error(stevi_ctx* ctx);
+STEVI_API int32_t stevi_ctx_create(int32_t device, void* stream, stevi_ctx** out);
+STEVI_API int32_t stevi_ctx_destroy(stevi_ctx* ctx);
+STEVI_API int32_t stevi_ctx_set_stream(stevi_ctx* ctx, void* stream);
+STEVI_API void* stevi_ctx_stream(stevi_ctx* ctx);
+STEVI_API int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
+STEVI_API const char* stevi_last_error(stevi_ctx* ctx);
 /* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */
-int64_t stevi_ctx_launch_count(stevi_ctx* ctx);
+STEVI_API int64_t stevi_ctx_launch_count(stevi_ctx* ctx);
 /* bytes currently held by the workspace arena */
-int64_t stevi_ctx_workspace_bytes(stevi_ctx* ctx);
-int32_t stevi_device_count(void);
-const char* stevi_version(void);
+STEVI_API int64_t stevi_ctx_workspace_bytes(stevi_ctx* ctx);
+STEVI_API int32_t stevi_device_count(void);
+STEVI_API const char* stevi_version(void);
 
 /* pinned host memory for callers that want DMA-speed staging of host operands */
-int32_t stevi_host_alloc(size_t bytes, void** out);
-int32_t stevi_host_free(void* p);
+STEVI_API int32_t stevi_host_alloc(size_t bytes, void** out);
+STEVI_API int32_t stevi_host_free(void* p);
 
 /* ---- features ------------------------------------------------------------------------------------------- */
 
 /* censusTransform2D (correlation/census.h:117-131) = unfold (unfold.h:248-291) + censusFeatures (census.h:69-115).
  * img (H,W) u8|f32  ->  out (H,W,nwords) u32, nwords = (F-1)/32+1, F=(2*h_radius+1)*(2*v_radius+1).
  * COMPAT: only completely filled 32-bit words are written, the trailing word is 0 (Q1). */
-int32_t stevi_census_transform(stevi_ctx* ctx, const stevi_array* img, int32_t h_radius, int32_t v_radius,
+STEVI_API int32_t stevi_census_transform(stevi_ctx* ctx, const stevi_array* img, int32_t h_radius, int32_t v_radius,
 							   int32_t semantics, stevi_array* out);
 
 /* ---- cost volumes ---------------------------------------------------------------------------------------- */
@@ -104,14 +110,14 @@ int32_t stevi_census_transform(stevi_ctx* ctx, const stevi_array* img, int32_t h
  * RIGHT_TO_LEFT, Wl for LEFT_TO_RIGHT. CENSUS: out u16|i32|f32 (hamming_cv_t = u16, matching_costs.h:234).
  * The reference lays the volume out as strides {W*D, 1, W} (cross_correlations.h:220); any strides are accepted.
  * Returns STEVI_E_SHAPE where the reference returns an empty array (heights differ, :751). */
-int32_t stevi_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+STEVI_API int32_t stevi_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
 						  int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction,
 						  int32_t semantics, stevi_array* out);
 
 /* aggregateCost<HAMMING|CENSUS> on ready-made census/binary features (correlation/cross_correlations.h:194-249):
  * feat_l (H,Wl,nw) u32, feat_r (H,Wr,nw) u32 -> out (H,Wsource,D). COMPAT rounds every target word through
  * float (Q2, :235-236). */
-int32_t stevi_hamming_cost_volume(stevi_ctx* ctx, const stevi_array* feat_l, const stevi_array* feat_r,
+STEVI_API int32_t stevi_hamming_cost_volume(stevi_ctx* ctx, const stevi_array* feat_l, const stevi_array* feat_r,
 								  int32_t disp_width, int32_t direction, int32_t semantics, stevi_array* out);
 
 /* ---- semi-global matching -------------------------------------------------------------------------------- */
@@ -119,17 +125,17 @@ int32_t stevi_hamming_cost_volume(stevi_ctx* ctx, const stevi_array* feat_l, con
 /* sgmCostVolume<nDirections, strategy, T_CV> (correlation/sgm.h:360-404). cv (H,W,D) u16|f32 -> out (H,W,D) f32.
  * n_directions in {4,8,16}. COMPAT reproduces Q3 (Cost mode ignores P1/P2) and Q4 (dead / half-run / doubled
  * directions); CORRECTED is the textbook recurrence over all directions. */
-int32_t stevi_sgm(stevi_ctx* ctx, const stevi_array* cv, int32_t n_directions, int32_t strategy,
+STEVI_API int32_t stevi_sgm(stevi_ctx* ctx, const stevi_array* cv, int32_t n_directions, int32_t strategy,
 				  float P1, float P2, float Pout, const stevi_margins* margins, int32_t semantics, stevi_array* out);
 
 /* ---- winner-take-all and friends -------------------------------------------------------------------------- */
 
 /* extractSelectedIndex<strategy, T_CV> (correlation/correlation_base.h:427-464): vol (H,W,D) u16|i32|f32 ->
  * out (H,W) i32. `<=` / `>=`: the LAST extremum wins (Q5); a NaN at d=0 sticks. */
-int32_t stevi_wta(stevi_ctx* ctx, const stevi_array* vol, int32_t strategy, stevi_array* out);
+STEVI_API int32_t stevi_wta(stevi_ctx* ctx, const stevi_array* vol, int32_t strategy, stevi_array* out);
 
 /* selectedIndexToDisp<disp_t, dDir> (correlation/correlation_base.h:511-532): disp = +-idx + offset */
-int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, int32_t direction, int32_t offset,
+STEVI_API int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, int32_t direction, int32_t offset,
 							stevi_array* out);
 
 /* ---- fused device-resident pipeline ------------------------------------------------------------------------ */
@@ -139,7 +145,7 @@ int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, int32_t dire
  * img_l, img_r (H,W) u8|f32; disp (H,W) i32 (required). cv_out (H,W,D) u16 and sgm_out (H,W,D) f32 are optional
  * (NULL = keep the volume in the ctx workspace / do not materialise it at all when the semantics allow).
  * Results are bit-identical to calling stevi_cost_volume, stevi_sgm, stevi_wta, stevi_index_to_disp in turn. */
-int32_t stevi_census_sgm_pipeline(stevi_ctx* ctx, const stevi_array* img_l, const stevi_array* img_r,
+STEVI_API int32_t stevi_census_sgm_pipeline(stevi_ctx* ctx, const stevi_array* img_l, const stevi_array* img_r,
 								  int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction,
 								  int32_t n_directions, float P1, float P2, float Pout, const stevi_margins* margins,
 								  int32_t semantics, stevi_array* cv_out, stevi_array* sgm_out, stevi_array* disp);

@@ -1,0 +1,303 @@
+"""Host-side mirror of the reference's ``StereoVision::Correlation`` functions over the C ABI.
+
+Function names, argument order and meaning follow the reference templates (file:line cited per function);
+template arguments become keyword arguments. Operands are numpy arrays (host memory: staged by the library) or
+torch CUDA tensors (device memory: used in place, asynchronous on the context's stream). Results come back in the
+same memory space as the inputs, shaped like the reference's and — with ``layout="ref"`` — laid out like them.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libstevi_b200.so")
+
+# enums (include/stevi_b200/c_api.h)
+OK, E_SHAPE, E_DTYPE, E_UNSUPPORTED, E_CUDA, E_NCCL, E_ARG = range(7)
+U8, U16, I32, U32, F32 = range(5)
+HOST, DEVICE = 0, 1
+COMPAT, CORRECTED = 0, 1
+CC, NCC, SSD, SAD, ZCC, ZNCC, ZSSD, ZSAD, MEDAD, ZMEDAD, HAMMING, CENSUS, KERMI = range(13)
+COST, SCORE = 0, 1
+LEFT_TO_RIGHT, RIGHT_TO_LEFT = 0, 1
+TCV_SAME, TCV_REVERSED, TCV_BOTH = 0, 1, 2
+EQUIANGULAR, PARABOLA, GAUSSIAN = 0, 1, 2
+SCORE_FUNCS = (CC, NCC, ZCC, ZNCC)
+
+_NP2DT = {np.dtype(np.uint8): U8, np.dtype(np.uint16): U16, np.dtype(np.int32): I32, np.dtype(np.uint32): U32,
+          np.dtype(np.float32): F32}
+_DT2NP = {v: k for k, v in _NP2DT.items()}
+
+
+class SteviError(RuntimeError):
+    def __init__(self, status, text):
+        super().__init__(f"stevi status {status}: {text}")
+        self.status = status
+
+
+class StArray(ctypes.Structure):
+    _fields_ = [("data", ctypes.c_void_p), ("dtype", ctypes.c_int32), ("ndim", ctypes.c_int32),
+                ("shape", ctypes.c_int32 * 4), ("strides", ctypes.c_int64 * 4), ("mem", ctypes.c_int32)]
+
+
+class StMargins(ctypes.Structure):
+    _fields_ = [("left", ctypes.c_int32), ("top", ctypes.c_int32), ("right", ctypes.c_int32), ("bottom", ctypes.c_int32)]
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(make -C libstevi_b200/csrc). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.stevi_last_error.restype = ctypes.c_char_p
+    lib.stevi_version.restype = ctypes.c_char_p
+    lib.stevi_ctx_stream.restype = ctypes.c_void_p
+    lib.stevi_ctx_launch_count.restype = ctypes.c_int64
+    lib.stevi_ctx_workspace_bytes.restype = ctypes.c_int64
+    return lib
+
+
+lib = _load()
+
+
+def _is_torch(x):
+    return hasattr(x, "data_ptr") and hasattr(x, "stride")
+
+
+def _torch_dtype_code(t):
+    import torch
+    return {torch.uint8: U8, torch.uint16: U16, torch.int32: I32, torch.uint32: U32, torch.float32: F32}[t.dtype]
+
+
+def describe(x):
+    """stevi_array descriptor of a numpy array (host) or torch CUDA tensor (device). Keeps no reference."""
+    a = StArray()
+    if _is_torch(x):
+        if not x.is_cuda:
+            raise TypeError("torch operands must live on a CUDA device; pass numpy arrays for host memory")
+        a.data = x.data_ptr()
+        a.dtype = _torch_dtype_code(x)
+        a.ndim = x.dim()
+        for k in range(x.dim()):
+            a.shape[k] = x.shape[k]
+            a.strides[k] = x.stride(k)
+        a.mem = DEVICE
+    else:
+        if x.dtype not in _NP2DT:
+            raise TypeError(f"unsupported dtype {x.dtype}")
+        a.data = x.ctypes.data
+        a.dtype = _NP2DT[x.dtype]
+        a.ndim = x.ndim
+        for k in range(x.ndim):
+            a.shape[k] = x.shape[k]
+            if x.strides[k] % x.itemsize:
+                raise ValueError("strides must be multiples of the item size")
+            a.strides[k] = x.strides[k] // x.itemsize
+        a.mem = HOST
+    return a
+
+
+class Context:
+    """One per host thread / CUDA stream (stevi_ctx). ``stream``: a raw cudaStream_t value, or None for an own stream;
+    ``torch_stream=True`` binds to torch's current stream on that device so torch events and tensors interoperate."""
+
+    def __init__(self, device=0, stream=None, torch_stream=False):
+        if torch_stream:
+            import torch
+            stream = torch.cuda.current_stream(device).cuda_stream
+        self._h = ctypes.c_void_p()
+        rc = lib.stevi_ctx_create(int(device), ctypes.c_void_p(stream), ctypes.byref(self._h))
+        if rc != OK:
+            raise SteviError(rc, "stevi_ctx_create failed: no usable CUDA device (there is no CPU fallback)")
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib.stevi_ctx_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != OK:
+            raise SteviError(rc, lib.stevi_last_error(self._h).decode())
+
+    def synchronize(self):
+        self.check(lib.stevi_ctx_synchronize(self._h))
+
+    @property
+    def launches(self):
+        return lib.stevi_ctx_launch_count(self._h)
+
+    @property
+    def workspace_bytes(self):
+        return lib.stevi_ctx_workspace_bytes(self._h)
+
+    @property
+    def handle(self):
+        return self._h
+
+
+_default_ctx = {}
+
+
+def default_context(device=0):
+    if device not in _default_ctx:
+        _default_ctx[device] = Context(device)
+    return _default_ctx[device]
+
+
+def _ctx_for(ctx, x):
+    if ctx is not None:
+        return ctx
+    return default_context(x.device.index if _is_torch(x) else 0)
+
+
+def _empty(like, shape, np_dtype, order=None):
+    """Uninitialised array in the memory space of ``like``; ``order`` = permutation giving the memory order
+    (slowest axis first), default C order."""
+    shape = tuple(int(s) for s in shape)
+    order = tuple(range(len(shape))) if order is None else tuple(order)
+    mem_shape = tuple(shape[k] for k in order)
+    inv = tuple(order.index(k) for k in range(len(shape)))
+    if _is_torch(like):
+        import torch
+        tdt = {np.dtype(np.uint8): torch.uint8, np.dtype(np.uint16): torch.uint16, np.dtype(np.int32): torch.int32,
+               np.dtype(np.uint32): torch.uint32, np.dtype(np.float32): torch.float32}[np.dtype(np_dtype)]
+        return torch.empty(mem_shape, dtype=tdt, device=like.device).permute(inv)
+    return np.empty(mem_shape, dtype=np_dtype).transpose(inv)
+
+
+# memory orders of (H,W,D) volumes
+ORDER_C = (0, 1, 2)      # [H][W][D]
+ORDER_REF_CV = (0, 2, 1)  # [H][D][W]: aggregateCost's strides {W*D, 1, W} (cross_correlations.h:220)
+
+
+def _volume_order(layout):
+    if layout in ("ref", "hdw"):
+        return ORDER_REF_CV
+    if layout in ("c", "hwd"):
+        return ORDER_C
+    if layout in ("f", "dwh"):
+        return (2, 1, 0)  # first index fastest
+    raise ValueError(layout)
+
+
+def strategy_of(matchfunc):
+    return SCORE if matchfunc in SCORE_FUNCS else COST
+
+
+def censusTransform2D(img, h_radius, v_radius, semantics=COMPAT, ctx=None):
+    """census.h:117-131. (H,W) u8|f32 -> (H,W,nwords) u32."""
+    ctx = _ctx_for(ctx, img)
+    F = (2 * h_radius + 1) * (2 * v_radius + 1)
+    out = _empty(img, img.shape + ((F - 1) // 32 + 1,), np.uint32)
+    a, o = describe(img), describe(out)
+    ctx.check(lib.stevi_census_transform(ctx.handle, ctypes.byref(a), h_radius, v_radius, semantics, ctypes.byref(o)))
+    return out
+
+
+def unfoldBasedCostVolume(matchFunc, img_l, img_r, h_radius, v_radius, disp_width, dDir=RIGHT_TO_LEFT, TCV=None,
+                          semantics=COMPAT, layout="ref", ctx=None):
+    """cross_correlations.h:740-765. Returns None where the reference returns an empty array."""
+    ctx = _ctx_for(ctx, img_l)
+    if TCV is None:
+        TCV = np.uint16 if matchFunc in (CENSUS, HAMMING) else np.float32
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    out = _empty(img_l, (img_l.shape[0], ws, disp_width), TCV, _volume_order(layout))
+    l, r, o = describe(img_l), describe(img_r), describe(out)
+    rc = lib.stevi_cost_volume(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, disp_width,
+                               dDir, semantics, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def hammingCostVolume(feat_l, feat_r, disp_width, dDir=RIGHT_TO_LEFT, TCV=np.uint16, semantics=COMPAT, layout="ref", ctx=None):
+    """aggregateCost<HAMMING> on (H,W,nw) u32 features, cross_correlations.h:194-249."""
+    ctx = _ctx_for(ctx, feat_l)
+    ws = feat_r.shape[1] if dDir == RIGHT_TO_LEFT else feat_l.shape[1]
+    out = _empty(feat_l, (feat_l.shape[0], ws, disp_width), TCV, _volume_order(layout))
+    l, r, o = describe(feat_l), describe(feat_r), describe(out)
+    rc = lib.stevi_hamming_cost_volume(ctx.handle, ctypes.byref(l), ctypes.byref(r), disp_width, dDir, semantics, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def sgmCostVolume(cv, P1, P2, margins=(0, 0, 0, 0), Pout=100.0, nDirections=8, strategy=COST, semantics=COMPAT,
+                  layout="same", ctx=None):
+    """sgm.h:360-404. margins = (left, top, right, bottom) like StereoVision::Margins' 4-argument constructor."""
+    ctx = _ctx_for(ctx, cv)
+    if layout == "same":
+        if _is_torch(cv):
+            order = tuple(sorted(range(3), key=lambda k: -cv.stride(k)))
+        else:
+            order = tuple(sorted(range(3), key=lambda k: -cv.strides[k]))
+    else:
+        order = _volume_order(layout)
+    out = _empty(cv, cv.shape, np.float32, order)
+    m = StMargins(*[int(v) for v in margins])
+    a, o = describe(cv), describe(out)
+    f32 = ctypes.c_float
+    ctx.check(lib.stevi_sgm(ctx.handle, ctypes.byref(a), nDirections, strategy, f32(P1), f32(P2), f32(Pout),
+                            ctypes.byref(m), semantics, ctypes.byref(o)))
+    return out
+
+
+def extractSelectedIndex(vol, strategy=COST, ctx=None):
+    """correlation_base.h:427-464."""
+    ctx = _ctx_for(ctx, vol)
+    out = _empty(vol, vol.shape[:2], np.int32)
+    a, o = describe(vol), describe(out)
+    ctx.check(lib.stevi_wta(ctx.handle, ctypes.byref(a), strategy, ctypes.byref(o)))
+    return out
+
+
+def selectedIndexToDisp(idx, offset=0, dDir=RIGHT_TO_LEFT, ctx=None):
+    """correlation_base.h:511-532."""
+    ctx = _ctx_for(ctx, idx)
+    out = _empty(idx, idx.shape, np.int32)
+    a, o = describe(idx), describe(out)
+    ctx.check(lib.stevi_index_to_disp(ctx.handle, ctypes.byref(a), dDir, offset, ctypes.byref(o)))
+    return out
+
+
+def censusSgmPipeline(img_l, img_r, h_radius, v_radius, disp_width, P1, P2, Pout=100.0, nDirections=8,
+                      margins=(0, 0, 0, 0), dDir=RIGHT_TO_LEFT, semantics=COMPAT, return_volumes=False, layout="ref",
+                      out=None, ctx=None):
+    """Census cost volume -> SGM -> WTA -> disparity in one call (benchmarkCrossCorrelationAlgorithms.cpp:289-293 with
+    CENSUS costs). Returns disp, or (cv, sgm, disp) with ``return_volumes``. ``out`` = preallocated (cv, sgm, disp) or disp."""
+    ctx = _ctx_for(ctx, img_l)
+    H = img_l.shape[0]
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    cv = sg = None
+    if out is not None:
+        if isinstance(out, tuple):
+            cv, sg, disp = out
+        else:
+            disp = out
+    else:
+        disp = _empty(img_l, (H, ws), np.int32)
+        if return_volumes:
+            cv = _empty(img_l, (H, ws, disp_width), np.uint16, _volume_order(layout))
+            sg = _empty(img_l, (H, ws, disp_width), np.float32, _volume_order(layout))
+    m = StMargins(*[int(v) for v in margins])
+    l, r, d = describe(img_l), describe(img_r), describe(disp)
+    dcv = describe(cv) if cv is not None else None
+    dsg = describe(sg) if sg is not None else None
+    f32 = ctypes.c_float
+    ctx.check(lib.stevi_census_sgm_pipeline(
+        ctx.handle, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, disp_width, dDir, nDirections,
+        f32(P1), f32(P2), f32(Pout), ctypes.byref(m), semantics,
+        ctypes.byref(dcv) if dcv is not None else None, ctypes.byref(dsg) if dsg is not None else None, ctypes.byref(d)))
+    if cv is not None or sg is not None:
+        return cv, sg, disp
+    return disp

@@ -1,0 +1,158 @@
+// extern "C" entry points (include/stevi_b200/c_api.h): argument checks, staging of host operands, stage chaining.
+#include "common.cuh"
+#include "kernels.cuh"
+#include <cmath>
+
+using namespace stevi;
+
+namespace {
+
+int32_t check_images(stevi_ctx* c, const View& l, const View& r) {
+	if (l.ndim != 2 || r.ndim != 2) return fail(c, STEVI_E_UNSUPPORTED, "images must be 2-D (H,W)");
+	if (l.dtype != r.dtype || (l.dtype != STEVI_U8 && l.dtype != STEVI_F32))
+		return fail(c, STEVI_E_DTYPE, "images must both be u8 or both f32");
+	if (l.shape[0] != r.shape[0]) return fail(c, STEVI_E_SHAPE, "image heights differ (cross_correlations.h:751)");
+	return STEVI_OK;
+}
+
+// dense (H,W,n) u32 workspace array with the word axis slowest ([n][H][W]): coalesced for every consumer
+int32_t alloc_census(stevi_ctx* c, int H, int W, int nw, View& v) {
+	uint32_t* p = nullptr;
+	STEVI_TRY(arena_alloc_t(c, (size_t)H * W * nw, &p));
+	v.p = p; v.dtype = STEVI_U32; v.ndim = 3;
+	v.shape[0] = H; v.shape[1] = W; v.shape[2] = nw;
+	v.st[0] = W; v.st[1] = 1; v.st[2] = (int64_t)H * W;
+	return STEVI_OK;
+}
+
+// census cost volume on device views; optionally emits the g map of the collapsed SGM
+int32_t census_cv_dev(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int direction, int semantics,
+					  const View& out, int32_t* gmap, int pout_i) {
+	STEVI_TRY(check_images(c, l, r));
+	const int nw = census_n_words(hr, vr);
+	View cl, cr;
+	STEVI_TRY(alloc_census(c, l.shape[0], l.shape[1], nw, cl));
+	STEVI_TRY(alloc_census(c, r.shape[0], r.shape[1], nw, cr));
+	STEVI_TRY(census_transform_dev(c, l, hr, vr, semantics, cl));
+	STEVI_TRY(census_transform_dev(c, r, hr, vr, semantics, cr));
+	// words past n_written are zero on both sides (and round to zero): no need to compare them
+	return hamming_cv_dev(c, cl, cr, census_n_written(hr, vr, semantics), D, direction, semantics == STEVI_COMPAT, out, gmap, pout_i);
+}
+
+} // namespace
+
+extern "C" {
+
+int32_t stevi_census_transform(stevi_ctx* c, const stevi_array* img, int32_t hr, int32_t vr, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(census_transform_dev(c, vi, hr, vr, semantics, vo));
+	return st.finish();
+}
+
+int32_t stevi_hamming_cost_volume(stevi_ctx* c, const stevi_array* fl, const stevi_array* fr, int32_t D, int32_t direction,
+								  int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	if (vl.ndim != 3) return fail(c, STEVI_E_SHAPE, "hamming: features must be 3-D");
+	STEVI_TRY(hamming_cv_dev(c, vl, vr, vl.shape[2], D, direction, semantics == STEVI_COMPAT, vo, nullptr, 0));
+	return st.finish();
+}
+
+int32_t stevi_cost_volume(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
+						  int32_t D, int32_t direction, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr_, vo;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	if (mf == STEVI_MF_CENSUS) {
+		STEVI_TRY(census_cv_dev(c, vl, vr_, hr, vr, D, direction, semantics, vo, nullptr, 0));
+	} else {
+		return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: matching function %d not available", mf);
+	}
+	return st.finish();
+}
+
+int32_t stevi_sgm(stevi_ctx* c, const stevi_array* cv, int32_t ndir, int32_t strategy, float P1, float P2, float Pout,
+				  const stevi_margins* margins, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vc, vo;
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	stevi_margins mg = margins ? *margins : stevi_margins{0, 0, 0, 0};
+	STEVI_TRY(sgm_dev(c, vc, ndir, strategy, P1, P2, Pout, mg, semantics, vo, nullptr, -1, nullptr));
+	return st.finish();
+}
+
+int32_t stevi_wta(stevi_ctx* c, const stevi_array* vol, int32_t strategy, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vv, vo;
+	STEVI_TRY(st.in(vol, vv, "vol"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(wta_dev(c, vv, strategy, vo));
+	return st.finish();
+}
+
+int32_t stevi_index_to_disp(stevi_ctx* c, const stevi_array* idx, int32_t direction, int32_t offset, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(index_to_disp_dev(c, vi, direction, offset, vo));
+	return st.finish();
+}
+
+int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr, int32_t D,
+								  int32_t direction, int32_t ndir, float P1, float P2, float Pout, const stevi_margins* margins,
+								  int32_t semantics, stevi_array* cv_out, stevi_array* sgm_out, stevi_array* disp) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr_, vcv, vs, vd;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(check_images(c, vl, vr_));
+	if (!disp) return fail(c, STEVI_E_ARG, "pipeline: disp is required");
+	STEVI_TRY(st.out(disp, vd, "disp"));
+	const int H = vl.shape[0];
+	const int Ws = direction == STEVI_RIGHT_TO_LEFT ? vr_.shape[1] : vl.shape[1];
+	// volumes the caller does not want live in the workspace, in the reference's [H][D][W] layout
+	auto workspace_volume = [&](int dtype, View& v) -> int32_t {
+		void* p = nullptr;
+		STEVI_TRY(arena_alloc(c, (size_t)H * Ws * D * dtype_size(dtype), &p));
+		v.p = p; v.dtype = dtype; v.ndim = 3;
+		v.shape[0] = H; v.shape[1] = Ws; v.shape[2] = D;
+		v.st[0] = (int64_t)Ws * D; v.st[1] = 1; v.st[2] = Ws;
+		return STEVI_OK;
+	};
+	if (cv_out) STEVI_TRY(st.out(cv_out, vcv, "cv_out")); else STEVI_TRY(workspace_volume(STEVI_U16, vcv));
+	if (sgm_out) STEVI_TRY(st.out(sgm_out, vs, "sgm_out")); else STEVI_TRY(workspace_volume(STEVI_F32, vs));
+	if (vcv.dtype != STEVI_U16) return fail(c, STEVI_E_DTYPE, "pipeline: cv_out must be u16 (hamming_cv_t)");
+	stevi_margins mg = margins ? *margins : stevi_margins{0, 0, 0, 0};
+	const bool pout_int = Pout == rintf(Pout) && fabsf(Pout) <= 1.0e6f;
+	const bool collapse = semantics == STEVI_COMPAT && pout_int;
+	int32_t* gmap = nullptr;
+	if (collapse) STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &gmap));
+	STEVI_TRY(census_cv_dev(c, vl, vr_, hr, vr, D, direction, semantics, vcv, gmap, (int)Pout));
+	const int max_cost = 32 * census_n_written(hr, vr, semantics);
+	View vidx;
+	int32_t* pidx = nullptr;
+	STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &pidx));
+	vidx.p = pidx; vidx.dtype = STEVI_I32; vidx.ndim = 2; vidx.shape[0] = H; vidx.shape[1] = Ws; vidx.st[0] = Ws; vidx.st[1] = 1;
+	STEVI_TRY(sgm_dev(c, vcv, ndir, STEVI_COST, P1, P2, Pout, mg, semantics, vs, gmap, max_cost, &vidx));
+	STEVI_TRY(index_to_disp_dev(c, vidx, direction, 0, vd));
+	return st.finish();
+}
+
+} // extern "C"

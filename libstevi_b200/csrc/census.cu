@@ -1,0 +1,321 @@
+// Census transform and Hamming cost volume (SURVEY.md §8(a) rows a1+a3 fused, a4+a5 for CENSUS/HAMMING).
+//
+// Reference behaviour reproduced here (file:line relative to the LibStevi tree):
+//   unfold.h:248-291      window order c = (2*h_r+1)*k + l, zero outside the image
+//   census.h:69-115       bit (c-1)%32 of word (c-1)/32 = (feat[0] > feat[c]); feat[0] is the TOP-LEFT window pixel;
+//                         Q1: a word is written only when its 32 bits are full
+//   cross_correlations.h:194-249  CV(i,j,d) = sum_n popcount(src(i,j,n) ^ tgt(i,j+s*d,n)), target 0 outside the image,
+//                         Q2: every target word is rounded through float first (:235-236)
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace stevi {
+
+// ---------------------------------------------------------------------------------------------------------------
+// census transform: one thread per pixel, 32x8 pixel tile plus the (2*h_r, 2*v_r) apron staged in shared memory
+// ---------------------------------------------------------------------------------------------------------------
+template<typename T>
+__global__ void __launch_bounds__(256) k_census_transform(const T* __restrict__ img, int64_t si, int64_t sj, int H, int W,
+														  int hr, int vr, int n_words, int n_written,
+														  uint32_t* __restrict__ out, int64_t so0, int64_t so1, int64_t so2) {
+	extern __shared__ unsigned char smem_raw[];
+	T* tile = reinterpret_cast<T*>(smem_raw);
+	const int hs = 2 * hr + 1, vs = 2 * vr + 1, F = hs * vs;
+	const int tw = 32 + 2 * hr, th = 8 + 2 * vr;
+	const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 8;
+	for (int t = threadIdx.y * 32 + threadIdx.x; t < tw * th; t += 256) {
+		int ty = t / tw, tx = t - ty * tw;
+		int ii = i0 - vr + ty, jj = j0 - hr + tx;
+		T v = T(0);
+		if (ii >= 0 && ii < H && jj >= 0 && jj < W) v = img[ii * si + jj * sj];
+		tile[t] = v;
+	}
+	__syncthreads();
+	const int i = i0 + threadIdx.y, j = j0 + threadIdx.x;
+	if (i >= H || j >= W) return;
+	const T* base = tile + threadIdx.y * tw + threadIdx.x;
+	const T ref = base[0];
+	uint32_t* o = out + i * so0 + j * so1;
+	uint32_t word = 0;
+	int b = 0, ch = 0;
+	int k = 0, l = 1; // c = hs*k + l, starting at c = 1
+	for (int c = 1; c < F; c++) {
+		T v = base[k * tw + l];
+		word |= (ref > v ? 1u : 0u) << b;
+		b++;
+		if (b == 32) { if (ch < n_written) o[ch * so2] = word; ch++; word = 0; b = 0; }
+		l++;
+		if (l == hs) { l = 0; k++; }
+	}
+	// CORRECTED semantics flush the partial word (n_written == n_words); COMPAT leaves it zero
+	if (b > 0 && ch < n_written) { o[ch * so2] = word; ch++; }
+	for (int n = (ch < n_written ? ch : n_written); n < n_words; n++) o[n * so2] = 0u;
+}
+
+int32_t census_n_words(int hr, int vr) { return ((2 * hr + 1) * (2 * vr + 1) - 1) / 32 + 1; }
+// number of words that can be non-zero
+int32_t census_n_written(int hr, int vr, int semantics) {
+	int ncmp = (2 * hr + 1) * (2 * vr + 1) - 1;
+	return semantics == STEVI_COMPAT ? ncmp / 32 : (ncmp + 31) / 32;
+}
+
+int32_t census_transform_dev(stevi_ctx* c, const View& img, int hr, int vr, int semantics, const View& out) {
+	if (img.ndim != 2) return fail(c, STEVI_E_UNSUPPORTED, "census: only 2-D images are supported");
+	if (hr < 0 || vr < 0 || hr > 31 || vr > 31) return fail(c, STEVI_E_ARG, "census: radius out of range");
+	const int H = img.shape[0], W = img.shape[1];
+	const int F = (2 * hr + 1) * (2 * vr + 1);
+	if (F <= 1) return fail(c, STEVI_E_SHAPE, "census: a single feature channel has no census (census.h:75-77)");
+	const int nw = census_n_words(hr, vr);
+	if (out.ndim != 3 || out.shape[0] != H || out.shape[1] != W || out.shape[2] != nw || out.dtype != STEVI_U32)
+		return fail(c, STEVI_E_SHAPE, "census: out must be (H,W,%d) u32", nw);
+	if (H == 0 || W == 0) return STEVI_OK;
+	dim3 block(32, 8), grid(cdiv(W, 32), cdiv(H, 8));
+	const int nwr = census_n_written(hr, vr, semantics);
+	if (img.dtype == STEVI_U8) {
+		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(uint8_t);
+		STEVI_LAUNCH(c, k_census_transform<uint8_t>, grid, block, sm, img.as<uint8_t>(), img.st[0], img.st[1], H, W, hr, vr,
+					 nw, nwr, out.as<uint32_t>(), out.st[0], out.st[1], out.st[2]);
+	} else if (img.dtype == STEVI_F32) {
+		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(float);
+		STEVI_LAUNCH(c, k_census_transform<float>, grid, block, sm, img.as<float>(), img.st[0], img.st[1], H, W, hr, vr,
+					 nw, nwr, out.as<uint32_t>(), out.st[0], out.st[1], out.st[2]);
+	} else return fail(c, STEVI_E_DTYPE, "census: image dtype must be u8 or f32");
+	return STEVI_OK;
+}
+
+} // namespace stevi
+
+// ---------------------------------------------------------------------------------------------------------------
+// Hamming cost volume
+// ---------------------------------------------------------------------------------------------------------------
+namespace stevi {
+
+struct HamParams {
+	const uint32_t* src; int64_t s0, s1, s2; // (row, column, word) strides of the source features
+	const uint32_t* tgt; int64_t t0, t1, t2;
+	int H, Ws, Wt, D, dchunk, n_words;
+	void* out; int64_t o0, o1, o2;            // (row, column, disparity) strides of the cost volume
+	int32_t* gmap; int pout;
+	int round;                                // Q2: round target words through float
+	int P;                                    // pitch of one of the 8 interleaved shared-memory lanes
+};
+
+// Q2 (cross_correlations.h:235-236): `float t = target; (uint32)t`. A word >= 0xFFFFFF80 rounds to 2^32 whose
+// conversion back is undefined in C++; scalar x86-64 code yields 0, which is the documented behaviour here.
+__device__ __forceinline__ uint32_t round_through_float(uint32_t w) {
+	float f = __uint2float_rn(w);
+	return f >= 4294967296.0f ? 0u : __float2uint_rz(f);
+}
+
+template<typename TO> __device__ __forceinline__ void store8(TO* p, const uint32_t (&c)[8]);
+template<> __device__ __forceinline__ void store8<uint16_t>(uint16_t* p, const uint32_t (&c)[8]) {
+	uint4 v;
+	v.x = c[0] | (c[1] << 16); v.y = c[2] | (c[3] << 16); v.z = c[4] | (c[5] << 16); v.w = c[6] | (c[7] << 16);
+	__stcs(reinterpret_cast<uint4*>(p), v);
+}
+template<> __device__ __forceinline__ void store8<int32_t>(int32_t* p, const uint32_t (&c)[8]) {
+	__stcs(reinterpret_cast<uint4*>(p), make_uint4(c[0], c[1], c[2], c[3]));
+	__stcs(reinterpret_cast<uint4*>(p) + 1, make_uint4(c[4], c[5], c[6], c[7]));
+}
+template<> __device__ __forceinline__ void store8<float>(float* p, const uint32_t (&c)[8]) {
+	__stcs(reinterpret_cast<float4*>(p), make_float4((float)c[0], (float)c[1], (float)c[2], (float)c[3]));
+	__stcs(reinterpret_cast<float4*>(p) + 1, make_float4((float)c[4], (float)c[5], (float)c[6], (float)c[7]));
+}
+
+// One block = one image row x 1024 source columns x one chunk of disparities. A thread owns 8 consecutive columns:
+// their source words stay in registers, the 8 target words slide by one column per disparity (one shared-memory
+// load per thread and disparity), and each disparity ends in one 16-byte store, so a warp writes 512 contiguous
+// bytes of the [H][D][W] volume. Target words of the row are staged once in shared memory, already rounded (Q2),
+// in 8 interleaved lanes so that the stride-8 accesses of a warp are bank-conflict free.
+template<int NW, int SIGN, typename TO, bool VEC, bool EMIT_G>
+__global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
+	extern __shared__ uint32_t sm[];
+	const int tid = threadIdx.x;
+	const int i = blockIdx.y;
+	const int j0 = blockIdx.x * 1024;
+	const int d0 = blockIdx.z * p.dchunk;
+	const int dn = min(p.D - d0, p.dchunk);
+	const int N = 1024 + dn - 1;
+	const int base = SIGN > 0 ? j0 + d0 : j0 - d0 - (dn - 1);
+	const int P = p.P;
+	for (int idx = tid; idx < N; idx += 128) {
+		const int col = base + idx;
+		const bool ok = col >= 0 && col < p.Wt;
+#pragma unroll
+		for (int n = 0; n < NW; n++) {
+			uint32_t w = ok ? __ldg(p.tgt + i * p.t0 + col * p.t1 + n * p.t2) : 0u;
+			if (p.round) w = round_through_float(w);
+			sm[n * 8 * P + (idx & 7) * P + (idx >> 3)] = w;
+		}
+	}
+	__syncthreads();
+	const int j = j0 + tid * 8;
+	if (j >= p.Ws) return;
+	uint32_t s[NW][8], w[NW][8];
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+#pragma unroll
+		for (int n = 0; n < NW; n++) s[n][k] = (j + k < p.Ws) ? __ldg(p.src + i * p.s0 + (j + k) * p.s1 + n * p.s2) : 0u;
+	}
+	const int off0 = SIGN > 0 ? 0 : dn - 1;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		const int idx = tid * 8 + k + off0;
+#pragma unroll
+		for (int n = 0; n < NW; n++) w[n][k] = sm[n * 8 * P + (idx & 7) * P + (idx >> 3)];
+	}
+	int gmin[8];
+	if (EMIT_G) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) gmin[k] = 0x7fffffff;
+	}
+	const bool full = j + 8 <= p.Ws;
+	TO* orow = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1;
+	for (int dr = 0; dr < dn; dr += 8) {
+#pragma unroll
+		for (int u = 0; u < 8; u++) {
+			if (dr + u < dn) {
+				const int d = d0 + dr + u;
+				uint32_t cst[8];
+#pragma unroll
+				for (int k = 0; k < 8; k++) {
+					uint32_t a = 0;
+#pragma unroll
+					for (int n = 0; n < NW; n++) a += __popc(s[n][k] ^ w[n][k]);
+					cst[k] = a;
+					if (EMIT_G) gmin[k] = min(gmin[k], (int)(2 * a) + ((j + k + d >= p.Ws) ? p.pout : 0));
+				}
+				TO* o = orow + d * p.o2;
+				if (VEC && full) store8<TO>(o, cst);
+				else {
+#pragma unroll
+					for (int k = 0; k < 8; k++) if (j + k < p.Ws) o[k * p.o1] = (TO)cst[k];
+				}
+				if (dr + u + 1 < dn) { // slide the target window by one column
+					if (SIGN > 0) {
+						const int idx = tid * 8 + 8 + dr + u;
+#pragma unroll
+						for (int n = 0; n < NW; n++) {
+#pragma unroll
+							for (int k = 0; k < 7; k++) w[n][k] = w[n][k + 1];
+							w[n][7] = sm[n * 8 * P + (idx & 7) * P + (idx >> 3)];
+						}
+					} else {
+						const int idx = tid * 8 + (dn - 1) - (dr + u + 1);
+#pragma unroll
+						for (int n = 0; n < NW; n++) {
+#pragma unroll
+							for (int k = 7; k > 0; k--) w[n][k] = w[n][k - 1];
+							w[n][0] = sm[n * 8 * P + (idx & 7) * P + (idx >> 3)];
+						}
+					}
+				}
+			}
+		}
+	}
+	if (EMIT_G) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) if (j + k < p.Ws) p.gmap[(int64_t)i * p.Ws + j + k] = gmin[k];
+	}
+}
+
+// any strides, any word count: one thread per source pixel walking the disparities
+template<typename TO>
+__global__ void __launch_bounds__(256) k_hamming_generic(const HamParams p, int sign) {
+	const int j = blockIdx.x * blockDim.x + threadIdx.x;
+	const int i = blockIdx.y;
+	if (j >= p.Ws) return;
+	TO* o = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1;
+	int gmin = 0x7fffffff;
+	for (int d = 0; d < p.D; d++) {
+		const int jt = j + sign * d;
+		const bool ok = jt >= 0 && jt < p.Wt;
+		uint32_t a = 0;
+		for (int n = 0; n < p.n_words; n++) {
+			uint32_t t = ok ? p.tgt[i * p.t0 + jt * p.t1 + n * p.t2] : 0u;
+			if (p.round) t = round_through_float(t);
+			a += __popc(p.src[i * p.s0 + j * p.s1 + n * p.s2] ^ t);
+		}
+		o[d * p.o2] = (TO)a;
+		gmin = min(gmin, (int)(2 * a) + ((j + d >= p.Ws) ? p.pout : 0));
+	}
+	if (p.gmap) p.gmap[(int64_t)i * p.Ws + j] = gmin;
+}
+
+template<int NW, int SIGN, typename TO>
+static int32_t launch_rows(stevi_ctx* c, const HamParams& p, dim3 grid, size_t smem, bool vec) {
+	if (p.gmap) {
+		if (vec) STEVI_LAUNCH(c, (k_hamming_rows<NW, SIGN, TO, true, true>), grid, 128, smem, p);
+		else STEVI_LAUNCH(c, (k_hamming_rows<NW, SIGN, TO, false, true>), grid, 128, smem, p);
+	} else {
+		if (vec) STEVI_LAUNCH(c, (k_hamming_rows<NW, SIGN, TO, true, false>), grid, 128, smem, p);
+		else STEVI_LAUNCH(c, (k_hamming_rows<NW, SIGN, TO, false, false>), grid, 128, smem, p);
+	}
+	return STEVI_OK;
+}
+
+template<typename TO>
+static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
+	const bool rows_ok = p.o1 == 1 && p.n_words >= 1 && p.n_words <= 4 && p.D <= 8192;
+	if (!rows_ok) {
+		dim3 grid(cdiv(p.Ws, 256), p.H);
+		STEVI_LAUNCH(c, k_hamming_generic<TO>, grid, 256, 0, p, sign);
+		return STEVI_OK;
+	}
+	const int xb = cdiv(p.Ws, 1024);
+	int dchunk = (p.D + 7) / 8 * 8;
+	const long want = 4L * c->sm_count;
+	if (!p.gmap && (long)xb * p.H < want) {
+		long parts = (want + (long)xb * p.H - 1) / ((long)xb * p.H);
+		int dc = (int)((p.D + parts - 1) / parts);
+		dc = std::max(32, (dc + 7) / 8 * 8);
+		dchunk = std::min(dchunk, dc);
+	}
+	p.dchunk = dchunk;
+	const int groups = (1024 + dchunk + 8) / 8 + 1;
+	int P = groups;
+	while (P % 32 != 4) P++;
+	p.P = P;
+	const size_t smem = (size_t)p.n_words * 8 * P * sizeof(uint32_t);
+	dim3 grid(xb, p.H, cdiv(p.D, dchunk));
+	const size_t esz = sizeof(TO);
+	const bool vec = ((uintptr_t)p.out % 16 == 0) && ((p.o0 * esz) % 16 == 0) && ((p.o2 * esz) % 16 == 0);
+#define STEVI_HAM_CASE(NW) \
+	case NW: return sign > 0 ? launch_rows<NW, 1, TO>(c, p, grid, smem, vec) : launch_rows<NW, -1, TO>(c, p, grid, smem, vec);
+	switch (p.n_words) {
+		STEVI_HAM_CASE(1) STEVI_HAM_CASE(2) STEVI_HAM_CASE(3) STEVI_HAM_CASE(4)
+	}
+#undef STEVI_HAM_CASE
+	return fail(c, STEVI_E_UNSUPPORTED, "hamming: unreachable");
+}
+
+int32_t hamming_cv_dev(stevi_ctx* c, const View& fl, const View& fr, int n_cmp, int D, int direction,
+					   bool round_target, const View& out, int32_t* gmap, int pout_i) {
+	if (fl.ndim != 3 || fr.ndim != 3 || fl.dtype != STEVI_U32 || fr.dtype != STEVI_U32)
+		return fail(c, STEVI_E_DTYPE, "hamming: features must be (H,W,n) u32");
+	if (fl.shape[0] != fr.shape[0] || fl.shape[2] != fr.shape[2])
+		return fail(c, STEVI_E_SHAPE, "hamming: feature volumes disagree (cross_correlations.h:209-211)");
+	if (D < 0) return fail(c, STEVI_E_ARG, "hamming: negative disparity width");
+	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
+	const View& src = r2l ? fr : fl;
+	const View& tgt = r2l ? fl : fr;
+	HamParams p;
+	p.src = src.as<uint32_t>(); p.s0 = src.st[0]; p.s1 = src.st[1]; p.s2 = src.st[2];
+	p.tgt = tgt.as<uint32_t>(); p.t0 = tgt.st[0]; p.t1 = tgt.st[1]; p.t2 = tgt.st[2];
+	p.H = src.shape[0]; p.Ws = src.shape[1]; p.Wt = tgt.shape[1]; p.D = D; p.dchunk = D;
+	p.n_words = std::min(n_cmp, src.shape[2]);
+	p.out = out.p; p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
+	p.gmap = gmap; p.pout = pout_i; p.round = round_target ? 1 : 0; p.P = 0;
+	if (out.ndim != 3 || out.shape[0] != p.H || out.shape[1] != p.Ws || out.shape[2] != D)
+		return fail(c, STEVI_E_SHAPE, "hamming: out must be (%d,%d,%d)", p.H, p.Ws, D);
+	if (p.H == 0 || p.Ws == 0 || D == 0) return STEVI_OK;
+	const int sign = r2l ? 1 : -1;
+	switch (out.dtype) {
+	case STEVI_U16: return hamming_typed<uint16_t>(c, p, sign);
+	case STEVI_I32: return hamming_typed<int32_t>(c, p, sign);
+	case STEVI_F32: return hamming_typed<float>(c, p, sign);
+	default: return fail(c, STEVI_E_DTYPE, "hamming: cost volume dtype must be u16, i32 or f32");
+	}
+}
+
+} // namespace stevi

@@ -1,0 +1,26 @@
+// Device-operand entry points of each stage (host wrappers that launch the kernels on ctx->stream). The C ABI
+// functions in api.cu stage host operands and then call these; the fused pipelines chain them directly.
+#pragma once
+#include "common.cuh"
+
+namespace stevi {
+
+// census.cu
+int32_t census_n_words(int hr, int vr);
+int32_t census_n_written(int hr, int vr, int semantics);
+int32_t census_transform_dev(stevi_ctx* c, const View& img, int hr, int vr, int semantics, const View& out);
+// feat_* (H,W*,nw) u32; n_cmp = how many leading words to compare (the rest are known to be zero on both sides);
+// gmap (optional, int32 [H*Ws] dense): min_d (2*C + pout_i*[j+d >= Ws]) for the collapsed SGM (sgm.cu)
+int32_t hamming_cv_dev(stevi_ctx* c, const View& feat_l, const View& feat_r, int n_cmp, int D, int direction,
+					   bool round_target, const View& out, int32_t* gmap, int pout_i);
+
+// sgm.cu
+int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
+				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
+				const View* wta_out);
+
+// wta.cu
+int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);
+int32_t index_to_disp_dev(stevi_ctx* c, const View& idx, int direction, int offset, const View& out);
+
+} // namespace stevi

@@ -1,0 +1,343 @@
+// Semi-global matching path aggregation (correlation/sgm.h:57-404 of the reference).
+//
+// Two implementations live here.
+//
+// (1) COLLAPSED — COMPAT semantics, Cost strategy, integer (uint16) cost volume, integer-valued Pout.
+//     As written (Q3, sgm.h:281-283) the reference's Cost recurrence stores `c_score` instead of the penalised
+//     previous score, so along a line only the scalar m(p) = min_d L(p,d) is handed from pixel to pixel:
+//         L(p,d) = C + ((C + Pout*[j+d >= W]) - m(prev)),   m(p) = g(p) - m(prev),   g(p) = min_d (2C + Pout*[j+d >= W])
+//         S(p,d) = C + sum over the live line passes r through p of ((C + Pout*[..]) - m_r(prev))
+//                = (1 + R_p)*C + R_p*Pout*[j+d >= W] - T_p,      R_p = #passes, T_p = sum_r m_r(prev)
+//     Every quantity is an integer; as long as all magnitudes stay below 2^24 the reference's float arithmetic is
+//     exact and order independent, so the integer evaluation below is bit-identical to it. The bound is checked
+//     (a priori when the caller knows the largest cost, else from the measured max |m|); if it does not hold the
+//     general implementation (2) is used instead. Volume traffic: one read of C for g (skipped when the cost-volume
+//     kernel already emitted g), one read of C and one write of S.
+//
+// (2) GENERAL — Score strategy (a genuine P1/P2 recurrence, sgm.h:218-256), float volumes, CORRECTED semantics:
+//     one warp per line, lanes strided over d. See the second half of this file.
+//
+// Live line sets (Q4, sgm.h:321-354): lines start at ZeroPos (top row / left column) or at EndPos which, as written,
+// is one past the last valid index, so those lines traverse nothing; the (top,left) corner line of a diagonal is
+// started by both loops and therefore counted twice. CORRECTED starts EndPos lines on the last valid index and starts
+// corner lines once.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace stevi {
+
+// sgm.h:57-155 directionTraits: {stepsVertical[0], stepsVertical[1], stepsHorizontal[0], stepsHorizontal[1]}
+__constant__ int c_sgm_steps[16][4] = {
+	{1, 1, 0, 0}, {-1, -1, 0, 0}, {0, 0, 1, 1}, {0, 0, -1, -1},
+	{1, 1, 1, 1}, {-1, -1, -1, -1}, {1, 1, -1, -1}, {-1, -1, 1, 1},
+	{0, 1, 1, 1}, {0, -1, -1, -1}, {0, 1, -1, -1}, {0, -1, 1, 1},
+	{1, 1, 0, 1}, {-1, -1, 0, -1}, {1, 1, 0, -1}, {-1, -1, 0, 1}};
+// call order of sgmCostVolume, sgm.h:379-401
+__constant__ int c_sgm_order[16] = {0, 1, 2, 3, 4, 5, 6, 7, 12, 13, 14, 15, 8, 9, 10, 11};
+static const int h_sgm_steps[16][4] = {
+	{1, 1, 0, 0}, {-1, -1, 0, 0}, {0, 0, 1, 1}, {0, 0, -1, -1},
+	{1, 1, 1, 1}, {-1, -1, -1, -1}, {1, 1, -1, -1}, {-1, -1, 1, 1},
+	{0, 1, 1, 1}, {0, -1, -1, -1}, {0, 1, -1, -1}, {0, -1, 1, 1},
+	{1, 1, 0, 1}, {-1, -1, 0, -1}, {1, 1, 0, -1}, {-1, -1, 0, 1}};
+static const int h_sgm_order[16] = {0, 1, 2, 3, 4, 5, 6, 7, 12, 13, 14, 15, 8, 9, 10, 11};
+
+struct SgmGeom { int H, W, top, bottom, left, right, corrected; };
+
+// sgm.h:162-184: 0 = NoStart, 1 = ZeroPos, 2 = EndPos
+__host__ __device__ __forceinline__ int sgm_start_pos(int s0, int s1) {
+	if (s0 == 0 && s1 == 0) return 0;
+	if (s0 >= 0 && s1 >= 0) return 1;
+	return 2;
+}
+
+struct SgmLines { int n_row, n_col, sj_row, si_col; };
+
+// sgm.h:313-356 addDirectionalCost: which lines a direction starts. kind 0 = lines starting on a column (one per row,
+// `rowStart`), kind 1 = lines starting on a row (one per column, `colStart`).
+__host__ __device__ __forceinline__ SgmLines sgm_lines(const int* st, const SgmGeom& g) {
+	SgmLines l;
+	const int colStart = sgm_start_pos(st[0], st[1]);
+	const int rowStart = sgm_start_pos(st[2], st[3]);
+	const int nr = g.H - g.bottom - g.top, nc = g.W - g.right - g.left;
+	l.n_row = (rowStart != 0 && nr > 0) ? nr : 0;
+	l.n_col = (colStart != 0 && nc > 0) ? nc : 0;
+	l.sj_row = rowStart == 1 ? g.left : g.W - g.right - (g.corrected ? 1 : 0);
+	l.si_col = colStart == 1 ? g.top : g.H - g.bottom - (g.corrected ? 1 : 0);
+	return l;
+}
+
+__device__ __forceinline__ bool sgm_inside(int i, int j, const SgmGeom& g) {
+	return i >= g.top && i < g.H - g.bottom && j >= g.left && j < g.W - g.right;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// (1) collapsed implementation
+// ------------------------------------------------------------------------------------------------------------------
+
+// g(p) = min_d (2*C(p,d) + pout*[j+d >= W]) for volumes with a pixel axis of stride 1: thread = 8 consecutive pixels
+__global__ void __launch_bounds__(128) k_sgm_gmap_planes(const uint16_t* __restrict__ cv, int64_t sa, int64_t sd, int na, int nb, int D,
+														 int W, int b_is_j, int pout, int32_t* __restrict__ g) {
+	const int b0 = (blockIdx.x * 128 + threadIdx.x) * 8;
+	const int a = blockIdx.y;
+	if (b0 >= nb) return;
+	const uint16_t* p = cv + a * sa + b0;
+	int gm[8];
+#pragma unroll
+	for (int k = 0; k < 8; k++) gm[k] = 0x7fffffff;
+	if (b0 + 8 <= nb) {
+#pragma unroll 8
+		for (int d = 0; d < D; d++) {
+			const uint4 r = __ldg(reinterpret_cast<const uint4*>(p + d * sd));
+			const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const int cst = (w[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+				const int j = b_is_j ? b0 + k : a;
+				gm[k] = min(gm[k], 2 * cst + (j + d >= W ? pout : 0));
+			}
+		}
+	} else {
+		for (int k = 0; b0 + k < nb; k++) {
+			const int j = b_is_j ? b0 + k : a;
+			for (int d = 0; d < D; d++) gm[k] = min(gm[k], 2 * (int)p[k + d * sd] + (j + d >= W ? pout : 0));
+		}
+	}
+#pragma unroll
+	for (int k = 0; k < 8; k++) if (b0 + k < nb) {
+		const int i = b_is_j ? a : b0 + k, j = b_is_j ? b0 + k : a;
+		g[(int64_t)i * W + j] = gm[k];
+	}
+}
+
+// any strides: a warp per pixel, lanes strided over d (coalesced when d is the fastest axis)
+__global__ void __launch_bounds__(256) k_sgm_gmap_generic(const uint16_t* __restrict__ cv, int64_t s0, int64_t s1, int64_t sd, int H, int W, int D,
+														  int pout, int32_t* __restrict__ g) {
+	const int lane = threadIdx.x & 31;
+	const int64_t pix = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+	if (pix >= (int64_t)H * W) return;
+	const int i = (int)(pix / W), j = (int)(pix - (int64_t)i * W);
+	const uint16_t* p = cv + i * s0 + j * s1;
+	int gm = 0x7fffffff;
+	for (int d = lane; d < D; d += 32) gm = min(gm, 2 * (int)p[d * sd] + (j + d >= W ? pout : 0));
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) gm = min(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+	if (lane == 0) g[pix] = gm;
+}
+
+// Scalar recurrences m(p) = g(p) - m(prev) along every live line of every direction: one thread per line, loads of g
+// batched 8 ahead (they do not depend on the recurrence). T(p) += m(prev), R(p) += 1; integer atomics, so the result
+// does not depend on the schedule. blockIdx.y = direction slot in the reference's call order.
+__global__ void __launch_bounds__(128) k_sgm_pathsum(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+													 int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+	const int dir = c_sgm_order[blockIdx.y];
+	const int* st = c_sgm_steps[dir];
+	const SgmLines L = sgm_lines(st, geom);
+	const int line = blockIdx.x * blockDim.x + threadIdx.x;
+	int mabs = 0;
+	if (line < L.n_row + L.n_col) {
+		int i, j;
+		if (line < L.n_row) { i = geom.top + line; j = L.sj_row; }
+		else { i = L.si_col; j = geom.left + (line - L.n_row); }
+		// CORRECTED: a corner line started by both loops is walked once
+		const bool dup = geom.corrected && line >= L.n_row && L.n_row > 0 && j == L.sj_row;
+		if (!dup) {
+			const int sv0 = st[0], sv1 = st[1], sh0 = st[2], sh1 = st[3];
+			int c = 0, m_prev = 0;
+			while (sgm_inside(i, j, geom)) {
+				int pos[8], gv[8];
+#pragma unroll
+				for (int u = 0; u < 8; u++) {
+					const bool ok = sgm_inside(i, j, geom);
+					pos[u] = ok ? i * geom.W + j : -1;
+					if (ok) { i += (c & 1) ? sv1 : sv0; j += (c & 1) ? sh1 : sh0; c++; }
+				}
+#pragma unroll
+				for (int u = 0; u < 8; u++) gv[u] = pos[u] >= 0 ? __ldg(g + pos[u]) : 0;
+#pragma unroll
+				for (int u = 0; u < 8; u++) if (pos[u] >= 0) {
+					atomicAdd(T + pos[u], m_prev);
+					atomicAdd(R + pos[u], 1);
+					m_prev = gv[u] - m_prev;
+					mabs = max(mabs, abs(m_prev));
+				}
+			}
+		}
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) mabs = max(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+	if ((threadIdx.x & 31) == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
+}
+
+// S = (1+R)*C + R*pout*[j+d >= W] - T on the reference's [H][D][W] layout (column stride 1 in and out): a thread owns 8
+// consecutive columns; per disparity one 16-byte load of costs and two 16-byte stores of floats. With WTA the running
+// arg-min (`<=`: last minimum wins, correlation_base.h:446) is kept along the way, so the aggregated volume is not read again.
+template<bool WTA>
+__global__ void __launch_bounds__(128) k_sgm_apply_rows(const uint16_t* __restrict__ cv, int64_t c0, int64_t cd,
+														float* __restrict__ S, int64_t s0, int64_t sd,
+														const int32_t* __restrict__ T, const int32_t* __restrict__ R,
+														int H, int W, int D, int dchunk, int pout,
+														int32_t* __restrict__ idx, int64_t i0, int64_t i1) {
+	const int j = (blockIdx.x * 128 + threadIdx.x) * 8;
+	const int i = blockIdx.y;
+	if (j >= W) return; // W is a multiple of 8 on this path
+	const int d_begin = blockIdx.z * dchunk, d_end = min(D, d_begin + dchunk);
+	int r1[8], rp[8], t[8];
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		const int r = __ldg(R + (int64_t)i * W + j + k);
+		r1[k] = 1 + r; rp[k] = r * pout; t[k] = __ldg(T + (int64_t)i * W + j + k);
+	}
+	const uint16_t* pc = cv + i * c0 + j;
+	float* ps = S + i * s0 + j;
+	int best[8], bd[8];
+	if (WTA) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) { best[k] = 0x7fffffff; bd[k] = 0; }
+	}
+#pragma unroll 4
+	for (int d = d_begin; d < d_end; d++) {
+		const uint4 r = __ldcs(reinterpret_cast<const uint4*>(pc + d * cd));
+		const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+		float o[8];
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			const int cst = (w[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+			const int s = r1[k] * cst + (j + k + d >= W ? rp[k] : 0) - t[k];
+			o[k] = (float)s;
+			if (WTA) { if (s <= best[k]) { best[k] = s; bd[k] = d; } }
+		}
+		__stcs(reinterpret_cast<float4*>(ps + d * sd), make_float4(o[0], o[1], o[2], o[3]));
+		__stcs(reinterpret_cast<float4*>(ps + d * sd) + 1, make_float4(o[4], o[5], o[6], o[7]));
+	}
+	if (WTA) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) idx[i * i0 + (j + k) * i1] = bd[k];
+	}
+}
+
+// any strides: one thread per pixel
+__global__ void __launch_bounds__(128) k_sgm_apply_generic(const uint16_t* __restrict__ cv, int64_t c0, int64_t c1, int64_t cd,
+														   float* __restrict__ S, int64_t s0, int64_t s1, int64_t sd,
+														   const int32_t* __restrict__ T, const int32_t* __restrict__ R,
+														   int H, int W, int D, int pout, int32_t* __restrict__ idx, int64_t i0, int64_t i1) {
+	const int j = blockIdx.x * 128 + threadIdx.x;
+	const int i = blockIdx.y;
+	if (j >= W) return;
+	const int r = R[(int64_t)i * W + j], t = T[(int64_t)i * W + j];
+	const uint16_t* pc = cv + i * c0 + j * c1;
+	float* ps = S + i * s0 + j * s1;
+	int best = 0x7fffffff, bd = 0;
+	for (int d = 0; d < D; d++) {
+		const int s = (1 + r) * (int)pc[d * cd] + (j + d >= W ? r * pout : 0) - t;
+		ps[d * sd] = (float)s;
+		if (s <= best) { best = s; bd = d; }
+	}
+	if (idx) idx[i * i0 + j * i1] = bd;
+}
+
+} // namespace stevi
+
+namespace stevi {
+
+static const int32_t STEVI_FALLBACK = -1000; // internal: the collapsed evaluation is not provably exact here
+
+static bool aligned16(const void* p, int64_t a, int64_t b, size_t esz) {
+	return ((uintptr_t)p % 16 == 0) && ((a * (int64_t)esz) % 16 == 0) && ((b * (int64_t)esz) % 16 == 0);
+}
+
+static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, const stevi_margins& mg, const View& out,
+							 const int32_t* gmap_ready, int max_cost_hint, const View* wta_out) {
+	const int H = cv.shape[0], W = cv.shape[1], D = cv.shape[2];
+	const size_t npix = (size_t)H * W;
+	int32_t* scratch = nullptr; // [T | R | max_abs_m]
+	STEVI_TRY(arena_alloc_t(c, 2 * npix + 64, &scratch));
+	int32_t* T = scratch;
+	int32_t* R = scratch + npix;
+	int32_t* d_max = scratch + 2 * npix;
+	STEVI_CUDA(c, cudaMemsetAsync(scratch, 0, (2 * npix + 64) * sizeof(int32_t), c->stream));
+	const int32_t* g = gmap_ready;
+	const uint16_t* pc = cv.as<uint16_t>();
+	if (!g) {
+		int32_t* gbuf = nullptr;
+		STEVI_TRY(arena_alloc_t(c, npix, &gbuf));
+		bool done = false;
+		if (cv.st[1] == 1 || cv.st[0] == 1) {
+			const int b = cv.st[1] == 1 ? 1 : 0, a = 1 - b;
+			if (aligned16(pc, cv.st[a], cv.st[2], 2) && cv.shape[a] <= 65535) {
+				dim3 grid(cdiv(cv.shape[b], 1024), cv.shape[a]);
+				STEVI_LAUNCH(c, k_sgm_gmap_planes, grid, 128, 0, pc, cv.st[a], cv.st[2], cv.shape[a], cv.shape[b], D, W, b, pout, gbuf);
+				done = true;
+			}
+		}
+		if (!done)
+			STEVI_LAUNCH(c, k_sgm_gmap_generic, (unsigned)((npix + 7) / 8), 256, 0, pc, cv.st[0], cv.st[1], cv.st[2], H, W, D, pout, gbuf);
+		g = gbuf;
+	}
+	SgmGeom geom{H, W, mg.top, mg.bottom, mg.left, mg.right, 0};
+	{
+		dim3 grid(cdiv(H + W, 128), ndir);
+		STEVI_LAUNCH(c, k_sgm_pathsum, grid, 128, 0, g, T, R, d_max, geom);
+	}
+	// exactness bound of the float arithmetic this replaces (all magnitudes < 2^24)
+	const long max_c = max_cost_hint >= 0 ? max_cost_hint : 65535;
+	const long rmax = ndir + 1, apout = labs((long)pout);
+	const long lim = 1L << 24;
+	const long m_apriori = (2 * max_c + apout) * (long)(H + W);
+	if ((1 + rmax) * max_c + rmax * apout + rmax * m_apriori >= lim) {
+		int32_t h_max = 0;
+		STEVI_CUDA(c, cudaMemcpyAsync(&h_max, d_max, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+		STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+		if ((1 + rmax) * max_c + rmax * apout + rmax * (long)h_max >= lim) return STEVI_FALLBACK;
+	}
+	float* ps = out.as<float>();
+	const bool rows = cv.st[1] == 1 && out.st[1] == 1 && (W % 8) == 0 && aligned16(pc, cv.st[0], cv.st[2], 2) &&
+					  aligned16(ps, out.st[0], out.st[2], 4) && H <= 65535;
+	if (rows) {
+		const int xb = cdiv(W, 1024);
+		int dchunk = D;
+		const long want = 4L * c->sm_count;
+		if (!wta_out && (long)xb * H < want) {
+			long parts = (want + (long)xb * H - 1) / ((long)xb * H);
+			dchunk = std::max(16, (int)((D + parts - 1) / parts));
+		}
+		dim3 grid(xb, H, cdiv(D, dchunk));
+		if (wta_out)
+			STEVI_LAUNCH(c, k_sgm_apply_rows<true>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
+						 wta_out->as<int32_t>(), wta_out->st[0], wta_out->st[1]);
+		else
+			STEVI_LAUNCH(c, k_sgm_apply_rows<false>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
+						 (int32_t*)nullptr, (int64_t)0, (int64_t)0);
+	} else {
+		dim3 grid(cdiv(W, 128), H);
+		STEVI_LAUNCH(c, k_sgm_apply_generic, grid, 128, 0, pc, cv.st[0], cv.st[1], cv.st[2], ps, out.st[0], out.st[1], out.st[2], T, R, H, W, D, pout,
+					 wta_out ? wta_out->as<int32_t>() : (int32_t*)nullptr, wta_out ? wta_out->st[0] : 0, wta_out ? wta_out->st[1] : 0);
+	}
+	return STEVI_OK;
+}
+
+int32_t sgm_general(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
+					const stevi_margins& mg, int semantics, const View& out);
+
+int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
+				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
+				const View* wta_out) {
+	if (ndir != 4 && ndir != 8 && ndir != 16) return fail(c, STEVI_E_ARG, "sgm: n_directions must be 4, 8 or 16");
+	if (cv.ndim != 3 || (cv.dtype != STEVI_U16 && cv.dtype != STEVI_F32))
+		return fail(c, STEVI_E_DTYPE, "sgm: cost volume must be (H,W,D) u16 or f32");
+	if (out.ndim != 3 || out.dtype != STEVI_F32 || out.shape[0] != cv.shape[0] || out.shape[1] != cv.shape[1] || out.shape[2] != cv.shape[2])
+		return fail(c, STEVI_E_SHAPE, "sgm: out must be an f32 volume of the same shape");
+	if (strategy != STEVI_COST && strategy != STEVI_SCORE) return fail(c, STEVI_E_ARG, "sgm: bad strategy");
+	if (mg.left < 0 || mg.right < 0 || mg.top < 0 || mg.bottom < 0) return fail(c, STEVI_E_ARG, "sgm: negative margins");
+	if (cv.shape[0] == 0 || cv.shape[1] == 0 || cv.shape[2] == 0) return STEVI_OK;
+	if (cv.shape[0] > 65535) return fail(c, STEVI_E_UNSUPPORTED, "sgm: more than 65535 rows");
+	const bool pout_int = Pout == rintf(Pout) && fabsf(Pout) <= 1.0e6f;
+	if (semantics == STEVI_COMPAT && strategy == STEVI_COST && cv.dtype == STEVI_U16 && pout_int) {
+		int32_t s = sgm_collapsed(c, cv, ndir, (int)Pout, mg, out, gmap_ready, max_cost_hint, wta_out);
+		if (s != STEVI_FALLBACK) return s;
+	}
+	STEVI_TRY(sgm_general(c, cv, ndir, strategy, P1, P2, Pout, mg, semantics, out));
+	if (wta_out) STEVI_TRY(wta_dev(c, out, strategy, *wta_out));
+	return STEVI_OK;
+}
+
+} // namespace stevi
