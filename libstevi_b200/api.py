@@ -106,6 +106,8 @@ class Context:
         if torch_stream:
             import torch
             stream = torch.cuda.current_stream(device).cuda_stream
+            if not stream:
+                stream = 1  # torch's default stream is the legacy stream: cudaStreamLegacy == (cudaStream_t)0x1
         self._h = ctypes.c_void_p()
         rc = lib.stevi_ctx_create(int(device), ctypes.c_void_p(stream), ctypes.byref(self._h))
         if rc != OK:
