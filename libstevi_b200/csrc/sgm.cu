@@ -124,12 +124,18 @@ __global__ void __launch_bounds__(256) k_sgm_gmap_generic(const uint16_t* __rest
 	if (lane == 0) g[pix] = gm;
 }
 
-// Scalar recurrences m(p) = g(p) - m(prev) along every live line of every direction: one thread per line, loads of g
-// batched 8 ahead (they do not depend on the recurrence). T(p) += m(prev), R(p) += 1; integer atomics, so the result
-// does not depend on the schedule. blockIdx.y = direction slot in the reference's call order.
+// Scalar recurrences m(p) = g(p) - m(prev) along every live line: T(p) += m(prev), R(p) += 1 per pass; integer atomics,
+// so the result does not depend on the schedule. Three kernels share the work:
+//   k_sgm_pathsum_sweep  vertical and diagonal directions: a thread per line, all threads of a warp on the same image
+//                        row at the same time, so every load and atomic of a warp touches one contiguous segment;
+//   k_sgm_pathsum_rows   horizontal directions: a warp per row, 32 columns per step through a signed warp scan
+//                        (m_k = (-1)^k * sum_{t<=k} (-1)^t g_t);
+//   k_sgm_pathsum        the generic line walker below, kept for the eight extra directions of the 16-direction set.
+// Generic walker: one thread per line, loads of g batched 8 ahead (they do not depend on the recurrence).
+// blockIdx.y + slot0 = direction slot in the reference's call order.
 __global__ void __launch_bounds__(128) k_sgm_pathsum(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
-													 int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
-	const int dir = c_sgm_order[blockIdx.y];
+													 int32_t* __restrict__ max_abs_m, const SgmGeom geom, int slot0) {
+	const int dir = c_sgm_order[slot0 + blockIdx.y];
 	const int* st = c_sgm_steps[dir];
 	const SgmLines L = sgm_lines(st, geom);
 	const int line = blockIdx.x * blockDim.x + threadIdx.x;
@@ -166,6 +172,103 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum(const int32_t* __restrict__
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1) mabs = max(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
 	if ((threadIdx.x & 31) == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
+}
+
+// number of times the reference walks a line, from which of its two start loops are live (sgm.h:329-354, Q4)
+__device__ __forceinline__ bool sgm_start_live(int start_pos, int corrected) { return start_pos == 1 || (start_pos == 2 && corrected); }
+
+__global__ void __launch_bounds__(128) k_sgm_pathsum_sweep(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+														   int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+	const int sweep_dirs[6] = {0, 1, 4, 5, 6, 7};
+	const int dir = sweep_dirs[blockIdx.y];
+	const int sv = c_sgm_steps[dir][0], sh = c_sgm_steps[dir][2];
+	const bool col_live = sgm_start_live(sgm_start_pos(sv, sv), geom.corrected);
+	const bool row_live = sh != 0 && sgm_start_live(sgm_start_pos(sh, sh), geom.corrected);
+	const int nrows = geom.H - geom.top - geom.bottom, ncols = geom.W - geom.left - geom.right;
+	if (nrows <= 0 || ncols <= 0 || (!col_live && !row_live)) return;
+	const int nlines = ncols + (sh != 0 ? nrows - 1 : 0);
+	const int t = blockIdx.x * 128 + threadIdx.x;
+	const int jlo = geom.left, jhi = geom.W - geom.right - 1;
+	// k counts rows in traversal order; the line sits on column j0 + sh*k
+	int j0 = 0, kf = 0x7fffffff, kl = 0, w = 0;
+	if (t < nlines) {
+		j0 = jlo + t - (sh > 0 ? nrows - 1 : 0);
+		kf = sh > 0 ? max(0, jlo - j0) : (sh < 0 ? max(0, j0 - jhi) : 0);
+		kl = sh > 0 ? min(nrows, jhi + 1 - j0) : (sh < 0 ? min(nrows, j0 - jlo + 1) : nrows);
+		if (kf == 0) {
+			w = col_live ? 1 : 0;
+			const bool corner = sh != 0 && j0 == (sh > 0 ? jlo : jhi);
+			if (corner && row_live) w = geom.corrected ? 1 : w + 1;
+		} else w = row_live ? 1 : 0;
+		if (w == 0 || kf >= kl) { kf = 0x7fffffff; kl = 0; }
+	}
+	const int k_begin = __reduce_min_sync(0xffffffffu, kf), k_end = __reduce_max_sync(0xffffffffu, kl);
+	int m_prev = 0, mabs = 0;
+	for (int k0 = k_begin; k0 < k_end; k0 += 16) {
+		int gv[16];
+#pragma unroll
+		for (int u = 0; u < 16; u++) {
+			const int k = k0 + u;
+			const int i = sv > 0 ? geom.top + k : geom.H - geom.bottom - 1 - k;
+			gv[u] = (k >= kf && k < kl) ? __ldg(g + (int64_t)i * geom.W + j0 + sh * k) : 0;
+		}
+#pragma unroll
+		for (int u = 0; u < 16; u++) {
+			const int k = k0 + u;
+			if (k >= kf && k < kl) {
+				const int i = sv > 0 ? geom.top + k : geom.H - geom.bottom - 1 - k;
+				const int64_t pos = (int64_t)i * geom.W + j0 + sh * k;
+				atomicAdd(T + pos, w * m_prev);
+				atomicAdd(R + pos, w);
+				m_prev = gv[u] - m_prev;
+				mabs = max(mabs, abs(m_prev));
+			}
+		}
+	}
+	mabs = __reduce_max_sync(0xffffffffu, mabs);
+	if ((threadIdx.x & 31) == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
+}
+
+__global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+														  int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+	const int dir = 2 + blockIdx.y; // Left2Right, Right2Left
+	const int sh = c_sgm_steps[dir][2];
+	if (!sgm_start_live(sgm_start_pos(sh, sh), geom.corrected)) return;
+	const int nrows = geom.H - geom.top - geom.bottom, ncols = geom.W - geom.left - geom.right;
+	const int lane = threadIdx.x & 31;
+	const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+	if (row >= nrows || ncols <= 0) return;
+	const int64_t base = (int64_t)(geom.top + row) * geom.W;
+	int carry = 0, mabs = 0;
+	for (int c0 = 0; c0 < ncols; c0 += 128) {
+		int gv[4];
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			const int kk = c0 + u * 32 + lane;
+			const int j = sh > 0 ? geom.left + kk : geom.W - geom.right - 1 - kk;
+			gv[u] = kk < ncols ? __ldg(g + base + j) : 0;
+		}
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			const int kk = c0 + u * 32 + lane;
+			const int h = (kk & 1) ? -gv[u] : gv[u];
+			int P = h;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) { const int n = __shfl_up_sync(0xffffffffu, P, o); if (lane >= o) P += n; }
+			P += carry;
+			if (kk < ncols) {
+				const int Pprev = P - h;
+				const int m_prev = (kk & 1) ? Pprev : -Pprev; // m_{k-1} = (-1)^(k-1) * P_{k-1}; zero for k = 0
+				const int j = sh > 0 ? geom.left + kk : geom.W - geom.right - 1 - kk;
+				atomicAdd(T + base + j, m_prev);
+				atomicAdd(R + base + j, 1);
+				mabs = max(mabs, abs(P));
+			}
+			carry = __shfl_sync(0xffffffffu, P, 31);
+		}
+	}
+	mabs = __reduce_max_sync(0xffffffffu, mabs);
+	if (lane == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
 }
 
 // S = (1+R)*C + R*pout*[j+d >= W] - T on the reference's [H][D][W] layout (column stride 1 in and out): a thread owns 8
@@ -275,8 +378,17 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 	}
 	SgmGeom geom{H, W, mg.top, mg.bottom, mg.left, mg.right, 0};
 	{
-		dim3 grid(cdiv(H + W, 128), ndir);
-		STEVI_LAUNCH(c, k_sgm_pathsum, grid, 128, 0, g, T, R, d_max, geom);
+		const int nrows = H - mg.top - mg.bottom;
+		dim3 gsweep(cdiv(H + W, 128), ndir == 4 ? 2 : 6);
+		STEVI_LAUNCH(c, k_sgm_pathsum_sweep, gsweep, 128, 0, g, T, R, d_max, geom);
+		if (nrows > 0) {
+			dim3 grows(cdiv(nrows, 4), 2);
+			STEVI_LAUNCH(c, k_sgm_pathsum_rows, grows, 128, 0, g, T, R, d_max, geom);
+		}
+		if (ndir == 16) {
+			dim3 gwalk(cdiv(H + W, 128), 8);
+			STEVI_LAUNCH(c, k_sgm_pathsum, gwalk, 128, 0, g, T, R, d_max, geom, 8);
+		}
 	}
 	// exactness bound of the float arithmetic this replaces (all magnitudes < 2^24)
 	const long max_c = max_cost_hint >= 0 ? max_cost_hint : 65535;
