@@ -86,6 +86,11 @@ STEVI_API int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
 STEVI_API const char* stevi_last_error(stevi_ctx* ctx);
 /* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */
 STEVI_API int64_t stevi_ctx_launch_count(stevi_ctx* ctx);
+/* per-kernel device timing for benchmarks: when enabled every kernel launch of this ctx is bracketed by a CUDA event
+ * pair on the ctx stream; the report is "name<TAB>milliseconds<NL>" per launch since the previous report (the call
+ * synchronises the stream). Leave it off for production calls. */
+STEVI_API int32_t stevi_ctx_set_timing(stevi_ctx* ctx, int32_t enable);
+STEVI_API const char* stevi_ctx_timing_report(stevi_ctx* ctx);
 /* bytes currently held by the workspace arena */
 STEVI_API int64_t stevi_ctx_workspace_bytes(stevi_ctx* ctx);
 STEVI_API int32_t stevi_device_count(void);

@@ -53,6 +53,7 @@ def _load():
     lib.stevi_last_error.restype = ctypes.c_char_p
     lib.stevi_version.restype = ctypes.c_char_p
     lib.stevi_ctx_stream.restype = ctypes.c_void_p
+    lib.stevi_ctx_timing_report.restype = ctypes.c_char_p
     lib.stevi_ctx_launch_count.restype = ctypes.c_int64
     lib.stevi_ctx_workspace_bytes.restype = ctypes.c_int64
     return lib
@@ -131,6 +132,14 @@ class Context:
 
     def synchronize(self):
         self.check(lib.stevi_ctx_synchronize(self._h))
+
+    def set_timing(self, enable):
+        self.check(lib.stevi_ctx_set_timing(self._h, 1 if enable else 0))
+
+    def timing_report(self):
+        """[(kernel name, ms)] per launch since the previous report (synchronises the stream)."""
+        txt = lib.stevi_ctx_timing_report(self._h).decode()
+        return [(ln.split("\t")[0], float(ln.split("\t")[1])) for ln in txt.splitlines() if ln]
 
     @property
     def launches(self):

@@ -33,8 +33,8 @@ int32_t census_cv_dev(stevi_ctx* c, const View& l, const View& r, int hr, int vr
 	View cl, cr;
 	STEVI_TRY(alloc_census(c, l.shape[0], l.shape[1], nw, cl));
 	STEVI_TRY(alloc_census(c, r.shape[0], r.shape[1], nw, cr));
-	STEVI_TRY(census_transform_dev(c, l, hr, vr, semantics, cl));
-	STEVI_TRY(census_transform_dev(c, r, hr, vr, semantics, cr));
+	const View imgs[2] = {l, r}, cens[2] = {cl, cr};
+	STEVI_TRY(census_transform_pair_dev(c, imgs, cens, 2, hr, vr, semantics));
 	// words past n_written are zero on both sides (and round to zero): no need to compare them
 	return hamming_cv_dev(c, cl, cr, census_n_written(hr, vr, semantics), D, direction, semantics == STEVI_COMPAT, out, gmap, pout_i);
 }

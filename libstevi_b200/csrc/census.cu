@@ -14,13 +14,21 @@ namespace stevi {
 // ---------------------------------------------------------------------------------------------------------------
 // census transform: one thread per pixel, 32x8 pixel tile plus the (2*h_r, 2*v_r) apron staged in shared memory
 // ---------------------------------------------------------------------------------------------------------------
+struct CensusImage { const void* img; int64_t si, sj; int H, W; uint32_t* out; int64_t so0, so1, so2; };
+struct CensusPair { CensusImage im[2]; };
+
+// blockIdx.z selects the image, so both images of a pair go through one launch
 template<typename T>
-__global__ void __launch_bounds__(256) k_census_transform(const T* __restrict__ img, int64_t si, int64_t sj, int H, int W,
-														  int hr, int vr, int n_words, int n_written,
-														  uint32_t* __restrict__ out, int64_t so0, int64_t so1, int64_t so2) {
+__global__ void __launch_bounds__(256) k_census_transform(const CensusPair pr, int hr, int vr, int n_words, int n_written, int c_end) {
 	extern __shared__ unsigned char smem_raw[];
 	T* tile = reinterpret_cast<T*>(smem_raw);
-	const int hs = 2 * hr + 1, vs = 2 * vr + 1, F = hs * vs;
+	const CensusImage& I = pr.im[blockIdx.z];
+	const T* __restrict__ img = static_cast<const T*>(I.img);
+	const int64_t si = I.si, sj = I.sj, so0 = I.so0, so1 = I.so1, so2 = I.so2;
+	const int H = I.H, W = I.W;
+	uint32_t* __restrict__ out = I.out;
+	if ((int)blockIdx.x * 32 >= W || (int)blockIdx.y * 8 >= H) return;
+	const int hs = 2 * hr + 1;
 	const int tw = 32 + 2 * hr, th = 8 + 2 * vr;
 	const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 8;
 	for (int t = threadIdx.y * 32 + threadIdx.x; t < tw * th; t += 256) {
@@ -39,7 +47,7 @@ __global__ void __launch_bounds__(256) k_census_transform(const T* __restrict__ 
 	uint32_t word = 0;
 	int b = 0, ch = 0;
 	int k = 0, l = 1; // c = hs*k + l, starting at c = 1
-	for (int c = 1; c < F; c++) {
+	for (int c = 1; c < c_end; c++) { // comparisons past the last written word are never looked at
 		T v = base[k * tw + l];
 		word |= (ref > v ? 1u : 0u) << b;
 		b++;
@@ -59,28 +67,48 @@ int32_t census_n_written(int hr, int vr, int semantics) {
 	return semantics == STEVI_COMPAT ? ncmp / 32 : (ncmp + 31) / 32;
 }
 
-int32_t census_transform_dev(stevi_ctx* c, const View& img, int hr, int vr, int semantics, const View& out) {
+static int32_t census_check(stevi_ctx* c, const View& img, int hr, int vr, const View& out) {
 	if (img.ndim != 2) return fail(c, STEVI_E_UNSUPPORTED, "census: only 2-D images are supported");
 	if (hr < 0 || vr < 0 || hr > 31 || vr > 31) return fail(c, STEVI_E_ARG, "census: radius out of range");
-	const int H = img.shape[0], W = img.shape[1];
 	const int F = (2 * hr + 1) * (2 * vr + 1);
 	if (F <= 1) return fail(c, STEVI_E_SHAPE, "census: a single feature channel has no census (census.h:75-77)");
 	const int nw = census_n_words(hr, vr);
-	if (out.ndim != 3 || out.shape[0] != H || out.shape[1] != W || out.shape[2] != nw || out.dtype != STEVI_U32)
+	if (out.ndim != 3 || out.shape[0] != img.shape[0] || out.shape[1] != img.shape[1] || out.shape[2] != nw || out.dtype != STEVI_U32)
 		return fail(c, STEVI_E_SHAPE, "census: out must be (H,W,%d) u32", nw);
-	if (H == 0 || W == 0) return STEVI_OK;
-	dim3 block(32, 8), grid(cdiv(W, 32), cdiv(H, 8));
-	const int nwr = census_n_written(hr, vr, semantics);
-	if (img.dtype == STEVI_U8) {
-		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(uint8_t);
-		STEVI_LAUNCH(c, k_census_transform<uint8_t>, grid, block, sm, img.as<uint8_t>(), img.st[0], img.st[1], H, W, hr, vr,
-					 nw, nwr, out.as<uint32_t>(), out.st[0], out.st[1], out.st[2]);
-	} else if (img.dtype == STEVI_F32) {
-		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(float);
-		STEVI_LAUNCH(c, k_census_transform<float>, grid, block, sm, img.as<float>(), img.st[0], img.st[1], H, W, hr, vr,
-					 nw, nwr, out.as<uint32_t>(), out.st[0], out.st[1], out.st[2]);
-	} else return fail(c, STEVI_E_DTYPE, "census: image dtype must be u8 or f32");
+	if (img.dtype != STEVI_U8 && img.dtype != STEVI_F32) return fail(c, STEVI_E_DTYPE, "census: image dtype must be u8 or f32");
 	return STEVI_OK;
+}
+
+// one launch for up to two images of the same dtype
+int32_t census_transform_pair_dev(stevi_ctx* c, const View* imgs, const View* outs, int n, int hr, int vr, int semantics) {
+	CensusPair pr;
+	int Hm = 0, Wm = 0;
+	for (int k = 0; k < n; k++) {
+		STEVI_TRY(census_check(c, imgs[k], hr, vr, outs[k]));
+		if (imgs[k].dtype != imgs[0].dtype) return fail(c, STEVI_E_DTYPE, "census: images of a pair must share a dtype");
+		pr.im[k] = CensusImage{imgs[k].p, imgs[k].st[0], imgs[k].st[1], imgs[k].shape[0], imgs[k].shape[1],
+							   outs[k].as<uint32_t>(), outs[k].st[0], outs[k].st[1], outs[k].st[2]};
+		Hm = std::max(Hm, imgs[k].shape[0]);
+		Wm = std::max(Wm, imgs[k].shape[1]);
+	}
+	if (n == 1) pr.im[1] = pr.im[0];
+	if (Hm == 0 || Wm == 0) return STEVI_OK;
+	const int F = (2 * hr + 1) * (2 * vr + 1);
+	const int nw = census_n_words(hr, vr), nwr = census_n_written(hr, vr, semantics);
+	const int c_end = std::min(F, 1 + 32 * nwr);
+	dim3 block(32, 8), grid(cdiv(Wm, 32), cdiv(Hm, 8), n);
+	if (imgs[0].dtype == STEVI_U8) {
+		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(uint8_t);
+		STEVI_LAUNCH(c, k_census_transform<uint8_t>, grid, block, sm, pr, hr, vr, nw, nwr, c_end);
+	} else {
+		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(float);
+		STEVI_LAUNCH(c, k_census_transform<float>, grid, block, sm, pr, hr, vr, nw, nwr, c_end);
+	}
+	return STEVI_OK;
+}
+
+int32_t census_transform_dev(stevi_ctx* c, const View& img, int hr, int vr, int semantics, const View& out) {
+	return census_transform_pair_dev(c, &img, &out, 1, hr, vr, semantics);
 }
 
 } // namespace stevi

@@ -24,6 +24,12 @@ struct stevi_ctx {
 	size_t cur = 0;   // index of the block being bumped
 	size_t off = 0;   // offset inside it
 	size_t high = 0;  // bytes handed out during the current call
+	// optional per-kernel timing (stevi_ctx_set_timing): one CUDA event pair per launch on the ctx stream
+	bool timing = false;
+	struct Timed { const char* name; cudaEvent_t e0, e1; };
+	std::vector<Timed> timed;
+	std::vector<cudaEvent_t> event_pool;
+	std::string report;
 };
 
 namespace stevi {
@@ -45,9 +51,14 @@ inline int32_t fail(stevi_ctx* c, int32_t code, const char* fmt, ...) {
 
 // kernel<<<grid, block, smem, ctx->stream>>>(args...) with launch counting and error check
 #define STEVI_LAUNCH(c, kern, grid, block, smem, ...) do { \
+	if ((c)->timing) stevi::timing_begin((c), #kern); \
 	kern<<<(grid), (block), (smem), (c)->stream>>>(__VA_ARGS__); \
+	if ((c)->timing) stevi::timing_end((c)); \
 	(c)->launches++; \
 	STEVI_CUDA((c), cudaPeekAtLastError()); } while (0)
+
+void timing_begin(stevi_ctx* c, const char* name);
+void timing_end(stevi_ctx* c);
 
 inline size_t dtype_size(int dt) {
 	switch (dt) {

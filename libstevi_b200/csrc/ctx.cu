@@ -48,6 +48,21 @@ int32_t arena_alloc(stevi_ctx* c, size_t bytes, void** out) {
 	return STEVI_OK;
 }
 
+static cudaEvent_t take_event(stevi_ctx* c) {
+	cudaEvent_t e = nullptr;
+	if (!c->event_pool.empty()) { e = c->event_pool.back(); c->event_pool.pop_back(); }
+	else cudaEventCreate(&e);
+	return e;
+}
+
+void timing_begin(stevi_ctx* c, const char* name) {
+	stevi_ctx::Timed t{name, take_event(c), take_event(c)};
+	cudaEventRecord(t.e0, c->stream);
+	c->timed.push_back(t);
+}
+
+void timing_end(stevi_ctx* c) { cudaEventRecord(c->timed.back().e1, c->stream); }
+
 int32_t Stager::check(const stevi_array* a, const char* name) {
 	if (!a || !a->data) return fail(c_, STEVI_E_ARG, "%s: null array", name);
 	if (a->ndim < 1 || a->ndim > STEVI_MAX_DIMS) return fail(c_, STEVI_E_ARG, "%s: ndim %d", name, a->ndim);
@@ -141,6 +156,8 @@ int32_t stevi_ctx_destroy(stevi_ctx* c) {
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
 	for (auto& b : c->blocks) cudaFree(b.p);
+	for (auto& t : c->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
+	for (auto e : c->event_pool) cudaEventDestroy(e);
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	delete c;
 	return STEVI_OK;
@@ -173,6 +190,31 @@ int64_t stevi_ctx_workspace_bytes(stevi_ctx* c) {
 	size_t t = 0;
 	for (auto& b : c->blocks) t += b.cap;
 	return (int64_t)t;
+}
+
+int32_t stevi_ctx_set_timing(stevi_ctx* c, int32_t enable) {
+	if (!c) return STEVI_E_ARG;
+	c->timing = enable != 0;
+	return STEVI_OK;
+}
+
+// "kernel name\tms\n" per launch recorded since the last report, in launch order; clears the record
+const char* stevi_ctx_timing_report(stevi_ctx* c) {
+	if (!c) return "";
+	cudaStreamSynchronize(c->stream);
+	c->report.clear();
+	char buf[64];
+	for (auto& t : c->timed) {
+		float ms = 0.f;
+		cudaEventElapsedTime(&ms, t.e0, t.e1);
+		c->report += t.name;
+		snprintf(buf, sizeof buf, "\t%.6f\n", ms);
+		c->report += buf;
+		c->event_pool.push_back(t.e0);
+		c->event_pool.push_back(t.e1);
+	}
+	c->timed.clear();
+	return c->report.c_str();
 }
 
 int32_t stevi_host_alloc(size_t bytes, void** out) {

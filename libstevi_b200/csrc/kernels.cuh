@@ -9,6 +9,7 @@ namespace stevi {
 int32_t census_n_words(int hr, int vr);
 int32_t census_n_written(int hr, int vr, int semantics);
 int32_t census_transform_dev(stevi_ctx* c, const View& img, int hr, int vr, int semantics, const View& out);
+int32_t census_transform_pair_dev(stevi_ctx* c, const View* imgs, const View* outs, int n, int hr, int vr, int semantics);
 // feat_* (H,W*,nw) u32; n_cmp = how many leading words to compare (the rest are known to be zero on both sides);
 // gmap (optional, int32 [H*Ws] dense): min_d (2*C + pout_i*[j+d >= Ws]) for the collapsed SGM (sgm.cu)
 int32_t hamming_cv_dev(stevi_ctx* c, const View& feat_l, const View& feat_r, int n_cmp, int D, int direction,
