@@ -1,0 +1,273 @@
+#!/usr/bin/env python
+"""Benchmark of the dense-stereo hot path (BASELINE.json metric: Gdisp/s = W*H*D / s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c5]
+
+One step = one pass of census 9x7 -> Hamming cost volume (u16) -> SGM 8 directions -> WTA -> disparity over one
+synthetic rectified pair (BASELINE.json configs[1]: 1920x1080, D=256; `--workload c5`: 1280x720, D=128).
+  value  whole-job Gdisp/s with the pair already resident in HBM; the cost volume, the aggregated SGM volume and the
+         disparity map are all written to HBM (what the reference's API returns as arrays).
+  e2e    the same call through the C ABI with HOST operands: pinned host images in, host disparity map out, copies inside
+         the timed region (the volumes stay in the device workspace).
+  roofline  the dominant kernel (SGM apply + fused WTA), timed per launch with CUDA events on the launching stream.
+  cpu_baseline / --impl reference  the reference's own CPU code (oracle/_ref, compiled from the unmodified LibStevi
+         headers) on the host cores, on a bounded row band of the same workload.
+N > 1 (torchrun): independent pairs are sharded across ranks, no data-path collective (weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (H, W, D, h_radius, v_radius, seed, d_max)
+    "c2": dict(H=1080, W=1920, D=256, hr=4, vr=3, seed=2, d_max=200,
+               name="census9x7+SGM8+WTA 1920x1080 D=256 u16 costs (BASELINE configs[1])"),
+    "c5": dict(H=720, W=1280, D=128, hr=4, vr=3, seed=1000, d_max=100,
+               name="census9x7+SGM8+WTA 1280x720 D=128 u16 costs (BASELINE configs[4], one pair per step per GPU)"),
+}
+P1, P2, POUT, NDIR = 10.0, 120.0, 100.0, 8
+# algorithmic bytes per disparity cell. CV: 2 written; SGM: 2 read + 4 written; WTA: 4 read.
+BYTES_PER_CELL_PIPELINE = 12
+BYTES_PER_CELL_SGM_APPLY = 6  # the dominant kernel: reads C (u16), writes S (f32); the WTA rides along for free
+
+
+def read_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([x.strip() for x in ln.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows if len(r) >= 7 for k in range(4) if r[3 + k].lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_run(wl, steps, warmup, band_rows=None, budget_s=15.0):
+    """The reference's own CPU implementation (oracle/_ref: unmodified LibStevi headers) on a row band of the workload."""
+    import oracle as O
+    from libstevi_b200 import synth
+    chk, kind = (O.ref, "reference") if O.ref is not None else (O.port, "port")
+    cores = os.cpu_count() or 1
+    chk.set_num_threads(cores)
+    H, W, D = wl["H"], wl["W"], wl["D"]
+    L, R, _ = synth.stereo_pair(H, W, wl["seed"], d_bg=8, d_sq=32, d_max=wl["d_max"])
+    if band_rows is None:
+        # the reference SGM is O(D^2) per pixel and line (~0.3 s per 1920-pixel row at D=256 on 8 cores): size the band
+        # so that all (warmup + steps) passes take about `budget_s` seconds of CPU work
+        t_row = 0.31 * (D / 256.0) ** 2 * (W / 1920.0) * 8.0 / cores
+        band_rows = int(budget_s / (max(steps + warmup, 1) * t_row))
+        band_rows = max(4, min(band_rows, H))
+    i0 = (H - band_rows) // 2
+    Lb, Rb = np.ascontiguousarray(L[i0:i0 + band_rows]), np.ascontiguousarray(R[i0:i0 + band_rows])
+
+    def step():
+        cv = chk.cost_volume(O.CENSUS, Lb, Rb, wl["hr"], wl["vr"], D)
+        sg = chk.sgm(cv, NDIR, O.COST, P1, P2, POUT)
+        return chk.index_to_disp(chk.wta(sg, O.COST))
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    cells = band_rows * W * D
+    return {"value": cells / dt / 1e9, "unit": "Gdisp/s", "cores": cores, "kind": kind,
+            "sample": f"rows {i0}..{i0 + band_rows} of the {W}x{H} pair ({band_rows}x{W}xD{D} cells per step), "
+                      f"{steps} step(s), {dt:.2f} s/step"}, dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    H, W, D = wl["H"], wl["W"], wl["D"]
+    cells = H * W * D
+    config = {"workload": wl["name"], "H": H, "W": W, "D": D, "census_window": "9x7", "sgm_directions": NDIR,
+              "P1": P1, "P2": P2, "Pout": POUT, "semantics": "compat (bit-exact with the reference CPU code)",
+              "pairs_per_step_per_gpu": 1, "sharding": "independent pairs per rank, no collective"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        base, dt = cpu_reference_run(wl, args.steps, args.warmup, budget_s=150.0)
+        line = {"impl": "reference", "metric": "Gdisp/s (W*H*D/s) census+SGM+WTA", "value": base["value"], "unit": "Gdisp/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+                "config": config, "cpu_baseline": base,
+                "e2e": {"value": base["value"], "unit": "Gdisp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    from libstevi_b200 import api, synth
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    # each rank owns its own pair (different seed): weak scaling over independent pairs
+    L, R, _ = synth.stereo_pair(H, W, wl["seed"] + rank, d_bg=8, d_sq=32, d_max=wl["d_max"])
+    dl, dr = torch.from_numpy(L).to(dev), torch.from_numpy(R).to(dev)
+    ctx = api.Context(local_rank, torch_stream=True)
+    cv = torch.empty((H, D, W), dtype=torch.uint16, device=dev).permute(0, 2, 1)   # [H][D][W], cross_correlations.h:220
+    sg = torch.empty((H, D, W), dtype=torch.float32, device=dev).permute(0, 2, 1)
+    disp = torch.empty((H, W), dtype=torch.int32, device=dev)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step_device():
+        api.censusSgmPipeline(dl, dr, wl["hr"], wl["vr"], D, P1, P2, POUT, NDIR, out=(cv, sg, disp), ctx=ctx)
+
+    hl, hr_ = torch.from_numpy(L).pin_memory(), torch.from_numpy(R).pin_memory()
+    hdisp = torch.empty((H, W), dtype=torch.int32).pin_memory()
+    nl, nr, nd = hl.numpy(), hr_.numpy(), hdisp.numpy()
+
+    def step_host():
+        api.censusSgmPipeline(nl, nr, wl["hr"], wl["vr"], D, P1, P2, POUT, NDIR, out=nd, ctx=ctx)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step, steps, sampler=None):
+        """Sum of per-step CUDA-event times; L2 flushed (512 MB memset) between steps, outside the event pairs."""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        if sampler:
+            sampler.start()
+        for e0, e1 in evs:
+            flush.zero_()
+            e0.record()
+            step()
+            e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+        if dist is not None:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, clocks
+
+    for _ in range(warmup):
+        step_device()
+    n0 = ctx.launches
+    ms_dev, clocks = timed(step_device, args.steps, ClockSampler(local_rank) if rank == 0 else None)
+    launches = ctx.launches - n0
+
+    for _ in range(warmup):
+        step_host()
+    ms_host, _ = timed(step_host, args.steps)
+
+    # dominant kernel, per launch, CUDA events on the launching stream (second pass with the ctx's event hooks on)
+    ctx.set_timing(True)
+    per_kernel = {}
+    for _ in range(max(3, min(args.steps, 10))):
+        flush.zero_()
+        step_device()
+        for name, ms in ctx.timing_report():
+            per_kernel.setdefault(name, []).append(ms)
+    ctx.set_timing(False)
+    kern_ms = {k: float(np.mean(v)) for k, v in per_kernel.items()}
+    dom = max(kern_ms, key=kern_ms.get)
+    peak, peak_src = read_peaks()
+    dom_bytes = cells * BYTES_PER_CELL_SGM_APPLY if "sgm_apply" in dom else None
+
+    # correctness guard inside the bench: device and host paths must agree bit for bit
+    torch.cuda.synchronize()
+    same = bool(np.array_equal(disp.cpu().numpy(), nd))
+
+    if rank == 0:
+        value = world * cells * args.steps / (ms_dev * 1e-3) / 1e9
+        e2e = world * cells * args.steps / (ms_host * 1e-3) / 1e9
+        line = {"metric": "Gdisp/s (W*H*D/s) census+SGM+WTA", "value": value, "unit": "Gdisp/s", "n_gpus": world,
+                "steps": args.steps, "warmup": warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u16", "data": "synthetic", "config": config,
+                "e2e": {"value": e2e, "unit": "Gdisp/s", "h2d_bytes_per_step": int(nl.nbytes + nr.nbytes),
+                        "d2h_bytes_per_step": int(nd.nbytes), "ms_per_step": ms_host / args.steps},
+                "gpu_launches": int(launches), "clocks": clocks,
+                "kernels_ms": {k.split("<")[0].strip("()"): round(v, 4) for k, v in kern_ms.items()},
+                "pipeline_algorithmic_GBps": cells * BYTES_PER_CELL_PIPELINE / (ms_dev / args.steps * 1e-3) / 1e9,
+                "host_device_paths_agree": same}
+        config["l2"] = "512 MB memset between timed steps (outside the event pairs); per-step working set 3.2 GB >> 126 MB L2"
+        if dom_bytes:
+            ach = dom_bytes / (kern_ms[dom] * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "kernel": dom.split("<")[0].strip("()"), "achieved": ach, "peak": peak,
+                                "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                                "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": kern_ms[dom]}
+        else:
+            line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
+                                "traffic": None, "peak_source": peak_src}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _ = cpu_reference_run(wl, 1, 0, budget_s=15.0)
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
