@@ -146,12 +146,10 @@ int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stev
 	if (collapse) STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &gmap));
 	STEVI_TRY(census_cv_dev(c, vl, vr_, hr, vr, D, direction, semantics, vcv, gmap, (int)Pout));
 	const int max_cost = 32 * census_n_written(hr, vr, semantics);
-	View vidx;
-	int32_t* pidx = nullptr;
-	STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &pidx));
-	vidx.p = pidx; vidx.dtype = STEVI_I32; vidx.ndim = 2; vidx.shape[0] = H; vidx.shape[1] = Ws; vidx.st[0] = Ws; vidx.st[1] = 1;
-	STEVI_TRY(sgm_dev(c, vcv, ndir, STEVI_COST, P1, P2, Pout, mg, semantics, vs, gmap, max_cost, &vidx));
-	STEVI_TRY(index_to_disp_dev(c, vidx, direction, 0, vd));
+	// the WTA rides on the last SGM pass and selectedIndexToDisp (correlation_base.h:511-532) is folded into its output
+	WtaSink sink{vd, direction == STEVI_RIGHT_TO_LEFT ? 1 : -1, 0};
+	if (vd.ndim != 2 || vd.dtype != STEVI_I32 || vd.shape[0] != H || vd.shape[1] != Ws) return fail(c, STEVI_E_SHAPE, "pipeline: disp must be (H,W) i32");
+	STEVI_TRY(sgm_dev(c, vcv, ndir, STEVI_COST, P1, P2, Pout, mg, semantics, vs, gmap, max_cost, &sink));
 	return st.finish();
 }
 

@@ -17,19 +17,21 @@ namespace stevi {
 struct CensusImage { const void* img; int64_t si, sj; int H, W; uint32_t* out; int64_t so0, so1, so2; };
 struct CensusPair { CensusImage im[2]; };
 
-// blockIdx.z selects the image, so both images of a pair go through one launch
-template<typename T>
+// blockIdx.z selects the image, so both images of a pair go through one launch. HS > 0 fixes the window width at
+// compile time (the inner loop unrolls and the shared-memory offsets become immediates); HS = 0 takes it from hr.
+template<typename T, int HS>
 __global__ void __launch_bounds__(256) k_census_transform(const CensusPair pr, int hr, int vr, int n_words, int n_written, int c_end) {
 	extern __shared__ unsigned char smem_raw[];
 	T* tile = reinterpret_cast<T*>(smem_raw);
-	const CensusImage& I = pr.im[blockIdx.z];
-	const T* __restrict__ img = static_cast<const T*>(I.img);
-	const int64_t si = I.si, sj = I.sj, so0 = I.so0, so1 = I.so1, so2 = I.so2;
-	const int H = I.H, W = I.W;
-	uint32_t* __restrict__ out = I.out;
+#define STEVI_SEL(f) (blockIdx.z ? pr.im[1].f : pr.im[0].f) // no dynamic indexing of kernel parameters (that spills them)
+	const T* __restrict__ img = static_cast<const T*>(STEVI_SEL(img));
+	const int64_t si = STEVI_SEL(si), sj = STEVI_SEL(sj), so0 = STEVI_SEL(so0), so1 = STEVI_SEL(so1), so2 = STEVI_SEL(so2);
+	const int H = STEVI_SEL(H), W = STEVI_SEL(W);
+	uint32_t* __restrict__ out = STEVI_SEL(out);
+#undef STEVI_SEL
 	if ((int)blockIdx.x * 32 >= W || (int)blockIdx.y * 8 >= H) return;
-	const int hs = 2 * hr + 1;
-	const int tw = 32 + 2 * hr, th = 8 + 2 * vr;
+	const int hs = HS > 0 ? HS : 2 * hr + 1, vs = 2 * vr + 1;
+	const int tw = 32 + hs - 1, th = 8 + 2 * vr;
 	const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 8;
 	for (int t = threadIdx.y * 32 + threadIdx.x; t < tw * th; t += 256) {
 		int ty = t / tw, tx = t - ty * tw;
@@ -45,15 +47,16 @@ __global__ void __launch_bounds__(256) k_census_transform(const CensusPair pr, i
 	const T ref = base[0];
 	uint32_t* o = out + i * so0 + j * so1;
 	uint32_t word = 0;
-	int b = 0, ch = 0;
-	int k = 0, l = 1; // c = hs*k + l, starting at c = 1
-	for (int c = 1; c < c_end; c++) { // comparisons past the last written word are never looked at
-		T v = base[k * tw + l];
-		word |= (ref > v ? 1u : 0u) << b;
-		b++;
-		if (b == 32) { if (ch < n_written) o[ch * so2] = word; ch++; word = 0; b = 0; }
-		l++;
-		if (l == hs) { l = 0; k++; }
+	int b = 0, ch = 0, c = 0; // c = hs*k + l
+	for (int k = 0; k < vs && c < c_end; k++) { // comparisons past the last written word are never looked at
+		const T* rowp = base + k * tw;
+#pragma unroll
+		for (int l = 0; l < hs; l++, c++) {
+			if (c == 0 || c >= c_end) continue;
+			word |= (ref > rowp[l] ? 1u : 0u) << b;
+			b++;
+			if (b == 32) { if (ch < n_written) o[ch * so2] = word; ch++; word = 0; b = 0; }
+		}
 	}
 	// CORRECTED semantics flush the partial word (n_written == n_words); COMPAT leaves it zero
 	if (b > 0 && ch < n_written) { o[ch * so2] = word; ch++; }
@@ -97,13 +100,25 @@ int32_t census_transform_pair_dev(stevi_ctx* c, const View* imgs, const View* ou
 	const int nw = census_n_words(hr, vr), nwr = census_n_written(hr, vr, semantics);
 	const int c_end = std::min(F, 1 + 32 * nwr);
 	dim3 block(32, 8), grid(cdiv(Wm, 32), cdiv(Hm, 8), n);
+#define STEVI_CENSUS_LAUNCH(T, HS) STEVI_LAUNCH(c, (k_census_transform<T, HS>), grid, block, sm, pr, hr, vr, nw, nwr, c_end)
+#define STEVI_CENSUS_SWITCH(T) \
+	switch (2 * hr + 1) { \
+	case 3: STEVI_CENSUS_LAUNCH(T, 3); break; \
+	case 5: STEVI_CENSUS_LAUNCH(T, 5); break; \
+	case 7: STEVI_CENSUS_LAUNCH(T, 7); break; \
+	case 9: STEVI_CENSUS_LAUNCH(T, 9); break; \
+	case 11: STEVI_CENSUS_LAUNCH(T, 11); break; \
+	default: STEVI_CENSUS_LAUNCH(T, 0); break; \
+	}
 	if (imgs[0].dtype == STEVI_U8) {
 		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(uint8_t);
-		STEVI_LAUNCH(c, k_census_transform<uint8_t>, grid, block, sm, pr, hr, vr, nw, nwr, c_end);
+		STEVI_CENSUS_SWITCH(uint8_t)
 	} else {
 		size_t sm = (size_t)(32 + 2 * hr) * (8 + 2 * vr) * sizeof(float);
-		STEVI_LAUNCH(c, k_census_transform<float>, grid, block, sm, pr, hr, vr, nw, nwr, c_end);
+		STEVI_CENSUS_SWITCH(float)
 	}
+#undef STEVI_CENSUS_SWITCH
+#undef STEVI_CENSUS_LAUNCH
 	return STEVI_OK;
 }
 
@@ -243,7 +258,10 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	}
 	if (EMIT_G) {
 #pragma unroll
-		for (int k = 0; k < 8; k++) if (j + k < p.Ws) p.gmap[(int64_t)i * p.Ws + j + k] = gmin[k];
+		for (int k = 0; k < 8; k++) if (j + k < p.Ws) {
+			if (gridDim.z > 1) atomicMin(p.gmap + (int64_t)i * p.Ws + j + k, gmin[k]); // the host pre-filled the map
+			else p.gmap[(int64_t)i * p.Ws + j + k] = gmin[k];
+		}
 	}
 }
 
@@ -292,13 +310,16 @@ static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
 	}
 	const int xb = cdiv(p.Ws, 1024);
 	int dchunk = (p.D + 7) / 8 * 8;
-	const long want = 4L * c->sm_count;
-	if (!p.gmap && (long)xb * p.H < want) {
+	// many short blocks (>= 8 waves of 7 resident blocks per SM) so that the last partial wave costs little
+	const long want = 8L * 7 * c->sm_count;
+	if ((long)xb * p.H < want) {
 		long parts = (want + (long)xb * p.H - 1) / ((long)xb * p.H);
 		int dc = (int)((p.D + parts - 1) / parts);
 		dc = std::max(32, (dc + 7) / 8 * 8);
 		dchunk = std::min(dchunk, dc);
 	}
+	if (p.gmap && dchunk < p.D) // chunks merge their minima with atomicMin
+		STEVI_CUDA(c, cudaMemsetAsync(p.gmap, 0x7f, (size_t)p.H * p.Ws * sizeof(int32_t), c->stream));
 	p.dchunk = dchunk;
 	const int groups = (1024 + dchunk + 8) / 8 + 1;
 	int P = groups;

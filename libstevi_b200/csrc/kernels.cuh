@@ -16,9 +16,11 @@ int32_t hamming_cv_dev(stevi_ctx* c, const View& feat_l, const View& feat_r, int
 					   bool round_target, const View& out, int32_t* gmap, int pout_i);
 
 // sgm.cu
+// optional fused winner-take-all of the aggregated volume: out(i,j) = sign * argmin_d + offset (selectedIndexToDisp folded in)
+struct WtaSink { View out; int sign; int offset; };
 int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
 				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
-				const View* wta_out);
+				const WtaSink* wta);
 
 // wta.cu
 int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);

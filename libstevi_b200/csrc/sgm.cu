@@ -274,12 +274,13 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restr
 // S = (1+R)*C + R*pout*[j+d >= W] - T on the reference's [H][D][W] layout (column stride 1 in and out): a thread owns 8
 // consecutive columns; per disparity one 16-byte load of costs and two 16-byte stores of floats. With WTA the running
 // arg-min (`<=`: last minimum wins, correlation_base.h:446) is kept along the way, so the aggregated volume is not read again.
+// blockIdx.z splits the disparity range so that the grid is many short blocks (no tail wave).
 template<bool WTA>
 __global__ void __launch_bounds__(128) k_sgm_apply_rows(const uint16_t* __restrict__ cv, int64_t c0, int64_t cd,
 														float* __restrict__ S, int64_t s0, int64_t sd,
 														const int32_t* __restrict__ T, const int32_t* __restrict__ R,
 														int H, int W, int D, int dchunk, int pout,
-														int32_t* __restrict__ idx, int64_t i0, int64_t i1) {
+														unsigned long long* __restrict__ keys) {
 	const int j = (blockIdx.x * 128 + threadIdx.x) * 8;
 	const int i = blockIdx.y;
 	if (j >= W) return; // W is a multiple of 8 on this path
@@ -313,16 +314,31 @@ __global__ void __launch_bounds__(128) k_sgm_apply_rows(const uint16_t* __restri
 		__stcs(reinterpret_cast<float4*>(ps + d * sd) + 1, make_float4(o[4], o[5], o[6], o[7]));
 	}
 	if (WTA) {
+		// the disparity range is split over blockIdx.z: merge through one 64-bit atomicMin per pixel and chunk on the key
+		// (S biased to unsigned) << 32 | (2^32-1 - d): smallest S wins, equal S -> largest d, i.e. the reference's `<=` rule
 #pragma unroll
-		for (int k = 0; k < 8; k++) idx[i * i0 + (j + k) * i1] = bd[k];
+		for (int k = 0; k < 8; k++) {
+			const unsigned long long key = ((unsigned long long)((uint32_t)best[k] ^ 0x80000000u) << 32) | (0xffffffffu - (uint32_t)bd[k]);
+			atomicMin(keys + (int64_t)i * W + j + k, key);
+		}
 	}
+}
+
+__global__ void __launch_bounds__(256) k_wta_decode_keys(const unsigned long long* __restrict__ keys, int H, int W, int sign, int offset,
+														 int32_t* __restrict__ out, int64_t o0, int64_t o1) {
+	const int j = blockIdx.x * 256 + threadIdx.x;
+	const int i = blockIdx.y;
+	if (j >= W) return;
+	const int d = (int)(0xffffffffu - (uint32_t)keys[(int64_t)i * W + j]);
+	out[i * o0 + j * o1] = sign * d + offset;
 }
 
 // any strides: one thread per pixel
 __global__ void __launch_bounds__(128) k_sgm_apply_generic(const uint16_t* __restrict__ cv, int64_t c0, int64_t c1, int64_t cd,
 														   float* __restrict__ S, int64_t s0, int64_t s1, int64_t sd,
 														   const int32_t* __restrict__ T, const int32_t* __restrict__ R,
-														   int H, int W, int D, int pout, int32_t* __restrict__ idx, int64_t i0, int64_t i1) {
+														   int H, int W, int D, int pout, int32_t* __restrict__ idx, int64_t i0, int64_t i1,
+														   int sign, int offset) {
 	const int j = blockIdx.x * 128 + threadIdx.x;
 	const int i = blockIdx.y;
 	if (j >= W) return;
@@ -335,7 +351,7 @@ __global__ void __launch_bounds__(128) k_sgm_apply_generic(const uint16_t* __res
 		ps[d * sd] = (float)s;
 		if (s <= best) { best = s; bd = d; }
 	}
-	if (idx) idx[i * i0 + j * i1] = bd;
+	if (idx) idx[i * i0 + j * i1] = sign * bd + offset;
 }
 
 } // namespace stevi
@@ -349,7 +365,7 @@ static bool aligned16(const void* p, int64_t a, int64_t b, size_t esz) {
 }
 
 static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, const stevi_margins& mg, const View& out,
-							 const int32_t* gmap_ready, int max_cost_hint, const View* wta_out) {
+							 const int32_t* gmap_ready, int max_cost_hint, const WtaSink* wta) {
 	const int H = cv.shape[0], W = cv.shape[1], D = cv.shape[2];
 	const size_t npix = (size_t)H * W;
 	int32_t* scratch = nullptr; // [T | R | max_abs_m]
@@ -406,23 +422,26 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 					  aligned16(ps, out.st[0], out.st[2], 4) && H <= 65535;
 	if (rows) {
 		const int xb = cdiv(W, 1024);
-		int dchunk = D;
-		const long want = 4L * c->sm_count;
-		if (!wta_out && (long)xb * H < want) {
-			long parts = (want + (long)xb * H - 1) / ((long)xb * H);
-			dchunk = std::max(16, (int)((D + parts - 1) / parts));
-		}
+		// many short blocks: aim at >= 8 waves of 6 resident blocks per SM so the last partial wave costs little
+		const long want = 8L * 6 * c->sm_count;
+		long parts = std::min<long>(std::max(1, D / 32), (want + (long)xb * H - 1) / ((long)xb * H));
+		const int dchunk = (int)((D + parts - 1) / parts);
 		dim3 grid(xb, H, cdiv(D, dchunk));
-		if (wta_out)
-			STEVI_LAUNCH(c, k_sgm_apply_rows<true>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
-						 wta_out->as<int32_t>(), wta_out->st[0], wta_out->st[1]);
-		else
+		if (wta) {
+			unsigned long long* keys = nullptr;
+			STEVI_TRY(arena_alloc_t(c, npix, &keys));
+			STEVI_CUDA(c, cudaMemsetAsync(keys, 0xff, npix * sizeof(unsigned long long), c->stream));
+			STEVI_LAUNCH(c, k_sgm_apply_rows<true>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys);
+			dim3 gdec(cdiv(W, 256), H);
+			STEVI_LAUNCH(c, k_wta_decode_keys, gdec, 256, 0, keys, H, W, wta->sign, wta->offset, wta->out.as<int32_t>(), wta->out.st[0], wta->out.st[1]);
+		} else
 			STEVI_LAUNCH(c, k_sgm_apply_rows<false>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
-						 (int32_t*)nullptr, (int64_t)0, (int64_t)0);
+						 (unsigned long long*)nullptr);
 	} else {
 		dim3 grid(cdiv(W, 128), H);
 		STEVI_LAUNCH(c, k_sgm_apply_generic, grid, 128, 0, pc, cv.st[0], cv.st[1], cv.st[2], ps, out.st[0], out.st[1], out.st[2], T, R, H, W, D, pout,
-					 wta_out ? wta_out->as<int32_t>() : (int32_t*)nullptr, wta_out ? wta_out->st[0] : 0, wta_out ? wta_out->st[1] : 0);
+					 wta ? wta->out.as<int32_t>() : (int32_t*)nullptr, wta ? wta->out.st[0] : 0, wta ? wta->out.st[1] : 0,
+					 wta ? wta->sign : 1, wta ? wta->offset : 0);
 	}
 	return STEVI_OK;
 }
@@ -432,7 +451,7 @@ int32_t sgm_general(stevi_ctx* c, const View& cv, int ndir, int strategy, float 
 
 int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
 				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
-				const View* wta_out) {
+				const WtaSink* wta) {
 	if (ndir != 4 && ndir != 8 && ndir != 16) return fail(c, STEVI_E_ARG, "sgm: n_directions must be 4, 8 or 16");
 	if (cv.ndim != 3 || (cv.dtype != STEVI_U16 && cv.dtype != STEVI_F32))
 		return fail(c, STEVI_E_DTYPE, "sgm: cost volume must be (H,W,D) u16 or f32");
@@ -444,11 +463,15 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 	if (cv.shape[0] > 65535) return fail(c, STEVI_E_UNSUPPORTED, "sgm: more than 65535 rows");
 	const bool pout_int = Pout == rintf(Pout) && fabsf(Pout) <= 1.0e6f;
 	if (semantics == STEVI_COMPAT && strategy == STEVI_COST && cv.dtype == STEVI_U16 && pout_int) {
-		int32_t s = sgm_collapsed(c, cv, ndir, (int)Pout, mg, out, gmap_ready, max_cost_hint, wta_out);
+		int32_t s = sgm_collapsed(c, cv, ndir, (int)Pout, mg, out, gmap_ready, max_cost_hint, wta);
 		if (s != STEVI_FALLBACK) return s;
 	}
 	STEVI_TRY(sgm_general(c, cv, ndir, strategy, P1, P2, Pout, mg, semantics, out));
-	if (wta_out) STEVI_TRY(wta_dev(c, out, strategy, *wta_out));
+	if (wta) {
+		STEVI_TRY(wta_dev(c, out, strategy, wta->out));
+		if (wta->sign != 1 || wta->offset != 0)
+			STEVI_TRY(index_to_disp_dev(c, wta->out, wta->sign > 0 ? STEVI_RIGHT_TO_LEFT : STEVI_LEFT_TO_RIGHT, wta->offset, wta->out));
+	}
 	return STEVI_OK;
 }
 
