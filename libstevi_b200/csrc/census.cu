@@ -7,6 +7,7 @@
 //   cross_correlations.h:194-249  CV(i,j,d) = sum_n popcount(src(i,j,n) ^ tgt(i,j+s*d,n)), target 0 outside the image,
 //                         Q2: every target word is rounded through float first (:235-236)
 #include "common.cuh"
+#include <type_traits>
 #include "kernels.cuh"
 
 namespace stevi {
@@ -153,7 +154,8 @@ __device__ __forceinline__ uint32_t round_through_float(uint32_t w) {
 template<typename TO> __device__ __forceinline__ void store8(TO* p, const uint32_t (&c)[8]);
 template<> __device__ __forceinline__ void store8<uint16_t>(uint16_t* p, const uint32_t (&c)[8]) {
 	uint4 v;
-	v.x = c[0] | (c[1] << 16); v.y = c[2] | (c[3] << 16); v.z = c[4] | (c[5] << 16); v.w = c[6] | (c[7] << 16);
+	v.x = __byte_perm(c[0], c[1], 0x5410); v.y = __byte_perm(c[2], c[3], 0x5410); // one PRMT per pair of costs
+	v.z = __byte_perm(c[4], c[5], 0x5410); v.w = __byte_perm(c[6], c[7], 0x5410);
 	__stcs(reinterpret_cast<uint4*>(p), v);
 }
 template<> __device__ __forceinline__ void store8<int32_t>(int32_t* p, const uint32_t (&c)[8]) {
@@ -214,6 +216,11 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	}
 	const bool full = j + 8 <= p.Ws;
 	TO* orow = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1;
+	// Pout only enters g where j + d reaches past the last column: threads that never get there (most of them) track
+	// the plain minimum of the costs and double it at the end
+	const bool edge = EMIT_G && (j + 7 + d0 + dn - 1 >= p.Ws);
+	auto sweep = [&](auto edge_tag) {
+	constexpr bool EDGE = decltype(edge_tag)::value;
 	for (int dr = 0; dr < dn; dr += 8) {
 #pragma unroll
 		for (int u = 0; u < 8; u++) {
@@ -226,7 +233,10 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 #pragma unroll
 					for (int n = 0; n < NW; n++) a += __popc(s[n][k] ^ w[n][k]);
 					cst[k] = a;
-					if (EMIT_G) gmin[k] = min(gmin[k], (int)(2 * a) + ((j + k + d >= p.Ws) ? p.pout : 0));
+					if (EMIT_G) {
+						if (EDGE) gmin[k] = min(gmin[k], (int)(2 * a) + ((j + k + d >= p.Ws) ? p.pout : 0));
+						else gmin[k] = min(gmin[k], (int)a);
+					}
 				}
 				TO* o = orow + d * p.o2;
 				if (VEC && full) store8<TO>(o, cst);
@@ -254,6 +264,15 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 					}
 				}
 			}
+		}
+	}
+	};
+	if (edge) sweep(std::true_type{});
+	else {
+		sweep(std::false_type{});
+		if (EMIT_G) {
+#pragma unroll
+			for (int k = 0; k < 8; k++) gmin[k] *= 2;
 		}
 	}
 	if (EMIT_G) {

@@ -271,53 +271,67 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restr
 	if (lane == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
 }
 
-// S = (1+R)*C + R*pout*[j+d >= W] - T on the reference's [H][D][W] layout (column stride 1 in and out): a thread owns 8
-// consecutive columns; per disparity one 16-byte load of costs and two 16-byte stores of floats. With WTA the running
+// S = (1+R)*C + R*pout*[j+d >= W] - T on the reference's [H][D][W] layout (column stride 1 in and out): a thread owns 4
+// consecutive columns; per disparity one 8-byte load of costs and one 16-byte store of floats. With WTA the running
 // arg-min (`<=`: last minimum wins, correlation_base.h:446) is kept along the way, so the aggregated volume is not read again.
 // blockIdx.z splits the disparity range so that the grid is many short blocks (no tail wave).
 template<bool WTA>
-__global__ void __launch_bounds__(128) k_sgm_apply_rows(const uint16_t* __restrict__ cv, int64_t c0, int64_t cd,
+__global__ void __launch_bounds__(256) k_sgm_apply_rows(const uint16_t* __restrict__ cv, int64_t c0, int64_t cd,
 														float* __restrict__ S, int64_t s0, int64_t sd,
 														const int32_t* __restrict__ T, const int32_t* __restrict__ R,
 														int H, int W, int D, int dchunk, int pout,
 														unsigned long long* __restrict__ keys) {
-	const int j = (blockIdx.x * 128 + threadIdx.x) * 8;
+	// 4 columns per thread: a warp loads 256 contiguous bytes of costs and stores 512 contiguous bytes of floats per
+	// disparity (every sector it touches is written whole by one instruction)
+	const int j = (blockIdx.x * 256 + threadIdx.x) * 4;
 	const int i = blockIdx.y;
 	if (j >= W) return; // W is a multiple of 8 on this path
 	const int d_begin = blockIdx.z * dchunk, d_end = min(D, d_begin + dchunk);
-	int r1[8], rp[8], t[8];
-#pragma unroll
-	for (int k = 0; k < 8; k++) {
-		const int r = __ldg(R + (int64_t)i * W + j + k);
-		r1[k] = 1 + r; rp[k] = r * pout; t[k] = __ldg(T + (int64_t)i * W + j + k);
+	int r1[4], rp[4], t[4];
+	{
+		const int4 rv = __ldg(reinterpret_cast<const int4*>(R + (int64_t)i * W + j));
+		const int4 tv = __ldg(reinterpret_cast<const int4*>(T + (int64_t)i * W + j));
+		r1[0] = 1 + rv.x; r1[1] = 1 + rv.y; r1[2] = 1 + rv.z; r1[3] = 1 + rv.w;
+		rp[0] = rv.x * pout; rp[1] = rv.y * pout; rp[2] = rv.z * pout; rp[3] = rv.w * pout;
+		t[0] = tv.x; t[1] = tv.y; t[2] = tv.z; t[3] = tv.w;
 	}
 	const uint16_t* pc = cv + i * c0 + j;
 	float* ps = S + i * s0 + j;
-	int best[8], bd[8];
+	int best[4], bd[4];
 	if (WTA) {
 #pragma unroll
-		for (int k = 0; k < 8; k++) { best[k] = 0x7fffffff; bd[k] = 0; }
+		for (int k = 0; k < 4; k++) { best[k] = 0x7fffffff; bd[k] = 0; }
 	}
-#pragma unroll 4
-	for (int d = d_begin; d < d_end; d++) {
-		const uint4 r = __ldcs(reinterpret_cast<const uint4*>(pc + d * cd));
-		const uint32_t w[4] = {r.x, r.y, r.z, r.w};
-		float o[8];
+	// explicit two-phase loop: all loads of a batch are issued before the first store (the compiler does not move the
+	// cache-hinted loads across the stores by itself), which keeps 8 x 8 bytes per thread in flight
+	constexpr int U = 8;
+	for (int d0 = d_begin; d0 < d_end; d0 += U) {
+		uint2 r[U];
 #pragma unroll
-		for (int k = 0; k < 8; k++) {
-			const int cst = (w[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-			const int s = r1[k] * cst + (j + k + d >= W ? rp[k] : 0) - t[k];
-			o[k] = (float)s;
-			if (WTA) { if (s <= best[k]) { best[k] = s; bd[k] = d; } }
+		for (int u = 0; u < U; u++)
+			r[u] = (d0 + u < d_end) ? __ldcs(reinterpret_cast<const uint2*>(pc + (d0 + u) * cd)) : make_uint2(0u, 0u);
+#pragma unroll
+		for (int u = 0; u < U; u++) {
+			const int d = d0 + u;
+			if (d < d_end) {
+				const uint32_t w[2] = {r[u].x, r[u].y};
+				float o[4];
+#pragma unroll
+				for (int k = 0; k < 4; k++) {
+					const int cst = (w[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+					const int s = r1[k] * cst + (j + k + d >= W ? rp[k] : 0) - t[k];
+					o[k] = (float)s;
+					if (WTA) { if (s <= best[k]) { best[k] = s; bd[k] = d; } }
+				}
+				__stcs(reinterpret_cast<float4*>(ps + d * sd), make_float4(o[0], o[1], o[2], o[3]));
+			}
 		}
-		__stcs(reinterpret_cast<float4*>(ps + d * sd), make_float4(o[0], o[1], o[2], o[3]));
-		__stcs(reinterpret_cast<float4*>(ps + d * sd) + 1, make_float4(o[4], o[5], o[6], o[7]));
 	}
 	if (WTA) {
 		// the disparity range is split over blockIdx.z: merge through one 64-bit atomicMin per pixel and chunk on the key
 		// (S biased to unsigned) << 32 | (2^32-1 - d): smallest S wins, equal S -> largest d, i.e. the reference's `<=` rule
 #pragma unroll
-		for (int k = 0; k < 8; k++) {
+		for (int k = 0; k < 4; k++) {
 			const unsigned long long key = ((unsigned long long)((uint32_t)best[k] ^ 0x80000000u) << 32) | (0xffffffffu - (uint32_t)bd[k]);
 			atomicMin(keys + (int64_t)i * W + j + k, key);
 		}
@@ -431,11 +445,11 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 			unsigned long long* keys = nullptr;
 			STEVI_TRY(arena_alloc_t(c, npix, &keys));
 			STEVI_CUDA(c, cudaMemsetAsync(keys, 0xff, npix * sizeof(unsigned long long), c->stream));
-			STEVI_LAUNCH(c, k_sgm_apply_rows<true>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys);
+			STEVI_LAUNCH(c, k_sgm_apply_rows<true>, grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys);
 			dim3 gdec(cdiv(W, 256), H);
 			STEVI_LAUNCH(c, k_wta_decode_keys, gdec, 256, 0, keys, H, W, wta->sign, wta->offset, wta->out.as<int32_t>(), wta->out.st[0], wta->out.st[1]);
 		} else
-			STEVI_LAUNCH(c, k_sgm_apply_rows<false>, grid, 128, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
+			STEVI_LAUNCH(c, k_sgm_apply_rows<false>, grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
 						 (unsigned long long*)nullptr);
 	} else {
 		dim3 grid(cdiv(W, 128), H);
