@@ -178,10 +178,13 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	const int tid = threadIdx.x;
 	const int i = blockIdx.y;
 	const int j0 = blockIdx.x * 1024;
-	const int d0 = blockIdx.z * p.dchunk;
-	const int dn = min(p.D - d0, p.dchunk);
-	const int N = 1024 + dn - 1;
-	const int base = SIGN > 0 ? j0 + d0 : j0 - d0 - (dn - 1);
+	const int d0 = blockIdx.z * p.dchunk;          // p.dchunk is a multiple of 8
+	const int dn = min(p.D - d0, p.dchunk);        // disparities of this block
+	const int dn8 = (dn + 7) & ~7;                 // ... padded to whole groups of 8 (the pad is computed, never stored)
+	const int N = 1024 + dn8 - 1;
+	// target column held at staging index idx: base + idx; a thread's window for relative disparity dr covers
+	// idx = 8*tid + k + dr (SIGN > 0) or 8*tid + k + (dn8 - 1 - dr) (SIGN < 0), k = 0..7
+	const int base = SIGN > 0 ? j0 + d0 : j0 - d0 - (dn8 - 1);
 	const int P = p.P;
 	for (int idx = tid; idx < N; idx += 128) {
 		const int col = base + idx;
@@ -202,30 +205,35 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 #pragma unroll
 		for (int n = 0; n < NW; n++) s[n][k] = (j + k < p.Ws) ? __ldg(p.src + i * p.s0 + (j + k) * p.s1 + n * p.s2) : 0u;
 	}
-	const int off0 = SIGN > 0 ? 0 : dn - 1;
+	// lane (= idx & 7) and group (= idx >> 3) of every window access are known up to a per-thread base, because
+	// dn8 and the loop step are multiples of 8: the shared-memory addresses are base + immediate
+	const int g8 = dn8 >> 3;
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
-		const int idx = tid * 8 + k + off0;
 #pragma unroll
-		for (int n = 0; n < NW; n++) w[n][k] = sm[n * 8 * P + (idx & 7) * P + (idx >> 3)];
+		for (int n = 0; n < NW; n++) {
+			if (SIGN > 0) w[n][k] = sm[n * 8 * P + k * P + tid];
+			else w[n][k] = (k == 0) ? sm[n * 8 * P + 7 * P + tid + g8 - 1] : sm[n * 8 * P + (k - 1) * P + tid + g8];
+		}
 	}
 	int gmin[8];
 	if (EMIT_G) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) gmin[k] = 0x7fffffff;
 	}
-	const bool full = j + 8 <= p.Ws;
-	TO* orow = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1;
+	const bool full = VEC && (j + 8 <= p.Ws);
+	TO* orow = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1 + (int64_t)d0 * p.o2;
 	// Pout only enters g where j + d reaches past the last column: threads that never get there (most of them) track
 	// the plain minimum of the costs and double it at the end
 	const bool edge = EMIT_G && (j + 7 + d0 + dn - 1 >= p.Ws);
-	auto sweep = [&](auto edge_tag) {
-	constexpr bool EDGE = decltype(edge_tag)::value;
-	for (int dr = 0; dr < dn; dr += 8) {
+	auto sweep = [&](auto edge_tag, auto full_tag) {
+		constexpr bool EDGE = decltype(edge_tag)::value, FULL = decltype(full_tag)::value;
+		TO* o = orow;
+		for (int gr = 0; gr < g8; gr++) { // 8 disparities per trip: dr = 8*gr + u
+			const int live = dn - 8 * gr;  // < 8 only in a ragged last group
+			const uint32_t* nxt = sm + tid + (SIGN > 0 ? gr + 1 : g8 - 1 - gr);
 #pragma unroll
-		for (int u = 0; u < 8; u++) {
-			if (dr + u < dn) {
-				const int d = d0 + dr + u;
+			for (int u = 0; u < 8; u++) {
 				uint32_t cst[8];
 #pragma unroll
 				for (int k = 0; k < 8; k++) {
@@ -233,43 +241,43 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 #pragma unroll
 					for (int n = 0; n < NW; n++) a += __popc(s[n][k] ^ w[n][k]);
 					cst[k] = a;
+				}
+				if (u < live) {
 					if (EMIT_G) {
-						if (EDGE) gmin[k] = min(gmin[k], (int)(2 * a) + ((j + k + d >= p.Ws) ? p.pout : 0));
-						else gmin[k] = min(gmin[k], (int)a);
+						const int d = d0 + 8 * gr + u;
+#pragma unroll
+						for (int k = 0; k < 8; k++) {
+							if (EDGE) gmin[k] = min(gmin[k], (int)(2 * cst[k]) + ((j + k + d >= p.Ws) ? p.pout : 0));
+							else gmin[k] = min(gmin[k], (int)cst[k]);
+						}
+					}
+					if (FULL) store8<TO>(o, cst);
+					else {
+#pragma unroll
+						for (int k = 0; k < 8; k++) if (j + k < p.Ws) o[k * p.o1] = (TO)cst[k];
 					}
 				}
-				TO* o = orow + d * p.o2;
-				if (VEC && full) store8<TO>(o, cst);
-				else {
+				o += p.o2;
+				if (gr + 1 < g8 || u < 7) { // slide the target window by one column
 #pragma unroll
-					for (int k = 0; k < 8; k++) if (j + k < p.Ws) o[k * p.o1] = (TO)cst[k];
-				}
-				if (dr + u + 1 < dn) { // slide the target window by one column
-					if (SIGN > 0) {
-						const int idx = tid * 8 + 8 + dr + u;
-#pragma unroll
-						for (int n = 0; n < NW; n++) {
+					for (int n = 0; n < NW; n++) {
+						if (SIGN > 0) {
 #pragma unroll
 							for (int k = 0; k < 7; k++) w[n][k] = w[n][k + 1];
-							w[n][7] = sm[n * 8 * P + (idx & 7) * P + (idx >> 3)];
-						}
-					} else {
-						const int idx = tid * 8 + (dn - 1) - (dr + u + 1);
-#pragma unroll
-						for (int n = 0; n < NW; n++) {
+							w[n][7] = nxt[n * 8 * P + u * P];
+						} else {
 #pragma unroll
 							for (int k = 7; k > 0; k--) w[n][k] = w[n][k - 1];
-							w[n][0] = sm[n * 8 * P + (idx & 7) * P + (idx >> 3)];
+							w[n][0] = (u < 7) ? nxt[n * 8 * P + (6 - u) * P] : nxt[n * 8 * P + 7 * P - 1];
 						}
 					}
 				}
 			}
 		}
-	}
 	};
-	if (edge) sweep(std::true_type{});
+	if (edge) { if (full) sweep(std::true_type{}, std::true_type{}); else sweep(std::true_type{}, std::false_type{}); }
 	else {
-		sweep(std::false_type{});
+		if (full) sweep(std::false_type{}, std::true_type{}); else sweep(std::false_type{}, std::false_type{});
 		if (EMIT_G) {
 #pragma unroll
 			for (int k = 0; k < 8; k++) gmin[k] *= 2;
@@ -340,7 +348,7 @@ static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
 	if (p.gmap && dchunk < p.D) // chunks merge their minima with atomicMin
 		STEVI_CUDA(c, cudaMemsetAsync(p.gmap, 0x7f, (size_t)p.H * p.Ws * sizeof(int32_t), c->stream));
 	p.dchunk = dchunk;
-	const int groups = (1024 + dchunk + 8) / 8 + 1;
+	const int groups = (1024 + dchunk + 8) / 8 + 2;
 	int P = groups;
 	while (P % 32 != 4) P++;
 	p.P = P;
