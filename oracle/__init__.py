@@ -118,6 +118,19 @@ class _Checker:
         out = np.empty((h, w, D), np.float32)
         m = np.asarray(margins, np.int32)
         f32 = ctypes.c_float
+        # Q8: with 16 directions the reference's OpenMP loops race (lines of one direction share pixels); its
+        # single-threaded result is the defined one
+        serial = self.prefix == "ref_" and ndir == 16
+        if serial:
+            nthreads = self.lib.ref_num_threads()
+            self.lib.ref_set_num_threads(1)
+        try:
+            return self._sgm(cv, ndir, strategy, P1, P2, Pout, m, out, f32, h, w, D)
+        finally:
+            if serial:
+                self.lib.ref_set_num_threads(nthreads)
+
+    def _sgm(self, cv, ndir, strategy, P1, P2, Pout, m, out, f32, h, w, D):
         if cv.dtype == np.uint16:
             rc = self._f("sgm_u16")(_p(_c(cv, np.uint16)), h, w, D, ndir, strategy, f32(P1), f32(P2), f32(Pout), _p(m), _p(out))
         else:

@@ -301,13 +301,16 @@ static void sgm_add_direction(int dirIdx, int strategy, const float* cv, float* 
 	int rowStart = sgm_start_pos(st[2], st[3]); /* from stepsHorizontal */
 	if (rowStart != 0) { /* lines starting on the left (or, Q4, one past the right) column: sgm.h:329-341 */
 		int sj = (rowStart == 1) ? left : w - right;
-		#pragma omp parallel for
+		/* Q8: lines of the eight extra directions of the 16-direction set (steps alternating between two moves) started
+		 * on neighbouring pixels share pixels, so the reference's own `omp parallel for` over them races on sgm_cv;
+		 * the sequential result is the defined one: those directions run on one thread here. */
+		#pragma omp parallel for if (dirIdx < 8)
 		for (int si = top; si < h - bottom; si++)
 			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg);
 	}
 	if (colStart != 0) { /* lines starting on the top (or, Q4, one past the bottom) row: sgm.h:343-354 */
 		int si = (colStart == 1) ? top : h - bottom;
-		#pragma omp parallel for
+		#pragma omp parallel for if (dirIdx < 8)
 		for (int sj = left; sj < w - right; sj++)
 			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg);
 	}

@@ -1,0 +1,70 @@
+"""Generates tests/golden/*.npz from the UNMODIFIED reference headers (oracle/_ref/libstevi_ref.so, built from
+/root/reference by oracle/Makefile). Run in the build container only (the GPU box has no reference tree):
+
+    python tests/golden/make_golden.py
+
+Inputs are produced by libstevi_b200.synth (counter-based, library independent) from the seeds stored in each file,
+so the fixtures hold the reference OUTPUTS plus the parameters needed to regenerate the inputs.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+import oracle as O  # noqa: E402
+from libstevi_b200 import synth  # noqa: E402
+
+
+def main():
+    ref = O.ref
+    assert ref is not None, "build oracle/_ref first (make -C oracle ref)"
+    H, W, D = 26, 44, 10
+    L8, R8, gt = synth.stereo_pair(H, W, 101, d_bg=2, d_sq=5, d_max=6)
+    Lf, Rf, _ = synth.stereo_pair(H, W, 102, d_bg=2, d_sq=5, d_max=6, dtype=np.float32)
+    out = {"H": H, "W": W, "D": D, "seed_u8": 101, "seed_f32": 102}
+
+    # census features and census cost volumes (u8 and f32 images, several windows, both directions)
+    for hr, vr in ((4, 3), (3, 3), (2, 2), (6, 5)):
+        out[f"census_u8_{hr}_{vr}"] = ref.census(L8, hr, vr)
+        out[f"census_f32_{hr}_{vr}"] = ref.census(Lf, hr, vr)
+        for direction in (0, 1):
+            out[f"censuscv_u8_{hr}_{vr}_{direction}"] = ref.cost_volume(O.CENSUS, L8, R8, hr, vr, D, direction)
+    cv = ref.cost_volume(O.CENSUS, L8, R8, 4, 3, D)
+    # SGM on the census volume: all direction sets, both strategies, with and without margins
+    for ndir in (4, 8, 16):
+        for strategy in (0, 1):
+            out[f"sgm_u16_{ndir}_{strategy}"] = ref.sgm(cv, ndir, strategy, 10, 120, 100)
+    out["sgm_u16_8_0_margins"] = ref.sgm(cv, 8, 0, 10, 120, 100, (2, 1, 3, 2))
+    out["wta_cost"] = ref.wta(out["sgm_u16_8_0"], 0)
+    out["wta_cv_u16"] = ref.wta(cv, 0)
+    # float cost volumes for every float matching function
+    for mf in (O.CC, O.NCC, O.SSD, O.SAD, O.ZCC, O.ZNCC, O.ZSSD, O.ZSAD):
+        for direction in (0, 1):
+            out[f"cv_f32_{mf}_{direction}"] = ref.cost_volume(mf, Lf, Rf, 2, 2, D, direction)
+    zn = out[f"cv_f32_{O.ZNCC}_1"]
+    out["sgm_f32_8_1"] = ref.sgm(zn, 8, 1, 0.001, 0.01, 100)
+    out["sgm_f32_8_0"] = ref.sgm(out[f"cv_f32_{O.SSD}_1"], 8, 0, 0.5, 2.0, 100)
+    idx = ref.wta(zn, 1)
+    out["wta_score"] = idx
+    out["disp"] = ref.index_to_disp(idx, 1, 3)
+    out["selected_cost"] = ref.selected_cost(zn, idx)
+    for tdir in (0, 1, 2):
+        out[f"tcv_{tdir}"] = ref.truncated_cost_volume(zn, idx, 2, 2, 1, 1, tdir)
+    for kernel in (0, 1, 2):
+        out[f"refined_{kernel}"] = ref.refine(out["tcv_0"], idx, kernel)
+    out["avgpool"] = ref.avgpool2(Lf)
+    out["avgpool_odd"] = ref.avgpool2(np.ascontiguousarray(Lf[:25, :43]))
+    for depth in (1, 2):
+        tcv, disp = ref.hierarchical(O.ZNCC, depth, Lf, Rf, 2, 2, D, 2)
+        out[f"hier_tcv_{depth}"], out[f"hier_disp_{depth}"] = tcv, disp
+    out["unfold_u8"] = ref.unfold(L8[:6, :7], 2, 1)
+    out["features_zncc"] = ref.feature_volume(O.ZNCC, Lf[:8, :9], 1, 1)
+    np.savez_compressed(os.path.join(HERE, "reference_outputs.npz"), **out)
+    print("wrote", os.path.join(HERE, "reference_outputs.npz"), os.path.getsize(os.path.join(HERE, "reference_outputs.npz")), "bytes")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,152 @@
+"""Pins the CPU oracle (oracle/stevi_oracle.c, test infrastructure) to the reference.
+
+1. against tests/golden/reference_outputs.npz — outputs of the UNMODIFIED reference headers (generator:
+   tests/golden/make_golden.py), so this runs anywhere, including the GPU box where /root/reference is absent;
+2. against the compiled reference itself (oracle/_ref) on further seeded inputs, when it is present;
+3. against Qt-free restatements of the reference's own unit tests (analytic expectations):
+   testCorrelationFilters.cpp:332-370 (ZNCC at the interior pixel), :384-445 (unfold), testCostRefinement.cpp:33-57
+   (parabola), testCorrelationHierarchical.cpp:22-139 (statistical criterion).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle as O
+from libstevi_b200 import synth
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_outputs.npz"))
+H, W, D = int(G["H"]), int(G["W"]), int(G["D"])
+L8, R8, _ = synth.stereo_pair(H, W, int(G["seed_u8"]), d_bg=2, d_sq=5, d_max=6)
+Lf, Rf, _ = synth.stereo_pair(H, W, int(G["seed_f32"]), d_bg=2, d_sq=5, d_max=6, dtype=np.float32)
+port = O.port
+
+
+def same(a, b):
+    return a.shape == b.shape and np.array_equal(a, b, equal_nan=True)
+
+
+@pytest.mark.parametrize("hr,vr", [(4, 3), (3, 3), (2, 2), (6, 5)])
+def test_golden_census(hr, vr):
+    assert same(port.census(L8, hr, vr), G[f"census_u8_{hr}_{vr}"])
+    assert same(port.census(Lf, hr, vr), G[f"census_f32_{hr}_{vr}"])
+    for direction in (0, 1):
+        assert same(port.cost_volume(O.CENSUS, L8, R8, hr, vr, D, direction), G[f"censuscv_u8_{hr}_{vr}_{direction}"])
+
+
+def test_golden_sgm_wta():
+    cv = G["censuscv_u8_4_3_1"]
+    for ndir in (4, 8, 16):
+        for strategy in (0, 1):
+            assert same(port.sgm(cv, ndir, strategy, 10, 120, 100), G[f"sgm_u16_{ndir}_{strategy}"]), (ndir, strategy)
+    assert same(port.sgm(cv, 8, 0, 10, 120, 100, (2, 1, 3, 2)), G["sgm_u16_8_0_margins"])
+    assert same(port.wta(G["sgm_u16_8_0"], 0), G["wta_cost"])
+    assert same(port.wta(cv, 0), G["wta_cv_u16"])
+    zn = G[f"cv_f32_{O.ZNCC}_1"]
+    assert same(port.sgm(zn, 8, 1, 0.001, 0.01, 100), G["sgm_f32_8_1"])
+    assert same(port.sgm(G[f"cv_f32_{O.SSD}_1"], 8, 0, 0.5, 2.0, 100), G["sgm_f32_8_0"])
+
+
+@pytest.mark.parametrize("mf", [O.CC, O.NCC, O.SSD, O.SAD, O.ZCC, O.ZNCC, O.ZSSD, O.ZSAD])
+def test_golden_float_cost_volumes(mf):
+    for direction in (0, 1):
+        assert same(port.cost_volume(mf, Lf, Rf, 2, 2, D, direction), G[f"cv_f32_{mf}_{direction}"])
+
+
+def test_golden_selection_refinement_hierarchy():
+    zn = G[f"cv_f32_{O.ZNCC}_1"]
+    idx = port.wta(zn, 1)
+    assert same(idx, G["wta_score"])
+    assert same(port.index_to_disp(idx, 1, 3), G["disp"])
+    assert same(port.selected_cost(zn, idx), G["selected_cost"])
+    for tdir in (0, 1, 2):
+        assert same(port.truncated_cost_volume(zn, idx, 2, 2, 1, 1, tdir), G[f"tcv_{tdir}"])
+    for kernel in (0, 1, 2):
+        got, want = port.refine(G["tcv_0"], idx, kernel), G[f"refined_{kernel}"]
+        assert np.allclose(got, want, rtol=1e-6, atol=1e-6, equal_nan=True)  # libm logf may differ in the last ulp
+    assert same(port.avgpool2(Lf), G["avgpool"])
+    assert same(port.avgpool2(np.ascontiguousarray(Lf[:25, :43])), G["avgpool_odd"])
+    for depth in (1, 2):
+        tcv, disp = port.hierarchical(O.ZNCC, depth, Lf, Rf, 2, 2, D, 2)
+        assert same(disp, G[f"hier_disp_{depth}"])
+        assert np.allclose(tcv, G[f"hier_tcv_{depth}"], atol=1e-6, equal_nan=True)
+    assert same(port.unfold(L8[:6, :7], 2, 1), G["unfold_u8"])
+    assert np.allclose(port.feature_volume(O.ZNCC, Lf[:8, :9], 1, 1), G["features_zncc"], atol=1e-7, equal_nan=True)
+
+
+@pytest.mark.skipif(O.ref is None, reason="compiled reference (oracle/_ref) not present on this machine")
+@pytest.mark.parametrize("seed", [7, 8])
+def test_port_equals_compiled_reference(seed):
+    ref = O.ref
+    L, R, _ = synth.stereo_pair(30, 52, seed, d_bg=3, d_sq=7, d_max=8)
+    for hr, vr in ((4, 3), (5, 1)):
+        cv = port.cost_volume(O.CENSUS, L, R, hr, vr, 12)
+        assert same(cv, ref.cost_volume(O.CENSUS, L, R, hr, vr, 12))
+    for ndir in (4, 8, 16):
+        for strategy in (0, 1):
+            assert same(port.sgm(cv, ndir, strategy, 7, 50, 64, (1, 0, 2, 1)), ref.sgm(cv, ndir, strategy, 7, 50, 64, (1, 0, 2, 1)))
+    Lq, Rq, _ = synth.stereo_pair(30, 52, seed, d_bg=3, d_sq=7, dtype=np.float32)
+    for mf in (O.ZNCC, O.SAD):
+        a, b = port.cost_volume(mf, Lq, Rq, 3, 2, 9), ref.cost_volume(mf, Lq, Rq, 3, 2, 9)
+        assert np.allclose(a, b, atol=1e-6, equal_nan=True)
+    a, b = port.hierarchical(O.ZNCC, 2, Lq, Rq, 2, 2, 12), ref.hierarchical(O.ZNCC, 2, Lq, Rq, 2, 2, 12)
+    assert same(a[1], b[1])
+
+
+# ---- restatements of the reference's own unit tests ------------------------------------------------------------------
+
+def naive_zncc(win_s, win_t):
+    """test/test_correlation_utils.h:52-98 InneficientZeromeanNormalizedCrossCorrelation"""
+    s, t = win_s.astype(np.float64).ravel(), win_t.astype(np.float64).ravel()
+    s, t = s - s.mean(), t - t.mean()
+    return float((s * t).sum() / np.sqrt((s * s).sum() * (t * t).sum()))
+
+
+@pytest.mark.parametrize("hr,vr", [(1, 1), (2, 3), (5, 5)])
+@pytest.mark.parametrize("D", [1, 5])
+def test_ref_testNCCFilter(hr, vr, D):
+    # testCorrelationFilters.cpp:332-370: source window from the right image at column 0, target windows from the left
+    # image at column d; only the single fully interior pixel is compared; tolerance 1e-3
+    h, w = 2 * vr + 1, 2 * hr + D
+    left, right = synth.random_image(h, w, 5, stream=1), synth.random_image(h, w, 5, stream=2)
+    cv = port.cost_volume(O.ZNCC, left, right, hr, vr, D)
+    for d in range(D):
+        want = naive_zncc(right[:, 0:2 * hr + 1], left[:, d:d + 2 * hr + 1])
+        assert abs(cv[vr, hr, d] - want) < 1e-3
+
+
+def test_ref_testUnfoldOperator():
+    # testCorrelationFilters.cpp:384-445 (auto padding): shape H x W x F and the centre pixel's features are the image
+    hr, vr = 2, 1
+    img = synth.random_image(2 * vr + 1, 2 * hr + 1, 9)
+    fv = port.unfold(img, hr, vr)
+    assert fv.shape == (3, 5, 15)
+    assert np.array_equal(np.sort(fv[vr, hr]), np.sort(img.ravel()))
+    assert np.array_equal(fv[vr, hr], img.ravel())  # Rotate0 channel order c = (2*hr+1)*k + l (unfold.h:180)
+
+
+def test_ref_test1dCostParabola():
+    # testCostRefinement.cpp:33-57: tcv = (a - b, 0, a + b)  =>  refined = idx - b / (2a)
+    rng = np.random.default_rng(0)
+    for _ in range(20):
+        a, b = rng.uniform(0.5, 2.0), rng.uniform(-0.4, 0.4)
+        tcv = np.array([[[a - b, 0.0, a + b]]], np.float32)
+        got = port.refine(tcv, np.array([[3]], np.int32), O.PARABOLA)
+        assert abs(got[0, 0] - (3 - b / (2 * a))) < 1e-5
+    assert port.refine(np.zeros((1, 1, 4), np.float32), np.zeros((1, 1), np.int32)) is None  # even depth: empty array
+
+
+@pytest.mark.parametrize("depth", [1, 2, 3])
+def test_ref_testCorrelationHierarchical(depth):
+    # testCorrelationHierarchical.cpp:22-139: 48x64 parallax-square pair, radii 2, D=16: all disparities within
+    # [-m, D+m], m = 2*sum 2^k*r, and >= 95 % of the interior square pixels equal the ground truth
+    h, w, D_, r = 48, 64, 16, 2
+    L, R, gt = synth.stereo_pair(h, w, 12, d_bg=2, d_sq=6, dtype=np.float32)
+    tcv, disp = port.hierarchical(O.ZNCC, depth, L, R, r, r, D_, 2)
+    assert disp.shape == (h, w) and tcv.shape == (h, w, 5)
+    m = 2 * sum(2 ** k * r for k in range(depth + 1))
+    assert disp.min() >= -m and disp.max() <= D_ + m
+    side = min(h, w) // 3
+    i0, j0 = (h - side) // 2, (w - side) // 2
+    inner = (slice(i0 + r + 2, i0 + side - r - 2), slice(j0 + r + 2, j0 + side - r - 2))
+    assert (disp[inner] == gt[inner]).mean() >= 0.95
