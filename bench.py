@@ -233,6 +233,13 @@ def main():
     dom = max(kern_ms, key=kern_ms.get)
     peak, peak_src = read_peaks()
     dom_bytes = cells * BYTES_PER_CELL_SGM_APPLY if "sgm_apply" in dom else None
+    traffic = None
+    try:  # measured DRAM traffic of that kernel from the committed ncu --set full capture (C2 workload only)
+        if args.workload == "c2":
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                traffic = json.load(f).get(dom.split("<")[0].strip("()"))
+    except Exception:
+        traffic = None
 
     # correctness guard inside the bench: device and host paths must agree bit for bit
     torch.cuda.synchronize()
@@ -254,7 +261,7 @@ def main():
         if dom_bytes:
             ach = dom_bytes / (kern_ms[dom] * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": dom.split("<")[0].strip("()"), "achieved": ach, "peak": peak,
-                                "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                                "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                                 "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": kern_ms[dom]}
         else:
             line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
