@@ -1,0 +1,83 @@
+"""GPU parity of the general SGM recurrence (Score strategy, float volumes) against the CPU oracle.
+
+Bit-exact for the 4- and 8-direction sets (same float operation order as the reference per path, directions and start
+loops in the reference's order). 16 directions: lines of one direction overlap (Q8), the GPU adds their contributions
+with float atomics => bit-exact for integer-valued data, 1e-4 otherwise.
+"""
+import numpy as np
+import pytest
+
+from libstevi_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def census_cv(api, ctx, h=37, w=70, D=24, seed=5, layout="ref"):
+    L, R, _ = synth.stereo_pair(h, w, seed, d_bg=2, d_sq=7, d_max=10)
+    return api.unfoldBasedCostVolume(api.CENSUS, L, R, 4, 3, D, layout=layout, ctx=ctx)
+
+
+def zncc_like_volume(h, w, D, seed):
+    rng = np.random.default_rng(seed)
+    return rng.uniform(-1, 1, size=(h, w, D)).astype(np.float32)
+
+
+@pytest.mark.parametrize("ndir", [4, 8, 16])
+@pytest.mark.parametrize("layout", ["ref", "c"])
+def test_score_mode_u16(api, ctx, oracle, ndir, layout):
+    cv = census_cv(api, ctx, layout=layout)
+    got = api.sgmCostVolume(cv, 3, 20, Pout=50, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(np.ascontiguousarray(cv), ndir, oracle.SCORE, 3, 20, 50)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("ndir", [4, 8])
+@pytest.mark.parametrize("D", [7, 32, 40, 100, 200])
+def test_score_mode_f32_bit_exact(api, ctx, oracle, ndir, D):
+    v = zncc_like_volume(21, 45, D, D)
+    got = api.sgmCostVolume(v, 0.001, 0.01, Pout=100, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, ndir, oracle.SCORE, 0.001, 0.01, 100)
+    assert np.array_equal(got, want)
+
+
+def test_score_mode_f32_16_directions(api, ctx, oracle):
+    v = zncc_like_volume(21, 45, 33, 3)
+    got = api.sgmCostVolume(v, 0.001, 0.01, Pout=100, nDirections=16, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, 16, oracle.SCORE, 0.001, 0.01, 100)
+    assert np.allclose(got, want, atol=1e-4)
+
+
+@pytest.mark.parametrize("margins", [(0, 0, 0, 0), (2, 3, 1, 4)])
+@pytest.mark.parametrize("P", [(0.5, 2.0), (2.0, 0.5)])  # P2 < P1 exercises the exclusion of the 3-window
+def test_score_margins_and_penalties(api, ctx, oracle, margins, P):
+    v = zncc_like_volume(25, 38, 19, 11)
+    got = api.sgmCostVolume(v, P[0], P[1], margins=margins, Pout=3.5, nDirections=8, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, 8, oracle.SCORE, P[0], P[1], 3.5, margins)
+    assert np.array_equal(got, want)
+
+
+def test_cost_mode_float_volume_compat(api, ctx, oracle):
+    # float costs: no integer collapse; Q3 evaluated per path in the reference's operation order
+    v = np.abs(zncc_like_volume(23, 41, 17, 2)) * 10
+    for ndir in (4, 8):
+        got = api.sgmCostVolume(v, 0.5, 2.0, Pout=100, nDirections=ndir, strategy=api.COST, ctx=ctx)
+        assert np.array_equal(got, oracle.port.sgm(v, ndir, oracle.COST, 0.5, 2.0, 100))
+
+
+def test_non_finite_scores(api, ctx, oracle):
+    v = zncc_like_volume(12, 30, 20, 4)
+    v[3, 5, :] = np.nan       # a flat ZNCC patch gives NaN scores (Q6)
+    v[6, 7, 3] = np.inf
+    v[8, :, 0] = -np.inf
+    got = api.sgmCostVolume(v, 0.1, 0.4, Pout=10, nDirections=8, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, 8, oracle.SCORE, 0.1, 0.4, 10)
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_large_u16_costs_fall_back_to_the_recurrence(api, ctx, oracle):
+    # costs so large that the collapsed integer evaluation cannot be proven exact: the general kernel takes over
+    rng = np.random.default_rng(1)
+    cv = rng.integers(60000, 65535, size=(20, 300, 9)).astype(np.uint16)
+    cv[:, ::2, :] //= 50
+    got = api.sgmCostVolume(cv, 1, 2, Pout=100, ctx=ctx)
+    assert np.array_equal(got, oracle.port.sgm(cv, 8, oracle.COST, 1, 2, 100))
