@@ -46,7 +46,10 @@ typedef enum {
 
 typedef enum { STEVI_U8 = 0, STEVI_U16 = 1, STEVI_I32 = 2, STEVI_U32 = 3, STEVI_F32 = 4 } stevi_dtype;
 typedef enum { STEVI_HOST = 0, STEVI_DEVICE = 1 } stevi_mem;
-typedef enum { STEVI_COMPAT = 0, STEVI_CORRECTED = 1 } stevi_semantics;
+typedef enum { STEVI_COMPAT = 0, STEVI_CORRECTED = 1,
+	/* flag, OR-ed in: float cost volumes evaluate the reference's own O(F) per-cell sums in its channel order (slow, as
+	 * close to the reference bits as IEEE arithmetic allows) instead of the O(1) box sums */
+	STEVI_EXACT_SUMS = 256 } stevi_semantics;
 
 /* mirrors StereoVision::Correlation::matchingFunctions, correlation/matching_costs.h:38-53 */
 typedef enum {
@@ -113,6 +116,9 @@ STEVI_API int32_t stevi_census_transform(stevi_ctx* ctx, const stevi_array* img,
 /* unfoldBasedCostVolume<matchFunc, T_L, T_R, 2, dDir, TCV> (correlation/cross_correlations.h:740-765).
  * img_l (H,Wl), img_r (H,Wr): u8|f32 (same dtype). out (H, Wsource, D) of dtype TCV, Wsource = Wr for
  * RIGHT_TO_LEFT, Wl for LEFT_TO_RIGHT. CENSUS: out u16|i32|f32 (hamming_cv_t = u16, matching_costs.h:234).
+ * CC, NCC, ZCC, ZNCC, SSD, ZSSD, SAD, ZSAD: out f32; u8 images only for CC/SSD/SAD (the reference's int16 fixed-point
+ * ZNCC/NCC features for u8 images, cross_correlations.h:416-462, are not provided). Flat windows give NaN for the
+ * normalised functions, like the reference (Q6). MEDAD, ZMEDAD, KERMI: STEVI_E_UNSUPPORTED.
  * The reference lays the volume out as strides {W*D, 1, W} (cross_correlations.h:220); any strides are accepted.
  * Returns STEVI_E_SHAPE where the reference returns an empty array (heights differ, :751). */
 STEVI_API int32_t stevi_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,

@@ -18,6 +18,7 @@ OK, E_SHAPE, E_DTYPE, E_UNSUPPORTED, E_CUDA, E_NCCL, E_ARG = range(7)
 U8, U16, I32, U32, F32 = range(5)
 HOST, DEVICE = 0, 1
 COMPAT, CORRECTED = 0, 1
+EXACT_SUMS = 256
 CC, NCC, SSD, SAD, ZCC, ZNCC, ZSSD, ZSAD, MEDAD, ZMEDAD, HAMMING, CENSUS, KERMI = range(13)
 COST, SCORE = 0, 1
 LEFT_TO_RIGHT, RIGHT_TO_LEFT = 0, 1
@@ -214,9 +215,12 @@ def censusTransform2D(img, h_radius, v_radius, semantics=COMPAT, ctx=None):
 
 
 def unfoldBasedCostVolume(matchFunc, img_l, img_r, h_radius, v_radius, disp_width, dDir=RIGHT_TO_LEFT, TCV=None,
-                          semantics=COMPAT, layout="ref", ctx=None):
-    """cross_correlations.h:740-765. Returns None where the reference returns an empty array."""
+                          semantics=COMPAT, layout="ref", exact_sums=False, ctx=None):
+    """cross_correlations.h:740-765. Returns None where the reference returns an empty array.
+    ``exact_sums``: float matching functions evaluate the reference's O(F) per-cell sums instead of the box sums."""
     ctx = _ctx_for(ctx, img_l)
+    if exact_sums:
+        semantics |= EXACT_SUMS
     if TCV is None:
         TCV = np.uint16 if matchFunc in (CENSUS, HAMMING) else np.float32
     ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]

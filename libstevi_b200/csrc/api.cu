@@ -75,9 +75,10 @@ int32_t stevi_cost_volume(stevi_ctx* c, int32_t mf, const stevi_array* l, const 
 	STEVI_TRY(st.in(r, vr_, "img_r"));
 	STEVI_TRY(st.out(out, vo, "out"));
 	if (mf == STEVI_MF_CENSUS) {
-		STEVI_TRY(census_cv_dev(c, vl, vr_, hr, vr, D, direction, semantics, vo, nullptr, 0));
+		STEVI_TRY(census_cv_dev(c, vl, vr_, hr, vr, D, direction, semantics & 1, vo, nullptr, 0));
 	} else {
-		return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: matching function %d not available", mf);
+		// semantics bit 8 (STEVI_EXACT_SUMS) asks for the reference's own O(F) per-cell sums instead of the box sums
+		STEVI_TRY(float_cv_dev(c, mf, vl, vr_, hr, vr, D, direction, vo, (semantics & STEVI_EXACT_SUMS) != 0));
 	}
 	return st.finish();
 }

@@ -1,0 +1,307 @@
+// Float cost volumes: CC / NCC / ZCC / ZNCC / SSD / ZSSD / SAD / ZSAD.
+//
+//   cross_correlations.h:740-765  unfoldBasedCostVolume = unfold both images -> getFeatureVolumeForMatchFunc -> aggregateCost
+//   correlation_base.h:1100-1136  channelsMean: mean = (sum_c v) * (1/F)     (sum in channel order, then one multiply)
+//   cross_correlations.h:61-104   channelsZeroMeanNorm: norm = sqrt(sum_c (v-mean)^2);  :149-191 channelsNorm: sqrt(sum_c v^2)
+//   cross_correlations.h:452      feature = (v-mean)/norm, no epsilon: a flat window gives 0/0 = NaN (Q6)
+//
+// Two evaluation paths:
+//   * box path (costvol_box.cuh): O(1) per cell, used for window half-widths 1..4 and every function but ZSAD;
+//   * direct path (k_cv_direct): the reference's own O(F) sum per cell, in its channel order — any window, ZSAD too.
+// Both read zero-padded float copies of the images (k_pad_image) and per-pixel window statistics (k_window_stats*).
+#include "common.cuh"
+#include "kernels.cuh"
+#include "costvol_box.cuh"
+
+namespace stevi {
+
+namespace {
+
+inline bool mf_zero_mean(int mf) { return mf == STEVI_MF_ZCC || mf == STEVI_MF_ZNCC || mf == STEVI_MF_ZSSD || mf == STEVI_MF_ZSAD; }
+inline bool mf_normalized(int mf) { return mf == STEVI_MF_NCC || mf == STEVI_MF_ZNCC; }
+__host__ __device__ inline int mf_op(int mf) {
+	switch (mf) {
+	case STEVI_MF_CC: case STEVI_MF_NCC: case STEVI_MF_ZCC: case STEVI_MF_ZNCC: return BOX_PROD;
+	case STEVI_MF_SSD: case STEVI_MF_ZSSD: return BOX_SQ;
+	default: return BOX_ABS;
+	}
+}
+
+// zero-padded float copy: pixel (i,j) at out[(i+pad_top)*pitch + pad_left + j]; the buffer was cleared beforehand
+template<typename TI>
+__global__ void __launch_bounds__(256) k_pad_image(const TI* __restrict__ img, int64_t s0, int64_t s1, int H, int W,
+												   float* __restrict__ out, int64_t pitch, int pad_top, int pad_left) {
+	const int j = blockIdx.x * 256 + threadIdx.x, i = blockIdx.y;
+	if (j < W) out[(int64_t)(i + pad_top) * pitch + pad_left + j] = (float)img[i * s0 + j * s1];
+}
+
+// what the statistics maps hold
+enum { STATS_RAW = 0,       // A = mean, B = norm                               (direct path, feature volumes)
+	   STATS_PROD_SRC = 1,  // A = F*mean, B = 1/norm (NaN when norm == 0)
+	   STATS_PROD_TGT = 2,  // A = mean,   B = 1/norm
+	   STATS_DIFF_SRC = 3,  // A = mean,   B = cost of the window against the all-zero vector (target outside the image)
+	   STATS_DIFF_TGT = 4 };// A = mean,   B = 1
+
+struct StatsParams {
+	const float* pimg;       // padded image at pixel (0,0)
+	int64_t pitch;
+	int H, W, hr, vr;
+	int zero_mean, normalized, op, kind;
+	float* A; float* B;      // same geometry as the padded image, at pixel (0,0)
+};
+
+__device__ __forceinline__ void stats_finish(const StatsParams& p, float mean, float acc, float& a, float& b) {
+	// acc: PROD -> sum of squares (normalised functions only); DIFF -> cost against zero
+	const float F = (float)((2 * p.hr + 1) * (2 * p.vr + 1));
+	float norm = p.normalized ? sqrtf(acc) : 1.f;
+	switch (p.kind) {
+	case STATS_RAW: a = mean; b = norm; break;
+	case STATS_PROD_SRC: a = F * mean; b = p.normalized ? (norm == 0.f ? __int_as_float(0x7fc00000) : 1.f / norm) : 1.f; break;
+	case STATS_PROD_TGT: a = mean; b = p.normalized ? (norm == 0.f ? __int_as_float(0x7fc00000) : 1.f / norm) : 1.f; break;
+	case STATS_DIFF_SRC: a = mean; b = acc; break;
+	default: a = mean; b = 1.f; break;
+	}
+}
+
+__device__ __forceinline__ float stats_term(int op, bool normalized, float f) {
+	if (op == BOX_PROD) return normalized ? __fmul_rn(f, f) : 0.f;
+	if (op == BOX_SQ) return __fmul_rn(f, f);
+	return fabsf(f);
+}
+
+// any window: one thread per pixel, channel order c = (2hr+1)k + l like the reference
+__global__ void __launch_bounds__(128) k_window_stats_generic(const StatsParams p) {
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+	if (j >= p.W) return;
+	const float* base = p.pimg + (int64_t)(i - p.vr) * p.pitch + (j - p.hr);
+	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1;
+	float mean = 0.f;
+	if (p.zero_mean) {
+		for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) mean = __fadd_rn(mean, __ldg(base + k * p.pitch + l));
+		mean = __fmul_rn(mean, 1.f / (float)(hs * vs));
+	}
+	float acc = 0.f;
+	if (p.op != BOX_PROD || p.normalized) {
+		for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) {
+			float f = __ldg(base + k * p.pitch + l);
+			if (p.zero_mean) f = __fsub_rn(f, mean);
+			acc = __fadd_rn(acc, stats_term(p.op, p.normalized, f));
+		}
+	}
+	float a, b;
+	stats_finish(p, mean, acc, a, b);
+	p.A[(int64_t)i * p.pitch + j] = a;
+	p.B[(int64_t)i * p.pitch + j] = b;
+}
+
+// windows up to 9 wide: a thread owns 4 consecutive pixels and reads each window row as four aligned 16-byte loads;
+// same summation order, a tenth of the load instructions
+template<int HR>
+__global__ void __launch_bounds__(128) k_window_stats(const StatsParams p) {
+	const int j0 = (blockIdx.x * 128 + threadIdx.x) * 4, i = blockIdx.y;
+	if (j0 >= p.W) return;
+	const float* base = p.pimg + (int64_t)(i - p.vr) * p.pitch + (j0 - 4);
+	const int vs = 2 * p.vr + 1;
+	constexpr int HS = 2 * HR + 1;
+	float mean[4] = {0.f, 0.f, 0.f, 0.f};
+	if (p.zero_mean) {
+		for (int k = 0; k < vs; k++) {
+			float r[16];
+			load_vec<16>(r, base + k * p.pitch);
+#pragma unroll
+			for (int q = 0; q < 4; q++)
+#pragma unroll
+				for (int l = 0; l < HS; l++) mean[q] = __fadd_rn(mean[q], r[4 - HR + q + l]);
+		}
+		const float sc = 1.f / (float)(HS * vs);
+#pragma unroll
+		for (int q = 0; q < 4; q++) mean[q] = __fmul_rn(mean[q], sc);
+	}
+	float acc[4] = {0.f, 0.f, 0.f, 0.f};
+	if (p.op != BOX_PROD || p.normalized) {
+		for (int k = 0; k < vs; k++) {
+			float r[16];
+			load_vec<16>(r, base + k * p.pitch);
+#pragma unroll
+			for (int q = 0; q < 4; q++)
+#pragma unroll
+				for (int l = 0; l < HS; l++) {
+					float f = r[4 - HR + q + l];
+					if (p.zero_mean) f = __fsub_rn(f, mean[q]);
+					acc[q] = __fadd_rn(acc[q], stats_term(p.op, p.normalized, f));
+				}
+		}
+	}
+	float a[4], b[4];
+#pragma unroll
+	for (int q = 0; q < 4; q++) stats_finish(p, mean[q], acc[q], a[q], b[q]);
+	// columns past W inside the last group of four must stay zero (they are "outside the image" for the box kernel)
+	const int64_t o = (int64_t)i * p.pitch + j0;
+#pragma unroll
+	for (int q = 0; q < 4; q++) if (j0 + q < p.W) { p.A[o + q] = a[q]; p.B[o + q] = b[q]; }
+}
+
+// The reference's own sum per cell: features rebuilt on the fly as (v-mean)/norm, accumulated in channel order.
+struct DirectParams {
+	const float* ps; const float* pt; int64_t pitch;
+	const float* Ms; const float* Ns; const float* Mt; const float* Nt;   // STATS_RAW maps
+	int H, Ws, Wt, D, hr, vr, sign, mf, zero_mean, normalized;
+	float* out; int64_t o0, o1, o2;
+};
+
+__global__ void __launch_bounds__(128) k_cv_direct(const DirectParams p) {
+	const int j = blockIdx.x * 128 + threadIdx.x, d = blockIdx.y, i = blockIdx.z;
+	if (j >= p.Ws) return;
+	const int jt = j + p.sign * d;
+	const bool inside = jt >= 0 && jt < p.Wt;
+	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1;
+	const float* sb = p.ps + (int64_t)(i - p.vr) * p.pitch + (j - p.hr);
+	const float* tb = p.pt + (int64_t)(i - p.vr) * p.pitch + (jt - p.hr);
+	const float ms = p.Ms[(int64_t)i * p.pitch + j], ns = p.Ns[(int64_t)i * p.pitch + j];
+	float mt = 0.f, nt = 1.f;
+	if (inside) { mt = p.Mt[(int64_t)i * p.pitch + jt]; nt = p.Nt[(int64_t)i * p.pitch + jt]; }
+	const int op = mf_op(p.mf);
+	float acc = 0.f;
+	for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) {
+		float s = __ldg(sb + k * p.pitch + l);
+		if (p.zero_mean) s = __fsub_rn(s, ms);
+		if (p.normalized) s = __fdiv_rn(s, ns);
+		float t = 0.f;
+		if (inside) {
+			t = __ldg(tb + k * p.pitch + l);
+			if (p.zero_mean) t = __fsub_rn(t, mt);
+			if (p.normalized) t = __fdiv_rn(t, nt);
+		}
+		if (op == BOX_PROD) acc = __fadd_rn(acc, __fmul_rn(s, t));
+		else if (op == BOX_SQ) { float e = __fsub_rn(s, t); acc = __fadd_rn(acc, __fmul_rn(e, e)); }
+		else acc = __fadd_rn(acc, fabsf(__fsub_rn(s, t)));
+	}
+	p.out[(int64_t)i * p.o0 + (int64_t)j * p.o1 + (int64_t)d * p.o2] = acc;
+}
+
+// band height: few enough bands that the (2vr+1)-row start-up is amortised, enough blocks that the tail wave is small
+int pick_band_rows(int H, int blocks_per_band, int vr, int resident) {
+	int best = 32;
+	double best_cost = 1e30;
+	for (int R = 12; R <= 64; R++) {
+		const int bands = cdiv(H, R);
+		const double waves = (double)bands * blocks_per_band / resident;
+		const double tail = std::max(1.0, (double)(int64_t)(waves + 0.999)) / std::max(waves, 1e-9);
+		const double startup = (2.0 * vr + 1 + 2.0 * (R - 1)) / (2.0 * R);
+		const double cost = (waves < 1.0 ? 1.0 : tail) * startup * (double)(bands * R) / H;
+		if (cost < best_cost) { best_cost = cost; best = R; }
+	}
+	return best;
+}
+
+} // namespace
+
+int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows) {
+	if (l.ndim != 2 || r.ndim != 2) return fail(c, STEVI_E_UNSUPPORTED, "images must be 2-D (H,W)");
+	if (l.dtype != r.dtype || (l.dtype != STEVI_U8 && l.dtype != STEVI_F32))
+		return fail(c, STEVI_E_DTYPE, "images must both be u8 or both f32");
+	if (l.shape[0] != r.shape[0]) return fail(c, STEVI_E_SHAPE, "image heights differ (cross_correlations.h:751)");
+	H = l.shape[0];
+	if (H > 65535) return fail(c, STEVI_E_UNSUPPORTED, "more than 65535 rows");
+	const int Wmax = std::max(l.shape[1], r.shape[1]);
+	pad_left = (D + hr + 24 + 3) / 4 * 4;
+	pad_top = vr + 1;
+	pitch = pad_left + (Wmax + 127) / 128 * 128 + pad_left + 32;
+	rows = pad_top + (H + band_rows) + vr + 1;
+	plane = (size_t)rows * pitch;
+	float* buf = nullptr;
+	STEVI_TRY(arena_alloc_t(c, plane * 6, &buf));
+	STEVI_CUDA(c, cudaMemsetAsync(buf, 0, plane * 6 * sizeof(float), c->stream));
+	const int64_t org = (int64_t)pad_top * pitch + pad_left;
+	for (int k = 0; k < 2; k++) {
+		img[k] = buf + plane * (3 * k) + org;
+		A[k] = buf + plane * (3 * k + 1) + org;
+		B[k] = buf + plane * (3 * k + 2) + org;
+		const View& v = k == 0 ? l : r;
+		W[k] = v.shape[1];
+		if (H == 0 || W[k] == 0) continue;
+		dim3 grid(cdiv(W[k], 256), H);
+		if (v.dtype == STEVI_U8) {
+			STEVI_LAUNCH(c, k_pad_image<uint8_t>, grid, 256, 0, v.as<uint8_t>(), v.st[0], v.st[1], H, W[k], img[k] - org, pitch, pad_top, pad_left);
+		} else {
+			STEVI_LAUNCH(c, k_pad_image<float>, grid, 256, 0, v.as<float>(), v.st[0], v.st[1], H, W[k], img[k] - org, pitch, pad_top, pad_left);
+		}
+	}
+	return STEVI_OK;
+}
+
+int32_t PaddedPair::stats(stevi_ctx* c, int which, int hr, int vr, int mf, int kind) {
+	if (H == 0 || W[which] == 0) return STEVI_OK;
+	StatsParams p;
+	p.pimg = img[which]; p.pitch = pitch; p.H = H; p.W = W[which]; p.hr = hr; p.vr = vr;
+	p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf); p.op = mf_op(mf); p.kind = kind;
+	p.A = A[which]; p.B = B[which];
+	if (hr >= 1 && hr <= 4) {
+		dim3 grid(cdiv(p.W, 512), H);
+		switch (hr) {
+		case 1: STEVI_LAUNCH(c, k_window_stats<1>, grid, 128, 0, p); break;
+		case 2: STEVI_LAUNCH(c, k_window_stats<2>, grid, 128, 0, p); break;
+		case 3: STEVI_LAUNCH(c, k_window_stats<3>, grid, 128, 0, p); break;
+		default: STEVI_LAUNCH(c, k_window_stats<4>, grid, 128, 0, p); break;
+		}
+	} else {
+		dim3 grid(cdiv(p.W, 128), H);
+		STEVI_LAUNCH(c, k_window_stats_generic, grid, 128, 0, p);
+	}
+	return STEVI_OK;
+}
+
+int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, int D, int direction, const View& out,
+					 bool force_direct) {
+	switch (mf) {
+	case STEVI_MF_CC: case STEVI_MF_NCC: case STEVI_MF_ZCC: case STEVI_MF_ZNCC:
+	case STEVI_MF_SSD: case STEVI_MF_ZSSD: case STEVI_MF_SAD: case STEVI_MF_ZSAD: break;
+	default: return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: matching function %d not available", mf);
+	}
+	if (hr < 0 || vr < 0 || hr > 127 || vr > 127) return fail(c, STEVI_E_ARG, "cost_volume: radii out of range");
+	if (D < 0) return fail(c, STEVI_E_ARG, "cost_volume: negative disparity width");
+	if (l.ndim == 2 && r.ndim == 2 && l.dtype == STEVI_U8 && r.dtype == STEVI_U8 && (mf_zero_mean(mf) || mf_normalized(mf)))
+		return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: the reference's int16 fixed-point features for u8 images (cross_correlations.h:416-462) are not available; pass float images");
+	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
+	const bool direct = force_direct || mf == STEVI_MF_ZSAD || hr < 1 || hr > 4;
+	const int blocks_per_band = cdiv(r2l ? r.shape[1] : l.shape[1], 128) * cdiv(std::max(D, 1), 64);
+	const int R = direct ? 1 : pick_band_rows(l.shape[0], blocks_per_band, vr, 2 * c->sm_count);
+	PaddedPair pp;
+	STEVI_TRY(pp.build(c, l, r, hr, vr, D, R));
+	const int si = r2l ? 1 : 0, ti = 1 - si;
+	const int H = pp.H, Ws = pp.W[si], Wt = pp.W[ti];
+	if (out.ndim != 3 || out.shape[0] != H || out.shape[1] != Ws || out.shape[2] != D || out.dtype != STEVI_F32)
+		return fail(c, STEVI_E_SHAPE, "cost_volume: out must be (%d,%d,%d) f32", H, Ws, D);
+	if (H == 0 || Ws == 0 || D == 0) return STEVI_OK;
+	const int op = mf_op(mf);
+	if (direct) {
+		if (D > 65535) return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: more than 65535 disparities");
+		STEVI_TRY(pp.stats(c, si, hr, vr, mf, STATS_RAW));
+		STEVI_TRY(pp.stats(c, ti, hr, vr, mf, STATS_RAW));
+		DirectParams p;
+		p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch;
+		p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
+		p.H = H; p.Ws = Ws; p.Wt = Wt; p.D = D; p.hr = hr; p.vr = vr; p.sign = r2l ? 1 : -1; p.mf = mf;
+		p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf);
+		p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
+		dim3 grid(cdiv(Ws, 128), D, H);
+		STEVI_LAUNCH(c, k_cv_direct, grid, 128, 0, p);
+		return STEVI_OK;
+	}
+	STEVI_TRY(pp.stats(c, si, hr, vr, mf, op == BOX_PROD ? STATS_PROD_SRC : STATS_DIFF_SRC));
+	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, op == BOX_PROD ? STATS_PROD_TGT : STATS_DIFF_TGT));
+	BoxParams p;
+	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.As = pp.A[si]; p.Bs = pp.B[si]; p.At = pp.A[ti]; p.Bt = pp.B[ti];
+	p.pitch = pp.pitch; p.H = H; p.Ws = Ws; p.D = D; p.vr = vr; p.R = R;
+	p.Ff = (float)((2 * hr + 1) * (2 * vr + 1));
+	p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
+	p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0;
+	if (cdiv(H, R) > 65535) return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: too many row bands");
+	switch (op) {
+	case BOX_PROD: return launch_cv_box_prod(c, p, hr, r2l ? 1 : -1);
+	case BOX_SQ: return launch_cv_box_sq(c, p, hr, r2l ? 1 : -1);
+	default: return launch_cv_box_abs(c, p, hr, r2l ? 1 : -1);
+	}
+}
+
+} // namespace stevi

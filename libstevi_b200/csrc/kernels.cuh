@@ -15,6 +15,23 @@ int32_t census_transform_pair_dev(stevi_ctx* c, const View* imgs, const View* ou
 int32_t hamming_cv_dev(stevi_ctx* c, const View& feat_l, const View& feat_r, int n_cmp, int D, int direction,
 					   bool round_target, const View& out, int32_t* gmap, int pout_i);
 
+// costvol.cu: zero-padded float copies of an image pair plus two per-pixel window-statistics maps per image, all with
+// the same geometry (pointers are at pixel (0,0); `pitch` floats per row; pads are zero). index 0 = left, 1 = right.
+struct PaddedPair {
+	int H = 0, W[2] = {0, 0};
+	int pad_left = 0, pad_top = 0, rows = 0;
+	int64_t pitch = 0;
+	size_t plane = 0;
+	float* img[2] = {nullptr, nullptr};
+	float* A[2] = {nullptr, nullptr};
+	float* B[2] = {nullptr, nullptr};
+	int32_t build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows);
+	int32_t stats(stevi_ctx* c, int which, int hr, int vr, int mf, int kind);
+};
+// unfoldBasedCostVolume for CC/NCC/ZCC/ZNCC/SSD/ZSSD/SAD/ZSAD, out (H,Wsource,D) f32
+int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, int D, int direction, const View& out,
+					 bool force_direct);
+
 // sgm.cu
 // optional fused winner-take-all of the aggregated volume: out(i,j) = sign * argmin_d + offset (selectedIndexToDisp folded in)
 struct WtaSink { View out; int sign; int offset; };
