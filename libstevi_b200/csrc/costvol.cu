@@ -27,12 +27,13 @@ __host__ __device__ inline int mf_op(int mf) {
 	}
 }
 
-// zero-padded float copy: pixel (i,j) at out[(i+pad_top)*pitch + pad_left + j]; the buffer was cleared beforehand
+// zero-padded float copy in the unit-de-interleaved row layout of costvol_box.cuh: pixel (i,j) at
+// out[i*pitch + pad_col_off(pad_left + j)] (out points at image row 0); the buffer was cleared beforehand
 template<typename TI>
 __global__ void __launch_bounds__(256) k_pad_image(const TI* __restrict__ img, int64_t s0, int64_t s1, int H, int W,
-												   float* __restrict__ out, int64_t pitch, int pad_top, int pad_left) {
+												   float* __restrict__ out, int64_t pitch, int half, int pad_left) {
 	const int j = blockIdx.x * 256 + threadIdx.x, i = blockIdx.y;
-	if (j < W) out[(int64_t)(i + pad_top) * pitch + pad_left + j] = (float)img[i * s0 + j * s1];
+	if (j < W) out[(int64_t)i * pitch + pad_col_off(pad_left + j, half)] = (float)img[i * s0 + j * s1];
 }
 
 // what the statistics maps hold
@@ -43,11 +44,12 @@ enum { STATS_RAW = 0,       // A = mean, B = norm                               
 	   STATS_DIFF_TGT = 4 };// A = mean,   B = 1
 
 struct StatsParams {
-	const float* pimg;       // padded image at pixel (0,0)
+	const float* pimg;       // padded image plane at (image row 0, padded column 0)
 	int64_t pitch;
+	int half, pad_left;
 	int H, W, hr, vr;
 	int zero_mean, normalized, op, kind;
-	float* A; float* B;      // same geometry as the padded image, at pixel (0,0)
+	float* A; float* B;      // same geometry as the padded image
 };
 
 __device__ __forceinline__ void stats_finish(const StatsParams& p, float mean, float acc, float& a, float& b) {
@@ -73,25 +75,27 @@ __device__ __forceinline__ float stats_term(int op, bool normalized, float f) {
 __global__ void __launch_bounds__(128) k_window_stats_generic(const StatsParams p) {
 	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
 	if (j >= p.W) return;
-	const float* base = p.pimg + (int64_t)(i - p.vr) * p.pitch + (j - p.hr);
+	const float* base = p.pimg + (int64_t)(i - p.vr) * p.pitch;
+	const int X0 = p.pad_left + j - p.hr;
 	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1;
 	float mean = 0.f;
 	if (p.zero_mean) {
-		for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) mean = __fadd_rn(mean, __ldg(base + k * p.pitch + l));
+		for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) mean = __fadd_rn(mean, __ldg(base + k * p.pitch + pad_col_off(X0 + l, p.half)));
 		mean = __fmul_rn(mean, 1.f / (float)(hs * vs));
 	}
 	float acc = 0.f;
 	if (p.op != BOX_PROD || p.normalized) {
 		for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) {
-			float f = __ldg(base + k * p.pitch + l);
+			float f = __ldg(base + k * p.pitch + pad_col_off(X0 + l, p.half));
 			if (p.zero_mean) f = __fsub_rn(f, mean);
 			acc = __fadd_rn(acc, stats_term(p.op, p.normalized, f));
 		}
 	}
 	float a, b;
 	stats_finish(p, mean, acc, a, b);
-	p.A[(int64_t)i * p.pitch + j] = a;
-	p.B[(int64_t)i * p.pitch + j] = b;
+	const int64_t o = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
+	p.A[o] = a;
+	p.B[o] = b;
 }
 
 // windows up to 9 wide: a thread owns 4 consecutive pixels and reads each window row as four aligned 16-byte loads;
@@ -100,14 +104,16 @@ template<int HR>
 __global__ void __launch_bounds__(128) k_window_stats(const StatsParams p) {
 	const int j0 = (blockIdx.x * 128 + threadIdx.x) * 4, i = blockIdx.y;
 	if (j0 >= p.W) return;
-	const float* base = p.pimg + (int64_t)(i - p.vr) * p.pitch + (j0 - 4);
+	const float* base = p.pimg + (int64_t)(i - p.vr) * p.pitch;
+	const int u = (p.pad_left + j0) >> 2;   // this thread's unit; the window rows span units u-1 .. u+2
+	const int oA = pad_unit_off(u - 1, p.half), oB = pad_unit_off(u, p.half);
 	const int vs = 2 * p.vr + 1;
 	constexpr int HS = 2 * HR + 1;
 	float mean[4] = {0.f, 0.f, 0.f, 0.f};
 	if (p.zero_mean) {
 		for (int k = 0; k < vs; k++) {
 			float r[16];
-			load_vec<16>(r, base + k * p.pitch);
+			load_units<4>(r, base + k * p.pitch, oA, oB);
 #pragma unroll
 			for (int q = 0; q < 4; q++)
 #pragma unroll
@@ -121,7 +127,7 @@ __global__ void __launch_bounds__(128) k_window_stats(const StatsParams p) {
 	if (p.op != BOX_PROD || p.normalized) {
 		for (int k = 0; k < vs; k++) {
 			float r[16];
-			load_vec<16>(r, base + k * p.pitch);
+			load_units<4>(r, base + k * p.pitch, oA, oB);
 #pragma unroll
 			for (int q = 0; q < 4; q++)
 #pragma unroll
@@ -136,14 +142,14 @@ __global__ void __launch_bounds__(128) k_window_stats(const StatsParams p) {
 #pragma unroll
 	for (int q = 0; q < 4; q++) stats_finish(p, mean[q], acc[q], a[q], b[q]);
 	// columns past W inside the last group of four must stay zero (they are "outside the image" for the box kernel)
-	const int64_t o = (int64_t)i * p.pitch + j0;
+	const int64_t o = (int64_t)i * p.pitch + oB;
 #pragma unroll
 	for (int q = 0; q < 4; q++) if (j0 + q < p.W) { p.A[o + q] = a[q]; p.B[o + q] = b[q]; }
 }
 
 // The reference's own sum per cell: features rebuilt on the fly as (v-mean)/norm, accumulated in channel order.
 struct DirectParams {
-	const float* ps; const float* pt; int64_t pitch;
+	const float* ps; const float* pt; int64_t pitch; int half, pad_left;
 	const float* Ms; const float* Ns; const float* Mt; const float* Nt;   // STATS_RAW maps
 	int H, Ws, Wt, D, hr, vr, sign, mf, zero_mean, normalized;
 	float* out; int64_t o0, o1, o2;
@@ -155,20 +161,25 @@ __global__ void __launch_bounds__(128) k_cv_direct(const DirectParams p) {
 	const int jt = j + p.sign * d;
 	const bool inside = jt >= 0 && jt < p.Wt;
 	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1;
-	const float* sb = p.ps + (int64_t)(i - p.vr) * p.pitch + (j - p.hr);
-	const float* tb = p.pt + (int64_t)(i - p.vr) * p.pitch + (jt - p.hr);
-	const float ms = p.Ms[(int64_t)i * p.pitch + j], ns = p.Ns[(int64_t)i * p.pitch + j];
+	const float* sb = p.ps + (int64_t)(i - p.vr) * p.pitch;
+	const float* tb = p.pt + (int64_t)(i - p.vr) * p.pitch;
+	const int Xs = p.pad_left + j - p.hr, Xt = p.pad_left + jt - p.hr;
+	const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
+	const float ms = p.Ms[os], ns = p.Ns[os];
 	float mt = 0.f, nt = 1.f;
-	if (inside) { mt = p.Mt[(int64_t)i * p.pitch + jt]; nt = p.Nt[(int64_t)i * p.pitch + jt]; }
+	if (inside) {
+		const int64_t ot = (int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half);
+		mt = p.Mt[ot]; nt = p.Nt[ot];
+	}
 	const int op = mf_op(p.mf);
 	float acc = 0.f;
 	for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) {
-		float s = __ldg(sb + k * p.pitch + l);
+		float s = __ldg(sb + k * p.pitch + pad_col_off(Xs + l, p.half));
 		if (p.zero_mean) s = __fsub_rn(s, ms);
 		if (p.normalized) s = __fdiv_rn(s, ns);
 		float t = 0.f;
 		if (inside) {
-			t = __ldg(tb + k * p.pitch + l);
+			t = __ldg(tb + k * p.pitch + pad_col_off(Xt + l, p.half));
 			if (p.zero_mean) t = __fsub_rn(t, mt);
 			if (p.normalized) t = __fdiv_rn(t, nt);
 		}
@@ -183,7 +194,7 @@ __global__ void __launch_bounds__(128) k_cv_direct(const DirectParams p) {
 int pick_band_rows(int H, int blocks_per_band, int vr, int resident) {
 	int best = 32;
 	double best_cost = 1e30;
-	for (int R = 12; R <= 64; R++) {
+	for (int R = 12; R <= 64 && R + 2 * vr <= BOX_MAX_TILE_ROWS; R++) {
 		const int bands = cdiv(H, R);
 		const double waves = (double)bands * blocks_per_band / resident;
 		const double tail = std::max(1.0, (double)(int64_t)(waves + 0.999)) / std::max(waves, 1e-9);
@@ -204,15 +215,16 @@ int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, in
 	H = l.shape[0];
 	if (H > 65535) return fail(c, STEVI_E_UNSUPPORTED, "more than 65535 rows");
 	const int Wmax = std::max(l.shape[1], r.shape[1]);
-	pad_left = (D + hr + 24 + 3) / 4 * 4;
+	pad_left = (D + hr + 48 + 7) / 8 * 8;
 	pad_top = vr + 1;
-	pitch = pad_left + (Wmax + 127) / 128 * 128 + pad_left + 32;
+	pitch = (pad_left + (Wmax + 127) / 128 * 128 + pad_left + 64 + 63) / 64 * 64;
+	half = (int)(pitch / 2);
 	rows = pad_top + (H + band_rows) + vr + 1;
 	plane = (size_t)rows * pitch;
 	float* buf = nullptr;
 	STEVI_TRY(arena_alloc_t(c, plane * 6, &buf));
 	STEVI_CUDA(c, cudaMemsetAsync(buf, 0, plane * 6 * sizeof(float), c->stream));
-	const int64_t org = (int64_t)pad_top * pitch + pad_left;
+	const int64_t org = (int64_t)pad_top * pitch;
 	for (int k = 0; k < 2; k++) {
 		img[k] = buf + plane * (3 * k) + org;
 		A[k] = buf + plane * (3 * k + 1) + org;
@@ -222,9 +234,9 @@ int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, in
 		if (H == 0 || W[k] == 0) continue;
 		dim3 grid(cdiv(W[k], 256), H);
 		if (v.dtype == STEVI_U8) {
-			STEVI_LAUNCH(c, k_pad_image<uint8_t>, grid, 256, 0, v.as<uint8_t>(), v.st[0], v.st[1], H, W[k], img[k] - org, pitch, pad_top, pad_left);
+			STEVI_LAUNCH(c, k_pad_image<uint8_t>, grid, 256, 0, v.as<uint8_t>(), v.st[0], v.st[1], H, W[k], img[k], pitch, half, pad_left);
 		} else {
-			STEVI_LAUNCH(c, k_pad_image<float>, grid, 256, 0, v.as<float>(), v.st[0], v.st[1], H, W[k], img[k] - org, pitch, pad_top, pad_left);
+			STEVI_LAUNCH(c, k_pad_image<float>, grid, 256, 0, v.as<float>(), v.st[0], v.st[1], H, W[k], img[k], pitch, half, pad_left);
 		}
 	}
 	return STEVI_OK;
@@ -233,7 +245,7 @@ int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, in
 int32_t PaddedPair::stats(stevi_ctx* c, int which, int hr, int vr, int mf, int kind) {
 	if (H == 0 || W[which] == 0) return STEVI_OK;
 	StatsParams p;
-	p.pimg = img[which]; p.pitch = pitch; p.H = H; p.W = W[which]; p.hr = hr; p.vr = vr;
+	p.pimg = img[which]; p.pitch = pitch; p.half = half; p.pad_left = pad_left; p.H = H; p.W = W[which]; p.hr = hr; p.vr = vr;
 	p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf); p.op = mf_op(mf); p.kind = kind;
 	p.A = A[which]; p.B = B[which];
 	if (hr >= 1 && hr <= 4) {
@@ -263,9 +275,9 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 	if (l.ndim == 2 && r.ndim == 2 && l.dtype == STEVI_U8 && r.dtype == STEVI_U8 && (mf_zero_mean(mf) || mf_normalized(mf)))
 		return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: the reference's int16 fixed-point features for u8 images (cross_correlations.h:416-462) are not available; pass float images");
 	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
-	const bool direct = force_direct || mf == STEVI_MF_ZSAD || hr < 1 || hr > 4;
-	const int blocks_per_band = cdiv(r2l ? r.shape[1] : l.shape[1], 128) * cdiv(std::max(D, 1), 64);
-	const int R = direct ? 1 : pick_band_rows(l.shape[0], blocks_per_band, vr, 2 * c->sm_count);
+	const bool direct = force_direct || mf == STEVI_MF_ZSAD || hr < 1 || hr > 4 || 12 + 2 * vr > BOX_MAX_TILE_ROWS;
+	const int blocks_per_band = cdiv(r2l ? r.shape[1] : l.shape[1], 128) * cdiv(std::max(D, 1), BOX_D_PER_BLOCK);
+	const int R = direct ? 1 : pick_band_rows(l.shape[0], blocks_per_band, vr, BOX_BLOCKS_PER_SM * c->sm_count);
 	PaddedPair pp;
 	STEVI_TRY(pp.build(c, l, r, hr, vr, D, R));
 	const int si = r2l ? 1 : 0, ti = 1 - si;
@@ -279,7 +291,7 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 		STEVI_TRY(pp.stats(c, si, hr, vr, mf, STATS_RAW));
 		STEVI_TRY(pp.stats(c, ti, hr, vr, mf, STATS_RAW));
 		DirectParams p;
-		p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch;
+		p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left;
 		p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
 		p.H = H; p.Ws = Ws; p.Wt = Wt; p.D = D; p.hr = hr; p.vr = vr; p.sign = r2l ? 1 : -1; p.mf = mf;
 		p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf);
@@ -292,7 +304,7 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, op == BOX_PROD ? STATS_PROD_TGT : STATS_DIFF_TGT));
 	BoxParams p;
 	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.As = pp.A[si]; p.Bs = pp.B[si]; p.At = pp.A[ti]; p.Bt = pp.B[ti];
-	p.pitch = pp.pitch; p.H = H; p.Ws = Ws; p.D = D; p.vr = vr; p.R = R;
+	p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left; p.H = H; p.Ws = Ws; p.D = D; p.vr = vr; p.R = R;
 	p.Ff = (float)((2 * hr + 1) * (2 * vr + 1));
 	p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
 	p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0;

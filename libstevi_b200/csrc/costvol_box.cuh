@@ -20,7 +20,9 @@
 // Work split: a thread owns 8 consecutive source columns x 4 consecutive disparities and walks down a band of R rows.
 // The vertical window sums V[q][c] (NV = 16 columns incl. the +-hr halo, hr <= 4) live in registers and are updated per row
 // with the entering and the leaving image row (2 FMA per V); the horizontal sums slide over the 8 output columns.
-// Image rows come through L1/L2 as aligned 16-byte loads from zero-padded float copies (they are a few MB: L2-resident);
+// The block's band of image rows (R + 2vr rows of 136 source and 168 target columns) is brought into shared memory by
+// the TMA engine (cp.async.bulk, one mbarrier) from zero-padded, unit-de-interleaved float copies of the images, and
+// read back with conflict-free 16-byte LDS;
 // stores are 2 x 16 bytes per (row, d) and thread — a half-warp writes 512 contiguous bytes of the reference's
 // [H][D][W] layout.
 #pragma once
@@ -29,83 +31,182 @@
 namespace stevi {
 
 enum { BOX_PROD = 0, BOX_SQ = 1, BOX_ABS = 2 };
+// a block = 16 column groups (128 source columns) x 8 disparity groups (32 disparities); three blocks per SM leave
+// 168 registers per thread, enough for the 64 window sums plus the row being consumed without spilling
+constexpr int BOX_THREADS = 128, BOX_BLOCKS_PER_SM = 3, BOX_D_PER_BLOCK = 32;
+
+// Geometry of the padded planes (images and statistics maps share it). A padded row holds `pitch` floats (a multiple of
+// 64); padded column X = pad_left + j. The row is stored DE-INTERLEAVED by 16-byte units: unit u = X/4 lives at
+// (u&1)*pitch/2 + (u>>1)*4. Threads of a warp own 8 consecutive columns each, i.e. their windows start two units apart:
+// with this layout the k-th 16-byte load of all lanes is one contiguous run (one wavefront per 128 bytes) instead of
+// 16-byte pieces at a 32-byte stride (two).
+__host__ __device__ __forceinline__ int pad_unit_off(int u, int half) { return (u & 1) * half + (u >> 1) * 4; }
+__host__ __device__ __forceinline__ int pad_col_off(int X, int half) { return pad_unit_off(X >> 2, half) + (X & 3); }
 
 struct BoxParams {
-	const float* ps; const float* pt;   // padded images, pointing at pixel (0,0); pitch in floats (multiple of 4)
-	const float* As; const float* Bs;   // source window statistics, same geometry as ps
-	const float* At; const float* Bt;   // target window statistics, same geometry as pt
+	const float* ps; const float* pt;   // padded image planes, pointing at padded column 0 of image row 0
+	const float* As; const float* Bs;   // source window statistics, same geometry
+	const float* At; const float* Bt;   // target window statistics
 	int64_t pitch;
+	int half, pad_left;
 	int H, Ws, D, vr, R;
 	float Ff;                           // number of features F as float
 	float* out; int64_t o0, o1, o2;
 	int vec_store;                      // o1 == 1, 16-byte aligned rows
 };
 
-template<int N> __device__ __forceinline__ void load_vec(float (&dst)[N], const float* __restrict__ p) {
+// NU consecutive units starting at a unit whose offset is offA (the next one is at offB, then offA+4, offB+4, ...)
+template<int NU> __device__ __forceinline__ void load_units(float (&dst)[4 * NU], const float* __restrict__ row, int offA, int offB) {
 #pragma unroll
-	for (int k = 0; k < N / 4; k++) {
-		float4 v = __ldg(reinterpret_cast<const float4*>(p) + k);
+	for (int k = 0; k < NU; k++) {
+		const float4 v = __ldg(reinterpret_cast<const float4*>(row + ((k & 1) ? offB : offA) + 4 * (k >> 1)));
 		dst[4 * k] = v.x; dst[4 * k + 1] = v.y; dst[4 * k + 2] = v.z; dst[4 * k + 3] = v.w;
 	}
 }
 
+__device__ __forceinline__ float4 load_unit(const float* __restrict__ row, int off) {
+	return __ldg(reinterpret_cast<const float4*>(row + off));
+}
+
+// ---- shared-memory band tile, filled by the TMA engine (1-D bulk copies completing on an mbarrier) -------------------
+// per tile row: [s: 17 units of the first parity | 17 of the other | t: 21 units of the first parity | 21 of the other]
+constexpr int BOX_S_UNITS = 17, BOX_T_UNITS = 21;
+constexpr int BOX_ROW_FLOATS = 4 * (2 * BOX_S_UNITS + 2 * BOX_T_UNITS);   // 304 floats = 1216 bytes
+constexpr int BOX_MAX_TILE_ROWS = 60;                                       // 3 blocks/SM x 60 x 1216 B = 214 KB
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+	asm volatile("{\n\t.reg .pred p;\n\tBOX_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra BOX_DONE;\n\tbra BOX_WAIT;\n\tBOX_DONE:\n\t}"
+				 :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (UBLKCP): 16-byte aligned on both sides, size a multiple of 16
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+				 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ float4 lds_unit(const float* __restrict__ row, int off) {
+	return *reinterpret_cast<const float4*>(row + off);
+}
+
+// V[q][c] += / -= op(s(c), t(c + SIGN*(d0+q))) for one tile row. The row is consumed unit by unit (4 source columns
+// against a sliding pair of target units) so that few loaded values are live at a time.
 template<int OP, int NV, int SIGN, bool ADD>
-__device__ __forceinline__ void box_accum_row(float (&V)[4][NV], const float* __restrict__ srow, const float* __restrict__ trow) {
-	float s[NV], t[NV + 4];
-	load_vec<NV>(s, srow);
-	load_vec<NV + 4>(t, trow);
+__device__ __forceinline__ void box_accum_row(float (&V)[4][NV], const float* __restrict__ row, int sA, int sB, int tA, int tB) {
+	float4 t0 = lds_unit(row, tA);
 #pragma unroll
-	for (int q = 0; q < 4; q++) {
+	for (int k = 0; k < NV / 4; k++) {
+		const float4 sv = lds_unit(row, ((k & 1) ? sB : sA) + 4 * (k >> 1));
+		const float4 t1 = lds_unit(row, (((k + 1) & 1) ? tB : tA) + 4 * ((k + 1) >> 1));
+		const float s[4] = {sv.x, sv.y, sv.z, sv.w};
+		const float t[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
 #pragma unroll
-		for (int c = 0; c < NV; c++) {
-			const float tv = SIGN > 0 ? t[c + q] : t[c + 4 - q];
-			if (OP == BOX_PROD) {
-				V[q][c] = fmaf(ADD ? s[c] : -s[c], tv, V[q][c]);
-			} else if (OP == BOX_SQ) {
-				const float e = s[c] - tv;
-				V[q][c] = fmaf(ADD ? e : -e, e, V[q][c]);
-			} else {
-				const float e = fabsf(s[c] - tv);
-				V[q][c] = ADD ? V[q][c] + e : V[q][c] - e;
+		for (int cc = 0; cc < 4; cc++) {
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				const float tv = SIGN > 0 ? t[cc + q] : t[cc + 4 - q];
+				float& v = V[q][4 * k + cc];
+				if (OP == BOX_PROD) {
+					v = fmaf(ADD ? s[cc] : -s[cc], tv, v);
+				} else if (OP == BOX_SQ) {
+					const float e = s[cc] - tv;
+					v = fmaf(ADD ? e : -e, e, v);
+				} else {
+					const float e = fabsf(s[cc] - tv);
+					v = ADD ? v + e : v - e;
+				}
 			}
 		}
+		t0 = t1;
 	}
 }
 
 template<int OP, int HR, int SIGN>
-__global__ void __launch_bounds__(256, 2) k_cv_box(const BoxParams p) {
+__global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const BoxParams p) {
 	static_assert(HR >= 1 && HR <= 4, "window half-width");
 	constexpr int NV = 16;                  // V columns j0-4 .. j0+11
 	constexpr int LH = 4;                   // left halo
+	extern __shared__ __align__(128) float tile[];
+	__shared__ uint64_t bar;
 	const int cg = threadIdx.x & 15, dg = threadIdx.x >> 4;
-	const int j0 = blockIdx.x * 128 + cg * 8;
-	const int d0 = blockIdx.y * 64 + dg * 4;
+	const int jb = blockIdx.x * 128, db = blockIdx.y * BOX_D_PER_BLOCK;
+	const int j0 = jb + cg * 8;
+	const int d0 = db + dg * 4;
 	const int i0 = blockIdx.z * p.R;
-	if (d0 >= p.D || j0 >= p.Ws) return;
+	const int n_rows = p.R + 2 * p.vr;      // tile row r <-> image row i0 - vr + r
+	// first unit of the block's source window, and of its target window (lowest column any of its threads reads)
+	const int us_blk = (p.pad_left + jb - LH) >> 2;
+	const int ut_blk = (p.pad_left + (SIGN > 0 ? (jb - LH + db) : (jb - LH - db - BOX_D_PER_BLOCK))) >> 2;
+	if (threadIdx.x == 0) {
+		mbar_init(&bar, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	if (threadIdx.x < 32) {
+		if (threadIdx.x == 0) mbar_expect_tx(&bar, (uint32_t)n_rows * BOX_ROW_FLOATS * 4);
+		__syncwarp();
+		const int gsA = pad_unit_off(us_blk, p.half), gsB = pad_unit_off(us_blk + 1, p.half);
+		const int gtA = pad_unit_off(ut_blk, p.half), gtB = pad_unit_off(ut_blk + 1, p.half);
+		for (int r = threadIdx.x; r < n_rows; r += 32) {
+			const int64_t go = (int64_t)(i0 - p.vr + r) * p.pitch;
+			float* dst = tile + r * BOX_ROW_FLOATS;
+			bulk_g2s(dst, p.ps + go + gsA, BOX_S_UNITS * 16, &bar);
+			bulk_g2s(dst + 4 * BOX_S_UNITS, p.ps + go + gsB, BOX_S_UNITS * 16, &bar);
+			bulk_g2s(dst + 8 * BOX_S_UNITS, p.pt + go + gtA, BOX_T_UNITS * 16, &bar);
+			bulk_g2s(dst + 8 * BOX_S_UNITS + 4 * BOX_T_UNITS, p.pt + go + gtB, BOX_T_UNITS * 16, &bar);
+		}
+	}
 	// V column c <-> source column j0-LH+c; target column = source column + SIGN*(d0+q):
-	//   SIGN>0: base j0-LH+d0, register c+q ; SIGN<0: base j0-LH-d0-4, register c+4-q
-	const float* __restrict__ sb = p.ps + (j0 - LH);
-	const float* __restrict__ tb = p.pt + (SIGN > 0 ? (j0 - LH + d0) : (j0 - LH - d0 - 4));
+	//   SIGN>0: first target column j0-LH+d0, register c+q ; SIGN<0: first target column j0-LH-d0-4, register c+4-q
+	// offsets inside a tile row: unit x of the block window sits in parity half (x&1) at index x>>1
+	const int sA = 4 * cg, sB = 4 * (BOX_S_UNITS + cg);
+	const int xt = 2 * cg + (SIGN > 0 ? dg : (BOX_D_PER_BLOCK / 4 - 1 - dg));
+	const int tbase = 8 * BOX_S_UNITS;
+	const int tA = tbase + ((xt & 1) ? 4 * (BOX_T_UNITS + (xt >> 1)) : 4 * (xt >> 1));
+	const int tB = tbase + ((xt & 1) ? 4 * ((xt + 1) >> 1) : 4 * (BOX_T_UNITS + (xt >> 1)));
+	// offsets of the same units in the global statistics planes
+	const int us = us_blk + 2 * cg, ut = ut_blk + xt;
+	const int gsA = pad_unit_off(us, p.half), gsB = pad_unit_off(us + 1, p.half);
+	const int gtA = pad_unit_off(ut, p.half), gtB = pad_unit_off(ut + 1, p.half);
+	const bool live = d0 < p.D && j0 < p.Ws;
 	float V[4][NV];
 #pragma unroll
 	for (int q = 0; q < 4; q++)
 #pragma unroll
 		for (int c = 0; c < NV; c++) V[q][c] = 0.f;
-	for (int k = -p.vr; k <= p.vr; k++)
-		box_accum_row<OP, NV, SIGN, true>(V, sb + (int64_t)(i0 + k) * p.pitch, tb + (int64_t)(i0 + k) * p.pitch);
+	mbar_wait(&bar, 0);
+	if (!live) return;
+	for (int r = 0; r <= 2 * p.vr; r++)
+		box_accum_row<OP, NV, SIGN, true>(V, tile + r * BOX_ROW_FLOATS, sA, sB, tA, tB);
 	const int i_end = min(i0 + p.R, p.H);
 	for (int i = i0; i < i_end; i++) {
+		const int64_t ro = (int64_t)i * p.pitch;
+		// per-pixel statistics of this row, requested before the window update so that their latency hides behind it:
+		// source: units of columns j0, j0+4; target: three units from column j0 + SIGN*d0 (-4)
+		const float4 as0 = load_unit(p.As + ro, gsB), as1 = load_unit(p.As + ro, gsA + 4);
+		const float4 bs0 = load_unit(p.Bs + ro, gsB), bs1 = load_unit(p.Bs + ro, gsA + 4);
+		float4 at0, at1, at2;
+		if (OP != BOX_ABS) { at0 = load_unit(p.At + ro, gtB); at1 = load_unit(p.At + ro, gtA + 4); at2 = load_unit(p.At + ro, gtB + 4); }
+		const float4 bt0 = load_unit(p.Bt + ro, gtB), bt1 = load_unit(p.Bt + ro, gtA + 4), bt2 = load_unit(p.Bt + ro, gtB + 4);
 		if (i > i0) {
-			box_accum_row<OP, NV, SIGN, true>(V, sb + (int64_t)(i + p.vr) * p.pitch, tb + (int64_t)(i + p.vr) * p.pitch);
-			box_accum_row<OP, NV, SIGN, false>(V, sb + (int64_t)(i - p.vr - 1) * p.pitch, tb + (int64_t)(i - p.vr - 1) * p.pitch);
+			const int r = i - i0;
+			box_accum_row<OP, NV, SIGN, true>(V, tile + (r + 2 * p.vr) * BOX_ROW_FLOATS, sA, sB, tA, tB);
+			box_accum_row<OP, NV, SIGN, false>(V, tile + (r - 1) * BOX_ROW_FLOATS, sA, sB, tA, tB);
 		}
-		// per-pixel statistics: source columns j0..j0+7; target columns j0+k+SIGN*(d0+q)
-		float as[8], bs[8], at[12], bt[12];
-		load_vec<8>(as, p.As + (int64_t)i * p.pitch + j0);
-		load_vec<8>(bs, p.Bs + (int64_t)i * p.pitch + j0);
-		const int64_t toff = (int64_t)i * p.pitch + (SIGN > 0 ? (j0 + d0) : (j0 - d0 - 4));
-		if (OP != BOX_ABS) load_vec<12>(at, p.At + toff);
-		load_vec<12>(bt, p.Bt + toff);
+		const float as[8] = {as0.x, as0.y, as0.z, as0.w, as1.x, as1.y, as1.z, as1.w};
+		const float bs[8] = {bs0.x, bs0.y, bs0.z, bs0.w, bs1.x, bs1.y, bs1.z, bs1.w};
+		float at[12];
+		if (OP != BOX_ABS) {
+			at[0] = at0.x; at[1] = at0.y; at[2] = at0.z; at[3] = at0.w; at[4] = at1.x; at[5] = at1.y; at[6] = at1.z; at[7] = at1.w;
+			at[8] = at2.x; at[9] = at2.y; at[10] = at2.z; at[11] = at2.w;
+		}
+		const float bt[12] = {bt0.x, bt0.y, bt0.z, bt0.w, bt1.x, bt1.y, bt1.z, bt1.w, bt2.x, bt2.y, bt2.z, bt2.w};
 #pragma unroll
 		for (int q = 0; q < 4; q++) {
 			if (d0 + q >= p.D) break;
@@ -130,10 +231,10 @@ __global__ void __launch_bounds__(256, 2) k_cv_box(const BoxParams p) {
 				}
 				o[k] = v;
 			}
+			float* dst = p.out + (int64_t)i * p.o0 + (int64_t)(d0 + q) * p.o2;
 			if (p.vec_store && j0 + 8 <= p.Ws) {
-				float4* dst = reinterpret_cast<float4*>(p.out + (int64_t)i * p.o0 + (int64_t)(d0 + q) * p.o2 + j0);
-				__stcs(dst, make_float4(o[0], o[1], o[2], o[3]));
-				__stcs(dst + 1, make_float4(o[4], o[5], o[6], o[7]));
+				__stcs(reinterpret_cast<float4*>(dst + j0), make_float4(o[0], o[1], o[2], o[3]));
+				__stcs(reinterpret_cast<float4*>(dst + j0 + 4), make_float4(o[4], o[5], o[6], o[7]));
 			} else {
 #pragma unroll
 				for (int k = 0; k < 8; k++)
@@ -145,14 +246,20 @@ __global__ void __launch_bounds__(256, 2) k_cv_box(const BoxParams p) {
 
 template<int OP, int HR>
 static int32_t launch_cv_box_hr(stevi_ctx* c, const BoxParams& p, int sign, dim3 grid) {
-	if (sign > 0) { STEVI_LAUNCH(c, (k_cv_box<OP, HR, 1>), grid, 256, 0, p); }
-	else { STEVI_LAUNCH(c, (k_cv_box<OP, HR, -1>), grid, 256, 0, p); }
+	const int smem = (p.R + 2 * p.vr) * BOX_ROW_FLOATS * 4;
+	if (sign > 0) {
+		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_MAX_TILE_ROWS * BOX_ROW_FLOATS * 4));
+		STEVI_LAUNCH(c, (k_cv_box<OP, HR, 1>), grid, BOX_THREADS, smem, p);
+	} else {
+		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_MAX_TILE_ROWS * BOX_ROW_FLOATS * 4));
+		STEVI_LAUNCH(c, (k_cv_box<OP, HR, -1>), grid, BOX_THREADS, smem, p);
+	}
 	return STEVI_OK;
 }
 
 template<int OP>
 int32_t launch_cv_box(stevi_ctx* c, const BoxParams& p, int hr, int sign) {
-	dim3 grid(cdiv(p.Ws, 128), cdiv(p.D, 64), cdiv(p.H, p.R));
+	dim3 grid(cdiv(p.Ws, 128), cdiv(p.D, BOX_D_PER_BLOCK), cdiv(p.H, p.R));
 	switch (hr) {
 	case 1: return launch_cv_box_hr<OP, 1>(c, p, sign, grid);
 	case 2: return launch_cv_box_hr<OP, 2>(c, p, sign, grid);

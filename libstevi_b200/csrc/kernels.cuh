@@ -16,10 +16,11 @@ int32_t hamming_cv_dev(stevi_ctx* c, const View& feat_l, const View& feat_r, int
 					   bool round_target, const View& out, int32_t* gmap, int pout_i);
 
 // costvol.cu: zero-padded float copies of an image pair plus two per-pixel window-statistics maps per image, all with
-// the same geometry (pointers are at pixel (0,0); `pitch` floats per row; pads are zero). index 0 = left, 1 = right.
+// the same geometry (pointers are at image row 0, padded column 0; `pitch` floats per row in the unit-de-interleaved
+// layout of costvol_box.cuh; pads are zero). index 0 = left, 1 = right.
 struct PaddedPair {
 	int H = 0, W[2] = {0, 0};
-	int pad_left = 0, pad_top = 0, rows = 0;
+	int pad_left = 0, pad_top = 0, rows = 0, half = 0;
 	int64_t pitch = 0;
 	size_t plane = 0;
 	float* img[2] = {nullptr, nullptr};
