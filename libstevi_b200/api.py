@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libstevi_b200.so")
+LIB_PATH = os.environ.get("STEVI_B200_LIB") or os.path.join(_HERE, "libstevi_b200.so")  # env override: kernel experiments
 
 # enums (include/stevi_b200/c_api.h)
 OK, E_SHAPE, E_DTYPE, E_UNSUPPORTED, E_CUDA, E_NCCL, E_ARG = range(7)

@@ -22,7 +22,8 @@
 // with the entering and the leaving image row (2 FMA per V); the horizontal sums slide over the 8 output columns.
 // The block's band of image rows (R + 2vr rows of 136 source and 168 target columns) is brought into shared memory by
 // the TMA engine (cp.async.bulk, one mbarrier) from zero-padded, unit-de-interleaved float copies of the images, and
-// read back with conflict-free 16-byte LDS;
+// read back with conflict-free 16-byte LDS; the per-pixel statistics rows follow through a 4-slot shared-memory ring
+// filled the same way three rows ahead (as plain LDGs they queued behind the stores: 0.46 ms vs 0.31 ms without them);
 // stores are 2 x 16 bytes per (row, d) and thread — a half-warp writes 512 contiguous bytes of the reference's
 // [H][D][W] layout.
 #pragma once
@@ -72,7 +73,11 @@ __device__ __forceinline__ float4 load_unit(const float* __restrict__ row, int o
 // per tile row: [s: 17 units of the first parity | 17 of the other | t: 21 units of the first parity | 21 of the other]
 constexpr int BOX_S_UNITS = 17, BOX_T_UNITS = 21;
 constexpr int BOX_ROW_FLOATS = 4 * (2 * BOX_S_UNITS + 2 * BOX_T_UNITS);   // 304 floats = 1216 bytes
-constexpr int BOX_MAX_TILE_ROWS = 60;                                       // 3 blocks/SM x 60 x 1216 B = 214 KB
+// ring of per-pixel statistics rows: [As: 16 units | 16][Bs: 16 | 16][At: 20 | 20][Bt: 20 | 20] (parity halves)
+constexpr int BOX_SS_UNITS = 16, BOX_ST_UNITS = 20, BOX_STAT_SLOTS = 4;
+constexpr int BOX_STAT_FLOATS = 4 * (4 * BOX_SS_UNITS + 4 * BOX_ST_UNITS);  // 576 floats = 2304 bytes
+constexpr int BOX_MAX_TILE_ROWS = 54;   // 3 blocks/SM x (54 x 1216 + 4 x 2304 + static) B = 219 KB of the 227 KB
+constexpr int BOX_SMEM_MAX = BOX_MAX_TILE_ROWS * BOX_ROW_FLOATS * 4 + BOX_STAT_SLOTS * BOX_STAT_FLOATS * 4;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -132,35 +137,58 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 	static_assert(HR >= 1 && HR <= 4, "window half-width");
 	constexpr int NV = 16;                  // V columns j0-4 .. j0+11
 	constexpr int LH = 4;                   // left halo
-	extern __shared__ __align__(128) float tile[];
-	__shared__ uint64_t bar;
+	extern __shared__ __align__(128) float smem[];
+	__shared__ uint64_t bar_img, bar_st[BOX_STAT_SLOTS];
+	float* stat_ring = smem;                                  // BOX_STAT_SLOTS rows of per-pixel statistics
+	float* tile = smem + BOX_STAT_SLOTS * BOX_STAT_FLOATS;    // the band of image rows
 	const int cg = threadIdx.x & 15, dg = threadIdx.x >> 4;
 	const int jb = blockIdx.x * 128, db = blockIdx.y * BOX_D_PER_BLOCK;
 	const int j0 = jb + cg * 8;
 	const int d0 = db + dg * 4;
 	const int i0 = blockIdx.z * p.R;
+	const int i_end = min(i0 + p.R, p.H);
 	const int n_rows = p.R + 2 * p.vr;      // tile row r <-> image row i0 - vr + r
 	// first unit of the block's source window, and of its target window (lowest column any of its threads reads)
 	const int us_blk = (p.pad_left + jb - LH) >> 2;
 	const int ut_blk = (p.pad_left + (SIGN > 0 ? (jb - LH + db) : (jb - LH - db - BOX_D_PER_BLOCK))) >> 2;
 	if (threadIdx.x == 0) {
-		mbar_init(&bar, 1);
+		mbar_init(&bar_img, 1);
+#pragma unroll
+		for (int k = 0; k < BOX_STAT_SLOTS; k++) mbar_init(&bar_st[k], 1);
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
 	__syncthreads();
+	// one row of statistics -> ring slot: 8 bulk copies (two parity halves of As, Bs, At, Bt), one per lane of warp 0.
+	// source statistics: 32 units from column jb; target statistics: 40 units from the unit after the target window's first
+	auto issue_stats = [&](int row, int slot) {
+		const int lane = threadIdx.x;
+		if (lane == 0) mbar_expect_tx(&bar_st[slot], BOX_STAT_FLOATS * 4);
+		__syncwarp();
+		if (lane < 8) {
+			const int plane = lane >> 1, hf = lane & 1;
+			const float* src = plane == 0 ? p.As : plane == 1 ? p.Bs : plane == 2 ? p.At : p.Bt;
+			const int units = plane < 2 ? BOX_SS_UNITS : BOX_ST_UNITS;
+			const int u = (plane < 2 ? us_blk : ut_blk) + 1 + hf;
+			const int dst = (plane == 0 ? 0 : plane == 1 ? 8 * BOX_SS_UNITS : plane == 2 ? 16 * BOX_SS_UNITS : 16 * BOX_SS_UNITS + 8 * BOX_ST_UNITS)
+							+ hf * 4 * units;
+			bulk_g2s(stat_ring + slot * BOX_STAT_FLOATS + dst, src + (int64_t)row * p.pitch + pad_unit_off(u, p.half), units * 16, &bar_st[slot]);
+		}
+	};
 	if (threadIdx.x < 32) {
-		if (threadIdx.x == 0) mbar_expect_tx(&bar, (uint32_t)n_rows * BOX_ROW_FLOATS * 4);
+		if (threadIdx.x == 0) mbar_expect_tx(&bar_img, (uint32_t)n_rows * BOX_ROW_FLOATS * 4);
 		__syncwarp();
 		const int gsA = pad_unit_off(us_blk, p.half), gsB = pad_unit_off(us_blk + 1, p.half);
 		const int gtA = pad_unit_off(ut_blk, p.half), gtB = pad_unit_off(ut_blk + 1, p.half);
 		for (int r = threadIdx.x; r < n_rows; r += 32) {
 			const int64_t go = (int64_t)(i0 - p.vr + r) * p.pitch;
 			float* dst = tile + r * BOX_ROW_FLOATS;
-			bulk_g2s(dst, p.ps + go + gsA, BOX_S_UNITS * 16, &bar);
-			bulk_g2s(dst + 4 * BOX_S_UNITS, p.ps + go + gsB, BOX_S_UNITS * 16, &bar);
-			bulk_g2s(dst + 8 * BOX_S_UNITS, p.pt + go + gtA, BOX_T_UNITS * 16, &bar);
-			bulk_g2s(dst + 8 * BOX_S_UNITS + 4 * BOX_T_UNITS, p.pt + go + gtB, BOX_T_UNITS * 16, &bar);
+			bulk_g2s(dst, p.ps + go + gsA, BOX_S_UNITS * 16, &bar_img);
+			bulk_g2s(dst + 4 * BOX_S_UNITS, p.ps + go + gsB, BOX_S_UNITS * 16, &bar_img);
+			bulk_g2s(dst + 8 * BOX_S_UNITS, p.pt + go + gtA, BOX_T_UNITS * 16, &bar_img);
+			bulk_g2s(dst + 8 * BOX_S_UNITS + 4 * BOX_T_UNITS, p.pt + go + gtB, BOX_T_UNITS * 16, &bar_img);
 		}
+		for (int k = 0; k < BOX_STAT_SLOTS - 1; k++)
+			if (i0 + k < i_end) issue_stats(i0 + k, k);
 	}
 	// V column c <-> source column j0-LH+c; target column = source column + SIGN*(d0+q):
 	//   SIGN>0: first target column j0-LH+d0, register c+q ; SIGN<0: first target column j0-LH-d0-4, register c+4-q
@@ -170,42 +198,44 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 	const int tbase = 8 * BOX_S_UNITS;
 	const int tA = tbase + ((xt & 1) ? 4 * (BOX_T_UNITS + (xt >> 1)) : 4 * (xt >> 1));
 	const int tB = tbase + ((xt & 1) ? 4 * ((xt + 1) >> 1) : 4 * (BOX_T_UNITS + (xt >> 1)));
-	// offsets of the same units in the global statistics planes
-	const int us = us_blk + 2 * cg, ut = ut_blk + xt;
-	const int gsA = pad_unit_off(us, p.half), gsB = pad_unit_off(us + 1, p.half);
-	const int gtA = pad_unit_off(ut, p.half), gtB = pad_unit_off(ut + 1, p.half);
+	// offsets inside a ring slot: source units of columns j0, j0+4; target units xt, xt+1, xt+2 of the 40
+	const int qs0 = 4 * cg, qs1 = 4 * (BOX_SS_UNITS + cg);
+	const int qt0 = ((xt & 1) ? 4 * (BOX_ST_UNITS + (xt >> 1)) : 4 * (xt >> 1));
+	const int qt1 = ((xt & 1) ? 4 * ((xt + 1) >> 1) : 4 * (BOX_ST_UNITS + (xt >> 1)));
 	const bool live = d0 < p.D && j0 < p.Ws;
 	float V[4][NV];
 #pragma unroll
 	for (int q = 0; q < 4; q++)
 #pragma unroll
 		for (int c = 0; c < NV; c++) V[q][c] = 0.f;
-	mbar_wait(&bar, 0);
-	if (!live) return;
-	for (int r = 0; r <= 2 * p.vr; r++)
-		box_accum_row<OP, NV, SIGN, true>(V, tile + r * BOX_ROW_FLOATS, sA, sB, tA, tB);
-	const int i_end = min(i0 + p.R, p.H);
+	mbar_wait(&bar_img, 0);
+	if (live)
+		for (int r = 0; r <= 2 * p.vr; r++)
+			box_accum_row<OP, NV, SIGN, true>(V, tile + r * BOX_ROW_FLOATS, sA, sB, tA, tB);
 	for (int i = i0; i < i_end; i++) {
-		const int64_t ro = (int64_t)i * p.pitch;
-		// per-pixel statistics of this row, requested before the window update so that their latency hides behind it:
-		// source: units of columns j0, j0+4; target: three units from column j0 + SIGN*d0 (-4)
-		const float4 as0 = load_unit(p.As + ro, gsB), as1 = load_unit(p.As + ro, gsA + 4);
-		const float4 bs0 = load_unit(p.Bs + ro, gsB), bs1 = load_unit(p.Bs + ro, gsA + 4);
-		float4 at0, at1, at2;
-		if (OP != BOX_ABS) { at0 = load_unit(p.At + ro, gtB); at1 = load_unit(p.At + ro, gtA + 4); at2 = load_unit(p.At + ro, gtB + 4); }
-		const float4 bt0 = load_unit(p.Bt + ro, gtB), bt1 = load_unit(p.Bt + ro, gtA + 4), bt2 = load_unit(p.Bt + ro, gtB + 4);
-		if (i > i0) {
-			const int r = i - i0;
-			box_accum_row<OP, NV, SIGN, true>(V, tile + (r + 2 * p.vr) * BOX_ROW_FLOATS, sA, sB, tA, tB);
-			box_accum_row<OP, NV, SIGN, false>(V, tile + (r - 1) * BOX_ROW_FLOATS, sA, sB, tA, tB);
+		const int n = i - i0, slot = n % BOX_STAT_SLOTS;
+		// every warp has finished row i-1, so its ring slot can take row i + BOX_STAT_SLOTS - 1
+		__syncthreads();
+		if (threadIdx.x < 32 && i + BOX_STAT_SLOTS - 1 < i_end) issue_stats(i + BOX_STAT_SLOTS - 1, (n + BOX_STAT_SLOTS - 1) % BOX_STAT_SLOTS);
+		if (!live) continue;
+		if (n > 0) {
+			box_accum_row<OP, NV, SIGN, true>(V, tile + (n + 2 * p.vr) * BOX_ROW_FLOATS, sA, sB, tA, tB);
+			box_accum_row<OP, NV, SIGN, false>(V, tile + (n - 1) * BOX_ROW_FLOATS, sA, sB, tA, tB);
 		}
-		const float as[8] = {as0.x, as0.y, as0.z, as0.w, as1.x, as1.y, as1.z, as1.w};
-		const float bs[8] = {bs0.x, bs0.y, bs0.z, bs0.w, bs1.x, bs1.y, bs1.z, bs1.w};
+		mbar_wait(&bar_st[slot], (n / BOX_STAT_SLOTS) & 1);
+		const float* st = stat_ring + slot * BOX_STAT_FLOATS;
+		const float4 as0 = lds_unit(st, qs0), as1 = lds_unit(st, qs1);
+		const float4 bs0 = lds_unit(st + 8 * BOX_SS_UNITS, qs0), bs1 = lds_unit(st + 8 * BOX_SS_UNITS, qs1);
+		const float* stt = st + 16 * BOX_SS_UNITS;
 		float at[12];
 		if (OP != BOX_ABS) {
+			const float4 at0 = lds_unit(stt, qt0), at1 = lds_unit(stt, qt1), at2 = lds_unit(stt, qt0 + 4);
 			at[0] = at0.x; at[1] = at0.y; at[2] = at0.z; at[3] = at0.w; at[4] = at1.x; at[5] = at1.y; at[6] = at1.z; at[7] = at1.w;
 			at[8] = at2.x; at[9] = at2.y; at[10] = at2.z; at[11] = at2.w;
 		}
+		const float4 bt0 = lds_unit(stt + 8 * BOX_ST_UNITS, qt0), bt1 = lds_unit(stt + 8 * BOX_ST_UNITS, qt1), bt2 = lds_unit(stt + 8 * BOX_ST_UNITS, qt0 + 4);
+		const float as[8] = {as0.x, as0.y, as0.z, as0.w, as1.x, as1.y, as1.z, as1.w};
+		const float bs[8] = {bs0.x, bs0.y, bs0.z, bs0.w, bs1.x, bs1.y, bs1.z, bs1.w};
 		const float bt[12] = {bt0.x, bt0.y, bt0.z, bt0.w, bt1.x, bt1.y, bt1.z, bt1.w, bt2.x, bt2.y, bt2.z, bt2.w};
 #pragma unroll
 		for (int q = 0; q < 4; q++) {
@@ -246,12 +276,12 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 
 template<int OP, int HR>
 static int32_t launch_cv_box_hr(stevi_ctx* c, const BoxParams& p, int sign, dim3 grid) {
-	const int smem = (p.R + 2 * p.vr) * BOX_ROW_FLOATS * 4;
+	const int smem = (p.R + 2 * p.vr) * BOX_ROW_FLOATS * 4 + BOX_STAT_SLOTS * BOX_STAT_FLOATS * 4;
 	if (sign > 0) {
-		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_MAX_TILE_ROWS * BOX_ROW_FLOATS * 4));
+		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_SMEM_MAX));
 		STEVI_LAUNCH(c, (k_cv_box<OP, HR, 1>), grid, BOX_THREADS, smem, p);
 	} else {
-		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_MAX_TILE_ROWS * BOX_ROW_FLOATS * 4));
+		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_SMEM_MAX));
 		STEVI_LAUNCH(c, (k_cv_box<OP, HR, -1>), grid, BOX_THREADS, smem, p);
 	}
 	return STEVI_OK;
