@@ -149,6 +149,34 @@ STEVI_API int32_t stevi_wta(stevi_ctx* ctx, const stevi_array* vol, int32_t stra
 STEVI_API int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, int32_t direction, int32_t offset,
 							stevi_array* out);
 
+/* selectedCost<T_CV> (correlation/correlation_base.h:557-577): out(i,j) = cv(i,j,idx(i,j)); out (H,W) of cv's dtype */
+STEVI_API int32_t stevi_selected_cost(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, stevi_array* out);
+
+/* truncatedCostVolume<float, dir, sdir> (correlation/correlation_base.h:579-674): cv (H,W,D) f32, idx (H,W) i32 ->
+ * out (H,W,2r+1) f32, or (H,W,4r+1) for STEVI_TCV_BOTH; NaN where the disparity is out of range or the matching window
+ * (h_radius, v_radius) leaves the image (:606-609). */
+STEVI_API int32_t stevi_truncated_cost_volume(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, int32_t h_radius,
+									int32_t v_radius, int32_t cost_vol_radius, int32_t direction, int32_t tcv_direction,
+									stevi_array* out);
+
+/* extractInBoundDomain<float, dir, sdir> (correlation/correlation_base.h:727-822): the same tests as a 1/0 mask;
+ * `width` is the disparity search width. out (H,W,2r+1 | 4r+1) f32. */
+STEVI_API int32_t stevi_in_bound_domain(stevi_ctx* ctx, const stevi_array* idx, int32_t width, int32_t h_radius, int32_t v_radius,
+							  int32_t cost_vol_radius, int32_t direction, int32_t tcv_direction, stevi_array* out);
+
+/* ---- cost-based subpixel refinement ------------------------------------------------------------------------ */
+
+/* refineDispCostInterpolation<kernel> (correlation/cost_based_refinement.h:128-163): tcv (H,W,2r+1) f32, idx (H,W) i32
+ * -> out (H,W) f32 = idx + delta(c[r-1], c[r], c[r+1]) (refineCostTriplet, :43-69). STEVI_E_SHAPE where the reference
+ * returns an empty array (depth even or < 3, :141-143). */
+STEVI_API int32_t stevi_refine_disp_cost_interp(stevi_ctx* ctx, const stevi_array* tcv, const stevi_array* idx, int32_t kernel,
+									  stevi_array* out);
+
+/* truncatedCostVolume<Same>(cost_vol_radius = 1) followed by refineDispCostInterpolation in one pass (three gathers per
+ * pixel): cv (H,W,D) f32, idx (H,W) i32 -> out (H,W) f32; tcv_out (H,W,3) f32 optional (NULL = not materialised). */
+STEVI_API int32_t stevi_refine_from_cost_volume(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, int32_t h_radius,
+									  int32_t v_radius, int32_t kernel, stevi_array* tcv_out, stevi_array* out);
+
 /* ---- fused device-resident pipeline ------------------------------------------------------------------------ */
 
 /* census cost volume -> SGM -> WTA -> disparity in one call, the sequence of

@@ -316,3 +316,61 @@ def censusSgmPipeline(img_l, img_r, h_radius, v_radius, disp_width, P1, P2, Pout
     if cv is not None or sg is not None:
         return cv, sg, disp
     return disp
+
+
+def selectedCost(cv, idx, ctx=None):
+    """correlation_base.h:557-577: out(i,j) = cv(i,j,idx(i,j))."""
+    ctx = _ctx_for(ctx, cv)
+    np_dt = _DT2NP[_torch_dtype_code(cv)] if _is_torch(cv) else cv.dtype
+    out = _empty(cv, cv.shape[:2], np_dt)
+    a, i, o = describe(cv), describe(idx), describe(out)
+    ctx.check(lib.stevi_selected_cost(ctx.handle, ctypes.byref(a), ctypes.byref(i), ctypes.byref(o)))
+    return out
+
+
+def _tcv_depth(radius, sdir):
+    return 4 * radius + 1 if sdir == TCV_BOTH else 2 * radius + 1
+
+
+def truncatedCostVolume(cv, idx, h_radius, v_radius, cost_vol_radius, dDir=RIGHT_TO_LEFT, sdir=TCV_SAME, ctx=None):
+    """correlation_base.h:579-674. (H,W,D) f32 + (H,W) i32 -> (H,W,2r+1 | 4r+1) f32 with NaN outside."""
+    ctx = _ctx_for(ctx, cv)
+    out = _empty(cv, tuple(cv.shape[:2]) + (_tcv_depth(cost_vol_radius, sdir),), np.float32)
+    a, i, o = describe(cv), describe(idx), describe(out)
+    ctx.check(lib.stevi_truncated_cost_volume(ctx.handle, ctypes.byref(a), ctypes.byref(i), h_radius, v_radius, cost_vol_radius,
+                                              dDir, sdir, ctypes.byref(o)))
+    return out
+
+
+def extractInBoundDomain(idx, width, h_radius, v_radius, cost_vol_radius, dDir=RIGHT_TO_LEFT, sdir=TCV_SAME, ctx=None):
+    """correlation_base.h:727-822. (H,W) i32 -> (H,W,2r+1 | 4r+1) f32 mask of 1/0."""
+    ctx = _ctx_for(ctx, idx)
+    out = _empty(idx, tuple(idx.shape) + (_tcv_depth(cost_vol_radius, sdir),), np.float32)
+    i, o = describe(idx), describe(out)
+    ctx.check(lib.stevi_in_bound_domain(ctx.handle, ctypes.byref(i), width, h_radius, v_radius, cost_vol_radius, dDir, sdir,
+                                        ctypes.byref(o)))
+    return out
+
+
+def refineDispCostInterpolation(tcv, idx, kernel=PARABOLA, ctx=None):
+    """cost_based_refinement.h:128-163. Returns None where the reference returns an empty array (even / too small depth)."""
+    ctx = _ctx_for(ctx, tcv)
+    out = _empty(tcv, tcv.shape[:2], np.float32)
+    t, i, o = describe(tcv), describe(idx), describe(out)
+    rc = lib.stevi_refine_disp_cost_interp(ctx.handle, ctypes.byref(t), ctypes.byref(i), kernel, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def refineFromCostVolume(cv, idx, h_radius, v_radius, kernel=PARABOLA, return_tcv=False, ctx=None):
+    """truncatedCostVolume<Same>(radius 1) + refineDispCostInterpolation fused into one pass over the winners."""
+    ctx = _ctx_for(ctx, cv)
+    out = _empty(cv, cv.shape[:2], np.float32)
+    tcv = _empty(cv, tuple(cv.shape[:2]) + (3,), np.float32) if return_tcv else None
+    a, i, o = describe(cv), describe(idx), describe(out)
+    t = describe(tcv) if tcv is not None else None
+    ctx.check(lib.stevi_refine_from_cost_volume(ctx.handle, ctypes.byref(a), ctypes.byref(i), h_radius, v_radius, kernel,
+                                                ctypes.byref(t) if t is not None else None, ctypes.byref(o)))
+    return (tcv, out) if return_tcv else out

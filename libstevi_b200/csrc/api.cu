@@ -115,6 +115,65 @@ int32_t stevi_index_to_disp(stevi_ctx* c, const stevi_array* idx, int32_t direct
 	return st.finish();
 }
 
+int32_t stevi_selected_cost(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vc, vi, vo;
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(selected_cost_dev(c, vc, vi, vo));
+	return st.finish();
+}
+
+int32_t stevi_truncated_cost_volume(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, int32_t hr, int32_t vr, int32_t r,
+									int32_t direction, int32_t tdir, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vc, vi, vo;
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(truncated_cv_dev(c, &vc, vi, 0, hr, vr, r, direction, tdir, vo));
+	return st.finish();
+}
+
+int32_t stevi_in_bound_domain(stevi_ctx* c, const stevi_array* idx, int32_t width, int32_t hr, int32_t vr, int32_t r,
+							  int32_t direction, int32_t tdir, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	if (vi.ndim != 2) return fail(c, STEVI_E_SHAPE, "in_bound_domain: index map must be (H,W)");
+	STEVI_TRY(truncated_cv_dev(c, nullptr, vi, width, hr, vr, r, direction, tdir, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_disp_cost_interp(stevi_ctx* c, const stevi_array* tcv, const stevi_array* idx, int32_t kernel, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vt, vi, vo;
+	STEVI_TRY(st.in(tcv, vt, "tcv"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine_interp_dev(c, vt, vi, kernel, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_from_cost_volume(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, int32_t hr, int32_t vr,
+									  int32_t kernel, stevi_array* tcv_out, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vc, vi, vt, vo;
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	if (tcv_out) STEVI_TRY(st.out(tcv_out, vt, "tcv_out"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine_from_cv_dev(c, vc, vi, hr, vr, kernel, tcv_out ? &vt : nullptr, vo));
+	return st.finish();
+}
+
 int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr, int32_t D,
 								  int32_t direction, int32_t ndir, float P1, float P2, float Pout, const stevi_margins* margins,
 								  int32_t semantics, stevi_array* cv_out, stevi_array* sgm_out, stevi_array* disp) {

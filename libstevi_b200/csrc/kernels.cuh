@@ -44,4 +44,14 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);
 int32_t index_to_disp_dev(stevi_ctx* c, const View& idx, int direction, int offset, const View& out);
 
+
+// refine.cu
+// cv == nullptr: extractInBoundDomain (0/1 mask, `width` = search width); else truncatedCostVolume of *cv
+int32_t truncated_cv_dev(stevi_ctx* c, const View* cv, const View& idx, int width, int hr, int vr, int r, int direction, int tdir,
+						 const View& out);
+int32_t selected_cost_dev(stevi_ctx* c, const View& cv, const View& idx, const View& out);
+int32_t refine_interp_dev(stevi_ctx* c, const View& tcv, const View& idx, int kernel, const View& out);
+// truncatedCostVolume<Same>(radius 1) + refineDispCostInterpolation in one pass over the winners; tcv_out optional
+int32_t refine_from_cv_dev(stevi_ctx* c, const View& cv, const View& idx, int hr, int vr, int kernel, const View* tcv_out, const View& out);
+
 } // namespace stevi

@@ -167,6 +167,13 @@ class _Checker:
                                              hr, vr, radius, direction, tdir, _p(out))
         return out
 
+    def in_bound_domain(self, idx, width, hr, vr, radius, direction=R2L, tdir=TCV_SAME):
+        h, w = idx.shape
+        T = 4 * radius + 1 if tdir == TCV_BOTH else 2 * radius + 1
+        out = np.empty((h, w, T), np.float32)
+        self._f("in_bound_domain_f32")(_p(_c(idx, np.int32)), h, w, width, hr, vr, radius, direction, tdir, _p(out))
+        return out
+
     def refine(self, tcv, idx, kernel=PARABOLA):
         h, w, T = tcv.shape
         out = np.empty((h, w), np.float32)

@@ -208,6 +208,18 @@ int ref_truncated_cost_volume_f32(const float* cv, const int32_t* idx, int h, in
 	return 0;
 }
 
+// correlation_base.h:727-822; out (h, w, 2*radius+1 | 4*radius+1) as float 1/0
+int ref_in_bound_domain_f32(const int32_t* idx, int h, int w, int width, int hr, int vr, int radius, int dir, int tdir, float* out) {
+	auto I = view2(idx, h, w);
+#define IB_CASE(DD, TD) out3(extractInBoundDomain<float, dispDirection::DD, truncatedCostVolumeDirection::TD>(I, uint32_t(width), hr, vr, radius), out)
+	bool r2l = dir == int(dispDirection::RightToLeft);
+	if (tdir == 0) { if (r2l) IB_CASE(RightToLeft, Same); else IB_CASE(LeftToRight, Same); }
+	else if (tdir == 1) { if (r2l) IB_CASE(RightToLeft, Reversed); else IB_CASE(LeftToRight, Reversed); }
+	else { if (r2l) IB_CASE(RightToLeft, Both); else IB_CASE(LeftToRight, Both); }
+#undef IB_CASE
+	return 0;
+}
+
 // cost_based_refinement.h:128-163; returns 1 (and leaves out untouched) when the reference returns an empty array
 int ref_refine_disp_cost_interp(const float* tcv, const int32_t* idx, int h, int w, int t, int kernel, float* out) {
 	auto T = view3(tcv, h, w, t);

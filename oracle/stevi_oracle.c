@@ -398,6 +398,32 @@ int orc_truncated_cost_volume_f32(const float* cv, const int32_t* idx, int h, in
 	return 0;
 }
 
+/* correlation_base.h:727-822: the tests of truncatedCostVolume as a 1/0 mask; `width` = disparity search width */
+int orc_in_bound_domain_f32(const int32_t* idx, int h, int w, int width, int hr, int vr, int r, int dir, int tdir, float* out) {
+	int T = tdir == 2 ? 4 * r + 1 : 2 * r + 1;
+	int sgn = dir == DIR_R2L ? -1 : 1;
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		float* o = out + ((size_t)i * w + j) * T;
+		int vbad = (i < vr) || (i + vr >= h);
+		for (int d = -r; d <= r; d++) {
+			int p = idx[(size_t)i * w + j] + d;
+			int jp = j + sgn * d;
+			int pbad = (p < 0) || (p >= width);
+			int same_bad = pbad || j < hr || j + p + hr >= w || vbad;
+			if (tdir == 0) { o[d + r] = same_bad ? 0.f : 1.f; continue; }
+			if (tdir == 2 && d == 0) jp = -1;
+			int lo = jp < j ? jp : j, hi = jp > j ? jp : j;
+			int rbad = pbad || lo < hr || hi + hr >= w || vbad;
+			if (tdir == 1) { o[d + r] = rbad ? 0.f : 1.f; continue; }
+			int d_d = 2 * (d + r), d_r = 2 * (d + r) + 1;
+			if (d > 0) { d_d -= 1; d_r -= 1; }
+			if (d_r < T) o[d_r] = rbad ? 0.f : 1.f; /* r == 0 would write past the array in the reference */
+			o[d_d] = same_bad ? 0.f : 1.f;
+		}
+	}
+	return 0;
+}
+
 /* cost_based_refinement.h:43-69 */
 float orc_refine_cost_triplet(int kernel, float cm1, float c0, float c1) {
 	if (kernel == K_EQUIANGULAR) {

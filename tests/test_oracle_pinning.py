@@ -91,6 +91,16 @@ def test_port_equals_compiled_reference(seed):
         assert np.allclose(a, b, atol=1e-6, equal_nan=True)
     a, b = port.hierarchical(O.ZNCC, 2, Lq, Rq, 2, 2, 12), ref.hierarchical(O.ZNCC, 2, Lq, Rq, 2, 2, 12)
     assert same(a[1], b[1])
+    # winner neighbourhoods: truncatedCostVolume and its mask twin extractInBoundDomain, all direction combinations
+    zn = port.cost_volume(O.ZNCC, Lq, Rq, 2, 2, 9)
+    idx = port.wta(zn, O.SCORE)
+    for direction in (0, 1):
+        for tdir in (0, 1, 2):
+            for radius in (1, 2):
+                assert same(port.truncated_cost_volume(zn, idx, 2, 2, radius, direction, tdir),
+                            ref.truncated_cost_volume(zn, idx, 2, 2, radius, direction, tdir))
+                assert same(port.in_bound_domain(idx, 9, 2, 2, radius, direction, tdir),
+                            ref.in_bound_domain(idx, 9, 2, 2, radius, direction, tdir))
 
 
 # ---- restatements of the reference's own unit tests ------------------------------------------------------------------
