@@ -177,6 +177,29 @@ STEVI_API int32_t stevi_refine_disp_cost_interp(stevi_ctx* ctx, const stevi_arra
 STEVI_API int32_t stevi_refine_from_cost_volume(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, int32_t h_radius,
 									  int32_t v_radius, int32_t kernel, stevi_array* tcv_out, stevi_array* out);
 
+/* ---- coarse-to-fine matching ---------------------------------------------------------------------------------- */
+
+/* Interpolation::averagePoolingDownsample<T_I, float> (interpolation/downsampling.h:67-118) with
+ * DownSampleWindows(win_h, win_v): img (H,W) u8|f32 -> out (ceil(H/win_v), ceil(W/win_h)) f32, mean over the in-image
+ * part of each window. */
+STEVI_API int32_t stevi_avgpool_downsample(stevi_ctx* ctx, const stevi_array* img, int32_t win_h, int32_t win_v, stevi_array* out);
+
+/* computeGuidedCV<matchFunc, ..., dDir, float> (correlation/hierarchical.h:73-233) fused with unfold +
+ * getFeatureVolumeForMatchFunc of both images: img_l, img_r (H,W*) f32 (u8 for CC/SSD/SAD), guide (h_g,w_g) i32 ->
+ * tcv (H,Wsource,2*radius+1) f32 (OffsetedCostVolume::truncated_cost_volume) and disp (H,Wsource) i32
+ * (OffsetedCostVolume::disp_estimate). radius <= 4. STEVI_E_SHAPE for axes of fewer than 2 pixels (Q7). */
+STEVI_API int32_t stevi_guided_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+								 int32_t h_radius, int32_t v_radius, const stevi_array* guide, int32_t upscale_disp_radius,
+								 int32_t direction, stevi_array* tcv, stevi_array* disp);
+
+/* hiearchicalTruncatedCostVolume<matchFunc, depth, ...> (sic; correlation/hierarchical.h:235-314). h_radii / v_radii:
+ * depth+1 entries, coarsest level first, like the reference's std::array arguments (NULL = h_radius / v_radius at every
+ * level, the overload at :297-314). img_l, img_r (H,W) f32 -> tcv (H,W,2*radius+1) f32, disp (H,W) i32. */
+STEVI_API int32_t stevi_hierarchical(stevi_ctx* ctx, int32_t matchfunc, int32_t depth, const stevi_array* img_l,
+						   const stevi_array* img_r, const int32_t* h_radii, const int32_t* v_radii, int32_t h_radius,
+						   int32_t v_radius, int32_t disp_width, int32_t upscale_disp_radius, int32_t direction,
+						   stevi_array* tcv, stevi_array* disp);
+
 /* ---- fused device-resident pipeline ------------------------------------------------------------------------ */
 
 /* census cost volume -> SGM -> WTA -> disparity in one call, the sequence of

@@ -374,3 +374,48 @@ def refineFromCostVolume(cv, idx, h_radius, v_radius, kernel=PARABOLA, return_tc
     ctx.check(lib.stevi_refine_from_cost_volume(ctx.handle, ctypes.byref(a), ctypes.byref(i), h_radius, v_radius, kernel,
                                                 ctypes.byref(t) if t is not None else None, ctypes.byref(o)))
     return (tcv, out) if return_tcv else out
+
+
+def averagePoolingDownsample(img, windows=2, ctx=None):
+    """interpolation/downsampling.h:67-118 with DownSampleWindows(windows) or (horizontal, vertical)."""
+    ctx = _ctx_for(ctx, img)
+    wh, wv = (windows, windows) if np.isscalar(windows) else windows
+    out = _empty(img, ((img.shape[0] + wv - 1) // wv, (img.shape[1] + wh - 1) // wh), np.float32)
+    a, o = describe(img), describe(out)
+    ctx.check(lib.stevi_avgpool_downsample(ctx.handle, ctypes.byref(a), wh, wv, ctypes.byref(o)))
+    return out
+
+
+def computeGuidedCV(matchFunc, img_l, img_r, h_radius, v_radius, guide, upscale_disp_radius=2, dDir=RIGHT_TO_LEFT, ctx=None):
+    """hierarchical.h:73-233 on the images (unfold + features fused in). Returns (truncated_cost_volume, disp_estimate),
+    or None where the reference returns an empty volume."""
+    ctx = _ctx_for(ctx, img_l)
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    tcv = _empty(img_l, (img_l.shape[0], ws, 2 * upscale_disp_radius + 1), np.float32)
+    disp = _empty(img_l, (img_l.shape[0], ws), np.int32)
+    l, r, g, t, d = describe(img_l), describe(img_r), describe(guide), describe(tcv), describe(disp)
+    rc = lib.stevi_guided_cost_volume(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, ctypes.byref(g),
+                                      upscale_disp_radius, dDir, ctypes.byref(t), ctypes.byref(d))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return tcv, disp
+
+
+def hiearchicalTruncatedCostVolume(matchFunc, depth, img_l, img_r, h_radius, v_radius, disp_width, upscale_disp_radius=2,
+                                   dDir=RIGHT_TO_LEFT, ctx=None):
+    """hierarchical.h:235-314 (sic). h_radius / v_radius: scalars, or depth+1 values coarsest level first.
+    Returns (truncated_cost_volume, disp_estimate) like OffsetedCostVolume."""
+    ctx = _ctx_for(ctx, img_l)
+    tcv = _empty(img_l, tuple(img_l.shape) + (2 * upscale_disp_radius + 1,), np.float32)
+    disp = _empty(img_l, img_l.shape, np.int32)
+    arr = ctypes.c_int32 * (depth + 1)
+    hrs = arr(*([int(h_radius)] * (depth + 1) if np.isscalar(h_radius) else [int(v) for v in h_radius]))
+    vrs = arr(*([int(v_radius)] * (depth + 1) if np.isscalar(v_radius) else [int(v) for v in v_radius]))
+    l, r, t, d = describe(img_l), describe(img_r), describe(tcv), describe(disp)
+    rc = lib.stevi_hierarchical(ctx.handle, matchFunc, depth, ctypes.byref(l), ctypes.byref(r), hrs, vrs, 0, 0, disp_width,
+                                upscale_disp_radius, dDir, ctypes.byref(t), ctypes.byref(d))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return tcv, disp

@@ -174,6 +174,47 @@ int32_t stevi_refine_from_cost_volume(stevi_ctx* c, const stevi_array* cv, const
 	return st.finish();
 }
 
+int32_t stevi_avgpool_downsample(stevi_ctx* c, const stevi_array* img, int32_t wh, int32_t wv, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(avgpool_dev(c, vi, wh, wv, vo));
+	return st.finish();
+}
+
+int32_t stevi_guided_cost_volume(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
+								 const stevi_array* guide, int32_t radius, int32_t direction, stevi_array* tcv, stevi_array* disp) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr_, vg, vt, vd;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(st.in(guide, vg, "guide"));
+	STEVI_TRY(st.out(tcv, vt, "tcv"));
+	STEVI_TRY(st.out(disp, vd, "disp"));
+	STEVI_TRY(guided_cv_dev(c, mf, vl, vr_, hr, vr, vg, radius, direction, vt, vd));
+	return st.finish();
+}
+
+int32_t stevi_hierarchical(stevi_ctx* c, int32_t mf, int32_t depth, const stevi_array* l, const stevi_array* r, const int32_t* h_radii,
+						   const int32_t* v_radii, int32_t hr, int32_t vr, int32_t D, int32_t radius, int32_t direction,
+						   stevi_array* tcv, stevi_array* disp) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr_, vt, vd;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(st.out(tcv, vt, "tcv"));
+	STEVI_TRY(st.out(disp, vd, "disp"));
+	if (depth < 1 || depth > 8) return fail(c, STEVI_E_ARG, "hierarchical: depth must be 1..8");
+	int32_t hrs[9], vrs[9];
+	for (int k = 0; k <= depth; k++) { hrs[k] = h_radii ? h_radii[k] : hr; vrs[k] = v_radii ? v_radii[k] : vr; }
+	STEVI_TRY(hierarchical_dev(c, mf, depth, vl, vr_, hrs, vrs, D, radius, direction, vt, vd));
+	return st.finish();
+}
+
 int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr, int32_t D,
 								  int32_t direction, int32_t ndir, float P1, float P2, float Pout, const stevi_margins* margins,
 								  int32_t semantics, stevi_array* cv_out, stevi_array* sgm_out, stevi_array* disp) {

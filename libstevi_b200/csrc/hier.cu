@@ -1,0 +1,282 @@
+// Average-pooling pyramid, guided cost volume and the coarse-to-fine driver.
+//
+//   interpolation/downsampling.h:67-118  averagePoolingDownsample: out ceil(H/wv) x ceil(W/wh); mean over the in-image part
+//                                        of each window, accumulated in row-major window order, divided by the count.
+//                                        Quirks kept: the inner loops both run to windows.horizontal() (:97,:101) and the
+//                                        row offset uses the WIDTH remainder, the column offset the HEIGHT remainder (:80-84)
+//   hierarchical.h:73-233                computeGuidedCV: bilinear guide upsampling in GLOBAL float coordinates
+//                                        i*(h_g-1)/(h-1) (Q7: int product, float division), d0 = sign*round(2*interp),
+//                                        best of the 2r+1 candidates with STRICT compare (first wins, unlike the dense WTA),
+//                                        output window re-centred on the winner (:194-226)
+//   hierarchical.h:235-314               hiearchicalTruncatedCostVolume (sic): pyramid by 2, full cost volume + WTA at the
+//                                        coarsest level with disp_width halved per level, guided volumes on the way up
+#include "common.cuh"
+#include "kernels.cuh"
+#include "costvol_box.cuh"
+
+namespace stevi {
+
+namespace {
+
+template<typename TI>
+__global__ void __launch_bounds__(128) k_avgpool(const TI* __restrict__ img, int64_t s0, int64_t s1, int H, int W, int wh, int wv,
+												 int off_v, int off_h, float* __restrict__ out, int64_t o0, int64_t o1, int nH, int nW) {
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+	if (j >= nW) return;
+	float val = 0.f;
+	int count = 0;
+	for (int dv = 0; dv < wh; dv++) {          // sic: horizontal() bounds both loops
+		const int pi = i * wv - off_v + dv;
+		for (int dh = 0; dh < wh; dh++) {
+			const int pj = j * wh - off_h + dh;
+			if (pi >= 0 && pi < H && pj >= 0 && pj < W) { val = __fadd_rn(val, (float)img[pi * s0 + pj * s1]); count++; }
+		}
+	}
+	out[i * o0 + j * o1] = __fdiv_rn(val, (float)count);
+}
+
+struct Guided {
+	const float* ps; const float* pt; int64_t pitch; int half, pad_left;
+	const float* Ms; const float* Ns; const float* Mt; const float* Nt;   // STATS_RAW maps (mean, norm)
+	const int32_t* guide; int64_t g0, g1; int hg, wg;
+	int H, Ws, Wt, hr, vr, r, sign, op, zero_mean, normalized, cost;
+	float* tcv; int64_t t0, t1, t2;
+	int32_t* disp; int64_t d0s, d1s;
+};
+
+constexpr int GUIDED_MAX_R = 4; // candidates at offsets -2r..2r around the guide: 4r+1 <= 17 accumulators
+
+// One thread per pixel. The 2r+1 candidates around the upsampled guide and the 2r+1 cells around the winner are all
+// comparisons against target columns j + d0 + e, e in [-2r, 2r]: each is evaluated once, over the raw window pixels
+//   correlations: (sum s*t - F*m_s*m_t) / (n_s*n_t);  costs: sum op((s - m_s) - (t - m_t))
+// instead of over materialised (v-mean)/norm feature volumes (49 x 4 bytes per pixel and image at C4).
+__global__ void __launch_bounds__(128) k_guided_cv(const Guided p) {
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+	if (j >= p.Ws) return;
+	// hierarchical.h:116-148, same operation order in fp32
+	const float v_pos = __fdiv_rn((float)(i * (p.hg - 1)), (float)(p.H - 1));
+	int v0 = (int)floorf(v_pos), v1 = (int)ceilf(v_pos);
+	if (v0 == v1) v1 += 1;
+	if (v1 == p.hg) { v0 -= 1; v1 -= 1; }
+	const float h_pos = __fdiv_rn((float)(j * (p.wg - 1)), (float)(p.Ws - 1));
+	int h0 = (int)floorf(h_pos), h1 = (int)ceilf(h_pos);
+	if (h0 == h1) h1 += 1;
+	if (h1 == p.wg) { h0 -= 1; h1 -= 1; }
+	const float av = __fsub_rn(v_pos, (float)v0), bv = __fsub_rn((float)v1, v_pos);
+	const float ah = __fsub_rn(h_pos, (float)h0), bh = __fsub_rn((float)h1, h_pos);
+	float id = 0.f;
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, ah), (float)p.guide[v1 * p.g0 + h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, ah), (float)p.guide[v0 * p.g0 + h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, bh), (float)p.guide[v1 * p.g0 + h0 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, bh), (float)p.guide[v0 * p.g0 + h0 * p.g1]));
+	id = __fmul_rn(id, 2.f);
+	const int d0 = p.sign * (int)roundf(id);
+
+	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1, nc = 4 * p.r + 1;
+	const float F = (float)(hs * vs);
+	const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
+	const float ms = p.Ms[os], ns = p.Ns[os];
+	float acc[4 * GUIDED_MAX_R + 1];
+#pragma unroll
+	for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) acc[e] = 0.f;
+	const int jt0 = j + d0 - 2 * p.r;   // target column of candidate e = 0
+	float mtv[4 * GUIDED_MAX_R + 1];    // target window means (costs of zero-mean functions subtract them per pixel)
+#pragma unroll
+	for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) {
+		const int jt = jt0 + e;
+		mtv[e] = 0.f;
+		if (e < nc && p.op != BOX_PROD && p.zero_mean && jt >= 0 && jt < p.Wt)
+			mtv[e] = p.Mt[(int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half)];
+	}
+	for (int k = 0; k < vs; k++) {
+		const float* srow = p.ps + (int64_t)(i - p.vr + k) * p.pitch;
+		const float* trow = p.pt + (int64_t)(i - p.vr + k) * p.pitch;
+		for (int l = 0; l < hs; l++) {
+			float s = __ldg(srow + pad_col_off(p.pad_left + j - p.hr + l, p.half));
+			if (p.op != BOX_PROD && p.zero_mean) s -= ms;
+#pragma unroll
+			for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) {
+				if (e >= nc) break;
+				const int jt = jt0 + e;
+				float t = 0.f;
+				if (jt >= 0 && jt < p.Wt) t = __ldg(trow + pad_col_off(p.pad_left + jt - p.hr + l, p.half));
+				if (p.op == BOX_PROD) acc[e] = fmaf(s, t, acc[e]);
+				else if (p.op == BOX_SQ) { const float q = s - (t - mtv[e]); acc[e] = fmaf(q, q, acc[e]); }
+				else acc[e] += fabsf(s - (t - mtv[e]));
+			}
+		}
+	}
+	if (p.op == BOX_PROD) {
+#pragma unroll
+		for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) {
+			if (e >= nc) break;
+			const int jt = jt0 + e;
+			float v = 0.f;
+			if (jt >= 0 && jt < p.Wt) {
+				const int64_t ot = (int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half);
+				v = acc[e];
+				if (p.zero_mean) v = fmaf(-F * ms, p.Mt[ot], v);
+				if (p.normalized) {                          // flat windows: NaN features in the reference (Q6)
+					const float nt = p.Nt[ot];
+					v = (ns == 0.f || nt == 0.f) ? __int_as_float(0x7fc00000) : v / (ns * nt);
+				}
+			} else if (p.normalized && ns == 0.f) {
+				v = __int_as_float(0x7fc00000);              // NaN source features times a zero target vector
+			}
+			acc[e] = v;
+		}
+	}
+	// best of the candidates d0-r .. d0+r, strict compare: the first extremum wins (hierarchical.h:179,184)
+	float score = p.cost ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+	int d_r = d0;
+	for (int dd = -p.r; dd <= p.r; dd++) {
+		float cmp = 0.f;
+#pragma unroll
+		for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) if (e == dd + 2 * p.r) cmp = acc[e];
+		if (p.cost ? (cmp < score) : (cmp > score)) { score = cmp; d_r = d0 + dd; }
+	}
+	p.disp[i * p.d0s + j * p.d1s] = p.sign * d_r;
+	// cell dd holds the comparison against target column j + d_r + sign*(dd - r) (after the reference's shift-and-refill)
+	float* o = p.tcv + i * p.t0 + j * p.t1;
+	for (int dd = 0; dd <= 2 * p.r; dd++) {
+		const int want = (d_r - d0) + p.sign * (dd - p.r) + 2 * p.r;
+		float cmp = 0.f;
+#pragma unroll
+		for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) if (e == want) cmp = acc[e];
+		o[dd * p.t2] = cmp;
+	}
+}
+
+} // namespace
+
+namespace {
+inline bool h_zero_mean(int mf) { return mf == STEVI_MF_ZCC || mf == STEVI_MF_ZNCC || mf == STEVI_MF_ZSSD || mf == STEVI_MF_ZSAD; }
+inline bool h_normalized(int mf) { return mf == STEVI_MF_NCC || mf == STEVI_MF_ZNCC; }
+inline bool h_score(int mf) { return mf == STEVI_MF_CC || mf == STEVI_MF_NCC || mf == STEVI_MF_ZCC || mf == STEVI_MF_ZNCC; }
+inline int h_op(int mf) { return h_score(mf) ? BOX_PROD : (mf == STEVI_MF_SSD || mf == STEVI_MF_ZSSD) ? BOX_SQ : BOX_ABS; }
+inline bool h_known(int mf) {
+	switch (mf) {
+	case STEVI_MF_CC: case STEVI_MF_NCC: case STEVI_MF_ZCC: case STEVI_MF_ZNCC:
+	case STEVI_MF_SSD: case STEVI_MF_ZSSD: case STEVI_MF_SAD: case STEVI_MF_ZSAD: return true;
+	default: return false;
+	}
+}
+
+// dense (H,W) workspace array
+template<typename T> int32_t alloc_map(stevi_ctx* c, int H, int W, int dtype, View& v) {
+	T* p = nullptr;
+	STEVI_TRY(arena_alloc_t(c, (size_t)H * W, &p));
+	v.p = p; v.dtype = dtype; v.ndim = 2;
+	v.shape[0] = H; v.shape[1] = W; v.st[0] = W; v.st[1] = 1;
+	return STEVI_OK;
+}
+} // namespace
+
+int32_t avgpool_dev(stevi_ctx* c, const View& img, int wh, int wv, const View& out) {
+	if (img.ndim != 2 || (img.dtype != STEVI_F32 && img.dtype != STEVI_U8)) return fail(c, STEVI_E_DTYPE, "avgpool: image must be (H,W) u8|f32");
+	if (wh < 1 || wv < 1) return fail(c, STEVI_E_ARG, "avgpool: window");
+	const int H = img.shape[0], W = img.shape[1];
+	const int nH = (H + wv - 1) / wv, nW = (W + wh - 1) / wh;
+	if (out.ndim != 2 || out.dtype != STEVI_F32 || out.shape[0] != nH || out.shape[1] != nW)
+		return fail(c, STEVI_E_SHAPE, "avgpool: out must be (%d,%d) f32", nH, nW);
+	if (nH == 0 || nW == 0) return STEVI_OK;
+	if (nH > 65535) return fail(c, STEVI_E_UNSUPPORTED, "avgpool: more than 65535 rows");
+	// downsampling.h:80-84 (names as in the reference): hRem from the height, vRem from the width; the ROW index uses
+	// initialVOffset (= vRem/2) and the COLUMN index initialHOffset (= hRem/2)
+	const int hRem = nH * wv - H, vRem = nW * wh - W;
+	dim3 grid(cdiv(nW, 128), nH);
+	if (img.dtype == STEVI_F32) {
+		STEVI_LAUNCH(c, k_avgpool<float>, grid, 128, 0, img.as<float>(), img.st[0], img.st[1], H, W, wh, wv, vRem / 2, hRem / 2,
+					 out.as<float>(), out.st[0], out.st[1], nH, nW);
+	} else {
+		STEVI_LAUNCH(c, k_avgpool<uint8_t>, grid, 128, 0, img.as<uint8_t>(), img.st[0], img.st[1], H, W, wh, wv, vRem / 2, hRem / 2,
+					 out.as<float>(), out.st[0], out.st[1], nH, nW);
+	}
+	return STEVI_OK;
+}
+
+int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const View& guide, int radius, int direction,
+					  const View& tcv, const View& disp) {
+	if (!h_known(mf)) return fail(c, STEVI_E_UNSUPPORTED, "guided_cv: matching function %d not available", mf);
+	if (radius < 0 || radius > GUIDED_MAX_R) return fail(c, STEVI_E_UNSUPPORTED, "guided_cv: upscale radius must be 0..%d", GUIDED_MAX_R);
+	if (hr < 0 || vr < 0 || hr > 127 || vr > 127) return fail(c, STEVI_E_ARG, "guided_cv: radii out of range");
+	if (l.ndim == 2 && l.dtype == STEVI_U8 && (h_zero_mean(mf) || h_normalized(mf)))
+		return fail(c, STEVI_E_UNSUPPORTED, "guided_cv: pass float images for zero-mean / normalised functions");
+	if (guide.ndim != 2 || guide.dtype != STEVI_I32) return fail(c, STEVI_E_DTYPE, "guided_cv: guide must be (h_g,w_g) i32");
+	PaddedPair pp;
+	STEVI_TRY(pp.build(c, l, r, hr, vr, 0, 1));
+	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
+	const int si = r2l ? 1 : 0, ti = 1 - si;
+	const int H = pp.H, Ws = pp.W[si];
+	// hierarchical.h:89-91 returns an empty volume on a shape mismatch; 1-pixel axes divide by zero (Q7)
+	if (H < 2 || Ws < 2 || guide.shape[0] < 2 || guide.shape[1] < 2) return fail(c, STEVI_E_SHAPE, "guided_cv: every axis needs at least 2 pixels (hierarchical.h:116,132)");
+	if (tcv.ndim != 3 || tcv.dtype != STEVI_F32 || tcv.shape[0] != H || tcv.shape[1] != Ws || tcv.shape[2] != 2 * radius + 1)
+		return fail(c, STEVI_E_SHAPE, "guided_cv: tcv must be (%d,%d,%d) f32", H, Ws, 2 * radius + 1);
+	if (disp.ndim != 2 || disp.dtype != STEVI_I32 || disp.shape[0] != H || disp.shape[1] != Ws)
+		return fail(c, STEVI_E_SHAPE, "guided_cv: disp must be (%d,%d) i32", H, Ws);
+	STEVI_TRY(pp.stats(c, si, hr, vr, mf, 0 /* raw: mean, norm */));
+	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, 0));
+	Guided p;
+	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left;
+	p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
+	p.guide = guide.as<int32_t>(); p.g0 = guide.st[0]; p.g1 = guide.st[1]; p.hg = guide.shape[0]; p.wg = guide.shape[1];
+	p.H = H; p.Ws = Ws; p.Wt = pp.W[ti]; p.hr = hr; p.vr = vr; p.r = radius; p.sign = r2l ? 1 : -1;
+	p.op = h_op(mf); p.zero_mean = h_zero_mean(mf); p.normalized = h_normalized(mf); p.cost = h_score(mf) ? 0 : 1;
+	p.tcv = tcv.as<float>(); p.t0 = tcv.st[0]; p.t1 = tcv.st[1]; p.t2 = tcv.st[2];
+	p.disp = disp.as<int32_t>(); p.d0s = disp.st[0]; p.d1s = disp.st[1];
+	dim3 grid(cdiv(Ws, 128), H);
+	STEVI_LAUNCH(c, k_guided_cv, grid, 128, 0, p);
+	return STEVI_OK;
+}
+
+// hierarchical.h:235-314. h_radii / v_radii hold depth+1 entries, coarsest level first (like the reference's arrays).
+int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const View& r, const int32_t* h_radii, const int32_t* v_radii,
+						 int D, int radius, int direction, const View& tcv, const View& disp) {
+	if (depth < 1 || depth > 8) return fail(c, STEVI_E_ARG, "hierarchical: depth must be 1..8");
+	if (l.ndim != 2 || r.ndim != 2 || l.dtype != STEVI_F32 || r.dtype != STEVI_F32)
+		return fail(c, STEVI_E_UNSUPPORTED, "hierarchical: images must be (H,W) f32");
+	if (l.shape[0] != r.shape[0]) return fail(c, STEVI_E_SHAPE, "hierarchical: image heights differ");
+	// pyramid: level `depth` = the input, level 0 = the coarsest
+	std::vector<View> pl(depth + 1), pr(depth + 1);
+	std::vector<int> dw(depth + 1);
+	pl[depth] = l; pr[depth] = r; dw[depth] = D;
+	for (int k = depth - 1; k >= 0; k--) {
+		STEVI_TRY(alloc_map<float>(c, (pl[k + 1].shape[0] + 1) / 2, (pl[k + 1].shape[1] + 1) / 2, STEVI_F32, pl[k]));
+		STEVI_TRY(alloc_map<float>(c, (pr[k + 1].shape[0] + 1) / 2, (pr[k + 1].shape[1] + 1) / 2, STEVI_F32, pr[k]));
+		STEVI_TRY(avgpool_dev(c, pl[k + 1], 2, 2, pl[k]));
+		STEVI_TRY(avgpool_dev(c, pr[k + 1], 2, 2, pr[k]));
+		dw[k] = (dw[k + 1] + 1) / 2;
+	}
+	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
+	// coarsest level: full cost volume + winner-take-all (raw indices are the guide, hierarchical.h:262)
+	const View& sl = r2l ? pr[0] : pl[0];
+	View cv, guide;
+	{
+		float* p = nullptr;
+		STEVI_TRY(arena_alloc_t(c, (size_t)sl.shape[0] * sl.shape[1] * dw[0], &p));
+		cv.p = p; cv.dtype = STEVI_F32; cv.ndim = 3;
+		cv.shape[0] = sl.shape[0]; cv.shape[1] = sl.shape[1]; cv.shape[2] = dw[0];
+		cv.st[0] = (int64_t)sl.shape[1] * dw[0]; cv.st[1] = 1; cv.st[2] = sl.shape[1];
+	}
+	STEVI_TRY(alloc_map<int32_t>(c, sl.shape[0], sl.shape[1], STEVI_I32, guide));
+	STEVI_TRY(float_cv_dev(c, mf, pl[0], pr[0], h_radii[0], v_radii[0], dw[0], direction, cv, false));
+	STEVI_TRY(wta_dev(c, cv, h_score(mf) ? STEVI_SCORE : STEVI_COST, guide));
+	for (int k = 1; k <= depth; k++) {
+		const View& s = r2l ? pr[k] : pl[k];
+		View t, d;
+		if (k == depth) { t = tcv; d = disp; }
+		else {
+			float* p = nullptr;
+			STEVI_TRY(arena_alloc_t(c, (size_t)s.shape[0] * s.shape[1] * (2 * radius + 1), &p));
+			t.p = p; t.dtype = STEVI_F32; t.ndim = 3;
+			t.shape[0] = s.shape[0]; t.shape[1] = s.shape[1]; t.shape[2] = 2 * radius + 1;
+			t.st[0] = (int64_t)s.shape[1] * t.shape[2]; t.st[1] = t.shape[2]; t.st[2] = 1;
+			STEVI_TRY(alloc_map<int32_t>(c, s.shape[0], s.shape[1], STEVI_I32, d));
+		}
+		STEVI_TRY(guided_cv_dev(c, mf, pl[k], pr[k], h_radii[k], v_radii[k], guide, radius, direction, t, d));
+		guide = d;
+	}
+	return STEVI_OK;
+}
+
+} // namespace stevi

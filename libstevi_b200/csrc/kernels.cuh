@@ -54,4 +54,11 @@ int32_t refine_interp_dev(stevi_ctx* c, const View& tcv, const View& idx, int ke
 // truncatedCostVolume<Same>(radius 1) + refineDispCostInterpolation in one pass over the winners; tcv_out optional
 int32_t refine_from_cv_dev(stevi_ctx* c, const View& cv, const View& idx, int hr, int vr, int kernel, const View* tcv_out, const View& out);
 
+// hier.cu
+int32_t avgpool_dev(stevi_ctx* c, const View& img, int win_h, int win_v, const View& out);
+int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const View& guide, int radius, int direction,
+					  const View& tcv, const View& disp);
+int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const View& r, const int32_t* h_radii, const int32_t* v_radii,
+						 int D, int radius, int direction, const View& tcv, const View& disp);
+
 } // namespace stevi

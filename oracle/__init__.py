@@ -186,6 +186,18 @@ class _Checker:
         self._f("avgpool2_f32")(_p(_c(img, np.float32)), h, w, _p(out))
         return out
 
+    def guided_cv(self, mf, left, right, hr, vr, guide, radius=2, direction=R2L):
+        h, wl = left.shape
+        wr = right.shape[1]
+        ws = wr if direction == R2L else wl
+        tcv = np.empty((h, ws, 2 * radius + 1), np.float32)
+        disp = np.empty((h, ws), np.int32)
+        g = _c(guide, np.int32)
+        rc = self._f("guided_cv_f32")(mf, _p(_c(left, np.float32)), _p(_c(right, np.float32)), h, wl, wr, hr, vr,
+                                      _p(g), g.shape[0], g.shape[1], radius, direction, _p(tcv), _p(disp))
+        assert rc == 0
+        return tcv, disp
+
     def hierarchical(self, mf, depth, left, right, hr, vr, D, radius=2, direction=R2L):
         h, w = left.shape
         tcv = np.empty((h, w, 2 * radius + 1), np.float32)
