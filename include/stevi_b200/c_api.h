@@ -111,6 +111,28 @@ STEVI_API int32_t stevi_host_free(void* p);
 STEVI_API int32_t stevi_census_transform(stevi_ctx* ctx, const stevi_array* img, int32_t h_radius, int32_t v_radius,
 							   int32_t semantics, stevi_array* out);
 
+/* unfold<T_I,T_O>(h_radius, v_radius, img, padding, orientation) (correlation/unfold.h:248-344): img (H,W) or (H,W,C)
+ * u8|f32 -> out (H',W',F*C) u8|f32, out(i,j,c) = img(i+k-pad_top, j+l-pad_left, ch), 0 outside, c = channelFromCord
+ * (:171-191; orientation 0..3 = Rotate0/90/180/270). padding = {left, top, right, bottom} like PaddingMargins; NULL or a
+ * negative entry = automatic (= the radii: H' = H, W' = W). The reference gives the 2-D overload's result strides
+ * {W*F, F, 1} (:272); any strides are accepted. */
+STEVI_API int32_t stevi_unfold(stevi_ctx* ctx, const stevi_array* img, int32_t h_radius, int32_t v_radius, const int32_t* padding,
+					 int32_t orientation, stevi_array* out);
+
+/* unfold(UnFoldCompressor(mask), img, padding) (correlation/unfold.h:36-137, :346-471): mask (mh,mw) i32 in HOST memory
+ * (labels > 0 form super-pixels, features in ascending label order); img (H,W) or (H,W,C) u8|f32 ->
+ * out (H',W',nFeatures*C) f32 of super-pixel means. */
+STEVI_API int32_t stevi_unfold_compressed(stevi_ctx* ctx, const stevi_array* mask, const stevi_array* img, const int32_t* padding,
+								stevi_array* out);
+
+/* censusFeatures (correlation/census.h:69-115) on a ready-made feature volume: feat (H,W,F) u8|f32 -> out (H,W,nwords) u32 */
+STEVI_API int32_t stevi_census_features(stevi_ctx* ctx, const stevi_array* feat, int32_t semantics, stevi_array* out);
+
+/* getFeatureVolumeForMatchFunc<matchFunc>(unfold(h_radius, v_radius, img)) (correlation/cross_correlations.h:645-722) for
+ * float images: img (H,W) f32 -> out (H,W,F) f32 = v | v-mean | v/norm | (v-mean)/norm per the function's traits. */
+STEVI_API int32_t stevi_feature_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img, int32_t h_radius,
+							 int32_t v_radius, stevi_array* out);
+
 /* ---- cost volumes ---------------------------------------------------------------------------------------- */
 
 /* unfoldBasedCostVolume<matchFunc, T_L, T_R, 2, dDir, TCV> (correlation/cross_correlations.h:740-765).

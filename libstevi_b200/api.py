@@ -419,3 +419,66 @@ def hiearchicalTruncatedCostVolume(matchFunc, depth, img_l, img_r, h_radius, v_r
         return None
     ctx.check(rc)
     return tcv, disp
+
+
+ROTATE0, ROTATE90, ROTATE180, ROTATE270 = range(4)
+
+
+def _padding_arg(padding):
+    if padding is None:
+        return None
+    return (ctypes.c_int32 * 4)(*[int(v) for v in padding])
+
+
+def unfold(h_radius, v_radius, img, padding=None, orientation=ROTATE0, T_O=None, ctx=None):
+    """unfold.h:248-344. padding = (left, top, right, bottom) or None for PaddingMargins() (automatic)."""
+    ctx = _ctx_for(ctx, img)
+    hs, vs = 2 * h_radius + 1, 2 * v_radius + 1
+    pl, pt, pr, pb = (h_radius, v_radius, h_radius, v_radius) if padding is None else padding
+    nch = img.shape[2] if len(img.shape) == 3 else 1
+    np_in = _DT2NP[_torch_dtype_code(img)] if _is_torch(img) else img.dtype
+    out = _empty(img, (img.shape[0] - vs + pt + pb + 1, img.shape[1] - hs + pl + pr + 1, hs * vs * nch), T_O or np_in)
+    a, o = describe(img), describe(out)
+    ctx.check(lib.stevi_unfold(ctx.handle, ctypes.byref(a), h_radius, v_radius, _padding_arg(padding), orientation, ctypes.byref(o)))
+    return out
+
+
+def compressor_geometry(mask):
+    """(n_features, width, height, margins(left, top, right, bottom)) of UnFoldCompressor(mask), unfold.h:48-107."""
+    mask = np.asarray(mask)
+    ii, jj = np.nonzero(mask > 0)
+    v_off, h_off = mask.shape[0] // 2, mask.shape[1] // 2
+    min_h, max_h = min(0, int((ii - v_off).min())), max(0, int((ii - v_off).max()))
+    min_w, max_w = min(0, int((jj - h_off).min())), max(0, int((jj - h_off).max()))
+    return len(np.unique(mask[mask > 0])), max_w - min_w + 1, max_h - min_h + 1, (-min_w, -min_h, max_w, max_h)
+
+
+def unfoldCompressed(mask, img, padding=None, ctx=None):
+    """unfold(UnFoldCompressor(mask), img, padding), unfold.h:346-471. mask: 2-D int array (host)."""
+    ctx = _ctx_for(ctx, img)
+    mask = np.ascontiguousarray(mask, np.int32)
+    nf, w, h, mg = compressor_geometry(mask)
+    pl, pt, pr, pb = mg if padding is None else padding
+    nch = img.shape[2] if len(img.shape) == 3 else 1
+    out = _empty(img, (img.shape[0] - h + pt + pb + 1, img.shape[1] - w + pl + pr + 1, nf * nch), np.float32)
+    m, a, o = describe(mask), describe(img), describe(out)
+    ctx.check(lib.stevi_unfold_compressed(ctx.handle, ctypes.byref(m), ctypes.byref(a), _padding_arg(padding), ctypes.byref(o)))
+    return out
+
+
+def censusFeatures(feat, semantics=COMPAT, ctx=None):
+    """census.h:69-115 on an (H,W,F) feature volume."""
+    ctx = _ctx_for(ctx, feat)
+    out = _empty(feat, tuple(feat.shape[:2]) + ((feat.shape[2] - 1) // 32 + 1,), np.uint32)
+    a, o = describe(feat), describe(out)
+    ctx.check(lib.stevi_census_features(ctx.handle, ctypes.byref(a), semantics, ctypes.byref(o)))
+    return out
+
+
+def getFeatureVolumeForMatchFunc(matchFunc, img, h_radius, v_radius, ctx=None):
+    """cross_correlations.h:645-722 applied to unfold(h_radius, v_radius, img), float images."""
+    ctx = _ctx_for(ctx, img)
+    out = _empty(img, tuple(img.shape) + ((2 * h_radius + 1) * (2 * v_radius + 1),), np.float32)
+    a, o = describe(img), describe(out)
+    ctx.check(lib.stevi_feature_volume(ctx.handle, matchFunc, ctypes.byref(a), h_radius, v_radius, ctypes.byref(o)))
+    return out

@@ -53,6 +53,49 @@ int32_t stevi_census_transform(stevi_ctx* c, const stevi_array* img, int32_t hr,
 	return st.finish();
 }
 
+int32_t stevi_unfold(stevi_ctx* c, const stevi_array* img, int32_t hr, int32_t vr, const int32_t* padding, int32_t orientation, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(unfold_dev(c, vi, hr, vr, padding, orientation, vo));
+	return st.finish();
+}
+
+int32_t stevi_unfold_compressed(stevi_ctx* c, const stevi_array* mask, const stevi_array* img, const int32_t* padding, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	if (!mask || !mask->data || mask->mem != STEVI_HOST || mask->ndim != 2 || mask->dtype != STEVI_I32)
+		return fail(c, STEVI_E_ARG, "unfold_compressed: mask must be a 2-D i32 array in host memory");
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(unfold_compressed_dev(c, static_cast<const int32_t*>(mask->data), mask->shape[0], mask->shape[1], mask->strides[0],
+									mask->strides[1], vi, padding, vo));
+	return st.finish();
+}
+
+int32_t stevi_census_features(stevi_ctx* c, const stevi_array* feat, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(feat, vi, "feat"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(census_features_dev(c, vi, semantics & 1, vo));
+	return st.finish();
+}
+
+int32_t stevi_feature_volume(stevi_ctx* c, int32_t mf, const stevi_array* img, int32_t hr, int32_t vr, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(feature_volume_dev(c, mf, vi, hr, vr, vo));
+	return st.finish();
+}
+
 int32_t stevi_hamming_cost_volume(stevi_ctx* c, const stevi_array* fl, const stevi_array* fr, int32_t D, int32_t direction,
 								  int32_t semantics, stevi_array* out) {
 	STEVI_TRY(begin_call(c));

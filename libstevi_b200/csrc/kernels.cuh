@@ -61,4 +61,11 @@ int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr
 int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const View& r, const int32_t* h_radii, const int32_t* v_radii,
 						 int D, int radius, int direction, const View& tcv, const View& disp);
 
+// unfold.cu (materialised feature volumes; pad = {left, top, right, bottom}, NULL or any negative entry = auto)
+int32_t unfold_dev(stevi_ctx* c, const View& img, int hr, int vr, const int32_t* pad, int orientation, const View& out);
+int32_t unfold_compressed_dev(stevi_ctx* c, const int32_t* mask, int mh, int mw, int64_t m0, int64_t m1, const View& img,
+							  const int32_t* pad, const View& out);
+int32_t census_features_dev(stevi_ctx* c, const View& fv, int semantics, const View& out);
+int32_t feature_volume_dev(stevi_ctx* c, int mf, const View& img, int hr, int vr, const View& out);
+
 } // namespace stevi

@@ -73,6 +73,39 @@ class _Checker:
             self._f("unfold_f32")(_p(_c(img, np.float32)), h, w, hr, vr, _p(out))
         return out
 
+    def unfold_general(self, img, hr, vr, padding=None, orientation=0):
+        img = _c(img, np.float32)
+        h, w = img.shape[:2]
+        c = img.shape[2] if img.ndim == 3 else 0
+        pad = np.asarray([-1, -1, -1, -1] if padding is None else padding, np.int32)
+        oh, ow = ctypes.c_int(), ctypes.c_int()
+        f = self._f("unfold_general_f32")
+        f(_p(img), h, w, c, hr, vr, _p(pad), orientation, None, ctypes.byref(oh), ctypes.byref(ow))
+        out = np.empty((oh.value, ow.value, (2 * hr + 1) * (2 * vr + 1) * max(c, 1)), np.float32)
+        f(_p(img), h, w, c, hr, vr, _p(pad), orientation, _p(out), ctypes.byref(oh), ctypes.byref(ow))
+        return out
+
+    def unfold_compressed(self, mask, img, padding=None):
+        img = _c(img, np.float32)
+        mask = _c(mask, np.int32)
+        h, w = img.shape[:2]
+        c = img.shape[2] if img.ndim == 3 else 0
+        pad = np.asarray([-1, -1, -1, -1] if padding is None else padding, np.int32)
+        oh, ow, nf = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        f = self._f("unfold_compressed_f32")
+        args = (_p(mask), mask.shape[0], mask.shape[1], _p(img), h, w, c, _p(pad))
+        f(*args, None, ctypes.byref(oh), ctypes.byref(ow), ctypes.byref(nf))
+        out = np.empty((oh.value, ow.value, nf.value * max(c, 1)), np.float32)
+        f(*args, _p(out), ctypes.byref(oh), ctypes.byref(ow), ctypes.byref(nf))
+        return out
+
+    def census_features(self, fv):
+        fv = _c(fv, np.float32)
+        h, w, F = fv.shape
+        out = np.zeros((h, w, (F - 1) // 32 + 1), np.uint32)
+        self._f("census_features_f32")(_p(fv), h, w, F, _p(out))
+        return out
+
     def census(self, img, hr, vr):
         h, w = img.shape
         F = (2 * hr + 1) * (2 * vr + 1)

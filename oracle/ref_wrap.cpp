@@ -113,6 +113,32 @@ int ref_unfold_u8(const uint8_t* img, int h, int w, int hr, int vr, uint8_t* out
 	out3(unfold<uint8_t, uint8_t>(uint8_t(hr), uint8_t(vr), view2(img, h, w)), out); return 0;
 }
 
+// unfold.h:248-344, any padding / orientation, 2-D (c == 0) or 3-D image. pad = {left, top, right, bottom}, pad[0] < 0 = auto.
+// out (h', w', F*max(c,1)) C-order; returns the output height in *oh, width in *ow.
+int ref_unfold_general_f32(const float* img, int h, int w, int c, int hr, int vr, const int* pad, int orientation, float* out, int* oh, int* ow) {
+	PaddingMargins pm = pad[0] < 0 ? PaddingMargins() : PaddingMargins(pad[0], pad[1], pad[2], pad[3]);
+	MD::Array<float, 3> r = c == 0 ? unfold<float, float>(uint8_t(hr), uint8_t(vr), view2(img, h, w), pm, UnfoldPatchOrientation(orientation))
+								   : unfold<float, float>(uint8_t(hr), uint8_t(vr), view3(img, h, w, c), pm, UnfoldPatchOrientation(orientation));
+	*oh = r.shape()[0]; *ow = r.shape()[1];
+	if (out) out3(r, out);
+	return 0;
+}
+
+// unfold.h:36-137 + :346-471: compressed unfold with UnFoldCompressor(mask). out (h', w', nFeatures*max(c,1)) float.
+int ref_unfold_compressed_f32(const int* mask, int mh, int mw, const float* img, int h, int w, int c, const int* pad, float* out, int* oh, int* ow, int* nf) {
+	UnFoldCompressor comp(view2(mask, mh, mw));
+	PaddingMargins pm = pad[0] < 0 ? PaddingMargins() : PaddingMargins(pad[0], pad[1], pad[2], pad[3]);
+	MD::Array<float, 3> r = c == 0 ? unfold<float, float>(comp, view2(img, h, w), pm) : unfold<float, float>(comp, view3(img, h, w, c), pm);
+	*oh = r.shape()[0]; *ow = r.shape()[1]; *nf = comp.nFeatures();
+	if (out) out3(r, out);
+	return 0;
+}
+
+// census.h:69-115 on a ready-made (h, w, F) float feature volume
+int ref_census_features_f32(const float* fv, int h, int w, int F, uint32_t* out) {
+	out3(censusFeatures(view3(fv, h, w, F)), out); return 0;
+}
+
 // census.h:117-131. out is (h, w, nwords) uint32 C-order, nwords = (F-2)/32+1... i.e. (F-1-1)/32+1 per census.h:79.
 int ref_census_u8(const uint8_t* img, int h, int w, int hr, int vr, uint32_t* out) {
 	out3(censusTransform2D(view2(img, h, w), int8_t(hr), int8_t(vr)), out); return 0;

@@ -67,6 +67,78 @@ static void NAME(const T* fv, int h, int w, int F, uint32_t* out) { \
 DEF_CENSUS_FEATS(census_feats_f32, float)
 DEF_CENSUS_FEATS(census_feats_u8, uint8_t)
 
+/* census.h:69-115 on a ready-made (h,w,F) float feature volume */
+int orc_census_features_f32(const float* fv, int h, int w, int F, uint32_t* out) { census_feats_f32(fv, h, w, F, out); return 0; }
+
+/* unfold.h:171-191 */
+static int channel_from_cord(int k, int l, int ch, int hs, int vs, int nch, int orientation) {
+	switch (orientation) {
+	case 0: return nch * hs * k + nch * l + ch;
+	case 1: return nch * vs * (hs - l - 1) + nch * k + ch;
+	case 2: return nch * hs * (vs - k - 1) + nch * (hs - l - 1) + ch;
+	default: return nch * vs * l + nch * (vs - k - 1) + ch;
+	}
+}
+
+/* unfold.h:248-344 with explicit padding {left, top, right, bottom} (pad[0] < 0: automatic = the radii) and orientation;
+ * c == 0: 2-D image. out (h', w', F*max(c,1)); the output size comes back in oh / ow (out may be NULL to query it). */
+int orc_unfold_general_f32(const float* img, int h, int w, int c, int hr, int vr, const int* pad, int orientation, float* out, int* oh, int* ow) {
+	int hs = 2 * hr + 1, vs = 2 * vr + 1, nch = c == 0 ? 1 : c;
+	int pl = pad[0] < 0 ? hr : pad[0], pt = pad[0] < 0 ? vr : pad[1], pr = pad[0] < 0 ? hr : pad[2], pb = pad[0] < 0 ? vr : pad[3];
+	int H = h - vs + pt + pb + 1, W = w - hs + pl + pr + 1, F = hs * vs * nch;
+	*oh = H; *ow = W;
+	if (!out) return 0;
+	for (int k = 0; k < vs; k++) for (int l = 0; l < hs; l++) for (int ch = 0; ch < nch; ch++) {
+		int cc = channel_from_cord(k, l, ch, hs, vs, nch, orientation);
+		for (int i = 0; i < H; i++) for (int j = 0; j < W; j++) {
+			int ii = i + k - pt, jj = j + l - pl;
+			out[((size_t)i * W + j) * F + cc] = (ii >= 0 && ii < h && jj >= 0 && jj < w) ? img[((size_t)ii * w + jj) * nch + ch] : 0.f;
+		}
+	}
+	return 0;
+}
+
+/* unfold.h:36-137 (UnFoldCompressor) + :346-471 (compressed unfold). Labels > 0, features in ascending label order,
+ * weight = (float)(1./count), accumulation in index order (per feature: row-major over the mask). */
+int orc_unfold_compressed_f32(const int* mask, int mh, int mw, const float* img, int h, int w, int c, const int* pad, float* out, int* oh, int* ow, int* nf) {
+	int v_off = mh / 2, h_off = mw / 2, minH = 0, maxH = 0, minW = 0, maxW = 0, nlab = 0;
+	int* labels = (int*)malloc(sizeof(int) * mh * mw);
+	for (int i = 0; i < mh; i++) for (int j = 0; j < mw; j++) {
+		int f = mask[i * mw + j];
+		if (f <= 0) continue;
+		if (i - v_off < minH) minH = i - v_off;
+		if (i - v_off > maxH) maxH = i - v_off;
+		if (j - h_off < minW) minW = j - h_off;
+		if (j - h_off > maxW) maxW = j - h_off;
+		int known = 0;
+		for (int n = 0; n < nlab; n++) if (labels[n] == f) known = 1;
+		if (!known) labels[nlab++] = f;
+	}
+	for (int a = 0; a < nlab; a++) for (int b = a + 1; b < nlab; b++) if (labels[b] < labels[a]) { int t = labels[a]; labels[a] = labels[b]; labels[b] = t; }
+	int nch = c == 0 ? 1 : c, cw = maxW - minW + 1, chh = maxH - minH + 1, top = -minH, left = -minW;
+	int pl = pad[0] < 0 ? -minW : pad[0], pt = pad[0] < 0 ? -minH : pad[1], pr = pad[0] < 0 ? maxW : pad[2], pb = pad[0] < 0 ? maxH : pad[3];
+	int H = h - chh + pt + pb + 1, W = w - cw + pl + pr + 1, F = nlab * nch;
+	*oh = H; *ow = W; *nf = nlab;
+	if (!out) { free(labels); return 0; }
+	memset(out, 0, sizeof(float) * (size_t)H * W * F);
+	for (int f = 0; f < nlab; f++) {
+		int count = 0;
+		for (int n = 0; n < mh * mw; n++) if (mask[n] == labels[f]) count++;
+		float wgt = (float)(1. / count);
+		for (int mi = 0; mi < mh; mi++) for (int mj = 0; mj < mw; mj++) {
+			if (mask[mi * mw + mj] != labels[f]) continue;
+			int k = mi - v_off, l = mj - h_off;
+			for (int ch = 0; ch < nch; ch++) for (int i = 0; i < H; i++) for (int j = 0; j < W; j++) {
+				int ii = i + k + top - pt, jj = j + l + left - pl;
+				float v = (ii >= 0 && ii < h && jj >= 0 && jj < w) ? img[((size_t)ii * w + jj) * nch + ch] : 0.f;
+				out[((size_t)i * W + j) * F + ch * nlab + f] += wgt * v;
+			}
+		}
+	}
+	free(labels);
+	return 0;
+}
+
 int orc_census_nwords(int hr, int vr) { int F = (2 * hr + 1) * (2 * vr + 1); return (F - 1) / 32 + 1; }
 
 /* census.h:117-131 censusTransform2D = unfold + censusFeatures */

@@ -160,3 +160,30 @@ def test_ref_testCorrelationHierarchical(depth):
     i0, j0 = (h - side) // 2, (w - side) // 2
     inner = (slice(i0 + r + 2, i0 + side - r - 2), slice(j0 + r + 2, j0 + side - r - 2))
     assert (disp[inner] == gt[inner]).mean() >= 0.95
+
+
+MASK = np.array([[1, 1, 2, 2, 2],
+                 [1, 3, 3, 3, 2],
+                 [0, 3, 7, 3, 0],
+                 [5, 3, 3, 3, 4],
+                 [5, 5, 0, 4, 4]], np.int32)
+
+
+@pytest.mark.skipif(O.ref is None, reason="compiled reference (oracle/_ref) not present on this machine")
+def test_port_equals_compiled_reference_unfold_family():
+    ref = O.ref
+    img2 = synth.random_image(11, 14, 21)
+    img3 = np.stack([synth.random_image(11, 14, 22 + k) for k in range(3)], -1)
+    for img in (img2, img3):
+        for orientation in range(4):
+            assert same(port.unfold_general(img, 2, 1, None, orientation), ref.unfold_general(img, 2, 1, None, orientation))
+        for pad in ((0, 0, 0, 0), (3, 1, 0, 2)):
+            assert same(port.unfold_general(img, 1, 2, pad, 0), ref.unfold_general(img, 1, 2, pad, 0))
+        for pad in (None, (0, 0, 0, 0), (1, 2, 3, 0)):
+            a, b = port.unfold_compressed(MASK, img, pad), ref.unfold_compressed(MASK, img, pad)
+            assert a.shape == b.shape and np.allclose(a, b, atol=1e-6)
+        a, b = port.unfold_compressed(MASK[:3, 1:4], img), ref.unfold_compressed(MASK[:3, 1:4], img)
+        assert a.shape == b.shape and np.allclose(a, b, atol=1e-6)
+    fv = port.unfold_general(img2, 3, 2)
+    assert same(port.census_features(fv), ref.census_features(fv))
+    assert same(port.census_features(fv), port.census(img2, 3, 2))
