@@ -234,6 +234,18 @@ STEVI_API int32_t stevi_census_sgm_pipeline(stevi_ctx* ctx, const stevi_array* i
 								  int32_t n_directions, float P1, float P2, float Pout, const stevi_margins* margins,
 								  int32_t semantics, stevi_array* cv_out, stevi_array* sgm_out, stevi_array* disp);
 
+/* float cost volume -> WTA -> truncated cost volume (radius 1) -> subpixel refinement in one call: the dense local
+ * matching sequence of test/benchmarks/benchmarkCrossCorrelationAlgorithms.cpp:93-95 followed by
+ * truncatedCostVolume + refineDispCostInterpolation (examples/stereo-match's refinement step). img_l, img_r (H,W*) f32
+ * (u8 for CC/SSD/SAD); refined (H,Wsource) f32 is required; cv_out (H,W,D) f32, idx_out (H,W) i32 (raw winner indices)
+ * and tcv_out (H,W,3) f32 are optional (NULL = kept in the workspace / not materialised). The winner follows the
+ * function's extraction strategy (Score for the correlations, Cost otherwise). Results are identical to calling
+ * stevi_cost_volume, stevi_wta, stevi_truncated_cost_volume and stevi_refine_disp_cost_interp in turn. */
+STEVI_API int32_t stevi_local_matching_pipeline(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+									  int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction,
+									  int32_t kernel, stevi_array* cv_out, stevi_array* idx_out, stevi_array* tcv_out,
+									  stevi_array* refined);
+
 #ifdef __cplusplus
 }
 #endif

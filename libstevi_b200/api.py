@@ -482,3 +482,34 @@ def getFeatureVolumeForMatchFunc(matchFunc, img, h_radius, v_radius, ctx=None):
     a, o = describe(img), describe(out)
     ctx.check(lib.stevi_feature_volume(ctx.handle, matchFunc, ctypes.byref(a), h_radius, v_radius, ctypes.byref(o)))
     return out
+
+
+def localMatchingPipeline(matchFunc, img_l, img_r, h_radius, v_radius, disp_width, kernel=PARABOLA, dDir=RIGHT_TO_LEFT,
+                          return_all=False, layout="ref", out=None, ctx=None):
+    """unfoldBasedCostVolume -> extractSelectedIndex -> truncatedCostVolume(radius 1) -> refineDispCostInterpolation in one
+    call. Returns the refined (H,W) f32 map, or (cv, idx, tcv, refined) with ``return_all``. ``out`` = preallocated
+    refined map or (cv, idx, tcv, refined) tuple (entries may be None)."""
+    ctx = _ctx_for(ctx, img_l)
+    H = img_l.shape[0]
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    cv = idx = tcv = None
+    if out is not None:
+        if isinstance(out, tuple):
+            cv, idx, tcv, refined = out
+        else:
+            refined = out
+    else:
+        refined = _empty(img_l, (H, ws), np.float32)
+        if return_all:
+            cv = _empty(img_l, (H, ws, disp_width), np.float32, _volume_order(layout))
+            idx = _empty(img_l, (H, ws), np.int32)
+            tcv = _empty(img_l, (H, ws, 3), np.float32)
+    l, r, o = describe(img_l), describe(img_r), describe(refined)
+    d = [describe(x) if x is not None else None for x in (cv, idx, tcv)]
+    ref = [ctypes.byref(x) if x is not None else None for x in d]
+    rc = lib.stevi_local_matching_pipeline(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, disp_width,
+                                           dDir, kernel, ref[0], ref[1], ref[2], ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return (cv, idx, tcv, refined) if (return_all or isinstance(out, tuple)) else refined

@@ -297,4 +297,40 @@ int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stev
 	return st.finish();
 }
 
+int32_t stevi_local_matching_pipeline(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr, int32_t D,
+									  int32_t direction, int32_t kernel, stevi_array* cv_out, stevi_array* idx_out, stevi_array* tcv_out,
+									  stevi_array* refined) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr_, vcv, vidx, vt, vo;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(check_images(c, vl, vr_));
+	if (!refined) return fail(c, STEVI_E_ARG, "pipeline: refined is required");
+	STEVI_TRY(st.out(refined, vo, "refined"));
+	const int H = vl.shape[0];
+	const int Ws = direction == STEVI_RIGHT_TO_LEFT ? vr_.shape[1] : vl.shape[1];
+	if (cv_out) STEVI_TRY(st.out(cv_out, vcv, "cv_out"));
+	else {
+		float* p = nullptr;
+		STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws * std::max(D, 0), &p));
+		vcv.p = p; vcv.dtype = STEVI_F32; vcv.ndim = 3;
+		vcv.shape[0] = H; vcv.shape[1] = Ws; vcv.shape[2] = D;
+		vcv.st[0] = (int64_t)Ws * D; vcv.st[1] = 1; vcv.st[2] = Ws;   // the reference's [H][D][W] layout
+	}
+	if (idx_out) STEVI_TRY(st.out(idx_out, vidx, "idx_out"));
+	else {
+		int32_t* p = nullptr;
+		STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &p));
+		vidx.p = p; vidx.dtype = STEVI_I32; vidx.ndim = 2; vidx.shape[0] = H; vidx.shape[1] = Ws; vidx.st[0] = Ws; vidx.st[1] = 1;
+	}
+	if (tcv_out) STEVI_TRY(st.out(tcv_out, vt, "tcv_out"));
+	if (D < 1) return fail(c, STEVI_E_ARG, "pipeline: disp_width must be positive");
+	STEVI_TRY(float_cv_dev(c, mf, vl, vr_, hr, vr, D, direction, vcv, false));
+	const bool score = mf == STEVI_MF_CC || mf == STEVI_MF_NCC || mf == STEVI_MF_ZCC || mf == STEVI_MF_ZNCC;
+	STEVI_TRY(wta_dev(c, vcv, score ? STEVI_SCORE : STEVI_COST, vidx));
+	STEVI_TRY(refine_from_cv_dev(c, vcv, vidx, hr, vr, kernel, tcv_out ? &vt : nullptr, vo));
+	return st.finish();
+}
+
 } // extern "C"
