@@ -85,6 +85,10 @@ STEVI_API int32_t stevi_ctx_create(int32_t device, void* stream, stevi_ctx** out
 STEVI_API int32_t stevi_ctx_destroy(stevi_ctx* ctx);
 STEVI_API int32_t stevi_ctx_set_stream(stevi_ctx* ctx, void* stream);
 STEVI_API void* stevi_ctx_stream(stevi_ctx* ctx);
+/* Row-band runs (one frame split over several GPUs): tells the ctx which global row of the frame is row 0 of the images
+ * passed to the following calls. It only anchors the kernels' internal row blocking (the float cost volumes keep running
+ * window sums per block of 32 rows), so that a band gives bit-identical rows to the whole-frame call. Default 0. */
+STEVI_API int32_t stevi_ctx_set_row_origin(stevi_ctx* ctx, int32_t global_row_of_row0);
 STEVI_API int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
 STEVI_API const char* stevi_last_error(stevi_ctx* ctx);
 /* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */
@@ -213,6 +217,16 @@ STEVI_API int32_t stevi_avgpool_downsample(stevi_ctx* ctx, const stevi_array* im
 STEVI_API int32_t stevi_guided_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
 								 int32_t h_radius, int32_t v_radius, const stevi_array* guide, int32_t upscale_disp_radius,
 								 int32_t direction, stevi_array* tcv, stevi_array* disp);
+
+/* Row-band form of stevi_guided_cost_volume for frames split across GPUs: img_l / img_r hold image
+ * rows img_row0 .. img_row0 + rows-1 of an image that is img_height rows tall, guide holds guide rows guide_row0 .. of a
+ * guide that is guide_height rows tall, and tcv / disp receive the rows out_row0 .. out_row0 + tcv.shape[0]-1. The guide
+ * is upsampled in the GLOBAL coordinates i*(guide_height-1)/(img_height-1) (hierarchical.h:116), so the band results are
+ * identical to the rows of the whole-frame call. The image band must carry v_radius halo rows on its inner edges. */
+typedef struct { int32_t img_row0, img_height, out_row0, guide_row0, guide_height; } stevi_band;
+STEVI_API int32_t stevi_guided_cost_volume_band(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+									  int32_t h_radius, int32_t v_radius, const stevi_array* guide, int32_t upscale_disp_radius,
+									  int32_t direction, const stevi_band* band, stevi_array* tcv, stevi_array* disp);
 
 /* hiearchicalTruncatedCostVolume<matchFunc, depth, ...> (sic; correlation/hierarchical.h:235-314). h_radii / v_radii:
  * depth+1 entries, coarsest level first, like the reference's std::array arguments (NULL = h_radius / v_radius at every

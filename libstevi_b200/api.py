@@ -134,6 +134,10 @@ class Context:
     def synchronize(self):
         self.check(lib.stevi_ctx_synchronize(self._h))
 
+    def set_row_origin(self, row):
+        """Global frame row of row 0 of the images passed next (row-band runs; see stevi_ctx_set_row_origin)."""
+        self.check(lib.stevi_ctx_set_row_origin(self._h, int(row)))
+
     def set_timing(self, enable):
         self.check(lib.stevi_ctx_set_timing(self._h, 1 if enable else 0))
 
@@ -513,3 +517,24 @@ def localMatchingPipeline(matchFunc, img_l, img_r, h_radius, v_radius, disp_widt
         return None
     ctx.check(rc)
     return (cv, idx, tcv, refined) if (return_all or isinstance(out, tuple)) else refined
+
+
+class StBand(ctypes.Structure):
+    _fields_ = [("img_row0", ctypes.c_int32), ("img_height", ctypes.c_int32), ("out_row0", ctypes.c_int32),
+                ("guide_row0", ctypes.c_int32), ("guide_height", ctypes.c_int32)]
+
+
+def computeGuidedCVBand(matchFunc, img_l, img_r, h_radius, v_radius, guide, img_row0, img_height, out_row0, n_rows,
+                        guide_row0, guide_height, upscale_disp_radius=2, dDir=RIGHT_TO_LEFT, ctx=None):
+    """Rows out_row0 .. out_row0+n_rows-1 of computeGuidedCV on a frame of img_height rows, from row bands of the images
+    (starting at global row img_row0) and of the guide (starting at global guide row guide_row0 of guide_height)."""
+    ctx = _ctx_for(ctx, img_l)
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    tcv = _empty(img_l, (n_rows, ws, 2 * upscale_disp_radius + 1), np.float32)
+    disp = _empty(img_l, (n_rows, ws), np.int32)
+    band = StBand(int(img_row0), int(img_height), int(out_row0), int(guide_row0), int(guide_height))
+    l, r, g, t, d = describe(img_l), describe(img_r), describe(guide), describe(tcv), describe(disp)
+    ctx.check(lib.stevi_guided_cost_volume_band(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius,
+                                                ctypes.byref(g), upscale_disp_radius, dDir, ctypes.byref(band),
+                                                ctypes.byref(t), ctypes.byref(d)))
+    return tcv, disp

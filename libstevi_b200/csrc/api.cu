@@ -237,7 +237,23 @@ int32_t stevi_guided_cost_volume(stevi_ctx* c, int32_t mf, const stevi_array* l,
 	STEVI_TRY(st.in(guide, vg, "guide"));
 	STEVI_TRY(st.out(tcv, vt, "tcv"));
 	STEVI_TRY(st.out(disp, vd, "disp"));
-	STEVI_TRY(guided_cv_dev(c, mf, vl, vr_, hr, vr, vg, radius, direction, vt, vd));
+	STEVI_TRY(guided_cv_dev(c, mf, vl, vr_, hr, vr, vg, radius, direction, nullptr, vt, vd));
+	return st.finish();
+}
+
+int32_t stevi_guided_cost_volume_band(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
+									  const stevi_array* guide, int32_t radius, int32_t direction, const stevi_band* band,
+									  stevi_array* tcv, stevi_array* disp) {
+	STEVI_TRY(begin_call(c));
+	if (!band) return fail(c, STEVI_E_ARG, "guided_cost_volume_band: band is required");
+	Stager st(c);
+	View vl, vr_, vg, vt, vd;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(st.in(guide, vg, "guide"));
+	STEVI_TRY(st.out(tcv, vt, "tcv"));
+	STEVI_TRY(st.out(disp, vd, "disp"));
+	STEVI_TRY(guided_cv_dev(c, mf, vl, vr_, hr, vr, vg, radius, direction, band, vt, vd));
 	return st.finish();
 }
 

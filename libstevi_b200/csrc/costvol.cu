@@ -190,21 +190,6 @@ __global__ void __launch_bounds__(128) k_cv_direct(const DirectParams p) {
 	p.out[(int64_t)i * p.o0 + (int64_t)j * p.o1 + (int64_t)d * p.o2] = acc;
 }
 
-// band height: few enough bands that the (2vr+1)-row start-up is amortised, enough blocks that the tail wave is small
-int pick_band_rows(int H, int blocks_per_band, int vr, int resident) {
-	int best = 32;
-	double best_cost = 1e30;
-	for (int R = 12; R <= 64 && R + 2 * vr <= BOX_MAX_TILE_ROWS; R++) {
-		const int bands = cdiv(H, R);
-		const double waves = (double)bands * blocks_per_band / resident;
-		const double tail = std::max(1.0, (double)(int64_t)(waves + 0.999)) / std::max(waves, 1e-9);
-		const double startup = (2.0 * vr + 1 + 2.0 * (R - 1)) / (2.0 * R);
-		const double cost = (waves < 1.0 ? 1.0 : tail) * startup * (double)(bands * R) / H;
-		if (cost < best_cost) { best_cost = cost; best = R; }
-	}
-	return best;
-}
-
 } // namespace
 
 int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows) {
@@ -275,9 +260,8 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 	if (l.ndim == 2 && r.ndim == 2 && l.dtype == STEVI_U8 && r.dtype == STEVI_U8 && (mf_zero_mean(mf) || mf_normalized(mf)))
 		return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: the reference's int16 fixed-point features for u8 images (cross_correlations.h:416-462) are not available; pass float images");
 	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
-	const bool direct = force_direct || mf == STEVI_MF_ZSAD || hr < 1 || hr > 4 || 12 + 2 * vr > BOX_MAX_TILE_ROWS;
-	const int blocks_per_band = cdiv(r2l ? r.shape[1] : l.shape[1], 128) * cdiv(std::max(D, 1), BOX_D_PER_BLOCK);
-	const int R = direct ? 1 : pick_band_rows(l.shape[0], blocks_per_band, vr, BOX_BLOCKS_PER_SM * c->sm_count);
+	const bool direct = force_direct || mf == STEVI_MF_ZSAD || hr < 1 || hr > 4 || BOX_BAND_ROWS + 2 * vr > BOX_MAX_TILE_ROWS;
+	const int R = direct ? 1 : BOX_BAND_ROWS;
 	PaddedPair pp;
 	STEVI_TRY(pp.build(c, l, r, hr, vr, D, R));
 	const int si = r2l ? 1 : 0, ti = 1 - si;
@@ -304,11 +288,10 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, op == BOX_PROD ? STATS_PROD_TGT : STATS_DIFF_TGT));
 	BoxParams p;
 	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.As = pp.A[si]; p.Bs = pp.B[si]; p.At = pp.A[ti]; p.Bt = pp.B[ti];
-	p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left; p.H = H; p.Ws = Ws; p.D = D; p.vr = vr; p.R = R;
+	p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left; p.H = H; p.Ws = Ws; p.D = D; p.vr = vr; p.R = R; p.row_shift = ((c->row_origin % R) + R) % R;
 	p.Ff = (float)((2 * hr + 1) * (2 * vr + 1));
 	p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
 	p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0;
-	if (cdiv(H, R) > 65535) return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: too many row bands");
 	switch (op) {
 	case BOX_PROD: return launch_cv_box_prod(c, p, hr, r2l ? 1 : -1);
 	case BOX_SQ: return launch_cv_box_sq(c, p, hr, r2l ? 1 : -1);

@@ -35,6 +35,9 @@ enum { BOX_PROD = 0, BOX_SQ = 1, BOX_ABS = 2 };
 // a block = 16 column groups (128 source columns) x 8 disparity groups (32 disparities); three blocks per SM leave
 // 168 registers per thread, enough for the 64 window sums plus the row being consumed without spilling
 constexpr int BOX_THREADS = 128, BOX_BLOCKS_PER_SM = 3, BOX_D_PER_BLOCK = 32;
+// rows per kernel band: fixed, so that band boundaries (and with them the rounding of the running sums) depend only on the
+// global row index; (2vr+1) + 2*31 row updates per 32 output rows = 1.1x the steady-state work at vr = 4
+constexpr int BOX_BAND_ROWS = 32;
 
 // Geometry of the padded planes (images and statistics maps share it). A padded row holds `pitch` floats (a multiple of
 // 64); padded column X = pad_left + j. The row is stored DE-INTERLEAVED by 16-byte units: unit u = X/4 lives at
@@ -50,7 +53,7 @@ struct BoxParams {
 	const float* At; const float* Bt;   // target window statistics
 	int64_t pitch;
 	int half, pad_left;
-	int H, Ws, D, vr, R;
+	int H, Ws, D, vr, R, row_shift;
 	float Ff;                           // number of features F as float
 	float* out; int64_t o0, o1, o2;
 	int vec_store;                      // o1 == 1, 16-byte aligned rows
@@ -145,8 +148,11 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 	const int jb = blockIdx.x * 128, db = blockIdx.y * BOX_D_PER_BLOCK;
 	const int j0 = jb + cg * 8;
 	const int d0 = db + dg * 4;
-	const int i0 = blockIdx.z * p.R;
-	const int i_end = min(i0 + p.R, p.H);
+	// kernel row bands are anchored at GLOBAL multiples of R (row_shift = global row of image row 0, mod R): the running
+	// sums of a row then round the same way whether the caller passes the whole frame or a row band of it
+	const int i0 = max((int)blockIdx.z * p.R - p.row_shift, 0);
+	const int i_end = min((int)(blockIdx.z + 1) * p.R - p.row_shift, p.H);
+	if (i0 >= i_end) return;
 	const int n_rows = p.R + 2 * p.vr;      // tile row r <-> image row i0 - vr + r
 	// first unit of the block's source window, and of its target window (lowest column any of its threads reads)
 	const int us_blk = (p.pad_left + jb - LH) >> 2;
@@ -289,7 +295,7 @@ static int32_t launch_cv_box_hr(stevi_ctx* c, const BoxParams& p, int sign, dim3
 
 template<int OP>
 int32_t launch_cv_box(stevi_ctx* c, const BoxParams& p, int hr, int sign) {
-	dim3 grid(cdiv(p.Ws, 128), cdiv(p.D, BOX_D_PER_BLOCK), cdiv(p.H, p.R));
+	dim3 grid(cdiv(p.Ws, 128), cdiv(p.D, BOX_D_PER_BLOCK), cdiv(p.H + p.row_shift, p.R));
 	switch (hr) {
 	case 1: return launch_cv_box_hr<OP, 1>(c, p, sign, grid);
 	case 2: return launch_cv_box_hr<OP, 2>(c, p, sign, grid);

@@ -175,6 +175,12 @@ int32_t stevi_ctx_set_stream(stevi_ctx* c, void* stream) {
 	return STEVI_OK;
 }
 
+int32_t stevi_ctx_set_row_origin(stevi_ctx* c, int32_t row) {
+	if (!c) return STEVI_E_ARG;
+	c->row_origin = row;
+	return STEVI_OK;
+}
+
 void* stevi_ctx_stream(stevi_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
 int32_t stevi_ctx_synchronize(stevi_ctx* c) {

@@ -38,8 +38,9 @@ __global__ void __launch_bounds__(128) k_avgpool(const TI* __restrict__ img, int
 struct Guided {
 	const float* ps; const float* pt; int64_t pitch; int half, pad_left;
 	const float* Ms; const float* Ns; const float* Mt; const float* Nt;   // STATS_RAW maps (mean, norm)
-	const int32_t* guide; int64_t g0, g1; int hg, wg;
-	int H, Ws, Wt, hr, vr, r, sign, op, zero_mean, normalized, cost;
+	const int32_t* guide; int64_t g0, g1; int hg, wg;   // hg, wg: GLOBAL guide size (interpolation coordinates)
+	int H, Ws, Wt, hr, vr, r, sign, op, zero_mean, normalized, cost;   // H: GLOBAL image height
+	int n_rows, out_row0, img_row0, guide_row0;       // row band: output rows out_row0.., image/guide buffers start at these global rows
 	float* tcv; int64_t t0, t1, t2;
 	int32_t* disp; int64_t d0s, d1s;
 };
@@ -51,10 +52,12 @@ constexpr int GUIDED_MAX_R = 4; // candidates at offsets -2r..2r around the guid
 //   correlations: (sum s*t - F*m_s*m_t) / (n_s*n_t);  costs: sum op((s - m_s) - (t - m_t))
 // instead of over materialised (v-mean)/norm feature volumes (49 x 4 bytes per pixel and image at C4).
 __global__ void __launch_bounds__(128) k_guided_cv(const Guided p) {
-	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+	const int j = blockIdx.x * 128 + threadIdx.x, io = blockIdx.y;
 	if (j >= p.Ws) return;
+	const int gi = p.out_row0 + io;        // global row: the guide is upsampled in global coordinates (Q7)
+	const int i = gi - p.img_row0;         // row inside the image band
 	// hierarchical.h:116-148, same operation order in fp32
-	const float v_pos = __fdiv_rn((float)(i * (p.hg - 1)), (float)(p.H - 1));
+	const float v_pos = __fdiv_rn((float)(gi * (p.hg - 1)), (float)(p.H - 1));
 	int v0 = (int)floorf(v_pos), v1 = (int)ceilf(v_pos);
 	if (v0 == v1) v1 += 1;
 	if (v1 == p.hg) { v0 -= 1; v1 -= 1; }
@@ -65,10 +68,11 @@ __global__ void __launch_bounds__(128) k_guided_cv(const Guided p) {
 	const float av = __fsub_rn(v_pos, (float)v0), bv = __fsub_rn((float)v1, v_pos);
 	const float ah = __fsub_rn(h_pos, (float)h0), bh = __fsub_rn((float)h1, h_pos);
 	float id = 0.f;
-	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, ah), (float)p.guide[v1 * p.g0 + h1 * p.g1]));
-	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, ah), (float)p.guide[v0 * p.g0 + h1 * p.g1]));
-	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, bh), (float)p.guide[v1 * p.g0 + h0 * p.g1]));
-	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, bh), (float)p.guide[v0 * p.g0 + h0 * p.g1]));
+	const int64_t gr0 = (int64_t)(v0 - p.guide_row0) * p.g0, gr1 = (int64_t)(v1 - p.guide_row0) * p.g0;
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, ah), (float)p.guide[gr1 + h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, ah), (float)p.guide[gr0 + h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, bh), (float)p.guide[gr1 + h0 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, bh), (float)p.guide[gr0 + h0 * p.g1]));
 	id = __fmul_rn(id, 2.f);
 	const int d0 = p.sign * (int)roundf(id);
 
@@ -135,9 +139,9 @@ __global__ void __launch_bounds__(128) k_guided_cv(const Guided p) {
 		for (int e = 0; e < 4 * GUIDED_MAX_R + 1; e++) if (e == dd + 2 * p.r) cmp = acc[e];
 		if (p.cost ? (cmp < score) : (cmp > score)) { score = cmp; d_r = d0 + dd; }
 	}
-	p.disp[i * p.d0s + j * p.d1s] = p.sign * d_r;
+	p.disp[io * p.d0s + j * p.d1s] = p.sign * d_r;
 	// cell dd holds the comparison against target column j + d_r + sign*(dd - r) (after the reference's shift-and-refill)
-	float* o = p.tcv + i * p.t0 + j * p.t1;
+	float* o = p.tcv + io * p.t0 + j * p.t1;
 	for (int dd = 0; dd <= 2 * p.r; dd++) {
 		const int want = (d_r - d0) + p.sign * (dd - p.r) + 2 * p.r;
 		float cmp = 0.f;
@@ -196,7 +200,7 @@ int32_t avgpool_dev(stevi_ctx* c, const View& img, int wh, int wv, const View& o
 }
 
 int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const View& guide, int radius, int direction,
-					  const View& tcv, const View& disp) {
+					  const stevi_band* band, const View& tcv, const View& disp) {
 	if (!h_known(mf)) return fail(c, STEVI_E_UNSUPPORTED, "guided_cv: matching function %d not available", mf);
 	if (radius < 0 || radius > GUIDED_MAX_R) return fail(c, STEVI_E_UNSUPPORTED, "guided_cv: upscale radius must be 0..%d", GUIDED_MAX_R);
 	if (hr < 0 || vr < 0 || hr > 127 || vr > 127) return fail(c, STEVI_E_ARG, "guided_cv: radii out of range");
@@ -207,24 +211,42 @@ int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr
 	STEVI_TRY(pp.build(c, l, r, hr, vr, 0, 1));
 	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
 	const int si = r2l ? 1 : 0, ti = 1 - si;
-	const int H = pp.H, Ws = pp.W[si];
+	const int Ws = pp.W[si];
+	// whole image: output rows = image rows, everything starts at global row 0
+	const int H = band ? band->img_height : pp.H, hg = band ? band->guide_height : guide.shape[0];
+	const int n_rows = band ? tcv.shape[0] : pp.H;
 	// hierarchical.h:89-91 returns an empty volume on a shape mismatch; 1-pixel axes divide by zero (Q7)
-	if (H < 2 || Ws < 2 || guide.shape[0] < 2 || guide.shape[1] < 2) return fail(c, STEVI_E_SHAPE, "guided_cv: every axis needs at least 2 pixels (hierarchical.h:116,132)");
-	if (tcv.ndim != 3 || tcv.dtype != STEVI_F32 || tcv.shape[0] != H || tcv.shape[1] != Ws || tcv.shape[2] != 2 * radius + 1)
-		return fail(c, STEVI_E_SHAPE, "guided_cv: tcv must be (%d,%d,%d) f32", H, Ws, 2 * radius + 1);
-	if (disp.ndim != 2 || disp.dtype != STEVI_I32 || disp.shape[0] != H || disp.shape[1] != Ws)
-		return fail(c, STEVI_E_SHAPE, "guided_cv: disp must be (%d,%d) i32", H, Ws);
+	if (H < 2 || Ws < 2 || hg < 2 || guide.shape[1] < 2) return fail(c, STEVI_E_SHAPE, "guided_cv: every axis needs at least 2 pixels (hierarchical.h:116,132)");
+	if (band) {
+		const int lo = band->out_row0 - band->img_row0;
+		if (band->img_row0 < 0 || lo < 0 || lo + n_rows > pp.H || band->out_row0 + n_rows > H || band->img_row0 + pp.H > H)
+			return fail(c, STEVI_E_ARG, "guided_cv: output rows must lie inside the image band and the image");
+		// the window of an output row may leave the band only where it also leaves the image
+		if ((lo < vr && band->img_row0 > 0) || (lo + n_rows + vr > pp.H && band->img_row0 + pp.H < H))
+			return fail(c, STEVI_E_ARG, "guided_cv: the image band needs v_radius halo rows on its inner edges");
+		// guide rows touched by the bilinear upsampling of the band's rows (same arithmetic as the kernel, conservatively)
+		const int v_lo = std::max(0, (int)((int64_t)band->out_row0 * (hg - 1) / (H - 1)) - 1);
+		const int v_hi = std::min(hg - 1, (int)((int64_t)(band->out_row0 + n_rows - 1) * (hg - 1) / (H - 1)) + 2);
+		if (band->guide_row0 > v_lo || band->guide_row0 + guide.shape[0] - 1 < v_hi || band->guide_row0 < 0)
+			return fail(c, STEVI_E_ARG, "guided_cv: the guide band must cover global guide rows %d..%d", v_lo, v_hi);
+	}
+	if (tcv.ndim != 3 || tcv.dtype != STEVI_F32 || tcv.shape[0] != n_rows || tcv.shape[1] != Ws || tcv.shape[2] != 2 * radius + 1)
+		return fail(c, STEVI_E_SHAPE, "guided_cv: tcv must be (%d,%d,%d) f32", n_rows, Ws, 2 * radius + 1);
+	if (disp.ndim != 2 || disp.dtype != STEVI_I32 || disp.shape[0] != n_rows || disp.shape[1] != Ws)
+		return fail(c, STEVI_E_SHAPE, "guided_cv: disp must be (%d,%d) i32", n_rows, Ws);
+	if (n_rows == 0) return STEVI_OK;
 	STEVI_TRY(pp.stats(c, si, hr, vr, mf, 0 /* raw: mean, norm */));
 	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, 0));
 	Guided p;
 	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left;
 	p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
-	p.guide = guide.as<int32_t>(); p.g0 = guide.st[0]; p.g1 = guide.st[1]; p.hg = guide.shape[0]; p.wg = guide.shape[1];
+	p.guide = guide.as<int32_t>(); p.g0 = guide.st[0]; p.g1 = guide.st[1]; p.hg = hg; p.wg = guide.shape[1];
+	p.n_rows = n_rows; p.out_row0 = band ? band->out_row0 : 0; p.img_row0 = band ? band->img_row0 : 0; p.guide_row0 = band ? band->guide_row0 : 0;
 	p.H = H; p.Ws = Ws; p.Wt = pp.W[ti]; p.hr = hr; p.vr = vr; p.r = radius; p.sign = r2l ? 1 : -1;
 	p.op = h_op(mf); p.zero_mean = h_zero_mean(mf); p.normalized = h_normalized(mf); p.cost = h_score(mf) ? 0 : 1;
 	p.tcv = tcv.as<float>(); p.t0 = tcv.st[0]; p.t1 = tcv.st[1]; p.t2 = tcv.st[2];
 	p.disp = disp.as<int32_t>(); p.d0s = disp.st[0]; p.d1s = disp.st[1];
-	dim3 grid(cdiv(Ws, 128), H);
+	dim3 grid(cdiv(Ws, 128), n_rows);
 	STEVI_LAUNCH(c, k_guided_cv, grid, 128, 0, p);
 	return STEVI_OK;
 }
@@ -273,7 +295,7 @@ int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const V
 			t.st[0] = (int64_t)s.shape[1] * t.shape[2]; t.st[1] = t.shape[2]; t.st[2] = 1;
 			STEVI_TRY(alloc_map<int32_t>(c, s.shape[0], s.shape[1], STEVI_I32, d));
 		}
-		STEVI_TRY(guided_cv_dev(c, mf, pl[k], pr[k], h_radii[k], v_radii[k], guide, radius, direction, t, d));
+		STEVI_TRY(guided_cv_dev(c, mf, pl[k], pr[k], h_radii[k], v_radii[k], guide, radius, direction, nullptr, t, d));
 		guide = d;
 	}
 	return STEVI_OK;

@@ -56,8 +56,9 @@ int32_t refine_from_cv_dev(stevi_ctx* c, const View& cv, const View& idx, int hr
 
 // hier.cu
 int32_t avgpool_dev(stevi_ctx* c, const View& img, int win_h, int win_v, const View& out);
+// band == nullptr: whole images; else the images / guide are row bands placed in global coordinates (c_api.h: stevi_band)
 int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const View& guide, int radius, int direction,
-					  const View& tcv, const View& disp);
+					  const stevi_band* band, const View& tcv, const View& disp);
 int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const View& r, const int32_t* h_radii, const int32_t* v_radii,
 						 int D, int radius, int direction, const View& tcv, const View& disp);
 
