@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the dense-stereo hot path (BASELINE.json metric: Gdisp/s = W*H*D / s).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c5|c3|c4]
 
 One step = one pass of census 9x7 -> Hamming cost volume (u16) -> SGM 8 directions -> WTA -> disparity over one
 synthetic rectified pair (BASELINE.json configs[1]: 1920x1080, D=256; `--workload c5`: 1280x720, D=128).
@@ -13,6 +13,9 @@ synthetic rectified pair (BASELINE.json configs[1]: 1920x1080, D=256; `--workloa
   cpu_baseline / --impl reference  the reference's own CPU code (oracle/_ref, compiled from the unmodified LibStevi
          headers) on the host cores, on a bounded row band of the same workload.
 N > 1 (torchrun): independent pairs are sharded across ranks, no data-path collective (weak scaling).
+Secondary workloads (not the headline line): `--workload c3` = ZNCC 9x9 cost volume + WTA + refinement (configs[2]);
+`--workload c4` = the coarse-to-fine driver on one 4096x3072 frame, split in row bands over the ranks and gathered with
+one NCCL all_gather (configs[3], strong scaling).
 """
 import argparse
 import json
@@ -33,6 +36,10 @@ WORKLOADS = {
                name="census9x7+SGM8+WTA 1920x1080 D=256 u16 costs (BASELINE configs[1])"),
     "c5": dict(H=720, W=1280, D=128, hr=4, vr=3, seed=1000, d_max=100,
                name="census9x7+SGM8+WTA 1280x720 D=128 u16 costs (BASELINE configs[4], one pair per step per GPU)"),
+    "c3": dict(kind="zncc", H=1080, W=1920, D=192, hr=4, vr=4, seed=3, d_max=120,
+               name="ZNCC9x9 cost volume + WTA + truncated volume + parabola refinement 1920x1080 D=192 f32 (BASELINE configs[2])"),
+    "c4": dict(kind="hier", H=3072, W=4096, D=512, hr=3, vr=3, seed=4, d_max=0, depth=3, radius=2,
+               name="hierarchical ZNCC7x7 depth 3, 4096x3072 D=512 f32, one frame split in row bands over the GPUs (BASELINE configs[3])"),
 }
 P1, P2, POUT, NDIR = 10.0, 120.0, 100.0, 8
 # algorithmic bytes per disparity cell. CV: 2 written; SGM: 2 read + 4 written; WTA: 4 read.
@@ -122,6 +129,207 @@ def cpu_reference_run(wl, steps, warmup, band_rows=None, budget_s=15.0):
                       f"{steps} step(s), {dt:.2f} s/step"}, dt
 
 
+def cpu_reference_float(wl, steps, warmup, budget_s=15.0):
+    """The reference's CPU code for the float workloads on a bounded sample: c3 = a row band of the 1080p pair through
+    cost volume + WTA + truncated volume + refinement; c4 = the whole hierarchical driver on a reduced frame."""
+    import oracle as O
+    from libstevi_b200 import synth
+    chk, kind = (O.ref, "reference") if O.ref is not None else (O.port, "port")
+    cores = os.cpu_count() or 1
+    chk.set_num_threads(cores)
+    n = max(steps + warmup, 1)
+    if wl["kind"] == "zncc":
+        H, W, D = wl["H"], wl["W"], wl["D"]
+        L, R, _ = synth.stereo_pair(H, W, wl["seed"], d_bg=8, d_sq=32, d_max=wl["d_max"], dtype=np.float32)
+        t_row = 0.035 * 8.0 / cores  # ~35 ms per 1920x192 row of 9x9 ZNCC on 8 cores (measured in the survey probe)
+        rows = max(2 * wl["vr"] + 2, min(H, int(budget_s / (n * t_row))))
+        i0 = (H - rows) // 2
+        Lb, Rb = np.ascontiguousarray(L[i0:i0 + rows]), np.ascontiguousarray(R[i0:i0 + rows])
+
+        def step():
+            cv = chk.cost_volume(O.ZNCC, Lb, Rb, wl["hr"], wl["vr"], D)
+            idx = chk.wta(cv, O.SCORE)
+            return chk.refine(chk.truncated_cost_volume(cv, idx, wl["hr"], wl["vr"], 1), idx, O.PARABOLA)
+        cells = rows * W * D
+        sample = f"rows {i0}..{i0 + rows} of the {W}x{H} pair ({rows}x{W}xD{D} cells per step)"
+    else:
+        H, W, D = wl["H"] // 8, wl["W"] // 8, wl["D"] // 8
+        L, R, _ = synth.stereo_pair(H, W, wl["seed"], d_bg=3, d_sq=12, dtype=np.float32)
+
+        def step():
+            return chk.hierarchical(O.ZNCC, wl["depth"], L, R, wl["hr"], wl["vr"], D, wl["radius"])
+        cells = H * W * D
+        sample = f"the same driver on a {W}x{H} D={D} frame (1/8 scale per axis; {cells} cells per step)"
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return {"value": cells / dt / 1e9, "unit": "Gdisp/s", "cores": cores, "kind": kind,
+            "sample": f"{sample}, {steps} step(s), {dt:.2f} s/step"}, dt
+
+
+def main_float(args, wl, rank, world, local_rank):
+    """c3 (ZNCC + refinement, independent pairs per rank) and c4 (coarse-to-fine on one frame split in row bands)."""
+    H, W, D = wl["H"], wl["W"], wl["D"]
+    cells = H * W * D
+    hier = wl["kind"] == "hier"
+    metric = "Gdisp/s (W*H*D/s) " + ("hierarchical ZNCC" if hier else "ZNCC cost volume+WTA+refinement")
+    config = {"workload": wl["name"], "H": H, "W": W, "D": D, "window": f"{2 * wl['hr'] + 1}x{2 * wl['vr'] + 1}",
+              "sharding": ("row bands with halos in global coordinates, one all_gather of the result bands (NCCL)" if hier
+                           else "independent pairs per rank, no collective")}
+    if hier:
+        config.update(depth=wl["depth"], upscale_disp_radius=wl["radius"])
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        base, dt = cpu_reference_float(wl, args.steps, args.warmup, budget_s=120.0)
+        print(json.dumps({"impl": "reference", "metric": metric, "value": base["value"], "unit": "Gdisp/s", "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+                          "scaling": "strong" if hier else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                          "config": config, "cpu_baseline": base, "gpu_launches": 0,
+                          "e2e": {"value": base["value"], "unit": "Gdisp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return 0
+    import torch
+    from libstevi_b200 import api, synth, sharding
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    warmup = max(args.warmup, 3)
+    seed = wl["seed"] + (0 if hier else rank)
+    L, R, gt = synth.stereo_pair(H, W, seed, d_bg=24 if hier else 8, d_sq=96 if hier else 32, d_max=wl["d_max"], dtype=np.float32)
+    ctx = api.Context(local_rank, torch_stream=True)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    hl, hr_ = torch.from_numpy(L).pin_memory(), torch.from_numpy(R).pin_memory()
+    if hier:
+        bands = sharding.row_bands(H, world, 2)
+        g0, g1 = bands[rank]
+        plan = sharding.band_plan(H, wl["depth"], [wl["vr"]] * (wl["depth"] + 1), g0, g1)[-1]
+        lo, hi = (0, H) if world == 1 else (plan.img_lo, plan.img_hi)
+        dl, dr = torch.from_numpy(L[lo:hi]).to(dev), torch.from_numpy(R[lo:hi]).to(dev)
+        res = {}
+
+        def run(l, r):
+            if world == 1:
+                return api.hiearchicalTruncatedCostVolume(api.ZNCC, wl["depth"], l, r, wl["hr"], wl["vr"], D, wl["radius"], ctx=ctx)
+            t, d = sharding.hierarchical_rows(api, api.ZNCC, wl["depth"], l, r, wl["hr"], wl["vr"], D, g0, g1, wl["radius"],
+                                              band_row0=lo, full_height=H, ctx=ctx)
+            return sharding.gather_rows(t, bands, dist), sharding.gather_rows(d, bands, dist)
+
+        def step_device():
+            res["tcv"], res["disp"] = run(dl, dr)
+
+        hdisp = torch.empty((H, W), dtype=torch.int32).pin_memory()
+
+        def step_host():  # host frame in, host disparity map out (the band's rows travel H2D, the gathered map D2H)
+            l, r = hl[lo:hi].to(dev, non_blocking=True), hr_[lo:hi].to(dev, non_blocking=True)
+            _, d = run(l, r)
+            hdisp.copy_(d, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        h2d, d2h = 2 * (hi - lo) * W * 4, H * W * 4
+        dom_key, dom_bytes = "k_guided_cv", None
+    else:
+        dl, dr = torch.from_numpy(L).to(dev), torch.from_numpy(R).to(dev)
+        cv = torch.empty((H, D, W), dtype=torch.float32, device=dev).permute(0, 2, 1)  # [H][D][W], cross_correlations.h:220
+        idx = torch.empty((H, W), dtype=torch.int32, device=dev)
+        tcv = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+        refined = torch.empty((H, W), dtype=torch.float32, device=dev)
+        res = {"disp": idx}
+
+        def step_device():
+            api.localMatchingPipeline(api.ZNCC, dl, dr, wl["hr"], wl["vr"], D, api.PARABOLA, out=(cv, idx, tcv, refined), ctx=ctx)
+
+        nl, nr = hl.numpy(), hr_.numpy()
+        href = torch.empty((H, W), dtype=torch.float32).pin_memory()
+        nref = href.numpy()
+
+        def step_host():
+            api.localMatchingPipeline(api.ZNCC, nl, nr, wl["hr"], wl["vr"], D, api.PARABOLA, out=nref, ctx=ctx)
+        h2d, d2h = 2 * H * W * 4, H * W * 4
+        dom_key, dom_bytes = "k_cv_box", cells * 4
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step, steps, sampler=None):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        if sampler:
+            sampler.start()
+        for e0, e1 in evs:
+            flush.zero_()
+            e0.record()
+            step()
+            e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+        if dist is not None:
+            ms = sharding.max_over_ranks(ms, dist, dev)
+        return ms, clocks
+
+    for _ in range(warmup):
+        step_device()
+    n0 = ctx.launches
+    ms_dev, clocks = timed(step_device, args.steps, ClockSampler(local_rank) if rank == 0 else None)
+    launches = ctx.launches - n0
+    for _ in range(warmup):
+        step_host()
+    ms_host, _ = timed(step_host, args.steps)
+    ctx.set_timing(True)
+    per_kernel = {}
+    for _ in range(max(3, min(args.steps, 10))):
+        flush.zero_()
+        step_device()
+        for name, ms in ctx.timing_report():
+            per_kernel.setdefault(name.split("<")[0].strip("()"), []).append(ms)
+    ctx.set_timing(False)
+    reps = max(3, min(args.steps, 10))
+    kern_ms = {k: float(np.sum(v)) / reps for k, v in per_kernel.items()}   # per step, summed over the launches of a step
+    torch.cuda.synchronize()
+    d = res["disp"].cpu().numpy()
+    inner = (slice(H // 3 + 40, 2 * H // 3 - 40), slice(W // 3 + 40, 2 * W // 3 - 40)) if hier else (slice(16, -16), slice(16, W - D))
+    accuracy = float((d[inner] == gt[inner]).mean())
+    if rank == 0:
+        peak, peak_src = read_peaks()
+        units = cells * (1 if hier else world)   # c4: one frame in total (strong scaling); c3: one pair per rank
+        line = {"metric": metric, "value": units * args.steps / (ms_dev * 1e-3) / 1e9, "unit": "Gdisp/s", "n_gpus": world,
+                "steps": args.steps, "warmup": warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+                "scaling": "strong" if hier else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "e2e": {"value": units * args.steps / (ms_host * 1e-3) / 1e9, "unit": "Gdisp/s", "h2d_bytes_per_step": int(h2d),
+                        "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_host / args.steps},
+                "gpu_launches": int(launches), "clocks": clocks, "kernels_ms_per_step": {k: round(v, 4) for k, v in kern_ms.items()},
+                "ground_truth_agreement": accuracy}
+        config["l2"] = "512 MB memset between timed steps (outside the event pairs)"
+        dom = dom_key if dom_key in kern_ms else max(kern_ms, key=kern_ms.get)
+        n_launch = len(per_kernel[dom]) / reps
+        if dom_bytes:
+            ach = dom_bytes / (kern_ms[dom] / n_launch * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
+                                "ms_per_launch": kern_ms[dom] / n_launch}
+        else:
+            line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
+                                "traffic": None, "peak_source": peak_src, "ms_per_step": kern_ms[dom],
+                                "note": "instruction-bound window sums over L2-resident images; no HBM roofline applies"}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _ = cpu_reference_float(wl, 1, 0, budget_s=15.0)
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -135,6 +343,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if wl.get("kind") in ("zncc", "hier"):
+        return main_float(args, wl, rank, world, local_rank)
     warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     H, W, D = wl["H"], wl["W"], wl["D"]
     cells = H * W * D
