@@ -151,6 +151,170 @@ __global__ void __launch_bounds__(128) k_guided_cv(const Guided p) {
 	}
 }
 
+
+// hierarchical.h:116-148: the guide upsampled at global row gi, column j, in the reference's fp32 operation order
+__device__ __forceinline__ int guided_d0(const Guided& p, int gi, int j) {
+	const float v_pos = __fdiv_rn((float)(gi * (p.hg - 1)), (float)(p.H - 1));
+	int v0 = (int)floorf(v_pos), v1 = (int)ceilf(v_pos);
+	if (v0 == v1) v1 += 1;
+	if (v1 == p.hg) { v0 -= 1; v1 -= 1; }
+	const float h_pos = __fdiv_rn((float)(j * (p.wg - 1)), (float)(p.Ws - 1));
+	int h0 = (int)floorf(h_pos), h1 = (int)ceilf(h_pos);
+	if (h0 == h1) h1 += 1;
+	if (h1 == p.wg) { h0 -= 1; h1 -= 1; }
+	const float av = __fsub_rn(v_pos, (float)v0), bv = __fsub_rn((float)v1, v_pos);
+	const float ah = __fsub_rn(h_pos, (float)h0), bh = __fsub_rn((float)h1, h_pos);
+	const int64_t gr0 = (int64_t)(v0 - p.guide_row0) * p.g0, gr1 = (int64_t)(v1 - p.guide_row0) * p.g0;
+	float id = 0.f;
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, ah), (float)p.guide[gr1 + h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, ah), (float)p.guide[gr0 + h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, bh), (float)p.guide[gr1 + h0 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, bh), (float)p.guide[gr0 + h0 * p.g1]));
+	id = __fmul_rn(id, 2.f);
+	return p.sign * (int)roundf(id);
+}
+
+// Tiled form for windows up to 9 wide and upscale radii 1..2: a block owns 128 consecutive pixels of one row. The window
+// rows of the source (128 + 2hr columns) and of the target (the span of all candidate columns of the block, the guide being
+// smooth) are staged in shared memory; a thread then reads each target window row once into registers and feeds all
+// 4r+1 candidates from it (2hr+1 + 4r loads for (2hr+1)(4r+1) FMAs). Blocks whose candidates spread over more than
+// GT_SPREAD columns (disparity edges) take the per-pixel kernel's path through global memory instead.
+constexpr int GT_SPREAD = 96;
+
+template<int HR, int R>
+__global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
+	constexpr int HS = 2 * HR + 1, NC = 4 * R + 1, TN = HS + NC - 1;
+	constexpr int SW = 128 + 2 * HR, TW = 128 + 2 * HR + NC + GT_SPREAD;
+	extern __shared__ float gsm[];
+	__shared__ int s_min[4], s_max[4];
+	const int vs = 2 * p.vr + 1;
+	float* ssrc = gsm;                 // vs x SW
+	float* stgt = gsm + vs * SW;       // vs x TW
+	const int tx = threadIdx.x, jb = blockIdx.x * 128, j = jb + tx, io = blockIdx.y;
+	const int gi = p.out_row0 + io, i = gi - p.img_row0;
+	const bool live = j < p.Ws;
+	const int d0 = live ? guided_d0(p, gi, j) : 0;
+	const int jt0 = j + d0 - 2 * R;
+	// span of the block's candidate columns
+	int lo = live ? jt0 : 0x7fffffff, hi = live ? jt0 : -0x7fffffff;
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+	if ((tx & 31) == 0) { s_min[tx >> 5] = lo; s_max[tx >> 5] = hi; }
+	__syncthreads();
+	const int tmin = min(min(s_min[0], s_min[1]), min(s_min[2], s_min[3])), tmax = max(max(s_max[0], s_max[1]), max(s_max[2], s_max[3]));
+	// columns outside [-(pad_left-HR), ...) are not in the padded planes: clamp the staged range to what exists; candidates
+	// outside the target image are masked below and never read the tile
+	const int t_first = max(tmin, -HR - 8);
+	const bool tiled = (tmax - t_first) <= GT_SPREAD + 128 - 1 && t_first + TW - HR < (int)p.pitch - p.pad_left - 8;
+	for (int n = tx; n < vs * SW; n += 128) {
+		const int k = n / SW, c = n - k * SW;
+		ssrc[n] = __ldg(p.ps + (int64_t)(i - p.vr + k) * p.pitch + pad_col_off(p.pad_left + jb - HR + c, p.half));
+	}
+	if (tiled)
+		for (int n = tx; n < vs * TW; n += 128) {
+			const int k = n / TW, c = n - k * TW;
+			stgt[n] = __ldg(p.pt + (int64_t)(i - p.vr + k) * p.pitch + pad_col_off(p.pad_left + t_first - HR + c, p.half));
+		}
+	__syncthreads();
+	if (!live) return;
+	const float F = (float)(HS * vs);
+	const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
+	const float ms = p.Ms[os], ns = p.Ns[os];
+	const bool sub_mean = p.op != BOX_PROD && p.zero_mean;
+	float acc[NC], mtv[NC], zacc = 0.f;   // zacc: the cost against the all-zero target vector
+#pragma unroll
+	for (int e = 0; e < NC; e++) {
+		acc[e] = 0.f; mtv[e] = 0.f;
+		const int jt = jt0 + e;
+		if (sub_mean && jt >= 0 && jt < p.Wt) mtv[e] = p.Mt[(int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half)];
+	}
+	for (int k = 0; k < vs; k++) {
+		float t[TN];
+		if (tiled) {
+			// threads whose candidates all lie left of the staged range (hence outside the image, masked below) read column 0
+			const float* T = stgt + k * TW + max(jt0 - t_first, 0);
+#pragma unroll
+			for (int n = 0; n < TN; n++) t[n] = T[n];
+		} else {
+			const float* trow = p.pt + (int64_t)(i - p.vr + k) * p.pitch;
+#pragma unroll
+			for (int n = 0; n < TN; n++) {
+				const int X = jt0 - HR + n;   // may lie far outside the padded row when the guide points off the image
+				t[n] = (X >= -p.pad_left + 8 && X < (int)p.pitch - p.pad_left - 8) ? __ldg(trow + pad_col_off(p.pad_left + X, p.half)) : 0.f;
+			}
+		}
+		const float* S = ssrc + k * SW + tx;
+#pragma unroll
+		for (int l = 0; l < HS; l++) {
+			float sv = S[l];
+			if (sub_mean) sv -= ms;
+			if (p.op == BOX_SQ) zacc = fmaf(sv, sv, zacc);
+			else if (p.op == BOX_ABS) zacc += fabsf(sv);
+#pragma unroll
+			for (int e = 0; e < NC; e++) {
+				if (p.op == BOX_PROD) acc[e] = fmaf(sv, t[l + e], acc[e]);
+				else if (p.op == BOX_SQ) { const float q = sv - (t[l + e] - mtv[e]); acc[e] = fmaf(q, q, acc[e]); }
+				else acc[e] += fabsf(sv - (t[l + e] - mtv[e]));
+			}
+		}
+	}
+#pragma unroll
+	for (int e = 0; e < NC; e++) {
+		const int jt = jt0 + e;
+		const bool inside = jt >= 0 && jt < p.Wt;
+		float v;
+		if (p.op == BOX_PROD) {
+			v = 0.f;
+			if (inside) {
+				const int64_t ot = (int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half);
+				v = acc[e];
+				if (p.zero_mean) v = fmaf(-F * ms, p.Mt[ot], v);
+				if (p.normalized) { const float nt = p.Nt[ot]; v = (ns == 0.f || nt == 0.f) ? __int_as_float(0x7fc00000) : v / (ns * nt); }
+			} else if (p.normalized && ns == 0.f) v = __int_as_float(0x7fc00000);
+		} else v = inside ? acc[e] : zacc;
+		acc[e] = v;
+	}
+	float score = p.cost ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+	int best = R;   // index of the candidate at d0 (hierarchical.h: d_r starts at d0 and moves only on a strict improvement)
+	bool moved = false;
+#pragma unroll
+	for (int dd = 0; dd <= 2 * R; dd++) {
+		const float cmp = acc[R + dd];
+		if (p.cost ? (cmp < score) : (cmp > score)) { score = cmp; best = dd; moved = true; }
+	}
+	const int d_r = moved ? d0 + best - R : d0;
+	p.disp[io * p.d0s + j * p.d1s] = p.sign * d_r;
+	float* o = p.tcv + io * p.t0 + j * p.t1;
+#pragma unroll
+	for (int dd = 0; dd <= 2 * R; dd++) {
+		const int want = (d_r - d0) + p.sign * (dd - R) + 2 * R;
+		float cmp = 0.f;
+#pragma unroll
+		for (int e = 0; e < NC; e++) if (e == want) cmp = acc[e];
+		o[dd * p.t2] = cmp;
+	}
+}
+
+template<int HR, int R>
+static int32_t launch_guided_tile(stevi_ctx* c, const Guided& p, dim3 grid) {
+	const int vs = 2 * p.vr + 1;
+	const int smem = vs * ((128 + 2 * HR) + (128 + 2 * HR + 4 * R + 1 + GT_SPREAD)) * 4;
+	STEVI_CUDA(c, cudaFuncSetAttribute(k_guided_cv_tile<HR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+	STEVI_LAUNCH(c, (k_guided_cv_tile<HR, R>), grid, 128, smem, p);
+	return STEVI_OK;
+}
+
+static int32_t launch_guided(stevi_ctx* c, const Guided& p, dim3 grid) {
+	const int vs = 2 * p.vr + 1;
+	if (p.hr >= 1 && p.hr <= 4 && (p.r == 1 || p.r == 2) && vs * (2 * 128 + 4 * 4 + 9 + GT_SPREAD) * 4 <= 100 * 1024) {
+#define GT_CASE(HR_) case HR_: return p.r == 1 ? launch_guided_tile<HR_, 1>(c, p, grid) : launch_guided_tile<HR_, 2>(c, p, grid);
+		switch (p.hr) { GT_CASE(1) GT_CASE(2) GT_CASE(3) GT_CASE(4) }
+#undef GT_CASE
+	}
+	STEVI_LAUNCH(c, k_guided_cv, grid, 128, 0, p);
+	return STEVI_OK;
+}
+
 } // namespace
 
 namespace {
@@ -247,8 +411,7 @@ int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr
 	p.tcv = tcv.as<float>(); p.t0 = tcv.st[0]; p.t1 = tcv.st[1]; p.t2 = tcv.st[2];
 	p.disp = disp.as<int32_t>(); p.d0s = disp.st[0]; p.d1s = disp.st[1];
 	dim3 grid(cdiv(Ws, 128), n_rows);
-	STEVI_LAUNCH(c, k_guided_cv, grid, 128, 0, p);
-	return STEVI_OK;
+	return launch_guided(c, p, grid);
 }
 
 // hierarchical.h:235-314. h_radii / v_radii hold depth+1 entries, coarsest level first (like the reference's arrays).
