@@ -1,0 +1,49 @@
+// B200 facade of LibStevi's correlation/cross_correlations.h: unfoldBasedCostVolume :740-765 (the fused unfold ->
+// getFeatureVolumeForMatchFunc -> aggregateCost chain) and getFeatureVolumeForMatchFunc :645-722 on images.
+// Result layout like the reference's aggregateCost (:220): strides {W*D, 1, W}.
+#ifndef STEVI_B200_CORRELATION_CROSS_CORRELATIONS_H
+#define STEVI_B200_CORRELATION_CROSS_CORRELATIONS_H
+
+#include "./matching_costs.h"
+#include "./unfold.h"
+#include "./census.h"
+
+namespace StereoVision {
+namespace Correlation {
+
+template<matchingFunctions matchFunc, class T_L, class T_R, int nImDim = 2, dispDirection dDir = dispDirection::RightToLeft, typename TCV = float>
+Multidim::Array<TCV, 3> unfoldBasedCostVolume(Multidim::Array<T_L, nImDim> const& img_l, Multidim::Array<T_R, nImDim> const& img_r,
+											  uint8_t h_radius, uint8_t v_radius, disp_t disp_width) {
+	static_assert(MatchingFunctionTraits<matchFunc>::onB200, "matching function not covered by the B200 library");
+	static_assert(nImDim == 2, "multi-channel images: unfold them and use the feature-level entry points");
+	static_assert(std::is_same_v<T_L, T_R>, "both images must have the same element type");
+	static_assert(MatchingFunctionTraits<matchFunc>::isCensusBased
+				  ? (std::is_same_v<TCV, hamming_cv_t> || std::is_same_v<TCV, int32_t> || std::is_same_v<TCV, float>)
+				  : std::is_same_v<TCV, float>, "cost volume type not covered");
+	auto l_shape = img_l.shape();
+	auto r_shape = img_r.shape();
+	if (l_shape[0] != r_shape[0]) return Multidim::Array<TCV, 3>(0, 0, 0);   // :751-753
+	const int h = l_shape[0], w = dDir == dispDirection::RightToLeft ? r_shape[1] : l_shape[1];
+	Multidim::Array<TCV, 3> cv({h, w, disp_width}, {w * disp_width, 1, w});
+	stevi_array l = B200::describe(img_l), r = B200::describe(img_r), o = B200::describe(cv);
+	if (!B200::ok(stevi_cost_volume(B200::threadContext(), int(matchFunc), &l, &r, h_radius, v_radius, disp_width, int(dDir), STEVI_COMPAT, &o)))
+		return Multidim::Array<TCV, 3>(0, 0, 0);
+	return cv;
+}
+
+// getFeatureVolumeForMatchFunc<matchFunc>(unfold<T, T>(h_radius, v_radius, img)) for float images, strides {W*F, F, 1} (:427)
+template<matchingFunctions matchFunc>
+Multidim::Array<float, 3> featureVolumeForMatchFunc(Multidim::Array<float, 2> const& img, uint8_t h_radius, uint8_t v_radius) {
+	static_assert(MatchingFunctionTraits<matchFunc>::onB200 && !MatchingFunctionTraits<matchFunc>::isCensusBased, "use censusTransform2D");
+	auto sh = img.shape();
+	const int F = (2 * h_radius + 1) * (2 * v_radius + 1);
+	Multidim::Array<float, 3> out({sh[0], sh[1], F}, {sh[1] * F, F, 1});
+	stevi_array i = B200::describe(img), o = B200::describe(out);
+	if (!B200::ok(stevi_feature_volume(B200::threadContext(), int(matchFunc), &i, h_radius, v_radius, &o))) return Multidim::Array<float, 3>();
+	return out;
+}
+
+} // namespace Correlation
+} // namespace StereoVision
+
+#endif

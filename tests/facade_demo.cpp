@@ -1,0 +1,57 @@
+// Reads like the bodies of the reference's benchmarks (test/benchmarks/benchmarkCrossCorrelationAlgorithms.cpp:93-95,
+// :216-221, :289-293), written against the B200 facade headers. Prints one line per stage: checksum of the result.
+// Built by tests/test_facade.py with g++ (no nvcc): the facade is plain C++17 over the C ABI.
+#include <cstdio>
+#include <cmath>
+#include <StereoVision/correlation/cross_correlations.h>
+#include <StereoVision/correlation/sgm.h>
+#include <StereoVision/correlation/cost_based_refinement.h>
+#include <StereoVision/correlation/hierarchical.h>
+
+using namespace StereoVision;
+using namespace StereoVision::Correlation;
+
+static uint64_t mix(uint64_t z) { z += 0x9E3779B97F4A7C15ull; z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; return z ^ (z >> 31); }
+
+template<class A> double checksum(A const& a) {
+	double s = 0; auto sh = a.shape(); typename A::IndexBlock ix; ix.fill(0);
+	if (a.empty()) return -1;
+	size_t n = 1; for (auto v : sh) n *= v;
+	for (size_t k = 0; k < n; k++) { double v = double(a.valueUnchecked(ix)); if (std::isfinite(v)) s += v * double(1 + k % 7); ix.moveToNextIndex(sh); }
+	return s;
+}
+
+int main() {
+	const int h = 40, w = 64, D = 16;
+	Multidim::Array<uint8_t, 2> l8(h, w), r8(h, w);
+	Multidim::Array<float, 2> lf(h, w), rf(h, w);
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		uint8_t v = uint8_t(mix(uint64_t(i) * w + j) >> 56);
+		r8.at<Multidim::AccessCheck::Nocheck>(i, j) = v; rf.at<Multidim::AccessCheck::Nocheck>(i, j) = v / 255.f;
+		int jt = j + 5;
+		if (jt < w) { l8.at<Multidim::AccessCheck::Nocheck>(i, jt) = v; lf.at<Multidim::AccessCheck::Nocheck>(i, jt) = v / 255.f; }
+	}
+	for (int i = 0; i < h; i++) for (int j = 0; j < 5; j++) { uint8_t v = uint8_t(mix(1000003ull + uint64_t(i) * w + j) >> 56); l8.at<Multidim::AccessCheck::Nocheck>(i, j) = v; lf.at<Multidim::AccessCheck::Nocheck>(i, j) = v / 255.f; }
+
+	auto cv = unfoldBasedCostVolume<matchingFunctions::CENSUS, uint8_t, uint8_t, 2, dispDirection::RightToLeft, hamming_cv_t>(l8, r8, 4, 3, D);
+	auto sg = sgmCostVolume<8, dispExtractionStartegy::Cost>(cv, 10.f, 120.f, Margins(), 100.f);
+	auto idx = extractSelectedIndex<dispExtractionStartegy::Cost>(sg);
+	auto disp = selectedIndexToDisp<disp_t, dispDirection::RightToLeft>(idx, 0);
+	std::printf("census_cv %.0f\nsgm %.0f\ndisp %.0f\n", checksum(cv), checksum(sg), checksum(disp));
+
+	auto zn = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, rf, 2, 2, D);
+	auto zi = extractSelectedIndex<MatchingFunctionTraits<matchingFunctions::ZNCC>::extractionStrategy>(zn);
+	auto tcv = truncatedCostVolume(zn, zi, 2, 2, 1);
+	auto ref = refineDispCostInterpolation<InterpolationKernel::Parabola>(tcv, zi);
+	int good = 0, n = 0;
+	for (int i = 4; i < h - 4; i++) for (int j = 4; j < w - 24; j++) { n++; good += zi.valueUnchecked(i, j) == 5; }
+	std::printf("zncc_idx %.0f\nzncc_match %.3f\nrefined %.3f\n", checksum(zi), double(good) / n, checksum(ref));
+
+	auto hier = hiearchicalTruncatedCostVolume<matchingFunctions::ZNCC, 2>(lf, rf, 2, 2, D, 2);
+	std::printf("hier_disp %.0f\n", checksum(hier.disp_estimate));
+	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);
+	std::printf("mismatch_empty %d\n", int(bad.empty()));
+	auto even = refineDispCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 3>(h, w, 4), zi);
+	std::printf("even_depth_empty %d\n", int(even.empty()));
+	return 0;
+}
