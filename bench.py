@@ -313,8 +313,14 @@ def main_float(args, wl, rank, world, local_rank):
         n_launch = len(per_kernel[dom]) / reps
         if dom_bytes:
             ach = dom_bytes / (kern_ms[dom] / n_launch * 1e-3) / 1e9
+            traffic = None
+            try:  # measured DRAM bytes of that kernel per launch, from the committed ncu --set full capture
+                with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                    traffic = json.load(f).get(dom)
+            except Exception:
+                traffic = None
             line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
+                                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                                 "ms_per_launch": kern_ms[dom] / n_launch}
         else:
             line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,

@@ -181,7 +181,7 @@ __device__ __forceinline__ int guided_d0(const Guided& p, int gi, int j) {
 // GT_SPREAD columns (disparity edges) take the per-pixel kernel's path through global memory instead.
 constexpr int GT_SPREAD = 96;
 
-template<int HR, int R>
+template<int HR, int R, int OP>
 __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 	constexpr int HS = 2 * HR + 1, NC = 4 * R + 1, TN = HS + NC - 1;
 	constexpr int SW = 128 + 2 * HR, TW = 128 + 2 * HR + NC + GT_SPREAD;
@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 	const float F = (float)(HS * vs);
 	const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
 	const float ms = p.Ms[os], ns = p.Ns[os];
-	const bool sub_mean = p.op != BOX_PROD && p.zero_mean;
+	const bool sub_mean = OP != BOX_PROD && p.zero_mean;
 	float acc[NC], mtv[NC], zacc = 0.f;   // zacc: the cost against the all-zero target vector
 #pragma unroll
 	for (int e = 0; e < NC; e++) {
@@ -248,12 +248,12 @@ __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 		for (int l = 0; l < HS; l++) {
 			float sv = S[l];
 			if (sub_mean) sv -= ms;
-			if (p.op == BOX_SQ) zacc = fmaf(sv, sv, zacc);
-			else if (p.op == BOX_ABS) zacc += fabsf(sv);
+			if (OP == BOX_SQ) zacc = fmaf(sv, sv, zacc);
+			else if (OP == BOX_ABS) zacc += fabsf(sv);
 #pragma unroll
 			for (int e = 0; e < NC; e++) {
-				if (p.op == BOX_PROD) acc[e] = fmaf(sv, t[l + e], acc[e]);
-				else if (p.op == BOX_SQ) { const float q = sv - (t[l + e] - mtv[e]); acc[e] = fmaf(q, q, acc[e]); }
+				if (OP == BOX_PROD) acc[e] = fmaf(sv, t[l + e], acc[e]);
+				else if (OP == BOX_SQ) { const float q = sv - (t[l + e] - mtv[e]); acc[e] = fmaf(q, q, acc[e]); }
 				else acc[e] += fabsf(sv - (t[l + e] - mtv[e]));
 			}
 		}
@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 		const int jt = jt0 + e;
 		const bool inside = jt >= 0 && jt < p.Wt;
 		float v;
-		if (p.op == BOX_PROD) {
+		if (OP == BOX_PROD) {
 			v = 0.f;
 			if (inside) {
 				const int64_t ot = (int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half);
@@ -299,9 +299,12 @@ template<int HR, int R>
 static int32_t launch_guided_tile(stevi_ctx* c, const Guided& p, dim3 grid) {
 	const int vs = 2 * p.vr + 1;
 	const int smem = vs * ((128 + 2 * HR) + (128 + 2 * HR + 4 * R + 1 + GT_SPREAD)) * 4;
-	STEVI_CUDA(c, cudaFuncSetAttribute(k_guided_cv_tile<HR, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-	STEVI_LAUNCH(c, (k_guided_cv_tile<HR, R>), grid, 128, smem, p);
-	return STEVI_OK;
+#define GT_OP(OP_) { STEVI_CUDA(c, cudaFuncSetAttribute(k_guided_cv_tile<HR, R, OP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)); \
+		STEVI_LAUNCH(c, (k_guided_cv_tile<HR, R, OP_>), grid, 128, smem, p); return STEVI_OK; }
+	if (p.op == BOX_PROD) GT_OP(BOX_PROD)
+	if (p.op == BOX_SQ) GT_OP(BOX_SQ)
+	GT_OP(BOX_ABS)
+#undef GT_OP
 }
 
 static int32_t launch_guided(stevi_ctx* c, const Guided& p, dim3 grid) {
