@@ -342,9 +342,8 @@ int32_t stevi_local_matching_pipeline(stevi_ctx* c, int32_t mf, const stevi_arra
 	}
 	if (tcv_out) STEVI_TRY(st.out(tcv_out, vt, "tcv_out"));
 	if (D < 1) return fail(c, STEVI_E_ARG, "pipeline: disp_width must be positive");
-	STEVI_TRY(float_cv_dev(c, mf, vl, vr_, hr, vr, D, direction, vcv, false));
-	const bool score = mf == STEVI_MF_CC || mf == STEVI_MF_NCC || mf == STEVI_MF_ZCC || mf == STEVI_MF_ZNCC;
-	STEVI_TRY(wta_dev(c, vcv, score ? STEVI_SCORE : STEVI_COST, vidx));
+	// the winner-take-all rides on the cost-volume kernel: the 4*W*H*D-byte volume is written once and never read back
+	STEVI_TRY(float_cv_dev(c, mf, vl, vr_, hr, vr, D, direction, vcv, false, &vidx));
 	STEVI_TRY(refine_from_cv_dev(c, vcv, vidx, hr, vr, kernel, tcv_out ? &vt : nullptr, vo));
 	return st.finish();
 }

@@ -249,7 +249,7 @@ int32_t PaddedPair::stats(stevi_ctx* c, int which, int hr, int vr, int mf, int k
 }
 
 int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, int D, int direction, const View& out,
-					 bool force_direct) {
+					 bool force_direct, const View* wta_out) {
 	switch (mf) {
 	case STEVI_MF_CC: case STEVI_MF_NCC: case STEVI_MF_ZCC: case STEVI_MF_ZNCC:
 	case STEVI_MF_SSD: case STEVI_MF_ZSSD: case STEVI_MF_SAD: case STEVI_MF_ZSAD: break;
@@ -282,6 +282,7 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 		p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
 		dim3 grid(cdiv(Ws, 128), D, H);
 		STEVI_LAUNCH(c, k_cv_direct, grid, 128, 0, p);
+		if (wta_out) STEVI_TRY(wta_dev(c, out, op == BOX_PROD ? STEVI_SCORE : STEVI_COST, *wta_out));
 		return STEVI_OK;
 	}
 	STEVI_TRY(pp.stats(c, si, hr, vr, mf, op == BOX_PROD ? STATS_PROD_SRC : STATS_DIFF_SRC));
@@ -291,12 +292,21 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 	p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left; p.H = H; p.Ws = Ws; p.D = D; p.vr = vr; p.R = R; p.row_shift = ((c->row_origin % R) + R) % R;
 	p.Ff = (float)((2 * hr + 1) * (2 * vr + 1));
 	p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
+	p.keys = nullptr;
+	if (wta_out) {
+		if (wta_out->ndim != 2 || wta_out->dtype != STEVI_I32 || wta_out->shape[0] != H || wta_out->shape[1] != Ws)
+			return fail(c, STEVI_E_SHAPE, "cost_volume: winner map must be (%d,%d) i32", H, Ws);
+		STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &p.keys));
+		STEVI_CUDA(c, cudaMemsetAsync(p.keys, 0, (size_t)H * Ws * sizeof(unsigned long long), c->stream));
+	}
 	p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0;
 	switch (op) {
-	case BOX_PROD: return launch_cv_box_prod(c, p, hr, r2l ? 1 : -1);
-	case BOX_SQ: return launch_cv_box_sq(c, p, hr, r2l ? 1 : -1);
-	default: return launch_cv_box_abs(c, p, hr, r2l ? 1 : -1);
+	case BOX_PROD: STEVI_TRY(launch_cv_box_prod(c, p, hr, r2l ? 1 : -1)); break;
+	case BOX_SQ: STEVI_TRY(launch_cv_box_sq(c, p, hr, r2l ? 1 : -1)); break;
+	default: STEVI_TRY(launch_cv_box_abs(c, p, hr, r2l ? 1 : -1)); break;
 	}
+	if (wta_out) STEVI_TRY(wta_decode_max_keys_dev(c, p.keys, H, Ws, *wta_out));
+	return STEVI_OK;
 }
 
 } // namespace stevi

@@ -57,7 +57,17 @@ struct BoxParams {
 	float Ff;                           // number of features F as float
 	float* out; int64_t o0, o1, o2;
 	int vec_store;                      // o1 == 1, 16-byte aligned rows
+	// optional fused winner-take-all (extractSelectedIndex, correlation_base.h:427-464): dense [H][Ws] keys, cleared to 0
+	// beforehand; key = (order-preserving bits of the score, negated for costs) << 32 | d, merged with atomicMax, so equal
+	// values resolve to the larger d = the reference's `>=` / `<=` (last extremum wins, Q5); a NaN at d = 0 "sticks"
+	// (:440-452: no later comparison is true) and is encoded as the largest key
+	unsigned long long* keys;
 };
+
+__device__ __forceinline__ unsigned wta_order_bits(float v) {
+	const unsigned u = __float_as_uint(v);
+	return (u >> 31) ? ~u : (u | 0x80000000u);
+}
 
 // NU consecutive units starting at a unit whose offset is offA (the next one is at offB, then offA+4, offB+4, ...)
 template<int NU> __device__ __forceinline__ void load_units(float (&dst)[4 * NU], const float* __restrict__ row, int offA, int offB) {
@@ -135,13 +145,19 @@ __device__ __forceinline__ void box_accum_row(float (&V)[4][NV], const float* __
 	}
 }
 
-template<int OP, int HR, int SIGN>
+// winner keys of one row, [d group][column slot]: slot = k * BOX_KEY_PITCH + cg for column jb + 8*cg + k, so that both the
+// per-thread writes (fixed k, consecutive cg) and the per-column reads (consecutive columns) are bank-conflict free
+constexpr int BOX_KEY_PITCH = 18;
+constexpr int BOX_KEY_ROW = 8 * BOX_KEY_PITCH;
+
+template<int OP, int HR, int SIGN, bool WTA>
 __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const BoxParams p) {
 	static_assert(HR >= 1 && HR <= 4, "window half-width");
 	constexpr int NV = 16;                  // V columns j0-4 .. j0+11
 	constexpr int LH = 4;                   // left halo
 	extern __shared__ __align__(128) float smem[];
 	__shared__ uint64_t bar_img, bar_st[BOX_STAT_SLOTS];
+	__shared__ unsigned long long kb[WTA ? 2 * 8 * BOX_KEY_ROW : 1];   // double-buffered: row i is merged while row i+1 is computed
 	float* stat_ring = smem;                                  // BOX_STAT_SLOTS rows of per-pixel statistics
 	float* tile = smem + BOX_STAT_SLOTS * BOX_STAT_FLOATS;    // the band of image rows
 	const int cg = threadIdx.x & 15, dg = threadIdx.x >> 4;
@@ -214,6 +230,20 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 	for (int q = 0; q < 4; q++)
 #pragma unroll
 		for (int c = 0; c < NV; c++) V[q][c] = 0.f;
+	// merge the 8 disparity groups' winners of one column and publish them: one 64-bit atomicMax per column, row and block
+	const int kslot = (threadIdx.x & 7) * BOX_KEY_PITCH + (threadIdx.x >> 3);
+	auto merge_keys = [&](int row, int buf) {
+		if (jb + (int)threadIdx.x >= p.Ws) return;
+		const unsigned long long* src = kb + buf * 8 * BOX_KEY_ROW + kslot;
+		unsigned long long key = src[0];
+#pragma unroll
+		for (int g = 1; g < 8; g++) { const unsigned long long o = src[g * BOX_KEY_ROW]; key = o > key ? o : key; }
+		if (key) atomicMax(p.keys + (int64_t)row * p.Ws + jb + threadIdx.x, key);
+	};
+	if (WTA && !live) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) { kb[dg * BOX_KEY_ROW + k * BOX_KEY_PITCH + cg] = 0; kb[(8 + dg) * BOX_KEY_ROW + k * BOX_KEY_PITCH + cg] = 0; }
+	}
 	mbar_wait(&bar_img, 0);
 	if (live)
 		for (int r = 0; r <= 2 * p.vr; r++)
@@ -223,6 +253,7 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 		// every warp has finished row i-1, so its ring slot can take row i + BOX_STAT_SLOTS - 1
 		__syncthreads();
 		if (threadIdx.x < 32 && i + BOX_STAT_SLOTS - 1 < i_end) issue_stats(i + BOX_STAT_SLOTS - 1, (n + BOX_STAT_SLOTS - 1) % BOX_STAT_SLOTS);
+		if (WTA && n > 0) merge_keys(i - 1, (n - 1) & 1);
 		if (!live) continue;
 		if (n > 0) {
 			box_accum_row<OP, NV, SIGN, true>(V, tile + (n + 2 * p.vr) * BOX_ROW_FLOATS, sA, sB, tA, tB);
@@ -243,6 +274,11 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 		const float as[8] = {as0.x, as0.y, as0.z, as0.w, as1.x, as1.y, as1.z, as1.w};
 		const float bs[8] = {bs0.x, bs0.y, bs0.z, bs0.w, bs1.x, bs1.y, bs1.z, bs1.w};
 		const float bt[12] = {bt0.x, bt0.y, bt0.z, bt0.w, bt1.x, bt1.y, bt1.z, bt1.w, bt2.x, bt2.y, bt2.z, bt2.w};
+		float bestv[8];
+		int bestq[8];
+		unsigned nan0 = 0;
+#pragma unroll
+		for (int k = 0; k < 8; k++) { bestv[k] = OP == BOX_PROD ? __int_as_float(0xff800000) : __int_as_float(0x7f800000); bestq[k] = -1; }
 #pragma unroll
 		for (int q = 0; q < 4; q++) {
 			if (d0 + q >= p.D) break;
@@ -266,6 +302,10 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 					v = bt[ti] != 0.f ? h : bs[k];
 				}
 				o[k] = v;
+				if (WTA) {
+					if (OP == BOX_PROD ? (v >= bestv[k]) : (v <= bestv[k])) { bestv[k] = v; bestq[k] = q; }
+					if (q == 0 && d0 == 0 && v != v) nan0 |= 1u << k;
+				}
 			}
 			float* dst = p.out + (int64_t)i * p.o0 + (int64_t)(d0 + q) * p.o2;
 			if (p.vec_store && j0 + 8 <= p.Ws) {
@@ -277,19 +317,41 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 					if (j0 + k < p.Ws) p.out[(int64_t)i * p.o0 + (int64_t)(j0 + k) * p.o1 + (int64_t)(d0 + q) * p.o2] = o[k];
 			}
 		}
+		if (WTA) {
+			unsigned long long* dstk = kb + ((n & 1) * 8 + dg) * BOX_KEY_ROW + cg;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				unsigned long long key = 0;
+				// + 0.f: -0 -> +0, the reference's comparisons see them as equal
+				if (bestq[k] >= 0)
+					key = ((unsigned long long)wta_order_bits((OP == BOX_PROD ? bestv[k] : -bestv[k]) + 0.f) << 32) | (unsigned)(d0 + bestq[k]);
+				if ((nan0 >> k) & 1u) key = 0xFFFFFFFF00000000ull;
+				dstk[k * BOX_KEY_PITCH] = key;
+			}
+		}
+	}
+	if (WTA) {
+		__syncthreads();
+		merge_keys(i_end - 1, (i_end - 1 - i0) & 1);
 	}
 }
 
 template<int OP, int HR>
 static int32_t launch_cv_box_hr(stevi_ctx* c, const BoxParams& p, int sign, dim3 grid) {
 	const int smem = (p.R + 2 * p.vr) * BOX_ROW_FLOATS * 4 + BOX_STAT_SLOTS * BOX_STAT_FLOATS * 4;
+#define STEVI_BOX_LAUNCH(S, W)                                                                                                     \
+	do {                                                                                                                           \
+		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, S, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_SMEM_MAX));    \
+		STEVI_LAUNCH(c, (k_cv_box<OP, HR, S, W>), grid, BOX_THREADS, smem, p);                                                     \
+	} while (0)
 	if (sign > 0) {
-		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_SMEM_MAX));
-		STEVI_LAUNCH(c, (k_cv_box<OP, HR, 1>), grid, BOX_THREADS, smem, p);
+		if (p.keys) STEVI_BOX_LAUNCH(1, true);
+		else STEVI_BOX_LAUNCH(1, false);
 	} else {
-		STEVI_CUDA(c, cudaFuncSetAttribute(k_cv_box<OP, HR, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BOX_SMEM_MAX));
-		STEVI_LAUNCH(c, (k_cv_box<OP, HR, -1>), grid, BOX_THREADS, smem, p);
+		if (p.keys) STEVI_BOX_LAUNCH(-1, true);
+		else STEVI_BOX_LAUNCH(-1, false);
 	}
+#undef STEVI_BOX_LAUNCH
 	return STEVI_OK;
 }
 

@@ -30,8 +30,10 @@ struct PaddedPair {
 	int32_t stats(stevi_ctx* c, int which, int hr, int vr, int mf, int kind);
 };
 // unfoldBasedCostVolume for CC/NCC/ZCC/ZNCC/SSD/ZSSD/SAD/ZSAD, out (H,Wsource,D) f32
+// wta_out (optional, (H,Wsource) i32): extractSelectedIndex of the volume with the function's own strategy, fused into the
+// cost-volume kernel (the volume is not read back)
 int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, int D, int direction, const View& out,
-					 bool force_direct);
+					 bool force_direct, const View* wta_out = nullptr);
 
 // sgm.cu
 // optional fused winner-take-all of the aggregated volume: out(i,j) = sign * argmin_d + offset (selectedIndexToDisp folded in)
@@ -42,6 +44,8 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 
 // wta.cu
 int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);
+// keys: dense [H][W], (order bits << 32 | d) merged with atomicMax, 0 = never written -> index 0
+int32_t wta_decode_max_keys_dev(stevi_ctx* c, const unsigned long long* keys, int H, int W, const View& out);
 int32_t index_to_disp_dev(stevi_ctx* c, const View& idx, int direction, int offset, const View& out);
 
 

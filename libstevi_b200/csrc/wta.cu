@@ -152,6 +152,20 @@ int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out) {
 	}
 }
 
+__global__ void __launch_bounds__(256) k_wta_decode_max_keys(const unsigned long long* __restrict__ keys, int H, int W,
+															 int32_t* __restrict__ out, int64_t o0, int64_t o1) {
+	const int j = blockIdx.x * 256 + threadIdx.x, i = blockIdx.y;
+	if (j >= W) return;
+	out[i * o0 + j * o1] = (int32_t)(unsigned)(keys[(int64_t)i * W + j] & 0xffffffffull);
+}
+
+int32_t wta_decode_max_keys_dev(stevi_ctx* c, const unsigned long long* keys, int H, int W, const View& out) {
+	if (H == 0 || W == 0) return STEVI_OK;
+	dim3 grid(cdiv(W, 256), H);
+	STEVI_LAUNCH(c, k_wta_decode_max_keys, grid, 256, 0, keys, H, W, out.as<int32_t>(), out.st[0], out.st[1]);
+	return STEVI_OK;
+}
+
 __global__ void k_index_to_disp(const int32_t* __restrict__ idx, int64_t s0, int64_t s1, int H, int W, int sign, int offset,
 								int32_t* __restrict__ out, int64_t o0, int64_t o1) {
 	const int j = blockIdx.x * blockDim.x + threadIdx.x;
