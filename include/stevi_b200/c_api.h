@@ -89,6 +89,12 @@ STEVI_API void* stevi_ctx_stream(stevi_ctx* ctx);
  * passed to the following calls. It only anchors the kernels' internal row blocking (the float cost volumes keep running
  * window sums per block of 32 rows), so that a band gives bit-identical rows to the whole-frame call. Default 0. */
 STEVI_API int32_t stevi_ctx_set_row_origin(stevi_ctx* ctx, int32_t global_row_of_row0);
+/* Streaming many pairs from host memory: with deferred host completion on, a call whose operands live in host memory
+ * enqueues its host->device copies, kernels and device->host copies on the ctx stream and RETURNS WITHOUT WAITING; the
+ * host buffers (page-locked, or the copies do not overlap) must stay alive and untouched, and the results are valid only
+ * after stevi_ctx_synchronize. One ctx (own stream, own workspace) per pair in flight lets the copies of one pair overlap
+ * the kernels of another. Default off: calls with host operands return with their results in place. */
+STEVI_API int32_t stevi_ctx_set_deferred_host(stevi_ctx* ctx, int32_t enable);
 STEVI_API int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
 STEVI_API const char* stevi_last_error(stevi_ctx* ctx);
 /* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */

@@ -134,6 +134,16 @@ class Context:
     def synchronize(self):
         self.check(lib.stevi_ctx_synchronize(self._h))
 
+    def set_deferred_host(self, enable):
+        """Calls with host operands enqueue their copies and return without waiting; results are valid after
+        ``synchronize()`` (see stevi_ctx_set_deferred_host)."""
+        self.check(lib.stevi_ctx_set_deferred_host(self._h, 1 if enable else 0))
+
+    @property
+    def stream(self):
+        """The ctx's cudaStream_t as an integer."""
+        return lib.stevi_ctx_stream(self._h) or 0
+
     def set_row_origin(self, row):
         """Global frame row of row 0 of the images passed next (row-band runs; see stevi_ctx_set_row_origin)."""
         self.check(lib.stevi_ctx_set_row_origin(self._h, int(row)))
@@ -157,6 +167,51 @@ class Context:
     @property
     def handle(self):
         return self._h
+
+
+class HostPairStream:
+    """Keeps ``depth`` stereo pairs in flight from page-locked host memory: slot k has its own Context (own stream, own
+    workspace) with deferred host completion, so the host->device copy of one pair, the kernels of another and the
+    device->host copy of a third overlap. The reference processes one pair per call on the host cores
+    (benchmarkCostVolumeWorkflow.cpp:175-260 loops over pairs); this is the same loop with the calls left in flight.
+
+        stream = HostPairStream(depth=3)
+        for k, (left, right) in enumerate(pairs):        # pinned numpy arrays
+            ctx = stream.acquire()                        # waits for the pair that used this slot `depth` calls ago
+            censusSgmPipeline(left, right, ..., out=results[k % 3], ctx=ctx)
+        stream.drain()
+    """
+
+    def __init__(self, depth=3, device=0):
+        if depth < 1:
+            raise ValueError("depth must be positive")
+        self.slots = [Context(device) for _ in range(depth)]
+        for c in self.slots:
+            c.set_deferred_host(True)
+        self._next = 0
+
+    @property
+    def slot(self):
+        """Index of the slot the next ``acquire`` hands out (callers key their result buffers on it)."""
+        return self._next
+
+    def acquire(self):
+        ctx = self.slots[self._next]
+        self._next = (self._next + 1) % len(self.slots)
+        ctx.synchronize()
+        return ctx
+
+    def drain(self):
+        for c in self.slots:
+            c.synchronize()
+
+    @property
+    def launches(self):
+        return sum(c.launches for c in self.slots)
+
+    def close(self):
+        for c in self.slots:
+            c.close()
 
 
 _default_ctx = {}

@@ -18,6 +18,7 @@ struct stevi_ctx {
 	std::string err;
 	int64_t launches = 0;
 	int sm_count = 148;
+	bool deferred_host = false; // stevi_ctx_set_deferred_host: calls with host operands do not wait for their copies
 	int row_origin = 0; // global row of row 0 of the images handed to the next calls (stevi_ctx_set_row_origin)
 	// grow-only bump arena; reset at the start of every API call (coalesced into one block when it had to grow)
 	struct Block { char* p; size_t cap; };

@@ -113,7 +113,7 @@ int32_t Stager::finish() {
 	for (auto& b : back_)
 		if (b.bytes) STEVI_CUDA(c_, cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, c_->stream));
 	back_.clear();
-	if (any_host_) STEVI_CUDA(c_, cudaStreamSynchronize(c_->stream));
+	if (any_host_ && !c_->deferred_host) STEVI_CUDA(c_, cudaStreamSynchronize(c_->stream));
 	return STEVI_OK;
 }
 
@@ -172,6 +172,12 @@ int32_t stevi_ctx_set_stream(stevi_ctx* c, void* stream) {
 		STEVI_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
 		c->own_stream = true;
 	}
+	return STEVI_OK;
+}
+
+int32_t stevi_ctx_set_deferred_host(stevi_ctx* c, int32_t enable) {
+	if (!c) return STEVI_E_ARG;
+	c->deferred_host = enable != 0;
 	return STEVI_OK;
 }
 
