@@ -296,19 +296,42 @@ int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stev
 		v.st[0] = (int64_t)Ws * D; v.st[1] = 1; v.st[2] = Ws;
 		return STEVI_OK;
 	};
-	if (cv_out) STEVI_TRY(st.out(cv_out, vcv, "cv_out")); else STEVI_TRY(workspace_volume(STEVI_U16, vcv));
-	if (sgm_out) STEVI_TRY(st.out(sgm_out, vs, "sgm_out")); else STEVI_TRY(workspace_volume(STEVI_F32, vs));
-	if (vcv.dtype != STEVI_U16) return fail(c, STEVI_E_DTYPE, "pipeline: cv_out must be u16 (hamming_cv_t)");
 	stevi_margins mg = margins ? *margins : stevi_margins{0, 0, 0, 0};
 	const bool pout_int = Pout == rintf(Pout) && fabsf(Pout) <= 1.0e6f;
 	const bool collapse = semantics == STEVI_COMPAT && pout_int;
+	if (vd.ndim != 2 || vd.dtype != STEVI_I32 || vd.shape[0] != H || vd.shape[1] != Ws) return fail(c, STEVI_E_SHAPE, "pipeline: disp must be (H,W) i32");
+	// the WTA rides on the last SGM pass and selectedIndexToDisp (correlation_base.h:511-532) is folded into its output
+	WtaSink sink{vd, direction == STEVI_RIGHT_TO_LEFT ? 1 : -1, 0};
+	const int max_cost = 32 * census_n_written(hr, vr, semantics);
+	if (!cv_out && !sgm_out && collapse && D >= 1) {
+		// disparity only: neither volume is ever in memory; the Hamming costs are recomputed from the census words by the
+		// g-map pass and by the aggregation + winner-take-all pass
+		const int nw = census_n_words(hr, vr);
+		View cl, cr;
+		STEVI_TRY(alloc_census(c, vl.shape[0], vl.shape[1], nw, cl));
+		STEVI_TRY(alloc_census(c, vr_.shape[0], vr_.shape[1], nw, cr));
+		const View imgs[2] = {vl, vr_}, cens[2] = {cl, cr};
+		STEVI_TRY(census_transform_pair_dev(c, imgs, cens, 2, hr, vr, semantics));
+		HamSource hs{cl, cr, census_n_written(hr, vr, semantics), D, direction, semantics == STEVI_COMPAT};
+		const int32_t s = sgm_census_disparity_dev(c, hs, ndir, (int)Pout, mg, max_cost, sink);
+		if (s != STEVI_NOT_FUSED) {
+			STEVI_TRY(s);
+			return st.finish();
+		}
+	}
+	if (cv_out) STEVI_TRY(st.out(cv_out, vcv, "cv_out")); else STEVI_TRY(workspace_volume(STEVI_U16, vcv));
+	if (sgm_out) STEVI_TRY(st.out(sgm_out, vs, "sgm_out"));
+	else {
+		// not asked for: the aggregated costs are evaluated in registers by the winner-take-all pass and never stored
+		// (sgm_dev allocates a workspace volume only on the paths that need one)
+		vs.p = nullptr; vs.dtype = STEVI_F32; vs.ndim = 3;
+		vs.shape[0] = H; vs.shape[1] = Ws; vs.shape[2] = D;
+		vs.st[0] = (int64_t)Ws * D; vs.st[1] = 1; vs.st[2] = Ws;
+	}
+	if (vcv.dtype != STEVI_U16) return fail(c, STEVI_E_DTYPE, "pipeline: cv_out must be u16 (hamming_cv_t)");
 	int32_t* gmap = nullptr;
 	if (collapse) STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &gmap));
 	STEVI_TRY(census_cv_dev(c, vl, vr_, hr, vr, D, direction, semantics, vcv, gmap, (int)Pout));
-	const int max_cost = 32 * census_n_written(hr, vr, semantics);
-	// the WTA rides on the last SGM pass and selectedIndexToDisp (correlation_base.h:511-532) is folded into its output
-	WtaSink sink{vd, direction == STEVI_RIGHT_TO_LEFT ? 1 : -1, 0};
-	if (vd.ndim != 2 || vd.dtype != STEVI_I32 || vd.shape[0] != H || vd.shape[1] != Ws) return fail(c, STEVI_E_SHAPE, "pipeline: disp must be (H,W) i32");
 	STEVI_TRY(sgm_dev(c, vcv, ndir, STEVI_COST, P1, P2, Pout, mg, semantics, vs, gmap, max_cost, &sink));
 	return st.finish();
 }

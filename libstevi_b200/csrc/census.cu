@@ -64,6 +64,55 @@ __global__ void __launch_bounds__(256) k_census_transform(const CensusPair pr, i
 	for (int n = (ch < n_written ? ch : n_written); n < n_words; n++) o[n * so2] = 0u;
 }
 
+// Window fixed at compile time: the comparison index, its bit and its word are constants, so a comparison is a byte load,
+// a compare and one predicated OR (the generic kernel above spends more on the bookkeeping than on the comparisons).
+// C_END = first comparison index that is not looked at (COMPAT stops at the last full word, Q1).
+template<typename T, int HS, int VS, int C_END>
+__global__ void __launch_bounds__(256) k_census_window(const CensusPair pr) {
+	constexpr int HR = HS / 2, VR = VS / 2;
+	constexpr int TW = 32 + HS - 1, TH = 8 + VS - 1;
+	constexpr int NW = (HS * VS - 1) / 32 + 1;          // words of the output
+	constexpr int NWRITTEN = (C_END - 1 + 31) / 32;     // words that carry comparisons
+	__shared__ T tile[TW * TH];
+#define STEVI_SEL(f) (blockIdx.z ? pr.im[1].f : pr.im[0].f)
+	const T* __restrict__ img = static_cast<const T*>(STEVI_SEL(img));
+	const int64_t si = STEVI_SEL(si), sj = STEVI_SEL(sj), so0 = STEVI_SEL(so0), so1 = STEVI_SEL(so1), so2 = STEVI_SEL(so2);
+	const int H = STEVI_SEL(H), W = STEVI_SEL(W);
+	uint32_t* __restrict__ out = STEVI_SEL(out);
+#undef STEVI_SEL
+	if ((int)blockIdx.x * 32 >= W || (int)blockIdx.y * 8 >= H) return;
+	const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 8;
+	for (int t = threadIdx.y * 32 + threadIdx.x; t < TW * TH; t += 256) {
+		const int ty = t / TW, tx = t - ty * TW;
+		const int ii = i0 - VR + ty, jj = j0 - HR + tx;
+		T v = T(0);
+		if (ii >= 0 && ii < H && jj >= 0 && jj < W) v = img[ii * si + jj * sj];
+		tile[t] = v;
+	}
+	__syncthreads();
+	const int i = i0 + threadIdx.y, j = j0 + threadIdx.x;
+	if (i >= H || j >= W) return;
+	const T* base = tile + threadIdx.y * TW + threadIdx.x;
+	const T ref = base[0];
+	uint32_t word[NW];
+#pragma unroll
+	for (int n = 0; n < NW; n++) word[n] = 0u;
+#pragma unroll
+	for (int k = 0; k < VS; k++) {
+#pragma unroll
+		for (int l = 0; l < HS; l++) {
+			constexpr int dummy = 0; (void)dummy;
+			const int c = HS * k + l;          // compile-time after unrolling
+			if (c >= 1 && c < C_END) {
+				if (ref > base[k * TW + l]) word[(c - 1) / 32] |= 1u << ((c - 1) % 32);
+			}
+		}
+	}
+	uint32_t* o = out + i * so0 + j * so1;
+#pragma unroll
+	for (int n = 0; n < NW; n++) o[n * so2] = n < NWRITTEN ? word[n] : 0u;
+}
+
 int32_t census_n_words(int hr, int vr) { return ((2 * hr + 1) * (2 * vr + 1) - 1) / 32 + 1; }
 // number of words that can be non-zero
 int32_t census_n_written(int hr, int vr, int semantics) {
@@ -101,6 +150,20 @@ int32_t census_transform_pair_dev(stevi_ctx* c, const View* imgs, const View* ou
 	const int nw = census_n_words(hr, vr), nwr = census_n_written(hr, vr, semantics);
 	const int c_end = std::min(F, 1 + 32 * nwr);
 	dim3 block(32, 8), grid(cdiv(Wm, 32), cdiv(Hm, 8), n);
+	// common windows, both semantics: everything about the window is a compile-time constant
+#define STEVI_CENSUS_WINDOW(T, HS, VS)                                                                                  \
+	if (2 * hr + 1 == HS && 2 * vr + 1 == VS) {                                                                         \
+		constexpr int ncmp = HS * VS - 1;                                                                               \
+		if (semantics == STEVI_COMPAT) STEVI_LAUNCH(c, (k_census_window<T, HS, VS, 1 + 32 * (ncmp / 32)>), grid, block, 0, pr); \
+		else STEVI_LAUNCH(c, (k_census_window<T, HS, VS, HS * VS>), grid, block, 0, pr);                                \
+		return STEVI_OK;                                                                                                \
+	}
+#define STEVI_CENSUS_WINDOWS(T) \
+	STEVI_CENSUS_WINDOW(T, 9, 7) STEVI_CENSUS_WINDOW(T, 9, 9) STEVI_CENSUS_WINDOW(T, 7, 7) STEVI_CENSUS_WINDOW(T, 5, 5) STEVI_CENSUS_WINDOW(T, 7, 5)
+	if (imgs[0].dtype == STEVI_U8) { STEVI_CENSUS_WINDOWS(uint8_t) }
+	else { STEVI_CENSUS_WINDOWS(float) }
+#undef STEVI_CENSUS_WINDOWS
+#undef STEVI_CENSUS_WINDOW
 #define STEVI_CENSUS_LAUNCH(T, HS) STEVI_LAUNCH(c, (k_census_transform<T, HS>), grid, block, sm, pr, hr, vr, nw, nwr, c_end)
 #define STEVI_CENSUS_SWITCH(T) \
 	switch (2 * hr + 1) { \
@@ -140,6 +203,7 @@ struct HamParams {
 	int H, Ws, Wt, D, dchunk, n_words;
 	void* out; int64_t o0, o1, o2;            // (row, column, disparity) strides of the cost volume
 	int32_t* gmap; int pout;
+	const int32_t* T; const int32_t* R; unsigned long long* keys;   // MODE 2: path sums in, winner keys out
 	int round;                                // Q2: round target words through float
 	int P;                                    // pitch of one of the 8 interleaved shared-memory lanes
 };
@@ -172,7 +236,13 @@ template<> __device__ __forceinline__ void store8<float>(float* p, const uint32_
 // load per thread and disparity), and each disparity ends in one 16-byte store, so a warp writes 512 contiguous
 // bytes of the [H][D][W] volume. Target words of the row are staged once in shared memory, already rounded (Q2),
 // in 8 interleaved lanes so that the stride-8 accesses of a warp are bank-conflict free.
-template<int NW, int SIGN, typename TO, bool VEC, bool EMIT_G>
+//
+// MODE 0 stores the cost volume (and, with EMIT_G, the g map of the collapsed SGM on the way). The disparity-only
+// census+SGM pipeline never has the volume in memory and runs the kernel twice instead, the costs recomputed from the
+// census words both times: MODE 1 = g map only; MODE 2 = the aggregated costs S = (1+R)*C + R*pout*[j+d >= W] - T
+// (sgm.cu, collapsed evaluation) and their running arg-min (`<=`: last minimum wins, correlation_base.h:446), merged
+// over the disparity chunks through the same 64-bit keys as k_sgm_apply_rows.
+template<int NW, int SIGN, typename TO, bool VEC, bool EMIT_G, int MODE = 0>
 __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	extern __shared__ uint32_t sm[];
 	const int tid = threadIdx.x;
@@ -225,7 +295,18 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	TO* orow = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1 + (int64_t)d0 * p.o2;
 	// Pout only enters g where j + d reaches past the last column: threads that never get there (most of them) track
 	// the plain minimum of the costs and double it at the end
-	const bool edge = EMIT_G && (j + 7 + d0 + dn - 1 >= p.Ws);
+	const bool edge = (EMIT_G || MODE == 2) && (j + 7 + d0 + dn - 1 >= p.Ws);
+	int r1[8], rp[8], tneg[8], best[8], bd[8];
+	if (MODE == 2) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			const bool in = j + k < p.Ws;
+			const int rr = in ? __ldg(p.R + (int64_t)i * p.Ws + j + k) : 0;
+			r1[k] = 1 + rr; rp[k] = rr * p.pout;
+			tneg[k] = in ? -__ldg(p.T + (int64_t)i * p.Ws + j + k) : 0;
+			best[k] = 0x7fffffff; bd[k] = 0;
+		}
+	}
 	auto sweep = [&](auto edge_tag, auto full_tag) {
 		constexpr bool EDGE = decltype(edge_tag)::value, FULL = decltype(full_tag)::value;
 		TO* o = orow;
@@ -251,10 +332,21 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 							else gmin[k] = min(gmin[k], (int)cst[k]);
 						}
 					}
-					if (FULL) store8<TO>(o, cst);
-					else {
+					if (MODE == 2) {
+						const int d = d0 + 8 * gr + u;
 #pragma unroll
-						for (int k = 0; k < 8; k++) if (j + k < p.Ws) o[k * p.o1] = (TO)cst[k];
+						for (int k = 0; k < 8; k++) {
+							int sc = r1[k] * (int)cst[k] + tneg[k];
+							if (EDGE) sc += (j + k + d >= p.Ws) ? rp[k] : 0;
+							if (sc <= best[k]) { best[k] = sc; bd[k] = d; }
+						}
+					}
+					if (MODE == 0) {
+						if (FULL) store8<TO>(o, cst);
+						else {
+#pragma unroll
+							for (int k = 0; k < 8; k++) if (j + k < p.Ws) o[k * p.o1] = (TO)cst[k];
+						}
 					}
 				}
 				o += p.o2;
@@ -281,6 +373,13 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 		if (EMIT_G) {
 #pragma unroll
 			for (int k = 0; k < 8; k++) gmin[k] *= 2;
+		}
+	}
+	if (MODE == 2) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) if (j + k < p.Ws) {
+			const unsigned long long key = ((unsigned long long)((uint32_t)best[k] ^ 0x80000000u) << 32) | (0xffffffffu - (uint32_t)bd[k]);
+			atomicMin(p.keys + (int64_t)i * p.Ws + j + k, key);   // the host pre-filled the keys with ones
 		}
 	}
 	if (EMIT_G) {
@@ -327,14 +426,8 @@ static int32_t launch_rows(stevi_ctx* c, const HamParams& p, dim3 grid, size_t s
 	return STEVI_OK;
 }
 
-template<typename TO>
-static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
-	const bool rows_ok = p.o1 == 1 && p.n_words >= 1 && p.n_words <= 4 && p.D <= 8192;
-	if (!rows_ok) {
-		dim3 grid(cdiv(p.Ws, 256), p.H);
-		STEVI_LAUNCH(c, k_hamming_generic<TO>, grid, 256, 0, p, sign);
-		return STEVI_OK;
-	}
+// grid and shared-memory layout of k_hamming_rows
+static int32_t hamming_rows_plan(stevi_ctx* c, HamParams& p, dim3& grid, size_t& smem) {
 	const int xb = cdiv(p.Ws, 1024);
 	int dchunk = (p.D + 7) / 8 * 8;
 	// many short blocks (>= 8 waves of 7 resident blocks per SM) so that the last partial wave costs little
@@ -352,8 +445,22 @@ static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
 	int P = groups;
 	while (P % 32 != 4) P++;
 	p.P = P;
-	const size_t smem = (size_t)p.n_words * 8 * P * sizeof(uint32_t);
-	dim3 grid(xb, p.H, cdiv(p.D, dchunk));
+	smem = (size_t)p.n_words * 8 * P * sizeof(uint32_t);
+	grid = dim3(xb, p.H, cdiv(p.D, dchunk));
+	return STEVI_OK;
+}
+
+template<typename TO>
+static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
+	const bool rows_ok = p.o1 == 1 && p.n_words >= 1 && p.n_words <= 4 && p.D <= 8192;
+	if (!rows_ok) {
+		dim3 grid(cdiv(p.Ws, 256), p.H);
+		STEVI_LAUNCH(c, k_hamming_generic<TO>, grid, 256, 0, p, sign);
+		return STEVI_OK;
+	}
+	dim3 grid;
+	size_t smem = 0;
+	STEVI_TRY(hamming_rows_plan(c, p, grid, smem));
 	const size_t esz = sizeof(TO);
 	const bool vec = ((uintptr_t)p.out % 16 == 0) && ((p.o0 * esz) % 16 == 0) && ((p.o2 * esz) % 16 == 0);
 #define STEVI_HAM_CASE(NW) \
@@ -363,6 +470,60 @@ static int32_t hamming_typed(stevi_ctx* c, HamParams p, int sign) {
 	}
 #undef STEVI_HAM_CASE
 	return fail(c, STEVI_E_UNSUPPORTED, "hamming: unreachable");
+}
+
+static int32_t ham_params(stevi_ctx* c, const HamSource& h, HamParams& p) {
+	const View& fl = h.fl; const View& fr = h.fr;
+	if (fl.ndim != 3 || fr.ndim != 3 || fl.dtype != STEVI_U32 || fr.dtype != STEVI_U32)
+		return fail(c, STEVI_E_DTYPE, "hamming: features must be (H,W,n) u32");
+	if (fl.shape[0] != fr.shape[0] || fl.shape[2] != fr.shape[2])
+		return fail(c, STEVI_E_SHAPE, "hamming: feature volumes disagree (cross_correlations.h:209-211)");
+	const bool r2l = h.direction == STEVI_RIGHT_TO_LEFT;
+	const View& src = r2l ? fr : fl;
+	const View& tgt = r2l ? fl : fr;
+	p.src = src.as<uint32_t>(); p.s0 = src.st[0]; p.s1 = src.st[1]; p.s2 = src.st[2];
+	p.tgt = tgt.as<uint32_t>(); p.t0 = tgt.st[0]; p.t1 = tgt.st[1]; p.t2 = tgt.st[2];
+	p.H = src.shape[0]; p.Ws = src.shape[1]; p.Wt = tgt.shape[1]; p.D = h.D; p.dchunk = h.D;
+	p.n_words = std::min(h.n_cmp, src.shape[2]);
+	p.out = nullptr; p.o0 = p.o2 = 0; p.o1 = 1;
+	p.gmap = nullptr; p.pout = 0; p.T = p.R = nullptr; p.keys = nullptr; p.round = h.round ? 1 : 0; p.P = 0;
+	return STEVI_OK;
+}
+
+bool hamming_fused_capable(const HamSource& h) {
+	const int nw = std::min(h.n_cmp, h.fl.shape[2]);
+	return nw >= 1 && nw <= 4 && h.D >= 1 && h.D <= 8192 && h.fl.shape[0] >= 1 && h.fl.shape[0] <= 65535 && h.fl.shape[1] >= 1 && h.fr.shape[1] >= 1;
+}
+
+template<int MODE>
+static int32_t hamming_fused_launch(stevi_ctx* c, HamParams& p, int sign) {
+	dim3 grid;
+	size_t smem = 0;
+	STEVI_TRY(hamming_rows_plan(c, p, grid, smem));
+#define STEVI_HAM_CASE(NW)                                                                                         \
+	case NW:                                                                                                       \
+		if (sign > 0) STEVI_LAUNCH(c, (k_hamming_rows<NW, 1, uint16_t, true, MODE == 1, MODE>), grid, 128, smem, p);  \
+		else STEVI_LAUNCH(c, (k_hamming_rows<NW, -1, uint16_t, true, MODE == 1, MODE>), grid, 128, smem, p);          \
+		return STEVI_OK;
+	switch (p.n_words) {
+		STEVI_HAM_CASE(1) STEVI_HAM_CASE(2) STEVI_HAM_CASE(3) STEVI_HAM_CASE(4)
+	}
+#undef STEVI_HAM_CASE
+	return fail(c, STEVI_E_UNSUPPORTED, "hamming: unreachable");
+}
+
+int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int pout_i) {
+	HamParams p;
+	STEVI_TRY(ham_params(c, h, p));
+	p.gmap = gmap; p.pout = pout_i;
+	return hamming_fused_launch<1>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
+}
+
+int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, unsigned long long* keys) {
+	HamParams p;
+	STEVI_TRY(ham_params(c, h, p));
+	p.T = T; p.R = R; p.keys = keys; p.pout = pout_i;
+	return hamming_fused_launch<2>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
 }
 
 int32_t hamming_cv_dev(stevi_ctx* c, const View& fl, const View& fr, int n_cmp, int D, int direction,
@@ -382,6 +543,7 @@ int32_t hamming_cv_dev(stevi_ctx* c, const View& fl, const View& fr, int n_cmp, 
 	p.n_words = std::min(n_cmp, src.shape[2]);
 	p.out = out.p; p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
 	p.gmap = gmap; p.pout = pout_i; p.round = round_target ? 1 : 0; p.P = 0;
+	p.T = p.R = nullptr; p.keys = nullptr;
 	if (out.ndim != 3 || out.shape[0] != p.H || out.shape[1] != p.Ws || out.shape[2] != D)
 		return fail(c, STEVI_E_SHAPE, "hamming: out must be (%d,%d,%d)", p.H, p.Ws, D);
 	if (p.H == 0 || p.Ws == 0 || D == 0) return STEVI_OK;

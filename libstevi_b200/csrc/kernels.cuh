@@ -38,6 +38,16 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 // sgm.cu
 // optional fused winner-take-all of the aggregated volume: out(i,j) = sign * argmin_d + offset (selectedIndexToDisp folded in)
 struct WtaSink { View out; int sign; int offset; };
+// Hamming costs recomputed from census words instead of read from a cost volume (disparity-only census+SGM pipeline)
+struct HamSource { View fl, fr; int n_cmp, D, direction; bool round; };
+bool hamming_fused_capable(const HamSource& h);
+int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int pout_i);
+int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, unsigned long long* keys);
+// census -> SGM -> WTA with no volume in memory; STEVI_NOT_FUSED when the collapsed evaluation does not apply (the caller
+// then runs the materialised path)
+constexpr int32_t STEVI_NOT_FUSED = -1001;
+int32_t sgm_census_disparity_dev(stevi_ctx* c, const HamSource& h, int ndir, int pout, const stevi_margins& mg, int max_cost,
+								 const WtaSink& wta);
 int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
 				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
 				const WtaSink* wta);

@@ -126,8 +126,9 @@ __global__ void __launch_bounds__(256) k_sgm_gmap_generic(const uint16_t* __rest
 
 // Scalar recurrences m(p) = g(p) - m(prev) along every live line: T(p) += m(prev), R(p) += 1 per pass; integer atomics,
 // so the result does not depend on the schedule. Three kernels share the work:
-//   k_sgm_pathsum_sweep  vertical and diagonal directions: a thread per line, all threads of a warp on the same image
-//                        row at the same time, so every load and atomic of a warp touches one contiguous segment;
+//   k_sgm_pathsum_sweep  vertical and diagonal directions: the lanes of a warp sit on 32 adjacent lines at the same image
+//                        row (every load and atomic of a warp touches one contiguous segment), the warps of a block
+//                        on 32 row segments of those lines, stitched through the linearity of the recurrence;
 //   k_sgm_pathsum_rows   horizontal directions: a warp per row, 32 columns per step through a signed warp scan
 //                        (m_k = (-1)^k * sum_{t<=k} (-1)^t g_t);
 //   k_sgm_pathsum        the generic line walker below, kept for the eight extra directions of the 16-direction set.
@@ -177,8 +178,18 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum(const int32_t* __restrict__
 // number of times the reference walks a line, from which of its two start loops are live (sgm.h:329-354, Q4)
 __device__ __forceinline__ bool sgm_start_live(int start_pos, int corrected) { return start_pos == 1 || (start_pos == 2 && corrected); }
 
-__global__ void __launch_bounds__(128) k_sgm_pathsum_sweep(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
-														   int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+// Vertical and diagonal directions. The recurrence m_k = g_k - m_{k-1} is linear, m_k = sum_{t<=k} (-1)^(k-t) g_t, so a
+// line does not have to be walked by one thread: a block owns 32 adjacent lines (lanes) and splits the rows into
+// SWEEP_SEGS segments (warps). Phase A: every warp forms the alternating sum of its segment with a zero carry-in;
+// phase B: the carry into a segment is folded from the sums of the segments before it (shared memory);
+// phase C: the segment is replayed with the true carry and accumulates T += w*m_prev, R += w. The serial chain is one
+// segment long (34 rows at 1080p) instead of the image height; integer arithmetic, so the split changes nothing.
+constexpr int SWEEP_SEGS = 32;
+
+__global__ void __launch_bounds__(32 * SWEEP_SEGS) k_sgm_pathsum_sweep(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+																		int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+	__shared__ int seg_sum[SWEEP_SEGS][32];
+	__shared__ int seg_cnt[SWEEP_SEGS][32];
 	const int sweep_dirs[6] = {0, 1, 4, 5, 6, 7};
 	const int dir = sweep_dirs[blockIdx.y];
 	const int sv = c_sgm_steps[dir][0], sh = c_sgm_steps[dir][2];
@@ -187,9 +198,10 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_sweep(const int32_t* __rest
 	const int nrows = geom.H - geom.top - geom.bottom, ncols = geom.W - geom.left - geom.right;
 	if (nrows <= 0 || ncols <= 0 || (!col_live && !row_live)) return;
 	const int nlines = ncols + (sh != 0 ? nrows - 1 : 0);
-	const int t = blockIdx.x * 128 + threadIdx.x;
+	const int lane = threadIdx.x & 31, seg = threadIdx.x >> 5;
+	const int t = blockIdx.x * 32 + lane;
 	const int jlo = geom.left, jhi = geom.W - geom.right - 1;
-	// k counts rows in traversal order; the line sits on column j0 + sh*k
+	// k counts rows in traversal order; the line sits on column j0 + sh*k and lives on rows kf <= k < kl
 	int j0 = 0, kf = 0x7fffffff, kl = 0, w = 0;
 	if (t < nlines) {
 		j0 = jlo + t - (sh > 0 ? nrows - 1 : 0);
@@ -202,22 +214,48 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_sweep(const int32_t* __rest
 		} else w = row_live ? 1 : 0;
 		if (w == 0 || kf >= kl) { kf = 0x7fffffff; kl = 0; }
 	}
-	const int k_begin = __reduce_min_sync(0xffffffffu, kf), k_end = __reduce_max_sync(0xffffffffu, kl);
-	int m_prev = 0, mabs = 0;
-	for (int k0 = k_begin; k0 < k_end; k0 += 16) {
+	const int seg_len = (nrows + SWEEP_SEGS - 1) / SWEEP_SEGS;
+	const int ka = max(seg * seg_len, kf), kb = min((seg + 1) * seg_len, kl);   // this thread's rows of its line
+	const int k_lo = __reduce_min_sync(0xffffffffu, ka), k_hi = __reduce_max_sync(0xffffffffu, kb);
+	auto row_of = [&](int k) { return sv > 0 ? geom.top + k : geom.H - geom.bottom - 1 - k; };
+	// phase A: m at the end of the segment for a zero carry-in
+	int m = 0;
+	for (int k0 = k_lo; k0 < k_hi; k0 += 16) {
 		int gv[16];
 #pragma unroll
 		for (int u = 0; u < 16; u++) {
 			const int k = k0 + u;
-			const int i = sv > 0 ? geom.top + k : geom.H - geom.bottom - 1 - k;
-			gv[u] = (k >= kf && k < kl) ? __ldg(g + (int64_t)i * geom.W + j0 + sh * k) : 0;
+			gv[u] = (k >= ka && k < kb) ? __ldg(g + (int64_t)row_of(k) * geom.W + j0 + sh * k) : 0;
 		}
 #pragma unroll
 		for (int u = 0; u < 16; u++) {
 			const int k = k0 + u;
-			if (k >= kf && k < kl) {
-				const int i = sv > 0 ? geom.top + k : geom.H - geom.bottom - 1 - k;
-				const int64_t pos = (int64_t)i * geom.W + j0 + sh * k;
+			if (k >= ka && k < kb) m = gv[u] - m;
+		}
+	}
+	seg_sum[seg][lane] = m;
+	seg_cnt[seg][lane] = max(kb - ka, 0);
+	__syncthreads();
+	// phase B: carry into this segment = m at the end of the previous one, with the carries before it folded in
+	int carry = 0;
+	for (int s = 0; s < seg; s++) {
+		const int n = seg_cnt[s][lane];
+		carry = seg_sum[s][lane] + ((n & 1) ? -carry : carry);
+	}
+	// phase C: replay with the true carry
+	int m_prev = carry, mabs = 0;
+	for (int k0 = k_lo; k0 < k_hi; k0 += 16) {
+		int gv[16];
+#pragma unroll
+		for (int u = 0; u < 16; u++) {
+			const int k = k0 + u;
+			gv[u] = (k >= ka && k < kb) ? __ldg(g + (int64_t)row_of(k) * geom.W + j0 + sh * k) : 0;
+		}
+#pragma unroll
+		for (int u = 0; u < 16; u++) {
+			const int k = k0 + u;
+			if (k >= ka && k < kb) {
+				const int64_t pos = (int64_t)row_of(k) * geom.W + j0 + sh * k;
 				atomicAdd(T + pos, w * m_prev);
 				atomicAdd(R + pos, w);
 				m_prev = gv[u] - m_prev;
@@ -226,7 +264,7 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_sweep(const int32_t* __rest
 		}
 	}
 	mabs = __reduce_max_sync(0xffffffffu, mabs);
-	if ((threadIdx.x & 31) == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
+	if (lane == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
 }
 
 __global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
@@ -275,7 +313,8 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restr
 // consecutive columns; per disparity one 8-byte load of costs and one 16-byte store of floats. With WTA the running
 // arg-min (`<=`: last minimum wins, correlation_base.h:446) is kept along the way, so the aggregated volume is not read again.
 // blockIdx.z splits the disparity range so that the grid is many short blocks (no tail wave).
-template<bool WTA>
+// STORE = false: the caller only wants the winners (disparity-only pipeline): the same S is evaluated, nothing is stored.
+template<bool WTA, bool STORE>
 __global__ void __launch_bounds__(256) k_sgm_apply_rows(const uint16_t* __restrict__ cv, int64_t c0, int64_t cd,
 														float* __restrict__ S, int64_t s0, int64_t sd,
 														const int32_t* __restrict__ T, const int32_t* __restrict__ R,
@@ -323,7 +362,7 @@ __global__ void __launch_bounds__(256) k_sgm_apply_rows(const uint16_t* __restri
 					o[k] = (float)s;
 					if (WTA) { if (s <= best[k]) { best[k] = s; bd[k] = d; } }
 				}
-				__stcs(reinterpret_cast<float4*>(ps + d * sd), make_float4(o[0], o[1], o[2], o[3]));
+				if (STORE) __stcs(reinterpret_cast<float4*>(ps + d * sd), make_float4(o[0], o[1], o[2], o[3]));
 			}
 		}
 	}
@@ -378,9 +417,19 @@ static bool aligned16(const void* p, int64_t a, int64_t b, size_t esz) {
 	return ((uintptr_t)p % 16 == 0) && ((a * (int64_t)esz) % 16 == 0) && ((b * (int64_t)esz) % 16 == 0);
 }
 
-static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, const stevi_margins& mg, const View& out,
-							 const int32_t* gmap_ready, int max_cost_hint, const WtaSink* wta) {
-	const int H = cv.shape[0], W = cv.shape[1], D = cv.shape[2];
+// the aggregated volume a caller did not ask for (out.p == nullptr) only exists on the paths that cannot do without it
+static int32_t ensure_volume(stevi_ctx* c, View& out) {
+	if (out.p) return STEVI_OK;
+	float* p = nullptr;
+	STEVI_TRY(arena_alloc_t(c, (size_t)out.shape[0] * out.shape[1] * out.shape[2], &p));
+	out.p = p;
+	return STEVI_OK;
+}
+
+// Path sums of the collapsed evaluation from the g map: T(p) = sum over passes of m(prev), R(p) = number of passes.
+// STEVI_FALLBACK when the float arithmetic this replaces is not provably exact (magnitudes >= 2^24).
+static int32_t collapsed_sums(stevi_ctx* c, const int32_t* g, int H, int W, int ndir, int pout, const stevi_margins& mg,
+							  int max_cost_hint, int32_t** T_out, int32_t** R_out) {
 	const size_t npix = (size_t)H * W;
 	int32_t* scratch = nullptr; // [T | R | max_abs_m]
 	STEVI_TRY(arena_alloc_t(c, 2 * npix + 64, &scratch));
@@ -388,29 +437,11 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 	int32_t* R = scratch + npix;
 	int32_t* d_max = scratch + 2 * npix;
 	STEVI_CUDA(c, cudaMemsetAsync(scratch, 0, (2 * npix + 64) * sizeof(int32_t), c->stream));
-	const int32_t* g = gmap_ready;
-	const uint16_t* pc = cv.as<uint16_t>();
-	if (!g) {
-		int32_t* gbuf = nullptr;
-		STEVI_TRY(arena_alloc_t(c, npix, &gbuf));
-		bool done = false;
-		if (cv.st[1] == 1 || cv.st[0] == 1) {
-			const int b = cv.st[1] == 1 ? 1 : 0, a = 1 - b;
-			if (aligned16(pc, cv.st[a], cv.st[2], 2) && cv.shape[a] <= 65535) {
-				dim3 grid(cdiv(cv.shape[b], 1024), cv.shape[a]);
-				STEVI_LAUNCH(c, k_sgm_gmap_planes, grid, 128, 0, pc, cv.st[a], cv.st[2], cv.shape[a], cv.shape[b], D, W, b, pout, gbuf);
-				done = true;
-			}
-		}
-		if (!done)
-			STEVI_LAUNCH(c, k_sgm_gmap_generic, (unsigned)((npix + 7) / 8), 256, 0, pc, cv.st[0], cv.st[1], cv.st[2], H, W, D, pout, gbuf);
-		g = gbuf;
-	}
 	SgmGeom geom{H, W, mg.top, mg.bottom, mg.left, mg.right, 0};
 	{
 		const int nrows = H - mg.top - mg.bottom;
-		dim3 gsweep(cdiv(H + W, 128), ndir == 4 ? 2 : 6);
-		STEVI_LAUNCH(c, k_sgm_pathsum_sweep, gsweep, 128, 0, g, T, R, d_max, geom);
+		dim3 gsweep(cdiv(H + W, 32), ndir == 4 ? 2 : 6);
+		STEVI_LAUNCH(c, k_sgm_pathsum_sweep, gsweep, 32 * SWEEP_SEGS, 0, g, T, R, d_max, geom);
 		if (nrows > 0) {
 			dim3 grows(cdiv(nrows, 4), 2);
 			STEVI_LAUNCH(c, k_sgm_pathsum_rows, grows, 128, 0, g, T, R, d_max, geom);
@@ -431,9 +462,40 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 		STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
 		if ((1 + rmax) * max_c + rmax * apout + rmax * (long)h_max >= lim) return STEVI_FALLBACK;
 	}
+	*T_out = T;
+	*R_out = R;
+	return STEVI_OK;
+}
+
+static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, const stevi_margins& mg, View& out,
+							 const int32_t* gmap_ready, int max_cost_hint, const WtaSink* wta) {
+	const int H = cv.shape[0], W = cv.shape[1], D = cv.shape[2];
+	const size_t npix = (size_t)H * W;
+	const int32_t* g = gmap_ready;
+	const uint16_t* pc = cv.as<uint16_t>();
+	if (!g) {
+		int32_t* gbuf = nullptr;
+		STEVI_TRY(arena_alloc_t(c, npix, &gbuf));
+		bool done = false;
+		if (cv.st[1] == 1 || cv.st[0] == 1) {
+			const int b = cv.st[1] == 1 ? 1 : 0, a = 1 - b;
+			if (aligned16(pc, cv.st[a], cv.st[2], 2) && cv.shape[a] <= 65535) {
+				dim3 grid(cdiv(cv.shape[b], 1024), cv.shape[a]);
+				STEVI_LAUNCH(c, k_sgm_gmap_planes, grid, 128, 0, pc, cv.st[a], cv.st[2], cv.shape[a], cv.shape[b], D, W, b, pout, gbuf);
+				done = true;
+			}
+		}
+		if (!done)
+			STEVI_LAUNCH(c, k_sgm_gmap_generic, (unsigned)((npix + 7) / 8), 256, 0, pc, cv.st[0], cv.st[1], cv.st[2], H, W, D, pout, gbuf);
+		g = gbuf;
+	}
+	int32_t *T = nullptr, *R = nullptr;
+	STEVI_TRY(collapsed_sums(c, g, H, W, ndir, pout, mg, max_cost_hint, &T, &R));
+	const bool store = out.p != nullptr || !wta;
+	const bool rows = cv.st[1] == 1 && (W % 8) == 0 && aligned16(pc, cv.st[0], cv.st[2], 2) && H <= 65535 &&
+					  (!store || (out.st[1] == 1 && aligned16(out.p, out.st[0], out.st[2], 4)));
+	if (store || !rows) STEVI_TRY(ensure_volume(c, out));
 	float* ps = out.as<float>();
-	const bool rows = cv.st[1] == 1 && out.st[1] == 1 && (W % 8) == 0 && aligned16(pc, cv.st[0], cv.st[2], 2) &&
-					  aligned16(ps, out.st[0], out.st[2], 4) && H <= 65535;
 	if (rows) {
 		const int xb = cdiv(W, 1024);
 		// many short blocks: aim at >= 8 waves of 6 resident blocks per SM so the last partial wave costs little
@@ -445,11 +507,14 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 			unsigned long long* keys = nullptr;
 			STEVI_TRY(arena_alloc_t(c, npix, &keys));
 			STEVI_CUDA(c, cudaMemsetAsync(keys, 0xff, npix * sizeof(unsigned long long), c->stream));
-			STEVI_LAUNCH(c, k_sgm_apply_rows<true>, grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys);
+			if (store)
+				STEVI_LAUNCH(c, (k_sgm_apply_rows<true, true>), grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys);
+			else
+				STEVI_LAUNCH(c, (k_sgm_apply_rows<true, false>), grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys);
 			dim3 gdec(cdiv(W, 256), H);
 			STEVI_LAUNCH(c, k_wta_decode_keys, gdec, 256, 0, keys, H, W, wta->sign, wta->offset, wta->out.as<int32_t>(), wta->out.st[0], wta->out.st[1]);
 		} else
-			STEVI_LAUNCH(c, k_sgm_apply_rows<false>, grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
+			STEVI_LAUNCH(c, (k_sgm_apply_rows<false, true>), grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout,
 						 (unsigned long long*)nullptr);
 	} else {
 		dim3 grid(cdiv(W, 128), H);
@@ -460,12 +525,40 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 	return STEVI_OK;
 }
 
+int32_t sgm_census_disparity_dev(stevi_ctx* c, const HamSource& h, int ndir, int pout, const stevi_margins& mg, int max_cost,
+								 const WtaSink& wta) {
+	if (ndir != 4 && ndir != 8 && ndir != 16) return fail(c, STEVI_E_ARG, "sgm: n_directions must be 4, 8 or 16");
+	if (mg.left < 0 || mg.right < 0 || mg.top < 0 || mg.bottom < 0) return fail(c, STEVI_E_ARG, "sgm: negative margins");
+	if (!hamming_fused_capable(h)) return STEVI_NOT_FUSED;
+	const bool r2l = h.direction == STEVI_RIGHT_TO_LEFT;
+	const int H = h.fl.shape[0], W = r2l ? h.fr.shape[1] : h.fl.shape[1];
+	const size_t npix = (size_t)H * W;
+	// pass 1: g(p) = min_d (2*C + pout*[j+d >= W]); the costs live in registers only
+	int32_t* g = nullptr;
+	STEVI_TRY(arena_alloc_t(c, npix, &g));
+	STEVI_TRY(hamming_gmap_dev(c, h, g, pout));
+	int32_t *T = nullptr, *R = nullptr;
+	const int32_t s = collapsed_sums(c, g, H, W, ndir, pout, mg, max_cost, &T, &R);
+	if (s == STEVI_FALLBACK) return STEVI_NOT_FUSED;
+	STEVI_TRY(s);
+	// pass 2: the costs again, S = (1+R)*C + R*pout*[j+d >= W] - T and its arg-min
+	unsigned long long* keys = nullptr;
+	STEVI_TRY(arena_alloc_t(c, npix, &keys));
+	STEVI_CUDA(c, cudaMemsetAsync(keys, 0xff, npix * sizeof(unsigned long long), c->stream));
+	STEVI_TRY(hamming_sgm_wta_dev(c, h, T, R, pout, keys));
+	dim3 gdec(cdiv(W, 256), H);
+	STEVI_LAUNCH(c, k_wta_decode_keys, gdec, 256, 0, keys, H, W, wta.sign, wta.offset, wta.out.as<int32_t>(), wta.out.st[0], wta.out.st[1]);
+	return STEVI_OK;
+}
+
 int32_t sgm_general(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
 					const stevi_margins& mg, int semantics, const View& out);
 
 int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
-				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
+				const stevi_margins& mg, int semantics, const View& out_, const int32_t* gmap_ready, int max_cost_hint,
 				const WtaSink* wta) {
+	View out = out_;   // out.p == nullptr (pipeline callers that only want the winners): no aggregated volume unless a path needs one
+	if (!out.p && !wta) return fail(c, STEVI_E_ARG, "sgm: no output requested");
 	if (ndir != 4 && ndir != 8 && ndir != 16) return fail(c, STEVI_E_ARG, "sgm: n_directions must be 4, 8 or 16");
 	if (cv.ndim != 3 || (cv.dtype != STEVI_U16 && cv.dtype != STEVI_F32))
 		return fail(c, STEVI_E_DTYPE, "sgm: cost volume must be (H,W,D) u16 or f32");
@@ -480,6 +573,7 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 		int32_t s = sgm_collapsed(c, cv, ndir, (int)Pout, mg, out, gmap_ready, max_cost_hint, wta);
 		if (s != STEVI_FALLBACK) return s;
 	}
+	STEVI_TRY(ensure_volume(c, out));
 	STEVI_TRY(sgm_general(c, cv, ndir, strategy, P1, P2, Pout, mg, semantics, out));
 	if (wta) {
 		STEVI_TRY(wta_dev(c, out, strategy, wta->out));

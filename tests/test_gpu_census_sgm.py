@@ -173,6 +173,27 @@ def test_pipeline_matches_stages_and_oracle(api, ctx, oracle, h, w, D, ndir):
     assert np.array_equal(api.censusSgmPipeline(L, R, 4, 3, D, 10, 120, Pout=100, nDirections=ndir, ctx=ctx), odisp)
 
 
+@pytest.mark.parametrize("h,w,D,hr,vr,ndir,direction,margins,pout", [
+    (37, 83, 19, 4, 3, 8, 1, (0, 0, 0, 0), 100),     # ragged width and disparity count
+    (37, 83, 19, 4, 3, 8, 0, (0, 0, 0, 0), 100),     # left-to-right
+    (40, 1100, 70, 2, 2, 16, 1, (0, 0, 0, 0), 35),   # more than one 1024-column block, 16 directions (Q8-free subset)
+    (52, 96, 33, 3, 1, 4, 1, (3, 2, 5, 1), 100),     # margins
+    (30, 64, 8, 5, 4, 8, 1, (0, 0, 0, 0), -7),       # 11x9 window (3 census words, one written), negative Pout
+    (20, 40, 64, 1, 1, 8, 1, (0, 0, 0, 0), 100),     # disparity range wider than the image
+])
+def test_disparity_only_pipeline_equals_materialised(api, ctx, h, w, D, hr, vr, ndir, direction, margins, pout):
+    """The disparity-only call keeps no volume in memory (costs recomputed from the census words by the g-map pass and by
+    the aggregation + WTA pass); its map is the one of the call that materialises both volumes."""
+    L, R, _ = pair(h, w, 5 + h, d_max=0)
+    kw = dict(Pout=pout, nDirections=ndir, margins=margins, dDir=direction, ctx=ctx)
+    _, sg, want = api.censusSgmPipeline(L, R, hr, vr, D, 10, 120, return_volumes=True, **kw)
+    got = api.censusSgmPipeline(L, R, hr, vr, D, 10, 120, **kw)
+    assert np.array_equal(got, want)
+    # and it is the last row-wise minimum of the aggregated volume (Q5), folded into a disparity
+    idx = D - 1 - np.argmin(sg[:, :, ::-1], axis=2)
+    assert np.array_equal(got, idx if direction == 1 else -idx)
+
+
 def test_pipeline_device_operands(api, ctx, oracle):
     torch = pytest.importorskip("torch")
     L, R, _ = pair(64, 128, 77)

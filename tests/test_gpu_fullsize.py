@@ -38,6 +38,8 @@ def test_census_sgm_full_size(api, tctx, oracle, H, W, D, seed):
     assert torch.equal(sg, sg2)
     idx = api.extractSelectedIndex(sg2, api.COST, ctx=tctx)
     assert torch.equal(disp, api.selectedIndexToDisp(idx, ctx=tctx))
+    # (1b) the disparity-only call (aggregated costs evaluated in registers, never stored) picks the same winners
+    assert torch.equal(disp, api.censusSgmPipeline(dl, dr, 4, 3, D, 10, 120, 100, 8, ctx=tctx))
     # (2) the general recurrence kernel (float volume) reproduces the collapsed evaluation
     sg3 = api.sgmCostVolume(cv2.to(torch.float32), 10, 120, Pout=100, nDirections=8, ctx=tctx)
     assert torch.equal(sg, sg3)
