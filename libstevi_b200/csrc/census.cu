@@ -241,7 +241,9 @@ template<> __device__ __forceinline__ void store8<float>(float* p, const uint32_
 // census+SGM pipeline never has the volume in memory and runs the kernel twice instead, the costs recomputed from the
 // census words both times: MODE 1 = g map only; MODE 2 = the aggregated costs S = (1+R)*C + R*pout*[j+d >= W] - T
 // (sgm.cu, collapsed evaluation) and their running arg-min (`<=`: last minimum wins, correlation_base.h:446), merged
-// over the disparity chunks through the same 64-bit keys as k_sgm_apply_rows.
+// over the disparity chunks through the same 64-bit keys as k_sgm_apply_rows. MODE 3 is MODE 2 with the running arg-min
+// packed in one word, (S + T) * 8192 + (8191 - d), so that a cell costs one multiply-add and one min (the host picks it
+// when |S + T| < 2^17; D <= 8192 on this path; T is constant along d and re-enters at the end).
 template<int NW, int SIGN, typename TO, bool VEC, bool EMIT_G, int MODE = 0>
 __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	extern __shared__ uint32_t sm[];
@@ -295,9 +297,9 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	TO* orow = reinterpret_cast<TO*>(p.out) + i * p.o0 + j * p.o1 + (int64_t)d0 * p.o2;
 	// Pout only enters g where j + d reaches past the last column: threads that never get there (most of them) track
 	// the plain minimum of the costs and double it at the end
-	const bool edge = (EMIT_G || MODE == 2) && (j + 7 + d0 + dn - 1 >= p.Ws);
+	const bool edge = (EMIT_G || MODE >= 2) && (j + 7 + d0 + dn - 1 >= p.Ws);
 	int r1[8], rp[8], tneg[8], best[8], bd[8];
-	if (MODE == 2) {
+	if (MODE >= 2) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) {
 			const bool in = j + k < p.Ws;
@@ -305,6 +307,7 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 			r1[k] = 1 + rr; rp[k] = rr * p.pout;
 			tneg[k] = in ? -__ldg(p.T + (int64_t)i * p.Ws + j + k) : 0;
 			best[k] = 0x7fffffff; bd[k] = 0;
+			if (MODE == 3) { r1[k] <<= 13; rp[k] <<= 13; }
 		}
 	}
 	auto sweep = [&](auto edge_tag, auto full_tag) {
@@ -330,6 +333,15 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 						for (int k = 0; k < 8; k++) {
 							if (EDGE) gmin[k] = min(gmin[k], (int)(2 * cst[k]) + ((j + k + d >= p.Ws) ? p.pout : 0));
 							else gmin[k] = min(gmin[k], (int)cst[k]);
+						}
+					}
+					if (MODE == 3) {
+						const int d = d0 + 8 * gr + u, inv = 8191 - d;
+#pragma unroll
+						for (int k = 0; k < 8; k++) {
+							int key = r1[k] * (int)cst[k] + inv;
+							if (EDGE) key += (j + k + d >= p.Ws) ? rp[k] : 0;
+							best[k] = min(best[k], key);
 						}
 					}
 					if (MODE == 2) {
@@ -375,7 +387,11 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 			for (int k = 0; k < 8; k++) gmin[k] *= 2;
 		}
 	}
-	if (MODE == 2) {
+	if (MODE == 3) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) { bd[k] = 8191 - (best[k] & 8191); best[k] = (best[k] >> 13) + tneg[k]; }
+	}
+	if (MODE >= 2) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) if (j + k < p.Ws) {
 			const unsigned long long key = ((unsigned long long)((uint32_t)best[k] ^ 0x80000000u) << 32) | (0xffffffffu - (uint32_t)bd[k]);
@@ -519,11 +535,16 @@ int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int po
 	return hamming_fused_launch<1>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
 }
 
-int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, unsigned long long* keys) {
+int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, int r_max,
+							unsigned long long* keys) {
 	HamParams p;
 	STEVI_TRY(ham_params(c, h, p));
 	p.T = T; p.R = R; p.keys = keys; p.pout = pout_i;
-	return hamming_fused_launch<2>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
+	const int sign = h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1;
+	// (1+R)*C + R*pout with R <= r_max passes and C <= 32 bits per word
+	const long bound = (1L + r_max) * 32 * p.n_words + (long)r_max * labs((long)pout_i);
+	if (bound < (1L << 17)) return hamming_fused_launch<3>(c, p, sign);
+	return hamming_fused_launch<2>(c, p, sign);
 }
 
 int32_t hamming_cv_dev(stevi_ctx* c, const View& fl, const View& fr, int n_cmp, int D, int direction,

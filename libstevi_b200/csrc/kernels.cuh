@@ -42,7 +42,9 @@ struct WtaSink { View out; int sign; int offset; };
 struct HamSource { View fl, fr; int n_cmp, D, direction; bool round; };
 bool hamming_fused_capable(const HamSource& h);
 int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int pout_i);
-int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, unsigned long long* keys);
+// r_max: upper bound of R (number of passes over a pixel)
+int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, int r_max,
+							unsigned long long* keys);
 // census -> SGM -> WTA with no volume in memory; STEVI_NOT_FUSED when the collapsed evaluation does not apply (the caller
 // then runs the materialised path)
 constexpr int32_t STEVI_NOT_FUSED = -1001;

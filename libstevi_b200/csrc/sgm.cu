@@ -545,7 +545,7 @@ int32_t sgm_census_disparity_dev(stevi_ctx* c, const HamSource& h, int ndir, int
 	unsigned long long* keys = nullptr;
 	STEVI_TRY(arena_alloc_t(c, npix, &keys));
 	STEVI_CUDA(c, cudaMemsetAsync(keys, 0xff, npix * sizeof(unsigned long long), c->stream));
-	STEVI_TRY(hamming_sgm_wta_dev(c, h, T, R, pout, keys));
+	STEVI_TRY(hamming_sgm_wta_dev(c, h, T, R, pout, 2 * ndir, keys));   // Q4: a line can be walked twice
 	dim3 gdec(cdiv(W, 256), H);
 	STEVI_LAUNCH(c, k_wta_decode_keys, gdec, 256, 0, keys, H, W, wta.sign, wta.offset, wta.out.as<int32_t>(), wta.out.st[0], wta.out.st[1]);
 	return STEVI_OK;
