@@ -11,6 +11,7 @@
 //   hierarchical.h:235-314               hiearchicalTruncatedCostVolume (sic): pyramid by 2, full cost volume + WTA at the
 //                                        coarsest level with disp_width halved per level, guided volumes on the way up
 #include "common.cuh"
+#include <type_traits>
 #include "kernels.cuh"
 #include "costvol_box.cuh"
 
@@ -174,131 +175,181 @@ __device__ __forceinline__ int guided_d0(const Guided& p, int gi, int j) {
 	return p.sign * (int)roundf(id);
 }
 
-// Tiled form for windows up to 9 wide and upscale radii 1..2: a block owns 128 consecutive pixels of one row. The window
-// rows of the source (128 + 2hr columns) and of the target (the span of all candidate columns of the block, the guide being
-// smooth) are staged in shared memory; a thread then reads each target window row once into registers and feeds all
-// 4r+1 candidates from it (2hr+1 + 4r loads for (2hr+1)(4r+1) FMAs). Blocks whose candidates spread over more than
-// GT_SPREAD columns (disparity edges) take the per-pixel kernel's path through global memory instead.
+// Tiled form for windows up to 9 wide and upscale radii 1..2: a block owns 128 consecutive pixels of GT_ROWS consecutive
+// rows. The image rows under those windows (GT_ROWS + 2vr of them) are staged once in shared memory, 16 bytes at a time:
+// 136 source columns and the span of all candidate columns of the block (the guide being smooth). A thread then walks its
+// GT_ROWS pixels; per window row it reads the target row once into registers and feeds all 4r+1 candidates from it
+// (2hr+1 + 4r loads for (2hr+1)(4r+1) FMAs). Blocks whose candidates spread over more than GT_SPREAD columns (disparity
+// edges) read the target through global memory instead.
 constexpr int GT_SPREAD = 96;
+constexpr int GT_ROWS = 8;
+constexpr int GT_SRC_UNITS = (128 + 8) / 4;   // source columns jb-4 .. jb+131
+
+template<int R> struct GtGeom {
+	static constexpr int NC = 4 * R + 1;
+	static constexpr int TGT_UNITS = (128 + 8 + NC + GT_SPREAD + 3 + 3) / 4;   // from the unit holding t_first-4
+};
 
 template<int HR, int R, int OP>
 __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 	constexpr int HS = 2 * HR + 1, NC = 4 * R + 1, TN = HS + NC - 1;
-	constexpr int SW = 128 + 2 * HR, TW = 128 + 2 * HR + NC + GT_SPREAD;
-	extern __shared__ float gsm[];
+	constexpr int SW = 4 * GT_SRC_UNITS, TU = GtGeom<R>::TGT_UNITS, TW = 4 * TU;
+	extern __shared__ __align__(16) float gsm[];
 	__shared__ int s_min[4], s_max[4];
 	const int vs = 2 * p.vr + 1;
-	float* ssrc = gsm;                 // vs x SW
-	float* stgt = gsm + vs * SW;       // vs x TW
-	const int tx = threadIdx.x, jb = blockIdx.x * 128, j = jb + tx, io = blockIdx.y;
-	const int gi = p.out_row0 + io, i = gi - p.img_row0;
+	const int tx = threadIdx.x, jb = blockIdx.x * 128, j = jb + tx, io0 = blockIdx.y * GT_ROWS;
+	const int n_out = min(GT_ROWS, p.n_rows - io0);      // rows of this block
+	const int n_stage = n_out + 2 * p.vr;
+	float* ssrc = gsm;                     // n_stage x SW, tile row q <-> image row i0 - vr + q
+	float* stgt = gsm + n_stage * SW;      // n_stage x TW
+	float* smt = stgt + n_stage * TW;      // n_out x TW: target means under the staged columns
+	float* snt = smt + n_out * TW;         // n_out x TW: target norms
+	const int gi0 = p.out_row0 + io0, i0 = gi0 - p.img_row0;
 	const bool live = j < p.Ws;
-	const int d0 = live ? guided_d0(p, gi, j) : 0;
-	const int jt0 = j + d0 - 2 * R;
-	// span of the block's candidate columns
-	int lo = live ? jt0 : 0x7fffffff, hi = live ? jt0 : -0x7fffffff;
+	// guide disparities of this thread's pixels, and the span of the block's candidate columns
+	int d0r[GT_ROWS];
+	int lo = 0x7fffffff, hi = -0x7fffffff;
+#pragma unroll
+	for (int rr = 0; rr < GT_ROWS; rr++) {
+		d0r[rr] = (live && rr < n_out) ? guided_d0(p, gi0 + rr, j) : 0;
+		if (live && rr < n_out) { lo = min(lo, j + d0r[rr] - 2 * R); hi = max(hi, j + d0r[rr] - 2 * R); }
+	}
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
 	if ((tx & 31) == 0) { s_min[tx >> 5] = lo; s_max[tx >> 5] = hi; }
 	__syncthreads();
 	const int tmin = min(min(s_min[0], s_min[1]), min(s_min[2], s_min[3])), tmax = max(max(s_max[0], s_max[1]), max(s_max[2], s_max[3]));
-	// columns outside [-(pad_left-HR), ...) are not in the padded planes: clamp the staged range to what exists; candidates
+	// columns left of -(pad_left-8) are not in the padded planes: clamp the staged range to what exists; candidates
 	// outside the target image are masked below and never read the tile
 	const int t_first = max(tmin, -HR - 8);
-	const bool tiled = (tmax - t_first) <= GT_SPREAD + 128 - 1 && t_first + TW - HR < (int)p.pitch - p.pad_left - 8;
-	for (int n = tx; n < vs * SW; n += 128) {
-		const int k = n / SW, c = n - k * SW;
-		ssrc[n] = __ldg(p.ps + (int64_t)(i - p.vr + k) * p.pitch + pad_col_off(p.pad_left + jb - HR + c, p.half));
-	}
-	if (tiled)
-		for (int n = tx; n < vs * TW; n += 128) {
-			const int k = n / TW, c = n - k * TW;
-			stgt[n] = __ldg(p.pt + (int64_t)(i - p.vr + k) * p.pitch + pad_col_off(p.pad_left + t_first - HR + c, p.half));
+	const int tu0 = (p.pad_left + t_first - 4) >> 2;     // first staged target unit; staged column c <-> image column 4*tu0 - pad_left + c
+	const int t_col0 = 4 * tu0 - p.pad_left;
+	const bool tiled = (tmax + NC + HR) - t_col0 <= TW && 4 * (tu0 + TU) <= (int)p.pitch - 8;   // last column read: tmax + NC-1 + HR
+	{
+		const int su0 = (p.pad_left + jb - 4) >> 2;
+		for (int n = tx; n < n_stage * GT_SRC_UNITS; n += 128) {
+			const int q = n / GT_SRC_UNITS, u = n - q * GT_SRC_UNITS;
+			const float4 v = __ldg(reinterpret_cast<const float4*>(p.ps + (int64_t)(i0 - p.vr + q) * p.pitch + pad_unit_off(su0 + u, p.half)));
+			*reinterpret_cast<float4*>(ssrc + q * SW + 4 * u) = v;
 		}
+		if (tiled)
+			for (int n = tx; n < n_stage * TU; n += 128) {
+				const int q = n / TU, u = n - q * TU;
+				const float4 v = __ldg(reinterpret_cast<const float4*>(p.pt + (int64_t)(i0 - p.vr + q) * p.pitch + pad_unit_off(tu0 + u, p.half)));
+				*reinterpret_cast<float4*>(stgt + q * TW + 4 * u) = v;
+			}
+		if (tiled)
+			for (int n = tx; n < n_out * TU; n += 128) {
+				const int q = n / TU, u = n - q * TU;
+				const int64_t o = (int64_t)(i0 + q) * p.pitch + pad_unit_off(tu0 + u, p.half);
+				*reinterpret_cast<float4*>(smt + q * TW + 4 * u) = __ldg(reinterpret_cast<const float4*>(p.Mt + o));
+				*reinterpret_cast<float4*>(snt + q * TW + 4 * u) = __ldg(reinterpret_cast<const float4*>(p.Nt + o));
+			}
+	}
 	__syncthreads();
 	if (!live) return;
 	const float F = (float)(HS * vs);
-	const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
-	const float ms = p.Ms[os], ns = p.Ns[os];
 	const bool sub_mean = OP != BOX_PROD && p.zero_mean;
-	float acc[NC], mtv[NC], zacc = 0.f;   // zacc: the cost against the all-zero target vector
+	// two copies of the pixel loop, so that the address arithmetic of the global-memory fallback is not hoisted into the
+	// tiled one
+	auto run = [&](auto tiled_tag) {
+	constexpr bool TILED = decltype(tiled_tag)::value;
+#pragma unroll 1
+	for (int rr = 0; rr < n_out; rr++) {
+		const int io = io0 + rr, i = i0 + rr;
+		int d0 = 0;
 #pragma unroll
-	for (int e = 0; e < NC; e++) {
-		acc[e] = 0.f; mtv[e] = 0.f;
-		const int jt = jt0 + e;
-		if (sub_mean && jt >= 0 && jt < p.Wt) mtv[e] = p.Mt[(int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half)];
-	}
-	for (int k = 0; k < vs; k++) {
-		float t[TN];
-		if (tiled) {
-			// threads whose candidates all lie left of the staged range (hence outside the image, masked below) read column 0
-			const float* T = stgt + k * TW + max(jt0 - t_first, 0);
+		for (int q = 0; q < GT_ROWS; q++) if (q == rr) d0 = d0r[q];
+		const int jt0 = j + d0 - 2 * R;
+		const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
+		const float ms = p.Ms[os], ns = p.Ns[os];
+		float acc[NC], mtv[NC], zacc = 0.f;   // zacc: the cost against the all-zero target vector
+		// statistics of the candidate columns: from the staged rows, else through global memory. Threads whose candidates
+		// all lie left of the staged range (outside the image, masked below) read column 0.
+		const int tstat0 = rr * TW + max(jt0 - t_col0, 0);
+		auto target_mean = [&](int e) { return TILED ? smt[tstat0 + e] : p.Mt[(int64_t)i * p.pitch + pad_col_off(p.pad_left + jt0 + e, p.half)]; };
+		auto target_norm = [&](int e) { return TILED ? snt[tstat0 + e] : p.Nt[(int64_t)i * p.pitch + pad_col_off(p.pad_left + jt0 + e, p.half)]; };
 #pragma unroll
-			for (int n = 0; n < TN; n++) t[n] = T[n];
-		} else {
-			const float* trow = p.pt + (int64_t)(i - p.vr + k) * p.pitch;
+		for (int e = 0; e < NC; e++) {
+			acc[e] = 0.f; mtv[e] = 0.f;
+			const int jt = jt0 + e;
+			if (sub_mean && jt >= 0 && jt < p.Wt) mtv[e] = target_mean(e);
+		}
+		for (int k = 0; k < vs; k++) {
+			float t[TN];
+			if (TILED) {
+				// threads whose candidates all lie left of the staged range (hence outside the image, masked below) read column 0
+				const float* T = stgt + (rr + k) * TW + max(jt0 - HR - t_col0, 0);
 #pragma unroll
-			for (int n = 0; n < TN; n++) {
-				const int X = jt0 - HR + n;   // may lie far outside the padded row when the guide points off the image
-				t[n] = (X >= -p.pad_left + 8 && X < (int)p.pitch - p.pad_left - 8) ? __ldg(trow + pad_col_off(p.pad_left + X, p.half)) : 0.f;
+				for (int n = 0; n < TN; n++) t[n] = T[n];
+			} else {
+				const float* trow = p.pt + (int64_t)(i - p.vr + k) * p.pitch;
+#pragma unroll
+				for (int n = 0; n < TN; n++) {
+					const int X = jt0 - HR + n;   // may lie far outside the padded row when the guide points off the image
+					t[n] = (X >= -p.pad_left + 8 && X < (int)p.pitch - p.pad_left - 8) ? __ldg(trow + pad_col_off(p.pad_left + X, p.half)) : 0.f;
+				}
+			}
+			const float* S = ssrc + (rr + k) * SW + tx + 4 - HR;
+#pragma unroll
+			for (int l = 0; l < HS; l++) {
+				float sv = S[l];
+				if (sub_mean) sv -= ms;
+				if (OP == BOX_SQ) zacc = fmaf(sv, sv, zacc);
+				else if (OP == BOX_ABS) zacc += fabsf(sv);
+#pragma unroll
+				for (int e = 0; e < NC; e++) {
+					if (OP == BOX_PROD) acc[e] = fmaf(sv, t[l + e], acc[e]);
+					else if (OP == BOX_SQ) { const float q = sv - (t[l + e] - mtv[e]); acc[e] = fmaf(q, q, acc[e]); }
+					else acc[e] += fabsf(sv - (t[l + e] - mtv[e]));
+				}
 			}
 		}
-		const float* S = ssrc + k * SW + tx;
 #pragma unroll
-		for (int l = 0; l < HS; l++) {
-			float sv = S[l];
-			if (sub_mean) sv -= ms;
-			if (OP == BOX_SQ) zacc = fmaf(sv, sv, zacc);
-			else if (OP == BOX_ABS) zacc += fabsf(sv);
+		for (int e = 0; e < NC; e++) {
+			const int jt = jt0 + e;
+			const bool inside = jt >= 0 && jt < p.Wt;
+			float v;
+			if (OP == BOX_PROD) {
+				v = 0.f;
+				if (inside) {
+					v = acc[e];
+					if (p.zero_mean) v = fmaf(-F * ms, target_mean(e), v);
+					if (p.normalized) { const float nt = target_norm(e); v = (ns == 0.f || nt == 0.f) ? __int_as_float(0x7fc00000) : v / (ns * nt); }
+				} else if (p.normalized && ns == 0.f) v = __int_as_float(0x7fc00000);
+			} else v = inside ? acc[e] : zacc;
+			acc[e] = v;
+		}
+		float score = p.cost ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+		int best = R;   // index of the candidate at d0 (hierarchical.h: d_r starts at d0 and moves only on a strict improvement)
+		bool moved = false;
 #pragma unroll
-			for (int e = 0; e < NC; e++) {
-				if (OP == BOX_PROD) acc[e] = fmaf(sv, t[l + e], acc[e]);
-				else if (OP == BOX_SQ) { const float q = sv - (t[l + e] - mtv[e]); acc[e] = fmaf(q, q, acc[e]); }
-				else acc[e] += fabsf(sv - (t[l + e] - mtv[e]));
+		for (int dd = 0; dd <= 2 * R; dd++) {
+			const float cmp = acc[R + dd];
+			if (p.cost ? (cmp < score) : (cmp > score)) { score = cmp; best = dd; moved = true; }
+		}
+		const int d_r = moved ? d0 + best - R : d0;
+		p.disp[io * p.d0s + j * p.d1s] = p.sign * d_r;
+		float* o = p.tcv + io * p.t0 + j * p.t1;
+		// re-centred window (hierarchical.h:194-226): cell dd is candidate (d_r - d0) + sign*(dd - R) + 2R, i.e. the 2R+1
+		// consecutive candidates from `first` on, in the direction of the sign
+		const int first = moved ? best : R;
+#pragma unroll
+		for (int b = 0; b <= 2 * R; b++) {
+			if (first == b) {
+#pragma unroll
+				for (int dd = 0; dd <= 2 * R; dd++) o[dd * p.t2] = acc[b + (p.sign > 0 ? dd : 2 * R - dd)];
 			}
 		}
 	}
-#pragma unroll
-	for (int e = 0; e < NC; e++) {
-		const int jt = jt0 + e;
-		const bool inside = jt >= 0 && jt < p.Wt;
-		float v;
-		if (OP == BOX_PROD) {
-			v = 0.f;
-			if (inside) {
-				const int64_t ot = (int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half);
-				v = acc[e];
-				if (p.zero_mean) v = fmaf(-F * ms, p.Mt[ot], v);
-				if (p.normalized) { const float nt = p.Nt[ot]; v = (ns == 0.f || nt == 0.f) ? __int_as_float(0x7fc00000) : v / (ns * nt); }
-			} else if (p.normalized && ns == 0.f) v = __int_as_float(0x7fc00000);
-		} else v = inside ? acc[e] : zacc;
-		acc[e] = v;
-	}
-	float score = p.cost ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
-	int best = R;   // index of the candidate at d0 (hierarchical.h: d_r starts at d0 and moves only on a strict improvement)
-	bool moved = false;
-#pragma unroll
-	for (int dd = 0; dd <= 2 * R; dd++) {
-		const float cmp = acc[R + dd];
-		if (p.cost ? (cmp < score) : (cmp > score)) { score = cmp; best = dd; moved = true; }
-	}
-	const int d_r = moved ? d0 + best - R : d0;
-	p.disp[io * p.d0s + j * p.d1s] = p.sign * d_r;
-	float* o = p.tcv + io * p.t0 + j * p.t1;
-#pragma unroll
-	for (int dd = 0; dd <= 2 * R; dd++) {
-		const int want = (d_r - d0) + p.sign * (dd - R) + 2 * R;
-		float cmp = 0.f;
-#pragma unroll
-		for (int e = 0; e < NC; e++) if (e == want) cmp = acc[e];
-		o[dd * p.t2] = cmp;
-	}
+	};
+	if (tiled) run(std::true_type{}); else run(std::false_type{});
 }
 
 template<int HR, int R>
-static int32_t launch_guided_tile(stevi_ctx* c, const Guided& p, dim3 grid) {
-	const int vs = 2 * p.vr + 1;
-	const int smem = vs * ((128 + 2 * HR) + (128 + 2 * HR + 4 * R + 1 + GT_SPREAD)) * 4;
+static int32_t launch_guided_tile(stevi_ctx* c, const Guided& p) {
+	const int smem = ((GT_ROWS + 2 * p.vr) * (GT_SRC_UNITS + GtGeom<R>::TGT_UNITS) + 2 * GT_ROWS * GtGeom<R>::TGT_UNITS) * 16;
+	dim3 grid(cdiv(p.Ws, 128), cdiv(p.n_rows, GT_ROWS));
 #define GT_OP(OP_) { STEVI_CUDA(c, cudaFuncSetAttribute(k_guided_cv_tile<HR, R, OP_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)); \
 		STEVI_LAUNCH(c, (k_guided_cv_tile<HR, R, OP_>), grid, 128, smem, p); return STEVI_OK; }
 	if (p.op == BOX_PROD) GT_OP(BOX_PROD)
@@ -308,9 +359,9 @@ static int32_t launch_guided_tile(stevi_ctx* c, const Guided& p, dim3 grid) {
 }
 
 static int32_t launch_guided(stevi_ctx* c, const Guided& p, dim3 grid) {
-	const int vs = 2 * p.vr + 1;
-	if (p.hr >= 1 && p.hr <= 4 && (p.r == 1 || p.r == 2) && vs * (2 * 128 + 4 * 4 + 9 + GT_SPREAD) * 4 <= 100 * 1024) {
-#define GT_CASE(HR_) case HR_: return p.r == 1 ? launch_guided_tile<HR_, 1>(c, p, grid) : launch_guided_tile<HR_, 2>(c, p, grid);
+	if (p.hr >= 1 && p.hr <= 4 && (p.r == 1 || p.r == 2) &&
+		((GT_ROWS + 2 * p.vr) * (GT_SRC_UNITS + GtGeom<2>::TGT_UNITS) + 2 * GT_ROWS * GtGeom<2>::TGT_UNITS) * 16 <= 100 * 1024) {
+#define GT_CASE(HR_) case HR_: return p.r == 1 ? launch_guided_tile<HR_, 1>(c, p) : launch_guided_tile<HR_, 2>(c, p);
 		switch (p.hr) { GT_CASE(1) GT_CASE(2) GT_CASE(3) GT_CASE(4) }
 #undef GT_CASE
 	}
