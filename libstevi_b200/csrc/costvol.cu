@@ -36,6 +36,23 @@ __global__ void __launch_bounds__(256) k_pad_image(const TI* __restrict__ img, i
 	if (j < W) out[(int64_t)i * pitch + pad_col_off(pad_left + j, half)] = (float)img[i * s0 + j * s1];
 }
 
+// the same for rows that can be read 4 pixels at a time (column stride 1, 4-pixel-aligned rows): a thread moves one unit
+template<typename TI>
+__global__ void __launch_bounds__(256) k_pad_image_units(const TI* __restrict__ img, int64_t s0, int H, int W,
+														 float* __restrict__ out, int64_t pitch, int half, int pad_left) {
+	const int j = (blockIdx.x * 256 + threadIdx.x) * 4, i = blockIdx.y;
+	if (j >= W) return;
+	float4 v;
+	if (j + 4 <= W) {
+		if (sizeof(TI) == 4) v = __ldg(reinterpret_cast<const float4*>(img + i * s0 + j));
+		else { const uchar4 b = __ldg(reinterpret_cast<const uchar4*>(img + i * s0 + j)); v = make_float4((float)b.x, (float)b.y, (float)b.z, (float)b.w); }
+	} else {
+		const TI* q = img + i * s0 + j;
+		v = make_float4((float)q[0], j + 1 < W ? (float)q[1] : 0.f, j + 2 < W ? (float)q[2] : 0.f, 0.f);
+	}
+	*reinterpret_cast<float4*>(out + (int64_t)i * pitch + pad_unit_off((pad_left + j) >> 2, half)) = v;
+}
+
 // what the statistics maps hold
 enum { STATS_RAW = 0,       // A = mean, B = norm                               (direct path, feature volumes)
 	   STATS_PROD_SRC = 1,  // A = F*mean, B = 1/norm (NaN when norm == 0)
@@ -229,6 +246,13 @@ int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, in
 		W[k] = v.shape[1];
 		if (H == 0 || W[k] == 0) continue;
 		dim3 grid(cdiv(W[k], 256), H);
+		const size_t esz = v.dtype == STEVI_U8 ? 1 : 4;
+		if (v.st[1] == 1 && (v.st[0] * esz) % (4 * esz) == 0 && (uintptr_t)v.p % (4 * esz) == 0) {
+			dim3 gu(cdiv(W[k], 1024), H);
+			if (v.dtype == STEVI_U8) STEVI_LAUNCH(c, k_pad_image_units<uint8_t>, gu, 256, 0, v.as<uint8_t>(), v.st[0], H, W[k], img[k], pitch, half, pad_left);
+			else STEVI_LAUNCH(c, k_pad_image_units<float>, gu, 256, 0, v.as<float>(), v.st[0], H, W[k], img[k], pitch, half, pad_left);
+			continue;
+		}
 		if (v.dtype == STEVI_U8) {
 			STEVI_LAUNCH(c, k_pad_image<uint8_t>, grid, 256, 0, v.as<uint8_t>(), v.st[0], v.st[1], H, W[k], img[k], pitch, half, pad_left);
 		} else {

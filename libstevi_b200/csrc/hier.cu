@@ -36,6 +36,19 @@ __global__ void __launch_bounds__(128) k_avgpool(const TI* __restrict__ img, int
 	out[i * o0 + j * o1] = __fdiv_rn(val, (float)count);
 }
 
+// 2x2 windows over an even-sized dense f32 image (every level of the coarse-to-fine pyramid of an even frame): a thread makes
+// two output pixels from two 16-byte loads; same accumulation order ((a00 + a01) + a10) + a11, same division
+__global__ void __launch_bounds__(128) k_avgpool_2x2(const float* __restrict__ img, int64_t s0, float* __restrict__ out, int64_t o0, int nW) {
+	const int j = (blockIdx.x * 128 + threadIdx.x) * 2, i = blockIdx.y;
+	if (j >= nW) return;
+	const float4 a = __ldg(reinterpret_cast<const float4*>(img + (int64_t)(2 * i) * s0 + 2 * j));
+	const float4 b = __ldg(reinterpret_cast<const float4*>(img + (int64_t)(2 * i + 1) * s0 + 2 * j));
+	float2 v;
+	v.x = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(0.f, a.x), a.y), b.x), b.y), 4.f);
+	v.y = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(0.f, a.z), a.w), b.z), b.w), 4.f);
+	*reinterpret_cast<float2*>(out + (int64_t)i * o0 + j) = v;
+}
+
 struct Guided {
 	const float* ps; const float* pt; int64_t pitch; int half, pad_left;
 	const float* Ms; const float* Ns; const float* Mt; const float* Nt;   // STATS_RAW maps (mean, norm)
@@ -407,6 +420,12 @@ int32_t avgpool_dev(stevi_ctx* c, const View& img, int wh, int wv, const View& o
 	// initialVOffset (= vRem/2) and the COLUMN index initialHOffset (= hRem/2)
 	const int hRem = nH * wv - H, vRem = nW * wh - W;
 	dim3 grid(cdiv(nW, 128), nH);
+	if (img.dtype == STEVI_F32 && wh == 2 && wv == 2 && H % 2 == 0 && W % 4 == 0 && img.st[1] == 1 && out.st[1] == 1 && img.st[0] % 4 == 0 &&
+		out.st[0] % 2 == 0 && (uintptr_t)img.p % 16 == 0 && (uintptr_t)out.p % 8 == 0) {
+		dim3 g2(cdiv(nW, 256), nH);
+		STEVI_LAUNCH(c, k_avgpool_2x2, g2, 128, 0, img.as<float>(), img.st[0], out.as<float>(), out.st[0], nW);
+		return STEVI_OK;
+	}
 	if (img.dtype == STEVI_F32) {
 		STEVI_LAUNCH(c, k_avgpool<float>, grid, 128, 0, img.as<float>(), img.st[0], img.st[1], H, W, wh, wv, vRem / 2, hRem / 2,
 					 out.as<float>(), out.st[0], out.st[1], nH, nW);
