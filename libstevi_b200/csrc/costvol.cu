@@ -303,8 +303,11 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 	const int H = pp.H, Ws = pp.W[si], Wt = pp.W[ti];
 	if (out.ndim != 3 || out.shape[0] != H || out.shape[1] != Ws || out.shape[2] != D || out.dtype != STEVI_F32)
 		return fail(c, STEVI_E_SHAPE, "cost_volume: out must be (%d,%d,%d) f32", H, Ws, D);
-	if (H == 0 || Ws == 0 || D == 0) return STEVI_OK;
 	const int op = mf_op(mf);
+	if (H == 0 || Ws == 0 || D == 0) {
+		if (wta_out) STEVI_TRY(wta_dev(c, out, op == BOX_PROD ? STEVI_SCORE : STEVI_COST, *wta_out));   // whatever the staged call does with an empty volume
+		return STEVI_OK;
+	}
 	if (direct) {
 		if (D > 65535) return fail(c, STEVI_E_UNSUPPORTED, "cost_volume: more than 65535 disparities");
 		STEVI_TRY(pp.stats(c, si, hr, vr, mf, STATS_RAW));

@@ -517,8 +517,8 @@ int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const V
 		cv.st[0] = (int64_t)sl.shape[1] * dw[0]; cv.st[1] = 1; cv.st[2] = sl.shape[1];
 	}
 	STEVI_TRY(alloc_map<int32_t>(c, sl.shape[0], sl.shape[1], STEVI_I32, guide));
-	STEVI_TRY(float_cv_dev(c, mf, pl[0], pr[0], h_radii[0], v_radii[0], dw[0], direction, cv, false));
-	STEVI_TRY(wta_dev(c, cv, h_score(mf) ? STEVI_SCORE : STEVI_COST, guide));
+	// the winner-take-all rides on the cost-volume kernel where the box kernel applies (falls back to the staged WTA inside)
+	STEVI_TRY(float_cv_dev(c, mf, pl[0], pr[0], h_radii[0], v_radii[0], dw[0], direction, cv, false, &guide));
 	for (int k = 1; k <= depth; k++) {
 		const View& s = r2l ? pr[k] : pl[k];
 		View t, d;

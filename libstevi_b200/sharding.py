@@ -141,6 +141,11 @@ def gather_rows(local, bands, dist, group=None):
     import torch
     world = dist.get_world_size(group)
     rows = max(b[1] - b[0] for b in bands)
+    if all(b[1] - b[0] == rows for b in bands):
+        # equal bands: the ranks' rows land in place in one output tensor (no padding, no concatenation)
+        out = torch.empty((world * rows,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local.contiguous(), group=group)
+        return out
     pad = torch.zeros((rows,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     pad[:local.shape[0]] = local
     parts = [torch.empty_like(pad) for _ in range(world)]

@@ -75,6 +75,13 @@ def _worker(rank, world, port, out_dir):
         assert torch.equal(got, full)
         vol = torch.arange(H * W * 3, dtype=torch.float32).reshape(H, W, 3)
         assert torch.equal(S.gather_rows(vol[g0:g1].clone(), bands, dist), vol)
+        # equal bands take the in-place all_gather_into_tensor path
+        He = 40
+        eq_bands = S.row_bands(He, world, 2)
+        assert len({b[1] - b[0] for b in eq_bands}) == 1
+        full_e = torch.arange(He * W * 3, dtype=torch.float32).reshape(He, W, 3)
+        e0, e1 = eq_bands[rank]
+        assert torch.equal(S.gather_rows(full_e[e0:e1].clone(), eq_bands, dist), full_e)
         slowest = S.max_over_ranks(1.5 + rank, dist)
         assert slowest == 1.5 + world - 1
         pairs = S.shard_pairs(9, world, rank)
