@@ -319,7 +319,8 @@ __global__ void __launch_bounds__(256) k_sgm_apply_rows(const uint16_t* __restri
 														float* __restrict__ S, int64_t s0, int64_t sd,
 														const int32_t* __restrict__ T, const int32_t* __restrict__ R,
 														int H, int W, int D, int dchunk, int pout,
-														unsigned long long* __restrict__ keys) {
+														unsigned long long* __restrict__ keys,
+														int32_t* __restrict__ dout, int64_t do0, int64_t do1, int dsign, int doffset) {
 	// COLS (4 or 8) columns per thread: per disparity a warp loads 32*COLS*2 contiguous bytes of costs and stores
 	// 32*COLS*4 contiguous bytes of floats (every sector it touches is written whole by one instruction)
 	static_assert(COLS == 4 || COLS == 8, "columns per thread");
@@ -377,6 +378,12 @@ __global__ void __launch_bounds__(256) k_sgm_apply_rows(const uint16_t* __restri
 		}
 	}
 	if (WTA) {
+		if (!keys) {
+			// the block saw every disparity: its winners are final (selectedIndexToDisp folded in)
+#pragma unroll
+			for (int k = 0; k < COLS; k++) dout[i * do0 + (j + k) * do1] = dsign * bd[k] + doffset;
+			return;
+		}
 		// the disparity range is split over blockIdx.z: merge through one 64-bit atomicMin per pixel and chunk on the key
 		// (S biased to unsigned) << 32 | (2^32-1 - d): smallest S wins, equal S -> largest d, i.e. the reference's `<=` rule
 #pragma unroll
@@ -509,20 +516,26 @@ static int32_t sgm_collapsed(stevi_ctx* c, const View& cv, int ndir, int pout, c
 	if (rows) {
 		constexpr int cols = 4;   // 8 columns per thread measured 0.82 ms against 0.60 ms at C2
 		const int xb = cdiv(W, 256 * cols);
-		// many short blocks: aim at >= 8 waves of 6 resident blocks per SM so the last partial wave costs little
-		const long want = 8L * 6 * c->sm_count;
+		// split the disparity range only when a row-per-block grid would leave SMs idle (< 2 waves of 6 resident blocks per
+		// SM): every split merges its winners through atomics and re-reads T and R (measured at C2: unsplit 0.567 ms, 2 chunks
+		// 0.570, 7 chunks 0.603, 14 chunks 0.655)
+		const long want = 2L * 6 * c->sm_count;
 		long parts = std::min<long>(std::max(1, D / 32), (want + (long)xb * H - 1) / ((long)xb * H));
 		const int dchunk = (int)((D + parts - 1) / parts);
 		dim3 grid(xb, H, cdiv(D, dchunk));
 		unsigned long long* keys = nullptr;
-		if (wta) {
+		const bool split = grid.z > 1;
+		if (wta && split) {
 			STEVI_TRY(arena_alloc_t(c, npix, &keys));
 			STEVI_CUDA(c, cudaMemsetAsync(keys, 0xff, npix * sizeof(unsigned long long), c->stream));
 		}
-#define STEVI_APPLY(W_, S_, C_) STEVI_LAUNCH(c, (k_sgm_apply_rows<W_, S_, C_>), grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys)
+		int32_t* dout = wta ? wta->out.as<int32_t>() : nullptr;
+		const int64_t do0 = wta ? wta->out.st[0] : 0, do1 = wta ? wta->out.st[1] : 0;
+		const int dsign = wta ? wta->sign : 1, doffset = wta ? wta->offset : 0;
+#define STEVI_APPLY(W_, S_, C_) STEVI_LAUNCH(c, (k_sgm_apply_rows<W_, S_, C_>), grid, 256, 0, pc, cv.st[0], cv.st[2], ps, out.st[0], out.st[2], T, R, H, W, D, dchunk, pout, keys, dout, do0, do1, dsign, doffset)
 		if (wta && store) STEVI_APPLY(true, true, cols); else if (wta) STEVI_APPLY(true, false, cols); else STEVI_APPLY(false, true, cols);
 #undef STEVI_APPLY
-		if (wta) {
+		if (wta && split) {
 			dim3 gdec(cdiv(W, 256), H);
 			STEVI_LAUNCH(c, k_wta_decode_keys, gdec, 256, 0, keys, H, W, wta->sign, wta->offset, wta->out.as<int32_t>(), wta->out.st[0], wta->out.st[1]);
 		}
