@@ -181,6 +181,25 @@ STEVI_API int32_t stevi_wta(stevi_ctx* ctx, const stevi_array* vol, int32_t stra
 STEVI_API int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, int32_t direction, int32_t offset,
 							stevi_array* out);
 
+/* ---- 2-D search ---------------------------------------------------------------------
+ * search = {lower0, upper0, lower1, upper1}: the arguments of searchOffset<2> (correlation/correlation_base.h:299-315),
+ * axis 0 = rows, axis 1 = columns; dH = upper0 - lower0 + 1, dW = upper1 - lower1 + 1. */
+
+/* unfoldBased2dDisparityCostVolume<matchFunc, float, float, 2, dDir, float> (correlation/cross_correlations.h:794-822, over
+ * aggregateCost :308-371): img_l, img_r (H,W) f32 of equal size -> out (H,W,dH,dW) f32 (the reference's strides are
+ * {W*dW*dH, 1, W*dW, W}; any strides are accepted). Cell (i,j,a,b) compares the source window at (i,j) with the target
+ * window at (i+a+lower0, j+b+lower1), zero features outside the target image; the direction only picks the source
+ * image. Float matching functions (CC..ZSAD); sizes that differ or an empty window -> STEVI_E_SHAPE (reference: empty array). */
+STEVI_API int32_t stevi_cost_volume_2d(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+							 int32_t h_radius, int32_t v_radius, const int32_t search[4], int32_t direction, stevi_array* out);
+
+/* extractSelected2dIndex<strategy, T_CV> (correlation/correlation_base.h:466-508): vol (H,W,D1,D2) f32 -> out (H,W,2) i32;
+ * row-major scan of (d1,d2) with `<=` / `>=`: the LAST extremum wins, a NaN at (0,0) sticks. */
+STEVI_API int32_t stevi_wta_2d(stevi_ctx* ctx, const stevi_array* vol, int32_t strategy, stevi_array* out);
+
+/* selected2dIndexToDisp<disp_t> (correlation/correlation_base.h:534-555): disp(i,j,k) = idx(i,j,k) + lower offset of axis k */
+STEVI_API int32_t stevi_index2d_to_disp(stevi_ctx* ctx, const stevi_array* idx, const int32_t search[4], stevi_array* out);
+
 /* selectedCost<T_CV> (correlation/correlation_base.h:557-577): out(i,j) = cv(i,j,idx(i,j)); out (H,W) of cv's dtype */
 STEVI_API int32_t stevi_selected_cost(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, stevi_array* out);
 

@@ -344,6 +344,43 @@ def selectedIndexToDisp(idx, offset=0, dDir=RIGHT_TO_LEFT, ctx=None):
     return out
 
 
+def _search4(search):
+    lo0, up0, lo1, up1 = [int(v) for v in search]
+    return (ctypes.c_int32 * 4)(lo0, up0, lo1, up1), up0 - lo0 + 1, up1 - lo1 + 1
+
+
+def unfoldBased2dDisparityCostVolume(matchFunc, img_l, img_r, h_radius, v_radius, searchWindows, dDir=RIGHT_TO_LEFT, layout="ref", ctx=None):
+    """cross_correlations.h:794-822. ``searchWindows`` = (lower0, upper0, lower1, upper1), the arguments of searchOffset<2>
+    (axis 0 = rows, axis 1 = columns). Returns (H, W, dH, dW) float32; ``layout`` "ref" = the reference's strides
+    {W*dW*dH, 1, W*dW, W}, "c" = C order. Raises SteviError(E_SHAPE) where the reference returns an empty array."""
+    ctx = _ctx_for(ctx, img_l)
+    so, dH, dW = _search4(searchWindows)
+    H, W = img_l.shape
+    out = _empty(img_l, (H, W, max(dH, 0), max(dW, 0)), np.float32, (0, 2, 3, 1) if layout == "ref" else None)
+    l, r, o = describe(img_l), describe(img_r), describe(out)
+    ctx.check(lib.stevi_cost_volume_2d(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, so, dDir, ctypes.byref(o)))
+    return out
+
+
+def extractSelected2dIndex(vol, strategy=COST, ctx=None):
+    """correlation_base.h:466-508: (H, W, D1, D2) -> (H, W, 2) int32."""
+    ctx = _ctx_for(ctx, vol)
+    out = _empty(vol, tuple(vol.shape[:2]) + (2,), np.int32)
+    a, o = describe(vol), describe(out)
+    ctx.check(lib.stevi_wta_2d(ctx.handle, ctypes.byref(a), strategy, ctypes.byref(o)))
+    return out
+
+
+def selected2dIndexToDisp(idx, searchWindows, ctx=None):
+    """correlation_base.h:534-555."""
+    ctx = _ctx_for(ctx, idx)
+    so, _, _ = _search4(searchWindows)
+    out = _empty(idx, idx.shape, np.int32)
+    a, o = describe(idx), describe(out)
+    ctx.check(lib.stevi_index2d_to_disp(ctx.handle, ctypes.byref(a), so, ctypes.byref(o)))
+    return out
+
+
 def censusSgmPipeline(img_l, img_r, h_radius, v_radius, disp_width, P1, P2, Pout=100.0, nDirections=8,
                       margins=(0, 0, 0, 0), dDir=RIGHT_TO_LEFT, semantics=COMPAT, return_volumes=False, layout="ref",
                       out=None, ctx=None):

@@ -158,6 +158,38 @@ int32_t stevi_index_to_disp(stevi_ctx* c, const stevi_array* idx, int32_t direct
 	return st.finish();
 }
 
+int32_t stevi_cost_volume_2d(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
+							 const int32_t* search, int32_t direction, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr_, vo;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr_, "img_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(float_cv2d_dev(c, mf, vl, vr_, hr, vr, search, direction, vo));
+	return st.finish();
+}
+
+int32_t stevi_wta_2d(stevi_ctx* c, const stevi_array* vol, int32_t strategy, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vv, vo;
+	STEVI_TRY(st.in(vol, vv, "vol"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(wta2d_dev(c, vv, strategy, vo));
+	return st.finish();
+}
+
+int32_t stevi_index2d_to_disp(stevi_ctx* c, const stevi_array* idx, const int32_t* search, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(index2d_to_disp_dev(c, vi, search, vo));
+	return st.finish();
+}
+
 int32_t stevi_selected_cost(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);

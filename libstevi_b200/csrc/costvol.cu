@@ -180,23 +180,24 @@ struct DirectParams {
 	const float* ps; const float* pt; int64_t pitch; int half, pad_left;
 	const float* Ms; const float* Ns; const float* Mt; const float* Nt;   // STATS_RAW maps
 	int H, Ws, Wt, D, hr, vr, sign, mf, zero_mean, normalized;
+	int dv, col_off;   // 2-D search volumes: the target pixel of (i, j, d) is (i + dv, j + sign*d + col_off); 0, 0 otherwise
 	float* out; int64_t o0, o1, o2;
 };
 
 __global__ void __launch_bounds__(128) k_cv_direct(const DirectParams p) {
 	const int j = blockIdx.x * 128 + threadIdx.x, d = blockIdx.y, i = blockIdx.z;
 	if (j >= p.Ws) return;
-	const int jt = j + p.sign * d;
-	const bool inside = jt >= 0 && jt < p.Wt;
+	const int jt = j + p.sign * d + p.col_off, it = i + p.dv;
+	const bool inside = jt >= 0 && jt < p.Wt && it >= 0 && it < p.H;
 	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1;
 	const float* sb = p.ps + (int64_t)(i - p.vr) * p.pitch;
-	const float* tb = p.pt + (int64_t)(i - p.vr) * p.pitch;
+	const float* tb = p.pt + (int64_t)(it - p.vr) * p.pitch;
 	const int Xs = p.pad_left + j - p.hr, Xt = p.pad_left + jt - p.hr;
 	const int64_t os = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
 	const float ms = p.Ms[os], ns = p.Ns[os];
 	float mt = 0.f, nt = 1.f;
 	if (inside) {
-		const int64_t ot = (int64_t)i * p.pitch + pad_col_off(p.pad_left + jt, p.half);
+		const int64_t ot = (int64_t)it * p.pitch + pad_col_off(p.pad_left + jt, p.half);
 		mt = p.Mt[ot]; nt = p.Nt[ot];
 	}
 	const int op = mf_op(p.mf);
@@ -283,6 +284,54 @@ int32_t PaddedPair::stats(stevi_ctx* c, int which, int hr, int vr, int mf, int k
 	return STEVI_OK;
 }
 
+// unfoldBased2dDisparityCostVolume (cross_correlations.h:794-822 over aggregateCost :308-371): cell (i, j, dh, dw) compares
+// the source window at (i, j) with the target window at (i + dh + lower0, j + dw + lower1), zero features outside the
+// target image, for both directions (the direction only picks the source image). One launch of the reference-order kernel
+// per row offset; search = {lower0, upper0, lower1, upper1}; out (H, W, dH, dW).
+int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const int32_t* search, int direction,
+					   const View& out) {
+	switch (mf) {
+	case STEVI_MF_CC: case STEVI_MF_NCC: case STEVI_MF_ZCC: case STEVI_MF_ZNCC:
+	case STEVI_MF_SSD: case STEVI_MF_ZSSD: case STEVI_MF_SAD: case STEVI_MF_ZSAD: break;
+	default: return fail(c, STEVI_E_UNSUPPORTED, "cost_volume_2d: matching function %d not available", mf);
+	}
+	if (!search) return fail(c, STEVI_E_ARG, "cost_volume_2d: null search window");
+	if (hr < 0 || vr < 0 || hr > 127 || vr > 127) return fail(c, STEVI_E_ARG, "cost_volume_2d: radii out of range");
+	if (l.ndim != 2 || r.ndim != 2 || l.dtype != STEVI_F32 || r.dtype != STEVI_F32)
+		return fail(c, STEVI_E_DTYPE, "cost_volume_2d: images must be (H,W) f32");
+	if (l.shape[0] != r.shape[0] || l.shape[1] != r.shape[1])
+		return fail(c, STEVI_E_SHAPE, "cost_volume_2d: image sizes differ (cross_correlations.h:804-810)");
+	const int dH = search[1] - search[0] + 1, dW = search[3] - search[2] + 1;
+	if (dH <= 0 || dW <= 0) return fail(c, STEVI_E_SHAPE, "cost_volume_2d: empty search window (cross_correlations.h:336-338)");
+	if (dH > 4096 || dW > 65535 || abs(search[0]) > 65535 || abs(search[1]) > 65535 || abs(search[2]) > 65535 || abs(search[3]) > 65535)
+		return fail(c, STEVI_E_UNSUPPORTED, "cost_volume_2d: search window too large");
+	const int H = l.shape[0], W = l.shape[1];
+	if (out.ndim != 4 || out.dtype != STEVI_F32 || out.shape[0] != H || out.shape[1] != W || out.shape[2] != dH || out.shape[3] != dW)
+		return fail(c, STEVI_E_SHAPE, "cost_volume_2d: out must be (%d,%d,%d,%d) f32", H, W, dH, dW);
+	if (H == 0 || W == 0) return STEVI_OK;
+	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
+	const int reach = std::max(abs(search[2]), abs(search[3]));   // the padded rows must hold every target column a cell can name
+	PaddedPair pp;
+	STEVI_TRY(pp.build(c, l, r, hr, vr, reach + 1, 1));
+	const int si = r2l ? 1 : 0, ti = 1 - si;
+	STEVI_TRY(pp.stats(c, si, hr, vr, mf, STATS_RAW));
+	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, STATS_RAW));
+	DirectParams p;
+	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left;
+	p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
+	p.H = H; p.Ws = W; p.Wt = W; p.D = dW; p.hr = hr; p.vr = vr; p.sign = 1; p.mf = mf;
+	p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf);
+	p.col_off = search[2];
+	p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[3];
+	dim3 grid(cdiv(W, 128), dW, H);
+	for (int a = 0; a < dH; a++) {
+		p.dv = a + search[0];
+		p.out = out.as<float>() + (int64_t)a * out.st[2];
+		STEVI_LAUNCH(c, k_cv_direct, grid, 128, 0, p);
+	}
+	return STEVI_OK;
+}
+
 int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, int D, int direction, const View& out,
 					 bool force_direct, const View* wta_out) {
 	switch (mf) {
@@ -316,7 +365,7 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 		p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left;
 		p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
 		p.H = H; p.Ws = Ws; p.Wt = Wt; p.D = D; p.hr = hr; p.vr = vr; p.sign = r2l ? 1 : -1; p.mf = mf;
-		p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf);
+		p.zero_mean = mf_zero_mean(mf); p.normalized = mf_normalized(mf); p.dv = 0; p.col_off = 0;
 		p.out = out.as<float>(); p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
 		dim3 grid(cdiv(Ws, 128), D, H);
 		STEVI_LAUNCH(c, k_cv_direct, grid, 128, 0, p);

@@ -54,7 +54,12 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 				const stevi_margins& mg, int semantics, const View& out, const int32_t* gmap_ready, int max_cost_hint,
 				const WtaSink* wta);
 
+// costvol.cu: 2-D search cost volume, search = {lower0, upper0, lower1, upper1}, out (H,W,dH,dW) f32
+int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const int32_t* search, int direction, const View& out);
+
 // wta.cu
+int32_t wta2d_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);
+int32_t index2d_to_disp_dev(stevi_ctx* c, const View& idx, const int32_t* search, const View& out);
 int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);
 // keys: dense [H][W], (order bits << 32 | d) merged with atomicMax, 0 = never written -> index 0
 int32_t wta_decode_max_keys_dev(stevi_ctx* c, const unsigned long long* keys, int H, int W, const View& out);

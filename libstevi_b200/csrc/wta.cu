@@ -152,6 +152,67 @@ int32_t wta_dev(stevi_ctx* c, const View& vol, int strategy, const View& out) {
 	}
 }
 
+// extractSelected2dIndex (correlation_base.h:466-508): a thread per pixel scans (d1, d2) in row-major order starting from
+// the value of cell (0,0), `<=` / `>=`: the last extremum wins, a NaN at (0,0) sticks (no comparison against it is true)
+template<bool SCORE>
+__global__ void __launch_bounds__(128) k_wta_2d(const float* __restrict__ v, int64_t s0, int64_t s1, int64_t s2, int64_t s3, int H, int W,
+												int D1, int D2, int32_t* __restrict__ out, int64_t o0, int64_t o1, int64_t o2) {
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+	if (j >= W) return;
+	const float* p = v + i * s0 + j * s1;
+	float best = p[0];
+	int b1 = 0, b2 = 0;
+	for (int a = 0; a < D1; a++)
+		for (int b = 0; b < D2; b++) {
+			const float x = p[a * s2 + b * s3];
+			if (SCORE ? (x >= best) : (x <= best)) { best = x; b1 = a; b2 = b; }
+		}
+	out[i * o0 + j * o1] = b1;
+	out[i * o0 + j * o1 + o2] = b2;
+}
+
+int32_t wta2d_dev(stevi_ctx* c, const View& vol, int strategy, const View& out) {
+	if (vol.ndim != 4 || vol.dtype != STEVI_F32) return fail(c, STEVI_E_SHAPE, "wta_2d: volume must be (H,W,D1,D2) f32");
+	if (out.ndim != 3 || out.shape[0] != vol.shape[0] || out.shape[1] != vol.shape[1] || out.shape[2] != 2 || out.dtype != STEVI_I32)
+		return fail(c, STEVI_E_SHAPE, "wta_2d: out must be (H,W,2) i32");
+	if (strategy != STEVI_COST && strategy != STEVI_SCORE) return fail(c, STEVI_E_ARG, "wta_2d: bad strategy");
+	const int H = vol.shape[0], W = vol.shape[1];
+	if (H == 0 || W == 0) return STEVI_OK;
+	if (vol.shape[2] < 1 || vol.shape[3] < 1) return fail(c, STEVI_E_SHAPE, "wta_2d: empty search axis");
+	if (H > 65535) return fail(c, STEVI_E_UNSUPPORTED, "wta_2d: more than 65535 rows");
+	dim3 grid(cdiv(W, 128), H);
+	if (strategy == STEVI_SCORE)
+		STEVI_LAUNCH(c, k_wta_2d<true>, grid, 128, 0, vol.as<float>(), vol.st[0], vol.st[1], vol.st[2], vol.st[3], H, W, vol.shape[2], vol.shape[3],
+					 out.as<int32_t>(), out.st[0], out.st[1], out.st[2]);
+	else
+		STEVI_LAUNCH(c, k_wta_2d<false>, grid, 128, 0, vol.as<float>(), vol.st[0], vol.st[1], vol.st[2], vol.st[3], H, W, vol.shape[2], vol.shape[3],
+					 out.as<int32_t>(), out.st[0], out.st[1], out.st[2]);
+	return STEVI_OK;
+}
+
+// selected2dIndexToDisp (correlation_base.h:534-555): index + lower offset of its axis
+__global__ void __launch_bounds__(256) k_index2d_to_disp(const int32_t* __restrict__ idx, int64_t s0, int64_t s1, int64_t s2, int H, int W, int lo0, int lo1,
+														  int32_t* __restrict__ out, int64_t o0, int64_t o1, int64_t o2) {
+	const int j = blockIdx.x * 256 + threadIdx.x, i = blockIdx.y;
+	if (j >= W) return;
+	out[i * o0 + j * o1] = idx[i * s0 + j * s1] + lo0;
+	out[i * o0 + j * o1 + o2] = idx[i * s0 + j * s1 + s2] + lo1;
+}
+
+int32_t index2d_to_disp_dev(stevi_ctx* c, const View& idx, const int32_t* search, const View& out) {
+	if (!search) return fail(c, STEVI_E_ARG, "index2d_to_disp: null search window");
+	if (idx.ndim != 3 || idx.shape[2] != 2 || idx.dtype != STEVI_I32 || out.ndim != 3 || out.dtype != STEVI_I32 ||
+		out.shape[0] != idx.shape[0] || out.shape[1] != idx.shape[1] || out.shape[2] != 2)
+		return fail(c, STEVI_E_SHAPE, "index2d_to_disp: idx and out must be (H,W,2) i32");
+	const int H = idx.shape[0], W = idx.shape[1];
+	if (H == 0 || W == 0) return STEVI_OK;
+	if (H > 65535) return fail(c, STEVI_E_UNSUPPORTED, "index2d_to_disp: more than 65535 rows");
+	dim3 grid(cdiv(W, 256), H);
+	STEVI_LAUNCH(c, k_index2d_to_disp, grid, 256, 0, idx.as<int32_t>(), idx.st[0], idx.st[1], idx.st[2], H, W, search[0], search[2],
+				 out.as<int32_t>(), out.st[0], out.st[1], out.st[2]);
+	return STEVI_OK;
+}
+
 __global__ void __launch_bounds__(256) k_wta_decode_max_keys(const unsigned long long* __restrict__ keys, int H, int W,
 															 int32_t* __restrict__ out, int64_t o0, int64_t o1) {
 	const int j = blockIdx.x * 256 + threadIdx.x, i = blockIdx.y;

@@ -146,6 +146,32 @@ class _Checker:
                                             h, wl, wr, hr, vr, D, direction, _p(out))
         return out if rc == 0 else None
 
+    def cost_volume_2d(self, mf, left, right, hr, vr, search, direction=R2L):
+        """unfoldBased2dDisparityCostVolume with searchOffset<2>(*search), search = (lower0, upper0, lower1, upper1);
+        (h, w, dH, dW) float32, None where the reference returns an empty array."""
+        if left.shape != right.shape:
+            return None
+        h, w = left.shape
+        so = np.asarray(search, np.int32)
+        dH, dW = int(so[1] - so[0] + 1), int(so[3] - so[2] + 1)
+        if dH <= 0 or dW <= 0:
+            return None
+        out = np.empty((h, w, dH, dW), np.float32)
+        rc = self._f("cost_volume_2d_f32")(mf, _p(_c(left, np.float32)), _p(_c(right, np.float32)), h, w, hr, vr, _p(so), direction, _p(out))
+        return out if rc == 0 else None
+
+    def wta_2d(self, vol, strategy):
+        h, w, d1, d2 = vol.shape
+        out = np.empty((h, w, 2), np.int32)
+        self._f("wta_2d_f32")(_p(_c(vol, np.float32)), h, w, d1, d2, strategy, _p(out))
+        return out
+
+    def index2d_to_disp(self, idx, search):
+        h, w, _ = idx.shape
+        out = np.empty((h, w, 2), np.int32)
+        self._f("index2d_to_disp")(_p(_c(idx, np.int32)), h, w, _p(np.asarray(search, np.int32)), _p(out))
+        return out
+
     def sgm(self, cv, ndir, strategy, P1, P2, Pout=100.0, margins=(0, 0, 0, 0)):
         h, w, D = cv.shape
         out = np.empty((h, w, D), np.float32)

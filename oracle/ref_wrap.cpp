@@ -62,6 +62,21 @@ int cv_dir(const TI* l, const TI* r, int h, int w, int wr, int hr, int vr, int D
 	return 0;
 }
 
+template<matchingFunctions F>
+int cv2d_dir(const float* l, const float* r, int h, int w, int hr, int vr, const int* so, int dir, float* out) {
+	auto L = view2(l, h, w);
+	auto R = view2(r, h, w);
+	searchOffset<2> range(so[0], so[1], so[2], so[3]);
+	MD::Array<float, 4> cv = dir == int(dispDirection::RightToLeft)
+		? unfoldBased2dDisparityCostVolume<F, float, float, 2, dispDirection::RightToLeft, float>(L, R, uint8_t(hr), uint8_t(vr), range)
+		: unfoldBased2dDisparityCostVolume<F, float, float, 2, dispDirection::LeftToRight, float>(L, R, uint8_t(hr), uint8_t(vr), range);
+	if (cv.empty()) return 1;
+	auto s = cv.shape();
+	for (int i = 0; i < s[0]; i++) for (int j = 0; j < s[1]; j++) for (int a = 0; a < s[2]; a++) for (int b = 0; b < s[3]; b++)
+		out[((size_t(i) * s[1] + j) * s[2] + a) * s[3] + b] = cv.valueUnchecked(i, j, a, b);
+	return 0;
+}
+
 template<dispExtractionStartegy S, typename T>
 int sgm_n(const T* cv, int h, int w, int d, int ndir, float P1, float P2, float Pout, const int* m, float* out) {
 	auto CV = view3(cv, h, w, d);
@@ -179,6 +194,37 @@ int ref_cost_volume_f32(int matchfunc, const float* l, const float* r, int h, in
 	case matchingFunctions::ZSAD: return cv_dir<matchingFunctions::ZSAD>(l, r, h, w, wr, hr, vr, D, dir, out);
 	default: return 2;
 	}
+}
+
+// cross_correlations.h:794-822: 2-D search cost volume, float images of equal size. so = {lower0, upper0, lower1, upper1}
+// (searchOffset<2> ctor order, correlation_base.h:299-315). out (h, w, upper0-lower0+1, upper1-lower1+1) C-order.
+int ref_cost_volume_2d_f32(int matchfunc, const float* l, const float* r, int h, int w, int hr, int vr, const int* so, int dir, float* out) {
+	switch (matchingFunctions(matchfunc)) {
+	case matchingFunctions::CC: return cv2d_dir<matchingFunctions::CC>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::NCC: return cv2d_dir<matchingFunctions::NCC>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::SSD: return cv2d_dir<matchingFunctions::SSD>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::SAD: return cv2d_dir<matchingFunctions::SAD>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::ZCC: return cv2d_dir<matchingFunctions::ZCC>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::ZNCC: return cv2d_dir<matchingFunctions::ZNCC>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::ZSSD: return cv2d_dir<matchingFunctions::ZSSD>(l, r, h, w, hr, vr, so, dir, out);
+	case matchingFunctions::ZSAD: return cv2d_dir<matchingFunctions::ZSAD>(l, r, h, w, hr, vr, so, dir, out);
+	default: return 2;
+	}
+}
+
+// correlation_base.h:466-508 on a (h, w, d1, d2) C-order volume; out (h, w, 2)
+int ref_wta_2d_f32(const float* v, int h, int w, int d1, int d2, int strategy, int32_t* out) {
+	MD::Array<float, 4> V(const_cast<float*>(v), {h, w, d1, d2}, {w * d1 * d2, d1 * d2, d2, 1}, false);
+	if (strategy == 0) out3(extractSelected2dIndex<dispExtractionStartegy::Cost>(V), out);
+	else out3(extractSelected2dIndex<dispExtractionStartegy::Score>(V), out);
+	return 0;
+}
+
+// correlation_base.h:534-555
+int ref_index2d_to_disp(const int32_t* idx, int h, int w, const int* so, int32_t* out) {
+	searchOffset<2> range(so[0], so[1], so[2], so[3]);
+	out3(selected2dIndexToDisp<disp_t>(view3(idx, h, w, 2), range), out);
+	return 0;
 }
 
 // census cost volume, hamming_cv_t (uint16) costs, as the C2/C5 configs use it.

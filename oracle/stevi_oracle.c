@@ -237,6 +237,54 @@ int orc_cost_volume_f32(int mf, const float* l, const float* r, int h, int wl, i
 	return 0;
 }
 
+/* ---- cross_correlations.h:308-371 aggregateCost over searchOffset<2> + :794-822 unfoldBased2dDisparityCostVolume, float
+ * images of equal size (the reference returns an empty array otherwise, :804-810). so = {lower0, upper0, lower1, upper1}:
+ * axis 0 = rows, axis 1 = columns (correlation_base.h:299-315). The target pixel of cell (i, j, dh, dw) is
+ * (i + dh + lower0, j + dw + lower1) for BOTH directions (:357) - the direction only picks which image is the source
+ * (condImgRef) - and its features are 0 outside the target image (valueOrAlt). out (h, w, dH, dW) C-order; returns 1 for an
+ * empty search window (:336-338). */
+int orc_cost_volume_2d_f32(int mf, const float* l, const float* r, int h, int w, int hr, int vr, const int* so, int dir, float* out) {
+	int dH = so[1] - so[0] + 1, dW = so[3] - so[2] + 1;
+	if (dH <= 0 || dW <= 0) return 1;
+	int F = (2 * hr + 1) * (2 * vr + 1);
+	float* fl = (float*)malloc((size_t)h * w * F * sizeof(float));
+	float* fr = (float*)malloc((size_t)h * w * F * sizeof(float));
+	orc_feature_volume_f32(mf, l, h, w, hr, vr, fl);
+	orc_feature_volume_f32(mf, r, h, w, hr, vr, fr);
+	const float* src = dir == DIR_R2L ? fr : fl;
+	const float* tgt = dir == DIR_R2L ? fl : fr;
+	float* zero = (float*)calloc((size_t)F, sizeof(float));
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) for (int a = 0; a < dH; a++) for (int b = 0; b < dW; b++) {
+		int it = i + a + so[0], jt = j + b + so[2];
+		const float* t = (it >= 0 && it < h && jt >= 0 && jt < w) ? tgt + ((size_t)it * w + jt) * F : zero;
+		out[(((size_t)i * w + j) * dH + a) * dW + b] = compare_f32(mf, src + ((size_t)i * w + j) * F, t, F);
+	}
+	free(zero); free(fl); free(fr);
+	return 0;
+}
+
+/* correlation_base.h:466-508 extractSelected2dIndex: the scan starts from cell (0,0) and visits it again, `<=` / `>=`, so
+ * the LAST extremum in (d1, d2) row-major order wins and a NaN at (0,0) sticks. out (h, w, 2). */
+int orc_wta_2d_f32(const float* v, int h, int w, int d1, int d2, int strategy, int32_t* out) {
+	for (size_t p = 0; p < (size_t)h * w; p++) {
+		const float* c = v + p * d1 * d2;
+		float best = c[0]; int32_t b1 = 0, b2 = 0;
+		for (int a = 0; a < d1; a++) for (int b = 0; b < d2; b++) {
+			float x = c[a * d2 + b];
+			if (strategy == STRAT_COST ? (x <= best) : (x >= best)) { best = x; b1 = a; b2 = b; }
+		}
+		out[2 * p] = b1; out[2 * p + 1] = b2;
+	}
+	return 0;
+}
+
+/* correlation_base.h:534-555 selected2dIndexToDisp: index + lower offset per axis */
+int orc_index2d_to_disp(const int32_t* idx, int h, int w, const int* so, int32_t* out) {
+	for (size_t p = 0; p < (size_t)h * w; p++) { out[2 * p] = idx[2 * p] + so[0]; out[2 * p + 1] = idx[2 * p + 1] + so[2]; }
+	return 0;
+}
+
 /* Q2 (cross_correlations.h:235-236): every TARGET feature passes through `float t` before being narrowed back
  * to the feature type. For uint32 census words that is a round-to-nearest-even to 24 significant bits; a word
  * >= 0xFFFFFF80 rounds to 2^32 whose conversion back is undefined behaviour in C++ — the scalar x86-64 result

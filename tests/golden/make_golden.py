@@ -66,5 +66,29 @@ def main():
     print("wrote", os.path.join(HERE, "reference_outputs.npz"), os.path.getsize(os.path.join(HERE, "reference_outputs.npz")), "bytes")
 
 
+def main_2d():
+    """2-D search: unfoldBased2dDisparityCostVolume, extractSelected2dIndex, selected2dIndexToDisp."""
+    ref = O.ref
+    assert ref is not None, "build oracle/_ref first (make -C oracle ref)"
+    H, W = 11, 15
+    search = (-1, 2, -3, 3)
+    Lf, Rf = synth.random_image(H, W, 201), synth.random_image(H, W, 202)
+    out = {"H": H, "W": W, "seed_l": 201, "seed_r": 202, "search": np.asarray(search, np.int32)}
+    for mf in (O.CC, O.NCC, O.SSD, O.SAD, O.ZCC, O.ZNCC, O.ZSSD, O.ZSAD):
+        for direction in (0, 1):
+            out[f"cv2d_{mf}_{direction}"] = ref.cost_volume_2d(mf, Lf, Rf, 2, 1, search, direction)
+    for mf, strategy in ((O.ZNCC, 1), (O.SSD, 0)):
+        idx = ref.wta_2d(out[f"cv2d_{mf}_1"], strategy)
+        out[f"wta2d_{mf}"] = idx
+        out[f"disp2d_{mf}"] = ref.index2d_to_disp(idx, search)
+    path = os.path.join(HERE, "reference_outputs_2d.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
-    main()
+    if "2d" in sys.argv[1:]:
+        main_2d()
+    else:
+        main()
+        main_2d()

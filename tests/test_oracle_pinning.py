@@ -187,3 +187,100 @@ def test_port_equals_compiled_reference_unfold_family():
     fv = port.unfold_general(img2, 3, 2)
     assert same(port.census_features(fv), ref.census_features(fv))
     assert same(port.census_features(fv), port.census(img2, 3, 2))
+
+
+# ---- 2-D search ---------------------------------------------------------------------------------
+
+G2 = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_outputs_2d.npz"))
+
+
+@pytest.mark.parametrize("mf", [O.CC, O.NCC, O.SSD, O.SAD, O.ZCC, O.ZNCC, O.ZSSD, O.ZSAD])
+def test_golden_2d_cost_volumes(mf):
+    Lq, Rq = synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_l"])), synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_r"]))
+    search = tuple(int(v) for v in G2["search"])
+    for direction in (0, 1):
+        assert same(port.cost_volume_2d(mf, Lq, Rq, 2, 1, search, direction), G2[f"cv2d_{mf}_{direction}"])
+
+
+def test_golden_2d_selection():
+    search = tuple(int(v) for v in G2["search"])
+    for mf, strategy in ((O.ZNCC, 1), (O.SSD, 0)):
+        idx = port.wta_2d(G2[f"cv2d_{mf}_1"], strategy)
+        assert same(idx, G2[f"wta2d_{mf}"])
+        assert same(port.index2d_to_disp(idx, search), G2[f"disp2d_{mf}"])
+    # ties: the last extremum in (d1, d2) row-major order wins; a NaN at (0,0) sticks
+    v = np.zeros((1, 2, 2, 3), np.float32)
+    v[0, 1, 0, 0] = np.nan
+    for strategy in (0, 1):
+        got = port.wta_2d(v, strategy)
+        assert got[0, 0].tolist() == [1, 2] and got[0, 1].tolist() == [0, 0]
+    assert port.cost_volume_2d(O.ZNCC, np.zeros((5, 6), np.float32), np.zeros((5, 7), np.float32), 1, 1, (0, 1, 0, 1)) is None
+    assert port.cost_volume_2d(O.ZNCC, np.zeros((5, 6), np.float32), np.zeros((5, 6), np.float32), 1, 1, (1, 0, 0, 1)) is None
+
+
+@pytest.mark.skipif(O.ref is None, reason="compiled reference (oracle/_ref) not present on this machine")
+def test_port_equals_compiled_reference_2d():
+    ref = O.ref
+    Lq, Rq = synth.random_image(14, 21, 31), synth.random_image(14, 21, 32)
+    for search in ((0, 2, 0, 4), (-3, -1, 2, 6), (-2, 2, -5, 0)):
+        for mf in (O.ZNCC, O.ZSAD, O.SSD, O.CC):
+            for direction in (0, 1):
+                a, b = port.cost_volume_2d(mf, Lq, Rq, 1, 2, search, direction), ref.cost_volume_2d(mf, Lq, Rq, 1, 2, search, direction)
+                assert same(a, b)
+            for strategy in (0, 1):
+                assert same(port.wta_2d(b, strategy), ref.wta_2d(b, strategy))
+        i2 = port.wta_2d(b, 0)
+        assert same(port.index2d_to_disp(i2, search), ref.index2d_to_disp(i2, search))
+
+
+def naive_match(mf, win_s, win_t):
+    """test/test_correlation_utils.h InneficientMatchingFunction: the textbook formula on two windows."""
+    s, t = win_s.astype(np.float64).ravel(), win_t.astype(np.float64).ravel()
+    if mf in (O.ZCC, O.ZNCC, O.ZSSD, O.ZSAD):
+        s, t = s - s.mean(), t - t.mean()
+    if mf in (O.NCC, O.ZNCC):
+        s, t = s / np.sqrt((s * s).sum()), t / np.sqrt((t * t).sum())
+    if mf in (O.CC, O.NCC, O.ZCC, O.ZNCC):
+        return float((s * t).sum())
+    if mf in (O.SSD, O.ZSSD):
+        return float(((s - t) ** 2).sum())
+    return float(np.abs(s - t).sum())
+
+
+def check_2d_matching(cost_volume_2d, mf, hr, vr, disp_w, disp_h, seed):
+    """testCorrelation2d.cpp:73-124 test2dMatching: cell (v_radius, h_radius, i, j) of the volume is the matching function of
+    the right image's first window against the left image's window shifted by (i, j); tolerance 1e-3 as in the reference."""
+    h, w = 2 * vr + disp_h + 1, 2 * hr + disp_w + 1
+    left, right = synth.random_image(h, w, seed) / 127.5 - 1.0, synth.random_image(h, w, seed + 1) / 127.5 - 1.0
+    left, right = left.astype(np.float32), right.astype(np.float32)
+    cv = cost_volume_2d(mf, left, right, hr, vr, (0, disp_h, 0, disp_w))
+    win1 = right[0:2 * vr + 1, 0:2 * hr + 1]
+    for i in range(disp_h):
+        for j in range(disp_w):
+            want = naive_match(mf, win1, left[i:i + 2 * vr + 1, j:j + 2 * hr + 1])
+            assert abs(want - float(cv[vr, hr, i, j])) < 1e-3, (mf, i, j)
+
+
+def check_2d_disparity(cost_volume_2d, wta_2d, index2d_to_disp, mf, hr, vr, seed):
+    """testCorrelation2d.cpp:128-194 test2dDisparity: a window planted at offset (-1,-1) / (disp_h-1, disp_w-1) is found."""
+    disp_w = disp_h = 3
+    h, w = 2 * vr + disp_h + 1, 2 * hr + disp_w + 1
+    rnd = lambda k: (synth.random_image(h, w, seed + k) / 127.5 - 1.0).astype(np.float32)
+    source, target0, targetmax = rnd(0), rnd(1), rnd(2)
+    for i in range(2 * vr + 1):
+        for j in range(2 * hr + 1):
+            target0[i, j] = source[i + 1, j + 1]
+            targetmax[i + disp_h, j + disp_w] = source[i + 1, j + 1]
+    search = (-1, disp_h - 1, -1, disp_w - 1)
+    strategy = O.strategy_of(mf)
+    d0 = index2d_to_disp(wta_2d(cost_volume_2d(mf, target0, source, hr, vr, search), strategy), search)
+    assert d0[vr + 1, hr + 1].tolist() == [-1, -1]
+    dm = index2d_to_disp(wta_2d(cost_volume_2d(mf, targetmax, source, hr, vr, search), strategy), search)
+    assert dm[vr + 1, hr + 1].tolist() == [disp_h - 1, disp_w - 1]
+
+
+@pytest.mark.parametrize("mf", [O.NCC, O.ZNCC, O.SSD, O.ZSSD, O.SAD, O.ZSAD])
+@pytest.mark.parametrize("hr,vr,dw,dh", [(1, 1, 5, 5), (3, 2, 4, 6)])
+def test_ref_test2dMatching_and_test2dDisparity(mf, hr, vr, dw, dh):
+    check_2d_matching(port.cost_volume_2d, mf, hr, vr, dw, dh, 77)
+    check_2d_disparity(port.cost_volume_2d, port.wta_2d, port.index2d_to_disp, mf, hr, vr, 91)
