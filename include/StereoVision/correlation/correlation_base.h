@@ -1,9 +1,12 @@
 // B200 facade of LibStevi's correlation/correlation_base.h (dense-stereo part): same names, template parameters and
 // defaults; bodies forward to the C ABI. Reference lines: enums :31-45, disp_t :47, extractSelectedIndex :427-464,
-// selectedIndexToDisp :511-532, selectedCost :557-577, truncatedCostVolume :579-674, extractInBoundDomain :727-822.
+// selectedIndexToDisp :511-532, selectedCost :557-577, truncatedCostVolume :579-674, extractInBoundDomain :727-822;
+// 2-D search: searchOffset :288-409, extractSelected2dIndex :466-509, selected2dIndexToDisp :534-555,
+// truncatedBidirectionaCostVolume :677-725.
 #ifndef STEVI_B200_CORRELATION_BASE_H
 #define STEVI_B200_CORRELATION_BASE_H
 
+#include <cstdlib>
 #include "../stevi_b200_bridge.h"
 
 namespace StereoVision {
@@ -14,6 +17,48 @@ enum class dispDirection { LeftToRight = 0, RightToLeft = 1 };
 enum class truncatedCostVolumeDirection { Same = 0, Reversed = 1, Both = 2 };
 
 typedef int32_t disp_t;
+
+// Inclusive [lower, upper] search range per axis (reference :288-409): same constructor order (lower0, upper0, lower1, upper1, ...),
+// same accessors. Plain host-side value type, nothing to offload.
+template<int nDim>
+class searchOffset {
+public:
+	searchOffset() : _valid(false) { _up.fill(0); _lo.fill(0); }
+	template<typename... Ds>
+	searchOffset(disp_t lowerOffset0, disp_t upperOffset0, Ds... nextOffsets) : _valid(true) {
+		static_assert(sizeof...(nextOffsets) == 2 * (nDim - 1), "two offsets per dimension");
+		const disp_t all[2 * nDim] = {lowerOffset0, upperOffset0, disp_t(nextOffsets)...};
+		for (int k = 0; k < nDim; k++) { _lo[k] = all[2 * k]; _up[k] = all[2 * k + 1]; }
+	}
+	bool isValid() const { return _valid; }
+	template<int dim> int& upperOffset() { return _up[dim]; }
+	template<int dim> int& lowerOffset() { return _lo[dim]; }
+	template<int dim> int const& upperOffset() const { return _up[dim]; }
+	template<int dim> int const& lowerOffset() const { return _lo[dim]; }
+	int& upperOffset(int dim) { return _up[dim]; }
+	int& lowerOffset(int dim) { return _lo[dim]; }
+	int const& upperOffset(int dim) const { return _up[dim]; }
+	int const& lowerOffset(int dim) const { return _lo[dim]; }
+	template<int dim> int dimRange() const { return dimRange(dim); }
+	int dimRange(int dim) const { return _up[dim] - _lo[dim] + 1; }
+	template<int dim> bool valueInRange(int val) const { return valueInRange(val, dim); }
+	bool valueInRange(int val, int dim) const { return val >= _lo[dim] && val <= _up[dim]; }
+	template<int dim> int setValueInRange(int val) const { return setValueInRange(val, dim); }
+	int setValueInRange(int val, int dim) const { return std::abs(val % dimRange(dim)) + _lo[dim]; }
+	template<int dim> int idx2disp(int idx) const { return _lo[dim] + idx; }
+	int idx2disp(int dim, int idx) const { return _lo[dim] + idx; }
+	template<int dim> int disp2idx(int disp) const { return disp - _lo[dim]; }
+	int disp2idx(int dim, int disp) const { return disp - _lo[dim]; }
+private:
+	std::array<disp_t, nDim> _up, _lo;
+	bool _valid;
+};
+
+namespace B200Detail {
+inline std::array<int32_t, 4> search4(searchOffset<2> const& s) {
+	return {s.lowerOffset(0), s.upperOffset(0), s.lowerOffset(1), s.upperOffset(1)};
+}
+} // namespace B200Detail
 
 template<dispExtractionStartegy strategy, class T_CV>
 Multidim::Array<disp_t, 2> extractSelectedIndex(Multidim::Array<T_CV, 3> const& costVolume) {
@@ -67,6 +112,42 @@ Multidim::Array<T_IB, 3> extractInBoundDomain(Multidim::Array<disp_t, 2> const& 
 		return Multidim::Array<T_IB, 3>();
 	if constexpr (std::is_same_v<T_IB, float>) return mask;
 	else return mask.template cast<T_IB>();
+}
+
+// :466-509 — (H,W,D1,D2) -> (H,W,2), last extremum in row-major (d1,d2) order
+template<dispExtractionStartegy strategy, class T_CV>
+Multidim::Array<disp_t, 3> extractSelected2dIndex(Multidim::Array<T_CV, 4> const& costVolume) {
+	static_assert(std::is_same_v<T_CV, float>, "2-D search volumes are float on the B200 library");
+	auto sh = costVolume.shape();
+	Multidim::Array<disp_t, 3> out(sh[0], sh[1], 2);
+	stevi_array v = B200::describe(costVolume), o = B200::describe(out);
+	if (!B200::ok(stevi_wta_2d(B200::threadContext(), &v, int(strategy), &o))) return Multidim::Array<disp_t, 3>();
+	return out;
+}
+
+// :534-555
+template<typename DT>
+Multidim::Array<DT, 3> selected2dIndexToDisp(Multidim::Array<DT, 3> const& selectedIndex, searchOffset<2> const& offset) {
+	static_assert(std::is_same_v<DT, disp_t>, "the B200 library returns disp_t disparities");
+	Multidim::Array<DT, 3> out(selectedIndex.shape());
+	const auto so = B200Detail::search4(offset);
+	stevi_array i = B200::describe(selectedIndex), o = B200::describe(out);
+	if (!B200::ok(stevi_index2d_to_disp(B200::threadContext(), &i, so.data(), &o))) return Multidim::Array<DT, 3>();
+	return out;
+}
+
+// :677-725 (sic). The radii are uint8_t with default uint8_t(-1) = 255, as in the reference.
+template<class T_CV, dispDirection dir = dispDirection::RightToLeft>
+Multidim::Array<T_CV, 4> truncatedBidirectionaCostVolume(Multidim::Array<T_CV, 4> const& costVolume, Multidim::Array<disp_t, 3> const& selectedIndex,
+														 uint8_t cost_vol_radius0 = -1, uint8_t cost_vol_radius1 = -1) {
+	static_assert(std::is_same_v<T_CV, float>, "2-D search volumes are float on the B200 library");
+	auto sh = costVolume.shape();
+	const int r0 = cost_vol_radius0 < 1 ? 1 : cost_vol_radius0, r1 = cost_vol_radius1 < 1 ? r0 : cost_vol_radius1;
+	Multidim::Array<T_CV, 4> out(sh[0], sh[1], 2 * r0 + 1, 2 * r1 + 1);
+	stevi_array v = B200::describe(costVolume), i = B200::describe(selectedIndex), o = B200::describe(out);
+	if (!B200::ok(stevi_truncated_cost_volume_2d(B200::threadContext(), &v, &i, cost_vol_radius0, cost_vol_radius1, &o)))
+		return Multidim::Array<T_CV, 4>();
+	return out;
 }
 
 } // namespace Correlation

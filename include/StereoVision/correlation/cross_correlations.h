@@ -1,6 +1,7 @@
 // B200 facade of LibStevi's correlation/cross_correlations.h: unfoldBasedCostVolume :740-765 (the fused unfold ->
 // getFeatureVolumeForMatchFunc -> aggregateCost chain) and getFeatureVolumeForMatchFunc :645-722 on images.
-// Result layout like the reference's aggregateCost (:220): strides {W*D, 1, W}.
+// Result layout like the reference's aggregateCost (:220): strides {W*D, 1, W}. 2-D search: unfoldBased2dDisparityCostVolume
+// :794-822, result strides {W*dW*dH, 1, W*dW, W} (:340-341).
 #ifndef STEVI_B200_CORRELATION_CROSS_CORRELATIONS_H
 #define STEVI_B200_CORRELATION_CROSS_CORRELATIONS_H
 
@@ -41,6 +42,26 @@ Multidim::Array<float, 3> featureVolumeForMatchFunc(Multidim::Array<float, 2> co
 	stevi_array i = B200::describe(img), o = B200::describe(out);
 	if (!B200::ok(stevi_feature_volume(B200::threadContext(), int(matchFunc), &i, h_radius, v_radius, &o))) return Multidim::Array<float, 3>();
 	return out;
+}
+
+template<matchingFunctions matchFunc, class T_L, class T_R, int nImDim = 2, dispDirection dDir = dispDirection::RightToLeft, typename TCV = float>
+Multidim::Array<TCV, 4> unfoldBased2dDisparityCostVolume(Multidim::Array<T_L, nImDim> const& img_l, Multidim::Array<T_R, nImDim> const& img_r,
+														 uint8_t h_radius, uint8_t v_radius, searchOffset<2> const& searchWindows) {
+	static_assert(MatchingFunctionTraits<matchFunc>::onB200 && !MatchingFunctionTraits<matchFunc>::isCensusBased,
+				  "2-D search runs the float matching functions on the B200 library");
+	static_assert(nImDim == 2, "multi-channel images: unfold them and use the feature-level entry points");
+	static_assert(std::is_same_v<T_L, float> && std::is_same_v<T_R, float> && std::is_same_v<TCV, float>, "float images and costs");
+	auto l_shape = img_l.shape();
+	auto r_shape = img_r.shape();
+	if (l_shape[0] != r_shape[0] || l_shape[1] != r_shape[1]) return Multidim::Array<TCV, 4>(0, 0, 0, 0);   // :804-810
+	const int h = l_shape[0], w = l_shape[1], dH = searchWindows.dimRange(0), dW = searchWindows.dimRange(1);
+	if (dH <= 0 || dW <= 0) return Multidim::Array<TCV, 4>(0, 0, 0, 0);   // :336-338
+	Multidim::Array<TCV, 4> cv({h, w, dH, dW}, {w * dW * dH, 1, w * dW, w});
+	const auto so = B200Detail::search4(searchWindows);
+	stevi_array l = B200::describe(img_l), r = B200::describe(img_r), o = B200::describe(cv);
+	if (!B200::ok(stevi_cost_volume_2d(B200::threadContext(), int(matchFunc), &l, &r, h_radius, v_radius, so.data(), int(dDir), &o)))
+		return Multidim::Array<TCV, 4>(0, 0, 0, 0);
+	return cv;
 }
 
 } // namespace Correlation

@@ -63,6 +63,8 @@ typedef enum { STEVI_LEFT_TO_RIGHT = 0, STEVI_RIGHT_TO_LEFT = 1 } stevi_directio
 typedef enum { STEVI_TCV_SAME = 0, STEVI_TCV_REVERSED = 1, STEVI_TCV_BOTH = 2 } stevi_tcv_direction;
 /* InterpolationKernel: correlation/cost_based_refinement.h:30-35 */
 typedef enum { STEVI_EQUIANGULAR = 0, STEVI_PARABOLA = 1, STEVI_GAUSSIAN = 2 } stevi_interp_kernel;
+/* IsotropyHypothesis: correlation/cost_based_refinement.h:37-41 */
+typedef enum { STEVI_ISOTROPIC = 0, STEVI_ANISOTROPIC = 1 } stevi_isotropy;
 
 typedef struct {
 	void* data;
@@ -199,6 +201,31 @@ STEVI_API int32_t stevi_wta_2d(stevi_ctx* ctx, const stevi_array* vol, int32_t s
 
 /* selected2dIndexToDisp<disp_t> (correlation/correlation_base.h:534-555): disp(i,j,k) = idx(i,j,k) + lower offset of axis k */
 STEVI_API int32_t stevi_index2d_to_disp(stevi_ctx* ctx, const stevi_array* idx, const int32_t search[4], stevi_array* out);
+
+/* truncatedBidirectionaCostVolume<float> (correlation/correlation_base.h:677-725): cv (H,W,D1,D2) f32, idx (H,W,2) i32 ->
+ * out (H,W,2*r0+1,2*r1+1) f32 = cv(i, j, idx0+a-r0, idx1+b-r1), NaN outside the search window (:718). radius0 / radius1 are
+ * the reference's uint8_t arguments (0..255; its default uint8_t(-1) is 255): r0 = radius0 < 1 ? 1 : radius0 and
+ * r1 = radius1 < 1 ? r0 : radius1 (:689-695). */
+STEVI_API int32_t stevi_truncated_cost_volume_2d(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, int32_t radius0,
+									   int32_t radius1, stevi_array* out);
+
+/* refineDisp2dCostInterpolation<kernel, isotropHypothesis> (correlation/cost_based_refinement.h:165-369): tcv (H,W,T0,T1) f32,
+ * raw_disparity (H,W,2) i32 -> out (H,W,2) f32 = raw + (delta0, delta1). Isotropic: one refineCostTriplet per axis through
+ * the centre cell. Anisotropic: the per-column / per-row optima of the rows and columns next to the centre give two ridge
+ * lines whose intersection is the estimate (:269-353); whether the volume holds scores is read off the centre pixel of the
+ * image (:184-206). |delta| > 1 or NaN on either axis resets both to 0 (:356-360). STEVI_E_SHAPE where the reference returns
+ * an empty array (a side even or < 3, :180-182). */
+STEVI_API int32_t stevi_refine_disp_2d_cost_interp(stevi_ctx* ctx, const stevi_array* tcv, const stevi_array* raw_disparity,
+										 int32_t kernel, int32_t isotropy, stevi_array* out);
+
+/* refineDisp2dCostPatchInterpolation<kernel> (correlation/cost_based_refinement.h:371-433 over refineCostPatch :71-126):
+ * least-squares quadric through the 3x3 cells around the centre of tcv (H,W,T0,T1) f32 (their logarithms for the Gaussian
+ * kernel) and its stationary point; out (H,W,2) f32 = raw + (delta0, delta1), both reset to 0 when either is beyond one cell
+ * or NaN. kernel = STEVI_PARABOLA | STEVI_GAUSSIAN (the reference static_asserts the same, :82). The reference solves the
+ * normal equations with Eigen's general inverse; here they are solved in closed form (same estimator, rounding differs:
+ * compare with a relative tolerance of 1e-4 on well-conditioned patches). */
+STEVI_API int32_t stevi_refine_disp_2d_cost_patch_interp(stevi_ctx* ctx, const stevi_array* tcv, const stevi_array* raw_disparity,
+											   int32_t kernel, stevi_array* out);
 
 /* selectedCost<T_CV> (correlation/correlation_base.h:557-577): out(i,j) = cv(i,j,idx(i,j)); out (H,W) of cv's dtype */
 STEVI_API int32_t stevi_selected_cost(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, stevi_array* out);

@@ -24,6 +24,7 @@ COST, SCORE = 0, 1
 LEFT_TO_RIGHT, RIGHT_TO_LEFT = 0, 1
 TCV_SAME, TCV_REVERSED, TCV_BOTH = 0, 1, 2
 EQUIANGULAR, PARABOLA, GAUSSIAN = 0, 1, 2
+ISOTROPIC, ANISOTROPIC = 0, 1  # IsotropyHypothesis, cost_based_refinement.h:37-41
 SCORE_FUNCS = (CC, NCC, ZCC, ZNCC)
 
 _NP2DT = {np.dtype(np.uint8): U8, np.dtype(np.uint16): U16, np.dtype(np.int32): I32, np.dtype(np.uint32): U32,
@@ -378,6 +379,45 @@ def selected2dIndexToDisp(idx, searchWindows, ctx=None):
     out = _empty(idx, idx.shape, np.int32)
     a, o = describe(idx), describe(out)
     ctx.check(lib.stevi_index2d_to_disp(ctx.handle, ctypes.byref(a), so, ctypes.byref(o)))
+    return out
+
+
+def truncatedBidirectionaCostVolume(cv, idx, cost_vol_radius0=255, cost_vol_radius1=255, ctx=None):
+    """correlation_base.h:677-725 (sic). (H, W, D1, D2) f32 + (H, W, 2) i32 -> (H, W, 2*r0+1, 2*r1+1) f32, NaN outside the
+    search window. The radii are the reference's uint8_t arguments: its default uint8_t(-1) is 255; 0 means 1 for axis 0
+    and "same as axis 0" for axis 1."""
+    ctx = _ctx_for(ctx, cv)
+    r0 = max(int(cost_vol_radius0), 1)
+    r1 = int(cost_vol_radius1) if int(cost_vol_radius1) >= 1 else r0
+    out = _empty(cv, tuple(cv.shape[:2]) + (2 * r0 + 1, 2 * r1 + 1), np.float32)
+    a, i, o = describe(cv), describe(idx), describe(out)
+    ctx.check(lib.stevi_truncated_cost_volume_2d(ctx.handle, ctypes.byref(a), ctypes.byref(i), cost_vol_radius0, cost_vol_radius1, ctypes.byref(o)))
+    return out
+
+
+def refineDisp2dCostInterpolation(tcv, rawDisparity, kernel=PARABOLA, isotropHypothesis=ISOTROPIC, ctx=None):
+    """cost_based_refinement.h:165-369. (H, W, T0, T1) f32 + (H, W, 2) i32 -> (H, W, 2) f32. Returns None where the reference
+    returns an empty array (a side of the neighbourhood even or < 3)."""
+    ctx = _ctx_for(ctx, tcv)
+    out = _empty(tcv, tuple(tcv.shape[:2]) + (2,), np.float32)
+    t, i, o = describe(tcv), describe(rawDisparity), describe(out)
+    rc = lib.stevi_refine_disp_2d_cost_interp(ctx.handle, ctypes.byref(t), ctypes.byref(i), kernel, isotropHypothesis, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def refineDisp2dCostPatchInterpolation(tcv, rawDisparity, kernel=PARABOLA, ctx=None):
+    """cost_based_refinement.h:371-433: stationary point of the least-squares quadric through the 3x3 centre cells.
+    Returns None where the reference returns an empty array; Equiangular is rejected (the reference static_asserts)."""
+    ctx = _ctx_for(ctx, tcv)
+    out = _empty(tcv, tuple(tcv.shape[:2]) + (2,), np.float32)
+    t, i, o = describe(tcv), describe(rawDisparity), describe(out)
+    rc = lib.stevi_refine_disp_2d_cost_patch_interp(ctx.handle, ctypes.byref(t), ctypes.byref(i), kernel, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
     return out
 
 

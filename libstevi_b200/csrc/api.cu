@@ -190,6 +190,41 @@ int32_t stevi_index2d_to_disp(stevi_ctx* c, const stevi_array* idx, const int32_
 	return st.finish();
 }
 
+int32_t stevi_truncated_cost_volume_2d(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, int32_t radius0, int32_t radius1,
+									   stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vc, vi, vo;
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(truncated_cv2d_dev(c, vc, vi, radius0, radius1, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_disp_2d_cost_interp(stevi_ctx* c, const stevi_array* tcv, const stevi_array* raw, int32_t kernel, int32_t isotropy,
+										 stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vt, vi, vo;
+	STEVI_TRY(st.in(tcv, vt, "tcv"));
+	STEVI_TRY(st.in(raw, vi, "raw_disparity"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine2d_interp_dev(c, vt, vi, kernel, isotropy, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_disp_2d_cost_patch_interp(stevi_ctx* c, const stevi_array* tcv, const stevi_array* raw, int32_t kernel, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vt, vi, vo;
+	STEVI_TRY(st.in(tcv, vt, "tcv"));
+	STEVI_TRY(st.in(raw, vi, "raw_disparity"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine2d_patch_dev(c, vt, vi, kernel, vo));
+	return st.finish();
+}
+
 int32_t stevi_selected_cost(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);

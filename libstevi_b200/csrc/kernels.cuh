@@ -75,6 +75,11 @@ int32_t refine_interp_dev(stevi_ctx* c, const View& tcv, const View& idx, int ke
 // truncatedCostVolume<Same>(radius 1) + refineDispCostInterpolation in one pass over the winners; tcv_out optional
 int32_t refine_from_cv_dev(stevi_ctx* c, const View& cv, const View& idx, int hr, int vr, int kernel, const View* tcv_out, const View& out);
 
+// 2-D search: truncatedBidirectionaCostVolume, refineDisp2dCostInterpolation
+int32_t truncated_cv2d_dev(stevi_ctx* c, const View& cv, const View& idx, int radius0, int radius1, const View& out);
+int32_t refine2d_interp_dev(stevi_ctx* c, const View& tcv, const View& raw, int kernel, int isotropy, const View& out);
+int32_t refine2d_patch_dev(stevi_ctx* c, const View& tcv, const View& raw, int kernel, const View& out);
+
 // hier.cu
 int32_t avgpool_dev(stevi_ctx* c, const View& img, int win_h, int win_v, const View& out);
 // band == nullptr: whole images; else the images / guide are row bands placed in global coordinates (c_api.h: stevi_band)

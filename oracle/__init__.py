@@ -239,6 +239,29 @@ class _Checker:
         rc = self._f("refine_disp_cost_interp")(_p(_c(tcv, np.float32)), _p(_c(idx, np.int32)), h, w, T, kernel, _p(out))
         return out if rc == 0 else None
 
+    def truncated_cost_volume_2d(self, cv, idx, radius0=255, radius1=255):
+        """truncatedBidirectionaCostVolume; the radii are the reference's uint8_t arguments (default uint8_t(-1) = 255)."""
+        h, w, d1, d2 = cv.shape
+        r0 = max(radius0 & 255, 1)
+        r1 = (radius1 & 255) or r0
+        out = np.empty((h, w, 2 * r0 + 1, 2 * r1 + 1), np.float32)
+        self._f("truncated_cost_volume_2d_f32")(_p(_c(cv, np.float32)), _p(_c(idx, np.int32)), h, w, d1, d2, radius0, radius1, _p(out))
+        return out
+
+    def refine_2d(self, tcv, raw, kernel=PARABOLA, anisotropic=False):
+        """refineDisp2dCostInterpolation; None where the reference returns an empty array."""
+        h, w, n0, n1 = tcv.shape
+        out = np.empty((h, w, 2), np.float32)
+        rc = self._f("refine_disp_2d_cost_interp")(_p(_c(tcv, np.float32)), _p(_c(raw, np.int32)), h, w, n0, n1, kernel, int(anisotropic), _p(out))
+        return out if rc == 0 else None
+
+    def refine_2d_patch(self, tcv, raw, kernel=PARABOLA):
+        """refineDisp2dCostPatchInterpolation (port only: the compiled reference needs Eigen for this one)."""
+        h, w, n0, n1 = tcv.shape
+        out = np.empty((h, w, 2), np.float32)
+        rc = self._f("refine_disp_2d_cost_patch_interp")(_p(_c(tcv, np.float32)), _p(_c(raw, np.int32)), h, w, n0, n1, kernel, _p(out))
+        return out if rc == 0 else None
+
     def avgpool2(self, img):
         h, w = img.shape
         out = np.empty(((h + 1) // 2, (w + 1) // 2), np.float32)

@@ -305,6 +305,34 @@ int ref_refine_disp_cost_interp(const float* tcv, const int32_t* idx, int h, int
 	return 0;
 }
 
+// correlation_base.h:677-725 truncatedBidirectionaCostVolume; cv (h, w, d1, d2) C-order, idx (h, w, 2); out (h, w, 2*r0+1, 2*r1+1)
+// with r0 = max(radius0, 1) and r1 = radius1 < 1 ? r0 : radius1 (the uint8_t arguments of the reference)
+int ref_truncated_cost_volume_2d_f32(const float* cv, const int32_t* idx, int h, int w, int d1, int d2, int radius0, int radius1, float* out) {
+	MD::Array<float, 4> CV(const_cast<float*>(cv), {h, w, d1, d2}, {w * d1 * d2, d1 * d2, d2, 1}, false);
+	MD::Array<float, 4> t = truncatedBidirectionaCostVolume<float>(CV, view3(idx, h, w, 2), uint8_t(radius0), uint8_t(radius1));
+	auto s = t.shape();
+	for (int i = 0; i < s[0]; i++) for (int j = 0; j < s[1]; j++) for (int a = 0; a < s[2]; a++) for (int b = 0; b < s[3]; b++)
+		out[((size_t(i) * s[1] + j) * s[2] + a) * s[3] + b] = t.valueUnchecked(i, j, a, b);
+	return 0;
+}
+
+// cost_based_refinement.h:165-369 refineDisp2dCostInterpolation<kernel, isotropy>; tcv (h, w, n0, n1) C-order, raw (h, w, 2);
+// returns 1 (out untouched) when the reference returns an empty array
+int ref_refine_disp_2d_cost_interp(const float* tcv, const int32_t* raw, int h, int w, int n0, int n1, int kernel, int anisotropic, float* out) {
+	MD::Array<float, 4> T(const_cast<float*>(tcv), {h, w, n0, n1}, {w * n0 * n1, n0 * n1, n1, 1}, false);
+	auto I = view3(raw, h, w, 2);
+	MD::Array<float, 3> r;
+#define R2D_CASE(K) r = anisotropic ? refineDisp2dCostInterpolation<InterpolationKernel::K, IsotropyHypothesis::Anisotropic>(T, I) \
+							   : refineDisp2dCostInterpolation<InterpolationKernel::K, IsotropyHypothesis::Isotropic>(T, I)
+	if (kernel == int(InterpolationKernel::Equiangular)) R2D_CASE(Equiangular);
+	else if (kernel == int(InterpolationKernel::Parabola)) R2D_CASE(Parabola);
+	else R2D_CASE(Gaussian);
+#undef R2D_CASE
+	if (r.empty()) return 1;
+	out3(r, out);
+	return 0;
+}
+
 // interpolation/downsampling.h:67-118; out is (ceil(h/2), ceil(w/2))
 int ref_avgpool2_f32(const float* img, int h, int w, float* out) {
 	out2(Interpolation::averagePoolingDownsample<float, float>(view2(img, h, w), Interpolation::DownSampleWindows(2)), out);

@@ -567,6 +567,122 @@ int orc_refine_disp_cost_interp(const float* tcv, const int32_t* idx, int h, int
 	return 0;
 }
 
+/* correlation_base.h:677-725 truncatedBidirectionaCostVolume: the (2*r0+1) x (2*r1+1) cells around the 2-D winner, NaN where an
+ * index leaves the search window (valueOrAlt, :718). The radii are uint8_t in the reference: 0 becomes 1 for axis 0 (:689-691)
+ * and "same as axis 0" for axis 1 (:693-695). cv (h, w, d1, d2), idx (h, w, 2), out (h, w, 2*r0+1, 2*r1+1), all C-order. */
+int orc_truncated_cost_volume_2d_f32(const float* cv, const int32_t* idx, int h, int w, int d1, int d2, int radius0, int radius1, float* out) {
+	int r0 = radius0 & 255, r1 = radius1 & 255;
+	if (r0 < 1) r0 = 1;
+	if (r1 < 1) r1 = r0;
+	int n0 = 2 * r0 + 1, n1 = 2 * r1 + 1;
+	for (size_t p = 0; p < (size_t)h * w; p++) {
+		const float* c = cv + p * d1 * d2;
+		float* o = out + p * n0 * n1;
+		for (int a = 0; a < n0; a++) for (int b = 0; b < n1; b++) {
+			int p0 = idx[2 * p] + a - r0, p1 = idx[2 * p + 1] + b - r1;
+			o[a * n1 + b] = (p0 >= 0 && p0 < d1 && p1 >= 0 && p1 < d2) ? c[p0 * d2 + p1] : nanf("");
+		}
+	}
+	return 0;
+}
+
+/* cost_based_refinement.h:208-246: last extremum (`<=` / `>=`) along axis 0 (fixed column `col` of axis 1) or along axis 1 */
+static int tcv_arg_best(const float* c, int n, int stride, int score) {
+	float best = score ? -INFINITY : INFINITY;
+	int arg = 0;
+	for (int a = 0; a < n; a++) {
+		float x = c[a * stride];
+		if (score ? (x >= best) : (x <= best)) { best = x; arg = a; }
+	}
+	return arg;
+}
+
+/* cost_based_refinement.h:165-369 refineDisp2dCostInterpolation<kernel, isotropy>. tcv (h, w, n0, n1), raw (h, w, 2),
+ * out (h, w, 2) C-order. Returns 1 (reference: empty array, :180-182) when a side is even or < 3. Whether the volume holds
+ * scores is guessed from the CENTRE pixel of the image (:184-206): any of its four neighbours below the centre cell. The
+ * isotropic estimate is one triplet per axis (:256-267); the anisotropic one (:269-353) fits the ridge of the per-row and
+ * per-column optima through the three rows / columns around the centre and intersects the two lines. Estimates beyond one
+ * cell, or NaN, are dropped (:356-360). */
+int orc_refine_disp_2d_cost_interp(const float* tcv, const int32_t* raw, int h, int w, int n0, int n1, int kernel, int anisotropic, float* out) {
+	int r0 = (n0 - 1) / 2, r1 = (n1 - 1) / 2;
+	if (r0 < 1 || r1 < 1 || 2 * r0 + 1 != n0 || 2 * r1 + 1 != n1) return 1;
+	int score = 0;
+	if (h > 0 && w > 0) {
+		const float* c = tcv + ((size_t)(h / 2) * w + (w / 2)) * n0 * n1;
+		float v0 = c[r0 * n1 + r1];
+		if (v0 > c[(r0 + 1) * n1 + r1]) score = 1;
+		if (v0 > c[(r0 - 1) * n1 + r1]) score = 1;
+		if (v0 > c[r0 * n1 + r1 + 1]) score = 1;
+		if (v0 > c[r0 * n1 + r1 - 1]) score = 1;
+	}
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		size_t p = (size_t)i * w + j;
+		const float* c = tcv + p * n0 * n1;
+#define TC(a, b) c[(a) * n1 + (b)]
+		float delta0, delta1;
+		float d0c = orc_refine_cost_triplet(kernel, TC(r0 - 1, r1), TC(r0, r1), TC(r0 + 1, r1));
+		float d1c = orc_refine_cost_triplet(kernel, TC(r0, r1 - 1), TC(r0, r1), TC(r0, r1 + 1));
+		if (!anisotropic) {
+			delta0 = d0c; delta1 = d1c;
+		} else {
+			float delta0_0 = d0c, delta0_2 = d0c, delta1_0 = d1c, delta1_2 = d1c;
+			int a = tcv_arg_best(c + (r1 - 1), n0, n1, score);
+			if (a > 0 && a < n0 - 1) delta0_0 = (float)(a - r0) + orc_refine_cost_triplet(kernel, TC(a - 1, r1 - 1), TC(a, r1 - 1), TC(a + 1, r1 - 1));
+			a = tcv_arg_best(c + (r1 + 1), n0, n1, score);
+			if (a > 0 && a < n0 - 1) delta0_2 = (float)(a - r0) + orc_refine_cost_triplet(kernel, TC(a - 1, r1 + 1), TC(a, r1 + 1), TC(a + 1, r1 + 1));
+			float a0 = (delta0_2 - delta0_0) / 2;
+			float b0 = (delta0_0 + d0c + delta0_2) / 3;
+			a = tcv_arg_best(c + (r0 - 1) * n1, n1, 1, score);
+			if (a > 0 && a < n1 - 1) delta1_0 = (float)(a - r1) + orc_refine_cost_triplet(kernel, TC(r0 - 1, a - 1), TC(r0 - 1, a), TC(r0 - 1, a + 1));
+			a = tcv_arg_best(c + (r0 + 1) * n1, n1, 1, score);
+			if (a > 0 && a < n1 - 1) delta1_2 = (float)(a - r1) + orc_refine_cost_triplet(kernel, TC(r0 + 1, a - 1), TC(r0 + 1, a), TC(r0 + 1, a + 1));
+			float a1 = (delta1_2 - delta1_0) / 2;
+			float b1 = (delta1_0 + d1c + delta1_2) / 3;
+			/* the reference's Release build (g++ -O3 on an FMA target: -ffp-contract=fast is the C++ default) contracts these
+			 * three products; fmaf states that explicitly so the restatement is bit-identical to oracle/_ref */
+			float den = fmaf(-a0, a1, 1.f);
+			delta0 = fmaf(a0, b1, b0) / den;
+			delta1 = fmaf(a1, b0, b1) / den;
+		}
+#undef TC
+		if (fabsf(delta0) > 1 || fabsf(delta1) > 1 || isnan(delta0) || isnan(delta1)) { delta0 = 0; delta1 = 0; }
+		out[2 * p] = (float)raw[2 * p] + delta0;
+		out[2 * p + 1] = (float)raw[2 * p + 1] + delta1;
+	}
+	return 0;
+}
+
+/* cost_based_refinement.h:71-126 refineCostPatch + :371-433 refineDisp2dCostPatchInterpolation. PARITY UNPINNED AT THE BIT
+ * LEVEL: the reference evaluates ((A^T A)^-1 A^T) L and a 2x2 inverse with Eigen, which is not in this image (the stand-in
+ * headers are parse-level only), so the compiled reference cannot run this function. This restates the same estimator in
+ * double precision with the normal equations solved in closed form (on the 3x3 grid they decouple into row, column and
+ * diagonal sums); it is pinned by the reference's own known-answer test (testCostRefinement.cpp:168-227) and by a float64
+ * numpy least-squares solve in tests/. kernel: K_PARABOLA or K_GAUSSIAN (logarithms of the costs). Returns 1 where the
+ * reference returns an empty array (:386-388), 2 for the Equiangular kernel (static_assert :82). */
+int orc_refine_disp_2d_cost_patch_interp(const float* tcv, const int32_t* raw, int h, int w, int n0, int n1, int kernel, float* out) {
+	int r0 = (n0 - 1) / 2, r1 = (n1 - 1) / 2;
+	if (r0 < 1 || r1 < 1 || 2 * r0 + 1 != n0 || 2 * r1 + 1 != n1) return 1;
+	if (kernel != K_PARABOLA && kernel != K_GAUSSIAN) return 2;
+	for (size_t p = 0; p < (size_t)h * w; p++) {
+		const float* c = tcv + p * n0 * n1;
+		double L[3][3];
+		for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) {
+			float x = c[(r0 - 1 + a) * n1 + (r1 - 1 + b)];
+			L[a][b] = kernel == K_GAUSSIAN ? (double)logf(x) : (double)x;
+		}
+		double rm = L[0][0] + L[0][1] + L[0][2], rz = L[1][0] + L[1][1] + L[1][2], rp = L[2][0] + L[2][1] + L[2][2];
+		double cm = L[0][0] + L[1][0] + L[2][0], cz = L[0][1] + L[1][1] + L[2][1], cp = L[0][2] + L[1][2] + L[2][2];
+		double qa = (rm + rp - 2 * rz) / 6, qg = (cm + cp - 2 * cz) / 6, qb = (L[0][0] + L[2][2] - L[0][2] - L[2][0]) / 4;
+		double qd = (rp - rm) / 6, qe = (cp - cm) / 6, det = 4 * qa * qg - qb * qb;
+		float delta0 = (float)((qb * qe - 2 * qg * qd) / det), delta1 = (float)((qb * qd - 2 * qa * qe) / det);
+		if (fabsf(delta0) > 1 || fabsf(delta1) > 1 || isnan(delta0) || isnan(delta1)) { delta0 = 0; delta1 = 0; }
+		out[2 * p] = (float)raw[2 * p] + delta0;
+		out[2 * p + 1] = (float)raw[2 * p + 1] + delta1;
+	}
+	return 0;
+}
+
 /* interpolation/downsampling.h:67-118 with DownSampleWindows(2): out (ceil(h/2), ceil(w/2)); the mean is over
  * the in-image part of each 2x2 window (offsets are 0 for window 2: hRem/2 == 0). Accumulates in float, in
  * row-major window order, then divides by the count. */

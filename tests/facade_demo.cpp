@@ -47,6 +47,26 @@ int main() {
 	for (int i = 4; i < h - 4; i++) for (int j = 4; j < w - 24; j++) { n++; good += zi.valueUnchecked(i, j) == 5; }
 	std::printf("zncc_idx %.0f\nzncc_match %.3f\nrefined %.3f\n", checksum(zi), double(good) / n, checksum(ref));
 
+	// 2-D search chain, as test/testCorrelation2d.cpp:76-127 and the refinement callers use it
+	Multidim::Array<float, 2> l2(h, w), r2(h, w);
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) l2.at<Multidim::AccessCheck::Nocheck>(i, j) = 0.f;
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		r2.at<Multidim::AccessCheck::Nocheck>(i, j) = float(mix(77777ull + uint64_t(i) * w + j) >> 40) / float(1 << 24);
+		int it = i + 1, jt = j - 2;   // the source pixel (i, j) of r2 is found at (i + 1, j - 2) in l2
+		if (it >= 0 && it < h && jt >= 0 && jt < w) l2.at<Multidim::AccessCheck::Nocheck>(it, jt) = r2.valueUnchecked(i, j);
+	}
+	searchOffset<2> window(-2, 2, -3, 3);
+	auto cv2 = unfoldBased2dDisparityCostVolume<matchingFunctions::ZNCC, float, float>(l2, r2, 2, 2, window);
+	auto i2 = extractSelected2dIndex<dispExtractionStartegy::Score>(cv2);
+	auto d2 = selected2dIndexToDisp(i2, window);
+	auto t2 = truncatedBidirectionaCostVolume(cv2, i2, 1, 1);
+	auto f2 = refineDisp2dCostInterpolation<InterpolationKernel::Parabola, IsotropyHypothesis::Anisotropic>(t2, d2);
+	int good2 = 0, n2 = 0;
+	for (int i = 5; i < h - 5; i++) for (int j = 6; j < w - 6; j++) { n2++; good2 += d2.valueUnchecked(i, j, 0) == 1 && d2.valueUnchecked(i, j, 1) == -2; }
+	std::printf("search2d_match %.3f\nsearch2d_idx %.0f\nsearch2d_refined %.3f\n", double(good2) / n2, checksum(i2), checksum(f2));
+	auto even2 = refineDisp2dCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 4>(h, w, 3, 4), d2);
+	std::printf("even_side_empty %d\n", int(even2.empty()));
+
 	auto hier = hiearchicalTruncatedCostVolume<matchingFunctions::ZNCC, 2>(lf, rf, 2, 2, D, 2);
 	std::printf("hier_disp %.0f\n", checksum(hier.disp_estimate));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);

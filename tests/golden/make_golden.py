@@ -67,7 +67,8 @@ def main():
 
 
 def main_2d():
-    """2-D search: unfoldBased2dDisparityCostVolume, extractSelected2dIndex, selected2dIndexToDisp."""
+    """2-D search: unfoldBased2dDisparityCostVolume, extractSelected2dIndex, selected2dIndexToDisp,
+    truncatedBidirectionaCostVolume, refineDisp2dCostInterpolation."""
     ref = O.ref
     assert ref is not None, "build oracle/_ref first (make -C oracle ref)"
     H, W = 11, 15
@@ -81,6 +82,14 @@ def main_2d():
         idx = ref.wta_2d(out[f"cv2d_{mf}_1"], strategy)
         out[f"wta2d_{mf}"] = idx
         out[f"disp2d_{mf}"] = ref.index2d_to_disp(idx, search)
+    # truncatedBidirectionaCostVolume + refineDisp2dCostInterpolation (all kernels, both isotropy hypotheses)
+    for mf in (O.ZNCC, O.SSD):
+        for r0, r1 in ((1, 1), (2, 1), (1, 0)):
+            t = ref.truncated_cost_volume_2d(out[f"cv2d_{mf}_1"], out[f"wta2d_{mf}"], r0, r1)
+            out[f"tcv2d_{mf}_{r0}_{r1}"] = t
+            for kernel in (O.EQUIANGULAR, O.PARABOLA, O.GAUSSIAN):
+                for aniso in (0, 1):
+                    out[f"refined2d_{mf}_{r0}_{r1}_{kernel}_{aniso}"] = ref.refine_2d(t, out[f"disp2d_{mf}"], kernel, aniso)
     path = os.path.join(HERE, "reference_outputs_2d.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes")

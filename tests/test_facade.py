@@ -32,7 +32,9 @@ def test_facade_headers_carry_the_reference_names():
                  "OffsetedCostVolume", "averagePoolingDownsample", "DownSampleWindows", "censusTransform2D", "censusFeatures",
                  "UnFoldCompressor", "channelFromCord", "dispExtractionStartegy", "truncatedCostVolumeDirection",
                  "matchingFunctions", "MatchingFunctionTraits", "hamming_cv_t", "census_data_t", "InterpolationKernel",
-                 "sgmDirections", "PaddingMargins", "disp_t"):
+                 "sgmDirections", "PaddingMargins", "disp_t", "searchOffset", "unfoldBased2dDisparityCostVolume",
+                 "extractSelected2dIndex", "selected2dIndexToDisp", "truncatedBidirectionaCostVolume", "refineDisp2dCostInterpolation",
+                 "IsotropyHypothesis"):
         assert name in text, name
 
 
@@ -66,7 +68,8 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
     cv, sg, disp = api.censusSgmPipeline(l8, r8, 4, 3, D, 10, 120, 100, 8, return_volumes=True, layout="c", ctx=ctx)
     # the demo walks arrays with IndexBlock::moveToNextIndex; the order only matters through the position weights, so
     # compare order-free sums as well
-    assert float(got["mismatch_empty"]) == 1 and float(got["even_depth_empty"]) == 1
+    assert float(got["mismatch_empty"]) == 1 and float(got["even_depth_empty"]) == 1 and float(got["even_side_empty"]) == 1
+    assert float(got["search2d_match"]) > 0.95
     zn = api.unfoldBasedCostVolume(api.ZNCC, lf, rf, 2, 2, D, layout="c", ctx=ctx)
     zi = api.extractSelectedIndex(zn, api.SCORE, ctx=ctx)
     assert abs(float(got["zncc_match"]) - float((zi[4:h - 4, 4:w - 24] == 5).mean())) < 1e-3

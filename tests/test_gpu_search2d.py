@@ -1,9 +1,15 @@
 """GPU parity of the 2-D search functions: unfoldBased2dDisparityCostVolume,
-extractSelected2dIndex, selected2dIndexToDisp, against the CPU oracle, the golden vectors of the compiled reference and
+extractSelected2dIndex, selected2dIndexToDisp, truncatedBidirectionaCostVolume, refineDisp2dCostInterpolation and
+refineDisp2dCostPatchInterpolation, against the CPU oracle, the golden vectors of the compiled reference and
 restatements of the reference's own tests (test/unittests/testCorrelation2d.cpp).
 
 Tolerance: the kernel sums in the reference's channel order (the `exact_sums` path of the 1-D volumes): 2e-6 of the
-largest magnitude (1.0 for the normalised correlations), NaNs in the same cells. Indices and disparities are bit-exact.
+largest magnitude (1.0 for the normalised correlations), NaNs in the same cells. Indices, disparities and the truncated
+volume (a gather) are bit-exact. refineDisp2dCostInterpolation: bit-exact against the oracle and the golden vectors of the
+compiled reference for the Equiangular and Parabola kernels (correctly rounded operations in the same order); 2e-6 absolute
+for the Gaussian kernel (logf of the device vs glibc, the 1-D refinement's bound; 1e-4 for its anisotropic estimate, whose line
+intersection amplifies those last-bit differences). Patch interpolation: 1e-4 absolute
+against the float64 oracle on patches with a clear extremum (closed-form float32 solve of the normal equations).
 """
 import os
 
@@ -11,7 +17,7 @@ import numpy as np
 import pytest
 
 from libstevi_b200 import synth
-from test_oracle_pinning import check_2d_disparity, check_2d_matching
+from test_oracle_pinning import check_2d_cost_refinement, check_2d_disparity, check_2d_matching, lstsq_patch_deltas
 
 pytestmark = pytest.mark.gpu
 
@@ -121,3 +127,115 @@ def test_ref_test2dMatching_and_test2dDisparity(api, ctx, oracle, name, hr, vr, 
     check_2d_matching(cv2d, mf, hr, vr, dw, dh, 77)
     check_2d_disparity(cv2d, lambda v, s: api.extractSelected2dIndex(v, s, ctx=ctx),
                        lambda i, s: api.selected2dIndexToDisp(i, s, ctx=ctx), mf, hr, vr, 91)
+
+
+# ---- truncatedBidirectionaCostVolume, refineDisp2dCostInterpolation, refineDisp2dCostPatchInterpolation ------------------
+
+def refined_close(got, want, kernel, oracle, aniso=0):
+    assert got.shape == want.shape and got.dtype == np.float32
+    if kernel == oracle.GAUSSIAN:
+        # a delta next to the |delta| > 1 cut may fall on either side of it: compare where both kept their estimate
+        kept = (got != np.round(got)) & (want != np.round(want))
+        # the line intersection of the anisotropic estimate divides by 1 - a0*a1 and amplifies the last-bit differences of logf
+        assert np.max(np.abs(got - want)[kept], initial=0.0) <= (1e-4 if aniso else 2e-6)
+        assert np.mean((got != want) & ~kept) <= 0.01
+    else:
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("name,strategy", [("ZNCC", 1), ("SSD", 0)])
+def test_truncation_and_refinement_2d_golden(api, ctx, oracle, name, strategy):
+    mf = getattr(oracle, name)
+    cv, idx, disp = G2[f"cv2d_{mf}_1"], G2[f"wta2d_{mf}"], G2[f"disp2d_{mf}"]
+    for r0, r1 in ((1, 1), (2, 1), (1, 0)):
+        t = api.truncatedBidirectionaCostVolume(cv, idx, r0, r1, ctx=ctx)
+        assert np.array_equal(t, G2[f"tcv2d_{mf}_{r0}_{r1}"], equal_nan=True)
+        for kernel in (oracle.EQUIANGULAR, oracle.PARABOLA, oracle.GAUSSIAN):
+            for aniso in (0, 1):
+                got = api.refineDisp2dCostInterpolation(t, disp, kernel, aniso, ctx=ctx)
+                refined_close(got, G2[f"refined2d_{mf}_{r0}_{r1}_{kernel}_{aniso}"], kernel, oracle, aniso)
+
+
+@pytest.mark.parametrize("name,strategy", [("ZNCC", 1), ("NCC", 1), ("SAD", 0), ("ZSSD", 0)])
+def test_truncation_and_refinement_2d_match_oracle(api, ctx, oracle, name, strategy):
+    L, R = synth.random_image(37, 150, 41), synth.random_image(37, 150, 42)
+    search = (-2, 3, -4, 4)
+    cv = oracle.port.cost_volume_2d(getattr(oracle, name), L, R, 2, 2, search)
+    idx = oracle.port.wta_2d(cv, strategy)
+    ref_layout = np.ascontiguousarray(cv.transpose(0, 2, 3, 1)).transpose(0, 3, 1, 2)     # the reference's cost-volume strides
+    for r0, r1 in ((1, 1), (0, 0), (3, 0), (1, 2), (2, 5)):
+        want = oracle.port.truncated_cost_volume_2d(cv, idx, r0, r1)
+        for vol in (cv, ref_layout):
+            t = api.truncatedBidirectionaCostVolume(vol, idx, r0, r1, ctx=ctx)
+            assert t.shape == want.shape and np.array_equal(t, want, equal_nan=True)
+        for kernel in (oracle.EQUIANGULAR, oracle.PARABOLA, oracle.GAUSSIAN):
+            for aniso in (0, 1):
+                refined_close(api.refineDisp2dCostInterpolation(want, idx, kernel, aniso, ctx=ctx), oracle.port.refine_2d(want, idx, kernel, aniso), kernel, oracle, aniso)
+        # strided operands: the neighbourhood axes first in memory
+        ts = np.ascontiguousarray(want.transpose(2, 3, 0, 1)).transpose(2, 3, 0, 1)
+        assert np.array_equal(api.refineDisp2dCostInterpolation(ts, idx, oracle.PARABOLA, 1, ctx=ctx), oracle.port.refine_2d(want, idx, oracle.PARABOLA, 1))
+
+
+def test_refinement_2d_reads_the_centre_pixel_for_the_volume_kind(api, ctx, oracle):
+    """cost_based_refinement.h:184-206: scores vs costs is decided from the image's centre pixel alone; the anisotropic
+    estimate of every other pixel follows that decision."""
+    rng = np.random.default_rng(3)
+    t = rng.uniform(0.1, 1.0, (6, 9, 5, 5)).astype(np.float32)
+    raw = rng.integers(-3, 4, (6, 9, 2)).astype(np.int32)
+    for centre_is_peak in (False, True):
+        t[3, 4] = rng.uniform(0.4, 0.6, (5, 5))
+        t[3, 4, 2, 2] = 0.9 if centre_is_peak else 0.1
+        want = oracle.port.refine_2d(t, raw, oracle.PARABOLA, 1)
+        assert np.array_equal(api.refineDisp2dCostInterpolation(t, raw, oracle.PARABOLA, 1, ctx=ctx), want)
+    t[0, 0, 1, 2] = np.nan      # NaN in a triplet: both deltas dropped
+    got = api.refineDisp2dCostInterpolation(t, raw, oracle.EQUIANGULAR, 0, ctx=ctx)
+    assert np.array_equal(got[0, 0], raw[0, 0].astype(np.float32))
+    assert np.array_equal(got, oracle.port.refine_2d(t, raw, oracle.EQUIANGULAR, 0))
+
+
+def test_ref_test2dCostRefinement(api, ctx):
+    """testCostRefinement.cpp:59-227 run against the CUDA functions."""
+    check_2d_cost_refinement(lambda t, raw, k, a: api.refineDisp2dCostInterpolation(t, raw, k, a, ctx=ctx),
+                             lambda t, raw, k: api.refineDisp2dCostPatchInterpolation(t, raw, k, ctx=ctx), 5)
+
+
+def test_patch_refinement_matches_oracle(api, ctx, oracle):
+    rng = np.random.default_rng(12)
+    t = rng.uniform(0.5, 2.0, (40, 150, 5, 3)).astype(np.float32)
+    t[:, :, 2, 1] = 0.1
+    raw = rng.integers(-5, 6, (40, 150, 2)).astype(np.int32)
+    for kernel in (oracle.PARABOLA, oracle.GAUSSIAN):
+        want = oracle.port.refine_2d_patch(t, raw, kernel)
+        got = api.refineDisp2dCostPatchInterpolation(t, raw, kernel, ctx=ctx)
+        kept = (got != raw) .all(axis=2) & (want != raw).all(axis=2)
+        assert kept.mean() > 0.6
+        assert np.max(np.abs(got - want)[kept]) <= 1e-4
+        d = got[0, 0] - raw[0, 0]
+        ref64 = lstsq_patch_deltas(np.log(t[0, 0, 1:4]) if kernel == oracle.GAUSSIAN else t[0, 0, 1:4])
+        if np.all(np.abs(ref64) < 0.99):
+            assert np.allclose(d, ref64, atol=1e-4)
+    with pytest.raises(api.SteviError) as e:       # cost_based_refinement.h:82 static_assert
+        api.refineDisp2dCostPatchInterpolation(t, raw, oracle.EQUIANGULAR, ctx=ctx)
+    assert e.value.status == api.E_ARG
+
+
+def test_refinement_2d_shape_rules_and_device_operands(api, ctx, oracle):
+    torch = pytest.importorskip("torch")
+    z = np.zeros((3, 3, 2), np.int32)
+    for shape in ((3, 3, 4, 3), (3, 3, 3, 1), (3, 3, 3, 6)):      # cost_based_refinement.h:180-182, :386-388: empty array
+        assert api.refineDisp2dCostInterpolation(np.zeros(shape, np.float32), z, ctx=ctx) is None
+        assert api.refineDisp2dCostPatchInterpolation(np.zeros(shape, np.float32), z, ctx=ctx) is None
+    L, R = synth.random_image(64, 200, 51), synth.random_image(64, 200, 52)
+    search = (-2, 2, -3, 3)
+    tctx = api.Context(0, torch_stream=True)
+    cv = api.unfoldBased2dDisparityCostVolume(api.ZNCC, torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda(), 2, 2, search, ctx=tctx)
+    idx = api.extractSelected2dIndex(cv, api.SCORE, ctx=tctx)
+    t = api.truncatedBidirectionaCostVolume(cv, idx, 1, 1, ctx=tctx)
+    disp = api.selected2dIndexToDisp(idx, search, ctx=tctx)
+    ref = api.refineDisp2dCostInterpolation(t, disp, api.PARABOLA, api.ANISOTROPIC, ctx=tctx)
+    torch.cuda.synchronize()
+    cvh = cv.cpu().numpy()
+    want_t = oracle.port.truncated_cost_volume_2d(np.ascontiguousarray(cvh), idx.cpu().numpy(), 1, 1)
+    assert np.array_equal(t.cpu().numpy(), want_t, equal_nan=True)
+    assert np.array_equal(ref.cpu().numpy(), oracle.port.refine_2d(want_t, disp.cpu().numpy(), oracle.PARABOLA, 1))
+    tctx.close()

@@ -233,6 +233,110 @@ def test_port_equals_compiled_reference_2d():
         assert same(port.index2d_to_disp(i2, search), ref.index2d_to_disp(i2, search))
 
 
+def test_golden_2d_truncation_and_refinement():
+    """truncatedBidirectionaCostVolume + refineDisp2dCostInterpolation of the port against outputs of the compiled reference."""
+    for mf in (O.ZNCC, O.SSD):
+        for r0, r1 in ((1, 1), (2, 1), (1, 0)):
+            t = port.truncated_cost_volume_2d(G2[f"cv2d_{mf}_1"], G2[f"wta2d_{mf}"], r0, r1)
+            assert same(t, G2[f"tcv2d_{mf}_{r0}_{r1}"])
+            for kernel in (O.EQUIANGULAR, O.PARABOLA, O.GAUSSIAN):
+                for aniso in (0, 1):
+                    assert same(port.refine_2d(t, G2[f"disp2d_{mf}"], kernel, aniso), G2[f"refined2d_{mf}_{r0}_{r1}_{kernel}_{aniso}"])
+    # the radii are uint8_t in the reference: 0 -> 1 on axis 0, 0 -> "as axis 0" on axis 1
+    assert port.truncated_cost_volume_2d(G2[f"cv2d_{O.SSD}_1"], G2[f"wta2d_{O.SSD}"], 0, 0).shape[2:] == (3, 3)
+    assert port.truncated_cost_volume_2d(G2[f"cv2d_{O.SSD}_1"], G2[f"wta2d_{O.SSD}"], 2, 0).shape[2:] == (5, 5)
+    # cost_based_refinement.h:180-182: even or too small sides -> empty array
+    z = np.zeros((3, 3, 2), np.int32)
+    for shape in ((3, 3, 4, 3), (3, 3, 3, 1), (3, 3, 1, 3), (3, 3, 3, 6)):
+        assert port.refine_2d(np.zeros(shape, np.float32), z) is None
+        assert port.refine_2d_patch(np.zeros(shape, np.float32), z) is None
+
+
+@pytest.mark.skipif(O.ref is None, reason="compiled reference (oracle/_ref) not present on this machine")
+def test_port_equals_compiled_reference_2d_refinement():
+    ref = O.ref
+    for seed, (H, W) in enumerate(((13, 17), (9, 40))):
+        Lq, Rq = synth.random_image(H, W, 301 + seed), synth.random_image(H, W, 352 + seed)
+        search = (-2, 3, -3, 3)
+        for mf, strategy in ((O.ZNCC, 1), (O.SAD, 0), (O.SSD, 0)):
+            cv = ref.cost_volume_2d(mf, Lq, Rq, 2, 1, search, 1)
+            idx = ref.wta_2d(cv, strategy)
+            for r0, r1 in ((1, 1), (2, 1), (0, 0), (2, 3)):
+                a, b = ref.truncated_cost_volume_2d(cv, idx, r0, r1), port.truncated_cost_volume_2d(cv, idx, r0, r1)
+                assert same(a, b)
+                for kernel in (O.EQUIANGULAR, O.PARABOLA, O.GAUSSIAN):
+                    for aniso in (0, 1):
+                        assert same(ref.refine_2d(a, idx, kernel, aniso), port.refine_2d(a, idx, kernel, aniso))
+    assert ref.refine_2d(np.zeros((3, 3, 4, 3), np.float32), np.zeros((3, 3, 2), np.int32)) is None
+
+
+def quadric_patch(n, A, b, s=1.0):
+    """cost(dx, dy) = s * (p - b)^T A (p - b) on an n x n neighbourhood centred on 0 (testCostRefinement.cpp:78-82, :139-142)."""
+    r = (n - 1) // 2
+    t = np.zeros((1, 1, n, n), np.float32)
+    for i in range(n):
+        for j in range(n):
+            p = np.array([i - r - b[0], j - r - b[1]], np.float64)
+            t[0, 0, i, j] = s * float(p @ A @ p)
+    return t
+
+
+def check_2d_cost_refinement(refine_2d, refine_2d_patch, seed):
+    """testCostRefinement.cpp:59-227: test2dCostIsotropicParabola, test2dCostAnisotropicParabola, test2dCostFullMatchingParabola.
+    The reference compares with QCOMPARE (float fuzzy compare, 1e-5 relative) / 1e-6 absolute on random draws; the same
+    bounds with a margin for the draw: 2e-5 absolute."""
+    rng = np.random.default_rng(seed)
+    raw = np.zeros((1, 1, 2), np.int32)
+    for _ in range(20):
+        s = rng.uniform(-1, 1)
+        s = 0.5 if abs(s) < 1e-4 else s
+        e = rng.uniform(-1, 1, 2)
+        got = refine_2d(quadric_patch(3, np.eye(2), e, s), raw, O.PARABOLA, 0)
+        assert np.allclose(got[0, 0], e, atol=2e-5), (got, e)
+        s = rng.uniform(-1, 1)
+        s = np.copysign(0.5, s) if abs(s) < 0.5 else s
+        d = s * rng.uniform(0.7, 1, 2)
+        b = rng.uniform(-0.5, 0.5, 2)
+        for alpha, fn, n in ((0.1 * rng.uniform(-1, 1), lambda t: refine_2d(t, raw, O.PARABOLA, 1), 5),
+                             (3 * rng.uniform(-1, 1), lambda t: refine_2d_patch(t, raw, O.PARABOLA), 3)):
+            rot = np.array([[np.cos(alpha), -np.sin(alpha)], [np.sin(alpha), np.cos(alpha)]])
+            A = rot @ np.diag(d) @ rot.T
+            got = fn(quadric_patch(n, A, b))
+            assert np.allclose(got[0, 0], b, atol=2e-5), (got, b, alpha)
+
+
+def lstsq_patch_deltas(t):
+    """refineCostPatch (cost_based_refinement.h:71-126) in float64 with a general least-squares solve."""
+    v, h = np.meshgrid([-1.0, 0.0, 1.0], [-1.0, 0.0, 1.0], indexing="ij")
+    v, h = v.ravel(), h.ravel()
+    A = np.stack([v * v, v * h, h * h, v, h, np.ones(9)], axis=1)
+    f = np.linalg.lstsq(A, t.astype(np.float64).ravel(), rcond=None)[0]
+    M = np.array([[2 * f[0], f[1]], [f[1], 2 * f[2]]])
+    return np.linalg.solve(M, -f[3:5])
+
+
+def test_ref_test2dCostRefinement():
+    check_2d_cost_refinement(port.refine_2d, port.refine_2d_patch, 5)
+
+
+def test_patch_refinement_equals_a_general_least_squares_solve():
+    rng = np.random.default_rng(9)
+    for kernel in (O.PARABOLA, O.GAUSSIAN):
+        n = 0
+        for _ in range(200):
+            t = rng.uniform(0.5, 2.0, (1, 1, 3, 3)).astype(np.float32)
+            t[0, 0, 1, 1] = 0.1                      # a clear minimum at the centre
+            want = lstsq_patch_deltas(np.log(t[0, 0]) if kernel == O.GAUSSIAN else t[0, 0])
+            got = port.refine_2d_patch(t, np.array([[[3, -2]]], np.int32), kernel)[0, 0] - np.array([3, -2], np.float32)
+            if np.all(np.abs(want) < 0.99):
+                n += 1
+                assert np.allclose(got, want, atol=1e-5), (got, want)
+            elif np.any(np.abs(want) > 1.01):
+                assert np.all(got == 0)
+        assert n > 100
+    assert port.refine_2d_patch(np.ones((1, 1, 3, 3), np.float32), np.zeros((1, 1, 2), np.int32), O.EQUIANGULAR) is None
+
+
 def naive_match(mf, win_s, win_t):
     """test/test_correlation_utils.h InneficientMatchingFunction: the textbook formula on two windows."""
     s, t = win_s.astype(np.float64).ravel(), win_t.astype(np.float64).ravel()
