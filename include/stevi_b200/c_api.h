@@ -242,6 +242,16 @@ STEVI_API int32_t stevi_truncated_cost_volume(stevi_ctx* ctx, const stevi_array*
 STEVI_API int32_t stevi_in_bound_domain(stevi_ctx* ctx, const stevi_array* idx, int32_t width, int32_t h_radius, int32_t v_radius,
 							  int32_t cost_vol_radius, int32_t direction, int32_t tcv_direction, stevi_array* out);
 
+/* ---- guided cost-volume aggregation ------------------------------------------------------ */
+
+/* variableCostVolumeAggregation<float, float> (correlation/guided_cost_filtering.h:102-176): cv (H,W,D) f32, windows
+ * (H,W,2v+1,2h+1) f32 (the per-pixel weights computeAggregationWindows :26-100 builds from the caller's functors) ->
+ * out (H,W,D) f32 = sum of w * cv over the in-image part of the pixel's window / sum of those w. Sums run in the reference's
+ * order (window rows outer, columns inner). STEVI_E_SHAPE where the reference returns an empty array (:108-130: windows
+ * of another image size, even or empty window sides). out must not alias cv. */
+STEVI_API int32_t stevi_variable_cost_volume_aggregation(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* windows,
+											   stevi_array* out);
+
 /* ---- cost-based subpixel refinement ------------------------------------------------------------------------ */
 
 /* refineDispCostInterpolation<kernel> (correlation/cost_based_refinement.h:128-163): tcv (H,W,2r+1) f32, idx (H,W) i32

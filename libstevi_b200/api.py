@@ -421,6 +421,22 @@ def refineDisp2dCostPatchInterpolation(tcv, rawDisparity, kernel=PARABOLA, ctx=N
     return out
 
 
+def variableCostVolumeAggregation(costVolume, aggregationWindows, layout="c", out=None, ctx=None):
+    """guided_cost_filtering.h:102-176. (H, W, D) f32 volume + (H, W, 2v+1, 2h+1) f32 per-pixel weights -> (H, W, D) f32 weighted
+    means over each pixel's (image-clipped) window. ``layout`` "ref" gives the result the strides {W*D, 1, W} of the reference's
+    cost volumes, "c" = C order (what the reference's ``Array(shape)`` gives). Returns None where the reference returns an empty
+    array (windows of another size, even or empty window sides)."""
+    ctx = _ctx_for(ctx, costVolume)
+    if out is None:
+        out = _empty(costVolume, tuple(costVolume.shape), np.float32, (0, 2, 1) if layout == "ref" else None)
+    a, w, o = describe(costVolume), describe(aggregationWindows), describe(out)
+    rc = lib.stevi_variable_cost_volume_aggregation(ctx.handle, ctypes.byref(a), ctypes.byref(w), ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
 def censusSgmPipeline(img_l, img_r, h_radius, v_radius, disp_width, P1, P2, Pout=100.0, nDirections=8,
                       margins=(0, 0, 0, 0), dDir=RIGHT_TO_LEFT, semantics=COMPAT, return_volumes=False, layout="ref",
                       out=None, ctx=None):

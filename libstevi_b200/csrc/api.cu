@@ -225,6 +225,18 @@ int32_t stevi_refine_disp_2d_cost_patch_interp(stevi_ctx* c, const stevi_array* 
 	return st.finish();
 }
 
+int32_t stevi_variable_cost_volume_aggregation(stevi_ctx* c, const stevi_array* cv, const stevi_array* windows, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	if (cv && out && cv->data == out->data && cv->data) return fail(c, STEVI_E_ARG, "variable_cost_volume_aggregation: out must not alias cv");
+	Stager st(c);
+	View vc, vw, vo;
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.in(windows, vw, "windows"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(var_aggregate_dev(c, vc, vw, vo));
+	return st.finish();
+}
+
 int32_t stevi_selected_cost(stevi_ctx* c, const stevi_array* cv, const stevi_array* idx, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);

@@ -80,6 +80,9 @@ int32_t truncated_cv2d_dev(stevi_ctx* c, const View& cv, const View& idx, int ra
 int32_t refine2d_interp_dev(stevi_ctx* c, const View& tcv, const View& raw, int kernel, int isotropy, const View& out);
 int32_t refine2d_patch_dev(stevi_ctx* c, const View& tcv, const View& raw, int kernel, const View& out);
 
+// aggregate.cu: variableCostVolumeAggregation (guided_cost_filtering.h:102-176)
+int32_t var_aggregate_dev(stevi_ctx* c, const View& cv, const View& win, const View& out);
+
 // hier.cu
 int32_t avgpool_dev(stevi_ctx* c, const View& img, int win_h, int win_v, const View& out);
 // band == nullptr: whole images; else the images / guide are row bands placed in global coordinates (c_api.h: stevi_band)

@@ -262,6 +262,14 @@ class _Checker:
         rc = self._f("refine_disp_2d_cost_patch_interp")(_p(_c(tcv, np.float32)), _p(_c(raw, np.int32)), h, w, n0, n1, kernel, _p(out))
         return out if rc == 0 else None
 
+    def variable_cost_volume_aggregation(self, cv, windows):
+        """variableCostVolumeAggregation<float, float>; None where the reference returns an empty array."""
+        h, w, d = cv.shape
+        hw, ww, n0, n1 = windows.shape
+        out = np.empty((h, w, d), np.float32)
+        rc = self._f("variable_cost_volume_aggregation_f32")(_p(_c(cv, np.float32)), h, w, d, _p(_c(windows, np.float32)), hw, ww, n0, n1, _p(out))
+        return out if rc == 0 else None
+
     def avgpool2(self, img):
         h, w = img.shape
         out = np.empty(((h + 1) // 2, (w + 1) // 2), np.float32)

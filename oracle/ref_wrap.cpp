@@ -18,6 +18,7 @@
 #include <correlation/census.h>
 #include <correlation/unfold.h>
 #include <interpolation/downsampling.h>
+#include <correlation/guided_cost_filtering.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -328,6 +329,16 @@ int ref_refine_disp_2d_cost_interp(const float* tcv, const int32_t* raw, int h, 
 	else if (kernel == int(InterpolationKernel::Parabola)) R2D_CASE(Parabola);
 	else R2D_CASE(Gaussian);
 #undef R2D_CASE
+	if (r.empty()) return 1;
+	out3(r, out);
+	return 0;
+}
+
+// guided_cost_filtering.h:102-176 variableCostVolumeAggregation<float, float>; cv (h, w, d), windows (hw, ww, n0, n1), out (h, w, d),
+// all C-order; returns 1 (out untouched) when the reference returns an empty array
+int ref_variable_cost_volume_aggregation_f32(const float* cv, int h, int w, int d, const float* win, int hw, int ww, int n0, int n1, float* out) {
+	MD::Array<float, 4> Wn(const_cast<float*>(win), {hw, ww, n0, n1}, {ww * n0 * n1, n0 * n1, n1, 1}, false);
+	MD::Array<float, 3> r = variableCostVolumeAggregation<float, float>(view3(cv, h, w, d), Wn);
 	if (r.empty()) return 1;
 	out3(r, out);
 	return 0;

@@ -683,6 +683,33 @@ int orc_refine_disp_2d_cost_patch_interp(const float* tcv, const int32_t* raw, i
 	return 0;
 }
 
+/* guided_cost_filtering.h:102-176 variableCostVolumeAggregation<float, float>: every cell of the volume becomes the weighted
+ * mean of its neighbours at the same disparity, with the pixel's own window of weights clipped to the image (:137-142); window
+ * rows outer, columns inner (:151-161). `acc += w*cv` is a separate multiply and add: the reference's Release build does not
+ * contract this one (checked against oracle/_ref, bit-identical). Returns 1 where the reference returns an empty array (:108-130). */
+int orc_variable_cost_volume_aggregation_f32(const float* cv, int h, int w, int d, const float* win, int hw, int ww, int n0, int n1, float* out) {
+	if (hw != h || ww != w || n0 <= 0 || n1 <= 0 || n0 % 2 != 1 || n1 % 2 != 1) return 1;
+	int vr = n0 / 2, hr = n1 / 2;
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) {
+		int lo_i = -vr > -i ? -vr : -i, hi_i = vr < h - 1 - i ? vr : h - 1 - i;
+		for (int j = 0; j < w; j++) {
+			int lo_j = -hr > -j ? -hr : -j, hi_j = hr < w - 1 - j ? hr : w - 1 - j;
+			const float* wp = win + (((size_t)i * w + j) * n0 + vr) * n1 + hr;
+			for (int c = 0; c < d; c++) {
+				float acc = 0, weight = 0;
+				for (int di = lo_i; di <= hi_i; di++) for (int dj = lo_j; dj <= hi_j; dj++) {
+					float x = wp[di * n1 + dj];
+					acc += x * cv[((size_t)(i + di) * w + (j + dj)) * d + c];
+					weight += x;
+				}
+				out[((size_t)i * w + j) * d + c] = acc / weight;
+			}
+		}
+	}
+	return 0;
+}
+
 /* interpolation/downsampling.h:67-118 with DownSampleWindows(2): out (ceil(h/2), ceil(w/2)); the mean is over
  * the in-image part of each 2x2 window (offsets are 0 for window 2: hRem/2 == 0). Accumulates in float, in
  * row-major window order, then divides by the count. */

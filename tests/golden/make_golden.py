@@ -90,6 +90,11 @@ def main_2d():
             for kernel in (O.EQUIANGULAR, O.PARABOLA, O.GAUSSIAN):
                 for aniso in (0, 1):
                     out[f"refined2d_{mf}_{r0}_{r1}_{kernel}_{aniso}"] = ref.refine_2d(t, out[f"disp2d_{mf}"], kernel, aniso)
+    # variableCostVolumeAggregation on a slice of the SSD volume with bilateral weights (tests/test_oracle_pinning.bilateral_windows)
+    sys.path.insert(0, os.path.dirname(HERE))
+    from test_oracle_pinning import bilateral_windows
+    out["aggregated_ssd_5x5"] = ref.variable_cost_volume_aggregation(np.ascontiguousarray(out[f"cv2d_{O.SSD}_1"][:, :, :, 2]),
+                                                                      bilateral_windows(Rf, 2, 2))
     path = os.path.join(HERE, "reference_outputs_2d.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes")

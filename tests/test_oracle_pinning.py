@@ -388,3 +388,59 @@ def check_2d_disparity(cost_volume_2d, wta_2d, index2d_to_disp, mf, hr, vr, seed
 def test_ref_test2dMatching_and_test2dDisparity(mf, hr, vr, dw, dh):
     check_2d_matching(port.cost_volume_2d, mf, hr, vr, dw, dh, 77)
     check_2d_disparity(port.cost_volume_2d, port.wta_2d, port.index2d_to_disp, mf, hr, vr, 91)
+
+
+# ---- guided cost-volume aggregation ------------------------------------------------------------------
+
+def bilateral_windows(guide, hr, vr, sigma_s=2.0, sigma_r=0.2):
+    """What computeAggregationWindows (guided_cost_filtering.h:26-100) returns for a Gaussian spatial weight and a Gaussian
+    weight on the guide difference: 0 outside the image."""
+    H, W = guide.shape
+    win = np.zeros((H, W, 2 * vr + 1, 2 * hr + 1), np.float32)
+    for di in range(-vr, vr + 1):
+        for dj in range(-hr, hr + 1):
+            ws = np.float32(np.exp(-(di * di + dj * dj) / (2 * sigma_s ** 2)))
+            i0, i1, j0, j1 = max(0, -di), min(H, H - di), max(0, -dj), min(W, W - dj)
+            diff = guide[i0 + di:i1 + di, j0 + dj:j1 + dj] - guide[i0:i1, j0:j1]
+            win[i0:i1, j0:j1, di + vr, dj + hr] = ws * np.exp(-(diff * diff) / np.float32(2 * sigma_r ** 2)).astype(np.float32)
+    return win
+
+
+def test_aggregation_port_against_the_definition_and_shape_rules():
+    rng = np.random.default_rng(2)
+    cv = rng.uniform(0, 4, (9, 12, 5)).astype(np.float32)
+    win = bilateral_windows(synth.random_image(9, 12, 3), 2, 1)
+    got = port.variable_cost_volume_aggregation(cv, win)
+    want = np.zeros(cv.shape, np.float64)
+    for i in range(9):
+        for j in range(12):
+            num, den = np.zeros(5), 0.0
+            for di in range(-1, 2):
+                for dj in range(-2, 3):
+                    if 0 <= i + di < 9 and 0 <= j + dj < 12:
+                        num += float(win[i, j, di + 1, dj + 2]) * cv[i + di, j + dj].astype(np.float64)
+                        den += float(win[i, j, di + 1, dj + 2])
+            want[i, j] = num / den
+    assert np.allclose(got, want, rtol=0, atol=2e-6)
+    # uniform weights on a constant volume: the constant comes back
+    assert np.allclose(port.variable_cost_volume_aggregation(np.full((5, 6, 3), 2.5, np.float32), np.ones((5, 6, 3, 3), np.float32)), 2.5)
+    # guided_cost_filtering.h:108-130
+    for bad in (np.ones((8, 12, 3, 3)), np.ones((9, 11, 3, 3)), np.ones((9, 12, 2, 3)), np.ones((9, 12, 3, 4)), np.ones((9, 12, 0, 3))):
+        assert port.variable_cost_volume_aggregation(cv, bad.astype(np.float32)) is None
+
+
+@pytest.mark.skipif(O.ref is None, reason="compiled reference (oracle/_ref) not present on this machine")
+def test_aggregation_port_equals_compiled_reference():
+    rng = np.random.default_rng(1)
+    for (H, W, D, n0, n1) in ((9, 13, 5, 3, 3), (12, 17, 7, 5, 5), (8, 20, 4, 7, 7), (10, 11, 6, 3, 7), (7, 9, 3, 9, 1), (6, 6, 2, 1, 1)):
+        cv = rng.uniform(-1, 1, (H, W, D)).astype(np.float32)
+        win = rng.uniform(0.01, 1, (H, W, n0, n1)).astype(np.float32)
+        assert same(O.ref.variable_cost_volume_aggregation(cv, win), port.variable_cost_volume_aggregation(cv, win))
+    assert O.ref.variable_cost_volume_aggregation(cv, win[:5]) is None
+    assert O.ref.variable_cost_volume_aggregation(cv, np.ones((6, 6, 2, 3), np.float32)) is None
+
+
+def test_aggregation_golden():
+    cv = G2[f"cv2d_{O.SSD}_1"][:, :, :, 2]          # an (H, W, dH) slice of the golden volume used as a 1-D volume
+    win = bilateral_windows(synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_r"])), 2, 2)
+    assert same(port.variable_cost_volume_aggregation(cv, win), G2["aggregated_ssd_5x5"])
