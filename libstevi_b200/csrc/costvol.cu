@@ -219,6 +219,69 @@ __global__ void __launch_bounds__(128) k_cv_direct(const DirectParams p) {
 	p.out[(int64_t)i * p.o0 + (int64_t)j * p.o1 + (int64_t)d * p.o2] = acc;
 }
 
+// ---- 2-D search volumes: feature planes + a register-tiled comparison -------------------------------------------------
+// k_cv_direct rebuilds both feature vectors of every cell ((v - mean) / norm per element: two IEEE divisions per window
+// element and cell), which is what makes it exact and what makes it slow once a search window has hundreds of candidates.
+// Here each image's features are evaluated once, with the very same operations, into F planes of H x W floats
+// (k_feature_planes), and the volume kernel only reads them: cell (i, j, a, b) accumulates op(S[f][i][j], T[f][it][jt]) over
+// f in the reference's channel order with separately rounded operations - the same bits as k_cv_direct. A thread owns one
+// source pixel and four consecutive column candidates: per feature one source load and four target loads that are
+// contiguous across the warp.
+struct PlaneParams {
+	const float* img; int64_t pitch; int half, pad_left;
+	const float* M; const float* N;
+	int H, W, hr, vr, zero_mean, normalized;
+	float* planes;   // [F][H][W]
+};
+
+__global__ void __launch_bounds__(128) k_feature_planes(const PlaneParams p) {
+	const int j = blockIdx.x * 128 + threadIdx.x, f = blockIdx.y, i = blockIdx.z;
+	if (j >= p.W) return;
+	const int hs = 2 * p.hr + 1, k = f / hs, l = f - k * hs;
+	float v = __ldg(p.img + (int64_t)(i - p.vr + k) * p.pitch + pad_col_off(p.pad_left + j - p.hr + l, p.half));
+	const int64_t o = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
+	if (p.zero_mean) v = __fsub_rn(v, p.M[o]);
+	if (p.normalized) v = __fdiv_rn(v, p.N[o]);
+	p.planes[((int64_t)f * p.H + i) * p.W + j] = v;
+}
+
+struct Cv2dParams {
+	const float* S; const float* T;   // [F][H][W]
+	int H, W, F, dH, dW, lo0, lo1;
+	float* out; int64_t o0, o1, o2, o3;
+};
+
+template<int OP>
+__global__ void __launch_bounds__(128) k_cv2d_planes(const Cv2dParams p) {
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.z;
+	if (j >= p.W) return;
+	const int groups = (p.dW + 3) >> 2;
+	const int a = blockIdx.y / groups, b0 = (blockIdx.y - a * groups) * 4;
+	const int it = i + a + p.lo0, jt0 = j + b0 + p.lo1;
+	const bool row_in = it >= 0 && it < p.H;
+	bool in[4];
+#pragma unroll
+	for (int q = 0; q < 4; q++) in[q] = row_in && jt0 + q >= 0 && jt0 + q < p.W;
+	const int64_t plane = (int64_t)p.H * p.W;
+	const float* s = p.S + (int64_t)i * p.W + j;
+	const float* t = p.T + (int64_t)(row_in ? it : 0) * p.W + jt0;
+	float acc[4] = {0.f, 0.f, 0.f, 0.f};
+	for (int f = 0; f < p.F; f++) {
+		const float sv = __ldg(s);
+#pragma unroll
+		for (int q = 0; q < 4; q++) {
+			const float tv = in[q] ? __ldg(t + q) : 0.f;   // zero features outside the target image (valueOrAlt)
+			if (OP == BOX_PROD) acc[q] = __fadd_rn(acc[q], __fmul_rn(sv, tv));
+			else if (OP == BOX_SQ) { const float e = __fsub_rn(sv, tv); acc[q] = __fadd_rn(acc[q], __fmul_rn(e, e)); }
+			else acc[q] = __fadd_rn(acc[q], fabsf(__fsub_rn(sv, tv)));
+		}
+		s += plane; t += plane;
+	}
+	float* o = p.out + (int64_t)i * p.o0 + (int64_t)j * p.o1 + (int64_t)a * p.o2 + (int64_t)b0 * p.o3;
+#pragma unroll
+	for (int q = 0; q < 4; q++) if (b0 + q < p.dW) o[q * p.o3] = acc[q];
+}
+
 } // namespace
 
 int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows) {
@@ -316,6 +379,31 @@ int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int h
 	const int si = r2l ? 1 : 0, ti = 1 - si;
 	STEVI_TRY(pp.stats(c, si, hr, vr, mf, STATS_RAW));
 	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, STATS_RAW));
+	const int F = (2 * hr + 1) * (2 * vr + 1);
+	const size_t plane_floats = (size_t)F * H * W;
+	if (F <= 65535 && (int64_t)dH * ((dW + 3) / 4) <= 65535 && plane_floats * 8 <= ((size_t)24 << 30)) {
+		// feature planes of both images, then the register-tiled comparison (same arithmetic as k_cv_direct, see above)
+		float* planes[2] = {nullptr, nullptr};
+		for (int k = 0; k < 2; k++) {
+			STEVI_TRY(arena_alloc_t(c, plane_floats, &planes[k]));
+			PlaneParams q;
+			q.img = pp.img[k]; q.pitch = pp.pitch; q.half = pp.half; q.pad_left = pp.pad_left; q.M = pp.A[k]; q.N = pp.B[k];
+			q.H = H; q.W = W; q.hr = hr; q.vr = vr; q.zero_mean = mf_zero_mean(mf); q.normalized = mf_normalized(mf); q.planes = planes[k];
+			dim3 gp(cdiv(W, 128), F, H);
+			STEVI_LAUNCH(c, k_feature_planes, gp, 128, 0, q);
+		}
+		Cv2dParams v;
+		v.S = planes[si]; v.T = planes[ti]; v.H = H; v.W = W; v.F = F; v.dH = dH; v.dW = dW; v.lo0 = search[0]; v.lo1 = search[2];
+		v.out = out.as<float>(); v.o0 = out.st[0]; v.o1 = out.st[1]; v.o2 = out.st[2]; v.o3 = out.st[3];
+		dim3 gv(cdiv(W, 128), dH * ((dW + 3) / 4), H);
+		switch (mf_op(mf)) {
+		case BOX_PROD: STEVI_LAUNCH(c, k_cv2d_planes<BOX_PROD>, gv, 128, 0, v); break;
+		case BOX_SQ: STEVI_LAUNCH(c, k_cv2d_planes<BOX_SQ>, gv, 128, 0, v); break;
+		default: STEVI_LAUNCH(c, k_cv2d_planes<BOX_ABS>, gv, 128, 0, v); break;
+		}
+		return STEVI_OK;
+	}
+	// windows or frames too large for the planes: one launch of the per-cell kernel per row offset
 	DirectParams p;
 	p.ps = pp.img[si]; p.pt = pp.img[ti]; p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left;
 	p.Ms = pp.A[si]; p.Ns = pp.B[si]; p.Mt = pp.A[ti]; p.Nt = pp.B[ti];
