@@ -42,6 +42,24 @@ def test_cost_volume_2d_matches_oracle(api, ctx, oracle, name, search):
         close(name, np.ascontiguousarray(got), oracle.port.cost_volume_2d(getattr(oracle, name), L, R, 2, 1, search, direction))
 
 
+@pytest.mark.parametrize("name", ["ZNCC", "SSD", "ZSAD", "CC"])
+@pytest.mark.parametrize("W", [40, 132, 516])
+@pytest.mark.parametrize("search", [(0, 1, 0, 6), (-1, 1, -3, 2), (-2, -1, -9, -5), (1, 2, 5, 5), (0, 0, -4, 3), (-1, 0, 1, 8)])
+def test_cost_volume_2d_aligned_rows_match_oracle(api, ctx, oracle, name, W, search):
+    """Widths that are multiples of 4 take the kernel with four source pixels x four column offsets per thread; its groups of
+    offsets start at a multiple of 4 at or below lower1, so unaligned and negative windows exercise the partial groups."""
+    L, R = synth.random_image(13, W, 5), synth.random_image(13, W, 6)
+    got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, ctx=ctx)
+    want = oracle.port.cost_volume_2d(getattr(oracle, name), L, R, 2, 1, search)
+    close(name, np.ascontiguousarray(got), want)
+    c_layout = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, layout="c", ctx=ctx)
+    assert np.array_equal(np.ascontiguousarray(got), c_layout, equal_nan=True)
+    # the same cells through the four-candidate kernel (odd width: the last column dropped) agree bit for bit
+    narrow = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L[:, :W - 1].copy(), R[:, :W - 1].copy(), 2, 1, search, layout="c", ctx=ctx)
+    inner = slice(8, W - 12)     # away from the dropped column's reach (window radius 2 + offsets up to 9)
+    assert np.array_equal(narrow[:, inner], c_layout[:, inner], equal_nan=True)
+
+
 @pytest.mark.parametrize("name", MFS)
 def test_cost_volume_2d_golden(api, ctx, oracle, name):
     L, R = synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_l"])), synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_r"]))
