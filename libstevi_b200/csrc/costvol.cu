@@ -235,14 +235,24 @@ struct PlaneParams {
 };
 
 __global__ void __launch_bounds__(128) k_feature_planes(const PlaneParams p) {
-	const int j = blockIdx.x * 128 + threadIdx.x, f = blockIdx.y, i = blockIdx.z;
+	// thread per pixel, all F features: mean and norm read once, plane writes contiguous across the warp
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
 	if (j >= p.W) return;
-	const int hs = 2 * p.hr + 1, k = f / hs, l = f - k * hs;
-	float v = __ldg(p.img + (int64_t)(i - p.vr + k) * p.pitch + pad_col_off(p.pad_left + j - p.hr + l, p.half));
+	const int hs = 2 * p.hr + 1, vs = 2 * p.vr + 1;
 	const int64_t o = (int64_t)i * p.pitch + pad_col_off(p.pad_left + j, p.half);
-	if (p.zero_mean) v = __fsub_rn(v, p.M[o]);
-	if (p.normalized) v = __fdiv_rn(v, p.N[o]);
-	p.planes[((int64_t)f * p.H + i) * p.W + j] = v;
+	const float m = p.zero_mean ? p.M[o] : 0.f, n = p.normalized ? p.N[o] : 1.f;
+	const int64_t plane = (int64_t)p.H * p.W;
+	float* dst = p.planes + (int64_t)i * p.W + j;
+	for (int k = 0; k < vs; k++) {
+		const float* row = p.img + (int64_t)(i - p.vr + k) * p.pitch;
+		for (int l = 0; l < hs; l++) {
+			float v = __ldg(row + pad_col_off(p.pad_left + j - p.hr + l, p.half));
+			if (p.zero_mean) v = __fsub_rn(v, m);
+			if (p.normalized) v = __fdiv_rn(v, n);
+			*dst = v;
+			dst += plane;
+		}
+	}
 }
 
 struct Cv2dParams {
@@ -428,7 +438,7 @@ int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int h
 	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, STATS_RAW));
 	const int F = (2 * hr + 1) * (2 * vr + 1);
 	const size_t plane_floats = (size_t)F * H * W;
-	if (F <= 65535 && (int64_t)dH * ((dW + 3) / 4) <= 65535 && plane_floats * 8 <= ((size_t)24 << 30)) {
+	if ((int64_t)dH * ((dW + 3) / 4) <= 65535 && plane_floats * 8 <= ((size_t)24 << 30)) {
 		// feature planes of both images, then the register-tiled comparison (same arithmetic as k_cv_direct, see above)
 		float* planes[2] = {nullptr, nullptr};
 		for (int k = 0; k < 2; k++) {
@@ -436,7 +446,7 @@ int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int h
 			PlaneParams q;
 			q.img = pp.img[k]; q.pitch = pp.pitch; q.half = pp.half; q.pad_left = pp.pad_left; q.M = pp.A[k]; q.N = pp.B[k];
 			q.H = H; q.W = W; q.hr = hr; q.vr = vr; q.zero_mean = mf_zero_mean(mf); q.normalized = mf_normalized(mf); q.planes = planes[k];
-			dim3 gp(cdiv(W, 128), F, H);
+			dim3 gp(cdiv(W, 128), H);
 			STEVI_LAUNCH(c, k_feature_planes, gp, 128, 0, q);
 		}
 		Cv2dParams v;

@@ -26,7 +26,9 @@ def lib():
 def test_header_declares_the_hot_path():
     names = declared_symbols()
     for needed in ("stevi_ctx_create", "stevi_census_transform", "stevi_cost_volume", "stevi_sgm", "stevi_wta",
-                   "stevi_index_to_disp", "stevi_census_sgm_pipeline"):
+                   "stevi_index_to_disp", "stevi_census_sgm_pipeline", "stevi_cost_volume_2d", "stevi_wta_2d", "stevi_index2d_to_disp",
+                   "stevi_truncated_cost_volume_2d", "stevi_refine_disp_2d_cost_interp", "stevi_refine_disp_2d_cost_patch_interp",
+                   "stevi_variable_cost_volume_aggregation"):
         assert needed in names
 
 
