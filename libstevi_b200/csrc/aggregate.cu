@@ -48,7 +48,24 @@ __global__ void __launch_bounds__(128) k_var_aggregate(const Agg p) {
 	const int c_begin = blockIdx.z * p.chunk, c_end = min(p.D, c_begin + p.chunk);
 	const float* src = p.cv + i * p.c0 + j * p.c1;
 	float* dst = p.out + i * p.o0 + j * p.o1;
-	if (inner) {
+	if (inner && p.c1 == 1) {
+		// contiguous columns: one pointer per window row advanced by the disparity stride, column offsets as immediates
+		const float* rowp[2 * VR + 1];
+#pragma unroll
+		for (int a = 0; a <= 2 * VR; a++) rowp[a] = src + (int64_t)(a - VR) * p.c0 + (int64_t)c_begin * p.c2;
+		float* o = dst + (int64_t)c_begin * p.o2;
+		for (int c = c_begin; c < c_end; c++) {
+			float acc = 0.f;
+#pragma unroll
+			for (int a = 0; a <= 2 * VR; a++) {
+#pragma unroll
+				for (int dj = -HR; dj <= HR; dj++) acc = __fadd_rn(acc, __fmul_rn(w[a][dj + HR], __ldg(rowp[a] + dj)));
+				rowp[a] += p.c2;
+			}
+			*o = __fdiv_rn(acc, weight);
+			o += p.o2;
+		}
+	} else if (inner) {
 		for (int c = c_begin; c < c_end; c++) {
 			const float* s = src + c * p.c2;
 			float acc = 0.f;
