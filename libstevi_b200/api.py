@@ -224,10 +224,27 @@ def default_context(device=0):
     return _default_ctx[device]
 
 
+_default_torch_ctx = {}
+
+
 def _ctx_for(ctx, x):
+    """The context a call without ``ctx=`` runs on. Host operands: an own-stream context (the call returns with its results in
+    place). Torch CUDA tensors: a context bound to torch's CURRENT stream on the tensor's device, re-bound on every call, so
+    the kernels are ordered after whatever produced the operands and before whatever reads the results, and the caching
+    allocator's stream bookkeeping holds. (A ``Context()`` with its own stream is for callers who order things themselves.)"""
     if ctx is not None:
         return ctx
-    return default_context(x.device.index if _is_torch(x) else 0)
+    if not _is_torch(x):
+        return default_context(0)
+    import torch
+    dev = x.device.index
+    stream = torch.cuda.current_stream(dev).cuda_stream or 1  # legacy default stream == (cudaStream_t)0x1
+    c = _default_torch_ctx.get(dev)
+    if c is None:
+        c = _default_torch_ctx[dev] = Context(dev, stream=stream)
+    else:
+        c.check(lib.stevi_ctx_set_stream(c.handle, ctypes.c_void_p(stream)))
+    return c
 
 
 def _empty(like, shape, np_dtype, order=None):

@@ -207,7 +207,7 @@ int32_t var_aggregate_dev(stevi_ctx* c, const View& cv, const View& win, const V
 	const int key = p.vr == p.hr ? p.vr : -1;
 	auto aligned = [](const void* q, int64_t a, int64_t b) { return (uintptr_t)q % 16 == 0 && a % 4 == 0 && b % 4 == 0; };
 	static const bool no_x4 = getenv("STEVI_AGG_NO_X4") != nullptr;   // measurement aid: the one-column-per-thread kernels only
-	const bool x4 = !no_x4 && (key == 1 || key == 2) && cv.st[1] == 1 && aligned(cv.p, cv.st[0], cv.st[2]) && W >= 16;
+	const bool x4 = !no_x4 && (key == 1 || key == 2) && cv.st[1] == 1 && aligned(cv.p, cv.st[0], cv.st[2]) && W >= 16 && W % 4 == 0;
 	p.vec_out = out.st[1] == 1 && aligned(out.p, out.st[0], out.st[2]) ? 1 : 0;
 	// slices of the disparity axis: enough blocks for a few waves over the SMs, each thread amortising its weight loads
 	const int col_blocks = x4 ? cdiv(cdiv(W, 4), 128) : cdiv(W, 128);

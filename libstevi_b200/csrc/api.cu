@@ -363,6 +363,7 @@ int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stev
 	STEVI_TRY(st.in(r, vr_, "img_r"));
 	STEVI_TRY(check_images(c, vl, vr_));
 	if (!disp) return fail(c, STEVI_E_ARG, "pipeline: disp is required");
+	if (D < 1) return fail(c, STEVI_E_ARG, "pipeline: disp_width must be positive");   // before any workspace is sized by it
 	STEVI_TRY(st.out(disp, vd, "disp"));
 	const int H = vl.shape[0];
 	const int Ws = direction == STEVI_RIGHT_TO_LEFT ? vr_.shape[1] : vl.shape[1];
@@ -425,6 +426,7 @@ int32_t stevi_local_matching_pipeline(stevi_ctx* c, int32_t mf, const stevi_arra
 	STEVI_TRY(st.in(r, vr_, "img_r"));
 	STEVI_TRY(check_images(c, vl, vr_));
 	if (!refined) return fail(c, STEVI_E_ARG, "pipeline: refined is required");
+	if (D < 1) return fail(c, STEVI_E_ARG, "pipeline: disp_width must be positive");
 	STEVI_TRY(st.out(refined, vo, "refined"));
 	const int H = vl.shape[0];
 	const int Ws = direction == STEVI_RIGHT_TO_LEFT ? vr_.shape[1] : vl.shape[1];
@@ -443,7 +445,6 @@ int32_t stevi_local_matching_pipeline(stevi_ctx* c, int32_t mf, const stevi_arra
 		vidx.p = p; vidx.dtype = STEVI_I32; vidx.ndim = 2; vidx.shape[0] = H; vidx.shape[1] = Ws; vidx.st[0] = Ws; vidx.st[1] = 1;
 	}
 	if (tcv_out) STEVI_TRY(st.out(tcv_out, vt, "tcv_out"));
-	if (D < 1) return fail(c, STEVI_E_ARG, "pipeline: disp_width must be positive");
 	// the winner-take-all rides on the cost-volume kernel: the 4*W*H*D-byte volume is written once and never read back
 	STEVI_TRY(float_cv_dev(c, mf, vl, vr_, hr, vr, D, direction, vcv, false, &vidx));
 	STEVI_TRY(refine_from_cv_dev(c, vcv, vidx, hr, vr, kernel, tcv_out ? &vt : nullptr, vo));

@@ -455,14 +455,19 @@ static int32_t hamming_rows_plan(stevi_ctx* c, HamParams& p, dim3& grid, size_t&
 		dc = std::max(32, (dc + 7) / 8 * 8);
 		dchunk = std::min(dchunk, dc);
 	}
+	// the staged target row (n_words x 8 lanes x P words) has to fit the 48 KB a kernel gets without opting in: long
+	// disparity ranges with 3-4 census words are cut into more chunks instead
+	auto plan = [&](int dc, int& P) {
+		P = (1024 + dc + 8) / 8 + 2;
+		while (P % 32 != 4) P++;
+		return (size_t)p.n_words * 8 * P * sizeof(uint32_t);
+	};
+	int P = 0;
+	while ((smem = plan(dchunk, P)) > 48 * 1024 && dchunk > 32) dchunk = std::max(32, (dchunk / 2 + 7) / 8 * 8);
 	if (p.gmap && dchunk < p.D) // chunks merge their minima with atomicMin
 		STEVI_CUDA(c, cudaMemsetAsync(p.gmap, 0x7f, (size_t)p.H * p.Ws * sizeof(int32_t), c->stream));
 	p.dchunk = dchunk;
-	const int groups = (1024 + dchunk + 8) / 8 + 2;
-	int P = groups;
-	while (P % 32 != 4) P++;
 	p.P = P;
-	smem = (size_t)p.n_words * 8 * P * sizeof(uint32_t);
 	grid = dim3(xb, p.H, cdiv(p.D, dchunk));
 	return STEVI_OK;
 }

@@ -32,6 +32,10 @@ struct stevi_ctx {
 	std::vector<Timed> timed;
 	std::vector<cudaEvent_t> event_pool;
 	std::string report;
+	// device-side fault flag (page-locked, mapped): a kernel that would otherwise wait forever on another block raises it
+	// and carries on; checked whenever the host synchronises the stream
+	int* fault_host = nullptr;
+	int* fault_dev = nullptr;
 };
 
 namespace stevi {
@@ -46,8 +50,10 @@ inline int32_t fail(stevi_ctx* c, int32_t code, const char* fmt, ...) {
 	return code;
 }
 
-#define STEVI_CUDA(c, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) \
-	return stevi::fail((c), STEVI_E_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); } while (0)
+// a failed runtime call leaves its code in the thread's "last error"; it is cleared here so that a recoverable failure (an
+// allocation that did not fit, a launch configuration that was refused) does not fail every later call of this host thread
+#define STEVI_CUDA(c, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { (void)cudaGetLastError(); \
+	return stevi::fail((c), STEVI_E_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); } } while (0)
 
 #define STEVI_TRY(expr) do { int32_t s__ = (expr); if (s__ != STEVI_OK) return s__; } while (0)
 
@@ -57,7 +63,7 @@ inline int32_t fail(stevi_ctx* c, int32_t code, const char* fmt, ...) {
 	kern<<<(grid), (block), (smem), (c)->stream>>>(__VA_ARGS__); \
 	if ((c)->timing) stevi::timing_end((c)); \
 	(c)->launches++; \
-	STEVI_CUDA((c), cudaPeekAtLastError()); } while (0)
+	STEVI_CUDA((c), cudaGetLastError()); } while (0)
 
 void timing_begin(stevi_ctx* c, const char* name);
 void timing_end(stevi_ctx* c);
@@ -121,5 +127,14 @@ inline int32_t begin_call(stevi_ctx* c) {
 }
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// after a stream synchronisation: did a kernel raise the fault flag?
+inline int32_t check_fault(stevi_ctx* c) {
+	if (c->fault_host && *c->fault_host) {
+		*c->fault_host = 0;
+		return fail(c, STEVI_E_CUDA, "a kernel gave up waiting for another thread block (device-side fault flag): results of this stream are invalid");
+	}
+	return STEVI_OK;
+}
 
 } // namespace stevi

@@ -113,7 +113,10 @@ int32_t Stager::finish() {
 	for (auto& b : back_)
 		if (b.bytes) STEVI_CUDA(c_, cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, c_->stream));
 	back_.clear();
-	if (any_host_ && !c_->deferred_host) STEVI_CUDA(c_, cudaStreamSynchronize(c_->stream));
+	if (any_host_ && !c_->deferred_host) {
+		STEVI_CUDA(c_, cudaStreamSynchronize(c_->stream));
+		return check_fault(c_);
+	}
 	return STEVI_OK;
 }
 
@@ -147,6 +150,14 @@ int32_t stevi_ctx_create(int32_t device, void* stream, stevi_ctx** out) {
 		c->own_stream = true;
 	}
 	cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+	if (cudaHostAlloc((void**)&c->fault_host, sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
+		cudaHostGetDevicePointer((void**)&c->fault_dev, c->fault_host, 0) != cudaSuccess) {
+		cudaGetLastError();
+		if (c->own_stream) cudaStreamDestroy(c->stream);
+		delete c;
+		return STEVI_E_CUDA;
+	}
+	*c->fault_host = 0;
 	*out = c;
 	return STEVI_OK;
 }
@@ -159,13 +170,15 @@ int32_t stevi_ctx_destroy(stevi_ctx* c) {
 	for (auto& t : c->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
 	for (auto e : c->event_pool) cudaEventDestroy(e);
 	if (c->own_stream) cudaStreamDestroy(c->stream);
+	if (c->fault_host) cudaFreeHost(c->fault_host);
 	delete c;
 	return STEVI_OK;
 }
 
 int32_t stevi_ctx_set_stream(stevi_ctx* c, void* stream) {
 	if (!c) return STEVI_E_ARG;
-	STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+	if (stream && static_cast<cudaStream_t>(stream) == c->stream) return STEVI_OK;
+	STEVI_CUDA(c, cudaStreamSynchronize(c->stream));   // the workspace is reused by the next call, on the new stream
 	if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
 	if (stream) c->stream = static_cast<cudaStream_t>(stream);
 	else {
@@ -192,7 +205,7 @@ void* stevi_ctx_stream(stevi_ctx* c) { return c ? (void*)c->stream : nullptr; }
 int32_t stevi_ctx_synchronize(stevi_ctx* c) {
 	if (!c) return STEVI_E_ARG;
 	STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
-	return STEVI_OK;
+	return check_fault(c);
 }
 
 const char* stevi_last_error(stevi_ctx* c) { return c ? c->err.c_str() : "null context"; }

@@ -220,9 +220,15 @@ static int32_t launch_lines(stevi_ctx* c, const GLineParams& p) {
 	return STEVI_OK;
 }
 
+bool sgm_sweep_capable(const View& cv, int ndir, int strategy, float P1, float P2, int semantics, const View& out);
+int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout, const stevi_margins& mg,
+				  int semantics, const View& out);
+
 int32_t sgm_general(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, float P2, float Pout,
 					const stevi_margins& mg, int semantics, const View& out) {
 	const int H = cv.shape[0], W = cv.shape[1], D = cv.shape[2];
+	// volumes with contiguous columns (the reference's layout): consumed in place by the sweep kernels (sgm_sweep.cu)
+	if (sgm_sweep_capable(cv, ndir, strategy, P1, P2, semantics, out)) return sgm_sweep(c, cv, ndir, strategy, P1, P2, Pout, mg, semantics, out);
 	if (D > 512) return fail(c, STEVI_E_UNSUPPORTED, "sgm: the general recurrence supports up to 512 disparities");
 	const size_t n = (size_t)H * W * D;
 	float *Cw = nullptr, *Sw = nullptr;

@@ -81,3 +81,83 @@ def test_large_u16_costs_fall_back_to_the_recurrence(api, ctx, oracle):
     cv[:, ::2, :] //= 50
     got = api.sgmCostVolume(cv, 1, 2, Pout=100, ctx=ctx)
     assert np.array_equal(got, oracle.port.sgm(cv, 8, oracle.COST, 1, 2, 100))
+
+
+# ---- volumes with contiguous columns (the reference's cost-volume layout {W*D, 1, W}): sgm_sweep.cu ---------------------------
+# horizontal paths by k_sgm_sweep_h, vertical and diagonal paths by the sheared-strip sweeps of k_sgm_sweep_v; additions in the
+# reference's order => bit-identical for the 4- and 8-direction sets
+
+def ref_layout(v):
+    """same values, memory order [H][D][W]"""
+    return np.ascontiguousarray(v.transpose(0, 2, 1)).transpose(0, 2, 1)
+
+
+@pytest.mark.parametrize("ndir", [4, 8])
+@pytest.mark.parametrize("shape", [(21, 45, 7), (21, 44, 32), (33, 48, 40), (19, 70, 100), (40, 37, 200), (25, 64, 256),
+                                   (18, 36, 300), (12, 40, 512), (130, 50, 20), (9, 200, 16), (1, 30, 9), (30, 1, 9), (5, 3, 2)])
+def test_sweep_score_f32_bit_exact(api, ctx, oracle, ndir, shape):
+    h, w, D = shape
+    v = zncc_like_volume(h, w, D, h + w + D)
+    got = api.sgmCostVolume(ref_layout(v), 0.001, 0.01, Pout=100, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, ndir, oracle.SCORE, 0.001, 0.01, 100)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("ndir", [4, 8])
+def test_sweep_against_the_compiled_reference(api, ctx, oracle, ndir):
+    if oracle.ref is None:
+        pytest.skip("oracle/_ref was not built")
+    v = zncc_like_volume(26, 75, 48, 77)
+    got = api.sgmCostVolume(ref_layout(v), 0.002, 0.02, Pout=5, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+    assert np.array_equal(got, oracle.ref.sgm(v, ndir, oracle.SCORE, 0.002, 0.02, 5))
+    c = (np.abs(v) * 10).astype(np.float32)
+    got = api.sgmCostVolume(ref_layout(c), 0.5, 2.0, Pout=100, nDirections=ndir, strategy=api.COST, ctx=ctx)
+    assert np.array_equal(got, oracle.ref.sgm(c, ndir, oracle.COST, 0.5, 2.0, 100))
+
+
+@pytest.mark.parametrize("margins", [(2, 3, 1, 4), (0, 5, 0, 0), (17, 0, 3, 0)])
+@pytest.mark.parametrize("ndir", [4, 8])
+def test_sweep_margins(api, ctx, oracle, margins, ndir):
+    v = zncc_like_volume(45, 58, 19, 11)
+    got = api.sgmCostVolume(ref_layout(v), 0.5, 2.0, margins=margins, Pout=3.5, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, ndir, oracle.SCORE, 0.5, 2.0, 3.5, margins)
+    assert np.array_equal(got, want)
+
+
+def test_sweep_u16_score_and_large_costs(api, ctx, oracle):
+    cv = census_cv(api, ctx, h=60, w=90, D=24, layout="ref")
+    for ndir in (4, 8):
+        got = api.sgmCostVolume(cv, 3, 20, Pout=50, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+        assert np.array_equal(got, oracle.port.sgm(np.ascontiguousarray(cv), ndir, oracle.SCORE, 3, 20, 50))
+    rng = np.random.default_rng(1)
+    big = rng.integers(60000, 65535, size=(20, 300, 9)).astype(np.uint16)
+    big[:, ::2, :] //= 50
+    got = api.sgmCostVolume(ref_layout(big), 1, 2, Pout=100, ctx=ctx)   # too large for the collapsed integer evaluation
+    assert np.array_equal(got, oracle.port.sgm(big, 8, oracle.COST, 1, 2, 100))
+
+
+def test_sweep_cost_mode_float_volume_compat(api, ctx, oracle):
+    v = np.abs(zncc_like_volume(43, 81, 17, 2)) * 10
+    for ndir in (4, 8):
+        got = api.sgmCostVolume(ref_layout(v), 0.5, 2.0, Pout=100, nDirections=ndir, strategy=api.COST, ctx=ctx)
+        assert np.array_equal(got, oracle.port.sgm(v, ndir, oracle.COST, 0.5, 2.0, 100))
+
+
+def test_sweep_non_finite_scores(api, ctx, oracle):
+    v = zncc_like_volume(32, 50, 20, 4)
+    v[3, 5, :] = np.nan
+    v[6, 7, 3] = np.inf
+    v[8, :, 0] = -np.inf
+    v[20, 17:40, :] = np.nan
+    got = api.sgmCostVolume(ref_layout(v), 0.1, 0.4, Pout=10, nDirections=8, strategy=api.SCORE, ctx=ctx)
+    want = oracle.port.sgm(v, 8, oracle.SCORE, 0.1, 0.4, 10)
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_sweep_column_slices_and_unaligned_rows(api, ctx, oracle):
+    # views whose rows are not 16-byte aligned take the scalar column tiles of the horizontal kernel
+    v = zncc_like_volume(20, 64, 24, 9)
+    base = ref_layout(v)
+    view = base[:, 3:50, :]
+    got = api.sgmCostVolume(view, 0.001, 0.01, Pout=100, nDirections=8, strategy=api.SCORE, ctx=ctx)
+    assert np.array_equal(got, oracle.port.sgm(np.ascontiguousarray(view), 8, oracle.SCORE, 0.001, 0.01, 100))
