@@ -36,6 +36,11 @@ struct stevi_ctx {
 	// and carries on; checked whenever the host synchronises the stream
 	int* fault_host = nullptr;
 	int* fault_dev = nullptr;
+	// strip-to-strip exchange buffer of the general SGM sweeps (sgm_sweep.cu): grow-only, holds {value, tag} pairs; the epoch
+	// makes the tags of every launch unique
+	void* sgm_xchg = nullptr;
+	size_t sgm_xchg_bytes = 0;
+	unsigned sgm_epoch = 0;
 };
 
 namespace stevi {

@@ -171,6 +171,7 @@ int32_t stevi_ctx_destroy(stevi_ctx* c) {
 	for (auto e : c->event_pool) cudaEventDestroy(e);
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	if (c->fault_host) cudaFreeHost(c->fault_host);
+	if (c->sgm_xchg) cudaFree(c->sgm_xchg);
 	delete c;
 	return STEVI_OK;
 }
@@ -212,7 +213,7 @@ const char* stevi_last_error(stevi_ctx* c) { return c ? c->err.c_str() : "null c
 int64_t stevi_ctx_launch_count(stevi_ctx* c) { return c ? c->launches : 0; }
 int64_t stevi_ctx_workspace_bytes(stevi_ctx* c) {
 	if (!c) return 0;
-	size_t t = 0;
+	size_t t = c->sgm_xchg_bytes;
 	for (auto& b : c->blocks) t += b.cap;
 	return (int64_t)t;
 }

@@ -42,7 +42,10 @@ template<int MODE> __device__ __forceinline__ float sw_worst() { return MODE == 
 template<int MODE> __device__ __forceinline__ float sw_better(float a, float b) { return MODE == SW_SCORE ? fmaxf(a, b) : fminf(a, b); }
 
 // one cell of one path: `in` = previous score at d (non-finite ones already replaced by the worst value), l / r = at d-1 / d+1,
-// M = extremum of the previous scores, farv = M -/+ P2. Returns actual_cost (sgm.h:251-254, :291-294).
+// farv = M -/+ P2 with M = extremum of the previous scores, FINITE (the caller handles the other case: actual_cost = c).
+// Returns actual_cost (sgm.h:251-254, :291-294). The reference's test isfinite(max_a_cost) always holds here in Score and
+// corrected Cost mode (M - P2 <= m <= M); in COMPAT Cost mode m = c_score [+ Pout], and for a non-finite c_score the reference's
+// "leave actual_cost = c" and c + (m - M) are the same value (NaN stays NaN, +-inf stays +-inf).
 template<int MODE>
 __device__ __forceinline__ float sw_cell(float c, float in, float l, float r, float M, float farv, float P1, float Pout, bool oor) {
 	float m;
@@ -53,12 +56,10 @@ __device__ __forceinline__ float sw_cell(float c, float in, float l, float r, fl
 		m = fminf(fminf(farv, fminf(l, r) + P1), in);
 		if (oor) m += Pout;
 	} else {   // Q3 (sgm.h:281-283): min_a_cost ends up as c_score as soon as one previous score is finite
-		m = isfinite(M) ? c : INFINITY;
+		m = c;
 		if (oor) m += Pout;
 	}
-	float a = c;
-	if (isfinite(m) && isfinite(M)) a += m - M;
-	return a;
+	return c + (m - M);
 }
 
 __device__ __forceinline__ int ld_acquire(const int* p) {
@@ -79,26 +80,67 @@ struct HSweep {
 	float P1, P2, Pout;
 };
 
-template<int CT> struct VecLoad;
-template<> struct VecLoad<1> {
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// a tile of CT columns of one disparity row: CT = 8 moves whole 32-byte sectors (two 16-byte accesses; one for u16 costs), so
+// no sector of C is fetched twice and no sector of A is written in halves; CT = 1 is the any-alignment path
+template<int CT> struct Tile;
+template<> struct Tile<1> {
 	static __device__ __forceinline__ void f32(const float* p, float* v) { v[0] = __ldg(p); }
 	static __device__ __forceinline__ void u16(const uint16_t* p, float* v) { v[0] = (float)__ldg(p); }
 	static __device__ __forceinline__ void st(float* p, const float* v) { p[0] = v[0]; }
 };
-template<> struct VecLoad<4> {
+template<> struct Tile<8> {
 	static __device__ __forceinline__ void f32(const float* p, float* v) {
-		const float4 x = __ldg(reinterpret_cast<const float4*>(p));
-		v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+		const float4 x = __ldg(reinterpret_cast<const float4*>(p)), y = __ldg(reinterpret_cast<const float4*>(p) + 1);
+		v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w; v[4] = y.x; v[5] = y.y; v[6] = y.z; v[7] = y.w;
 	}
 	static __device__ __forceinline__ void u16(const uint16_t* p, float* v) {
-		const ushort4 x = __ldg(reinterpret_cast<const ushort4*>(p));
-		v[0] = (float)x.x; v[1] = (float)x.y; v[2] = (float)x.z; v[3] = (float)x.w;
+		const uint4 x = __ldg(reinterpret_cast<const uint4*>(p));
+		v[0] = (float)(x.x & 0xffffu); v[1] = (float)(x.x >> 16); v[2] = (float)(x.y & 0xffffu); v[3] = (float)(x.y >> 16);
+		v[4] = (float)(x.z & 0xffffu); v[5] = (float)(x.z >> 16); v[6] = (float)(x.w & 0xffffu); v[7] = (float)(x.w >> 16);
 	}
-	static __device__ __forceinline__ void st(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+	static __device__ __forceinline__ void st(float* p, const float* v) {
+		reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+		reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+	}
 };
 
-// warp = one image row; lane l = disparities l*DH .. l*DH+DH-1; columns in aligned tiles of CT (CT = 4 needs 16-byte aligned
-// rows of C; A is ours and always is). REVERSE walks right to left and adds to what A already holds.
+// one column step of one path for the DN consecutive disparities a thread owns. st: previous scores in, new scores out (non-finite
+// ones replaced by the worst value, so that the extremum and the neighbour terms skip them like the reference's isfinite tests);
+// lo / hi: previous scores just below / above the thread's range; acc += actual_cost - c (sgm.h:298-300), twice for a line the
+// reference walks twice (Q4). c is NaN for disparities past D: those cells stay at the worst value by themselves.
+template<int DN, int MODE, bool POUT, bool TWICE>
+__device__ __forceinline__ void sw_path(const float (&c)[DN], float (&st)[DN], float lo, float hi, float M, float P1, float P2, float Pout,
+										int kout, float (&acc)[DN], bool twice) {
+	const float WORST = sw_worst<MODE>();
+	if (!isfinite(M)) {   // no finite previous score at all (warp-uniform): actual_cost = c, nothing is added (sgm.h:252, :292)
+#pragma unroll
+		for (int m = 0; m < DN; m++) {
+			const float contrib = c[m] - c[m];   // 0, or NaN for a non-finite cost: what `actual_cost - cv_base` gives (sgm.h:299)
+			acc[m] += contrib;
+			if (TWICE && twice) acc[m] += contrib;
+			st[m] = isfinite(c[m]) ? c[m] : WORST;
+		}
+		return;
+	}
+	const float farv = MODE == SW_SCORE ? M - P2 : M + P2;
+	float left = lo;
+#pragma unroll
+	for (int m = 0; m < DN; m++) {
+		const float cur = st[m];
+		const float right = m < DN - 1 ? st[m < DN - 1 ? m + 1 : 0] : hi;
+		const float a = sw_cell<MODE>(c[m], cur, left, right, M, farv, P1, Pout, POUT && m >= kout);
+		const float contrib = a - c[m];
+		acc[m] += contrib;
+		if (TWICE && twice) acc[m] += contrib;
+		left = cur;
+		st[m] = isfinite(a) ? a : WORST;
+	}
+}
+
+// warp = one image row; lane l = disparities l*DH .. l*DH+DH-1; columns in aligned tiles of CT. The contributions replace the
+// costs in the tile registers and leave as whole tiles. REVERSE walks right to left and adds to what A already holds.
 template<int DH, int CT, int MODE, bool REVERSE>
 __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 	const int lane = threadIdx.x & 31;
@@ -113,34 +155,49 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 	const int64_t crow = (int64_t)i * p.c0 + (int64_t)d0 * p.c2;
 	float* arow = p.A + (int64_t)i * p.a0 + (int64_t)d0 * p.a2;
 	const int t_first = REVERSE ? (je - 1) / CT : jb / CT, t_last = REVERSE ? jb / CT : (je - 1) / CT;
+	const int dt = REVERSE ? -1 : 1;
+	const float nanv = __int_as_float(0x7fc00000);
 	auto load_tile = [&](int tile, float (&v)[DH][CT]) {
 #pragma unroll
 		for (int k = 0; k < DH; k++) {
 			if (d0 + k < p.D) {
 				const int64_t o = crow + (int64_t)k * p.c2 + (int64_t)tile * CT;
-				if (p.c_u16) VecLoad<CT>::u16(static_cast<const uint16_t*>(p.C) + o, v[k]);
-				else VecLoad<CT>::f32(static_cast<const float*>(p.C) + o, v[k]);
+				if (p.c_u16) Tile<CT>::u16(static_cast<const uint16_t*>(p.C) + o, v[k]);
+				else Tile<CT>::f32(static_cast<const float*>(p.C) + o, v[k]);
 			} else {
 #pragma unroll
-				for (int q = 0; q < CT; q++) v[k][q] = 0.f;
+				for (int q = 0; q < CT; q++) v[k][q] = nanv;
+			}
+		}
+	};
+	// the sectors two tiles ahead are pulled into L2 while the next tile's loads are in flight
+	auto prefetch_tile = [&](int tile) {
+		if (CT == 1 || (REVERSE ? tile < t_last : tile > t_last)) return;
+#pragma unroll
+		for (int k = 0; k < DH; k++) {
+			if (d0 + k < p.D) {
+				const int64_t o = crow + (int64_t)k * p.c2 + (int64_t)tile * CT;
+				prefetch_l2(p.c_u16 ? (const void*)(static_cast<const uint16_t*>(p.C) + o) : (const void*)(static_cast<const float*>(p.C) + o));
 			}
 		}
 	};
 	float cn[DH][CT];
 	load_tile(t_first, cn);
-	for (int tile = t_first; REVERSE ? tile >= t_last : tile <= t_last; tile += REVERSE ? -1 : 1) {
-		float c[DH][CT], o[DH][CT];
+	prefetch_tile(t_first + dt);
+	for (int tile = t_first; REVERSE ? tile >= t_last : tile <= t_last; tile += dt) {
+		float c[DH][CT];
 #pragma unroll
 		for (int k = 0; k < DH; k++)
 #pragma unroll
 			for (int q = 0; q < CT; q++) c[k][q] = cn[k][q];
-		if (tile != t_last) load_tile(tile + (REVERSE ? -1 : 1), cn);   // the next tile's loads fly while this one is worked on
+		if (tile != t_last) load_tile(tile + dt, cn);   // the next tile's loads fly while this one is worked on
+		prefetch_tile(tile + 2 * dt);
 		const bool full = tile * CT >= jb && tile * CT + CT <= je;
-		if (REVERSE || !full) {   // REVERSE adds to the forward pass's contributions; partial tiles keep what they do not own
+		float old[REVERSE ? DH : 1][CT];
+		if (REVERSE) {
 #pragma unroll
-			for (int k = 0; k < DH; k++) {
-				if (d0 + k < p.D) VecLoad<CT>::f32(arow + (int64_t)k * p.a2 + (int64_t)tile * CT, o[k]);
-			}
+			for (int k = 0; k < DH; k++)
+				if (d0 + k < p.D) Tile<CT>::f32(arow + (int64_t)k * p.a2 + (int64_t)tile * CT, old[k]);
 		}
 #pragma unroll
 		for (int qq = 0; qq < CT; qq++) {
@@ -152,245 +209,348 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 			for (int k = 0; k < DH; k++) mx = sw_better<MODE>(mx, pf[k]);
 #pragma unroll
 			for (int s = 16; s > 0; s >>= 1) mx = sw_better<MODE>(mx, __shfl_xor_sync(0xffffffffu, mx, s));
-			const float M = mx;
 			float nlo = __shfl_up_sync(0xffffffffu, pf[DH - 1], 1), nhi = __shfl_down_sync(0xffffffffu, pf[0], 1);
 			if (lane == 0) nlo = WORST;
 			if (lane == 31) nhi = WORST;
-			const float farv = MODE == SW_SCORE ? M - p.P2 : M + p.P2;
-			const int kout = p.W - j - d0;   // j + d >= W  <=>  k >= kout
-			float nf[DH];
+			float cc[DH], acc[DH];
 #pragma unroll
-			for (int k = 0; k < DH; k++) {
-				const float l = k > 0 ? pf[k > 0 ? k - 1 : 0] : nlo, r = k < DH - 1 ? pf[k < DH - 1 ? k + 1 : 0] : nhi;
-				const float a = sw_cell<MODE>(c[k][q], pf[k], l, r, M, farv, p.P1, p.Pout, k >= kout);
-				const float contrib = a - c[k][q];
-				o[k][q] = REVERSE ? o[k][q] + contrib : contrib;
-				nf[k] = (isfinite(a) && d0 + k < p.D) ? a : WORST;
-			}
+			for (int k = 0; k < DH; k++) { cc[k] = c[k][q]; acc[k] = REVERSE ? old[REVERSE ? k : 0][q] : 0.f; }
+			// j + d >= W (the Pout term) only concerns the last D columns
+			if (j + p.D <= p.W) sw_path<DH, MODE, false, false>(cc, pf, nlo, nhi, mx, p.P1, p.P2, p.Pout, 0, acc, false);
+			else sw_path<DH, MODE, true, false>(cc, pf, nlo, nhi, mx, p.P1, p.P2, p.Pout, p.W - j - d0, acc, false);
 #pragma unroll
-			for (int k = 0; k < DH; k++) pf[k] = nf[k];
+			for (int k = 0; k < DH; k++) c[k][q] = acc[k];
 		}
+		if (full) {
 #pragma unroll
-		for (int k = 0; k < DH; k++)
-			if (d0 + k < p.D) VecLoad<CT>::st(arow + (int64_t)k * p.a2 + (int64_t)tile * CT, o[k]);
+			for (int k = 0; k < DH; k++)
+				if (d0 + k < p.D) Tile<CT>::st(arow + (int64_t)k * p.a2 + (int64_t)tile * CT, c[k]);
+		} else {   // a tile the margins cut: only its own columns
+#pragma unroll
+			for (int k = 0; k < DH; k++)
+#pragma unroll
+				for (int q = 0; q < CT; q++)
+					if (d0 + k < p.D && tile * CT + q >= jb && tile * CT + q < je) arow[(int64_t)k * p.a2 + (int64_t)tile * CT + q] = c[k][q];
+		}
 	}
 }
 
 // ---- vertical and diagonal paths: sheared strips -----------------------------------------------------------------------------
 
-constexpr int SW_CW = 16;          // columns per strip
-constexpr int SW_QL = 32 / SW_CW;  // disparity chunks per warp
-constexpr int SW_MAXW = 16;        // warps per block
+constexpr int SW_TW = 16;          // columns per strip
+constexpr int SW_NWARP = 8;        // warps per block, two columns each
+constexpr int SW_TWP = SW_TW + 1;  // tile pitch (odd: a warp reading one column over 32 rows touches 32 banks)
 constexpr int SW_SPIN_LIMIT = 1 << 22;
 
 struct VSweep {
 	const void* C; int64_t c0, c2; int c_u16;
 	float* S; int64_t s0, s2;
 	const float* A; int64_t a0, a2;        // horizontal contributions (nullptr: none), added after the straight path's
-	float* xchg; int* progress; int* claim; int* fault;
-	int H, W, D, Dpad, top, left, nrows, ncols;
+	uint2* xchg; unsigned tag_base; int* claim; int* fault;   // xchg: {value bits, tag} pairs, see k_sgm_sweep_t
+	int H, W, D, top, left, nrows, ncols;
 	int sweep;                             // +1: rows top -> bottom, -1: bottom -> top
 	int en[3];                             // path with shift k (0: along the shear, 1: straight, 2: against the shear) is live
 	int rowlive[3], collive[3];            // its lines started by the row-start / the column-start loop are live (Q4)
 	int corner_once;                       // CORRECTED: the corner line is started once (COMPAT: twice, Q4)
 	int accumulate;                        // 0: S = C + contributions, 1: S += contributions
 	int s_lo, s_hi, n_strips;
+	int dbg;                               // measurement aid (STEVI_SGM_DBG): 2 = no wait (results invalid)
 	float P1, P2, Pout;
 };
 
-template<int DC, int MAXW, int MODE>
-__global__ void __launch_bounds__(MAXW * 32) k_sgm_sweep_v(const VSweep p) {
-	constexpr int CW = SW_CW, QL = SW_QL;
-	__shared__ float red[2][3][SW_MAXW][CW];        // per-warp extremum of a column
-	__shared__ float wlo[2][3][SW_MAXW][CW];        // previous score at the warp's lowest disparity
-	__shared__ float whi[2][3][SW_MAXW][CW];        // ... and at its highest
+__device__ __forceinline__ uint4 ld_relaxed_v4(const uint2* p) {
+	uint4 v;
+	asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint2 ld_relaxed_v2(const uint2* p) {
+	uint2 v;
+	asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
+	const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4s(unsigned dst_smem, const void* src) {
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// One block walks one strip down (or up) the rows. Per row the strip's slab of the volume, [D][16 columns], is brought into
+// shared memory with coalesced 64-byte runs (asynchronous copies, one row ahead; an L2 prefetch several rows ahead) and read
+// back TRANSPOSED: a warp works on one pixel at a time, lane l holding the DH consecutive disparities l*DH .. l*DH+DH-1 of
+// each of the three paths through it (previous scores in registers; extremum over d = one warp reduction; the neighbours
+// d-1 / d+1 are in registers except at the lane borders: two shuffles). The tile rows are stored permuted ((d % DH)*32 + d / DH)
+// with an odd pitch, so that the transposed reads and writes are free of bank conflicts. The aggregated costs are staged in
+// the tile of the horizontal contributions (read a, write S in place) and leave with the same 64-byte runs.
+// Warp w owns the tile columns 2w and 2w+1. The tile slides one column to the right per row (the shear), so along the shear a
+// path stays in its registers; the straight path moves one column to the left inside the tile, the path against the shear
+// two: three vectors per warp and row go to the warp on the left through shared memory — and from warp 0 to the strip on the
+// left, from the strip on the right to warp 7, through global memory: every float travels as an 8-byte {bits, tag} pair written
+// by one store (tag = launch epoch << 16 | row + 1), so the reader needs no fence and no separate flag: it polls the pairs
+// it needs until their tags are this launch's and this row's.
+template<int DH, int MODE>
+__global__ void __launch_bounds__(SW_NWARP * 32, DH <= 8 ? 2 : 1) k_sgm_sweep_t(const VSweep p) {
+	constexpr int TW = SW_TW, TWP = SW_TWP, NWARP = SW_NWARP, DR = 32 * DH, TILE = DR * TWP;
+	extern __shared__ float smem[];
+	float* Ct = smem;                                   // [2][DR][TWP] costs
+	float* Xt = Ct + 2 * TILE;                          // [2][DR][TWP] horizontal contributions (if any)
+	float* Yt = Xt + (p.A ? 2 * TILE : 0);              // [2][DR][TWP] the volume being added to (second sweep, framed first sweep)
+	float* ex = Yt + (p.accumulate ? 2 * TILE : 0);     // [3][NWARP + 1][DR] vectors handed to the warp on the left (slot NWARP: from the strip on the right)
+	float* Ot = p.A ? Xt : Yt;                          // the tile the results are staged in
 	__shared__ int s_claim;
 	const float WORST = sw_worst<MODE>();
-	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NW = blockDim.x >> 5;
-	const int x = lane % CW, q = lane / CW;
-	const int d0 = (w * QL + q) * DC;
+	const float nanv = __int_as_float(0x7fc00000);
+	const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+	const int d0 = lane * DH;
+	const int dn = min(DH, p.D - d0);                   // disparities of this lane that exist
+	const bool xch = p.en[1] || p.en[2];
+	const int fcol = tid & 15, frow = tid >> 4;         // fill / flush role: column of the tile, first of the disparity rows
 	for (;;) {
-		if (threadIdx.x == 0) s_claim = atomicAdd(p.claim, 1);
+		if (tid == 0) s_claim = atomicAdd(p.claim, 1);
 		__syncthreads();
 		const int claim = s_claim;
 		__syncthreads();
 		if (claim >= p.n_strips) return;
 		const int s = p.s_hi - claim;   // right to left: whatever this strip waits for has been claimed before
-		const int t_begin = max(0, -s * CW - (CW - 1)), t_end = min(p.nrows, p.ncols - s * CW);
+		const int t_begin = max(0, -s * TW - (TW - 1)), t_end = min(p.nrows, p.ncols - s * TW);
 		const bool has_right = s + 1 <= p.s_hi;
-		const int rt_begin = max(0, -(s + 1) * CW - (CW - 1)), rt_end = min(p.nrows, p.ncols - (s + 1) * CW);
-		const float* xin = p.xchg + (int64_t)(s + 1 - p.s_lo) * p.nrows * 3 * p.Dpad + d0;
-		float* xout = p.xchg + (int64_t)(s - p.s_lo) * p.nrows * 3 * p.Dpad + d0;
-		const int* prog_in = p.progress + (int64_t)(s + 1 - p.s_lo) * SW_MAXW + w;
-		int* prog_out = p.progress + (int64_t)(s - p.s_lo) * SW_MAXW + w;
-		int seen = 0;
-		float st[3][DC];   // what this lane computed in the previous step, per path
-#pragma unroll
-		for (int k = 0; k < 3; k++)
-#pragma unroll
-			for (int m = 0; m < DC; m++) st[k][m] = WORST;
+		const int rt_begin = max(0, -(s + 1) * TW - (TW - 1)), rt_end = min(p.nrows, p.ncols - (s + 1) * TW);
+		const uint2* xin = p.xchg + (int64_t)(s + 1 - p.s_lo) * p.nrows * 3 * DR + d0;
+		uint2* xout = p.xchg + (int64_t)(s - p.s_lo) * p.nrows * 3 * DR + d0;
 		auto row_of = [&](int t) { return p.sweep > 0 ? p.top + t : p.top + p.nrows - 1 - t; };
-		auto load_c = [&](int t, int cc, float (&v)[DC]) {
-			const bool ok = cc >= 0 && cc < p.ncols && t < t_end;
-			const int64_t o = (int64_t)row_of(t) * p.c0 + (int64_t)d0 * p.c2 + (p.left + cc);
+		// ---- tile traffic
+		constexpr int NU = 2 * DH, SRU = (16 / DH) * TWP;   // disparity rows per thread; tile offset between two of them
+		const int srow0 = ((frow % DH) * 32 + frow / DH) * TWP + fcol;   // (row d = frow + 16 u sits at tile row (d % DH) * 32 + d / DH)
+		const int nu = min(NU, (p.D - frow + 15) / 16);                  // disparity rows of this thread that exist
+		const int fcc0 = s * TW + fcol;                                  // this thread's column in row t: fcc0 + t
+		// running pointers of the thread's first disparity row at (row t, its column in row t): one 64-bit add per row and stream
+		const int64_t row_b = p.sweep > 0 ? p.top + t_begin : p.top + p.nrows - 1 - t_begin;
+		const int64_t rs = p.sweep > 0 ? 1 : -1;
+		const int64_t col_b = p.left + fcc0 + t_begin;
+		const char* gC = static_cast<const char*>(p.C) + (row_b * p.c0 + (int64_t)frow * p.c2 + col_b) * (p.c_u16 ? 2 : 4);
+		const float* gA = p.A ? p.A + row_b * p.a0 + (int64_t)frow * p.a2 + col_b : nullptr;
+		float* gS = p.S + row_b * p.s0 + (int64_t)frow * p.s2 + col_b;
+		const int64_t stepC = (rs * p.c0 + 1) * (p.c_u16 ? 2 : 4), stepA = rs * p.a0 + 1, stepS = rs * p.s0 + 1;
+		const int64_t dC = 16 * p.c2 * (p.c_u16 ? 2 : 4), dA = 16 * p.a2, dS = 16 * p.s2;
+		const unsigned sC = (unsigned)__cvta_generic_to_shared(Ct) + 4u * srow0, sX = (unsigned)__cvta_generic_to_shared(Xt) + 4u * srow0,
+					   sY = (unsigned)__cvta_generic_to_shared(Yt) + 4u * srow0;
+		// slab of the row the pointers stand on (row t) -> buffer t & 1 (asynchronous; u16 costs through registers)
+		auto fill = [&](int t, const char* pc, const float* pa, const float* ps) {
+			if (t >= t_end) return;
+			const int cc = fcc0 + t;
+			if (cc < 0 || cc >= p.ncols) return;
+			const unsigned bo = (t & 1) * (4u * TILE);
+			if (p.c_u16) {   // no 2-byte asynchronous copies: all loads first, then the stores
+				uint16_t v[NU];
 #pragma unroll
-			for (int m = 0; m < DC; m++) {
-				v[m] = 0.f;
-				if (ok && d0 + m < p.D) v[m] = p.c_u16 ? (float)__ldg(static_cast<const uint16_t*>(p.C) + o + m * p.c2)
-												   : __ldg(static_cast<const float*>(p.C) + o + m * p.c2);
+				for (int u = 0; u < NU; u++, pc += dC) v[u] = u < nu ? __ldg(reinterpret_cast<const uint16_t*>(pc)) : (uint16_t)0;
+#pragma unroll
+				for (int u = 0; u < NU; u++) if (u < nu) Ct[(t & 1) * TILE + srow0 + u * SRU] = (float)v[u];
+			} else {
+#pragma unroll
+				for (int u = 0; u < NU; u++, pc += dC) if (u < nu) cp_async4s(sC + bo + 4u * (u * SRU), pc);
+			}
+			if (p.A) {
+#pragma unroll
+				for (int u = 0; u < NU; u++, pa += dA) if (u < nu) cp_async4s(sX + bo + 4u * (u * SRU), pa);
+			}
+			if (p.accumulate) {
+#pragma unroll
+				for (int u = 0; u < NU; u++, ps += dS) if (u < nu) cp_async4s(sY + bo + 4u * (u * SRU), ps);
 			}
 		};
-		float cn[DC];
-		load_c(t_begin, s * CW + t_begin + x, cn);
-		for (int t = t_begin; t < t_end; t++) {
-			const int buf = t & 1;
-			const int cc = s * CW + t + x;   // column inside the margin rectangle
-			const bool valid = cc >= 0 && cc < p.ncols;
-			const int i = row_of(t), j = p.left + cc;
-			float c[DC];
+		auto flush = [&](int t, float* ps) {   // staged results of row t -> S (ps stands on row t)
+			const int cc = fcc0 + t;
+			if (cc < 0 || cc >= p.ncols) return;
+			const float* src = Ot + (t & 1) * TILE + srow0;
 #pragma unroll
-			for (int m = 0; m < DC; m++) c[m] = cn[m];
-			load_c(t + 1, cc + 1, cn);
-			// this step's other operands: issued now, used after the recurrences
-			float av[DC], sacc[DC];
-			{
-				const int64_t oa = (int64_t)i * p.a0 + (int64_t)d0 * p.a2 + j;
-				const int64_t os = (int64_t)i * p.s0 + (int64_t)d0 * p.s2 + j;
-#pragma unroll
-				for (int m = 0; m < DC; m++) {
-					av[m] = 0.f; sacc[m] = 0.f;
-					if (valid && d0 + m < p.D) {
-						if (p.A) av[m] = __ldg(p.A + oa + m * p.a2);
-						if (p.accumulate) sacc[m] = p.S[os + m * p.s2];
-					}
-				}
+			for (int u = 0; u < NU; u++, ps += dS) if (u < nu) *ps = src[u * SRU];
+		};
+		constexpr int PD = 5;
+		auto prefetch = [&](int t) {   // thread = one disparity row of the slab PD rows ahead: its first and last sector
+			if (t >= t_end || tid >= p.D) return;
+			const int64_t r = row_of(t);
+			const int j0 = p.left + min(max(s * TW + t, 0), p.ncols - 1), j1 = p.left + min(max(s * TW + t + TW - 1, 0), p.ncols - 1);
+			if (p.c_u16) {
+				const uint16_t* q = static_cast<const uint16_t*>(p.C) + r * p.c0 + (int64_t)tid * p.c2;
+				prefetch_l2(q + j0); prefetch_l2(q + j1);
+			} else {
+				const float* q = static_cast<const float*>(p.C) + r * p.c0 + (int64_t)tid * p.c2;
+				prefetch_l2(q + j0); prefetch_l2(q + j1);
 			}
-			// ---- inputs of the three paths
-			// shift 1 / 2: the state of the lane one / two to the right; beyond the strip: what the right neighbour published
-			const bool need_in = has_right && t >= 1 && t - 1 >= rt_begin && t - 1 < rt_end && x >= CW - 2 && (p.en[1] || p.en[2]);
-			if (need_in && seen < t) {
-				int spins = 0;
-				while ((seen = ld_acquire(prog_in)) < t) {
-					if (++spins > SW_SPIN_LIMIT) { *p.fault = 1; seen = INT_MAX; break; }   // raise the fault flag instead of hanging
-					__nanosleep(20);
-				}
+			if (p.A) { const float* q = p.A + r * p.a0 + (int64_t)tid * p.a2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
+			if (p.accumulate) { const float* q = p.S + r * p.s0 + (int64_t)tid * p.s2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
+		};
+		// ---- state: previous scores of the three paths through the warp's two columns, and the vectors coming in from the right
+		float st[3][2][DH];
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+#pragma unroll
+			for (int m = 0; m < DH; m++) { st[k][0][m] = WORST; st[k][1][m] = WORST; }
+		}
+		for (int u = tid; u < 3 * (NWARP + 1) * DR; u += NWARP * 32) ex[u] = WORST;
+		float* const exr = ex + (w + 1) * DR + lane;   // what the warp (or strip) on the right handed over: exr[(k * (NWARP + 1)) * DR + m * 32]
+		// what the strip on the right published for row t - 1 (warp 7 only): slot 0 = straight path of its first column,
+		// slots 1, 2 = path against the shear of its first and second column
+		bool pending = false;
+		// warp 7: the vectors of the strip on the right for row t go to exchange slot NWARP. block = false: only if they are
+		// already there (asked at the end of the previous row: the wait, if any, is left to the start of the row that needs them)
+		auto fetch_right = [&](int t, bool block) {
+			pending = false;
+			const bool need = xch && has_right && t >= 1 && t - 1 >= rt_begin && t - 1 < rt_end && t < t_end;
+			float* dstx = ex + NWARP * DR + lane;
+			if (!need) {
+#pragma unroll
+				for (int k = 0; k < 3; k++)
+#pragma unroll
+					for (int m = 0; m < DH; m++) dstx[(k * (NWARP + 1)) * DR + m * 32] = WORST;
+				return;
 			}
-			float in[3][DC];
+			const uint2* src = xin + (int64_t)(t - 1) * 3 * DR;
+			const unsigned tag = p.tag_base | (unsigned)t;   // what the neighbour wrote for its row t - 1
+			for (int spins = 0;; spins++) {
+				bool ok = true;
+				float v3[3][DH];
 #pragma unroll
-			for (int m = 0; m < DC; m++) in[0][m] = st[0][m];
-#pragma unroll
-			for (int k = 1; k < 3; k++) {
-				if (!p.en[k]) continue;
-#pragma unroll
-				for (int m = 0; m < DC; m++) in[k][m] = __shfl_down_sync(0xffffffffu, st[k][m], k, CW);
-				if (x + k >= CW) {
-					if (need_in) {
-						const int slot = k == 1 ? 0 : 1 + (x + 2 - CW);
-						const float4* src = reinterpret_cast<const float4*>(xin + ((int64_t)(t - 1) * 3 + slot) * p.Dpad);
-#pragma unroll
-						for (int m4 = 0; m4 < DC / 4; m4++) {
-							const float4 v = __ldcg(src + m4);
-							in[k][4 * m4] = v.x; in[k][4 * m4 + 1] = v.y; in[k][4 * m4 + 2] = v.z; in[k][4 * m4 + 3] = v.w;
-						}
+				for (int k = 0; k < 3; k++) {
+					if (DH == 1) {
+						const uint2 v = ld_relaxed_v2(src + k * DR);
+						ok = ok && v.y == tag;
+						v3[k][0] = __uint_as_float(v.x);
 					} else {
 #pragma unroll
-						for (int m = 0; m < DC; m++) in[k][m] = WORST;
+						for (int m = 0; m < DH; m += 2) {
+							const uint4 v = ld_relaxed_v4(src + k * DR + m);
+							ok = ok && v.y == tag && v.w == tag;
+							v3[k][m] = __uint_as_float(v.x);
+							v3[k][m + 1 < DH ? m + 1 : 0] = __uint_as_float(v.z);
+						}
+					}
+				}
+				if (__all_sync(0xffffffffu, ok) || (p.dbg & 2)) {
+#pragma unroll
+					for (int k = 0; k < 3; k++)
+#pragma unroll
+						for (int m = 0; m < DH; m++) dstx[(k * (NWARP + 1)) * DR + m * 32] = v3[k][m];
+					return;
+				}
+				if (!block) { pending = true; return; }
+				if (spins > SW_SPIN_LIMIT) { *p.fault = 1; return; }   // raise the fault flag instead of hanging
+				__nanosleep(100);
+			}
+		};
+		for (int u = 0; u < PD; u++) prefetch(t_begin + u);
+		fill(t_begin, gC, gA, gS);
+		if (w == NWARP - 1) fetch_right(t_begin, true);
+		for (int t = t_begin; t < t_end; t++) {
+			cp_async_wait_all();
+			__syncthreads();   // the slab of row t is in place; everyone is done with the previous row's tiles and exchange vectors
+			float* const gS_now = gS;
+			gC += stepC; gA += stepA; gS += stepS;   // (gA is only dereferenced when there is an A)
+			fill(t + 1, gC, gA, gS);
+			prefetch(t + PD);
+			const int tb = (t & 1) * TILE;
+			if (w == NWARP - 1 && pending) { fetch_right(t, true); __syncwarp(); }
+#pragma unroll
+			for (int ci = 0; ci < 2; ci++) {
+				const int l = 2 * w + ci;
+				const int cc = s * TW + t + l;   // column inside the margin rectangle
+				if (cc < 0 || cc >= p.ncols) continue;   // (warp-uniform)
+				const int j = p.left + cc;
+				float c[DH], acc[DH];
+#pragma unroll
+				for (int m = 0; m < DH; m++) c[m] = m < dn ? Ct[tb + (m * 32 + lane) * TWP + l] : nanv;
+				if (p.accumulate) {
+#pragma unroll
+					for (int m = 0; m < DH; m++) acc[m] = Yt[tb + (m * 32 + lane) * TWP + l];
+				} else {
+#pragma unroll
+					for (int m = 0; m < DH; m++) acc[m] = c[m];   // sgm.h:371-377
+				}
+				// the reference's order of additions: Up2Down, Left2Right, UpLeft2DownRight, UpRight2DownLeft (sgm.h:379-388)
+				const int order[3] = {1, 0, 2};
+#pragma unroll
+				for (int oi = 0; oi < 3; oi++) {
+					const int k = order[oi];
+					if (p.en[k]) {
+						// line weight (Q4): how many times the reference walks the line through this pixel on this path
+						const int sh = 1 - k;
+						const int kr = sh > 0 ? cc : (sh < 0 ? p.ncols - 1 - cc : INT_MAX), kc = t;
+						int wt = ((kr <= kc && p.rowlive[k]) ? 1 : 0) + ((kc <= kr && p.collive[k]) ? 1 : 0);
+						if (wt == 2 && p.corner_once) wt = 1;
+						// previous scores: where the line was one row ago
+						float in[DH];
+						if (k == 0) {
+#pragma unroll
+							for (int m = 0; m < DH; m++) in[m] = st[0][ci][m];
+						} else if (k == 1) {
+#pragma unroll
+							for (int m = 0; m < DH; m++) in[m] = ci == 0 ? st[1][1][m] : exr[m * 32];
+						} else {
+#pragma unroll
+							for (int m = 0; m < DH; m++) in[m] = exr[((1 + ci) * (NWARP + 1)) * DR + m * 32];
+						}
+						// a path whose previous pixel lies outside the margin rectangle starts here: previous_cost = 0 (sgm.h:206-208)
+						const bool fresh = t == 0 || (k == 0 && cc == 0) || (k == 2 && cc == p.ncols - 1);
+						if (fresh) {
+#pragma unroll
+							for (int m = 0; m < DH; m++) in[m] = m < dn ? 0.f : WORST;
+						}
+						if (wt) {   // a line that is not walked never is: its state does not matter
+							float mx = WORST;
+#pragma unroll
+							for (int m = 0; m < DH; m++) mx = sw_better<MODE>(mx, in[m]);
+#pragma unroll
+							for (int o = 16; o > 0; o >>= 1) mx = sw_better<MODE>(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+							float lo = __shfl_up_sync(0xffffffffu, in[DH - 1], 1), hi = __shfl_down_sync(0xffffffffu, in[0], 1);
+							if (lane == 0) lo = WORST;
+							if (lane == 31) hi = WORST;
+							if (j + p.D <= p.W) sw_path<DH, MODE, false, true>(c, in, lo, hi, mx, p.P1, p.P2, p.Pout, 0, acc, k == 0 && wt == 2);
+							else sw_path<DH, MODE, true, true>(c, in, lo, hi, mx, p.P1, p.P2, p.Pout, p.W - j - d0, acc, k == 0 && wt == 2);
+						}
+#pragma unroll
+						for (int m = 0; m < DH; m++) st[k][ci][m] = in[m];
+					}
+					if (oi == 0 && p.A) {
+#pragma unroll
+						for (int m = 0; m < DH; m++) acc[m] += Xt[tb + (m * 32 + lane) * TWP + l];
+					}
+				}
+#pragma unroll
+				for (int m = 0; m < DH; m++) if (m < dn) Ot[tb + (m * 32 + lane) * TWP + l] = acc[m];
+			}
+			// ---- hand-over to the strip on the left / from the strip on the right (global memory)
+			if (w == 0 && xch && s > p.s_lo) {
+				uint2* dst = xout + (int64_t)t * 3 * DR;
+				const unsigned tag = p.tag_base | (unsigned)(t + 1);
+				const float* src[3] = {st[1][0], st[2][0], st[2][1]};
+#pragma unroll
+				for (int k = 0; k < 3; k++) {
+					if (DH == 1) __stcg(dst + k * DR, make_uint2(__float_as_uint(src[k][0]), tag));
+					else {
+#pragma unroll
+						for (int m = 0; m < DH; m += 2)
+							__stcg(reinterpret_cast<uint4*>(dst + k * DR + m),
+								   make_uint4(__float_as_uint(src[k][m]), tag, __float_as_uint(src[k][m + 1 < DH ? m + 1 : 0]), tag));
 					}
 				}
 			}
-			// a path whose previous pixel lies outside the margin rectangle starts here: previous_cost = 0 (sgm.h:206-208)
-			const bool fresh[3] = {t == 0 || cc == 0, t == 0, t == 0 || cc == p.ncols - 1};
+			if (w == NWARP - 1) fetch_right(t + 1, false);
+			__syncthreads();   // results of row t staged; everyone has read this row's exchange vectors
+			if (w > 0) {   // vectors for the warp on the left (next row)
 #pragma unroll
-			for (int k = 0; k < 3; k++)
-				if (fresh[k]) {
-#pragma unroll
-					for (int m = 0; m < DC; m++) in[k][m] = (d0 + m < p.D) ? 0.f : WORST;
-				}
-			// ---- per-column extremum over d and the neighbours across chunk borders
-			float nlo[3], nhi[3];
-#pragma unroll
-			for (int k = 0; k < 3; k++) {
-				if (!p.en[k]) continue;
-				float mx = WORST;
-#pragma unroll
-				for (int m = 0; m < DC; m++) mx = sw_better<MODE>(mx, in[k][m]);
-#pragma unroll
-				for (int o = CW; o < 32; o <<= 1) mx = sw_better<MODE>(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-				nlo[k] = __shfl_up_sync(0xffffffffu, in[k][DC - 1], CW);     // chunk q-1 of this warp
-				nhi[k] = __shfl_down_sync(0xffffffffu, in[k][0], CW);        // chunk q+1
-				if (q == 0) { red[buf][k][w][x] = mx; wlo[buf][k][w][x] = in[k][0]; }
-				if (q == QL - 1) whi[buf][k][w][x] = in[k][DC - 1];
-			}
-			__syncthreads();
-			// line weights (Q4): how many times the reference walks the line through this pixel for each path
-			int wt[3];
-#pragma unroll
-			for (int k = 0; k < 3; k++) {
-				const int sh = 1 - k;
-				const int kr = sh > 0 ? cc : (sh < 0 ? p.ncols - 1 - cc : INT_MAX), kc = t;
-				int n = ((kr <= kc && p.rowlive[k]) ? 1 : 0) + ((kc <= kr && p.collive[k]) ? 1 : 0);
-				if (n == 2 && p.corner_once) n = 1;
-				wt[k] = (p.en[k] && valid) ? n : 0;
-			}
-			if (!p.accumulate) {
-#pragma unroll
-				for (int m = 0; m < DC; m++) sacc[m] = c[m];   // sgm.h:371-377
-			}
-			const int kout = p.W - j - d0;
-			// the reference's order of additions: Up2Down, Left2Right, UpLeft2DownRight, UpRight2DownLeft (sgm.h:379-388)
-			const int order[3] = {1, 0, 2};
-#pragma unroll
-			for (int oi = 0; oi < 3; oi++) {
-				const int k = order[oi];
-				if (p.en[k]) {
-					float M = WORST;
-					for (int ww = 0; ww < NW; ww++) M = sw_better<MODE>(M, red[buf][k][ww][x]);
-					float lo = nlo[k], hi = nhi[k];
-					if (q == 0) lo = w > 0 ? whi[buf][k][w > 0 ? w - 1 : 0][x] : WORST;
-					if (q == QL - 1) hi = w + 1 < NW ? wlo[buf][k][w + 1 < NW ? w + 1 : 0][x] : WORST;
-					const float farv = MODE == SW_SCORE ? M - p.P2 : M + p.P2;
-#pragma unroll
-					for (int m = 0; m < DC; m++) {
-						const float l = m > 0 ? in[k][m > 0 ? m - 1 : 0] : lo, r = m < DC - 1 ? in[k][m < DC - 1 ? m + 1 : 0] : hi;
-						const float a = sw_cell<MODE>(c[m], in[k][m], l, r, M, farv, p.P1, p.Pout, m >= kout);
-						const float contrib = a - c[m];
-						if (wt[k] >= 1) sacc[m] += contrib;
-						if (wt[k] >= 2) sacc[m] += contrib;
-						st[k][m] = (isfinite(a) && d0 + m < p.D) ? a : WORST;
-					}
-				}
-				if (oi == 0 && p.A && valid) {
-#pragma unroll
-					for (int m = 0; m < DC; m++) sacc[m] += av[m];
+				for (int m = 0; m < DH; m++) {
+					ex[(0 * (NWARP + 1) + w) * DR + m * 32 + lane] = st[1][0][m];
+					ex[(1 * (NWARP + 1) + w) * DR + m * 32 + lane] = st[2][0][m];
+					ex[(2 * (NWARP + 1) + w) * DR + m * 32 + lane] = st[2][1][m];
 				}
 			}
-			if (valid) {
-				const int64_t os = (int64_t)i * p.s0 + (int64_t)d0 * p.s2 + j;
-#pragma unroll
-				for (int m = 0; m < DC; m++)
-					if (d0 + m < p.D) p.S[os + m * p.s2] = sacc[m];
-			}
-			// ---- publish the two leftmost lanes for the strip on the left
-			if (s > p.s_lo && (p.en[1] || p.en[2])) {
-				if (x < 2) {
-					float* dst = xout + (int64_t)t * 3 * p.Dpad;
-					if (x == 0 && p.en[1]) {
-#pragma unroll
-						for (int m4 = 0; m4 < DC / 4; m4++)
-							__stcg(reinterpret_cast<float4*>(dst) + m4, make_float4(st[1][4 * m4], st[1][4 * m4 + 1], st[1][4 * m4 + 2], st[1][4 * m4 + 3]));
-					}
-					if (p.en[2]) {
-						float4* d2 = reinterpret_cast<float4*>(dst + (1 + x) * p.Dpad);
-#pragma unroll
-						for (int m4 = 0; m4 < DC / 4; m4++)
-							__stcg(d2 + m4, make_float4(st[2][4 * m4], st[2][4 * m4 + 1], st[2][4 * m4 + 2], st[2][4 * m4 + 3]));
-					}
-					__threadfence();
-				}
-				__syncwarp();
-				if (lane == 0) st_release(prog_out, t + 1);
-			}
+			flush(t, gS_now);
 		}
+		cp_async_wait_all();
+		__syncthreads();
 	}
 }
 
@@ -407,22 +567,35 @@ static int32_t launch_h(stevi_ctx* c, const HSweep& p, bool vec) {
 	const int rows = p.H - p.top - p.bottom;
 	dim3 grid(cdiv(rows, 4));
 	const int dh = cdiv(p.D, 32);
-#define STEVI_H(DH) do { if (vec) STEVI_LAUNCH(c, (k_sgm_sweep_h<DH, 4, MODE, REVERSE>), grid, 128, 0, p); \
+#define STEVI_H(DH) do { if (vec) STEVI_LAUNCH(c, (k_sgm_sweep_h<DH, 8, MODE, REVERSE>), grid, 128, 0, p); \
 	else STEVI_LAUNCH(c, (k_sgm_sweep_h<DH, 1, MODE, REVERSE>), grid, 128, 0, p); } while (0)
 	if (dh <= 1) STEVI_H(1); else if (dh <= 2) STEVI_H(2); else if (dh <= 4) STEVI_H(4); else if (dh <= 8) STEVI_H(8); else STEVI_H(16);
 #undef STEVI_H
 	return STEVI_OK;
 }
 
+static size_t sweep_smem(int dh, bool has_a, bool accumulate) {
+	const size_t tile = (size_t)32 * dh * SW_TWP;
+	return (2 * tile * (1 + (has_a ? 1 : 0) + (accumulate ? 1 : 0)) + (size_t)3 * (SW_NWARP + 1) * 32 * dh) * sizeof(float);
+}
+
 template<int MODE>
 static int32_t launch_v(stevi_ctx* c, const VSweep& p) {
-	const int dc = p.D <= 64 ? 4 : p.D <= 128 ? 8 : 16;
-	const int nw = std::max(1, cdiv(cdiv(p.D, dc), SW_QL));
-	dim3 grid(std::min(p.n_strips, c->sm_count * (nw <= 8 ? 2 : 1)));
-	if (dc == 4) STEVI_LAUNCH(c, (k_sgm_sweep_v<4, 8, MODE>), grid, nw * 32, 0, p);
-	else if (dc == 8) STEVI_LAUNCH(c, (k_sgm_sweep_v<8, 8, MODE>), grid, nw * 32, 0, p);
-	else if (nw <= 8) STEVI_LAUNCH(c, (k_sgm_sweep_v<16, 8, MODE>), grid, nw * 32, 0, p);
-	else STEVI_LAUNCH(c, (k_sgm_sweep_v<16, 16, MODE>), grid, nw * 32, 0, p);
+	const int dh = p.D <= 32 ? 1 : p.D <= 64 ? 2 : p.D <= 128 ? 4 : p.D <= 256 ? 8 : 16;
+	const size_t smem = sweep_smem(dh, p.A != nullptr, p.accumulate != 0);
+	const int per_sm = std::max(1, std::min(dh <= 8 ? 2 : 1, (int)((220u << 10) / smem)));
+	dim3 grid(std::min(p.n_strips, c->sm_count * per_sm));
+#define STEVI_T(DH) do { \
+	STEVI_CUDA(c, cudaFuncSetAttribute((k_sgm_sweep_t<DH, MODE>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+	STEVI_LAUNCH(c, (k_sgm_sweep_t<DH, MODE>), grid, SW_NWARP * 32, smem, p); } while (0)
+	switch (dh) {
+	case 1: STEVI_T(1); break;
+	case 2: STEVI_T(2); break;
+	case 4: STEVI_T(4); break;
+	case 8: STEVI_T(8); break;
+	default: STEVI_T(16); break;
+	}
+#undef STEVI_T
 	return STEVI_OK;
 }
 
@@ -450,7 +623,7 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 		if (nrows <= 0 || ncols <= 0) return STEVI_OK;
 	}
 	// ---- horizontal paths -> A (dense [H][D][W4], rows 16-byte aligned)
-	const int W4 = (W + 3) / 4 * 4;
+	const int W4 = (W + 7) / 8 * 8;   // rows of A start on 32-byte sectors
 	float* A = nullptr;
 	STEVI_TRY(arena_alloc_t(c, (size_t)H * D * W4, &A));
 	HSweep h;
@@ -459,7 +632,7 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 	h.H = H; h.W = W; h.D = D; h.top = mg.top; h.bottom = mg.bottom; h.left = mg.left; h.right = mg.right;
 	h.P1 = P1; h.P2 = P2; h.Pout = Pout;
 	const size_t esz = dtype_size(cv.dtype);
-	const bool vec = (uintptr_t)cv.p % (4 * esz) == 0 && cv.st[0] % 4 == 0 && cv.st[2] % 4 == 0 && W % 4 == 0;
+	const bool vec = (uintptr_t)cv.p % (8 * esz) == 0 && cv.st[0] % 8 == 0 && cv.st[2] % 8 == 0 && W % 8 == 0;
 	if (mode == SW_SCORE) STEVI_TRY((launch_h<SW_SCORE, false>(c, h, vec)));
 	else if (mode == SW_COST) STEVI_TRY((launch_h<SW_COST, false>(c, h, vec)));
 	else STEVI_TRY((launch_h<SW_COST_COMPAT, false>(c, h, vec)));
@@ -473,25 +646,33 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 	v.S = out.as<float>(); v.s0 = out.st[0]; v.s2 = out.st[2];
 	v.a0 = h.a0; v.a2 = h.a2;
 	v.H = H; v.W = W; v.D = D; v.top = mg.top; v.left = mg.left; v.nrows = nrows; v.ncols = ncols;
-	const int dc = D <= 64 ? 4 : D <= 128 ? 8 : 16;
-	v.Dpad = cdiv(D, dc * SW_QL) * dc * SW_QL;
+	const int cw = SW_TW;
+	const int dr = 32 * (D <= 32 ? 1 : D <= 64 ? 2 : D <= 128 ? 4 : D <= 256 ? 8 : 16);   // disparity rows of a tile
 	v.P1 = P1; v.P2 = P2; v.Pout = Pout;
 	v.corner_once = corrected ? 1 : 0;
 	v.fault = c->fault_dev;
-	v.s_lo = -((nrows - 1 + SW_CW - 1) / SW_CW);
-	const int s_all = (ncols - 1) / SW_CW;
-	const size_t xn = (size_t)(s_all - v.s_lo + 1) * nrows * 3 * v.Dpad;
-	const size_t pn = (size_t)(s_all - v.s_lo + 1) * SW_MAXW + 1;
-	int* flags = nullptr;
-	STEVI_TRY(arena_alloc_t(c, xn, &v.xchg));
-	STEVI_TRY(arena_alloc_t(c, 2 * pn, &flags));
-	STEVI_CUDA(c, cudaMemsetAsync(flags, 0, 2 * pn * sizeof(int), c->stream));
+	{ static const char* e = getenv("STEVI_SGM_DBG"); v.dbg = e ? atoi(e) : 0; }
+	v.s_lo = -((nrows - 1 + cw - 1) / cw);
+	const int s_all = (ncols - 1) / cw;
+	// exchange buffer between neighbouring strips: persistent in the ctx (only ever holds this kernel's tagged pairs)
+	const size_t xbytes = (size_t)(s_all - v.s_lo + 1) * nrows * 3 * dr * sizeof(uint2);
+	if (c->sgm_xchg_bytes < xbytes) {
+		STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+		if (c->sgm_xchg) cudaFree(c->sgm_xchg);
+		c->sgm_xchg = nullptr; c->sgm_xchg_bytes = 0;
+		STEVI_CUDA(c, cudaMalloc(&c->sgm_xchg, xbytes));
+		c->sgm_xchg_bytes = xbytes;
+		c->sgm_epoch = 0;
+	}
+	v.xchg = static_cast<uint2*>(c->sgm_xchg);
+	int* claims = nullptr;
+	STEVI_TRY(arena_alloc_t(c, 2, &claims));
+	STEVI_CUDA(c, cudaMemsetAsync(claims, 0, 2 * sizeof(int), c->stream));
 	for (int pass = 0; pass < 2; pass++) {
 		v.sweep = pass == 0 ? 1 : -1;
 		v.A = pass == 0 ? A : nullptr;
 		v.accumulate = (pass == 1 || framed) ? 1 : 0;
-		v.progress = flags + pass * pn;
-		v.claim = v.progress + pn - 1;
+		v.claim = claims + pass;
 		bool any = false, any_col = false;
 		for (int k = 0; k < 3; k++) {
 			const int sh = 1 - k;
@@ -508,6 +689,12 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 		// (the only row starts of a sweep without live column starts) stay at or left of the diagonal through the corner
 		v.s_hi = (any_col || pass == 0) ? s_all : 0;
 		v.n_strips = v.s_hi - v.s_lo + 1;
+		// a tag no earlier launch on this buffer has used (zeroed buffer = tag 0 = never valid)
+		if (c->sgm_epoch == 0 || c->sgm_epoch >= 0xffffu) {
+			STEVI_CUDA(c, cudaMemsetAsync(c->sgm_xchg, 0, c->sgm_xchg_bytes, c->stream));
+			c->sgm_epoch = 0;
+		}
+		v.tag_base = (unsigned)(++c->sgm_epoch) << 16;
 		if (mode == SW_SCORE) STEVI_TRY(launch_v<SW_SCORE>(c, v));
 		else if (mode == SW_COST) STEVI_TRY(launch_v<SW_COST>(c, v));
 		else STEVI_TRY(launch_v<SW_COST_COMPAT>(c, v));

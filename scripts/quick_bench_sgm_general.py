@@ -37,12 +37,7 @@ def breakdown(fn):
     fn()
     rep = ctx.timing_report()
     ctx.set_timing(False)
-    agg = {}
-    for name, ms in rep:
-        agg.setdefault(name, [0, 0.0])
-        agg[name][0] += 1
-        agg[name][1] += ms
-    return {k: {"launches": v[0], "ms": round(v[1], 4)} for k, v in agg.items()}
+    return [[name.strip("()"), round(ms, 4)] for name, ms in rep]   # in launch order
 
 
 H, W, D = (int(x) for x in os.environ.get("SGM_SHAPE", "1080,1920,256").split(","))
