@@ -237,8 +237,8 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 
 // ---- vertical and diagonal paths: sheared strips -----------------------------------------------------------------------------
 
-constexpr int SW_TW = 16;          // columns per strip
-constexpr int SW_NWARP = 8;        // warps per block, two columns each
+constexpr int SW_TW = 16;          // columns per strip = warps per block (a warp per column)
+constexpr int SW_NWARP = SW_TW;
 constexpr int SW_TWP = SW_TW + 1;  // tile pitch (odd: a warp reading one column over 32 rows touches 32 banks)
 constexpr int SW_SPIN_LIMIT = 1 << 22;
 
@@ -249,8 +249,8 @@ struct VSweep {
 	uint2* xchg; unsigned tag_base; int* claim; int* fault;   // xchg: {value bits, tag} pairs, see k_sgm_sweep_t
 	int H, W, D, top, left, nrows, ncols;
 	int sweep;                             // +1: rows top -> bottom, -1: bottom -> top
-	int en[3];                             // path with shift k (0: along the shear, 1: straight, 2: against the shear) is live
-	int rowlive[3], collive[3];            // its lines started by the row-start / the column-start loop are live (Q4)
+	int rowlive[3], collive[3];            // path k (0: along the shear, 1: straight, 2: against the shear): its lines started by
+	                                       // the row-start / the column-start loop are live (Q4)
 	int corner_once;                       // CORRECTED: the corner line is started once (COMPAT: twice, Q4)
 	int accumulate;                        // 0: S = C + contributions, 1: S += contributions
 	int s_lo, s_hi, n_strips;
@@ -268,36 +268,84 @@ __device__ __forceinline__ uint2 ld_relaxed_v2(const uint2* p) {
 	asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
 	return v;
 }
-__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
-	const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
-	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
-}
 __device__ __forceinline__ void cp_async4s(unsigned dst_smem, const void* src) {
 	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_smem), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
+// One path through one pixel, branch-free so that the three paths of a pixel form one block of independent instruction
+// streams: st = previous scores in / new scores out, wsel = 1.f for a line that is walked (0.f otherwise: nothing is added and the
+// state is of no consequence), twice = the corner line of the path along the shear (Q4).
+template<int DN, int MODE, bool POUT, bool TWICE>
+__device__ __forceinline__ void sw_path_bf(const float (&c)[DN], float (&st)[DN], float lo, float hi, float M, float P1, float P2, float Pout,
+										   int kout, float (&acc)[DN], bool walked, bool twice) {
+	const float WORST = sw_worst<MODE>();
+	const bool mfin = isfinite(M);   // no finite previous score at all: actual_cost = c (sgm.h:252, :292)
+	const float farv = MODE == SW_SCORE ? M - P2 : M + P2;
+	float left = lo;
+#pragma unroll
+	for (int m = 0; m < DN; m++) {
+		const float cur = st[m];
+		const float right = m < DN - 1 ? st[m < DN - 1 ? m + 1 : 0] : hi;
+		float a = sw_cell<MODE>(c[m], cur, left, right, M, farv, P1, Pout, POUT && m >= kout);
+		a = mfin ? a : c[m];
+		const float contrib = walked ? a - c[m] : 0.f;
+		acc[m] += contrib;
+		if (TWICE) acc[m] += twice ? contrib : 0.f;
+		left = cur;
+		st[m] = isfinite(a) ? a : WORST;
+	}
+}
+
+// The same for the common pixel: every path walked once, a finite extremum, no Pout term in reach (j + D <= W)
+template<int DN, int MODE>
+__device__ __forceinline__ void sw_path_fast(const float (&c)[DN], float (&st)[DN], float lo, float hi, float M, float P1, float P2, float (&acc)[DN]) {
+	const float WORST = sw_worst<MODE>();
+	const float farv = MODE == SW_SCORE ? M - P2 : M + P2;
+	float left = lo;
+#pragma unroll
+	for (int m = 0; m < DN; m++) {
+		const float cur = st[m];
+		const float right = m < DN - 1 ? st[m < DN - 1 ? m + 1 : 0] : hi;
+		const float a = sw_cell<MODE>(c[m], cur, left, right, M, farv, P1, 0.f, false);
+		acc[m] += a - c[m];
+		left = cur;
+		st[m] = isfinite(a) ? a : WORST;
+	}
+}
 
 // One block walks one strip down (or up) the rows. Per row the strip's slab of the volume, [D][16 columns], is brought into
 // shared memory with coalesced 64-byte runs (asynchronous copies, one row ahead; an L2 prefetch several rows ahead) and read
-// back TRANSPOSED: a warp works on one pixel at a time, lane l holding the DH consecutive disparities l*DH .. l*DH+DH-1 of
-// each of the three paths through it (previous scores in registers; extremum over d = one warp reduction; the neighbours
-// d-1 / d+1 are in registers except at the lane borders: two shuffles). The tile rows are stored permuted ((d % DH)*32 + d / DH)
-// with an odd pitch, so that the transposed reads and writes are free of bank conflicts. The aggregated costs are staged in
-// the tile of the horizontal contributions (read a, write S in place) and leave with the same 64-byte runs.
-// Warp w owns the tile columns 2w and 2w+1. The tile slides one column to the right per row (the shear), so along the shear a
-// path stays in its registers; the straight path moves one column to the left inside the tile, the path against the shear
-// two: three vectors per warp and row go to the warp on the left through shared memory — and from warp 0 to the strip on the
-// left, from the strip on the right to warp 7, through global memory: every float travels as an 8-byte {bits, tag} pair written
-// by one store (tag = launch epoch << 16 | row + 1), so the reader needs no fence and no separate flag: it polls the pairs
-// it needs until their tags are this launch's and this row's.
-template<int DH, int MODE>
-__global__ void __launch_bounds__(SW_NWARP * 32, DH <= 8 ? 2 : 1) k_sgm_sweep_t(const VSweep p) {
+// back TRANSPOSED: warp w works on column w of the tile, lane l holding the DH consecutive disparities l*DH .. l*DH+DH-1 of
+// each of the three paths through the pixel (previous scores in registers; extremum over d = one warp reduction; the
+// neighbours d-1 / d+1 are in registers except at the lane borders: two shuffles). The tile rows are stored permuted
+// ((d % DH)*32 + d / DH) with an odd pitch, so that the transposed reads and writes are free of bank conflicts. The aggregated
+// costs are staged in the tile of the horizontal contributions (read a, write S in place) and leave with the same 64-byte runs.
+// The tile slides one column to the right per row (the shear), so along the shear a path stays in its registers; the straight
+// path is found one column to the right in the previous row, the path against the shear two: after a row each warp leaves those
+// two vectors in shared memory for the warps on its left — warps 0 and 1 also for the strip on the left, through global memory:
+// every float travels as an 8-byte {bits, tag} pair written by one store (tag = launch epoch << 16 | row + 1), so the reader
+// needs no fence and no separate flag: it polls the pairs it needs until their tags are this launch's and this row's. The
+// reader is a 17th warp that does nothing else: it collects what the strip on the right left for the NEXT row while the 16
+// others work on the current one (its trips to L2 are off their critical path) and joins them at the barrier that opens a row.
+// DIRS: bit k = path k is part of the direction set of this sweep.
+constexpr int SW_NIO = 8;          // warps that only move tiles
+
+template<int DH, int MODE, int DIRS>
+__global__ void __launch_bounds__((SW_NWARP + 1 + SW_NIO) * 32, 1) k_sgm_sweep_t(const VSweep p) {
 	constexpr int TW = SW_TW, TWP = SW_TWP, NWARP = SW_NWARP, DR = 32 * DH, TILE = DR * TWP;
+	constexpr bool EN0 = (DIRS & 1) != 0, EN1 = (DIRS & 2) != 0, EN2 = (DIRS & 4) != 0, XCH = EN1 || EN2;
+	constexpr int NCT = NWARP * 32, NIOT = SW_NIO * 32, NALL = NCT + 32 + NIOT;   // computing threads, tile movers, everyone
 	extern __shared__ float smem[];
-	float* Ct = smem;                                   // [2][DR][TWP] costs
-	float* Xt = Ct + 2 * TILE;                          // [2][DR][TWP] horizontal contributions (if any)
-	float* Yt = Xt + (p.A ? 2 * TILE : 0);              // [2][DR][TWP] the volume being added to (second sweep, framed first sweep)
-	float* ex = Yt + (p.accumulate ? 2 * TILE : 0);     // [3][NWARP + 1][DR] vectors handed to the warp on the left (slot NWARP: from the strip on the right)
+	constexpr int NB = DH <= 8 ? 3 : 2;                 // tile buffers per stream: a slab is asked for NB - 1 rows before it is needed
+	float* Ct = smem;                                   // [NB][DR][TWP] costs
+	float* Xt = Ct + NB * TILE;                         // [NB][DR][TWP] horizontal contributions (if any)
+	float* Yt = Xt + (p.A ? NB * TILE : 0);             // [NB][DR][TWP] the volume being added to (second sweep, framed first sweep)
+	float* ex1 = Yt + (p.accumulate ? NB * TILE : 0);    // [NWARP][DR] straight path: previous scores of column w, for column w - 1
+	float* ex2 = ex1 + NWARP * DR;                      // [NWARP][DR] path against the shear: of column w, for column w - 2
+	float* exr = ex2 + NWARP * DR;                      // [2][3][DR] what the strip on the right left (by row parity): straight path of
+	                                                    // its column 0, path against the shear of its columns 0 and 1
 	float* Ot = p.A ? Xt : Yt;                          // the tile the results are staged in
 	__shared__ int s_claim;
 	const float WORST = sw_worst<MODE>();
@@ -305,8 +353,6 @@ __global__ void __launch_bounds__(SW_NWARP * 32, DH <= 8 ? 2 : 1) k_sgm_sweep_t(
 	const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 	const int d0 = lane * DH;
 	const int dn = min(DH, p.D - d0);                   // disparities of this lane that exist
-	const bool xch = p.en[1] || p.en[2];
-	const int fcol = tid & 15, frow = tid >> 4;         // fill / flush role: column of the tile, first of the disparity rows
 	for (;;) {
 		if (tid == 0) s_claim = atomicAdd(p.claim, 1);
 		__syncthreads();
@@ -315,241 +361,316 @@ __global__ void __launch_bounds__(SW_NWARP * 32, DH <= 8 ? 2 : 1) k_sgm_sweep_t(
 		if (claim >= p.n_strips) return;
 		const int s = p.s_hi - claim;   // right to left: whatever this strip waits for has been claimed before
 		const int t_begin = max(0, -s * TW - (TW - 1)), t_end = min(p.nrows, p.ncols - s * TW);
+		for (int u = tid; u < (2 * NWARP + 6) * DR; u += NALL) ex1[u] = WORST;
+		__syncthreads();   // exchange slots initialised
+		auto row_of = [&](int t) { return p.sweep > 0 ? p.top + t : p.top + p.nrows - 1 - t; };
+
+		if (w > NWARP) {
+			// ================= tile movers: slab of row t+1 in (asynchronous copies), results of row t out =================
+			// thread = tile column fcol, disparity rows frow + 16 u. (Row d sits at tile row (d % DH) * 32 + d / DH.)
+			constexpr int FR = NIOT / 16;                   // disparity rows the movers cover at a time (16)
+			const int it = tid - NCT - 32, fcol = it & 15, frow = it >> 4;   // frow 0..FR-1
+			constexpr int NU = DR / FR;
+			auto tile_row = [&](int u) { return (frow % DH) * 32 + frow / DH + u * (FR / DH); };   // (FR is a multiple of DH)
+			const int nu = min(NU, (p.D - frow + FR - 1) / FR);   // disparity rows of this thread that exist
+			const int fcc0 = s * TW + fcol;                 // this thread's column in row t: fcc0 + t
+			const int esz = p.c_u16 ? 2 : 4;
+			const int64_t rs = p.sweep > 0 ? 1 : -1;
+			const int64_t stepC = (rs * p.c0 + 1) * esz, stepA = rs * p.a0 + 1, stepS = rs * p.s0 + 1;
+			const int64_t dC = FR * p.c2 * esz, dA = FR * p.a2, dS = FR * p.s2;
+			// running pointers of the thread's first disparity row at (row t, its column in row t)
+			const int64_t row_b = row_of(t_begin), col_b = p.left + fcc0 + t_begin;
+			const char* gC = static_cast<const char*>(p.C) + (row_b * p.c0 + (int64_t)frow * p.c2 + col_b) * esz;
+			const float* gA = p.A ? p.A + row_b * p.a0 + (int64_t)frow * p.a2 + col_b : nullptr;
+			float* gS = p.S + row_b * p.s0 + (int64_t)frow * p.s2 + col_b;   // (next row to fill from, when accumulating)
+			float* gF = gS;                                                  // (next row to flush to)
+			const unsigned sC = (unsigned)__cvta_generic_to_shared(Ct) + 4u * fcol, sX = (unsigned)__cvta_generic_to_shared(Xt) + 4u * fcol,
+						   sY = (unsigned)__cvta_generic_to_shared(Yt) + 4u * fcol;
+			auto fill = [&](int t, int b) {   // the slab of row t (the pointers stand on it) -> buffer b
+				const int cc = fcc0 + t;
+				if (t < t_end && cc >= 0 && cc < p.ncols) {
+					const unsigned bo = b * (4u * TILE);
+					const char* pc = gC;
+					if (p.c_u16) {   // no 2-byte asynchronous copies: all loads first, then the stores
+						uint16_t v[NU];
+#pragma unroll
+						for (int u = 0; u < NU; u++, pc += dC) v[u] = u < nu ? __ldg(reinterpret_cast<const uint16_t*>(pc)) : (uint16_t)0;
+#pragma unroll
+						for (int u = 0; u < NU; u++) if (u < nu) Ct[b * TILE + tile_row(u) * TWP + fcol] = (float)v[u];
+					} else if (nu == NU) {
+#pragma unroll
+						for (int u = 0; u < NU; u++, pc += dC) cp_async4s(sC + bo + 4u * (tile_row(u) * TWP), pc);
+					} else {
+#pragma unroll
+						for (int u = 0; u < NU; u++, pc += dC) if (u < nu) cp_async4s(sC + bo + 4u * (tile_row(u) * TWP), pc);
+					}
+					if (p.A) {
+						const float* pa = gA;
+						if (nu == NU) {
+#pragma unroll
+							for (int u = 0; u < NU; u++, pa += dA) cp_async4s(sX + bo + 4u * (tile_row(u) * TWP), pa);
+						} else {
+#pragma unroll
+							for (int u = 0; u < NU; u++, pa += dA) if (u < nu) cp_async4s(sX + bo + 4u * (tile_row(u) * TWP), pa);
+						}
+					}
+					if (p.accumulate) {
+						const float* ps = gS;
+						if (nu == NU) {
+#pragma unroll
+							for (int u = 0; u < NU; u++, ps += dS) cp_async4s(sY + bo + 4u * (tile_row(u) * TWP), ps);
+						} else {
+#pragma unroll
+							for (int u = 0; u < NU; u++, ps += dS) if (u < nu) cp_async4s(sY + bo + 4u * (tile_row(u) * TWP), ps);
+						}
+					}
+				}
+				asm volatile("cp.async.commit_group;" ::: "memory");
+				gC += stepC; gA += stepA; gS += stepS;   // (gA is only dereferenced when there is an A)
+			};
+			auto flush = [&](int t, int b) {   // results of row t, staged in buffer b -> S
+				const int cc = fcc0 + t;
+				if (t >= t_begin && cc >= 0 && cc < p.ncols) {
+					const float* src = Ot + b * TILE + fcol;
+					float* ps = gF;
+					if (nu == NU) {
+#pragma unroll
+						for (int u = 0; u < NU; u++, ps += dS) *ps = src[tile_row(u) * TWP];
+					} else {
+#pragma unroll
+						for (int u = 0; u < NU; u++, ps += dS) if (u < nu) *ps = src[tile_row(u) * TWP];
+					}
+				}
+				gF += stepS;
+			};
+			constexpr int PD = 6;
+			auto prefetch = [&](int t) {   // the tile movers share the disparity rows of the slab PD rows ahead: first and last sector
+				if (t >= t_end) return;
+				const int64_t r = row_of(t);
+				const int j0 = p.left + min(max(s * TW + t, 0), p.ncols - 1), j1 = p.left + min(max(s * TW + t + TW - 1, 0), p.ncols - 1);
+				for (int d = it; d < p.D; d += NIOT) {
+					if (p.c_u16) {
+						const uint16_t* q = static_cast<const uint16_t*>(p.C) + r * p.c0 + (int64_t)d * p.c2;
+						prefetch_l2(q + j0); prefetch_l2(q + j1);
+					} else {
+						const float* q = static_cast<const float*>(p.C) + r * p.c0 + (int64_t)d * p.c2;
+						prefetch_l2(q + j0); prefetch_l2(q + j1);
+					}
+					if (p.A) { const float* q = p.A + r * p.a0 + (int64_t)d * p.a2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
+					if (p.accumulate) { const float* q = p.S + r * p.s0 + (int64_t)d * p.s2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
+				}
+			};
+			for (int u = NB - 1; u < PD; u++) prefetch(t_begin + u);
+#pragma unroll
+			for (int u = 0; u < NB - 1; u++) fill(t_begin + u, u);
+			int b = 0;   // buffer of row t
+			for (int t = t_begin; t < t_end; t++, b = b == NB - 1 ? 0 : b + 1) {
+				// the slab of row t has landed (the later ones may still be in flight)
+				if (NB == 3) asm volatile("cp.async.wait_group 1;" ::: "memory"); else asm volatile("cp.async.wait_group 0;" ::: "memory");
+				bar_sync(1, NALL);                                      // row t opens (and the results of row t - 1 are staged)
+				if (p.dbg & 4) continue;   // (measurement aid)
+				const int bp = b == 0 ? NB - 1 : b - 1;                 // buffer of row t - 1 = buffer of row t + NB - 1
+				if (t > t_begin && !(p.dbg & 32)) flush(t - 1, bp);
+				if (!(p.dbg & 64)) fill(t + NB - 1, bp);                // into the buffer just flushed
+				if (!(p.dbg & 128)) prefetch(t + PD);
+			}
+			asm volatile("cp.async.wait_all;" ::: "memory");
+			__syncthreads();   // the last row's results are staged
+			flush(t_end - 1, b == 0 ? NB - 1 : b - 1);
+			continue;
+		}
+
 		const bool has_right = s + 1 <= p.s_hi;
 		const int rt_begin = max(0, -(s + 1) * TW - (TW - 1)), rt_end = min(p.nrows, p.ncols - (s + 1) * TW);
 		const uint2* xin = p.xchg + (int64_t)(s + 1 - p.s_lo) * p.nrows * 3 * DR + d0;
 		uint2* xout = p.xchg + (int64_t)(s - p.s_lo) * p.nrows * 3 * DR + d0;
-		auto row_of = [&](int t) { return p.sweep > 0 ? p.top + t : p.top + p.nrows - 1 - t; };
-		// ---- tile traffic
-		constexpr int NU = 2 * DH, SRU = (16 / DH) * TWP;   // disparity rows per thread; tile offset between two of them
-		const int srow0 = ((frow % DH) * 32 + frow / DH) * TWP + fcol;   // (row d = frow + 16 u sits at tile row (d % DH) * 32 + d / DH)
-		const int nu = min(NU, (p.D - frow + 15) / 16);                  // disparity rows of this thread that exist
-		const int fcc0 = s * TW + fcol;                                  // this thread's column in row t: fcc0 + t
-		// running pointers of the thread's first disparity row at (row t, its column in row t): one 64-bit add per row and stream
-		const int64_t row_b = p.sweep > 0 ? p.top + t_begin : p.top + p.nrows - 1 - t_begin;
-		const int64_t rs = p.sweep > 0 ? 1 : -1;
-		const int64_t col_b = p.left + fcc0 + t_begin;
-		const char* gC = static_cast<const char*>(p.C) + (row_b * p.c0 + (int64_t)frow * p.c2 + col_b) * (p.c_u16 ? 2 : 4);
-		const float* gA = p.A ? p.A + row_b * p.a0 + (int64_t)frow * p.a2 + col_b : nullptr;
-		float* gS = p.S + row_b * p.s0 + (int64_t)frow * p.s2 + col_b;
-		const int64_t stepC = (rs * p.c0 + 1) * (p.c_u16 ? 2 : 4), stepA = rs * p.a0 + 1, stepS = rs * p.s0 + 1;
-		const int64_t dC = 16 * p.c2 * (p.c_u16 ? 2 : 4), dA = 16 * p.a2, dS = 16 * p.s2;
-		const unsigned sC = (unsigned)__cvta_generic_to_shared(Ct) + 4u * srow0, sX = (unsigned)__cvta_generic_to_shared(Xt) + 4u * srow0,
-					   sY = (unsigned)__cvta_generic_to_shared(Yt) + 4u * srow0;
-		// slab of the row the pointers stand on (row t) -> buffer t & 1 (asynchronous; u16 costs through registers)
-		auto fill = [&](int t, const char* pc, const float* pa, const float* ps) {
-			if (t >= t_end) return;
-			const int cc = fcc0 + t;
-			if (cc < 0 || cc >= p.ncols) return;
-			const unsigned bo = (t & 1) * (4u * TILE);
-			if (p.c_u16) {   // no 2-byte asynchronous copies: all loads first, then the stores
-				uint16_t v[NU];
-#pragma unroll
-				for (int u = 0; u < NU; u++, pc += dC) v[u] = u < nu ? __ldg(reinterpret_cast<const uint16_t*>(pc)) : (uint16_t)0;
-#pragma unroll
-				for (int u = 0; u < NU; u++) if (u < nu) Ct[(t & 1) * TILE + srow0 + u * SRU] = (float)v[u];
-			} else {
-#pragma unroll
-				for (int u = 0; u < NU; u++, pc += dC) if (u < nu) cp_async4s(sC + bo + 4u * (u * SRU), pc);
-			}
-			if (p.A) {
-#pragma unroll
-				for (int u = 0; u < NU; u++, pa += dA) if (u < nu) cp_async4s(sX + bo + 4u * (u * SRU), pa);
-			}
-			if (p.accumulate) {
-#pragma unroll
-				for (int u = 0; u < NU; u++, ps += dS) if (u < nu) cp_async4s(sY + bo + 4u * (u * SRU), ps);
-			}
-		};
-		auto flush = [&](int t, float* ps) {   // staged results of row t -> S (ps stands on row t)
-			const int cc = fcc0 + t;
-			if (cc < 0 || cc >= p.ncols) return;
-			const float* src = Ot + (t & 1) * TILE + srow0;
-#pragma unroll
-			for (int u = 0; u < NU; u++, ps += dS) if (u < nu) *ps = src[u * SRU];
-		};
-		constexpr int PD = 5;
-		auto prefetch = [&](int t) {   // thread = one disparity row of the slab PD rows ahead: its first and last sector
-			if (t >= t_end || tid >= p.D) return;
-			const int64_t r = row_of(t);
-			const int j0 = p.left + min(max(s * TW + t, 0), p.ncols - 1), j1 = p.left + min(max(s * TW + t + TW - 1, 0), p.ncols - 1);
-			if (p.c_u16) {
-				const uint16_t* q = static_cast<const uint16_t*>(p.C) + r * p.c0 + (int64_t)tid * p.c2;
-				prefetch_l2(q + j0); prefetch_l2(q + j1);
-			} else {
-				const float* q = static_cast<const float*>(p.C) + r * p.c0 + (int64_t)tid * p.c2;
-				prefetch_l2(q + j0); prefetch_l2(q + j1);
-			}
-			if (p.A) { const float* q = p.A + r * p.a0 + (int64_t)tid * p.a2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
-			if (p.accumulate) { const float* q = p.S + r * p.s0 + (int64_t)tid * p.s2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
-		};
-		// ---- state: previous scores of the three paths through the warp's two columns, and the vectors coming in from the right
-		float st[3][2][DH];
-#pragma unroll
-		for (int k = 0; k < 3; k++) {
-#pragma unroll
-			for (int m = 0; m < DH; m++) { st[k][0][m] = WORST; st[k][1][m] = WORST; }
-		}
-		for (int u = tid; u < 3 * (NWARP + 1) * DR; u += NWARP * 32) ex[u] = WORST;
-		float* const exr = ex + (w + 1) * DR + lane;   // what the warp (or strip) on the right handed over: exr[(k * (NWARP + 1)) * DR + m * 32]
-		// what the strip on the right published for row t - 1 (warp 7 only): slot 0 = straight path of its first column,
-		// slots 1, 2 = path against the shear of its first and second column
-		bool pending = false;
-		// warp 7: the vectors of the strip on the right for row t go to exchange slot NWARP. block = false: only if they are
-		// already there (asked at the end of the previous row: the wait, if any, is left to the start of the row that needs them)
-		auto fetch_right = [&](int t, bool block) {
-			pending = false;
-			const bool need = xch && has_right && t >= 1 && t - 1 >= rt_begin && t - 1 < rt_end && t < t_end;
-			float* dstx = ex + NWARP * DR + lane;
-			if (!need) {
-#pragma unroll
-				for (int k = 0; k < 3; k++)
-#pragma unroll
-					for (int m = 0; m < DH; m++) dstx[(k * (NWARP + 1)) * DR + m * 32] = WORST;
-				return;
-			}
-			const uint2* src = xin + (int64_t)(t - 1) * 3 * DR;
-			const unsigned tag = p.tag_base | (unsigned)t;   // what the neighbour wrote for its row t - 1
-			for (int spins = 0;; spins++) {
-				bool ok = true;
-				float v3[3][DH];
-#pragma unroll
-				for (int k = 0; k < 3; k++) {
-					if (DH == 1) {
-						const uint2 v = ld_relaxed_v2(src + k * DR);
-						ok = ok && v.y == tag;
-						v3[k][0] = __uint_as_float(v.x);
-					} else {
-#pragma unroll
-						for (int m = 0; m < DH; m += 2) {
-							const uint4 v = ld_relaxed_v4(src + k * DR + m);
-							ok = ok && v.y == tag && v.w == tag;
-							v3[k][m] = __uint_as_float(v.x);
-							v3[k][m + 1 < DH ? m + 1 : 0] = __uint_as_float(v.z);
-						}
-					}
-				}
-				if (__all_sync(0xffffffffu, ok) || (p.dbg & 2)) {
+		if (w == NWARP) {
+			// ================= the collecting warp: what the strip on the right left for row t (its row t - 1) -> exr[t & 1] =========
+			// one row ahead of the computing warps; joins them at the barrier that opens the row
+			for (int t = t_begin; t < t_end; t++) {
+				const bool need = XCH && has_right && t >= 1 && t - 1 >= rt_begin && t - 1 < rt_end && !(p.dbg & 8);
+				float* dx = exr + (t & 1) * 3 * DR + lane;
+				if (!need) {
 #pragma unroll
 					for (int k = 0; k < 3; k++)
 #pragma unroll
-						for (int m = 0; m < DH; m++) dstx[(k * (NWARP + 1)) * DR + m * 32] = v3[k][m];
-					return;
+						for (int m = 0; m < DH; m++) dx[k * DR + m * 32] = WORST;
+				} else {
+					const uint2* src = xin + (int64_t)(t - 1) * 3 * DR;
+					const unsigned tag = p.tag_base | (unsigned)t;   // what the neighbour wrote for its row t - 1
+					for (int spins = 0;; spins++) {
+						bool ok = true;
+						float v3[3][DH];
+#pragma unroll
+						for (int k = 0; k < 3; k++) {
+							if (!(k == 0 ? EN1 : EN2)) {   // never published
+#pragma unroll
+								for (int m = 0; m < DH; m++) v3[k][m] = WORST;
+								continue;
+							}
+							if (DH == 1) {
+								const uint2 v = ld_relaxed_v2(src + k * DR);
+								ok = ok && v.y == tag;
+								v3[k][0] = __uint_as_float(v.x);
+							} else {
+#pragma unroll
+								for (int m = 0; m < DH; m += 2) {
+									const uint4 v = ld_relaxed_v4(src + k * DR + m);
+									ok = ok && v.y == tag && v.w == tag;
+									v3[k][m] = __uint_as_float(v.x);
+									v3[k][m + 1 < DH ? m + 1 : 0] = __uint_as_float(v.z);
+								}
+							}
+						}
+						const bool all_ok = __all_sync(0xffffffffu, ok) || (p.dbg & 2);
+						if (!all_ok && spins > SW_SPIN_LIMIT) *p.fault = 1;   // raise the fault flag instead of hanging
+						if (all_ok || spins > SW_SPIN_LIMIT) {
+#pragma unroll
+							for (int k = 0; k < 3; k++)
+#pragma unroll
+								for (int m = 0; m < DH; m++) dx[k * DR + m * 32] = v3[k][m];
+							break;
+						}
+						__nanosleep(100);
+					}
 				}
-				if (!block) { pending = true; return; }
-				if (spins > SW_SPIN_LIMIT) { *p.fault = 1; return; }   // raise the fault flag instead of hanging
-				__nanosleep(100);
+				bar_sync(1, NALL);
+			}
+			__syncthreads();
+			continue;
+		}
+
+		// ================= computing warps: warp w = column w of the tile ============================================================
+		auto publish = [&](int t, int slot, const float (&v)[DH]) {   // one vector for the strip on the left
+			uint2* dst = xout + ((int64_t)t * 3 + slot) * DR;
+			const unsigned tag = p.tag_base | (unsigned)(t + 1);
+			if (DH == 1) __stcg(dst, make_uint2(__float_as_uint(v[0]), tag));
+			else {
+#pragma unroll
+				for (int m = 0; m < DH; m += 2)
+					__stcg(reinterpret_cast<uint4*>(dst + m), make_uint4(__float_as_uint(v[m]), tag, __float_as_uint(v[m + 1 < DH ? m + 1 : 0]), tag));
 			}
 		};
-		for (int u = 0; u < PD; u++) prefetch(t_begin + u);
-		fill(t_begin, gC, gA, gS);
-		if (w == NWARP - 1) fetch_right(t_begin, true);
-		for (int t = t_begin; t < t_end; t++) {
-			cp_async_wait_all();
-			__syncthreads();   // the slab of row t is in place; everyone is done with the previous row's tiles and exchange vectors
-			float* const gS_now = gS;
-			gC += stepC; gA += stepA; gS += stepS;   // (gA is only dereferenced when there is an A)
-			fill(t + 1, gC, gA, gS);
-			prefetch(t + PD);
-			const int tb = (t & 1) * TILE;
-			if (w == NWARP - 1 && pending) { fetch_right(t, true); __syncwarp(); }
+		float st[3][DH];   // previous scores of the three paths through the warp's column
 #pragma unroll
-			for (int ci = 0; ci < 2; ci++) {
-				const int l = 2 * w + ci;
-				const int cc = s * TW + t + l;   // column inside the margin rectangle
-				if (cc < 0 || cc >= p.ncols) continue;   // (warp-uniform)
+		for (int k = 0; k < 3; k++)
+#pragma unroll
+			for (int m = 0; m < DH; m++) st[k][m] = WORST;
+		// the line weight of the path along the shear is the same for the whole strip and column (Q4): row starts where the column
+		// offset is <= 0, column starts where it is >= 0 (both for the corner line)
+		const int sx = s * TW + w;
+		int wt0 = ((sx <= 0 && p.rowlive[0]) ? 1 : 0) + ((sx >= 0 && p.collive[0]) ? 1 : 0);
+		if (wt0 == 2 && p.corner_once) wt0 = 1;
+		// where the vectors from the right are found: the next warps' slots, or (last warps) what the collecting warp brought
+		const float* in1 = (w + 1 < NWARP ? ex1 + (w + 1) * DR : exr) + lane;
+		const float* in2 = (w + 2 < NWARP ? ex2 + (w + 2) * DR : exr + (1 + (w + 2 - NWARP)) * DR) + lane;
+		const int par1 = w + 1 < NWARP ? 0 : 3 * DR, par2 = w + 2 < NWARP ? 0 : 3 * DR;   // offset of the odd rows' buffer
+		int bcur = 0;   // tile buffer of row t
+		for (int t = t_begin; t < t_end; t++, bcur = bcur == NB - 1 ? 0 : bcur + 1) {
+			bar_sync(1, NALL);   // the slab of row t and the vectors from the right are in place; everyone is done with row t - 1
+			const int tb = bcur * TILE + lane * TWP + w;
+			const int cc = sx + t;   // column inside the margin rectangle
+			if (cc >= 0 && cc < p.ncols) {   // (warp-uniform)
 				const int j = p.left + cc;
 				float c[DH], acc[DH];
 #pragma unroll
-				for (int m = 0; m < DH; m++) c[m] = m < dn ? Ct[tb + (m * 32 + lane) * TWP + l] : nanv;
+				for (int m = 0; m < DH; m++) c[m] = m < dn ? Ct[tb + m * 32 * TWP] : nanv;
 				if (p.accumulate) {
 #pragma unroll
-					for (int m = 0; m < DH; m++) acc[m] = Yt[tb + (m * 32 + lane) * TWP + l];
+					for (int m = 0; m < DH; m++) acc[m] = Yt[tb + m * 32 * TWP];
 				} else {
 #pragma unroll
 					for (int m = 0; m < DH; m++) acc[m] = c[m];   // sgm.h:371-377
 				}
-				// the reference's order of additions: Up2Down, Left2Right, UpLeft2DownRight, UpRight2DownLeft (sgm.h:379-388)
-				const int order[3] = {1, 0, 2};
+				// previous scores: where each line was one row ago
+				if (EN1) {
+					const float* q = in1 + (t & 1) * par1;
 #pragma unroll
-				for (int oi = 0; oi < 3; oi++) {
-					const int k = order[oi];
-					if (p.en[k]) {
-						// line weight (Q4): how many times the reference walks the line through this pixel on this path
-						const int sh = 1 - k;
-						const int kr = sh > 0 ? cc : (sh < 0 ? p.ncols - 1 - cc : INT_MAX), kc = t;
-						int wt = ((kr <= kc && p.rowlive[k]) ? 1 : 0) + ((kc <= kr && p.collive[k]) ? 1 : 0);
-						if (wt == 2 && p.corner_once) wt = 1;
-						// previous scores: where the line was one row ago
-						float in[DH];
-						if (k == 0) {
+					for (int m = 0; m < DH; m++) st[1][m] = q[m * 32];
+				}
+				if (EN2) {
+					const float* q = in2 + (t & 1) * par2;
 #pragma unroll
-							for (int m = 0; m < DH; m++) in[m] = st[0][ci][m];
-						} else if (k == 1) {
+					for (int m = 0; m < DH; m++) st[2][m] = q[m * 32];
+				}
+				// a path whose previous pixel lies outside the margin rectangle starts here: previous_cost = 0 (sgm.h:206-208)
+				if (t == 0 || cc == 0 || cc == p.ncols - 1) {   // (rare)
+					const bool fresh[3] = {t == 0 || cc == 0, t == 0, t == 0 || cc == p.ncols - 1};
 #pragma unroll
-							for (int m = 0; m < DH; m++) in[m] = ci == 0 ? st[1][1][m] : exr[m * 32];
-						} else {
+					for (int k = 0; k < 3; k++) {
+						if (!((DIRS >> k) & 1) || !fresh[k]) continue;
 #pragma unroll
-							for (int m = 0; m < DH; m++) in[m] = exr[((1 + ci) * (NWARP + 1)) * DR + m * 32];
-						}
-						// a path whose previous pixel lies outside the margin rectangle starts here: previous_cost = 0 (sgm.h:206-208)
-						const bool fresh = t == 0 || (k == 0 && cc == 0) || (k == 2 && cc == p.ncols - 1);
-						if (fresh) {
-#pragma unroll
-							for (int m = 0; m < DH; m++) in[m] = m < dn ? 0.f : WORST;
-						}
-						if (wt) {   // a line that is not walked never is: its state does not matter
-							float mx = WORST;
-#pragma unroll
-							for (int m = 0; m < DH; m++) mx = sw_better<MODE>(mx, in[m]);
-#pragma unroll
-							for (int o = 16; o > 0; o >>= 1) mx = sw_better<MODE>(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-							float lo = __shfl_up_sync(0xffffffffu, in[DH - 1], 1), hi = __shfl_down_sync(0xffffffffu, in[0], 1);
-							if (lane == 0) lo = WORST;
-							if (lane == 31) hi = WORST;
-							if (j + p.D <= p.W) sw_path<DH, MODE, false, true>(c, in, lo, hi, mx, p.P1, p.P2, p.Pout, 0, acc, k == 0 && wt == 2);
-							else sw_path<DH, MODE, true, true>(c, in, lo, hi, mx, p.P1, p.P2, p.Pout, p.W - j - d0, acc, k == 0 && wt == 2);
-						}
-#pragma unroll
-						for (int m = 0; m < DH; m++) st[k][ci][m] = in[m];
-					}
-					if (oi == 0 && p.A) {
-#pragma unroll
-						for (int m = 0; m < DH; m++) acc[m] += Xt[tb + (m * 32 + lane) * TWP + l];
+						for (int m = 0; m < DH; m++) st[k][m] = m < dn ? 0.f : WORST;
 					}
 				}
-#pragma unroll
-				for (int m = 0; m < DH; m++) if (m < dn) Ot[tb + (m * 32 + lane) * TWP + l] = acc[m];
-			}
-			// ---- hand-over to the strip on the left / from the strip on the right (global memory)
-			if (w == 0 && xch && s > p.s_lo) {
-				uint2* dst = xout + (int64_t)t * 3 * DR;
-				const unsigned tag = p.tag_base | (unsigned)(t + 1);
-				const float* src[3] = {st[1][0], st[2][0], st[2][1]};
+				// per path: extremum over d (the three reductions run side by side), neighbours across the lane borders
+				float M[3], lo[3], hi[3];
 #pragma unroll
 				for (int k = 0; k < 3; k++) {
-					if (DH == 1) __stcg(dst + k * DR, make_uint2(__float_as_uint(src[k][0]), tag));
-					else {
+					M[k] = WORST;
+					if (!((DIRS >> k) & 1)) continue;
 #pragma unroll
-						for (int m = 0; m < DH; m += 2)
-							__stcg(reinterpret_cast<uint4*>(dst + k * DR + m),
-								   make_uint4(__float_as_uint(src[k][m]), tag, __float_as_uint(src[k][m + 1 < DH ? m + 1 : 0]), tag));
-					}
+					for (int m = 0; m < DH; m++) M[k] = sw_better<MODE>(M[k], st[k][m]);
 				}
+#pragma unroll
+				for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+					for (int k = 0; k < 3; k++)
+						if ((DIRS >> k) & 1) M[k] = sw_better<MODE>(M[k], __shfl_xor_sync(0xffffffffu, M[k], o));
+				}
+#pragma unroll
+				for (int k = 0; k < 3; k++) {
+					if (!((DIRS >> k) & 1)) continue;
+					lo[k] = __shfl_up_sync(0xffffffffu, st[k][DH - 1], 1);
+					hi[k] = __shfl_down_sync(0xffffffffu, st[k][0], 1);
+					if (lane == 0) lo[k] = WORST;
+					if (lane == 31) hi[k] = WORST;
+				}
+				// line weights (Q4): how many times the reference walks the line through this pixel on each path
+				const int kr2 = p.ncols - 1 - cc;
+				int wt2 = ((kr2 <= t && p.rowlive[2]) ? 1 : 0) + ((t <= kr2 && p.collive[2]) ? 1 : 0);
+				if (wt2 == 2 && p.corner_once) wt2 = 1;
+				const bool walked[3] = {wt0 > 0, p.collive[1] != 0, wt2 > 0};
+				const int kout = p.W - j - d0;   // j + d >= W  <=>  m >= kout
+				bool plain = j + p.D <= p.W && wt0 != 2;
+#pragma unroll
+				for (int k = 0; k < 3; k++)
+					if ((DIRS >> k) & 1) plain = plain && walked[k] && isfinite(M[k]);
+				// the reference's order of additions: Up2Down, Left2Right, UpLeft2DownRight, UpRight2DownLeft (sgm.h:379-388)
+				if (plain) {   // (warp-uniform)
+					if (EN1) sw_path_fast<DH, MODE>(c, st[1], lo[1], hi[1], M[1], p.P1, p.P2, acc);
+					if (p.A) {
+#pragma unroll
+						for (int m = 0; m < DH; m++) acc[m] += Xt[tb + m * 32 * TWP];
+					}
+					if (EN0) sw_path_fast<DH, MODE>(c, st[0], lo[0], hi[0], M[0], p.P1, p.P2, acc);
+					if (EN2) sw_path_fast<DH, MODE>(c, st[2], lo[2], hi[2], M[2], p.P1, p.P2, acc);
+				} else {
+					if (EN1) sw_path_bf<DH, MODE, true, false>(c, st[1], lo[1], hi[1], M[1], p.P1, p.P2, p.Pout, kout, acc, walked[1], false);
+					if (p.A) {
+#pragma unroll
+						for (int m = 0; m < DH; m++) acc[m] += Xt[tb + m * 32 * TWP];
+					}
+					if (EN0) sw_path_bf<DH, MODE, true, true>(c, st[0], lo[0], hi[0], M[0], p.P1, p.P2, p.Pout, kout, acc, walked[0], wt0 == 2);
+					if (EN2) sw_path_bf<DH, MODE, true, false>(c, st[2], lo[2], hi[2], M[2], p.P1, p.P2, p.Pout, kout, acc, walked[2], false);
+				}
+#pragma unroll
+				for (int m = 0; m < DH; m++) if (m < dn) Ot[tb + m * 32 * TWP] = acc[m];
 			}
-			if (w == NWARP - 1) fetch_right(t + 1, false);
-			__syncthreads();   // results of row t staged; everyone has read this row's exchange vectors
-			if (w > 0) {   // vectors for the warp on the left (next row)
+			// hand-over to the strip on the left (global memory)
+			if (XCH && s > p.s_lo && !(p.dbg & 16)) {
+				if (w == 0) { if (EN1) publish(t, 0, st[1]); if (EN2) publish(t, 1, st[2]); }
+				if (w == 1 && EN2) publish(t, 2, st[2]);
+			}
+			bar_sync(2, NCT);   // everyone has read this row's exchange vectors
+			if (XCH) {   // vectors for the warps on the left (next row)
 #pragma unroll
 				for (int m = 0; m < DH; m++) {
-					ex[(0 * (NWARP + 1) + w) * DR + m * 32 + lane] = st[1][0][m];
-					ex[(1 * (NWARP + 1) + w) * DR + m * 32 + lane] = st[2][0][m];
-					ex[(2 * (NWARP + 1) + w) * DR + m * 32 + lane] = st[2][1][m];
+					if (EN1) ex1[w * DR + m * 32 + lane] = st[1][m];
+					if (EN2) ex2[w * DR + m * 32 + lane] = st[2][m];
 				}
 			}
-			flush(t, gS_now);
 		}
-		cp_async_wait_all();
 		__syncthreads();
 	}
 }
@@ -576,18 +697,18 @@ static int32_t launch_h(stevi_ctx* c, const HSweep& p, bool vec) {
 
 static size_t sweep_smem(int dh, bool has_a, bool accumulate) {
 	const size_t tile = (size_t)32 * dh * SW_TWP;
-	return (2 * tile * (1 + (has_a ? 1 : 0) + (accumulate ? 1 : 0)) + (size_t)3 * (SW_NWARP + 1) * 32 * dh) * sizeof(float);
+	return ((dh <= 8 ? 3 : 2) * tile * (1 + (has_a ? 1 : 0) + (accumulate ? 1 : 0)) + (size_t)(2 * SW_NWARP + 6) * 32 * dh) * sizeof(float);
 }
 
-template<int MODE>
+template<int MODE, int DIRS>
 static int32_t launch_v(stevi_ctx* c, const VSweep& p) {
 	const int dh = p.D <= 32 ? 1 : p.D <= 64 ? 2 : p.D <= 128 ? 4 : p.D <= 256 ? 8 : 16;
 	const size_t smem = sweep_smem(dh, p.A != nullptr, p.accumulate != 0);
-	const int per_sm = std::max(1, std::min(dh <= 8 ? 2 : 1, (int)((220u << 10) / smem)));
-	dim3 grid(std::min(p.n_strips, c->sm_count * per_sm));
+	if (smem > (227u << 10)) return fail(c, STEVI_E_UNSUPPORTED, "sgm: the sweep tiles do not fit in shared memory");
+	dim3 grid(std::min(p.n_strips, c->sm_count));
 #define STEVI_T(DH) do { \
-	STEVI_CUDA(c, cudaFuncSetAttribute((k_sgm_sweep_t<DH, MODE>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-	STEVI_LAUNCH(c, (k_sgm_sweep_t<DH, MODE>), grid, SW_NWARP * 32, smem, p); } while (0)
+	STEVI_CUDA(c, cudaFuncSetAttribute((k_sgm_sweep_t<DH, MODE, DIRS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+	STEVI_LAUNCH(c, (k_sgm_sweep_t<DH, MODE, DIRS>), grid, (SW_NWARP + 1 + SW_NIO) * 32, smem, p); } while (0)
 	switch (dh) {
 	case 1: STEVI_T(1); break;
 	case 2: STEVI_T(2); break;
@@ -597,6 +718,16 @@ static int32_t launch_v(stevi_ctx* c, const VSweep& p) {
 	}
 #undef STEVI_T
 	return STEVI_OK;
+}
+
+template<int MODE>
+static int32_t launch_v_dirs(stevi_ctx* c, const VSweep& p, int dirs) {
+	switch (dirs) {
+	case 7: return launch_v<MODE, 7>(c, p);
+	case 2: return launch_v<MODE, 2>(c, p);
+	case 1: return launch_v<MODE, 1>(c, p);
+	default: return fail(c, STEVI_E_UNSUPPORTED, "sgm: unexpected direction set of a sweep");
+	}
 }
 
 bool sgm_sweep_capable(const View& cv, int ndir, int strategy, float P1, float P2, int semantics, const View& out) {
@@ -673,21 +804,21 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 		v.A = pass == 0 ? A : nullptr;
 		v.accumulate = (pass == 1 || framed) ? 1 : 0;
 		v.claim = claims + pass;
-		bool any = false, any_col = false;
+		bool any_col = false;
+		int dirs = 0;
 		for (int k = 0; k < 3; k++) {
 			const int sh = 1 - k;
 			const bool in_set = ndir == 8 || sh == 0;
 			// sgm.h:162-184 with :331,:345: ZeroPos starts are live; EndPos starts (negative steps) only with the corrected rule
 			v.rowlive[k] = in_set && sh != 0 && (sh > 0 || corrected);
 			v.collive[k] = in_set && (v.sweep > 0 || corrected);
-			v.en[k] = v.rowlive[k] || v.collive[k];
-			any |= v.en[k] != 0;
+			if (v.rowlive[k] || v.collive[k]) dirs |= 1 << k;
 			any_col |= v.collive[k] != 0;
 		}
-		if (!any && !(pass == 0)) continue;
+		if (!dirs) continue;
 		// strips that hold live pixels: lines started by the column loop reach everywhere, lines started on the left column
 		// (the only row starts of a sweep without live column starts) stay at or left of the diagonal through the corner
-		v.s_hi = (any_col || pass == 0) ? s_all : 0;
+		v.s_hi = any_col ? s_all : 0;
 		v.n_strips = v.s_hi - v.s_lo + 1;
 		// a tag no earlier launch on this buffer has used (zeroed buffer = tag 0 = never valid)
 		if (c->sgm_epoch == 0 || c->sgm_epoch >= 0xffffu) {
@@ -695,9 +826,9 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 			c->sgm_epoch = 0;
 		}
 		v.tag_base = (unsigned)(++c->sgm_epoch) << 16;
-		if (mode == SW_SCORE) STEVI_TRY(launch_v<SW_SCORE>(c, v));
-		else if (mode == SW_COST) STEVI_TRY(launch_v<SW_COST>(c, v));
-		else STEVI_TRY(launch_v<SW_COST_COMPAT>(c, v));
+		if (mode == SW_SCORE) STEVI_TRY(launch_v_dirs<SW_SCORE>(c, v, dirs));
+		else if (mode == SW_COST) STEVI_TRY(launch_v_dirs<SW_COST>(c, v, dirs));
+		else STEVI_TRY(launch_v_dirs<SW_COST_COMPAT>(c, v, dirs));
 	}
 	return STEVI_OK;
 }
