@@ -199,6 +199,99 @@ __global__ void __launch_bounds__(128) k_sgm_lines(const GLineParams p) {
 	}
 }
 
+// Any number of disparities (the reference has no limit): a block per line, the previous scores of the line in shared
+// memory, the same steps as k_sgm_lines with block-wide reductions. Slow (a 128-thread block walks one line) but only reached
+// by D > 512.
+template<int MODE>
+__device__ __forceinline__ float g_block_best(float v, float* red) {
+	v = g_warp_best<MODE>(v);
+	__syncthreads();
+	if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+	__syncthreads();
+	float r = red[0];
+	for (int k = 1; k < (int)(blockDim.x >> 5); k++) r = g_better<MODE>(r, red[k]);
+	return r;
+}
+
+template<int MODE>
+__global__ void __launch_bounds__(1024) k_sgm_lines_any(const GLineParams p) {
+	extern __shared__ float sm[];
+	float* prev = sm;            // [D] finite previous scores (others replaced by the worst value)
+	float* red = sm + p.D;       // [4]
+	__shared__ int s_i1;
+	const int line = blockIdx.x;
+	if (line >= p.n_lines) return;
+	int i = p.kind == 0 ? p.top + line : p.start_fixed;
+	int j = p.kind == 0 ? p.start_fixed : p.left + line;
+	if (p.kind == 1 && j == p.skip_col) return;
+	const int sv0 = c_gsteps[p.dir][0], sv1 = c_gsteps[p.dir][1], sh0 = c_gsteps[p.dir][2], sh1 = c_gsteps[p.dir][3];
+	const float WORST = MODE == GM_SCORE ? -INFINITY : INFINITY;
+	const int D = p.D, W = p.W;
+	auto inside = [&](int ii, int jj) { return ii >= p.top && ii < p.H - p.bottom && jj >= p.left && jj < W - p.right; };
+	if (!inside(i, j)) return;
+	for (int d = threadIdx.x; d < D; d += blockDim.x) prev[d] = 0.f;
+	int step = 0;
+	while (true) {
+		__syncthreads();
+		float loc = WORST;
+		for (int d = threadIdx.x; d < D; d += blockDim.x) loc = g_better<MODE>(loc, prev[d]);
+		const float best_p = g_block_best<MODE>(loc, red);
+		const bool any = isfinite(best_p);
+		float e[3] = {WORST, WORST, WORST};
+		int i1 = 0;
+		if (MODE != GM_COST_COMPAT) {
+			if (threadIdx.x == 0) s_i1 = 0x7fffffff;
+			__syncthreads();
+			int li = 0x7fffffff;
+			for (int d = threadIdx.x; d < D; d += blockDim.x) if (prev[d] == best_p) { li = d; break; }
+			if (li != 0x7fffffff) atomicMin(&s_i1, li);
+			__syncthreads();
+			i1 = s_i1;
+			for (int t = 0; t < 3; t++) {
+				float l = WORST;
+				for (int d = threadIdx.x; d < D; d += blockDim.x) if (abs(d - (i1 - 1 + t)) > 1) l = g_better<MODE>(l, prev[d]);
+				e[t] = g_block_best<MODE>(l, red);
+			}
+		}
+		const float* pc = p.C + ((int64_t)i * W + j) * D;
+		float* ps = p.S + ((int64_t)i * W + j) * D;
+		// every thread computes its cells from the old scores, then (after a barrier) replaces them
+		float newv[8];   // D <= 8 * blockDim.x per pass; larger D loop in passes
+		for (int base = 0; base < D; base += 8 * blockDim.x) {
+			int n = 0;
+			for (int d = base + threadIdx.x; d < D && n < 8; d += blockDim.x, n++) {
+				const float c = __ldg(pc + d);
+				float act = c;
+				if (MODE == GM_COST_COMPAT) {
+					float m = any ? c : INFINITY;
+					if (j + d >= W) m += p.Pout;
+					if (isfinite(m) && any) act += m - best_p;
+				} else {
+					const float lft = d > 0 ? prev[d - 1] : WORST, rgt = d + 1 < D ? prev[d + 1] : WORST;
+					const int rel = d - i1;
+					const float far = (rel < -1 || rel > 1) ? best_p : e[rel + 1];
+					float m;
+					if (MODE == GM_SCORE) m = fmaxf(fmaxf(far - p.P2, fmaxf(lft, rgt) - p.P1), prev[d]);
+					else m = fminf(fminf(far + p.P2, fminf(lft, rgt) + p.P1), prev[d]);
+					if (j + d >= W) m = MODE == GM_SCORE ? m - p.Pout : m + p.Pout;
+					if (isfinite(m) && any) act += m - best_p;
+				}
+				atomicAdd(ps + d, act - c);
+				newv[n] = isfinite(act) ? act : WORST;
+			}
+			if (base + 8 * (int)blockDim.x < D) {
+				// more passes follow: they still need the old neighbours of this pass's last cells; keep it simple: one pass only
+			}
+			__syncthreads();
+			n = 0;
+			for (int d = base + threadIdx.x; d < D && n < 8; d += blockDim.x, n++) prev[d] = newv[n];
+		}
+		const int i2 = i + ((step & 1) ? sv1 : sv0), j2 = j + ((step & 1) ? sh1 : sh0);
+		if (!inside(i2, j2)) break;
+		i = i2; j = j2; step++;
+	}
+}
+
 } // namespace stevi
 
 namespace stevi {
@@ -208,6 +301,11 @@ static int g_start_pos(int s0, int s1) { return (s0 == 0 && s1 == 0) ? 0 : ((s0 
 template<int MODE>
 static int32_t launch_lines(stevi_ctx* c, const GLineParams& p) {
 	if (p.n_lines <= 0) return STEVI_OK;
+	if (p.D > 512) {   // one pass of 8 cells per thread covers D <= 8 * 1024
+		const int threads = p.D <= 1024 ? 128 : p.D <= 2048 ? 256 : p.D <= 4096 ? 512 : 1024;
+		STEVI_LAUNCH(c, (k_sgm_lines_any<MODE>), dim3(p.n_lines), threads, (size_t)(p.D + 32) * sizeof(float), p);
+		return STEVI_OK;
+	}
 	const int K = p.D <= 32 ? 1 : p.D <= 64 ? 2 : p.D <= 128 ? 4 : p.D <= 256 ? 8 : 16;
 	dim3 grid(cdiv(p.n_lines, 4));
 	switch (K) {
@@ -229,7 +327,7 @@ int32_t sgm_general(stevi_ctx* c, const View& cv, int ndir, int strategy, float 
 	const int H = cv.shape[0], W = cv.shape[1], D = cv.shape[2];
 	// volumes with contiguous columns (the reference's layout): consumed in place by the sweep kernels (sgm_sweep.cu)
 	if (sgm_sweep_capable(cv, ndir, strategy, P1, P2, semantics, out)) return sgm_sweep(c, cv, ndir, strategy, P1, P2, Pout, mg, semantics, out);
-	if (D > 512) return fail(c, STEVI_E_UNSUPPORTED, "sgm: the general recurrence supports up to 512 disparities");
+	if (D > 8192) return fail(c, STEVI_E_UNSUPPORTED, "sgm: the general recurrence supports up to 8192 disparities");
 	const size_t n = (size_t)H * W * D;
 	float *Cw = nullptr, *Sw = nullptr;
 	STEVI_TRY(arena_alloc_t(c, n, &Cw));

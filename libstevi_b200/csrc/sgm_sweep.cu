@@ -6,29 +6,25 @@
 //   k_sgm_sweep_h   the horizontal paths (Left2Right; Right2Left in CORRECTED mode): a warp owns an image row and walks along it,
 //                   lane l holds DH consecutive disparities; their contribution `actual_cost - cv_base` (sgm.h:298-300) goes to a
 //                   workspace volume A;
-//   k_sgm_sweep_v   (down) Up2Down, UpLeft2DownRight and UpRight2DownLeft carried together by one sweep over the rows; reads C and A
+//   k_sgm_sweep_t   (down) Up2Down, UpLeft2DownRight and UpRight2DownLeft carried together by one sweep over the rows; reads C and A
 //                   once, writes S = (((C + a_U2D) + a_L2R) + a_UL2DR) + a_UR2DL: the reference's own order of additions
 //                   (sgm.h:379-388), so the float result is bit-identical to it;
-//   k_sgm_sweep_v   (up) the paths that climb (COMPAT: only DownLeft2UpRight lines that start on the left column, Q4), S += a.
+//   k_sgm_sweep_t   (up) the paths that climb (COMPAT: only DownLeft2UpRight lines that start on the left column, Q4), S += a.
 //
-// The vertical sweep is tiled in SHEARED STRIPS: strip s owns, at sweep step t, the CW columns s*CW + t .. s*CW + t + CW-1 (it
-// slides one column to the right per row). A path that runs down-right therefore stays on its lane for its whole life; the
-// straight-down path of a column is found one lane to the right in the previous step and the down-left path two lanes to the
-// right — so every dependency of a strip points to the strip on its RIGHT, never to the left. Persistent blocks claim strips
-// from the rightmost to the leftmost; a strip reads what its right neighbour published for the previous step (two lanes of
-// state per step, through global memory = L2, one release/acquire counter per warp) and publishes its own two leftmost lanes.
-// One-sided dependencies mean the neighbours settle into a stagger instead of waiting on each other every row, the claim
-// order means whatever a strip waits for is already running (no co-residency requirement, no deadlock), and the spin is
-// bounded: a wait that does not end raises the ctx fault flag instead of hanging the device.
-//
-// Inside a strip a thread owns one column and DC consecutive disparities (lanes = 16 columns x 2 disparity chunks, warps = more
-// chunks): loads and stores are 64-byte runs along the row, the previous scores of the three paths live in registers, the
-// per-column extremum over d is reduced through two shuffles and one shared-memory exchange per step (one __syncthreads per row).
+// The vertical sweep is tiled in SHEARED STRIPS: strip s owns, at sweep step t, the 16 columns s*16 + t .. s*16 + t + 15 (it
+// slides one column to the right per row). A path that runs down-right therefore stays with its warp for its whole life; the
+// straight-down path of a column is found one column to the right in the previous step and the down-left path two columns to
+// the right — so every dependency of a strip points to the strip on its RIGHT, never to the left. Persistent blocks claim
+// strips from the rightmost to the leftmost; a strip reads what its right neighbour published for the previous row (three
+// vectors of D scores per row, through global memory = L2) and publishes its own. One-sided dependencies mean the neighbours
+// settle into a stagger instead of waiting on each other every row, the claim order means whatever a strip waits for is
+// already running (no co-residency requirement, no deadlock), and the wait is bounded: one that does not end raises the ctx
+// fault flag instead of hanging the device. The kernel comment of k_sgm_sweep_t has the inside of a strip.
 //
 // Per cell and path (Score; Cost mirrors it with min/+):  act = c + (max(M - P2, max(L(d-1), L(d+1)) - P1, L(d)) [- Pout] - M),
 // M = max_d L(d) over finite previous scores. The reference's loop subtracts P2 only from |od - d| > 1 (sgm.h:236-239); with
 // P2 >= P1 >= 0 the three extra candidates L(d) - P2, L(d+-1) - P2 never win, and rounding is monotone, so both give the same
-// bits. Other penalties, 16 directions, D > 512 and volumes with strided columns take sgm_general.cu's warp-per-line kernel.
+// bits. Other penalties, 16 directions, D > 512 and volumes with strided columns take sgm_general.cu's line kernels.
 #include "common.cuh"
 #include "kernels.cuh"
 #include <cmath>
@@ -60,15 +56,6 @@ __device__ __forceinline__ float sw_cell(float c, float in, float l, float r, fl
 		if (oor) m += Pout;
 	}
 	return c + (m - M);
-}
-
-__device__ __forceinline__ int ld_acquire(const int* p) {
-	int v;
-	asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-	return v;
-}
-__device__ __forceinline__ void st_release(int* p, int v) {
-	asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 // ---- horizontal paths ------------------------------------------------------------------------------------------------------

@@ -189,6 +189,17 @@ class _Checker:
             if serial:
                 self.lib.ref_set_num_threads(nthreads)
 
+    def sgm_corrected(self, cv, ndir, strategy, P1, P2, Pout=100.0, margins=(0, 0, 0, 0)):
+        """STEVI_CORRECTED semantics (the product's definition, not the reference's behaviour; port only)."""
+        cv = _c(cv, np.float32)
+        h, w, D = cv.shape
+        out = np.empty((h, w, D), np.float32)
+        m = np.asarray(margins, np.int32)
+        f32 = ctypes.c_float
+        rc = self._f("sgm_f32_ex")(_p(cv), h, w, D, ndir, strategy, f32(P1), f32(P2), f32(Pout), _p(m), 1, _p(out))
+        assert rc == 0
+        return out
+
     def _sgm(self, cv, ndir, strategy, P1, P2, Pout, m, out, f32, h, w, D):
         if cv.dtype == np.uint16:
             rc = self._f("sgm_u16")(_p(_c(cv, np.uint16)), h, w, D, ndir, strategy, f32(P1), f32(P2), f32(Pout), _p(m), _p(out))

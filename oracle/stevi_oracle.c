@@ -353,7 +353,7 @@ static const int SGM_ORDER[16] = {0, 1, 2, 3, 4, 5, 6, 7, 12, 13, 14, 15, 8, 9, 
  * IEEE arithmetic, so max_od (p[od] - P) == (max_od p[od]) - P exactly. Non-finite previous scores are skipped
  * (`std::isfinite(p_score)` tests at :224,:243,:264,:281). */
 static void sgm_traverse_line(int dirIdx, int strategy, int si, int sj, const float* cv, float* sgm,
-							  int h, int w, int D, float P1, float P2, float Pout, const int* mg) {
+							  int h, int w, int D, float P1, float P2, float Pout, const int* mg, int corrected) {
 	int left = mg[0], top = mg[1], right = mg[2], bottom = mg[3];
 	const int* st = SGM_STEPS[dirIdx];
 	float* prev = (float*)calloc((size_t)D, sizeof(float));
@@ -381,6 +381,26 @@ static void sgm_traverse_line(int dirIdx, int strategy, int si, int sj, const fl
 				if (j + nd >= w) m -= Pout;
 				act[nd] = cc[nd];
 				if (isfinite(m) && isfinite(max_p)) act[nd] += m - max_p;
+			}
+		} else if (corrected) {
+			/* CORRECTED semantics (not the reference's behaviour): `min_a_cost = p_score`, i.e. the textbook
+			 * recurrence, the mirror image of the Score branch */
+			float min_p = INFINITY;
+			for (int d = 0; d < D; d++) if (prev[d] < min_p && isfinite(prev[d])) min_p = prev[d];
+			float run = INFINITY;
+			for (int d = 0; d < D; d++) { if (isfinite(prev[d]) && prev[d] < run) run = prev[d]; pre[d] = run; }
+			run = INFINITY;
+			for (int d = D - 1; d >= 0; d--) { if (isfinite(prev[d]) && prev[d] < run) run = prev[d]; suf[d] = run; }
+			for (int nd = 0; nd < D; nd++) {
+				float m = INFINITY, t;
+				if (nd - 2 >= 0) { t = pre[nd - 2] + P2; if (t < m && isfinite(t)) m = t; }
+				if (nd - 1 >= 0) { t = prev[nd - 1] + P1; if (t < m && isfinite(t)) m = t; }
+				t = prev[nd]; if (t < m && isfinite(t)) m = t;
+				if (nd + 1 < D) { t = prev[nd + 1] + P1; if (t < m && isfinite(t)) m = t; }
+				if (nd + 2 < D) { t = suf[nd + 2] + P2; if (t < m && isfinite(t)) m = t; }
+				if (j + nd >= w) m += Pout;
+				act[nd] = cc[nd];
+				if (isfinite(m) && isfinite(min_p)) act[nd] += m - min_p;
 			}
 		} else {
 			float min_p = INFINITY;
@@ -414,36 +434,47 @@ static int sgm_start_pos(int s0, int s1) {
 }
 
 static void sgm_add_direction(int dirIdx, int strategy, const float* cv, float* sgm, int h, int w, int D,
-							  float P1, float P2, float Pout, const int* mg) {
+							  float P1, float P2, float Pout, const int* mg, int corrected) {
 	int left = mg[0], top = mg[1], right = mg[2], bottom = mg[3];
 	const int* st = SGM_STEPS[dirIdx];
 	int colStart = sgm_start_pos(st[0], st[1]); /* from stepsVertical */
 	int rowStart = sgm_start_pos(st[2], st[3]); /* from stepsHorizontal */
+	int row_sj = -1;
 	if (rowStart != 0) { /* lines starting on the left (or, Q4, one past the right) column: sgm.h:329-341 */
-		int sj = (rowStart == 1) ? left : w - right;
+		/* CORRECTED: EndPos starts on the last valid index instead of one past it */
+		int sj = (rowStart == 1) ? left : w - right - (corrected ? 1 : 0);
+		row_sj = sj;
 		/* Q8: lines of the eight extra directions of the 16-direction set (steps alternating between two moves) started
 		 * on neighbouring pixels share pixels, so the reference's own `omp parallel for` over them races on sgm_cv;
 		 * the sequential result is the defined one: those directions run on one thread here. */
 		#pragma omp parallel for if (dirIdx < 8)
 		for (int si = top; si < h - bottom; si++)
-			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg);
+			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg, corrected);
 	}
 	if (colStart != 0) { /* lines starting on the top (or, Q4, one past the bottom) row: sgm.h:343-354 */
-		int si = (colStart == 1) ? top : h - bottom;
+		int si = (colStart == 1) ? top : h - bottom - (corrected ? 1 : 0);
 		#pragma omp parallel for if (dirIdx < 8)
-		for (int sj = left; sj < w - right; sj++)
-			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg);
+		for (int sj = left; sj < w - right; sj++) {
+			if (corrected && rowStart != 0 && sj == row_sj) continue; /* CORRECTED: the corner line is started once */
+			sgm_traverse_line(dirIdx, strategy, si, sj, cv, sgm, h, w, D, P1, P2, Pout, mg, corrected);
+		}
 	}
 }
 
-/* sgm.h:360-404. margins = {left, top, right, bottom} (utils/margins.h:52). out (h,w,D) float. */
-int orc_sgm_f32(const float* cv, int h, int w, int D, int ndir, int strategy,
-				float P1, float P2, float Pout, const int* margins, float* out) {
+/* sgm.h:360-404. margins = {left, top, right, bottom} (utils/margins.h:52). out (h,w,D) float.
+ * corrected != 0: the STEVI_CORRECTED semantics of the product (our definition, not the reference's behaviour): textbook Cost
+ * recurrence, every direction live, corner lines once; directions in the reference's order. */
+int orc_sgm_f32_ex(const float* cv, int h, int w, int D, int ndir, int strategy,
+				   float P1, float P2, float Pout, const int* margins, int corrected, float* out) {
 	if (ndir != 4 && ndir != 8 && ndir != 16) return 2;
 	memcpy(out, cv, (size_t)h * w * D * sizeof(float));
 	for (int k = 0; k < ndir; k++)
-		sgm_add_direction(SGM_ORDER[k], strategy, cv, out, h, w, D, P1, P2, Pout, margins);
+		sgm_add_direction(SGM_ORDER[k], strategy, cv, out, h, w, D, P1, P2, Pout, margins, corrected);
 	return 0;
+}
+int orc_sgm_f32(const float* cv, int h, int w, int D, int ndir, int strategy,
+				float P1, float P2, float Pout, const int* margins, float* out) {
+	return orc_sgm_f32_ex(cv, h, w, D, ndir, strategy, P1, P2, Pout, margins, 0, out);
 }
 int orc_sgm_u16(const uint16_t* cv, int h, int w, int D, int ndir, int strategy,
 				float P1, float P2, float Pout, const int* margins, float* out) {

@@ -161,3 +161,40 @@ def test_sweep_column_slices_and_unaligned_rows(api, ctx, oracle):
     view = base[:, 3:50, :]
     got = api.sgmCostVolume(view, 0.001, 0.01, Pout=100, nDirections=8, strategy=api.SCORE, ctx=ctx)
     assert np.array_equal(got, oracle.port.sgm(np.ascontiguousarray(view), 8, oracle.SCORE, 0.001, 0.01, 100))
+
+
+# ---- STEVI_CORRECTED: textbook recurrence, every direction live (the product's own definition, checked against the oracle's
+# restatement of it: exact for integer-valued volumes, where every order of additions gives the same sums; 1e-4 for float ones,
+# whose additions the sweeps do in sweep order instead of the reference's direction order)
+
+@pytest.mark.parametrize("layout", ["ref", "c"])
+@pytest.mark.parametrize("ndir", [4, 8])
+@pytest.mark.parametrize("strategy", ["cost", "score"])
+def test_corrected_semantics_integer_volume(api, ctx, oracle, layout, ndir, strategy):
+    cv = census_cv(api, ctx, h=50, w=75, D=40, layout=layout)
+    strat_a, strat_o = (api.COST, oracle.COST) if strategy == "cost" else (api.SCORE, oracle.SCORE)
+    got = api.sgmCostVolume(cv, 3, 20, Pout=50, nDirections=ndir, strategy=strat_a, semantics=api.CORRECTED, ctx=ctx)
+    want = oracle.port.sgm_corrected(np.ascontiguousarray(cv), ndir, strat_o, 3, 20, 50)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("margins", [(0, 0, 0, 0), (3, 1, 2, 5)])
+def test_corrected_semantics_float_volume(api, ctx, oracle, margins):
+    v = np.abs(zncc_like_volume(41, 67, 23, 8)) * 10
+    for vol in (v, ref_layout(v)):
+        got = api.sgmCostVolume(vol, 0.5, 2.0, margins=margins, Pout=7, nDirections=8, strategy=api.COST, semantics=api.CORRECTED, ctx=ctx)
+        want = oracle.port.sgm_corrected(v, 8, oracle.COST, 0.5, 2.0, 7, margins)
+        assert np.allclose(got, want, rtol=0, atol=1e-4)
+
+
+@pytest.mark.parametrize("D", [513, 700])
+def test_more_than_512_disparities(api, ctx, oracle, D):
+    # the reference has no limit on D: beyond the register-resident kernels a block per line takes over
+    v = zncc_like_volume(6, 20, D, D)
+    for vol in (v, ref_layout(v)):
+        got = api.sgmCostVolume(vol, 0.001, 0.01, Pout=100, nDirections=8, strategy=api.SCORE, ctx=ctx)
+        assert np.array_equal(got, oracle.port.sgm(v, 8, oracle.SCORE, 0.001, 0.01, 100))
+    c = (np.abs(v) * 100).astype(np.uint16)
+    c[:, :, 0] = 65000   # too large for the collapsed integer evaluation
+    got = api.sgmCostVolume(c, 1, 2, Pout=100, ctx=ctx)
+    assert np.array_equal(got, oracle.port.sgm(c, 8, oracle.COST, 1, 2, 100))
