@@ -140,6 +140,11 @@ class _Checker:
             else:
                 rc = self._f("census_cost_volume_f32")(_p(_c(left, np.float32)), _p(_c(right, np.float32)),
                                                        h, wl, wr, hr, vr, D, direction, _p(out))
+        elif left.dtype == np.uint8 and mf in (CC, SSD, SAD) and self.has("cost_volume_u8"):
+            # the reference's own uint8 instantiation (compiled reference only)
+            out = np.empty((h, ws, D), np.float32)
+            rc = self._f("cost_volume_u8")(mf, _p(_c(left, np.uint8)), _p(_c(right, np.uint8)),
+                                           h, wl, wr, hr, vr, D, direction, _p(out))
         else:
             out = np.empty((h, ws, D), np.float32)
             rc = self._f("cost_volume_f32")(mf, _p(_c(left, np.float32)), _p(_c(right, np.float32)),

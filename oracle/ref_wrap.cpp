@@ -197,6 +197,18 @@ int ref_cost_volume_f32(int matchfunc, const float* l, const float* r, int h, in
 	}
 }
 
+// the same with uint8 images through the reference's own uint8 instantiation (CC / SSD / SAD: the functions whose feature type
+// for uint8 input is not the fixed-point one, cross_correlations.h:716-720)
+int ref_cost_volume_u8(int matchfunc, const uint8_t* l, const uint8_t* r, int h, int w, int wr,
+					   int hr, int vr, int D, int dir, float* out) {
+	switch (matchingFunctions(matchfunc)) {
+	case matchingFunctions::CC: return cv_dir<matchingFunctions::CC>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::SSD: return cv_dir<matchingFunctions::SSD>(l, r, h, w, wr, hr, vr, D, dir, out);
+	case matchingFunctions::SAD: return cv_dir<matchingFunctions::SAD>(l, r, h, w, wr, hr, vr, D, dir, out);
+	default: return 2;
+	}
+}
+
 // cross_correlations.h:794-822: 2-D search cost volume, float images of equal size. so = {lower0, upper0, lower1, upper1}
 // (searchOffset<2> ctor order, correlation_base.h:299-315). out (h, w, upper0-lower0+1, upper1-lower1+1) C-order.
 int ref_cost_volume_2d_f32(int matchfunc, const float* l, const float* r, int h, int w, int hr, int vr, const int* so, int dir, float* out) {
