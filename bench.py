@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the dense-stereo hot path (BASELINE.json metric: Gdisp/s = W*H*D / s).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c5|c3|c4]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c5|c3|c4|c1] [--pairs P]
 
 One step = one pass of census 9x7 -> Hamming cost volume (u16) -> SGM 8 directions -> WTA -> disparity over one
 synthetic rectified pair (BASELINE.json configs[1]: 1920x1080, D=256; `--workload c5`: 1280x720, D=128).
@@ -13,7 +13,10 @@ synthetic rectified pair (BASELINE.json configs[1]: 1920x1080, D=256; `--workloa
   cpu_baseline / --impl reference  the reference's own CPU code (oracle/_ref, compiled from the unmodified LibStevi
          headers) on the host cores, on a bounded row band of the same workload.
 N > 1 (torchrun): independent pairs are sharded across ranks, no data-path collective (weak scaling).
-Secondary workloads (not the headline line): `--workload c3` = ZNCC 9x9 cost volume + WTA + refinement (configs[2]);
+The default (c2) line also carries `sustained` (>= 2 s of back-to-back pairs, clocks sampled throughout) and `secondary`: the
+other configurations (c1, c3, c4, c5 incl. a streamed batch of distinct pairs, and the general SGM recurrence as a stage) with
+fewer steps each. `--workload c5 --pairs 1024` streams the batch of BASELINE configs[4] and reports pairs/s.
+Secondary workloads on their own: `--workload c3` = ZNCC 9x9 cost volume + WTA + refinement (configs[2]);
 `--workload c4` = the coarse-to-fine driver on one 4096x3072 frame, split in row bands over the ranks and gathered with
 one NCCL all_gather (configs[3], strong scaling).
 """
@@ -38,6 +41,8 @@ WORKLOADS = {
                name="census9x7+SGM8+WTA 1280x720 D=128 u16 costs (BASELINE configs[4], one pair per step per GPU)"),
     "c3": dict(kind="zncc", H=1080, W=1920, D=192, hr=4, vr=4, seed=3, d_max=120,
                name="ZNCC9x9 cost volume + WTA + truncated volume + parabola refinement 1920x1080 D=192 f32 (BASELINE configs[2])"),
+    "c1": dict(kind="zncc", H=480, W=640, D=64, hr=2, vr=2, seed=1, d_max=0,
+               name="ZNCC5x5 cost volume + WTA (+ radius-1 refinement) 640x480 D=64 f32 (BASELINE configs[0], its dense form: SURVEY 3.5)"),
     "c4": dict(kind="hier", H=3072, W=4096, D=512, hr=3, vr=3, seed=4, d_max=0, depth=3, radius=2,
                name="hierarchical ZNCC7x7 depth 3, 4096x3072 D=512 f32, one frame split in row bands over the GPUs (BASELINE configs[3])"),
 }
@@ -124,7 +129,8 @@ def cpu_reference_run(wl, steps, warmup, band_rows=None, budget_s=15.0):
         step()
     dt = (time.perf_counter() - t0) / max(steps, 1)
     cells = band_rows * W * D
-    return {"value": cells / dt / 1e9, "unit": "Gdisp/s", "cores": cores, "kind": kind,
+    return {"value": cells / dt / 1e9, "unit": "Gdisp/s", "cores": cores, "kind": kind, "band_rows": band_rows, "frame_rows": H,
+            "full_frame_s_extrapolated": round(dt * H / band_rows, 1),
             "sample": f"rows {i0}..{i0 + band_rows} of the {W}x{H} pair ({band_rows}x{W}xD{D} cells per step), "
                       f"{steps} step(s), {dt:.2f} s/step"}, dt
 
@@ -170,7 +176,6 @@ def cpu_reference_float(wl, steps, warmup, budget_s=15.0):
             "sample": f"{sample}, {steps} step(s), {dt:.2f} s/step"}, dt
 
 
-E2E_DEPTH = 3
 
 
 def timed_pair_stream(api, torch, call, outs, steps, warmup, device, barrier, flush):
@@ -200,8 +205,10 @@ def timed_pair_stream(api, torch, call, outs, steps, warmup, device, barrier, fl
     return ms
 
 
-def main_float(args, wl, rank, world, local_rank):
-    """c3 (ZNCC + refinement, independent pairs per rank) and c4 (coarse-to-fine on one frame split in row bands)."""
+def main_float(args, wl, rank, world, local_rank, dist=None, steps=None, with_cpu=True):
+    """c1 / c3 (ZNCC [+ refinement], independent pairs per rank) and c4 (coarse-to-fine on one frame split in row bands).
+    Returns the JSON line as a dict on rank 0 (None elsewhere)."""
+    steps = steps or args.steps
     H, W, D = wl["H"], wl["W"], wl["D"]
     cells = H * W * D
     hier = wl["kind"] == "hier"
@@ -213,24 +220,17 @@ def main_float(args, wl, rank, world, local_rank):
         config.update(depth=wl["depth"], upscale_disp_radius=wl["radius"])
     if args.impl == "reference":
         if rank != 0:
-            return 0
+            return None
         base, dt = cpu_reference_float(wl, args.steps, args.warmup, budget_s=120.0)
-        print(json.dumps({"impl": "reference", "metric": metric, "value": base["value"], "unit": "Gdisp/s", "n_gpus": args.gpus,
-                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-                          "scaling": "strong" if hier else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                          "config": config, "cpu_baseline": base, "gpu_launches": 0,
-                          "e2e": {"value": base["value"], "unit": "Gdisp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
-        return 0
+        config["cpu_sample"] = base["sample"]
+        return {"impl": "reference", "metric": metric, "value": base["value"], "unit": "Gdisp/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+                "scaling": "strong" if hier else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": config, "cpu_baseline": base, "gpu_launches": 0,
+                "e2e": {"value": base["value"], "unit": "Gdisp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     import torch
     from libstevi_b200 import api, synth, sharding
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
     warmup = max(args.warmup, 3)
     seed = wl["seed"] + (0 if hier else rank)
     L, R, gt = synth.stereo_pair(H, W, seed, d_bg=24 if hier else 8, d_sq=96 if hier else 32, d_max=wl["d_max"], dtype=np.float32)
@@ -284,7 +284,7 @@ def main_float(args, wl, rank, world, local_rank):
 
         def call_stream(c, out):
             api.localMatchingPipeline(api.ZNCC, nl, nr, wl["hr"], wl["vr"], D, api.PARABOLA, out=out, ctx=c)
-        stream_outs = [nref] + [torch.empty((H, W), dtype=torch.float32).pin_memory().numpy() for _ in range(E2E_DEPTH - 1)]
+        stream_outs = [nref] + [torch.empty((H, W), dtype=torch.float32).pin_memory().numpy() for _ in range(args.inflight - 1)]
         h2d, d2h = 2 * H * W * 4, H * W * 4
         dom_key, dom_bytes = "k_cv_box", cells * 4
 
@@ -313,40 +313,41 @@ def main_float(args, wl, rank, world, local_rank):
     for _ in range(warmup):
         step_device()
     n0 = ctx.launches
-    ms_dev, clocks = timed(step_device, args.steps, ClockSampler(local_rank) if rank == 0 else None)
+    ms_dev, clocks = timed(step_device, steps, ClockSampler(local_rank) if rank == 0 else None)
     launches = ctx.launches - n0
     for _ in range(warmup):
         step_host()
-    ms_host, _ = timed(step_host, args.steps)
+    ms_host, _ = timed(step_host, steps)
     ms_serial, e2e_mode = ms_host, "one pair at a time, the call returns with the result in host memory"
     if not hier:
-        ms_host = timed_pair_stream(api, torch, call_stream, stream_outs, args.steps, warmup, local_rank, barrier, flush)
+        ms_host = timed_pair_stream(api, torch, call_stream, stream_outs, steps, warmup, local_rank, barrier, flush)
         if dist is not None:
             ms_host = sharding.max_over_ranks(ms_host, dist, dev)
-        e2e_mode = f"{E2E_DEPTH} pairs in flight (HostPairStream: one ctx+stream per slot, stevi_ctx_set_deferred_host)"
+        e2e_mode = f"{args.inflight} pairs in flight (HostPairStream: one ctx+stream per slot, stevi_ctx_set_deferred_host)"
     ctx.set_timing(True)
     per_kernel = {}
-    for _ in range(max(3, min(args.steps, 10))):
+    for _ in range(max(3, min(steps, 10))):
         flush.zero_()
         step_device()
         for name, ms in ctx.timing_report():
             per_kernel.setdefault(name.split("<")[0].strip("()"), []).append(ms)
     ctx.set_timing(False)
-    reps = max(3, min(args.steps, 10))
+    reps = max(3, min(steps, 10))
     kern_ms = {k: float(np.sum(v)) / reps for k, v in per_kernel.items()}   # per step, summed over the launches of a step
     torch.cuda.synchronize()
     d = res["disp"].cpu().numpy()
     inner = (slice(H // 3 + 40, 2 * H // 3 - 40), slice(W // 3 + 40, 2 * W // 3 - 40)) if hier else (slice(16, -16), slice(16, W - D))
     accuracy = float((d[inner] == gt[inner]).mean())
+    line = None
     if rank == 0:
         peak, peak_src = read_peaks()
         units = cells * (1 if hier else world)   # c4: one frame in total (strong scaling); c3: one pair per rank
-        line = {"metric": metric, "value": units * args.steps / (ms_dev * 1e-3) / 1e9, "unit": "Gdisp/s", "n_gpus": world,
-                "steps": args.steps, "warmup": warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        line = {"metric": metric, "value": units * steps / (ms_dev * 1e-3) / 1e9, "unit": "Gdisp/s", "n_gpus": world,
+                "steps": steps, "warmup": warmup, "ms_per_step": ms_dev / steps, "higher_is_better": True,
                 "scaling": "strong" if hier else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                "e2e": {"value": units * args.steps / (ms_host * 1e-3) / 1e9, "unit": "Gdisp/s", "h2d_bytes_per_step": int(h2d),
-                        "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_host / args.steps, "mode": e2e_mode,
-                        "serial_ms_per_step": ms_serial / args.steps},
+                "e2e": {"value": units * steps / (ms_host * 1e-3) / 1e9, "unit": "Gdisp/s", "h2d_bytes_per_step": int(h2d),
+                        "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_host / steps, "mode": e2e_mode,
+                        "serial_ms_per_step": ms_serial / steps},
                 "gpu_launches": int(launches), "clocks": clocks, "kernels_ms_per_step": {k: round(v, 4) for k, v in kern_ms.items()},
                 "ground_truth_agreement": accuracy}
         config["l2"] = "512 MB memset between timed steps (outside the event pairs)"
@@ -355,9 +356,9 @@ def main_float(args, wl, rank, world, local_rank):
         if dom_bytes:
             ach = dom_bytes / (kern_ms[dom] / n_launch * 1e-3) / 1e9
             traffic = None
-            try:  # measured DRAM bytes of that kernel per launch, from the committed ncu --set full capture
+            try:  # measured DRAM bytes of that kernel per launch, from the committed ncu --set full capture (taken on C3)
                 with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-                    traffic = json.load(f).get(dom)
+                    traffic = json.load(f).get(dom) if (H, W, D) == (1080, 1920, 192) else None
             except Exception:
                 traffic = None
             line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -367,31 +368,19 @@ def main_float(args, wl, rank, world, local_rank):
             line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
                                 "traffic": None, "peak_source": peak_src, "ms_per_step": kern_ms[dom],
                                 "note": "instruction-bound window sums over L2-resident images; no HBM roofline applies"}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and with_cpu and not args.no_cpu_baseline:
             line["cpu_baseline"], _ = cpu_reference_float(wl, 1, 0, budget_s=15.0)
-        print(json.dumps(line))
     if dist is not None:
         dist.barrier()
-        dist.destroy_process_group()
     ctx.close()
-    return 0
+    del flush
+    torch.cuda.empty_cache()
+    return line
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if wl.get("kind") in ("zncc", "hier"):
-        return main_float(args, wl, rank, world, local_rank)
+def main_census(args, wl, rank, world, local_rank, dist=None, steps=None, with_cpu=True):
+    """c2 / c5: census -> Hamming cost volume -> SGM -> WTA, independent pairs per rank. Returns the line (rank 0)."""
+    steps = steps or args.steps
     warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     H, W, D = wl["H"], wl["W"], wl["D"]
     cells = H * W * D
@@ -401,26 +390,21 @@ def main():
 
     if args.impl == "reference":
         if rank != 0:
-            return 0
-        base, dt = cpu_reference_run(wl, args.steps, args.warmup, budget_s=150.0)
+            return None
+        base, dt = cpu_reference_run(wl, steps, args.warmup, budget_s=150.0)
+        # what this arm really ran: a row band of the frame per step (the reference's SGM is O(D^2) per pixel and line)
+        config.update(cpu_band_rows=base["band_rows"], frame_rows=H, cpu_sample=base["sample"],
+                      cpu_full_frame_s_extrapolated=round(dt * H / base["band_rows"], 1))
         line = {"impl": "reference", "metric": "Gdisp/s (W*H*D/s) census+SGM+WTA", "value": base["value"], "unit": "Gdisp/s",
-                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+                "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16", "data": "synthetic",
                 "config": config, "cpu_baseline": base,
                 "e2e": {"value": base["value"], "unit": "Gdisp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line))
-        return 0
+        return line
 
     import torch
     from libstevi_b200 import api, synth
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
 
     # each rank owns its own pair (different seed): weak scaling over independent pairs
@@ -449,7 +433,9 @@ def main():
 
     def call_stream(c, out):
         api.censusSgmPipeline(nl, nr, wl["hr"], wl["vr"], D, P1, P2, POUT, NDIR, out=out, ctx=c)
-    stream_outs = [nd] + [torch.empty((H, W), dtype=torch.int32).pin_memory().numpy() for _ in range(E2E_DEPTH - 1)]
+    stream_outs = [nd] + [torch.empty((H, W), dtype=torch.int32).pin_memory().numpy() for _ in range(args.inflight - 1)]
+
+    d2h_bytes = H * W * (1 if D <= 256 else 2 if D <= 65536 else 4)
 
     def barrier():
         if dist is not None:
@@ -479,25 +465,49 @@ def main():
     for _ in range(warmup):
         step_device()
     n0 = ctx.launches
-    ms_dev, clocks = timed(step_device, args.steps, ClockSampler(local_rank) if rank == 0 else None)
+    ms_dev, clocks = timed(step_device, steps, ClockSampler(local_rank) if rank == 0 else None)
     launches = ctx.launches - n0
 
     for _ in range(warmup):
         step_host()
     for _ in range(warmup):
         step_device_disp()
-    ms_disp, _ = timed(step_device_disp, args.steps)
-    ms_serial, _ = timed(step_host, args.steps)
-    ms_host = timed_pair_stream(api, torch, call_stream, stream_outs, args.steps, warmup, local_rank, barrier, flush)
+    ms_disp, _ = timed(step_device_disp, steps)
+    ms_serial, _ = timed(step_host, steps)
+    ms_host = timed_pair_stream(api, torch, call_stream, stream_outs, steps, warmup, local_rank, barrier, flush)
     if dist is not None:
         t = torch.tensor([ms_host], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_host = float(t.item())
 
+    # sustained: back-to-back pairs for >= 2 s (no memset in between: every pair streams 3.2 GB through the 126 MB L2 anyway),
+    # clocks sampled throughout (>= 20 samples at 50 ms)
+    sustained = None
+    if with_cpu:   # (the headline run only)
+        n_sus = max(20, int(2.2e3 / max(ms_dev / steps, 1e-3)))
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        barrier()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_sus):
+            step_device()
+        e1.record()
+        barrier()
+        sus_clocks = sampler.stop() if sampler else None
+        ms_sus = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms_sus], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_sus = float(t.item())
+        sustained = {"value": world * cells * n_sus / (ms_sus * 1e-3) / 1e9, "unit": "Gdisp/s", "pairs": n_sus, "seconds": ms_sus * 1e-3,
+                     "ms_per_step": ms_sus / n_sus, "clocks": sus_clocks}
+
     # dominant kernel, per launch, CUDA events on the launching stream (second pass with the ctx's event hooks on)
     ctx.set_timing(True)
     per_kernel = {}
-    for _ in range(max(3, min(args.steps, 10))):
+    for _ in range(max(3, min(steps, 10))):
         flush.zero_()
         step_device()
         for name, ms in ctx.timing_report():
@@ -509,7 +519,7 @@ def main():
     dom_bytes = cells * BYTES_PER_CELL_SGM_APPLY if "sgm_apply" in dom else None
     traffic = None
     try:  # measured DRAM traffic of that kernel from the committed ncu --set full capture (C2 workload only)
-        if args.workload == "c2":
+        if (H, W, D) == (1080, 1920, 256):
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 traffic = json.load(f).get(dom.split("<")[0].strip("()"))
     except Exception:
@@ -519,24 +529,28 @@ def main():
     torch.cuda.synchronize()
     same = bool(np.array_equal(disp.cpu().numpy(), nd)) and bool(torch.equal(disp, disp_only))
 
+    line = None
     if rank == 0:
-        value = world * cells * args.steps / (ms_dev * 1e-3) / 1e9
-        e2e = world * cells * args.steps / (ms_host * 1e-3) / 1e9
+        value = world * cells * steps / (ms_dev * 1e-3) / 1e9
+        e2e = world * cells * steps / (ms_host * 1e-3) / 1e9
         line = {"metric": "Gdisp/s (W*H*D/s) census+SGM+WTA", "value": value, "unit": "Gdisp/s", "n_gpus": world,
-                "steps": args.steps, "warmup": warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+                "steps": steps, "warmup": warmup, "ms_per_step": ms_dev / steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u16", "data": "synthetic", "config": config,
                 "e2e": {"value": e2e, "unit": "Gdisp/s", "h2d_bytes_per_step": int(nl.nbytes + nr.nbytes),
-                        "d2h_bytes_per_step": int(nd.nbytes), "ms_per_step": ms_host / args.steps,
-                        "mode": f"{E2E_DEPTH} pairs in flight (HostPairStream: one ctx+stream per slot, stevi_ctx_set_deferred_host)",
-                        "serial_ms_per_step": ms_serial / args.steps},
+                        "d2h_bytes_per_step": int(d2h_bytes), "ms_per_step": ms_host / steps,
+                        "d2h_wire": f"disparity map as u{8 * d2h_bytes // (H * W)} over PCIe, widened into the caller's int32 array by "
+                                    "the host inside the timed region (stevi_ctx_set_narrow_wire)",
+                        "pcie_GBps_per_gpu": round((nl.nbytes + nr.nbytes + d2h_bytes) / (ms_host / steps * 1e-3) / 1e9, 2),
+                        "mode": f"{args.inflight} pairs in flight (HostPairStream: one ctx+stream per slot, stevi_ctx_set_deferred_host)",
+                        "serial_ms_per_step": ms_serial / steps},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "kernels_ms": {k.split("<")[0].strip("()"): round(v, 4) for k, v in kern_ms.items()},
-                "pipeline_algorithmic_GBps": cells * BYTES_PER_CELL_PIPELINE / (ms_dev / args.steps * 1e-3) / 1e9,
-                "disparity_only": {"ms_per_step": ms_disp / args.steps, "value": world * cells * args.steps / (ms_disp * 1e-3) / 1e9,
+                "pipeline_algorithmic_GBps": cells * BYTES_PER_CELL_PIPELINE / (ms_dev / steps * 1e-3) / 1e9,
+                "disparity_only": {"ms_per_step": ms_disp / steps, "value": world * cells * steps / (ms_disp * 1e-3) / 1e9,
                                    "unit": "Gdisp/s", "note": "same pipeline, caller asks for the disparity map only: the aggregated "
                                    "costs are evaluated in registers by the winner-take-all pass and not stored (what the e2e call runs); "
                                    "`value` is with the cost volume and the aggregated volume materialised as the reference's calls return them"},
-                "host_device_paths_agree": same}
+                "sustained": sustained, "host_device_paths_agree": same}
         config["l2"] = "512 MB memset between timed steps (outside the event pairs); per-step working set 3.2 GB >> 126 MB L2"
         if dom_bytes:
             ach = dom_bytes / (kern_ms[dom] * 1e-3) / 1e9
@@ -546,13 +560,194 @@ def main():
         else:
             line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None,
                                 "traffic": None, "peak_source": peak_src}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and with_cpu and not args.no_cpu_baseline:
             line["cpu_baseline"], _ = cpu_reference_run(wl, 1, 0, budget_s=15.0)
+            config.update(cpu_band_rows=line["cpu_baseline"]["band_rows"], frame_rows=H)
+    if dist is not None:
+        dist.barrier()
+    ctx.close()
+    del flush, cv, sg
+    torch.cuda.empty_cache()
+    return line if rank == 0 else None
+
+
+def main_c5_batch(args, wl, rank, world, local_rank, dist=None, pairs=1024):
+    """BASELINE configs[4] as the batch it is: `pairs` DISTINCT synthetic 1280x720 pairs (seeds 1000 ...), sharded over the ranks
+    (pair k -> rank k mod N, sharding.shard_pairs), streamed from page-locked host memory through the C ABI with
+    `--inflight` pairs in flight per GPU; every result lands in its own host array. The loop of
+    test/benchmarks/benchmarkCostVolumeWorkflow.cpp:175-260 with the calls left in flight."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from libstevi_b200 import api, synth, sharding
+    dev = torch.device("cuda", local_rank)
+    H, W, D = wl["H"], wl["W"], wl["D"]
+    mine = sharding.shard_pairs(pairs, world, rank)
+    Ls = torch.empty((len(mine), H, W), dtype=torch.uint8).pin_memory()
+    Rs = torch.empty((len(mine), H, W), dtype=torch.uint8).pin_memory()
+    out = torch.empty((len(mine), H, W), dtype=torch.int32).pin_memory()
+    nL, nR, nO = Ls.numpy(), Rs.numpy(), out.numpy()
+
+    def gen(k):
+        nL[k], nR[k], _ = synth.stereo_pair(H, W, wl["seed"] + mine[k], d_bg=8, d_sq=32, d_max=wl["d_max"])
+    with ThreadPoolExecutor(min(8, os.cpu_count() or 1)) as ex:
+        list(ex.map(gen, range(len(mine))))
+    hs = api.HostPairStream(args.inflight, local_rank)
+
+    def run(n):
+        for k in range(n):
+            api.censusSgmPipeline(nL[k], nR[k], wl["hr"], wl["vr"], D, P1, P2, POUT, NDIR, out=nO[k], ctx=hs.acquire())
+        hs.drain()
+    run(min(len(mine), 3 * args.inflight))   # workspaces settle
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    run(len(mine))
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    launches = hs.launches
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # spot check: the first and the last pair of this rank against the device-resident call
+    ctx = api.Context(local_rank, torch_stream=True)
+    ok = True
+    for k in (0, len(mine) - 1):
+        d = api.censusSgmPipeline(torch.from_numpy(nL[k]).to(dev), torch.from_numpy(nR[k]).to(dev), wl["hr"], wl["vr"], D, P1, P2, POUT, NDIR, ctx=ctx)
+        ok = ok and bool(np.array_equal(d.cpu().numpy(), nO[k]))
+    ctx.close()
+    hs.close()
+    if rank != 0:
+        return None
+    per_pair_bytes = 2 * H * W + H * W * (1 if D <= 256 else 2)
+    return {"workload": wl["name"], "pairs": pairs, "n_gpus": world, "inflight_per_gpu": args.inflight, "seconds": ms * 1e-3,
+            "pairs_per_s": pairs / (ms * 1e-3), "pairs_per_s_per_gpu": pairs / (ms * 1e-3) / world,
+            "Gdisp_per_s": pairs * H * W * D / (ms * 1e-3) / 1e9, "ms_per_pair_per_gpu": ms / len(mine),
+            "pcie_bytes_per_pair": per_pair_bytes, "pcie_GBps_per_gpu": round(per_pair_bytes * len(mine) / (ms * 1e-3) / 1e9, 2),
+            "roofline_pairs_per_s_per_gpu_at_100pct": round(read_peaks()[0] * 1e9 / (12 * H * W * D), 1),
+            "results_equal_device_resident_call": ok, "gpu_launches": int(launches)}
+
+
+def sgm_general_stage(local_rank, steps=3):
+    """The real SGM recurrence at C2 size (sgmCostVolume<8, Score> on a float volume of scores: the reference's own SGM benchmark
+    case, benchmarkCrossCorrelationAlgorithms.cpp:282-303) - a stage figure, device resident, CUDA events."""
+    import torch
+    from libstevi_b200 import api
+    dev = torch.device("cuda", local_rank)
+    H, W, D = 1080, 1920, 256
+    ctx = api.Context(local_rank, torch_stream=True)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1)
+    v = (torch.rand((H, D, W), device=dev, generator=g) * 2 - 1).permute(0, 2, 1)
+    fn = lambda: api.sgmCostVolume(v, 0.001, 0.01, Pout=100.0, nDirections=8, strategy=api.SCORE, ctx=ctx)
+    for _ in range(2):
+        fn()
+    ts = []
+    for _ in range(steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ctx.set_timing(True); ctx.timing_report(); fn()
+    kern = [[n.split("<")[0].strip("()"), round(ms, 4)] for n, ms in ctx.timing_report()]
+    ctx.set_timing(False)
+    ms = float(np.median(ts))
+    alg = H * W * D * 8
+    peak, _ = read_peaks()
+    ctx.close()
+    del v
+    torch.cuda.empty_cache()
+    return {"stage": "sgmCostVolume<8, Score> on a 1920x1080x256 f32 volume (general recurrence, sgm_sweep.cu)", "ms": ms,
+            "Gcells_per_s": H * W * D / ms / 1e6, "algorithmic_bytes": alg, "algorithmic_GBps": alg / ms / 1e6,
+            "frac_of_hbm_peak": alg / ms / 1e6 / peak, "kernels_ms": kern}
+
+
+def pin_rank_to_cores(local_rank, world):
+    """Each rank keeps to its own slice of the host cores (copy engines are fed by host threads; 8 ranks hopping over all
+    cores of a virtual machine slow each other's copies down)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cores) // max(world, 1))
+        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        os.sched_setaffinity(0, mine)
+        os.environ.setdefault("STEVI_HOST_THREADS", str(max(1, min(4, len(mine)))))
+        return len(mine)
+    except Exception:
+        return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--pairs", type=int, default=0, help="c5: stream this many distinct pairs (the batch of BASELINE configs[4])")
+    ap.add_argument("--inflight", type=int, default=4, help="pairs in flight per GPU in the end-to-end measurements")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="c2: leave the other configurations out of the line")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    is_float = wl.get("kind") in ("zncc", "hier")
+    if args.impl == "reference":
+        line = (main_float if is_float else main_census)(args, wl, rank, world, local_rank)
+        if line is not None:
+            print(json.dumps(line))
+        return 0
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    cores = pin_rank_to_cores(local_rank, world)
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if args.workload == "c5" and args.pairs > 0:
+        line = main_c5_batch(args, wl, rank, world, local_rank, dist, args.pairs)
+        if line is not None:
+            line = {"metric": "pairs/s census+SGM D=128 1280x720 batch", "value": line["pairs_per_s"], "unit": "pairs/s", "n_gpus": world,
+                    "higher_is_better": True, "scaling": "strong", "dtype": "u16", "data": "synthetic", "vs_baseline": None,
+                    "config": {"workload": wl["name"], "pairs": args.pairs}, "batch": line}
+    else:
+        line = (main_float if is_float else main_census)(args, wl, rank, world, local_rank, dist)
+    if line is not None:
+        line["host_cores_per_rank"] = cores
+    if args.workload == "c2" and not args.no_secondary and args.pairs == 0:
+        # the other configurations, in the same line (fewer steps each; the driver only runs the default command)
+        sec = {}
+        k = max(3, min(args.steps, 8))
+        for name in ("c1", "c3", "c4"):
+            r = main_float(args, WORKLOADS[name], rank, world, local_rank, dist, steps=k, with_cpu=False)
+            if r is not None:
+                sec[name] = {q: r[q] for q in ("value", "unit", "ms_per_step", "scaling", "e2e", "roofline", "kernels_ms_per_step",
+                                               "ground_truth_agreement", "gpu_launches") if q in r}
+                sec[name]["workload"] = r["config"]["workload"]
+        r = main_census(args, WORKLOADS["c5"], rank, world, local_rank, dist, steps=k, with_cpu=False)
+        if r is not None:
+            sec["c5"] = {q: r[q] for q in ("value", "unit", "ms_per_step", "e2e", "roofline", "gpu_launches") if q in r}
+            sec["c5"]["workload"] = r["config"]["workload"]
+        b = main_c5_batch(args, WORKLOADS["c5"], rank, world, local_rank, dist, pairs=128 * world)
+        if b is not None:
+            sec["c5"]["batch"] = b
+        if world == 1:
+            sec["sgm_general"] = sgm_general_stage(local_rank)
+        if line is not None:
+            line["secondary"] = sec
+    if line is not None:
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
-    ctx.close()
     return 0
 
 

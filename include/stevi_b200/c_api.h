@@ -98,6 +98,11 @@ STEVI_API int32_t stevi_ctx_set_row_origin(stevi_ctx* ctx, int32_t global_row_of
  * the kernels of another. Default off: calls with host operands return with their results in place. */
 STEVI_API int32_t stevi_ctx_set_deferred_host(stevi_ctx* ctx, int32_t enable);
 STEVI_API int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
+/* Disparity / index maps that go back to HOST memory as dense (H,W) int32 arrays (disp_t, correlation_base.h:47) cross PCIe as
+ * the narrowest exact type (u8 for up to 256 disparities, u16 up to 65536) and are widened into the caller's int32 array by the
+ * host when the copy has landed (inside the call, or inside stevi_ctx_synchronize with deferred host completion): the same
+ * values with a quarter / half of the device->host bytes. On by default; 0 sends the int32 map itself. */
+STEVI_API int32_t stevi_ctx_set_narrow_wire(stevi_ctx* ctx, int32_t enable);
 STEVI_API const char* stevi_last_error(stevi_ctx* ctx);
 /* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */
 STEVI_API int64_t stevi_ctx_launch_count(stevi_ctx* ctx);

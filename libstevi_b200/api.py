@@ -145,6 +145,10 @@ class Context:
         """The ctx's cudaStream_t as an integer."""
         return lib.stevi_ctx_stream(self._h) or 0
 
+    def set_narrow_wire(self, enable):
+        """Index / disparity maps returned to host memory cross PCIe as u8 / u16 and are widened by the host (default on)."""
+        self.check(lib.stevi_ctx_set_narrow_wire(self._h, 1 if enable else 0))
+
     def set_row_origin(self, row):
         """Global frame row of row 0 of the images passed next (row-band runs; see stevi_ctx_set_row_origin)."""
         self.check(lib.stevi_ctx_set_row_origin(self._h, int(row)))

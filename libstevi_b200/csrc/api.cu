@@ -143,7 +143,7 @@ int32_t stevi_wta(stevi_ctx* c, const stevi_array* vol, int32_t strategy, stevi_
 	Stager st(c);
 	View vv, vo;
 	STEVI_TRY(st.in(vol, vv, "vol"));
-	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(st.out_index(out, vo, vv.ndim == 3 ? vv.shape[2] : 0, 1, 0, "out"));
 	STEVI_TRY(wta_dev(c, vv, strategy, vo));
 	return st.finish();
 }
@@ -364,7 +364,8 @@ int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stev
 	STEVI_TRY(check_images(c, vl, vr_));
 	if (!disp) return fail(c, STEVI_E_ARG, "pipeline: disp is required");
 	if (D < 1) return fail(c, STEVI_E_ARG, "pipeline: disp_width must be positive");   // before any workspace is sized by it
-	STEVI_TRY(st.out(disp, vd, "disp"));
+	// selectedIndexToDisp is folded into the result: disp = +-index (correlation_base.h:511-532)
+	STEVI_TRY(st.out_index(disp, vd, D, direction == STEVI_RIGHT_TO_LEFT ? 1 : -1, 0, "disp"));
 	const int H = vl.shape[0];
 	const int Ws = direction == STEVI_RIGHT_TO_LEFT ? vr_.shape[1] : vl.shape[1];
 	// volumes the caller does not want live in the workspace, in the reference's [H][D][W] layout
@@ -438,7 +439,7 @@ int32_t stevi_local_matching_pipeline(stevi_ctx* c, int32_t mf, const stevi_arra
 		vcv.shape[0] = H; vcv.shape[1] = Ws; vcv.shape[2] = D;
 		vcv.st[0] = (int64_t)Ws * D; vcv.st[1] = 1; vcv.st[2] = Ws;   // the reference's [H][D][W] layout
 	}
-	if (idx_out) STEVI_TRY(st.out(idx_out, vidx, "idx_out"));
+	if (idx_out) STEVI_TRY(st.out_index(idx_out, vidx, D, 1, 0, "idx_out"));
 	else {
 		int32_t* p = nullptr;
 		STEVI_TRY(arena_alloc_t(c, (size_t)H * Ws, &p));

@@ -41,6 +41,14 @@ struct stevi_ctx {
 	void* sgm_xchg = nullptr;
 	size_t sgm_xchg_bytes = 0;
 	unsigned sgm_epoch = 0;
+	// disparity maps going to host memory travel as the narrowest exact type (u8 / u16) and are widened into the caller's
+	// int32 array by the host once the copy has landed (ctx.cu: Stager::out_index): tasks waiting for that, and the
+	// page-locked staging buffers they use (a free list; a buffer is busy from its call to the synchronisation that widens it)
+	struct Widen { void* staged; int32_t* dst; size_t n; int bytes_per; int sign, offset; size_t slot; };
+	std::vector<Widen> widen;
+	struct Pinned { void* p; size_t cap; bool busy; };
+	std::vector<Pinned> pinned;
+	bool narrow_wire = true;
 };
 
 namespace stevi {
@@ -114,13 +122,18 @@ public:
 	explicit Stager(stevi_ctx* c) : c_(c) {}
 	int32_t in(const stevi_array* a, View& v, const char* name);
 	int32_t out(const stevi_array* a, View& v, const char* name);
+	// an (H,W) i32 result whose values are sign * k + offset with k in [0, n_values): a host array receives k as u8 / u16
+	// and is widened by the host after the copy (4x / 2x fewer bytes over PCIe); anything else behaves like out()
+	int32_t out_index(const stevi_array* a, View& v, int n_values, int sign, int offset, const char* name);
 	// issues the D2H copies; synchronises the stream when any operand lived in host memory
 	int32_t finish();
 private:
 	int32_t check(const stevi_array* a, const char* name);
 	struct Back { void* host; void* dev; size_t bytes; };
+	struct Narrow { int32_t* host; const int32_t* dev; size_t n; int bytes_per; int sign, offset; };
 	stevi_ctx* c_;
 	std::vector<Back> back_;
+	std::vector<Narrow> narrow_;
 	bool any_host_ = false;
 };
 
@@ -132,6 +145,9 @@ inline int32_t begin_call(stevi_ctx* c) {
 }
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// after a stream synchronisation: widen the narrow disparity maps that have landed (ctx.cu)
+void finish_host(stevi_ctx* c);
 
 // after a stream synchronisation: did a kernel raise the fault flag?
 inline int32_t check_fault(stevi_ctx* c) {

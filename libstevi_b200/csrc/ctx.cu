@@ -109,12 +109,81 @@ int32_t Stager::out(const stevi_array* a, View& v, const char* name) {
 	return STEVI_OK;
 }
 
+template<typename TN>
+__global__ void __launch_bounds__(256) k_narrow_index(const int32_t* __restrict__ src, TN* __restrict__ dst, size_t n, int sign, int offset) {
+	const size_t k = (size_t)blockIdx.x * 256 + threadIdx.x;
+	if (k < n) dst[k] = (TN)((src[k] - offset) * sign);
+}
+
+int32_t Stager::out_index(const stevi_array* a, View& v, int n_values, int sign, int offset, const char* name) {
+	STEVI_TRY(check(a, name));
+	const bool dense2 = a->ndim == 2 && a->strides[1] == 1 && a->strides[0] == a->shape[1];
+	if (a->mem == STEVI_DEVICE || !c_->narrow_wire || a->dtype != STEVI_I32 || !dense2 || n_values > 65536 || n_values < 1 ||
+		(sign != 1 && sign != -1))
+		return out(a, v, name);
+	fill_view(a, v);
+	any_host_ = true;
+	const size_t n = v.count();
+	void* d = nullptr;
+	STEVI_TRY(arena_alloc(c_, n * sizeof(int32_t), &d));
+	v.p = d;
+	narrow_.push_back({static_cast<int32_t*>(a->data), static_cast<const int32_t*>(d), n, n_values <= 256 ? 1 : 2, sign, offset});
+	return STEVI_OK;
+}
+
+static int host_threads() {
+	static int n = [] { const char* e = getenv("STEVI_HOST_THREADS"); int v = e ? atoi(e) : 4; return v < 1 ? 1 : v; }();
+	return n;
+}
+
+void finish_host(stevi_ctx* c) {
+	for (auto& w : c->widen) {
+		const long n = (long)w.n;
+		int32_t* dst = w.dst;
+		const int sign = w.sign, offset = w.offset;
+		if (w.bytes_per == 1) {
+			const uint8_t* src = static_cast<const uint8_t*>(w.staged);
+#pragma omp parallel for num_threads(host_threads()) schedule(static)
+			for (long k = 0; k < n; k++) dst[k] = sign * (int32_t)src[k] + offset;
+		} else {
+			const uint16_t* src = static_cast<const uint16_t*>(w.staged);
+#pragma omp parallel for num_threads(host_threads()) schedule(static)
+			for (long k = 0; k < n; k++) dst[k] = sign * (int32_t)src[k] + offset;
+		}
+		c->pinned[w.slot].busy = false;
+	}
+	c->widen.clear();
+}
+
 int32_t Stager::finish() {
 	for (auto& b : back_)
 		if (b.bytes) STEVI_CUDA(c_, cudaMemcpyAsync(b.host, b.dev, b.bytes, cudaMemcpyDeviceToHost, c_->stream));
 	back_.clear();
+	for (auto& nw : narrow_) {
+		if (!nw.n) continue;
+		const size_t bytes = nw.n * nw.bytes_per;
+		void* dn = nullptr;
+		STEVI_TRY(arena_alloc(c_, bytes, &dn));
+		const unsigned blocks = (unsigned)((nw.n + 255) / 256);
+		if (nw.bytes_per == 1) STEVI_LAUNCH(c_, k_narrow_index<uint8_t>, blocks, 256, 0, nw.dev, static_cast<uint8_t*>(dn), nw.n, nw.sign, nw.offset);
+		else STEVI_LAUNCH(c_, k_narrow_index<uint16_t>, blocks, 256, 0, nw.dev, static_cast<uint16_t*>(dn), nw.n, nw.sign, nw.offset);
+		// a page-locked staging buffer that no pending task uses
+		size_t slot = c_->pinned.size();
+		for (size_t k = 0; k < c_->pinned.size(); k++)
+			if (!c_->pinned[k].busy && c_->pinned[k].cap >= bytes) { slot = k; break; }
+		if (slot == c_->pinned.size()) {
+			void* hp = nullptr;
+			STEVI_CUDA(c_, cudaHostAlloc(&hp, bytes, cudaHostAllocDefault));
+			c_->pinned.push_back({hp, bytes, false});
+		}
+		c_->pinned[slot].busy = true;
+		STEVI_CUDA(c_, cudaMemcpyAsync(c_->pinned[slot].p, dn, bytes, cudaMemcpyDeviceToHost, c_->stream));
+		c_->widen.push_back({c_->pinned[slot].p, nw.host, nw.n, nw.bytes_per, nw.sign, nw.offset, slot});
+	}
+	narrow_.clear();
 	if (any_host_ && !c_->deferred_host) {
 		STEVI_CUDA(c_, cudaStreamSynchronize(c_->stream));
+		finish_host(c_);
 		return check_fault(c_);
 	}
 	return STEVI_OK;
@@ -172,6 +241,8 @@ int32_t stevi_ctx_destroy(stevi_ctx* c) {
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	if (c->fault_host) cudaFreeHost(c->fault_host);
 	if (c->sgm_xchg) cudaFree(c->sgm_xchg);
+	c->widen.clear();   // (results nobody synchronised for are dropped: their host arrays may be gone)
+	for (auto& pb : c->pinned) cudaFreeHost(pb.p);
 	delete c;
 	return STEVI_OK;
 }
@@ -206,7 +277,14 @@ void* stevi_ctx_stream(stevi_ctx* c) { return c ? (void*)c->stream : nullptr; }
 int32_t stevi_ctx_synchronize(stevi_ctx* c) {
 	if (!c) return STEVI_E_ARG;
 	STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
+	finish_host(c);
 	return check_fault(c);
+}
+
+int32_t stevi_ctx_set_narrow_wire(stevi_ctx* c, int32_t enable) {
+	if (!c) return STEVI_E_ARG;
+	c->narrow_wire = enable != 0;
+	return STEVI_OK;
 }
 
 const char* stevi_last_error(stevi_ctx* c) { return c ? c->err.c_str() : "null context"; }

@@ -54,3 +54,44 @@ def test_deferred_flag_off_by_default_and_reversible(api):
     c.set_deferred_host(False)
     assert np.array_equal(a, api.censusSgmPipeline(L, R, 2, 2, 8, 5.0, 50.0, ctx=c))
     c.close()
+
+
+# ---- narrow wire: index / disparity maps returned to host memory cross PCIe as u8 / u16 and are widened by the host ----------
+
+@pytest.mark.parametrize("D", [40, 256, 300])
+@pytest.mark.parametrize("ddir", ["r2l", "l2r"])
+def test_narrow_wire_gives_the_same_disparities(api, D, ddir):
+    from libstevi_b200 import synth
+    L, R, _ = synth.stereo_pair(60, 400, 9, d_bg=5, d_sq=20, d_max=60)
+    direction = api.RIGHT_TO_LEFT if ddir == "r2l" else api.LEFT_TO_RIGHT
+    a, b = api.Context(0), api.Context(0)
+    b.set_narrow_wire(False)
+    try:
+        da = api.censusSgmPipeline(L, R, 4, 3, D, 10, 120, 100, 8, dDir=direction, ctx=a)
+        db = api.censusSgmPipeline(L, R, 4, 3, D, 10, 120, 100, 8, dDir=direction, ctx=b)
+        assert da.dtype == np.int32 and np.array_equal(da, db)
+        assert (da.min() < 0) == (ddir == "l2r")
+        # a strided host result (not a dense map) takes the plain int32 copy and still agrees
+        wide = np.full((60, 2 * da.shape[1]), -7, np.int32)
+        api.censusSgmPipeline(L, R, 4, 3, D, 10, 120, 100, 8, dDir=direction, out=wide[:, ::2], ctx=a)
+        assert np.array_equal(wide[:, ::2], db) and (wide[:, 1::2] == -7).all()
+        # extractSelectedIndex of a host volume
+        v = np.random.default_rng(1).integers(0, 50, (30, 40, D)).astype(np.uint16)
+        assert np.array_equal(api.extractSelectedIndex(v, api.COST, ctx=a), api.extractSelectedIndex(v, api.COST, ctx=b))
+    finally:
+        a.close(); b.close()
+
+
+def test_narrow_wire_with_pairs_in_flight(api):
+    from libstevi_b200 import synth
+    hs = api.HostPairStream(3, 0)
+    pairs = [synth.stereo_pair(48, 200, 30 + k, d_bg=3, d_sq=11, d_max=20)[:2] for k in range(7)]
+    outs = [np.empty((48, 200), np.int32) for _ in pairs]
+    for (L, R), o in zip(pairs, outs):
+        api.censusSgmPipeline(L, R, 4, 3, 32, 10, 120, 100, 8, out=o, ctx=hs.acquire())
+    hs.drain()
+    c = api.Context(0)
+    c.set_narrow_wire(False)
+    for (L, R), o in zip(pairs, outs):
+        assert np.array_equal(o, api.censusSgmPipeline(L, R, 4, 3, 32, 10, 120, 100, 8, ctx=c))
+    c.close(); hs.close()
