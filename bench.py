@@ -30,6 +30,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# the library's host-side widening threads (OpenMP) must sleep between pairs, not spin on the cores that feed the copy engines
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")
+os.environ.setdefault("GOMP_SPINCOUNT", "0")
 
 import numpy as np  # noqa: E402
 
@@ -178,13 +181,13 @@ def cpu_reference_float(wl, steps, warmup, budget_s=15.0):
 
 
 
-def timed_pair_stream(api, torch, call, outs, steps, warmup, device, barrier, flush):
+def timed_pair_stream(api, torch, call, outs, steps, warmup, device, barrier, flush, narrow_wire=True):
     """End-to-end throughput with len(outs) pairs in flight (api.HostPairStream: one ctx + stream per slot, deferred host
     completion): every step enqueues its own H2D copies from pinned memory, its kernels and its D2H copy; the copies of one
     pair overlap the kernels of another. Device time from the first enqueue to the last result landing in host memory
     (event pair on the idle default stream, recorded after a full synchronise and after the drain). No L2 flush is possible
     between overlapped steps; each step streams >= 1.6 GB of cost volume through the 126 MB L2."""
-    hs = api.HostPairStream(len(outs), device)
+    hs = api.HostPairStream(len(outs), device, narrow_wire=narrow_wire)
     for _ in range(max(warmup, 3 * len(outs))):   # a ctx's workspace settles on its third call (grow, consolidate, steady)
         slot = hs.slot
         call(hs.acquire(), outs[slot])
@@ -475,10 +478,16 @@ def main_census(args, wl, rank, world, local_rank, dist=None, steps=None, with_c
     ms_disp, _ = timed(step_device_disp, steps)
     ms_serial, _ = timed(step_host, steps)
     ms_host = timed_pair_stream(api, torch, call_stream, stream_outs, steps, warmup, local_rank, barrier, flush)
+    # the same loop with the int32 map itself on the wire, and with the caller taking the map as u8 / u16 (no widening)
+    ms_wide = timed_pair_stream(api, torch, call_stream, stream_outs, steps, warmup, local_rank, barrier, flush, narrow_wire=False)
+    ntype = np.uint8 if D <= 256 else np.uint16
+    narrow_outs = [torch.empty((H, W), dtype=torch.uint8 if D <= 256 else torch.uint16).pin_memory().numpy() for _ in range(args.inflight)]
+    ms_narrow = timed_pair_stream(api, torch, call_stream, narrow_outs, steps, warmup, local_rank, barrier, flush)
+    narrow_same = bool(np.array_equal(narrow_outs[0].astype(np.int32), stream_outs[0]))
     if dist is not None:
-        t = torch.tensor([ms_host], dtype=torch.float64, device=dev)
+        t = torch.tensor([ms_host, ms_wide, ms_narrow], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_host = float(t.item())
+        ms_host, ms_wide, ms_narrow = (float(x) for x in t.tolist())
 
     # sustained: back-to-back pairs for >= 2 s (no memset in between: every pair streams 3.2 GB through the 126 MB L2 anyway),
     # clocks sampled throughout (>= 20 samples at 50 ms)
@@ -541,6 +550,12 @@ def main_census(args, wl, rank, world, local_rank, dist=None, steps=None, with_c
                         "d2h_wire": f"disparity map as u{8 * d2h_bytes // (H * W)} over PCIe, widened into the caller's int32 array by "
                                     "the host inside the timed region (stevi_ctx_set_narrow_wire)",
                         "pcie_GBps_per_gpu": round((nl.nbytes + nr.nbytes + d2h_bytes) / (ms_host / steps * 1e-3) / 1e9, 2),
+                        "variants": {
+                            "int32_map_on_the_wire": {"ms_per_step": ms_wide / steps, "value": world * cells * steps / (ms_wide * 1e-3) / 1e9,
+                                                      "d2h_bytes_per_step": int(nd.nbytes)},
+                            "caller_takes_a_narrow_map": {"ms_per_step": ms_narrow / steps, "value": world * cells * steps / (ms_narrow * 1e-3) / 1e9,
+                                                          "d2h_bytes_per_step": int(narrow_outs[0].nbytes), "dtype": str(np.dtype(ntype)),
+                                                          "equal_to_the_int32_map": narrow_same}},
                         "mode": f"{args.inflight} pairs in flight (HostPairStream: one ctx+stream per slot, stevi_ctx_set_deferred_host)",
                         "serial_ms_per_step": ms_serial / steps},
                 "gpu_launches": int(launches), "clocks": clocks,
@@ -584,14 +599,15 @@ def main_c5_batch(args, wl, rank, world, local_rank, dist=None, pairs=1024):
     mine = sharding.shard_pairs(pairs, world, rank)
     Ls = torch.empty((len(mine), H, W), dtype=torch.uint8).pin_memory()
     Rs = torch.empty((len(mine), H, W), dtype=torch.uint8).pin_memory()
-    out = torch.empty((len(mine), H, W), dtype=torch.int32).pin_memory()
+    odt = {"int32": torch.int32, "u8": torch.uint8, "u16": torch.uint16}[args.result_dtype]
+    out = torch.empty((len(mine), H, W), dtype=odt).pin_memory()
     nL, nR, nO = Ls.numpy(), Rs.numpy(), out.numpy()
 
     def gen(k):
         nL[k], nR[k], _ = synth.stereo_pair(H, W, wl["seed"] + mine[k], d_bg=8, d_sq=32, d_max=wl["d_max"])
     with ThreadPoolExecutor(min(8, os.cpu_count() or 1)) as ex:
         list(ex.map(gen, range(len(mine))))
-    hs = api.HostPairStream(args.inflight, local_rank)
+    hs = api.HostPairStream(args.inflight, local_rank, narrow_wire=not args.wide_wire)
 
     def run(n):
         for k in range(n):
@@ -619,17 +635,18 @@ def main_c5_batch(args, wl, rank, world, local_rank, dist=None, pairs=1024):
     ok = True
     for k in (0, len(mine) - 1):
         d = api.censusSgmPipeline(torch.from_numpy(nL[k]).to(dev), torch.from_numpy(nR[k]).to(dev), wl["hr"], wl["vr"], D, P1, P2, POUT, NDIR, ctx=ctx)
-        ok = ok and bool(np.array_equal(d.cpu().numpy(), nO[k]))
+        ok = ok and bool(np.array_equal(d.cpu().numpy(), nO[k].astype(np.int32)))
     ctx.close()
     hs.close()
     if rank != 0:
         return None
-    per_pair_bytes = 2 * H * W + H * W * (1 if D <= 256 else 2)
+    per_pair_bytes = 2 * H * W + H * W * (4 if (args.wide_wire and args.result_dtype == "int32") else 2 if (D > 256 or args.result_dtype == "u16") else 1)
     return {"workload": wl["name"], "pairs": pairs, "n_gpus": world, "inflight_per_gpu": args.inflight, "seconds": ms * 1e-3,
             "pairs_per_s": pairs / (ms * 1e-3), "pairs_per_s_per_gpu": pairs / (ms * 1e-3) / world,
             "Gdisp_per_s": pairs * H * W * D / (ms * 1e-3) / 1e9, "ms_per_pair_per_gpu": ms / len(mine),
             "pcie_bytes_per_pair": per_pair_bytes, "pcie_GBps_per_gpu": round(per_pair_bytes * len(mine) / (ms * 1e-3) / 1e9, 2),
             "roofline_pairs_per_s_per_gpu_at_100pct": round(read_peaks()[0] * 1e9 / (12 * H * W * D), 1),
+            "result_dtype": args.result_dtype, "wire": "int32 map" if (args.wide_wire and args.result_dtype == "int32") else "narrow map",
             "results_equal_device_resident_call": ok, "gpu_launches": int(launches)}
 
 
@@ -680,6 +697,49 @@ def pin_rank_to_cores(local_rank, world):
         return None
 
 
+def copy_ceiling(rank, world, local_rank, dist, seconds=0.6):
+    """What the box's host path gives when every rank copies at once (no kernels): pinned-memory H2D of one C2 image pair (4.1 MB)
+    and D2H of one disparity map (8.3 MB as int32, 2.1 MB as u8), back to back on two streams. GB/s per GPU, min over ranks."""
+    import torch
+    dev = torch.device("cuda", local_rank)
+    H, W = 1080, 1920
+    out = {}
+    for name, h2d_b, d2h_b in (("h2d_pair_only", 2 * H * W, 0), ("d2h_int32_map_only", 0, 4 * H * W), ("d2h_u8_map_only", 0, H * W),
+                                ("pair_in_int32_map_out", 2 * H * W, 4 * H * W), ("pair_in_u8_map_out", 2 * H * W, H * W)):
+        hin = torch.empty(max(h2d_b, 1), dtype=torch.uint8).pin_memory()
+        din = torch.empty(max(h2d_b, 1), dtype=torch.uint8, device=dev)
+        hout = torch.empty(max(d2h_b, 1), dtype=torch.uint8).pin_memory()
+        dout = torch.empty(max(d2h_b, 1), dtype=torch.uint8, device=dev)
+        s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+        def burst(n):
+            for _ in range(n):
+                if h2d_b:
+                    with torch.cuda.stream(s1):
+                        din.copy_(hin, non_blocking=True)
+                if d2h_b:
+                    with torch.cuda.stream(s2):
+                        hout.copy_(dout, non_blocking=True)
+        burst(20)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        n = 400
+        t0 = time.perf_counter()
+        burst(n)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            dist.barrier()
+        gbps = n * (h2d_b + d2h_b) / dt / 1e9
+        if dist is not None:
+            t = torch.tensor([gbps], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            gbps = float(t.item())
+        out[name] = {"GBps_per_gpu_min_over_ranks": round(gbps, 2), "ms_per_pair": round((h2d_b + d2h_b) / gbps / 1e6, 4)}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -690,6 +750,10 @@ def main():
     ap.add_argument("--pairs", type=int, default=0, help="c5: stream this many distinct pairs (the batch of BASELINE configs[4])")
     ap.add_argument("--inflight", type=int, default=4, help="pairs in flight per GPU in the end-to-end measurements")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--result-dtype", default="int32", choices=["int32", "u8", "u16"], help="c5 batch: type of the host disparity maps")
+    ap.add_argument("--wide-wire", action="store_true", help="c5 batch: send int32 maps over PCIe (no narrow wire)")
+    ap.add_argument("--copy-ceiling", action="store_true", help="also measure what pinned copies alone reach with every rank copying")
+    ap.add_argument("--no-pin", action="store_true", help="do not pin the rank to its slice of the host cores")
     ap.add_argument("--no-secondary", action="store_true", help="c2: leave the other configurations out of the line")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -706,7 +770,7 @@ def main():
     import torch
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
-    cores = pin_rank_to_cores(local_rank, world)
+    cores = None if args.no_pin else pin_rank_to_cores(local_rank, world)
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -720,8 +784,11 @@ def main():
                     "config": {"workload": wl["name"], "pairs": args.pairs}, "batch": line}
     else:
         line = (main_float if is_float else main_census)(args, wl, rank, world, local_rank, dist)
+    ceiling = copy_ceiling(rank, world, local_rank, dist) if args.copy_ceiling else None
     if line is not None:
         line["host_cores_per_rank"] = cores
+        if ceiling:
+            line["pinned_copy_ceiling"] = ceiling
     if args.workload == "c2" and not args.no_secondary and args.pairs == 0:
         # the other configurations, in the same line (fewer steps each; the driver only runs the default command)
         sec = {}

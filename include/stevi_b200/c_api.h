@@ -307,7 +307,8 @@ STEVI_API int32_t stevi_hierarchical(stevi_ctx* ctx, int32_t matchfunc, int32_t 
 
 /* census cost volume -> SGM -> WTA -> disparity in one call, the sequence of
  * test/benchmarks/benchmarkCrossCorrelationAlgorithms.cpp:289-293 with matchFunc = CENSUS and strategy = Cost.
- * img_l, img_r (H,W) u8|f32; disp (H,W) i32 (required). cv_out (H,W,D) u16 and sgm_out (H,W,D) f32 are optional
+ * img_l, img_r (H,W) u8|f32; disp (H,W) i32 (required; a dense u8 / u16 array is accepted for RIGHT_TO_LEFT when disp_width fits
+ * the type: a quarter / half of the bytes for callers that keep disparities narrow). cv_out (H,W,D) u16 and sgm_out (H,W,D) f32 are optional
  * (NULL = keep the volume in the ctx workspace / do not materialise it at all when the semantics allow).
  * Results are bit-identical to calling stevi_cost_volume, stevi_sgm, stevi_wta, stevi_index_to_disp in turn. */
 STEVI_API int32_t stevi_census_sgm_pipeline(stevi_ctx* ctx, const stevi_array* img_l, const stevi_array* img_r,

@@ -187,12 +187,13 @@ class HostPairStream:
         stream.drain()
     """
 
-    def __init__(self, depth=3, device=0):
+    def __init__(self, depth=3, device=0, narrow_wire=True):
         if depth < 1:
             raise ValueError("depth must be positive")
         self.slots = [Context(device) for _ in range(depth)]
         for c in self.slots:
             c.set_deferred_host(True)
+            c.set_narrow_wire(narrow_wire)
         self._next = 0
 
     @property

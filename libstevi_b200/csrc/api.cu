@@ -380,7 +380,7 @@ int32_t stevi_census_sgm_pipeline(stevi_ctx* c, const stevi_array* l, const stev
 	stevi_margins mg = margins ? *margins : stevi_margins{0, 0, 0, 0};
 	const bool pout_int = Pout == rintf(Pout) && fabsf(Pout) <= 1.0e6f;
 	const bool collapse = semantics == STEVI_COMPAT && pout_int;
-	if (vd.ndim != 2 || vd.dtype != STEVI_I32 || vd.shape[0] != H || vd.shape[1] != Ws) return fail(c, STEVI_E_SHAPE, "pipeline: disp must be (H,W) i32");
+	if (vd.ndim != 2 || vd.dtype != STEVI_I32 || vd.shape[0] != H || vd.shape[1] != Ws) return fail(c, STEVI_E_SHAPE, "pipeline: disp must be (H,W) i32 (or u8 / u16 for RIGHT_TO_LEFT maps that fit)");
 	// the WTA rides on the last SGM pass and selectedIndexToDisp (correlation_base.h:511-532) is folded into its output
 	WtaSink sink{vd, direction == STEVI_RIGHT_TO_LEFT ? 1 : -1, 0};
 	const int max_cost = 32 * census_n_written(hr, vr, semantics);

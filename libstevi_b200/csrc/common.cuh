@@ -130,7 +130,8 @@ public:
 private:
 	int32_t check(const stevi_array* a, const char* name);
 	struct Back { void* host; void* dev; size_t bytes; };
-	struct Narrow { int32_t* host; const int32_t* dev; size_t n; int bytes_per; int sign, offset; };
+	// final != nullptr: the caller's own array is u8 / u16 (device, or host: no widening), the narrowed map goes straight there
+	struct Narrow { int32_t* host; const int32_t* dev; size_t n; int bytes_per; int sign, offset; void* final; int final_mem; };
 	stevi_ctx* c_;
 	std::vector<Back> back_;
 	std::vector<Narrow> narrow_;

@@ -1,5 +1,6 @@
 // Context, workspace arena and host-operand staging for the C ABI (include/stevi_b200/c_api.h).
 #include "common.cuh"
+#include <immintrin.h>
 
 namespace stevi {
 
@@ -118,6 +119,19 @@ __global__ void __launch_bounds__(256) k_narrow_index(const int32_t* __restrict_
 int32_t Stager::out_index(const stevi_array* a, View& v, int n_values, int sign, int offset, const char* name) {
 	STEVI_TRY(check(a, name));
 	const bool dense2 = a->ndim == 2 && a->strides[1] == 1 && a->strides[0] == a->shape[1];
+	if (a->dtype == STEVI_U8 || a->dtype == STEVI_U16) {
+		// the caller takes the map in a narrow type (non-negative indices only): computed as int32, narrowed into its array
+		if (!dense2 || sign != 1 || offset != 0 || n_values < 1 || n_values > (a->dtype == STEVI_U8 ? 256 : 65536))
+			return fail(c_, STEVI_E_DTYPE, "%s: a u8 / u16 map must be dense, hold non-negative values (RIGHT_TO_LEFT, offset 0) and fit its type", name);
+		fill_view(a, v);
+		const size_t n = v.count();
+		void* d = nullptr;
+		STEVI_TRY(arena_alloc(c_, n * sizeof(int32_t), &d));
+		v.p = d; v.dtype = STEVI_I32;
+		if (a->mem != STEVI_DEVICE) any_host_ = true;
+		narrow_.push_back({nullptr, static_cast<const int32_t*>(d), n, a->dtype == STEVI_U8 ? 1 : 2, 1, 0, a->data, a->mem});
+		return STEVI_OK;
+	}
 	if (a->mem == STEVI_DEVICE || !c_->narrow_wire || a->dtype != STEVI_I32 || !dense2 || n_values > 65536 || n_values < 1 ||
 		(sign != 1 && sign != -1))
 		return out(a, v, name);
@@ -127,7 +141,7 @@ int32_t Stager::out_index(const stevi_array* a, View& v, int n_values, int sign,
 	void* d = nullptr;
 	STEVI_TRY(arena_alloc(c_, n * sizeof(int32_t), &d));
 	v.p = d;
-	narrow_.push_back({static_cast<int32_t*>(a->data), static_cast<const int32_t*>(d), n, n_values <= 256 ? 1 : 2, sign, offset});
+	narrow_.push_back({static_cast<int32_t*>(a->data), static_cast<const int32_t*>(d), n, n_values <= 256 ? 1 : 2, sign, offset, nullptr, 0});
 	return STEVI_OK;
 }
 
@@ -136,19 +150,33 @@ static int host_threads() {
 	return n;
 }
 
+// dst[k] = sign * src[k] + offset. The int32 map is written with streaming stores: it is 4x / 2x the bytes that crossed PCIe and
+// is not read again by this code, so it should not pull its cache lines in first.
+template<typename TN>
+static void widen_range(const TN* src, int32_t* dst, long n, int sign, int offset) {
+	long k = 0;
+	while (k < n && ((uintptr_t)(dst + k) & 31)) { dst[k] = sign * (int32_t)src[k] + offset; k++; }
+	const __m256i vo = _mm256_set1_epi32(offset);
+	for (; k + 8 <= n; k += 8) {
+		__m256i w;
+		if (sizeof(TN) == 1) w = _mm256_cvtepu8_epi32(_mm_loadl_epi64(reinterpret_cast<const __m128i*>(src + k)));
+		else w = _mm256_cvtepu16_epi32(_mm_loadu_si128(reinterpret_cast<const __m128i*>(src + k)));
+		if (sign < 0) w = _mm256_sub_epi32(_mm256_setzero_si256(), w);
+		_mm256_stream_si256(reinterpret_cast<__m256i*>(dst + k), _mm256_add_epi32(w, vo));
+	}
+	for (; k < n; k++) dst[k] = sign * (int32_t)src[k] + offset;
+	_mm_sfence();
+}
+
 void finish_host(stevi_ctx* c) {
 	for (auto& w : c->widen) {
 		const long n = (long)w.n;
-		int32_t* dst = w.dst;
-		const int sign = w.sign, offset = w.offset;
-		if (w.bytes_per == 1) {
-			const uint8_t* src = static_cast<const uint8_t*>(w.staged);
-#pragma omp parallel for num_threads(host_threads()) schedule(static)
-			for (long k = 0; k < n; k++) dst[k] = sign * (int32_t)src[k] + offset;
-		} else {
-			const uint16_t* src = static_cast<const uint16_t*>(w.staged);
-#pragma omp parallel for num_threads(host_threads()) schedule(static)
-			for (long k = 0; k < n; k++) dst[k] = sign * (int32_t)src[k] + offset;
+		const int nt = (int)std::max(1L, std::min((long)host_threads(), n / 65536));
+#pragma omp parallel for num_threads(nt) schedule(static)
+		for (int t = 0; t < nt; t++) {
+			const long a = n * t / nt / 8 * 8, b = t + 1 == nt ? n : n * (t + 1) / nt / 8 * 8;
+			if (w.bytes_per == 1) widen_range(static_cast<const uint8_t*>(w.staged) + a, w.dst + a, b - a, w.sign, w.offset);
+			else widen_range(static_cast<const uint16_t*>(w.staged) + a, w.dst + a, b - a, w.sign, w.offset);
 		}
 		c->pinned[w.slot].busy = false;
 	}
@@ -163,10 +191,15 @@ int32_t Stager::finish() {
 		if (!nw.n) continue;
 		const size_t bytes = nw.n * nw.bytes_per;
 		void* dn = nullptr;
-		STEVI_TRY(arena_alloc(c_, bytes, &dn));
+		if (nw.final && nw.final_mem == STEVI_DEVICE) dn = nw.final;
+		else STEVI_TRY(arena_alloc(c_, bytes, &dn));
 		const unsigned blocks = (unsigned)((nw.n + 255) / 256);
 		if (nw.bytes_per == 1) STEVI_LAUNCH(c_, k_narrow_index<uint8_t>, blocks, 256, 0, nw.dev, static_cast<uint8_t*>(dn), nw.n, nw.sign, nw.offset);
 		else STEVI_LAUNCH(c_, k_narrow_index<uint16_t>, blocks, 256, 0, nw.dev, static_cast<uint16_t*>(dn), nw.n, nw.sign, nw.offset);
+		if (nw.final) {   // the caller's array is narrow itself
+			if (nw.final_mem != STEVI_DEVICE) STEVI_CUDA(c_, cudaMemcpyAsync(nw.final, dn, bytes, cudaMemcpyDeviceToHost, c_->stream));
+			continue;
+		}
 		// a page-locked staging buffer that no pending task uses
 		size_t slot = c_->pinned.size();
 		for (size_t k = 0; k < c_->pinned.size(); k++)

@@ -1,6 +1,9 @@
-mkdir -p gpurun_out/r2n
-timeout 600 python -m pytest tests/test_gpu_stream.py -m gpu -x -q 2>&1 | tail -5
-timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/r2n/bench_c2.json 2> gpurun_out/r2n/bench_c2.err; tail -3 gpurun_out/r2n/bench_c2.err; python -c "
-import json; l=json.load(open('gpurun_out/r2n/bench_c2.json'))
-print({k:l[k] for k in ('value','ms_per_step','e2e','sustained','roofline','cpu_baseline','gpu_launches')})
-for k,v in l['secondary'].items(): print(k, json.dumps(v)[:900])"
+mkdir -p gpurun_out/r2r
+python bench.py --workload c5 --pairs 1024 --result-dtype u8 > gpurun_out/r2r/c5_1gpu_u8.json 2>/dev/null
+python bench.py --workload c5 --pairs 1024 > gpurun_out/r2r/c5_1gpu_narrowwire.json 2>/dev/null
+python bench.py --workload c5 --pairs 1024 --wide-wire > gpurun_out/r2r/c5_1gpu_widewire.json 2>/dev/null
+for f in gpurun_out/r2r/c5*.json; do python -c "
+import json
+for ln in open('$f'):
+    if ln.startswith('{'):
+        b=json.loads(ln)['batch']; print('$f', round(b['pairs_per_s']), round(b['ms_per_pair_per_gpu'],3), b['pcie_GBps_per_gpu'])"; done
