@@ -170,6 +170,36 @@ STEVI_API int32_t stevi_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const ste
 STEVI_API int32_t stevi_hamming_cost_volume(stevi_ctx* ctx, const stevi_array* feat_l, const stevi_array* feat_r,
 								  int32_t disp_width, int32_t direction, int32_t semantics, stevi_array* out);
 
+/* ---- feature-level forms: callers that bring their own (H,W,F) float feature volumes ---------------------------------- */
+
+/* getFeatureVolumeForMatchFunc<matchFunc>(feature_vol) (correlation/cross_correlations.h:645-722) on a ready-made volume:
+ * feat (H,W,F) f32 -> out (H,W,F) f32 = v | v-mean | v/norm | (v-mean)/norm per the function's traits (CC..ZSAD). */
+STEVI_API int32_t stevi_features_for_matchfunc(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat, stevi_array* out);
+
+/* aggregateCost<matchFunc, float, float, dDir, float> (correlation/cross_correlations.h:194-249) and its searchOffset<1> overload
+ * (:251-308): feat_l (H,Wl,F), feat_r (H,Wr,F) f32 -> out (H,Wsource,upper-lower+1) f32, cell d compares the source vector with the
+ * target vector lower + d columns away (zero features outside the target image). The disp_width overload is lower = 0,
+ * upper = disp_width - 1. The features are taken as they are (apply stevi_features_for_matchfunc first where the function wants it). */
+STEVI_API int32_t stevi_aggregate_cost(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_l, const stevi_array* feat_r,
+							 int32_t lower_offset, int32_t upper_offset, int32_t direction, stevi_array* out);
+
+/* featureVolume2CostVolume<matchFunc> (correlation/cross_correlations.h:724-738): getFeatureVolumeForMatchFunc of both volumes, then
+ * aggregateCost. feat_l, feat_r (H,W*,F) f32 (raw unfolded features) -> out (H,Wsource,D): f32 for CC..ZSAD; u16|i32|f32 for CENSUS
+ * (censusFeatures + Hamming distances, :712-714). */
+STEVI_API int32_t stevi_feature_volume_to_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_l, const stevi_array* feat_r,
+											int32_t disp_width, int32_t direction, int32_t semantics, stevi_array* out);
+
+/* unfoldBasedCostVolume(img_l, img_r, UnFoldCompressor const&, disp_width) (correlation/cross_correlations.h:767-791): mask (mh,mw)
+ * i32 in HOST memory (as for stevi_unfold_compressed); images (H,W) or (H,W,C) u8|f32. */
+STEVI_API int32_t stevi_cost_volume_compressed(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* mask, const stevi_array* img_l,
+									 const stevi_array* img_r, int32_t disp_width, int32_t direction, int32_t semantics, stevi_array* out);
+
+/* unfoldBasedCostVolume<matchFunc, T_L, T_R, 3, ...> (correlation/cross_correlations.h:740-765 over the 3-D image unfold,
+ * unfold.h:293-344): img_l, img_r (H,W,C) u8|f32 with equal channel counts. */
+STEVI_API int32_t stevi_cost_volume_multichannel(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+									   int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction, int32_t semantics,
+									   stevi_array* out);
+
 /* ---- semi-global matching -------------------------------------------------------------------------------- */
 
 /* sgmCostVolume<nDirections, strategy, T_CV> (correlation/sgm.h:360-404). cv (H,W,D) u16|f32 -> out (H,W,D) f32.

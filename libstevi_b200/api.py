@@ -329,6 +329,84 @@ def hammingCostVolume(feat_l, feat_r, disp_width, dDir=RIGHT_TO_LEFT, TCV=np.uin
     return out
 
 
+def getFeatureVolumeForMatchFuncFromFeatures(matchFunc, feature_vol, ctx=None):
+    """getFeatureVolumeForMatchFunc<matchFunc>(feature_vol) on a ready-made (H,W,F) f32 volume, cross_correlations.h:645-722."""
+    ctx = _ctx_for(ctx, feature_vol)
+    out = _empty(feature_vol, feature_vol.shape, np.float32)
+    a, o = describe(feature_vol), describe(out)
+    ctx.check(lib.stevi_features_for_matchfunc(ctx.handle, matchFunc, ctypes.byref(a), ctypes.byref(o)))
+    return out
+
+
+def aggregateCost(matchFunc, feat_l, feat_r, disp_width=None, searchRange=None, dDir=RIGHT_TO_LEFT, layout="ref", ctx=None):
+    """aggregateCost on processed float feature volumes, cross_correlations.h:194-249; ``searchRange=(lower, upper)`` is the
+    searchOffset<1> overload (:251-308). Returns None where the reference returns an empty array."""
+    ctx = _ctx_for(ctx, feat_l)
+    lower, upper = (0, disp_width - 1) if searchRange is None else searchRange
+    ws = feat_r.shape[1] if dDir == RIGHT_TO_LEFT else feat_l.shape[1]
+    if upper < lower:
+        return None
+    out = _empty(feat_l, (feat_l.shape[0], ws, upper - lower + 1), np.float32, _volume_order(layout))
+    l, r, o = describe(feat_l), describe(feat_r), describe(out)
+    rc = lib.stevi_aggregate_cost(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), lower, upper, dDir, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def featureVolume2CostVolume(matchFunc, feature_vol_l, feature_vol_r, disp_width, dDir=RIGHT_TO_LEFT, TCV=None, semantics=COMPAT,
+                             layout="ref", ctx=None):
+    """cross_correlations.h:724-738: getFeatureVolumeForMatchFunc of both volumes, then aggregateCost."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    if TCV is None:
+        TCV = np.uint16 if matchFunc in (CENSUS, HAMMING) else np.float32
+    ws = feature_vol_r.shape[1] if dDir == RIGHT_TO_LEFT else feature_vol_l.shape[1]
+    out = _empty(feature_vol_l, (feature_vol_l.shape[0], ws, disp_width), TCV, _volume_order(layout))
+    l, r, o = describe(feature_vol_l), describe(feature_vol_r), describe(out)
+    rc = lib.stevi_feature_volume_to_cost_volume(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), disp_width, dDir, semantics,
+                                                 ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def unfoldBasedCostVolumeCompressed(matchFunc, img_l, img_r, compressor_mask, disp_width, dDir=RIGHT_TO_LEFT, TCV=None,
+                                    semantics=COMPAT, layout="ref", ctx=None):
+    """unfoldBasedCostVolume(img_l, img_r, UnFoldCompressor(mask), disp_width), cross_correlations.h:767-791. Images (H,W) or (H,W,C)."""
+    ctx = _ctx_for(ctx, img_l)
+    if TCV is None:
+        TCV = np.uint16 if matchFunc in (CENSUS, HAMMING) else np.float32
+    mask = np.ascontiguousarray(compressor_mask, np.int32)
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    out = _empty(img_l, (img_l.shape[0], ws, disp_width), TCV, _volume_order(layout))
+    m, l, r, o = describe(mask), describe(img_l), describe(img_r), describe(out)
+    rc = lib.stevi_cost_volume_compressed(ctx.handle, matchFunc, ctypes.byref(m), ctypes.byref(l), ctypes.byref(r), disp_width, dDir,
+                                          semantics, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def unfoldBasedCostVolumeMultiChannel(matchFunc, img_l, img_r, h_radius, v_radius, disp_width, dDir=RIGHT_TO_LEFT, TCV=None,
+                                      semantics=COMPAT, layout="ref", ctx=None):
+    """unfoldBasedCostVolume<matchFunc, T, T, 3> on (H,W,C) images, cross_correlations.h:740-765 with unfold.h:293-344."""
+    ctx = _ctx_for(ctx, img_l)
+    if TCV is None:
+        TCV = np.uint16 if matchFunc in (CENSUS, HAMMING) else np.float32
+    ws = img_r.shape[1] if dDir == RIGHT_TO_LEFT else img_l.shape[1]
+    out = _empty(img_l, (img_l.shape[0], ws, disp_width), TCV, _volume_order(layout))
+    l, r, o = describe(img_l), describe(img_r), describe(out)
+    rc = lib.stevi_cost_volume_multichannel(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, disp_width,
+                                            dDir, semantics, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
 def sgmCostVolume(cv, P1, P2, margins=(0, 0, 0, 0), Pout=100.0, nDirections=8, strategy=COST, semantics=COMPAT,
                   layout="same", ctx=None):
     """sgm.h:360-404. margins = (left, top, right, bottom) like StereoVision::Margins' 4-argument constructor."""

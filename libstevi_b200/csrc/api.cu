@@ -1,5 +1,7 @@
 // extern "C" entry points (include/stevi_b200/c_api.h): argument checks, staging of host operands, stage chaining.
 #include "common.cuh"
+#include <algorithm>
+#include <vector>
 #include "kernels.cuh"
 #include <cmath>
 
@@ -106,6 +108,127 @@ int32_t stevi_hamming_cost_volume(stevi_ctx* c, const stevi_array* fl, const ste
 	STEVI_TRY(st.out(out, vo, "out"));
 	if (vl.ndim != 3) return fail(c, STEVI_E_SHAPE, "hamming: features must be 3-D");
 	STEVI_TRY(hamming_cv_dev(c, vl, vr, vl.shape[2], D, direction, semantics == STEVI_COMPAT, vo, nullptr, 0));
+	return st.finish();
+}
+
+int32_t stevi_features_for_matchfunc(stevi_ctx* c, int32_t mf, const stevi_array* feat, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(feat, vi, "feat"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(features_for_matchfunc_dev(c, mf, vi, vo));
+	return st.finish();
+}
+
+int32_t stevi_aggregate_cost(stevi_ctx* c, int32_t mf, const stevi_array* fl, const stevi_array* fr, int32_t lower, int32_t upper,
+							 int32_t direction, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(aggregate_cost_dev(c, mf, vl, vr, lower, upper - lower + 1, direction, vo));
+	return st.finish();
+}
+
+namespace stevi {
+// a workspace (H,W,F) f32 volume in C order
+static int32_t ws_volume(stevi_ctx* c, int H, int W, int F, int dtype, View& v) {
+	void* p = nullptr;
+	STEVI_TRY(arena_alloc(c, (size_t)H * W * F * dtype_size(dtype), &p));
+	v.p = p; v.dtype = dtype; v.ndim = 3;
+	v.shape[0] = H; v.shape[1] = W; v.shape[2] = F;
+	v.st[0] = (int64_t)W * F; v.st[1] = F; v.st[2] = 1;
+	return STEVI_OK;
+}
+
+// featureVolume2CostVolume (cross_correlations.h:724-738) on device views: features of both volumes, then aggregateCost
+static int32_t feature_volumes_to_cv(stevi_ctx* c, int mf, const View& fl, const View& fr, int D, int direction, int semantics, const View& out) {
+	if (fl.ndim != 3 || fr.ndim != 3) return fail(c, STEVI_E_SHAPE, "feature volumes must be (H,W,F)");
+	if (fl.shape[0] != fr.shape[0] || fl.shape[2] != fr.shape[2])
+		return fail(c, STEVI_E_SHAPE, "feature volumes disagree in height or feature count (cross_correlations.h:751-759)");
+	if (mf == STEVI_MF_CENSUS) {   // :712-714: census bit strings, then the Hamming volume
+		const int nw = (fl.shape[2] - 1) / 32 + 1;
+		View cl, cr;
+		STEVI_TRY(ws_volume(c, fl.shape[0], fl.shape[1], nw, STEVI_U32, cl));
+		STEVI_TRY(ws_volume(c, fr.shape[0], fr.shape[1], nw, STEVI_U32, cr));
+		STEVI_TRY(census_features_dev(c, fl, semantics & 1, cl));
+		STEVI_TRY(census_features_dev(c, fr, semantics & 1, cr));
+		return hamming_cv_dev(c, cl, cr, nw, D, direction, (semantics & 1) == STEVI_COMPAT, out, nullptr, 0);
+	}
+	View gl, gr;
+	STEVI_TRY(ws_volume(c, fl.shape[0], fl.shape[1], fl.shape[2], STEVI_F32, gl));
+	STEVI_TRY(ws_volume(c, fr.shape[0], fr.shape[1], fr.shape[2], STEVI_F32, gr));
+	STEVI_TRY(features_for_matchfunc_dev(c, mf, fl, gl));
+	STEVI_TRY(features_for_matchfunc_dev(c, mf, fr, gr));
+	return aggregate_cost_dev(c, mf, gl, gr, 0, D, direction, out);
+}
+} // namespace stevi
+
+int32_t stevi_feature_volume_to_cost_volume(stevi_ctx* c, int32_t mf, const stevi_array* fl, const stevi_array* fr, int32_t D,
+											int32_t direction, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	if (vl.dtype != STEVI_F32 || vr.dtype != STEVI_F32) return fail(c, STEVI_E_DTYPE, "feature_volume_to_cost_volume: feature volumes must be f32");
+	STEVI_TRY(feature_volumes_to_cv(c, mf, vl, vr, D, direction, semantics, vo));
+	return st.finish();
+}
+
+int32_t stevi_cost_volume_compressed(stevi_ctx* c, int32_t mf, const stevi_array* mask, const stevi_array* l, const stevi_array* r,
+									 int32_t D, int32_t direction, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	if (!mask || !mask->data || mask->mem != STEVI_HOST || mask->ndim != 2 || mask->dtype != STEVI_I32)
+		return fail(c, STEVI_E_ARG, "cost_volume_compressed: mask must be a 2-D i32 array in host memory");
+	Stager st(c);
+	View vl, vr, vo;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr, "img_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	if (vl.ndim != vr.ndim || (vl.ndim != 2 && vl.ndim != 3)) return fail(c, STEVI_E_SHAPE, "cost_volume_compressed: images must both be (H,W) or (H,W,C)");
+	// number of features = number of distinct positive labels (UnFoldCompressor, unfold.h:36-137)
+	const int32_t* m = static_cast<const int32_t*>(mask->data);
+	std::vector<int32_t> labels;
+	for (int a = 0; a < mask->shape[0]; a++)
+		for (int b = 0; b < mask->shape[1]; b++) {
+			const int32_t v = m[a * mask->strides[0] + b * mask->strides[1]];
+			if (v > 0 && std::find(labels.begin(), labels.end(), v) == labels.end()) labels.push_back(v);
+		}
+	const int C = vl.ndim == 3 ? vl.shape[2] : 1;
+	if (vr.ndim == 3 && vr.shape[2] != C) return fail(c, STEVI_E_SHAPE, "cost_volume_compressed: channel counts differ (cross_correlations.h:775-777)");
+	const int F = (int)labels.size() * C;
+	View fl, fr;
+	STEVI_TRY(ws_volume(c, vl.shape[0], vl.shape[1], F, STEVI_F32, fl));
+	STEVI_TRY(ws_volume(c, vr.shape[0], vr.shape[1], F, STEVI_F32, fr));
+	STEVI_TRY(unfold_compressed_dev(c, m, mask->shape[0], mask->shape[1], mask->strides[0], mask->strides[1], vl, nullptr, fl));
+	STEVI_TRY(unfold_compressed_dev(c, m, mask->shape[0], mask->shape[1], mask->strides[0], mask->strides[1], vr, nullptr, fr));
+	STEVI_TRY(feature_volumes_to_cv(c, mf, fl, fr, D, direction, semantics, vo));
+	return st.finish();
+}
+
+int32_t stevi_cost_volume_multichannel(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr_,
+									   int32_t D, int32_t direction, int32_t semantics, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vo;
+	STEVI_TRY(st.in(l, vl, "img_l"));
+	STEVI_TRY(st.in(r, vr, "img_r"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	if (vl.ndim != 3 || vr.ndim != 3) return fail(c, STEVI_E_SHAPE, "cost_volume_multichannel: images must be (H,W,C)");
+	if (vl.shape[2] != vr.shape[2]) return fail(c, STEVI_E_SHAPE, "cost_volume_multichannel: channel counts differ (cross_correlations.h:755-759)");
+	if (hr < 0 || vr_ < 0 || hr > 127 || vr_ > 127) return fail(c, STEVI_E_ARG, "cost_volume_multichannel: radii");
+	const int F = (2 * hr + 1) * (2 * vr_ + 1) * vl.shape[2];
+	View fl, fr;
+	STEVI_TRY(ws_volume(c, vl.shape[0], vl.shape[1], F, STEVI_F32, fl));
+	STEVI_TRY(ws_volume(c, vr.shape[0], vr.shape[1], F, STEVI_F32, fr));
+	STEVI_TRY(unfold_dev(c, vl, hr, vr_, nullptr, 0, fl));   // unfold.h:293-344 (3-D image overload), automatic padding
+	STEVI_TRY(unfold_dev(c, vr, hr, vr_, nullptr, 0, fr));
+	STEVI_TRY(feature_volumes_to_cv(c, mf, fl, fr, D, direction, semantics, vo));
 	return st.finish();
 }
 

@@ -57,6 +57,11 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 // costvol.cu: 2-D search cost volume, search = {lower0, upper0, lower1, upper1}, out (H,W,dH,dW) f32
 int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const int32_t* search, int direction, const View& out);
 
+// features_cv.cu: feature-level forms (caller-supplied float feature volumes)
+int32_t features_for_matchfunc_dev(stevi_ctx* c, int mf, const View& in, const View& out);
+// cv(i,j,d) = compare(source(i,j,.), target(i, j + sign*(d + lower), .)), d < D
+int32_t aggregate_cost_dev(stevi_ctx* c, int mf, const View& fl, const View& fr, int lower, int D, int direction, const View& out);
+
 // wta.cu
 int32_t wta2d_dev(stevi_ctx* c, const View& vol, int strategy, const View& out);
 int32_t index2d_to_disp_dev(stevi_ctx* c, const View& idx, const int32_t* search, const View& out);

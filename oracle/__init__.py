@@ -151,6 +151,58 @@ class _Checker:
                                             h, wl, wr, hr, vr, D, direction, _p(out))
         return out if rc == 0 else None
 
+    # --- feature-level forms (caller-supplied float feature volumes) --------------------
+    def features_for_matchfunc(self, mf, fv):
+        fv = _c(fv, np.float32)
+        h, w, F = fv.shape
+        out = np.empty((h, w, F), np.float32)
+        rc = self._f("features_for_matchfunc_f32")(mf, _p(fv), h, w, F, _p(out))
+        assert rc == 0
+        return out
+
+    def aggregate_cost(self, mf, fl, fr, lower, upper, direction=R2L):
+        """aggregateCost (searchOffset<1>(lower, upper) overload) on processed features; None where the reference returns empty."""
+        fl, fr = _c(fl, np.float32), _c(fr, np.float32)
+        h, wl, F = fl.shape
+        if fr.shape[0] != h or upper < lower:
+            return None
+        wr = fr.shape[1]
+        out = np.empty((h, wr if direction == R2L else wl, upper - lower + 1), np.float32)
+        rc = self._f("aggregate_cost_f32")(mf, _p(fl), _p(fr), h, wl, wr, F, lower, upper, direction, _p(out))
+        return out if rc == 0 else None
+
+    def feature_volume_to_cost_volume(self, mf, fl, fr, D, direction=R2L):
+        if self.has("feature_volume_to_cost_volume_f32"):   # the compiled reference has the template itself
+            fl, fr = _c(fl, np.float32), _c(fr, np.float32)
+            h, wl, F = fl.shape
+            wr = fr.shape[1]
+            out = np.empty((h, wr if direction == R2L else wl, D), np.float32)
+            rc = self._f("feature_volume_to_cost_volume_f32")(mf, _p(fl), _p(fr), h, wl, wr, F, D, direction, _p(out))
+            return out if rc == 0 else None
+        return self.aggregate_cost(mf, self.features_for_matchfunc(mf, fl), self.features_for_matchfunc(mf, fr), 0, D - 1, direction)
+
+    def cost_volume_compressed(self, mf, mask, left, right, D, direction=R2L):
+        if self.has("cost_volume_compressed_f32"):
+            left, right, mask = _c(left, np.float32), _c(right, np.float32), _c(mask, np.int32)
+            h, wl = left.shape[:2]
+            wr = right.shape[1]
+            c = left.shape[2] if left.ndim == 3 else 0
+            out = np.empty((h, wr if direction == R2L else wl, D), np.float32)
+            rc = self._f("cost_volume_compressed_f32")(mf, _p(mask), mask.shape[0], mask.shape[1], _p(left), _p(right), h, wl, wr, c,
+                                                       D, direction, _p(out))
+            return out if rc == 0 else None
+        return self.feature_volume_to_cost_volume(mf, self.unfold_compressed(mask, left), self.unfold_compressed(mask, right), D, direction)
+
+    def cost_volume_multichannel(self, mf, left, right, hr, vr, D, direction=R2L):
+        if self.has("cost_volume_multichannel_f32"):
+            left, right = _c(left, np.float32), _c(right, np.float32)
+            h, wl, c = left.shape
+            wr = right.shape[1]
+            out = np.empty((h, wr if direction == R2L else wl, D), np.float32)
+            rc = self._f("cost_volume_multichannel_f32")(mf, _p(left), _p(right), h, wl, wr, c, hr, vr, D, direction, _p(out))
+            return out if rc == 0 else None
+        return self.feature_volume_to_cost_volume(mf, self.unfold_general(left, hr, vr), self.unfold_general(right, hr, vr), D, direction)
+
     def cost_volume_2d(self, mf, left, right, hr, vr, search, direction=R2L):
         """unfoldBased2dDisparityCostVolume with searchOffset<2>(*search), search = (lower0, upper0, lower1, upper1);
         (h, w, dH, dW) float32, None where the reference returns an empty array."""

@@ -116,6 +116,62 @@ int hier_d(const float* l, const float* r, int h, int w, int hr, int vr, int D, 
 
 } // namespace
 
+template<matchingFunctions F>
+int agg_dir(const float* l, const float* r, int h, int wl, int wr, int f, int lower, int upper, int dir, float* out) {
+	auto L = view3(l, h, wl, f);
+	auto R = view3(r, h, wr, f);
+	searchOffset<1> range(lower, upper);
+	MD::Array<float, 3> cv = dir == int(dispDirection::RightToLeft)
+		? aggregateCost<F, float, float, dispDirection::RightToLeft, float>(L, R, range)
+		: aggregateCost<F, float, float, dispDirection::LeftToRight, float>(L, R, range);
+	if (cv.empty()) return 1;
+	out3(cv, out);
+	return 0;
+}
+
+template<matchingFunctions F>
+int fv2cv_dir(const float* l, const float* r, int h, int wl, int wr, int f, int D, int dir, float* out) {
+	auto L = view3(l, h, wl, f);
+	auto R = view3(r, h, wr, f);
+	MD::Array<float, 3> cv = dir == int(dispDirection::RightToLeft)
+		? featureVolume2CostVolume<F, float, float, disp_t, dispDirection::RightToLeft, float>(L, R, disp_t(D))
+		: featureVolume2CostVolume<F, float, float, disp_t, dispDirection::LeftToRight, float>(L, R, disp_t(D));
+	if (cv.empty()) return 1;
+	out3(cv, out);
+	return 0;
+}
+
+template<matchingFunctions F, int ND>
+int cv_comp_dir(const int* mask, int mh, int mw, const float* l, const float* r, int h, int wl, int wr, int c, int D, int dir, float* out) {
+	UnFoldCompressor comp(view2(mask, mh, mw));
+	MD::Array<float, 3> cv;
+	if constexpr (ND == 2) {
+		auto L = view2(l, h, wl); auto R = view2(r, h, wr);
+		cv = dir == int(dispDirection::RightToLeft)
+			? unfoldBasedCostVolume<F, float, float, 2, dispDirection::RightToLeft, float>(L, R, comp, D)
+			: unfoldBasedCostVolume<F, float, float, 2, dispDirection::LeftToRight, float>(L, R, comp, D);
+	} else {
+		auto L = view3(l, h, wl, c); auto R = view3(r, h, wr, c);
+		cv = dir == int(dispDirection::RightToLeft)
+			? unfoldBasedCostVolume<F, float, float, 3, dispDirection::RightToLeft, float>(L, R, comp, D)
+			: unfoldBasedCostVolume<F, float, float, 3, dispDirection::LeftToRight, float>(L, R, comp, D);
+	}
+	if (cv.empty()) return 1;
+	out3(cv, out);
+	return 0;
+}
+
+template<matchingFunctions F>
+int cv3_dir(const float* l, const float* r, int h, int wl, int wr, int c, int hr, int vr, int D, int dir, float* out) {
+	auto L = view3(l, h, wl, c); auto R = view3(r, h, wr, c);
+	MD::Array<float, 3> cv = dir == int(dispDirection::RightToLeft)
+		? unfoldBasedCostVolume<F, float, float, 3, dispDirection::RightToLeft, float>(L, R, uint8_t(hr), uint8_t(vr), D)
+		: unfoldBasedCostVolume<F, float, float, 3, dispDirection::LeftToRight, float>(L, R, uint8_t(hr), uint8_t(vr), D);
+	if (cv.empty()) return 1;
+	out3(cv, out);
+	return 0;
+}
+
 extern "C" {
 
 int ref_num_threads() { return omp_get_max_threads(); }
@@ -207,6 +263,61 @@ int ref_cost_volume_u8(int matchfunc, const uint8_t* l, const uint8_t* r, int h,
 	case matchingFunctions::SAD: return cv_dir<matchingFunctions::SAD>(l, r, h, w, wr, hr, vr, D, dir, out);
 	default: return 2;
 	}
+}
+
+// ---- feature-level forms: the reference templates on caller-supplied float feature volumes -----------------------------------
+#define STEVI_MF_SWITCH(CALL) \
+	switch (matchingFunctions(matchfunc)) { \
+	case matchingFunctions::CC: CALL(matchingFunctions::CC); break; \
+	case matchingFunctions::NCC: CALL(matchingFunctions::NCC); break; \
+	case matchingFunctions::SSD: CALL(matchingFunctions::SSD); break; \
+	case matchingFunctions::SAD: CALL(matchingFunctions::SAD); break; \
+	case matchingFunctions::ZCC: CALL(matchingFunctions::ZCC); break; \
+	case matchingFunctions::ZNCC: CALL(matchingFunctions::ZNCC); break; \
+	case matchingFunctions::ZSSD: CALL(matchingFunctions::ZSSD); break; \
+	case matchingFunctions::ZSAD: CALL(matchingFunctions::ZSAD); break; \
+	default: return 2; }
+
+// cross_correlations.h:645-722
+int ref_features_for_matchfunc_f32(int matchfunc, const float* fv, int h, int w, int F, float* out) {
+	auto V = view3(fv, h, w, F);
+#define CALL(MF) out3(getFeatureVolumeForMatchFunc<MF>(V), out)
+	STEVI_MF_SWITCH(CALL)
+#undef CALL
+	return 0;
+}
+
+// cross_correlations.h:251-308 (searchOffset<1> overload; lower = 0, upper = disp_width - 1 is the disp_width overload :194-249)
+int ref_aggregate_cost_f32(int matchfunc, const float* fl, const float* fr, int h, int wl, int wr, int F, int lower, int upper, int dir, float* out) {
+#define CALL(MF) return agg_dir<MF>(fl, fr, h, wl, wr, F, lower, upper, dir, out)
+	STEVI_MF_SWITCH(CALL)
+#undef CALL
+	return 0;
+}
+
+// cross_correlations.h:724-738
+int ref_feature_volume_to_cost_volume_f32(int matchfunc, const float* fl, const float* fr, int h, int wl, int wr, int F, int D, int dir, float* out) {
+#define CALL(MF) return fv2cv_dir<MF>(fl, fr, h, wl, wr, F, D, dir, out)
+	STEVI_MF_SWITCH(CALL)
+#undef CALL
+	return 0;
+}
+
+// cross_correlations.h:767-791: the UnFoldCompressor overload of unfoldBasedCostVolume; c = 0: (h,w) images, else (h,w,c)
+int ref_cost_volume_compressed_f32(int matchfunc, const int* mask, int mh, int mw, const float* l, const float* r, int h, int wl, int wr, int c,
+								   int D, int dir, float* out) {
+#define CALL(MF) return c == 0 ? cv_comp_dir<MF, 2>(mask, mh, mw, l, r, h, wl, wr, c, D, dir, out) : cv_comp_dir<MF, 3>(mask, mh, mw, l, r, h, wl, wr, c, D, dir, out)
+	STEVI_MF_SWITCH(CALL)
+#undef CALL
+	return 0;
+}
+
+// cross_correlations.h:740-765 with nImDim = 3 (multi-channel images)
+int ref_cost_volume_multichannel_f32(int matchfunc, const float* l, const float* r, int h, int wl, int wr, int c, int hr, int vr, int D, int dir, float* out) {
+#define CALL(MF) return cv3_dir<MF>(l, r, h, wl, wr, c, hr, vr, D, dir, out)
+	STEVI_MF_SWITCH(CALL)
+#undef CALL
+	return 0;
 }
 
 // cross_correlations.h:794-822: 2-D search cost volume, float images of equal size. so = {lower0, upper0, lower1, upper1}

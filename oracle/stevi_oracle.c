@@ -237,6 +237,33 @@ int orc_cost_volume_f32(int mf, const float* l, const float* r, int h, int wl, i
 	return 0;
 }
 
+/* ---- feature-level forms ------------------------------------------------------------------------------------------------
+ * cross_correlations.h:645-722 getFeatureVolumeForMatchFunc on a ready-made (h, w, F) float volume (copy, then in place) */
+int orc_features_for_matchfunc_f32(int mf, const float* fv, int h, int w, int F, float* out) {
+	memcpy(out, fv, (size_t)h * w * F * sizeof(float));
+	features_inplace(mf, out, (size_t)h * w, F);
+	return 0;
+}
+
+/* cross_correlations.h:194-249 aggregateCost and its searchOffset<1> overload (:251-308) on processed feature volumes
+ * fl (h, wl, F), fr (h, wr, F): cell d compares the source vector with the target vector `lower + d` columns away
+ * (idx2disp, correlation_base.h:288-409), zero features outside the target image. out (h, w_source, upper - lower + 1). */
+int orc_aggregate_cost_f32(int mf, const float* fl, const float* fr, int h, int wl, int wr, int F, int lower, int upper, int dir, float* out) {
+	const float* src = dir == DIR_R2L ? fr : fl; int ws = dir == DIR_R2L ? wr : wl;
+	const float* tgt = dir == DIR_R2L ? fl : fr; int wt = dir == DIR_R2L ? wl : wr;
+	int sgn = dir == DIR_R2L ? 1 : -1, D = upper - lower + 1;
+	if (D < 1) return 1;
+	float* zero = (float*)calloc((size_t)F, sizeof(float));
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) for (int j = 0; j < ws; j++) for (int d = 0; d < D; d++) {
+		int jt = j + sgn * (d + lower);
+		const float* t = (jt >= 0 && jt < wt) ? tgt + ((size_t)i * wt + jt) * F : zero;
+		out[((size_t)i * ws + j) * D + d] = compare_f32(mf, src + ((size_t)i * ws + j) * F, t, F);
+	}
+	free(zero);
+	return 0;
+}
+
 /* ---- cross_correlations.h:308-371 aggregateCost over searchOffset<2> + :794-822 unfoldBased2dDisparityCostVolume, float
  * images of equal size (the reference returns an empty array otherwise, :804-810). so = {lower0, upper0, lower1, upper1}:
  * axis 0 = rows, axis 1 = columns (correlation_base.h:299-315). The target pixel of cell (i, j, dh, dw) is
