@@ -101,6 +101,46 @@ Multidim::Array<T_O, 3> unfold(UnFoldCompressor const& compressor, Multidim::Arr
 	return out;
 }
 
+// The two super-pixel masks the reference ships for UnFoldCompressor (unfold.h:476-691): 17 super-pixels over a 7x7 / 9x9
+// window. Data, kept as tables (checked against the reference's functions by tests/test_facade.py).
+namespace CompressorGenerators {
+
+namespace Detail {
+inline Multidim::Array<int, 2> maskFromTable(const int* t, int n) {
+	Multidim::Array<int, 2> out(n, n);
+	for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) out.atUnchecked(i, j) = t[i * n + j];
+	return out;
+}
+} // namespace Detail
+
+inline Multidim::Array<int, 2> GrPix17R3Filter() {
+	static const int t[49] = {
+		14, 14, 10, 10, 10, 16, 16,
+		14, 14,  6,  4,  7, 16, 16,
+		11,  6,  6,  4,  7,  7, 13,
+		11,  2,  2,  1,  3,  3, 13,
+		11,  8,  8,  5,  9,  9, 13,
+		15, 15,  8,  5,  9, 17, 17,
+		15, 15, 12, 12, 12, 17, 17};
+	return Detail::maskFromTable(t, 7);
+}
+
+inline Multidim::Array<int, 2> GrPix17R4Filter() {
+	static const int t[81] = {
+		14, 14, 14, 10, 10, 10, 16, 16, 16,
+		14, 14, 14, 10, 10, 10, 16, 16, 16,
+		14, 14,  6,  6,  4,  7,  7, 16, 16,
+		11, 11,  6,  6,  4,  7,  7, 13, 13,
+		11, 11,  2,  2,  1,  3,  3, 13, 13,
+		11, 11,  8,  8,  5,  9,  9, 13, 13,
+		15, 15,  8,  8,  5,  9,  9, 17, 17,
+		15, 15, 15, 12, 12, 12, 17, 17, 17,
+		15, 15, 15, 12, 12, 12, 17, 17, 17};
+	return Detail::maskFromTable(t, 9);
+}
+
+} // namespace CompressorGenerators
+
 } // namespace Correlation
 } // namespace StereoVision
 

@@ -358,6 +358,22 @@ STEVI_API int32_t stevi_local_matching_pipeline(stevi_ctx* ctx, int32_t matchfun
 									  int32_t kernel, stevi_array* cv_out, stevi_array* idx_out, stevi_array* tcv_out,
 									  stevi_array* refined);
 
+/* ---- batches of independent pairs over several contexts / devices ---------------------------------------------------- */
+
+/* One stereo pair of a batch: images and result as for stevi_census_sgm_pipeline (host or device memory; page-locked host memory
+ * lets the copies overlap the kernels). */
+typedef struct { const stevi_array* img_l; const stevi_array* img_r; stevi_array* disp; } stevi_pair;
+
+/* stevi_census_sgm_pipeline (disparity map only) over n_pairs independent pairs, the loop of
+ * test/benchmarks/benchmarkCostVolumeWorkflow.cpp:175-260 with the calls left in flight. ctxs: n_ctx contexts, each with its own
+ * stream (stevi_ctx_create(device, NULL, ..)); several contexts on one device = that many pairs in flight there (3-4 hide the
+ * copies), contexts on different devices run side by side, one host thread per device inside the call. Pair k goes to device
+ * group k mod (number of devices among ctxs). Returns when every result is in place; the first failure (its text in the
+ * failing context's stevi_last_error) stops the batch. No collective is involved: the pairs are independent. */
+STEVI_API int32_t stevi_batch_census_sgm(stevi_ctx* const* ctxs, int32_t n_ctx, const stevi_pair* pairs, int32_t n_pairs,
+							   int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction, int32_t n_directions,
+							   float P1, float P2, float Pout, const stevi_margins* margins, int32_t semantics);
+
 #ifdef __cplusplus
 }
 #endif

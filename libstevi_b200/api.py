@@ -570,6 +570,29 @@ def censusSgmPipeline(img_l, img_r, h_radius, v_radius, disp_width, P1, P2, Pout
     return disp
 
 
+class StPair(ctypes.Structure):
+    _fields_ = [("img_l", ctypes.POINTER(StArray)), ("img_r", ctypes.POINTER(StArray)), ("disp", ctypes.POINTER(StArray))]
+
+
+def batchCensusSgm(ctxs, pairs, h_radius, v_radius, disp_width, P1, P2, Pout=100.0, nDirections=8, margins=(0, 0, 0, 0),
+                   dDir=RIGHT_TO_LEFT, semantics=COMPAT):
+    """stevi_batch_census_sgm: ``pairs`` = [(img_l, img_r, disp_out)], ``ctxs`` = contexts (own streams) on one or several devices;
+    the library keeps one pair in flight per context and drives every device from its own host thread. Results land in disp_out."""
+    n = len(pairs)
+    descs = [(describe(l), describe(r), describe(d)) for l, r, d in pairs]
+    arr = (StPair * max(n, 1))()
+    for k, (l, r, d) in enumerate(descs):
+        arr[k].img_l, arr[k].img_r, arr[k].disp = ctypes.pointer(l), ctypes.pointer(r), ctypes.pointer(d)
+    hs = (ctypes.c_void_p * len(ctxs))(*[c.handle for c in ctxs])
+    m = StMargins(*[int(v) for v in margins])
+    f32 = ctypes.c_float
+    rc = lib.stevi_batch_census_sgm(hs, len(ctxs), arr, n, h_radius, v_radius, disp_width, dDir, nDirections, f32(P1), f32(P2), f32(Pout),
+                                    ctypes.byref(m), semantics)
+    if rc != OK:
+        texts = [lib.stevi_last_error(c.handle).decode() for c in ctxs]
+        raise SteviError(rc, "; ".join(t for t in texts if t))
+
+
 def selectedCost(cv, idx, ctx=None):
     """correlation_base.h:557-577: out(i,j) = cv(i,j,idx(i,j))."""
     ctx = _ctx_for(ctx, cv)

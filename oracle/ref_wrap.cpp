@@ -265,6 +265,14 @@ int ref_cost_volume_u8(int matchfunc, const uint8_t* l, const uint8_t* r, int h,
 	}
 }
 
+// unfold.h:476-691: the two super-pixel masks the reference ships for UnFoldCompressor. radius 3 -> 7x7, radius 4 -> 9x9.
+int ref_grpix17_filter(int radius, int* out) {
+	MD::Array<int, 2> m = radius == 3 ? CompressorGenerators::GrPix17R3Filter() : CompressorGenerators::GrPix17R4Filter();
+	const int n = 2 * radius + 1;
+	for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) out[i * n + j] = m.value<MD::AccessCheck::Nocheck>(i, j);
+	return 0;
+}
+
 // ---- feature-level forms: the reference templates on caller-supplied float feature volumes -----------------------------------
 #define STEVI_MF_SWITCH(CALL) \
 	switch (matchingFunctions(matchfunc)) { \

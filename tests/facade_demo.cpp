@@ -67,6 +67,25 @@ int main() {
 	auto even2 = refineDisp2dCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 4>(h, w, 3, 4), d2);
 	std::printf("even_side_empty %d\n", int(even2.empty()));
 
+	// feature-level forms: compressed unfold (the shipped 17-super-pixel mask), multi-channel images, aggregateCost on features
+	UnFoldCompressor comp(CompressorGenerators::GrPix17R3Filter());
+	auto ccv = unfoldBasedCostVolume<matchingFunctions::ZNCC, float, float>(lf, rf, comp, D);
+	auto cidx = extractSelectedIndex<dispExtractionStartegy::Score>(ccv);
+	int goodc = 0, nc = 0;
+	for (int i = 5; i < h - 5; i++) for (int j = 5; j < w - 24; j++) { nc++; goodc += cidx.valueUnchecked(i, j) == 5; }
+	std::printf("compressed_features %d\ncompressed_match %.3f\ncompressed_cv %.4f\n", comp.nFeatures(), double(goodc) / nc, checksum(ccv));
+	Multidim::Array<float, 3> l3(h, w, 2), r3(h, w, 2);
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		l3.atUnchecked(i, j, 0) = lf.valueUnchecked(i, j); l3.atUnchecked(i, j, 1) = 1.f - lf.valueUnchecked(i, j);
+		r3.atUnchecked(i, j, 0) = rf.valueUnchecked(i, j); r3.atUnchecked(i, j, 1) = 1.f - rf.valueUnchecked(i, j);
+	}
+	auto mcv = unfoldBasedCostVolume<matchingFunctions::SAD, float, float, 3>(l3, r3, 1, 1, D);
+	auto fvl = unfold<float, float>(2, 2, lf), fvr = unfold<float, float>(2, 2, rf);
+	auto f2c = featureVolume2CostVolume<matchingFunctions::ZNCC, float, float>(fvl, fvr, D);
+	auto agg = aggregateCost<matchingFunctions::ZNCC, float, float>(getFeatureVolumeForMatchFunc<matchingFunctions::ZNCC>(fvl),
+																		 getFeatureVolumeForMatchFunc<matchingFunctions::ZNCC>(fvr), searchOffset<1>(2, 9));
+	std::printf("multichannel_cv %.3f\nfv2cv %.4f\naggregate_offset_depth %d\n", checksum(mcv), checksum(f2c), agg.shape()[2]);
+
 	auto hier = hiearchicalTruncatedCostVolume<matchingFunctions::ZNCC, 2>(lf, rf, 2, 2, D, 2);
 	std::printf("hier_disp %.0f\n", checksum(hier.disp_estimate));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);

@@ -34,8 +34,36 @@ def test_facade_headers_carry_the_reference_names():
                  "matchingFunctions", "MatchingFunctionTraits", "hamming_cv_t", "census_data_t", "InterpolationKernel",
                  "sgmDirections", "PaddingMargins", "disp_t", "searchOffset", "unfoldBased2dDisparityCostVolume",
                  "extractSelected2dIndex", "selected2dIndexToDisp", "truncatedBidirectionaCostVolume", "refineDisp2dCostInterpolation",
-                 "IsotropyHypothesis"):
+                 "IsotropyHypothesis", "GrPix17R3Filter", "GrPix17R4Filter", "aggregateCost", "featureVolume2CostVolume",
+                 "getFeatureVolumeForMatchFunc"):
         assert name in text, name
+
+
+_GRPIX17R3 = [[14, 14, 10, 10, 10, 16, 16], [14, 14, 6, 4, 7, 16, 16], [11, 6, 6, 4, 7, 7, 13], [11, 2, 2, 1, 3, 3, 13],
+              [11, 8, 8, 5, 9, 9, 13], [15, 15, 8, 5, 9, 17, 17], [15, 15, 12, 12, 12, 17, 17]]
+
+
+def test_shipped_compressor_masks_equal_the_reference(tmp_path):
+    """GrPix17R3Filter / GrPix17R4Filter of the facade against the reference's own functions (oracle/_ref), unfold.h:476-691."""
+    import ctypes
+    import oracle as O
+    if O.ref is None or not O.ref.has("grpix17_filter"):
+        pytest.skip("oracle/_ref was not built")
+    src = os.path.join(str(tmp_path), "masks.cpp")
+    open(src, "w").write('#include <cstdio>\n#include <StereoVision/correlation/unfold.h>\nint main() { using namespace StereoVision::Correlation;\n'
+                         'for (int r = 3; r <= 4; r++) { auto m = r == 3 ? CompressorGenerators::GrPix17R3Filter() : CompressorGenerators::GrPix17R4Filter();\n'
+                         'for (int i = 0; i < 2 * r + 1; i++) for (int j = 0; j < 2 * r + 1; j++) std::printf("%d ", m.valueUnchecked(i, j)); std::printf("\\n"); } }\n')
+    exe = os.path.join(str(tmp_path), "masks")
+    r = subprocess.run(["g++", "-std=c++17", "-I" + os.path.join(ROOT, "include"), src, "-o", exe, "-L" + LIBDIR, "-lstevi_b200",
+                        "-Wl,-rpath," + LIBDIR], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = subprocess.run([exe], capture_output=True, text=True).stdout.strip().splitlines()
+    for radius, ln in zip((3, 4), lines):
+        n = 2 * radius + 1
+        want = np.zeros((n, n), np.int32)
+        O.ref.lib.ref_grpix17_filter(radius, want.ctypes.data_as(ctypes.c_void_p))
+        assert np.array_equal(np.array(ln.split(), np.int32).reshape(n, n), want)
+    assert np.array_equal(np.array(_GRPIX17R3), np.array(lines[0].split(), int).reshape(7, 7))
 
 
 def _mix(z):
@@ -70,6 +98,17 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
     # compare order-free sums as well
     assert float(got["mismatch_empty"]) == 1 and float(got["even_depth_empty"]) == 1 and float(got["even_side_empty"]) == 1
     assert float(got["search2d_match"]) > 0.95
+    assert int(got["compressed_features"]) == 17 and float(got["compressed_match"]) > 0.9 and int(got["aggregate_offset_depth"]) == 8
+    # the feature-level results against the Python mirror (order-free: both volumes are in the reference's layout)
+    mask = np.array(_GRPIX17R3, np.int32)
+    ccv = api.unfoldBasedCostVolumeCompressed(api.ZNCC, lf, rf, mask, D, ctx=ctx)
+    l3, r3 = np.stack([lf, 1 - lf], axis=2).astype(np.float32), np.stack([rf, 1 - rf], axis=2).astype(np.float32)
+    mcv = api.unfoldBasedCostVolumeMultiChannel(api.SAD, l3, r3, 1, 1, D, ctx=ctx)
+    f2c = api.featureVolume2CostVolume(api.ZNCC, api.unfold(2, 2, lf, ctx=ctx), api.unfold(2, 2, rf, ctx=ctx), D, ctx=ctx)
+    for name, arr in (("compressed_cv", ccv), ("multichannel_cv", mcv), ("fv2cv", f2c)):
+        a = np.asarray(arr)
+        cands = {_checksum(a), _checksum(np.transpose(a))}
+        assert any(abs(float(got[name]) - c) <= 2e-3 * max(1.0, abs(c)) for c in cands), (name, got[name], cands)
     zn = api.unfoldBasedCostVolume(api.ZNCC, lf, rf, 2, 2, D, layout="c", ctx=ctx)
     zi = api.extractSelectedIndex(zn, api.SCORE, ctx=ctx)
     assert abs(float(got["zncc_match"]) - float((zi[4:h - 4, 4:w - 24] == 5).mean())) < 1e-3

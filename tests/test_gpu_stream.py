@@ -95,3 +95,44 @@ def test_narrow_wire_with_pairs_in_flight(api):
     for (L, R), o in zip(pairs, outs):
         assert np.array_equal(o, api.censusSgmPipeline(L, R, 4, 3, 32, 10, 120, 100, 8, ctx=c))
     c.close(); hs.close()
+
+
+# ---- the batch entry of the C ABI: pairs over several contexts (and devices), one pair in flight per context ---------------
+
+@pytest.mark.parametrize("n_ctx", [1, 3])
+def test_batch_entry_equals_single_calls(api, n_ctx):
+    from libstevi_b200 import synth
+    pairs = [synth.stereo_pair(40, 180, 50 + k, d_bg=3, d_sq=9, d_max=16)[:2] for k in range(7)]
+    outs = [np.full((40, 180), -1, np.int32) for _ in pairs]
+    ctxs = [api.Context(0) for _ in range(n_ctx)]
+    api.batchCensusSgm(ctxs, [(L, R, o) for (L, R), o in zip(pairs, outs)], 4, 3, 24, 10, 120, 100, 8)
+    one = api.Context(0)
+    for (L, R), o in zip(pairs, outs):
+        assert np.array_equal(o, api.censusSgmPipeline(L, R, 4, 3, 24, 10, 120, 100, 8, ctx=one))
+    # u8 results and an empty batch
+    o8 = [np.empty((40, 180), np.uint8) for _ in pairs]
+    api.batchCensusSgm(ctxs, [(L, R, o) for (L, R), o in zip(pairs, o8)], 4, 3, 24, 10, 120, 100, 8)
+    assert all(np.array_equal(a.astype(np.int32), b) for a, b in zip(o8, outs))
+    api.batchCensusSgm(ctxs, [], 4, 3, 24, 10, 120, 100, 8)
+    # a failing pair stops the batch with the library's status
+    with pytest.raises(api.SteviError):
+        api.batchCensusSgm(ctxs, [(pairs[0][0], pairs[0][1][:30], outs[0])], 4, 3, 24, 10, 120, 100, 8)
+    for c in ctxs + [one]:
+        c.close()
+
+
+def test_batch_entry_over_all_devices(api):
+    import ctypes
+    n_dev = api.lib.stevi_device_count()
+    if n_dev < 2:
+        pytest.skip("one device")
+    from libstevi_b200 import synth
+    pairs = [synth.stereo_pair(48, 160, 70 + k, d_bg=3, d_sq=9, d_max=16)[:2] for k in range(4 * n_dev + 1)]
+    outs = [np.empty((48, 160), np.int32) for _ in pairs]
+    ctxs = [api.Context(d) for d in range(n_dev) for _ in range(2)]
+    api.batchCensusSgm(ctxs, [(L, R, o) for (L, R), o in zip(pairs, outs)], 4, 3, 24, 10, 120, 100, 8)
+    one = api.Context(0)
+    for (L, R), o in zip(pairs, outs):
+        assert np.array_equal(o, api.censusSgmPipeline(L, R, 4, 3, 24, 10, 120, 100, 8, ctx=one))
+    for c in ctxs + [one]:
+        c.close()
