@@ -1,9 +1,10 @@
-// B200 facade of LibStevi's correlation/hierarchical.h: OffsetedCostVolume :33-37, hiearchicalTruncatedCostVolume (sic)
-// :235-314 (both overloads). The guided volume of each level is computed from the images directly (unfold and feature
+// B200 facade of LibStevi's correlation/hierarchical.h: OffsetedCostVolume :33-37, FeatureVolumePyramid / buildFeaturePyramid
+// :39-71, hiearchicalTruncatedCostVolume (sic) :235-314 (both overloads). The guided volume of each level is computed from the images directly (unfold and feature
 // normalisation are fused into the kernel), so the feature-volume form of computeGuidedCV (:73-233) is offered on images.
 #ifndef STEVI_B200_CORRELATION_HIERARCHICAL_H
 #define STEVI_B200_CORRELATION_HIERARCHICAL_H
 
+#include <vector>
 #include "./cross_correlations.h"
 #include "../interpolation/downsampling.h"
 
@@ -15,6 +16,27 @@ struct OffsetedCostVolume {
 	Multidim::Array<TCV, 3> truncated_cost_volume;
 	Multidim::Array<disp_t, 2> disp_estimate;
 };
+
+// hierarchical.h:39-71: the unfolded features of an image at nLevels resolutions, level k = unfold of the image after k
+// 2x2 average poolings (level 0 = full resolution); an empty pyramid for nLevels <= 0
+template<typename F_T>
+using FeatureVolumePyramid = std::vector<Multidim::Array<F_T, 3>>;
+
+template<typename F_T, int nImDim = 2>
+FeatureVolumePyramid<F_T> buildFeaturePyramid(Multidim::Array<F_T, nImDim> const& img, uint8_t h_radius, uint8_t v_radius, int nLevels,
+											  PaddingMargins const& padding = PaddingMargins(), UnfoldPatchOrientation orientation = Rotate0) {
+	static_assert(nImDim == 2 && std::is_same_v<F_T, float>, "the feature pyramid is built from (H,W) float images on the B200 library");
+	FeatureVolumePyramid<F_T> ret;
+	if (nLevels <= 0) return ret;
+	ret.reserve(nLevels);
+	ret.emplace_back(unfold<F_T, F_T>(h_radius, v_radius, img, padding, orientation));
+	Multidim::Array<F_T, 2> level = Interpolation::averagePoolingDownsample<F_T, F_T>(img, Interpolation::DownSampleWindows(2));
+	for (int k = 1; k < nLevels; k++) {
+		ret.emplace_back(unfold<F_T, F_T>(h_radius, v_radius, level, padding, orientation));
+		if (k + 1 < nLevels) level = Interpolation::averagePoolingDownsample<F_T, F_T>(level, Interpolation::DownSampleWindows(2));
+	}
+	return ret;
+}
 
 template<matchingFunctions matchFunc, int depth, class T_L, class T_R, int nImDim = 2, dispDirection dDir = dispDirection::RightToLeft, class TCV = float>
 OffsetedCostVolume<TCV> hiearchicalTruncatedCostVolume(Multidim::Array<T_L, nImDim> const& img_l, Multidim::Array<T_R, nImDim> const& img_r,

@@ -88,6 +88,10 @@ int main() {
 
 	auto hier = hiearchicalTruncatedCostVolume<matchingFunctions::ZNCC, 2>(lf, rf, 2, 2, D, 2);
 	std::printf("hier_disp %.0f\n", checksum(hier.disp_estimate));
+	auto pyr = buildFeaturePyramid<float>(lf, 1, 1, 3);
+	auto psh = pyr.back().shape();
+	std::printf("pyramid_levels %d\npyramid_last_shape %dx%dx%d\npyramid_empty %d\n", int(pyr.size()), psh[0], psh[1], psh[2],
+				int(buildFeaturePyramid<float>(lf, 1, 1, 0).empty()));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);
 	std::printf("mismatch_empty %d\n", int(bad.empty()));
 	auto even = refineDispCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 3>(h, w, 4), zi);

@@ -35,7 +35,7 @@ def test_facade_headers_carry_the_reference_names():
                  "sgmDirections", "PaddingMargins", "disp_t", "searchOffset", "unfoldBased2dDisparityCostVolume",
                  "extractSelected2dIndex", "selected2dIndexToDisp", "truncatedBidirectionaCostVolume", "refineDisp2dCostInterpolation",
                  "IsotropyHypothesis", "GrPix17R3Filter", "GrPix17R4Filter", "aggregateCost", "featureVolume2CostVolume",
-                 "getFeatureVolumeForMatchFunc"):
+                 "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid"):
         assert name in text, name
 
 
@@ -98,6 +98,7 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
     # compare order-free sums as well
     assert float(got["mismatch_empty"]) == 1 and float(got["even_depth_empty"]) == 1 and float(got["even_side_empty"]) == 1
     assert float(got["search2d_match"]) > 0.95
+    assert int(got["pyramid_levels"]) == 3 and got["pyramid_last_shape"] == "10x16x9" and int(got["pyramid_empty"]) == 1
     assert int(got["compressed_features"]) == 17 and float(got["compressed_match"]) > 0.9 and int(got["aggregate_offset_depth"]) == 8
     # the feature-level results against the Python mirror (order-free: both volumes are in the reference's layout)
     mask = np.array(_GRPIX17R3, np.int32)
