@@ -374,6 +374,26 @@ STEVI_API int32_t stevi_batch_census_sgm(stevi_ctx* const* ctxs, int32_t n_ctx, 
 							   int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction, int32_t n_directions,
 							   float P1, float P2, float Pout, const stevi_margins* margins, int32_t semantics);
 
+/* ---- an entry point that allocates nothing ----------------------------------------------------------------------------- */
+
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The census cost volume of a pair, result identical to stevi_cost_volume(ctx, STEVI_MF_CENSUS, ..): img_l (H,Wl), img_r (H,Wr)
+ * u8|f32 (same dtype), out (H,Wsource,D) u16|i32|f32 — ALL THREE IN DEVICE MEMORY (STEVI_DEVICE; a host operand is refused with
+ * STEVI_E_ARG). The scratch memory of the stage, the census words of the two images, is a static __device__ array of
+ * STEVI_NOALLOC_SCRATCH_BYTES inside the library instead of the context's workspace: every GPU that loads the library holds it
+ * until the process exits, and the call neither grows the workspace nor calls cudaMalloc / cudaFree / any allocating routine.
+ * Limit: round256(H*Wl*nw*4) + round256(H*Wr*nw*4) <= STEVI_NOALLOC_SCRATCH_BYTES with nw = ((2*h_radius+1)*(2*v_radius+1)-1)/32+1
+ * words per pixel (1280x720 at 9x7 fits, 1920x1080 fits up to 5x5 windows = one word; 1920x1080 at 9x7 does not) — larger pairs get STEVI_E_UNSUPPORTED and a message stating both
+ * figures. A context with per-kernel timing switched on is refused (timing creates events).
+ * All calls, from every context and stream of the process, share the one array per GPU; it keeps the last call's contents (the
+ * part a call uses is cleared first, on the context's stream). Calls that overlap on the GPU — different streams without an
+ * ordering between them — race on it: serialise them. Work is enqueued on the context's stream like every other entry point. */
+#define STEVI_NOALLOC_SCRATCH_BYTES (16u << 20)
+STEVI_API int32_t stevi_census_cost_volume_noalloc(stevi_ctx* ctx, const stevi_array* img_l, const stevi_array* img_r,
+										 int32_t h_radius, int32_t v_radius, int32_t disp_width, int32_t direction,
+										 int32_t semantics, stevi_array* out);
+
 #ifdef __cplusplus
 }
 #endif

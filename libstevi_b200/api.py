@@ -329,6 +329,21 @@ def hammingCostVolume(feat_l, feat_r, disp_width, dDir=RIGHT_TO_LEFT, TCV=np.uin
     return out
 
 
+NOALLOC_SCRATCH_BYTES = 16 << 20   # STEVI_NOALLOC_SCRATCH_BYTES (c_api.h)
+
+
+def censusCostVolumeNoAlloc(img_l, img_r, h_radius, v_radius, disp_width, out, dDir=RIGHT_TO_LEFT, semantics=COMPAT, ctx=None):
+    """stevi_census_cost_volume_noalloc: unfoldBasedCostVolume<CENSUS> into the caller's ``out`` with the census words in the
+    library's static device scratch array (no counterpart in the reference; for callers that cannot call cudaMalloc). Device
+    tensors only; nothing is allocated here either: ``out`` (H, Wsource, D) u16|i32|f32 comes from the caller and is returned.
+    Pairs whose census words exceed NOALLOC_SCRATCH_BYTES raise SteviError; calls that overlap on the GPU race on the array."""
+    ctx = _ctx_for(ctx, img_l)
+    l, r, o = describe(img_l), describe(img_r), describe(out)
+    ctx.check(lib.stevi_census_cost_volume_noalloc(ctx.handle, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, disp_width,
+                                                   dDir, semantics, ctypes.byref(o)))
+    return out
+
+
 def getFeatureVolumeForMatchFuncFromFeatures(matchFunc, feature_vol, ctx=None):
     """getFeatureVolumeForMatchFunc<matchFunc>(feature_vol) on a ready-made (H,W,F) f32 volume, cross_correlations.h:645-722."""
     ctx = _ctx_for(ctx, feature_vol)
