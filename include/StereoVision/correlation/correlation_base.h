@@ -2,7 +2,7 @@
 // defaults; bodies forward to the C ABI. Reference lines: enums :31-45, disp_t :47, extractSelectedIndex :427-464,
 // selectedIndexToDisp :511-532, selectedCost :557-577, truncatedCostVolume :579-674, extractInBoundDomain :727-822;
 // 2-D search: searchOffset :288-409, extractSelected2dIndex :466-509, selected2dIndexToDisp :534-555,
-// truncatedBidirectionaCostVolume :677-725.
+// truncatedBidirectionaCostVolume :677-725; box filters: meanFilter2D :881-1004, sigmaFilter :1006-1077.
 #ifndef STEVI_B200_CORRELATION_BASE_H
 #define STEVI_B200_CORRELATION_BASE_H
 
@@ -148,6 +148,31 @@ Multidim::Array<T_CV, 4> truncatedBidirectionaCostVolume(Multidim::Array<T_CV, 4
 	if (!B200::ok(stevi_truncated_cost_volume_2d(B200::threadContext(), &v, &i, cost_vol_radius0, cost_vol_radius1, &o)))
 		return Multidim::Array<T_CV, 4>();
 	return out;
+}
+
+// meanFilter2D :881-1004 ((H,W) and (H,W,C) overloads) and sigmaFilter :1006-1077: same running-sum arithmetic as the reference
+// (bit-identical interior); the border the reference leaves uninitialised is 0. An empty array when the window does not fit.
+template<class T_I, int nDim>
+Multidim::Array<float, 2> meanFilter2D(uint8_t h_radius, uint8_t v_radius, Multidim::Array<T_I, nDim> const& in_data) {
+	static_assert(nDim == 2 || nDim == 3, "meanFilter2D takes (H,W) or (H,W,C) images");
+	static_assert(std::is_same_v<T_I, float> || std::is_same_v<T_I, uint8_t>, "u8 or float images on the B200 library");
+	auto sh = in_data.shape();
+	Multidim::Array<float, 2> mean(sh[0], sh[1]);
+	stevi_array i = B200::describe(in_data), o = B200::describe(mean);
+	if (!B200::ok(stevi_mean_filter_2d(B200::threadContext(), &i, h_radius, v_radius, &o))) return Multidim::Array<float, 2>();
+	return mean;
+}
+
+template<class T_I, int nDim>
+Multidim::Array<float, 2> sigmaFilter(uint8_t h_radius, uint8_t v_radius, Multidim::Array<float, 2> const& mean,
+									  Multidim::Array<T_I, nDim> const& in_data) {
+	static_assert(nDim == 2 || nDim == 3, "sigmaFilter takes (H,W) or (H,W,C) images");
+	static_assert(std::is_same_v<T_I, float> || std::is_same_v<T_I, uint8_t>, "u8 or float images on the B200 library");
+	auto sh = in_data.shape();
+	Multidim::Array<float, 2> sigma(sh[0], sh[1]);
+	stevi_array m = B200::describe(mean), i = B200::describe(in_data), o = B200::describe(sigma);
+	if (!B200::ok(stevi_sigma_filter(B200::threadContext(), &m, &i, h_radius, v_radius, &o))) return Multidim::Array<float, 2>();
+	return sigma;
 }
 
 } // namespace Correlation

@@ -302,6 +302,18 @@ STEVI_API int32_t stevi_refine_from_cost_volume(stevi_ctx* ctx, const stevi_arra
 
 /* ---- coarse-to-fine matching ---------------------------------------------------------------------------------- */
 
+/* meanFilter2D(h_radius, v_radius, in_data) (correlation/correlation_base.h:881-938 for (H,W), :941-1004 for (H,W,C) images):
+ * img u8|f32 -> out (H,W) f32, the mean over the (2*h_radius+1) x (2*v_radius+1) (x C) box, computed like the reference by running
+ * sums in float along the rows and then along the columns (bit-identical to it: every value carries the rounding of the chain
+ * before it). The reference writes only the interior [v_radius, H-v_radius) x [h_radius, W-h_radius) of its result and leaves the
+ * rest uninitialised; here the border is 0. STEVI_E_SHAPE when the window does not fit the image (out of bounds in the reference). */
+STEVI_API int32_t stevi_mean_filter_2d(stevi_ctx* ctx, const stevi_array* img, int32_t h_radius, int32_t v_radius, stevi_array* out);
+/* sigmaFilter(h_radius, v_radius, mean, in_data) (correlation/correlation_base.h:1006-1077): out(i,j) = sqrtf(sum over the box
+ * (rows, columns, channels in that order) of (in - mean(i,j))^2) on the interior, 0 on the border; product and sum rounded
+ * separately (what g++ emits for three of the four instantiations; its contracted 3-D f32 one differs by <= 2 ulp). */
+STEVI_API int32_t stevi_sigma_filter(stevi_ctx* ctx, const stevi_array* mean, const stevi_array* img, int32_t h_radius,
+						   int32_t v_radius, stevi_array* out);
+
 /* Interpolation::averagePoolingDownsample<T_I, float> (interpolation/downsampling.h:67-118) with
  * DownSampleWindows(win_h, win_v): img (H,W) u8|f32 -> out (ceil(H/win_v), ceil(W/win_h)) f32, mean over the in-image
  * part of each window. */

@@ -676,6 +676,31 @@ def averagePoolingDownsample(img, windows=2, ctx=None):
     return out
 
 
+def meanFilter2D(h_radius, v_radius, in_data, ctx=None):
+    """correlation_base.h:881-1004: (H,W) or (H,W,C) u8|f32 -> (H,W) f32 box mean by the reference's running sums (interior
+    bit-identical; the border it leaves uninitialised is 0). None when the window does not fit the image."""
+    ctx = _ctx_for(ctx, in_data)
+    out = _empty(in_data, in_data.shape[:2], np.float32)
+    a, o = describe(in_data), describe(out)
+    rc = lib.stevi_mean_filter_2d(ctx.handle, ctypes.byref(a), h_radius, v_radius, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def sigmaFilter(h_radius, v_radius, mean, in_data, ctx=None):
+    """correlation_base.h:1006-1077: sqrt of the box sum of (in - mean(i,j))^2 on the interior, 0 on the border."""
+    ctx = _ctx_for(ctx, in_data)
+    out = _empty(in_data, in_data.shape[:2], np.float32)
+    m, a, o = describe(mean), describe(in_data), describe(out)
+    rc = lib.stevi_sigma_filter(ctx.handle, ctypes.byref(m), ctypes.byref(a), h_radius, v_radius, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
 def computeGuidedCV(matchFunc, img_l, img_r, h_radius, v_radius, guide, upscale_disp_radius=2, dDir=RIGHT_TO_LEFT, ctx=None):
     """hierarchical.h:73-233 on the images (unfold + features fused in). Returns (truncated_cost_volume, disp_estimate),
     or None where the reference returns an empty volume."""

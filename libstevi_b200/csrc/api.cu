@@ -419,6 +419,27 @@ int32_t stevi_refine_from_cost_volume(stevi_ctx* c, const stevi_array* cv, const
 	return st.finish();
 }
 
+int32_t stevi_mean_filter_2d(stevi_ctx* c, const stevi_array* img, int32_t hr, int32_t vr, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vi, vo;
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(mean_filter_dev(c, vi, hr, vr, vo));
+	return st.finish();
+}
+
+int32_t stevi_sigma_filter(stevi_ctx* c, const stevi_array* mean, const stevi_array* img, int32_t hr, int32_t vr, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vm, vi, vo;
+	STEVI_TRY(st.in(mean, vm, "mean"));
+	STEVI_TRY(st.in(img, vi, "img"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(sigma_filter_dev(c, vm, vi, hr, vr, vo));
+	return st.finish();
+}
+
 int32_t stevi_avgpool_downsample(stevi_ctx* c, const stevi_array* img, int32_t wh, int32_t wv, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);

@@ -90,6 +90,9 @@ int32_t var_aggregate_dev(stevi_ctx* c, const View& cv, const View& win, const V
 
 // hier.cu
 int32_t avgpool_dev(stevi_ctx* c, const View& img, int win_h, int win_v, const View& out);
+// filters.cu: meanFilter2D / sigmaFilter (correlation_base.h:881-1077)
+int32_t mean_filter_dev(stevi_ctx* c, const View& img, int hr, int vr, const View& out);
+int32_t sigma_filter_dev(stevi_ctx* c, const View& mean, const View& img, int hr, int vr, const View& out);
 // band == nullptr: whole images; else the images / guide are row bands placed in global coordinates (c_api.h: stevi_band)
 int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const View& guide, int radius, int direction,
 					  const stevi_band* band, const View& tcv, const View& disp);

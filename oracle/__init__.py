@@ -364,6 +364,30 @@ class _Checker:
                                          hr, vr, D, radius, direction, _p(tcv), _p(disp))
         return (tcv, disp) if rc == 0 else None
 
+    # --- correlation_base.h:881-1077 ------------------------------------------------------
+    def mean_filter_2d(self, img, hr, vr, fill=np.nan):
+        """meanFilter2D on (H,W) or (H,W,C) u8|f32. Only the interior [vr,H-vr) x [hr,W-hr) is defined by the reference; the
+        rest of the returned array holds ``fill``. None if the window does not fit."""
+        h, w = img.shape[:2]
+        c = img.shape[2] if img.ndim == 3 else 0
+        out = np.full((h, w), fill, np.float32)
+        if img.dtype == np.uint8:
+            rc = self._f("mean_filter_2d_u8")(_p(_c(img, np.uint8)), h, w, c, hr, vr, _p(out))
+        else:
+            rc = self._f("mean_filter_2d_f32")(_p(_c(img, np.float32)), h, w, c, hr, vr, _p(out))
+        return out if rc == 0 else None
+
+    def sigma_filter(self, mean, img, hr, vr, fill=np.nan):
+        """sigmaFilter(h_radius, v_radius, mean, in_data); interior only, like mean_filter_2d."""
+        h, w = img.shape[:2]
+        c = img.shape[2] if img.ndim == 3 else 0
+        out = np.full((h, w), fill, np.float32)
+        if img.dtype == np.uint8:
+            rc = self._f("sigma_filter_u8")(_p(_c(mean, np.float32)), _p(_c(img, np.uint8)), h, w, c, hr, vr, _p(out))
+        else:
+            rc = self._f("sigma_filter_f32")(_p(_c(mean, np.float32)), _p(_c(img, np.float32)), h, w, c, hr, vr, _p(out))
+        return out if rc == 0 else None
+
 
 def _load():
     port_path = os.path.join(_HERE, "libstevi_oracle.so")

@@ -47,6 +47,15 @@ void out2(MD::Array<T, 2> const& a, TO* out) {
 		out[size_t(i) * s[1] + j] = static_cast<TO>(a.valueUnchecked(i, j));
 }
 
+// copies the interior [vr, h-vr) x [hr, w-hr) of a filter result (the reference never writes the rest of its array)
+template<typename T>
+int interior(MD::Array<T, 2> const& a, int hr, int vr, float* out) {
+	auto s = a.shape();
+	if (s[1] < 2 * hr + 1 || s[0] < 2 * vr + 1) return 1;
+	for (int i = vr; i < s[0] - vr; i++) for (int j = hr; j < s[1] - hr; j++) out[size_t(i) * s[1] + j] = a.valueUnchecked(i, j);
+	return 0;
+}
+
 template<matchingFunctions F, typename TI, typename TCV>
 int cv_dir(const TI* l, const TI* r, int h, int w, int wr, int hr, int vr, int D, int dir, TCV* out) {
 	auto L = view2(l, h, w);
@@ -499,6 +508,23 @@ int ref_hierarchical_f32(int matchfunc, int depth, const float* l, const float* 
 	default: return 2;
 	}
 #undef HIER
+}
+
+// correlation_base.h:881-1004 meanFilter2D, :1006-1077 sigmaFilter; in (h,w) when c == 0, else (h,w,c). Only the interior
+// [vr, h-vr) x [hr, w-hr) of the reference's result is ever written; the wrapper copies that part and leaves the rest of out alone.
+int ref_mean_filter_2d_f32(const float* in, int h, int w, int c, int hr, int vr, float* out) {
+	return c > 0 ? interior(meanFilter2D<float>(hr, vr, view3(in, h, w, c)), hr, vr, out) : interior(meanFilter2D<float>(hr, vr, view2(in, h, w)), hr, vr, out);
+}
+int ref_mean_filter_2d_u8(const uint8_t* in, int h, int w, int c, int hr, int vr, float* out) {
+	return c > 0 ? interior(meanFilter2D<uint8_t>(hr, vr, view3(in, h, w, c)), hr, vr, out) : interior(meanFilter2D<uint8_t>(hr, vr, view2(in, h, w)), hr, vr, out);
+}
+int ref_sigma_filter_f32(const float* mean, const float* in, int h, int w, int c, int hr, int vr, float* out) {
+	auto m = view2(mean, h, w);
+	return c > 0 ? interior(sigmaFilter<float>(hr, vr, m, view3(in, h, w, c)), hr, vr, out) : interior(sigmaFilter<float>(hr, vr, m, view2(in, h, w)), hr, vr, out);
+}
+int ref_sigma_filter_u8(const float* mean, const uint8_t* in, int h, int w, int c, int hr, int vr, float* out) {
+	auto m = view2(mean, h, w);
+	return c > 0 ? interior(sigmaFilter<uint8_t>(hr, vr, m, view3(in, h, w, c)), hr, vr, out) : interior(sigmaFilter<uint8_t>(hr, vr, m, view2(in, h, w)), hr, vr, out);
 }
 
 } // extern "C"

@@ -879,3 +879,64 @@ int orc_hierarchical_f32(int mf, int depth, const float* l, const float* r, int 
 	if (depth < 1) return 2;
 	return hier_level(mf, depth, l, r, h, w, hr, vr, D, radius, dir, tcv, disp);
 }
+
+/* ---- correlation_base.h:881-1004 meanFilter2D on (h,w) (c == 0) or (h,w,c) images: running row sums, then running column
+ * sums of those, then a division by the box size (times c). Each running sum is a chain of float additions in the reference's
+ * order: mH(i,j) = mH(i,j-1) + (in(i,j+hr) - in(i,j-hr-1)), the difference taken in the image's own type first (int for u8
+ * images, :908), one += per channel for 3-D images (:972-974). Only the interior [vr, h-vr) x [hr, w-hr) of `out` is defined by
+ * the reference (the rest of its array is never written); it is left untouched here. Returns 1 if the window does not fit. */
+#define ORC_MEAN_FILTER(NAME, T, DIFF_T) \
+int NAME(const T* in, int h, int w, int c, int hr, int vr, float* out) { \
+	if (w < 2 * hr + 1 || h < 2 * vr + 1) return 1; \
+	int nc = c > 0 ? c : 1; \
+	float* mh = (float*)malloc((size_t)h * w * sizeof(float)); \
+	_Pragma("omp parallel for") \
+	for (int i = 0; i < h; i++) { \
+		const T* row = in + (size_t)i * w * nc; \
+		float m = 0.f; \
+		for (int j = 0; j <= 2 * hr; j++) for (int k = 0; k < nc; k++) m += (float)row[j * nc + k]; \
+		mh[(size_t)i * w + hr] = m; \
+		for (int j = hr + 1; j < w - hr; j++) { \
+			for (int k = 0; k < nc; k++) m += (float)((DIFF_T)row[(j + hr) * nc + k] - (DIFF_T)row[(j - hr - 1) * nc + k]); \
+			mh[(size_t)i * w + j] = m; \
+		} \
+	} \
+	float box = (float)((size_t)(2 * vr + 1) * (2 * hr + 1) * nc); \
+	_Pragma("omp parallel for") \
+	for (int j = hr; j < w - hr; j++) { \
+		float m = 0.f; \
+		for (int i = 0; i <= 2 * vr; i++) m += mh[(size_t)i * w + j]; \
+		out[(size_t)vr * w + j] = m / box; \
+		for (int i = vr + 1; i < h - vr; i++) { \
+			m += mh[(size_t)(i + vr) * w + j] - mh[(size_t)(i - vr - 1) * w + j]; \
+			out[(size_t)i * w + j] = m / box; \
+		} \
+	} \
+	free(mh); \
+	return 0; \
+}
+ORC_MEAN_FILTER(orc_mean_filter_2d_f32, float, float)
+ORC_MEAN_FILTER(orc_mean_filter_2d_u8, uint8_t, int)
+
+/* ---- correlation_base.h:1006-1077 sigmaFilter: sqrtf of the sum over the window (rows, then columns, then channels) of
+ * (in - mean(i,j))^2, interior only. Product and sum are rounded separately, as the source reads. Whether a Release build of the
+ * reference contracts `s += tmp*tmp` into a fused multiply-add is the compiler's choice per instantiation: g++ 13 -O3 on an FMA
+ * target (oracle/_ref) leaves the 2-D f32, 2-D u8 and 3-D u8 instantiations uncontracted (this restatement is bit-identical to
+ * them) and contracts the 3-D f32 one (differs by <= 2 ulp). tests/test_oracle_pinning.py holds both statements. */
+#define ORC_SIGMA_FILTER(NAME, T) \
+int NAME(const float* mean, const T* in, int h, int w, int c, int hr, int vr, float* out) { \
+	if (w < 2 * hr + 1 || h < 2 * vr + 1) return 1; \
+	int nc = c > 0 ? c : 1; \
+	_Pragma("omp parallel for") \
+	for (int i = vr; i < h - vr; i++) for (int j = hr; j < w - hr; j++) { \
+		float s = 0.f, m = mean[(size_t)i * w + j]; \
+		for (int k = -vr; k <= vr; k++) for (int l = -hr; l <= hr; l++) for (int q = 0; q < nc; q++) { \
+			float tmp = (float)in[((size_t)(i + k) * w + (j + l)) * nc + q] - m; \
+			s += tmp * tmp; \
+		} \
+		out[(size_t)i * w + j] = sqrtf(s); \
+	} \
+	return 0; \
+}
+ORC_SIGMA_FILTER(orc_sigma_filter_f32, float)
+ORC_SIGMA_FILTER(orc_sigma_filter_u8, uint8_t)

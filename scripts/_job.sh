@@ -1,5 +1,3 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/noalloc_alone.log 2>&1; echo "alone rc=$?" | tee -a gpurun_out/noalloc_alone.log
-tail -5 gpurun_out/noalloc_alone.log
-timeout 1500 python -m pytest tests -m gpu -x -q -rs > gpurun_out/gpu_suite.log 2>&1; echo "suite rc=$?" | tee -a gpurun_out/gpu_suite.log
-tail -8 gpurun_out/gpu_suite.log
+timeout 900 python -m pytest tests/test_gpu_filters.py tests/test_facade.py -m gpu -x -q 2>&1 | tail -12
+timeout 300 python scripts/quick_bench_filters.py 2>&1 | tee gpurun_out/stage_filters.jsonl | tail -6

@@ -92,6 +92,10 @@ int main() {
 	auto psh = pyr.back().shape();
 	std::printf("pyramid_levels %d\npyramid_last_shape %dx%dx%d\npyramid_empty %d\n", int(pyr.size()), psh[0], psh[1], psh[2],
 				int(buildFeaturePyramid<float>(lf, 1, 1, 0).empty()));
+	auto mean = meanFilter2D(2, 1, lf);
+	auto sigma = sigmaFilter(2, 1, mean, lf);
+	std::printf("mean_filter %.4f\nsigma_filter %.4f\nmean_filter_empty %d\n", checksum(mean), checksum(sigma),
+				int(meanFilter2D(uint8_t(w), 1, lf).empty()));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);
 	std::printf("mismatch_empty %d\n", int(bad.empty()));
 	auto even = refineDispCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 3>(h, w, 4), zi);

@@ -100,9 +100,33 @@ def main_2d():
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+def main_filters():
+    """meanFilter2D / sigmaFilter (correlation_base.h:881-1077) on (H,W) and (H,W,C) u8|f32 images. Only the interior the
+    reference writes is stored; the rest of each array is NaN."""
+    ref = O.ref
+    assert ref is not None, "build oracle/_ref first (make -C oracle ref)"
+    H, W = 23, 31
+    out = {"H": H, "W": W, "seed": 301}
+    imgs = {"f32": synth.random_image(H, W, 301),
+            "u8": synth.stereo_pair(H, W, 302)[0],
+            "f32c3": np.stack([synth.random_image(H, W, 303 + k) for k in range(3)], axis=2),
+            "u8c2": np.stack([synth.stereo_pair(H, W, 306 + k)[0] for k in range(2)], axis=2)}
+    for name, img in imgs.items():
+        for hr, vr in ((1, 1), (3, 2), (0, 4), (5, 0)):
+            m = ref.mean_filter_2d(img, hr, vr)
+            out[f"mean_{name}_{hr}_{vr}"] = m
+            out[f"sigma_{name}_{hr}_{vr}"] = ref.sigma_filter(m, img, hr, vr)
+    path = os.path.join(HERE, "reference_outputs_filters.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     if "2d" in sys.argv[1:]:
         main_2d()
+    elif "filters" in sys.argv[1:]:
+        main_filters()
     else:
         main()
         main_2d()
+        main_filters()

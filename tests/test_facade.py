@@ -35,7 +35,7 @@ def test_facade_headers_carry_the_reference_names():
                  "sgmDirections", "PaddingMargins", "disp_t", "searchOffset", "unfoldBased2dDisparityCostVolume",
                  "extractSelected2dIndex", "selected2dIndexToDisp", "truncatedBidirectionaCostVolume", "refineDisp2dCostInterpolation",
                  "IsotropyHypothesis", "GrPix17R3Filter", "GrPix17R4Filter", "aggregateCost", "featureVolume2CostVolume",
-                 "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid"):
+                 "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid", "meanFilter2D", "sigmaFilter"):
         assert name in text, name
 
 
@@ -106,7 +106,10 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
     l3, r3 = np.stack([lf, 1 - lf], axis=2).astype(np.float32), np.stack([rf, 1 - rf], axis=2).astype(np.float32)
     mcv = api.unfoldBasedCostVolumeMultiChannel(api.SAD, l3, r3, 1, 1, D, ctx=ctx)
     f2c = api.featureVolume2CostVolume(api.ZNCC, api.unfold(2, 2, lf, ctx=ctx), api.unfold(2, 2, rf, ctx=ctx), D, ctx=ctx)
-    for name, arr in (("compressed_cv", ccv), ("multichannel_cv", mcv), ("fv2cv", f2c)):
+    mean = api.meanFilter2D(2, 1, lf, ctx=ctx)
+    assert int(got["mean_filter_empty"]) == 1
+    for name, arr in (("compressed_cv", ccv), ("multichannel_cv", mcv), ("fv2cv", f2c), ("mean_filter", mean),
+                      ("sigma_filter", api.sigmaFilter(2, 1, mean, lf, ctx=ctx))):
         a = np.asarray(arr)
         cands = {_checksum(a), _checksum(np.transpose(a))}
         assert any(abs(float(got[name]) - c) <= 2e-3 * max(1.0, abs(c)) for c in cands), (name, got[name], cands)

@@ -444,3 +444,77 @@ def test_aggregation_golden():
     cv = G2[f"cv2d_{O.SSD}_1"][:, :, :, 2]          # an (H, W, dH) slice of the golden volume used as a 1-D volume
     win = bilateral_windows(synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_r"])), 2, 2)
     assert same(port.variable_cost_volume_aggregation(cv, win), G2["aggregated_ssd_5x5"])
+
+
+# ---- meanFilter2D / sigmaFilter (correlation_base.h:881-1077) ----------------------------------------------------------
+
+@pytest.mark.parametrize("hr,vr,eh,ev", [(0, 0, 0, 0), (1, 1, 1, 1), (5, 1, 7, 7), (1, 5, 7, 7), (5, 5, 7, 7)])
+def test_ref_testMeanFilter(hr, vr, eh, ev):
+    # test/unittests/testCorrelationFilters.cpp:82-136, same rows: the last interior pixel against the plain window mean
+    rng = np.random.default_rng(100 + hr * 7 + vr)
+    h, w = 2 * vr + 1 + ev, 2 * hr + 1 + eh
+    img = rng.uniform(-1, 1, (h, w)).astype(np.float32)
+    want = img[ev:, eh:].sum(dtype=np.float32) / ((2 * hr + 1) * (2 * vr + 1))
+    for chk in (O.port, O.ref):
+        if chk is None:
+            continue
+        avg = chk.mean_filter_2d(img, hr, vr)
+        assert abs(want - avg[vr + ev, hr + eh]) < 1e-3
+        assert np.isnan(avg[:vr]).all() and np.isnan(avg[:, :hr]).all()   # outside the interior nothing is defined / written
+
+
+@pytest.mark.parametrize("hr,vr", [(1, 1), (5, 1), (1, 5), (5, 5)])
+def test_ref_testSigmaFilter(hr, vr):
+    # testCorrelationFilters.cpp:172-221
+    rng = np.random.default_rng(200 + hr * 7 + vr)
+    img = rng.uniform(-1, 1, (2 * vr + 1, 2 * hr + 1)).astype(np.float32)
+    mean = img.sum(dtype=np.float32) / img.size
+    want = np.sqrt(((img - mean) ** 2).sum(dtype=np.float32))
+    for chk in (O.port, O.ref):
+        if chk is None:
+            continue
+        sigma = chk.sigma_filter(chk.mean_filter_2d(img, hr, vr), img, hr, vr)
+        assert abs(want - sigma[vr, hr]) < 1e-3
+
+
+@pytest.mark.skipif(O.ref is None, reason="compiled reference (oracle/_ref) not present on this machine")
+@pytest.mark.parametrize("shape", [(40, 57), (33, 41, 3), (21, 30, 1)])
+@pytest.mark.parametrize("dtype", [np.float32, np.uint8])
+@pytest.mark.parametrize("hr,vr", [(1, 1), (3, 2), (0, 4), (6, 0)])
+def test_filters_port_equals_compiled_reference(shape, dtype, hr, vr):
+    rng = np.random.default_rng(7)
+    img = (rng.random(shape) * 255).astype(np.uint8) if dtype == np.uint8 else rng.uniform(-1, 1, shape).astype(np.float32)
+    a, b = O.port.mean_filter_2d(img, hr, vr), O.ref.mean_filter_2d(img, hr, vr)
+    assert np.array_equal(a, b, equal_nan=True)          # running sums in the reference's order: bit for bit
+    sa, sb = O.port.sigma_filter(b, img, hr, vr), O.ref.sigma_filter(b, img, hr, vr)
+    assert np.array_equal(np.isnan(sa), np.isnan(sb))
+    if dtype == np.float32 and len(shape) == 3:
+        # the one instantiation g++ contracts into fused multiply-adds (see oracle/stevi_oracle.c): a few ulp
+        inner = np.isfinite(sb)
+        assert np.abs(sa[inner] - sb[inner]).max() <= 4e-7 * np.abs(sb[inner]).max()
+    else:
+        assert np.array_equal(sa, sb, equal_nan=True)
+    assert O.port.mean_filter_2d(img[:2 * vr], hr, vr) is None if vr else True   # window taller than the image
+
+
+GF = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_outputs_filters.npz"))
+
+
+def filter_images():
+    h, w = int(GF["H"]), int(GF["W"])
+    return {"f32": synth.random_image(h, w, 301), "u8": synth.stereo_pair(h, w, 302)[0],
+            "f32c3": np.stack([synth.random_image(h, w, 303 + k) for k in range(3)], axis=2),
+            "u8c2": np.stack([synth.stereo_pair(h, w, 306 + k)[0] for k in range(2)], axis=2)}
+
+
+@pytest.mark.parametrize("name", ["f32", "u8", "f32c3", "u8c2"])
+@pytest.mark.parametrize("hr,vr", [(1, 1), (3, 2), (0, 4), (5, 0)])
+def test_golden_filters(name, hr, vr):
+    img = filter_images()[name]
+    m = GF[f"mean_{name}_{hr}_{vr}"]
+    assert same(port.mean_filter_2d(img, hr, vr), m)
+    s, want = port.sigma_filter(m, img, hr, vr), GF[f"sigma_{name}_{hr}_{vr}"]
+    if name == "f32c3":   # contracted by g++ in the compiled reference (oracle/stevi_oracle.c)
+        assert np.array_equal(np.isnan(s), np.isnan(want)) and np.nanmax(np.abs(s - want)) <= 4e-7 * np.nanmax(want)
+    else:
+        assert same(s, want)
