@@ -6,11 +6,11 @@
 // carries the rounding of the whole chain before it, and the only way to get the reference's bits is to walk the chains in its
 // order: H independent chains of W steps, then W chains of H steps. The kernels keep the chains sequential and make everything
 // around them parallel:
-//   k_mean_rows   block = 32 rows, two warps: warp 1 fetches the next 32 steps of all 32 rows (coalesced along the row) and leaves
-//                 their differences in shared memory, warp 0 (lane = row) walks the previous 32 steps and writes a 32x32 tile of mH
-//                 back coalesced. Multi-channel rows are walked as the flattened sequence (j, c).
-//   k_mean_cols   thread = column (coalesced by construction), 16 steps of operands prefetched ahead of the chain; stores
-//                 mean = sum / box (the reference divides after the sums are complete, :928-934: same value).
+//   k_mean_chain  a block owns 32 chains; one warp walks them (lane = chain, one dependent addition per step, operands and
+//                 results in shared memory) while twelve helper warps load the operands three tiles ahead, coalesced, and write
+//                 the results back, coalesced (the row pass transposes through shared memory). Multi-channel rows are walked as
+//                 the flattened sequence (j, c). The column pass stores mean = sum / box (the reference divides after the
+//                 sums are complete, :928-934: same value).
 // The reference never writes the border of its result (outside [vr, H-vr) x [hr, W-hr): uninitialised memory); it is set to 0 here.
 //
 // sigmaFilter: thread per interior pixel, the window read through L1 (neighbouring threads read neighbouring addresses), the sum
@@ -24,122 +24,131 @@ namespace {
 
 template<typename T> __device__ __forceinline__ float ldf(const T* p) { return (float)__ldg(p); }
 
-struct RowsParams {
-	const void* in; int64_t s0, s1, s2;
-	int H, W, C, hr;
-	float* mh;   // dense (H, W)
-};
-
-template<typename T>
-__global__ void __launch_bounds__(64) k_mean_rows(const RowsParams p) {
-	__shared__ float delta[2][32][33];   // [buffer][row][step]
-	__shared__ float tile[32][33];       // mH values of the 32 steps just walked
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	const int r0 = blockIdx.x * 32;
-	const T* in = static_cast<const T*>(p.in);
-	const int C = p.C, hr = p.hr;
-	// the chain of a row: mH(i,hr) = sum of the first 2hr+1 pixels, then steps f = 0 .. n_steps-1, step f adds channel f % C of
-	// column j = hr + 1 + f / C; mH(i,j) is complete after the last channel of j
-	const int64_t n_steps = (int64_t)(p.W - 2 * hr - 1) * C;
-	const int n_tiles = (int)((n_steps + 31) / 32);
-	auto fetch = [&](int t, int buf) {   // warp 1: differences of steps [32t, 32t+32) of the 32 rows
-		const int64_t f = (int64_t)t * 32 + lane;
-		const bool live = f < n_steps;
-		const int j = hr + 1 + (int)(f / C), c = (int)(f % C);
-		const T* lead = in + (int64_t)(j + hr) * p.s1 + (int64_t)c * p.s2;
-		const T* trail = in + (int64_t)(j - hr - 1) * p.s1 + (int64_t)c * p.s2;
-#pragma unroll 8
-		for (int r = 0; r < 32; r++) {
-			const int i = r0 + r;
-			float d = 0.f;
-			// the difference is taken in the image's own type first (:908): exact for u8, the same float subtraction for f32
-			if (live && i < p.H) d = __fsub_rn(ldf(lead + i * p.s0), ldf(trail + i * p.s0));
-			delta[buf][r][lane] = d;
-		}
-	};
-	float m = 0.f;
-	const int row = r0 + lane;
-	if (warp == 0) {
-		if (row < p.H) {
-			const T* q = in + row * p.s0;
-			for (int j = 0; j <= 2 * hr; j++)
-				for (int c = 0; c < C; c++) m = __fadd_rn(m, ldf(q + (int64_t)j * p.s1 + (int64_t)c * p.s2));
-			p.mh[(int64_t)row * p.W + hr] = m;
-		}
-	} else if (n_tiles > 0) fetch(0, 0);
-	__syncthreads();
-	for (int t = 0; t < n_tiles; t++) {
-		const int buf = t & 1;
-		if (warp == 1) {
-			if (t + 1 < n_tiles) fetch(t + 1, buf ^ 1);
-		} else {
-			const int64_t f0 = (int64_t)t * 32;
-#pragma unroll 8
-			for (int x = 0; x < 32; x++) {
-				m = __fadd_rn(m, delta[buf][lane][x]);
-				tile[lane][x] = m;
-			}
-			__syncwarp();
-			// coalesced write-back: lane = step; a step closes a column when it is the column's last channel
-			const int64_t f = f0 + lane;
-			const bool closes = f < n_steps && (int)(f % C) == C - 1;
-			const int j = hr + 1 + (int)(f / C);
-			for (int r = 0; r < 32; r++) {
-				const int i = r0 + r;
-				if (closes && i < p.H) p.mh[(int64_t)i * p.W + j] = tile[r][lane];
-			}
-			__syncwarp();
-		}
-		__syncthreads();
-	}
-}
-
-struct ColsParams {
-	const float* mh;
-	float* out; int64_t o0, o1;
-	int H, W, hr, vr;
+// One kernel for both passes. A block owns 32 LINES (image rows for the row pass, columns of mH for the column pass) and walks
+// them in tiles of 32 STEPS. Warp 0 is the chain: lane = line, one dependent float addition per step, operands and results in
+// shared memory. Warps 1..12 are helpers in three groups of four; group g handles the tiles t = g (mod 3): it loads the two
+// operands of every step of its tile three tiles ahead of the chain (coalesced: lane = step along the row for the row pass,
+// lane = column for the column pass; the loads stay in flight, in registers, for three chain tiles), leaves their difference
+// in shared memory one tile ahead, and writes the chain's results of the tile just finished back to global memory (the row pass
+// transposes through shared memory, so both sides of it are coalesced; the column pass divides by the box size on the way).
+struct ChainParams {
+	const void* in; int64_t s0, s1, s2;   // row pass: the image; column pass: mH as (H, W, 1) with s1 = 1
+	float* out; int64_t o0, o1;           // row pass: mH (dense); column pass: the mean
+	int H, W, C, hr, vr;
 	float box;
 };
 
-__global__ void __launch_bounds__(32) k_mean_cols(const ColsParams p) {
-	const int j = blockIdx.x * 32 + threadIdx.x;
-	if (j >= p.W) return;
-	float* o = p.out + (int64_t)j * p.o1;
-	const int H = p.H, vr = p.vr;
-	if (j < p.hr || j >= p.W - p.hr) {   // border columns
-		for (int i = 0; i < H; i++) o[(int64_t)i * p.o0] = 0.f;
-		return;
-	}
-	for (int i = 0; i < vr; i++) { o[(int64_t)i * p.o0] = 0.f; o[(int64_t)(H - 1 - i) * p.o0] = 0.f; }
-	const float* q = p.mh + j;
-	const int64_t W = p.W;
-	float m = 0.f;
-	for (int i = 0; i <= 2 * vr; i++) m = __fadd_rn(m, q[i * W]);
-	o[(int64_t)vr * p.o0] = __fdiv_rn(m, p.box);
-	constexpr int B = 16;
-	float d[B], nd[B];
-	const int first = vr + 1, last = H - vr;   // steps i in [first, last)
-	auto load = [&](int i0, float (&v)[B]) {
+template<typename T, bool ROWS>
+__global__ void __launch_bounds__(416) k_mean_chain(const ChainParams p) {
+	__shared__ float delta[2][32][33];
+	__shared__ float sums[2][32][33];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int l0 = blockIdx.x * 32;                 // first line of the block
+	const T* in = static_cast<const T*>(p.in);
+	const int C = ROWS ? p.C : 1, hr = p.hr, vr = p.vr;
+	const int n_lines = ROWS ? p.H : p.W;
+	// steps: row pass f = (column - hr - 1) * C + channel; column pass s = row - vr - 1
+	const int64_t n_steps = ROWS ? (int64_t)(p.W - 2 * hr - 1) * C : (int64_t)(p.H - 2 * vr - 1);
+	const int n_tiles = (int)((n_steps + 31) / 32);
+	const int group = (warp - 1) >> 2, q = (warp - 1) & 3;   // helpers
+	float lead[8], trail[8];
+
+	// operands of tile t for the 8 (row pass: lines; column pass: steps) this helper warp owns
+	auto issue = [&](int t) {
+		if (t >= n_tiles) return;
+		if (ROWS) {
+			const int64_t f = (int64_t)t * 32 + lane;
+			const bool live = f < n_steps;
+			const int j = hr + 1 + (int)(f / C), c = (int)(f - (int64_t)(j - hr - 1) * C);
+			const T* a = in + (int64_t)(j + hr) * p.s1 + (int64_t)c * p.s2;
+			const T* b = in + (int64_t)(j - hr - 1) * p.s1 + (int64_t)c * p.s2;
 #pragma unroll
-		for (int k = 0; k < B; k++) {
-			const int i = i0 + k;
-			v[k] = i < last ? __fsub_rn(q[(int64_t)(i + vr) * W], q[(int64_t)(i - vr - 1) * W]) : 0.f;
-		}
-	};
-	load(first, d);
-	for (int i0 = first; i0 < last; i0 += B) {
-		load(i0 + B, nd);
+			for (int k = 0; k < 8; k++) {
+				const int i = l0 + q * 8 + k;
+				const bool ok = live && i < p.H;
+				lead[k] = ok ? ldf(a + i * p.s0) : 0.f;
+				trail[k] = ok ? ldf(b + i * p.s0) : 0.f;
+			}
+		} else {
+			const int j = l0 + lane;
+			const bool live = j >= hr && j < p.W - hr;
 #pragma unroll
-		for (int k = 0; k < B; k++) {
-			const int i = i0 + k;
-			if (i < last) {
-				m = __fadd_rn(m, d[k]);
-				o[(int64_t)i * p.o0] = __fdiv_rn(m, p.box);
+			for (int k = 0; k < 8; k++) {
+				const int64_t s = (int64_t)t * 32 + q * 8 + k;
+				const bool ok = live && s < n_steps;
+				lead[k] = ok ? ldf(in + (s + 2 * vr + 1) * p.s0 + j) : 0.f;
+				trail[k] = ok ? ldf(in + s * p.s0 + j) : 0.f;
 			}
 		}
+	};
+	// the difference is taken in the image's own type first (:908, :924): exact for u8, the same float subtraction for f32
+	auto land = [&](int t) {
+		if (t >= n_tiles) return;
 #pragma unroll
-		for (int k = 0; k < B; k++) d[k] = nd[k];
+		for (int k = 0; k < 8; k++) delta[t & 1][q * 8 + k][lane] = __fsub_rn(lead[k], trail[k]);
+	};
+	// results of tile t: sums[t & 1] holds, row pass [line][step], column pass [step][line]
+	auto write_back = [&](int t) {
+		if (ROWS) {
+			const int64_t f = (int64_t)t * 32 + lane;
+			const int j = hr + 1 + (int)(f / C);
+			const bool closes = f < n_steps && f - (int64_t)(j - hr - 1) * C == C - 1;   // the column's last channel
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const int i = l0 + q * 8 + k;
+				if (closes && i < p.H) p.out[(int64_t)i * p.o0 + j] = sums[t & 1][q * 8 + k][lane];
+			}
+		} else {
+			const int j = l0 + lane;
+			const bool live = j >= hr && j < p.W - hr;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const int64_t s = (int64_t)t * 32 + q * 8 + k;
+				if (j < p.W && s < n_steps) p.out[(s + vr + 1) * p.o0 + j * p.o1] = live ? __fdiv_rn(sums[t & 1][q * 8 + k][lane], p.box) : 0.f;
+			}
+		}
+	};
+	float m = 0.f;
+	if (warp == 0) {
+		// the head of the chain: the first full window (:899-903, :916-920)
+		const int line = l0 + lane;
+		if (ROWS) {
+			if (line < p.H) {
+				const T* row = in + line * p.s0;
+				for (int j = 0; j <= 2 * hr; j++)
+					for (int c = 0; c < C; c++) m = __fadd_rn(m, ldf(row + (int64_t)j * p.s1 + (int64_t)c * p.s2));
+				p.out[(int64_t)line * p.o0 + hr] = m;
+			}
+		} else if (line < p.W) {
+			const bool live = line >= hr && line < p.W - hr;
+			if (live) for (int i = 0; i <= 2 * vr; i++) m = __fadd_rn(m, ldf(in + i * p.s0 + line));
+			p.out[(int64_t)vr * p.o0 + line * p.o1] = live ? __fdiv_rn(m, p.box) : 0.f;
+		}
+	} else {
+		if (!ROWS && l0 + lane < p.W)   // rows above and below the interior: never written by the reference, 0 here
+			for (int i = warp - 1; i < vr; i += 12) {
+				p.out[(int64_t)i * p.o0 + (l0 + lane) * p.o1] = 0.f;
+				p.out[(int64_t)(p.H - 1 - i) * p.o0 + (l0 + lane) * p.o1] = 0.f;
+			}
+		issue(group);
+		if (group == 0) { land(0); issue(3); }
 	}
+	__syncthreads();
+	for (int t = 0; t < n_tiles; t++) {
+		if (warp == 0) {
+			const int b = t & 1;
+#pragma unroll
+			for (int x = 0; x < 32; x++) {
+				m = __fadd_rn(m, ROWS ? delta[b][lane][x] : delta[b][x][lane]);
+				if (ROWS) sums[b][lane][x] = m; else sums[b][x][lane] = m;
+			}
+		} else {
+			if (group == (t + 1) % 3) { land(t + 1); issue(t + 4); }
+			else if (group == (t + 2) % 3 && t > 0) write_back(t - 1);
+		}
+		__syncthreads();
+	}
+	if (warp != 0 && group == 0 && n_tiles > 0) write_back(n_tiles - 1);
 }
 
 struct SigmaParams {
@@ -156,15 +165,24 @@ __global__ void __launch_bounds__(256) k_sigma_filter(const SigmaParams p) {
 	float* o = p.out + i * p.o0 + j * p.o1;
 	if (i < p.vr || i >= p.H - p.vr || j < p.hr || j >= p.W - p.hr) { *o = 0.f; return; }
 	const float m = __ldg(p.mean + i * p.m0 + j * p.m1);
-	const T* in = static_cast<const T*>(p.in);
+	const T* row = static_cast<const T*>(p.in) + (int64_t)(i - p.vr) * p.s0 + (int64_t)(j - p.hr) * p.s1;
+	const int nh = 2 * p.hr + 1, nv = 2 * p.vr + 1;
 	float s = 0.f;
-	for (int k = -p.vr; k <= p.vr; k++) {
-		const T* row = in + (int64_t)(i + k) * p.s0;
-		for (int l = -p.hr; l <= p.hr; l++) {
-			const T* px = row + (int64_t)(j + l) * p.s1;
-			for (int c = 0; c < p.C; c++) {
-				const float tmp = __fsub_rn(ldf(px + (int64_t)c * p.s2), m);
+	for (int k = 0; k < nv; k++, row += p.s0) {
+		const T* px = row;
+		if (p.C == 1) {
+#pragma unroll 4
+			for (int l = 0; l < nh; l++, px += p.s1) {
+				const float tmp = __fsub_rn(ldf(px), m);
 				s = __fadd_rn(s, __fmul_rn(tmp, tmp));
+			}
+		} else {
+			for (int l = 0; l < nh; l++, px += p.s1) {
+				const T* pc = px;
+				for (int c = 0; c < p.C; c++, pc += p.s2) {
+					const float tmp = __fsub_rn(ldf(pc), m);
+					s = __fadd_rn(s, __fmul_rn(tmp, tmp));
+				}
 			}
 		}
 	}
@@ -193,16 +211,17 @@ int32_t mean_filter_dev(stevi_ctx* c, const View& img, int hr, int vr, const Vie
 	const int H = img.shape[0], W = img.shape[1];
 	float* mh = nullptr;
 	STEVI_TRY(arena_alloc_t(c, (size_t)H * W, &mh));
-	RowsParams r;
+	ChainParams r;
 	r.in = img.p; r.s0 = img.st[0]; r.s1 = img.st[1]; r.s2 = img.ndim == 3 ? img.st[2] : 0;
-	r.H = H; r.W = W; r.C = C; r.hr = hr; r.mh = mh;
-	if (img.dtype == STEVI_U8) STEVI_LAUNCH(c, k_mean_rows<uint8_t>, cdiv(H, 32), 64, 0, r);
-	else STEVI_LAUNCH(c, k_mean_rows<float>, cdiv(H, 32), 64, 0, r);
-	ColsParams q;
-	q.mh = mh; q.out = out.as<float>(); q.o0 = out.st[0]; q.o1 = out.st[1];
-	q.H = H; q.W = W; q.hr = hr; q.vr = vr;
+	r.out = mh; r.o0 = W; r.o1 = 1;
+	r.H = H; r.W = W; r.C = C; r.hr = hr; r.vr = vr; r.box = 1.f;
+	if (img.dtype == STEVI_U8) STEVI_LAUNCH(c, (k_mean_chain<uint8_t, true>), cdiv(H, 32), 416, 0, r);
+	else STEVI_LAUNCH(c, (k_mean_chain<float, true>), cdiv(H, 32), 416, 0, r);
+	ChainParams q = r;
+	q.in = mh; q.s0 = W; q.s1 = 1; q.s2 = 0; q.C = 1;
+	q.out = out.as<float>(); q.o0 = out.st[0]; q.o1 = out.st[1];
 	q.box = (float)((size_t)(2 * vr + 1) * (size_t)(2 * hr + 1) * (size_t)(img.ndim == 3 ? C : 1));   // size_t -> float (:932, :998)
-	STEVI_LAUNCH(c, k_mean_cols, cdiv(W, 32), 32, 0, q);
+	STEVI_LAUNCH(c, (k_mean_chain<float, false>), cdiv(W, 32), 416, 0, q);
 	return STEVI_OK;
 }
 
