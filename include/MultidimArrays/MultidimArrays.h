@@ -53,6 +53,12 @@ struct IndexBlockT : public std::array<int, nDim> {
 		for (int v : l) { if (k < nDim) (*this)[k++] = v; }
 	}
 	void setZero() { this->fill(0); }
+	IndexBlockT operator+(IndexBlockT const& o) const { IndexBlockT r; for (int k = 0; k < nDim; k++) r[k] = (*this)[k] + o[k]; return r; }
+	IndexBlockT operator-(IndexBlockT const& o) const { IndexBlockT r; for (int k = 0; k < nDim; k++) r[k] = (*this)[k] - o[k]; return r; }
+	IndexBlockT operator+(int v) const { IndexBlockT r; for (int k = 0; k < nDim; k++) r[k] = (*this)[k] + v; return r; }
+	IndexBlockT operator-(int v) const { IndexBlockT r; for (int k = 0; k < nDim; k++) r[k] = (*this)[k] - v; return r; }
+	bool isInLimit(std::array<int, nDim> const& shape) const { for (int k = 0; k < nDim; k++) if ((*this)[k] < 0 || (*this)[k] >= shape[k]) return false; return true; }
+	void clip(std::array<int, nDim> const& shape) { for (int k = 0; k < nDim; k++) (*this)[k] = (*this)[k] < 0 ? 0 : ((*this)[k] >= shape[k] ? shape[k] - 1 : (*this)[k]); }
 	// first index fastest, like upstream's flat traversal
 	void moveToNextIndex(std::array<int, nDim> const& shape) {
 		for (int k = 0; k < nDim; k++) {

@@ -300,6 +300,47 @@ STEVI_API int32_t stevi_refine_disp_cost_interp(stevi_ctx* ctx, const stevi_arra
 STEVI_API int32_t stevi_refine_from_cost_volume(stevi_ctx* ctx, const stevi_array* cv, const stevi_array* idx, int32_t h_radius,
 									  int32_t v_radius, int32_t kernel, stevi_array* tcv_out, stevi_array* out);
 
+/* ---- feature-domain subpixel refinement (correlation/image_based_refinement.h) --------------------
+ * feat_l (H,Wl,F), feat_r (H,Wr,F) f32: the feature volumes the refinement works on (the reference's callers pass the zero-mean
+ * and / or normalised volumes of refined*FeatureVol, :1692-2424; any strides). The source is feat_r for RIGHT_TO_LEFT, feat_l
+ * otherwise; idx / out have the source's (H,W). The per-pixel fits are the reference's estimators — NCC, ZNCC:
+ * Optimization::sphericalAffineBestApproximation (optimization/sphericaloptimization.h:35-63); SSD, ZSSD:
+ * affineBestL2Approximation (l2optimization.h:48-63); SAD, ZSAD: affineBestL1Approximation (l1optimization.h:293-310) — solved
+ * from the fp64 Gram matrix of the vectors instead of Eigen's float QR: same solution, other rounding (compare with a
+ * tolerance: 1e-3 px). CC, ZCC and the other functions have no barycentric approximation in the reference either
+ * (matching_costs.h:442-457, :505-520): STEVI_E_UNSUPPORTED. */
+typedef enum { STEVI_QUEEN = 0, STEVI_ROOK = 1, STEVI_BISHOP = 2 } stevi_contiguity; /* utils/contiguity.h:31-35 */
+
+/* refineBarycentricDisp<matchFunc, dDir> (correlation/image_based_refinement.h:184-355): the source vector is fitted by the two
+ * affine pairs (target(jd), target(jd+1)) and (target(jd-1), target(jd)); a coefficient inside (0,1) whose interpolated vector
+ * compares better than the winner moves the disparity by that fraction. idx (H,W) i32 -> out (H,W) f32; pixels whose target
+ * column jd = j +- idx is within one column of the border keep idx (:214). */
+STEVI_API int32_t stevi_refine_barycentric_disp(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_l, const stevi_array* feat_r,
+									  const stevi_array* idx, int32_t direction, stevi_array* out);
+
+/* refineBarycentricSymmetricDisp<matchFunc, refineRadius, dDir> (:31-105): one fit over the 2*radius+1 target vectors around jd,
+ * out = idx + sum(coeff_p * p) when that is below one pixel; idx at the borders, at index 0 and at disp_width - 1 (:64-69).
+ * radius 1..3. SAD / ZSAD: STEVI_E_UNSUPPORTED (with more than two columns the reference runs a randomised descent,
+ * l1optimization.h:98-252, whose result depends on Eigen's Random()). */
+STEVI_API int32_t stevi_refine_barycentric_symmetric_disp(stevi_ctx* ctx, int32_t matchfunc, int32_t radius, const stevi_array* feat_l,
+												const stevi_array* feat_r, const stevi_array* idx, int32_t disp_width, int32_t direction,
+												stevi_array* out);
+
+/* refineBarycentric2dDisp<matchFunc, contiguity, dDir> (:675-880; symmetric = 0): for each of the four quadrants the source is
+ * fitted by the corner directions of the contiguity (utils/contiguity.h:139-164) and the winner; the best-scoring admissible
+ * fit moves the 2-D disparity. refineBarycentricSymmetric2dDisp (:1068-1241; symmetric = 1): one fit over all the directions of
+ * the contiguity (:98-135). feat_l, feat_r (H,W,F) of one size, idx (H,W,2) i32 (row, column displacement), search = {lower0,
+ * upper0, lower1, upper1} as for stevi_cost_volume_2d -> out (H,W,2) f32. NCC, ZNCC, SSD, ZSSD. */
+STEVI_API int32_t stevi_refine_barycentric_2d_disp(stevi_ctx* ctx, int32_t matchfunc, int32_t contiguity, int32_t symmetric,
+										 const stevi_array* feat_l, const stevi_array* feat_r, const stevi_array* idx,
+										 const int32_t search[4], int32_t direction, stevi_array* out);
+
+/* refineCostSymmetricDisp<matchFunc, dDir> (:1591-1690): the parabola through the winner's three costs, averaged with the
+ * parabola through the comparisons of the half-pixel source vector with the three target vectors. cv (H,W,D) f32 is the
+ * cost volume idx was taken from. CC .. ZSAD. */
+STEVI_API int32_t stevi_refine_cost_symmetric_disp(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_l, const stevi_array* feat_r,
+										 const stevi_array* idx, const stevi_array* cv, int32_t direction, stevi_array* out);
+
 /* ---- coarse-to-fine matching ---------------------------------------------------------------------------------- */
 
 /* meanFilter2D(h_radius, v_radius, in_data) (correlation/correlation_base.h:881-938 for (H,W), :941-1004 for (H,W,C) images):

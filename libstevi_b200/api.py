@@ -25,6 +25,7 @@ LEFT_TO_RIGHT, RIGHT_TO_LEFT = 0, 1
 TCV_SAME, TCV_REVERSED, TCV_BOTH = 0, 1, 2
 EQUIANGULAR, PARABOLA, GAUSSIAN = 0, 1, 2
 ISOTROPIC, ANISOTROPIC = 0, 1  # IsotropyHypothesis, cost_based_refinement.h:37-41
+QUEEN, ROOK, BISHOP = 0, 1, 2  # Contiguity::bidimensionalContiguity, utils/contiguity.h:31-35
 SCORE_FUNCS = (CC, NCC, ZCC, ZNCC)
 
 _NP2DT = {np.dtype(np.uint8): U8, np.dtype(np.uint16): U16, np.dtype(np.int32): I32, np.dtype(np.uint32): U32,
@@ -652,6 +653,136 @@ def refineDispCostInterpolation(tcv, idx, kernel=PARABOLA, ctx=None):
         return None
     ctx.check(rc)
     return out
+
+
+def _source_of(feat_l, feat_r, dDir):
+    return feat_r if dDir == RIGHT_TO_LEFT else feat_l
+
+
+def refineBarycentricDisp(matchFunc, feature_vol_l, feature_vol_r, selectedIndex, dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:184-355 (NCC, ZNCC, SSD, ZSSD, SAD, ZSAD). (H,W,F) f32 feature volumes, (H,W) i32 winners."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    out = _empty(feature_vol_l, _source_of(feature_vol_l, feature_vol_r, dDir).shape[:2], np.float32)
+    l, r, i, o = describe(feature_vol_l), describe(feature_vol_r), describe(selectedIndex), describe(out)
+    ctx.check(lib.stevi_refine_barycentric_disp(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), ctypes.byref(i), dDir, ctypes.byref(o)))
+    return out
+
+
+def refineBarycentricSymmetricDisp(matchFunc, feature_vol_l, feature_vol_r, selectedIndex, disp_width, refineRadius=1,
+                                   dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:31-105 (NCC, ZNCC, SSD, ZSSD; refineRadius 1..3)."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    out = _empty(feature_vol_l, _source_of(feature_vol_l, feature_vol_r, dDir).shape[:2], np.float32)
+    l, r, i, o = describe(feature_vol_l), describe(feature_vol_r), describe(selectedIndex), describe(out)
+    ctx.check(lib.stevi_refine_barycentric_symmetric_disp(ctx.handle, matchFunc, refineRadius, ctypes.byref(l), ctypes.byref(r),
+                                                          ctypes.byref(i), disp_width, dDir, ctypes.byref(o)))
+    return out
+
+
+def refineBarycentric2dDisp(matchFunc, feature_vol_l, feature_vol_r, selectedIndices, searchWindows, contiguity=QUEEN,
+                            dDir=RIGHT_TO_LEFT, symmetric=False, ctx=None):
+    """image_based_refinement.h:675-880; ``symmetric=True``: refineBarycentricSymmetric2dDisp, :1068-1241."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    out = _empty(feature_vol_l, tuple(feature_vol_l.shape[:2]) + (2,), np.float32)
+    l, r, i, o = describe(feature_vol_l), describe(feature_vol_r), describe(selectedIndices), describe(out)
+    ctx.check(lib.stevi_refine_barycentric_2d_disp(ctx.handle, matchFunc, contiguity, int(bool(symmetric)), ctypes.byref(l), ctypes.byref(r),
+                                                   ctypes.byref(i), _search4(searchWindows)[0], dDir, ctypes.byref(o)))
+    return out
+
+
+def refineBarycentricSymmetric2dDisp(matchFunc, feature_vol_l, feature_vol_r, selectedIndices, searchWindows, contiguity=QUEEN,
+                                     dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:1068-1241."""
+    return refineBarycentric2dDisp(matchFunc, feature_vol_l, feature_vol_r, selectedIndices, searchWindows, contiguity, dDir, True, ctx)
+
+
+def refineCostSymmetricDisp(matchFunc, feature_vol_l, feature_vol_r, selectedIndex, cost_volume, dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:1591-1690 (CC .. ZSAD)."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    out = _empty(feature_vol_l, _source_of(feature_vol_l, feature_vol_r, dDir).shape[:2], np.float32)
+    l, r, i, c, o = (describe(feature_vol_l), describe(feature_vol_r), describe(selectedIndex), describe(cost_volume), describe(out))
+    ctx.check(lib.stevi_refine_cost_symmetric_disp(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), ctypes.byref(i), ctypes.byref(c),
+                                                   dDir, ctypes.byref(o)))
+    return out
+
+
+ZERO_MEAN_FUNCS = (ZCC, ZNCC, ZSSD, ZSAD)
+NORMALIZED_FUNCS = (NCC, ZNCC)
+
+
+def _refinement_volumes(matchFunc, feature_vol_l, feature_vol_r, preNormalize, ctx):
+    """The volumes refined*FeatureVol (image_based_refinement.h:1692-1765, :1854-1927) matches on and refines on: the matching
+    volumes are the function's processed features; the refinement runs on the zero-mean (not normalised) ones unless
+    ``preNormalize``. Zero mean only = the processed features of the function's un-normalised sibling."""
+    match = [getFeatureVolumeForMatchFuncFromFeatures(matchFunc, f, ctx=ctx) for f in (feature_vol_l, feature_vol_r)]
+    if matchFunc not in NORMALIZED_FUNCS or preNormalize:
+        return match, match
+    if matchFunc in ZERO_MEAN_FUNCS:
+        return match, [getFeatureVolumeForMatchFuncFromFeatures(ZCC, f, ctx=ctx) for f in (feature_vol_l, feature_vol_r)]
+    return match, [feature_vol_l, feature_vol_r]
+
+
+def refinedBarycentricDispFeatureVol(matchFunc, feature_vol_l, feature_vol_r, searchRange, preNormalize=False, dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:1854-1927: process the features, aggregateCost, extractSelectedIndex, refineBarycentricDisp."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    match, fine = _refinement_volumes(matchFunc, feature_vol_l, feature_vol_r, preNormalize, ctx)
+    cv = aggregateCost(matchFunc, match[0], match[1], searchRange, dDir=dDir, ctx=ctx)
+    if cv is None:
+        return None
+    idx = extractSelectedIndex(cv, strategy_of(matchFunc), ctx=ctx)
+    return refineBarycentricDisp(matchFunc, fine[0], fine[1], idx, dDir, ctx=ctx)
+
+
+def refinedBarycentricSymmetricDispFeatureVol(matchFunc, feature_vol_l, feature_vol_r, searchRange, preNormalize=False, refineRadius=1,
+                                              dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:1692-1765."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    match, fine = _refinement_volumes(matchFunc, feature_vol_l, feature_vol_r, preNormalize, ctx)
+    cv = aggregateCost(matchFunc, match[0], match[1], searchRange, dDir=dDir, ctx=ctx)
+    if cv is None:
+        return None
+    idx = extractSelectedIndex(cv, strategy_of(matchFunc), ctx=ctx)
+    return refineBarycentricSymmetricDisp(matchFunc, fine[0], fine[1], idx, searchRange, refineRadius, dDir, ctx=ctx)
+
+
+def refinedCostSymmetricDispFeatureVol(matchFunc, feature_vol_l, feature_vol_r, searchRange, preNormalize=False, dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:2351-2424."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    match, fine = _refinement_volumes(matchFunc, feature_vol_l, feature_vol_r, preNormalize, ctx)
+    cv = aggregateCost(matchFunc, match[0], match[1], searchRange, dDir=dDir, ctx=ctx)
+    if cv is None:
+        return None
+    idx = extractSelectedIndex(cv, strategy_of(matchFunc), ctx=ctx)
+    return refineCostSymmetricDisp(matchFunc, fine[0], fine[1], idx, cv, dDir, ctx=ctx)
+
+
+def refinedBarycentricDisp(matchFunc, img_l, img_r, h_radius, v_radius, searchRange, preNormalize=False, dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:2502-2544: unfold both images, then refinedBarycentricDispFeatureVol. None where the reference
+    returns an empty array (heights differ)."""
+    if img_l.shape[0] != img_r.shape[0]:
+        return None
+    ctx = _ctx_for(ctx, img_l)
+    fl, fr = (unfold(h_radius, v_radius, im, T_O=np.float32, ctx=ctx) for im in (img_l, img_r))
+    return refinedBarycentricDispFeatureVol(matchFunc, fl, fr, searchRange, preNormalize, dDir, ctx=ctx)
+
+
+def refinedBarycentricSymmetricDisp(matchFunc, img_l, img_r, h_radius, v_radius, searchRange, preNormalize=False, refineRadius=1,
+                                    dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:2426-2470."""
+    if img_l.shape[0] != img_r.shape[0]:
+        return None
+    ctx = _ctx_for(ctx, img_l)
+    fl, fr = (unfold(h_radius, v_radius, im, T_O=np.float32, ctx=ctx) for im in (img_l, img_r))
+    return refinedBarycentricSymmetricDispFeatureVol(matchFunc, fl, fr, searchRange, preNormalize, refineRadius, dDir, ctx=ctx)
+
+
+def refinedCostSymmetricDisp(matchFunc, img_l, img_r, h_radius, v_radius, searchRange, preNormalize=False, dDir=RIGHT_TO_LEFT, ctx=None):
+    """image_based_refinement.h:2573-2598."""
+    if img_l.shape[0] != img_r.shape[0]:
+        return None
+    ctx = _ctx_for(ctx, img_l)
+    fl, fr = (unfold(h_radius, v_radius, im, T_O=np.float32, ctx=ctx) for im in (img_l, img_r))
+    return refinedCostSymmetricDispFeatureVol(matchFunc, fl, fr, searchRange, preNormalize, dDir, ctx=ctx)
 
 
 def refineFromCostVolume(cv, idx, h_radius, v_radius, kernel=PARABOLA, return_tcv=False, ctx=None):

@@ -419,6 +419,60 @@ int32_t stevi_refine_from_cost_volume(stevi_ctx* c, const stevi_array* cv, const
 	return st.finish();
 }
 
+int32_t stevi_refine_barycentric_disp(stevi_ctx* c, int32_t mf, const stevi_array* fl, const stevi_array* fr, const stevi_array* idx,
+									  int32_t direction, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vi, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine_barycentric_dev(c, mf, vl, vr, vi, direction, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_barycentric_symmetric_disp(stevi_ctx* c, int32_t mf, int32_t radius, const stevi_array* fl, const stevi_array* fr,
+												const stevi_array* idx, int32_t disp_width, int32_t direction, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vi, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine_barycentric_symmetric_dev(c, mf, radius, vl, vr, vi, disp_width, direction, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_barycentric_2d_disp(stevi_ctx* c, int32_t mf, int32_t contiguity, int32_t symmetric, const stevi_array* fl,
+										 const stevi_array* fr, const stevi_array* idx, const int32_t search[4], int32_t direction,
+										 stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vi, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine_barycentric_2d_dev(c, mf, contiguity, symmetric, vl, vr, vi, search, direction, vo));
+	return st.finish();
+}
+
+int32_t stevi_refine_cost_symmetric_disp(stevi_ctx* c, int32_t mf, const stevi_array* fl, const stevi_array* fr, const stevi_array* idx,
+										 const stevi_array* cv, int32_t direction, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vi, vc, vo;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.in(idx, vi, "idx"));
+	STEVI_TRY(st.in(cv, vc, "cv"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(refine_cost_symmetric_dev(c, mf, vl, vr, vi, vc, direction, vo));
+	return st.finish();
+}
+
 int32_t stevi_mean_filter_2d(stevi_ctx* c, const stevi_array* img, int32_t hr, int32_t vr, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);

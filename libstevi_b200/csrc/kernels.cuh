@@ -85,6 +85,14 @@ int32_t truncated_cv2d_dev(stevi_ctx* c, const View& cv, const View& idx, int ra
 int32_t refine2d_interp_dev(stevi_ctx* c, const View& tcv, const View& raw, int kernel, int isotropy, const View& out);
 int32_t refine2d_patch_dev(stevi_ctx* c, const View& tcv, const View& raw, int kernel, const View& out);
 
+// barycentric.cu: feature-domain refinement (image_based_refinement.h); idx2 / out2 are (H,W,2)
+int32_t refine_barycentric_dev(stevi_ctx* c, int mf, const View& fl, const View& fr, const View& idx, int direction, const View& out);
+int32_t refine_barycentric_symmetric_dev(stevi_ctx* c, int mf, int radius, const View& fl, const View& fr, const View& idx, int disp_width,
+										 int direction, const View& out);
+int32_t refine_barycentric_2d_dev(stevi_ctx* c, int mf, int contiguity, int symmetric, const View& fl, const View& fr, const View& idx2,
+								  const int32_t* search, int direction, const View& out2);
+int32_t refine_cost_symmetric_dev(stevi_ctx* c, int mf, const View& fl, const View& fr, const View& idx, const View& cv, int direction, const View& out);
+
 // aggregate.cu: variableCostVolumeAggregation (guided_cost_filtering.h:102-176)
 int32_t var_aggregate_dev(stevi_ctx* c, const View& cv, const View& win, const View& out);
 

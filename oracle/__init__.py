@@ -5,6 +5,8 @@ ctypes/numpy front-end to the two CPU checkers:
 * ``oracle.port``  — ``oracle/libstevi_oracle.so``: our plain-C restatement (``oracle/stevi_oracle.c``).
 * ``oracle.ref``   — ``oracle/_ref/libstevi_ref.so``: the UNMODIFIED reference headers compiled from
   ``/root/reference`` by ``oracle/Makefile`` (``None`` when it was never built).
+* ``oracle.ref_ibr`` — ``oracle/_ref/libstevi_ref_ibr.so``: the reference's ``correlation/image_based_refinement.h``,
+  unmodified, with the Eigen calls inside it served by the stand-in of ``oracle/shims/Eigen`` + ``oracle/small_qr.h``.
 
 Both expose the same method names. Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
 ``cpu_baseline`` / ``--impl reference`` legs may import this module; ``libstevi_b200`` never does.
@@ -389,6 +391,43 @@ class _Checker:
         return out if rc == 0 else None
 
 
+    # --- feature-domain refinement (image_based_refinement.h) --------------------------
+    def refine_barycentric(self, mf, fl, fr, idx, direction=R2L):
+        fl, fr, idx = _c(fl, np.float32), _c(fr, np.float32), _c(idx, np.int32)
+        out = np.empty(idx.shape, np.float32)
+        rc = self._f("refine_barycentric_disp")(mf, _p(fl), _p(fr), fl.shape[0], fl.shape[1], fr.shape[1], fl.shape[2], _p(idx), direction, _p(out))
+        return out if rc == 0 else None
+
+    def refine_barycentric_symmetric(self, mf, radius, fl, fr, idx, width, direction=R2L):
+        fl, fr, idx = _c(fl, np.float32), _c(fr, np.float32), _c(idx, np.int32)
+        out = np.empty(idx.shape, np.float32)
+        rc = self._f("refine_barycentric_symmetric_disp")(mf, radius, _p(fl), _p(fr), fl.shape[0], fl.shape[1], fr.shape[1], fl.shape[2],
+                                                          _p(idx), width, direction, _p(out))
+        return out if rc == 0 else None
+
+    def refine_barycentric_2d(self, mf, contiguity, symmetric, fl, fr, idx, search, direction=R2L):
+        fl, fr, idx = _c(fl, np.float32), _c(fr, np.float32), _c(idx, np.int32)
+        so = np.asarray(search, np.int32)
+        out = np.empty(idx.shape, np.float32)
+        rc = self._f("refine_barycentric_2d_disp")(mf, contiguity, int(bool(symmetric)), _p(fl), _p(fr), fl.shape[0], fl.shape[1], fl.shape[2],
+                                                   _p(idx), _p(so), direction, _p(out))
+        return out if rc == 0 else None
+
+    def refine_cost_symmetric(self, mf, fl, fr, idx, cv, direction=R2L):
+        fl, fr, idx, cv = _c(fl, np.float32), _c(fr, np.float32), _c(idx, np.int32), _c(cv, np.float32)
+        out = np.empty(idx.shape, np.float32)
+        rc = self._f("refine_cost_symmetric_disp")(mf, _p(fl), _p(fr), fl.shape[0], fl.shape[1], fr.shape[1], fl.shape[2], _p(idx), _p(cv),
+                                                   cv.shape[2], direction, _p(out))
+        return out if rc == 0 else None
+
+    def refined_barycentric_disp(self, mf, left, right, hr, vr, width, prenormalize=False):
+        left, right = _c(left, np.float32), _c(right, np.float32)
+        out = np.empty(right.shape, np.float32)
+        rc = self._f("refined_barycentric_disp_f32")(mf, _p(left), _p(right), left.shape[0], left.shape[1], right.shape[1], hr, vr, width,
+                                                     int(bool(prenormalize)), _p(out))
+        return out if rc == 0 else None
+
+
 def _load():
     port_path = os.path.join(_HERE, "libstevi_oracle.so")
     ref_path = os.path.join(_HERE, "_ref", "libstevi_ref.so")
@@ -398,7 +437,11 @@ def _load():
     p.lib.orc_refine_cost_triplet.restype = ctypes.c_float
     p.lib.orc_round_through_float.restype = ctypes.c_uint32
     r = _Checker(ref_path, "ref_") if os.path.exists(ref_path) else None
-    return p, r
+    # correlation/image_based_refinement.h compiled as its own library (oracle/ref_wrap_ibr.cpp): the reference's code with the
+    # stand-in linear algebra of oracle/shims/Eigen
+    ibr_path = os.path.join(_HERE, "_ref", "libstevi_ref_ibr.so")
+    i = _Checker(ibr_path, "ref_") if os.path.exists(ibr_path) else None
+    return p, r, i
 
 
-port, ref = _load()
+port, ref, ref_ibr = _load()

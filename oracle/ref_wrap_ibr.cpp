@@ -1,0 +1,134 @@
+// TEST INFRASTRUCTURE — not product code. Only tests/ may load the library built from this file.
+//
+// extern "C" wrappers over the UNMODIFIED reference header correlation/image_based_refinement.h (included from $STEVI_REF,
+// never copied into this repo), built by oracle/Makefile into oracle/_ref/libstevi_ref_ibr.so (its own translation unit so
+// that it compiles beside ref_wrap.cpp). The reference's code runs as it is — its border rules, its comparisons, its float
+// loops; the Eigen calls inside it (small vectors, FullPivHouseholderQR::solve) are served by the stand-in of
+// oracle/shims/Eigen (+ oracle/small_qr.h): Eigen itself is not in this image. All buffers are dense C-order.
+#include <cstdint>
+#include <cstring>
+#include <cmath>
+#include <cassert>
+#include <omp.h>
+
+#include <correlation/image_based_refinement.h>
+
+using namespace StereoVision;
+using namespace StereoVision::Correlation;
+namespace MD = Multidim;
+
+namespace {
+
+template<typename T> MD::Array<T, 2> view2(const T* p, int h, int w) { return MD::Array<T, 2>(const_cast<T*>(p), {h, w}, {w, 1}, false); }
+template<typename T> MD::Array<T, 3> view3(const T* p, int h, int w, int c) { return MD::Array<T, 3>(const_cast<T*>(p), {h, w, c}, {w * c, c, 1}, false); }
+void out2(MD::Array<float, 2> const& a, float* out) {
+	auto s = a.shape();
+	for (int i = 0; i < s[0]; i++) for (int j = 0; j < s[1]; j++) out[size_t(i) * s[1] + j] = a.valueUnchecked(i, j);
+}
+void out3(MD::Array<float, 3> const& a, float* out) {
+	auto s = a.shape();
+	for (int i = 0; i < s[0]; i++) for (int j = 0; j < s[1]; j++) for (int k = 0; k < s[2]; k++)
+		out[(size_t(i) * s[1] + j) * s[2] + k] = a.valueUnchecked(i, j, k);
+}
+
+// the 1-column overload of leastAbsoluteDifferences (l1optimization.h:257-283) sorts break points that can be NaN (0/0);
+// the wrapper runs it single-threaded like everything else here so a result is at least repeatable
+template<matchingFunctions F, dispDirection D>
+int bary1d(const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* idx, int wi, float* out) {
+	auto r = refineBarycentricDisp<F, D>(view3(fl, h, wl, f), view3(fr, h, wr, f), view2(idx, h, wi));
+	out2(r, out);
+	return 0;
+}
+template<matchingFunctions F, int R, dispDirection D>
+int barysym1d(const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* idx, int wi, int width, float* out) {
+	auto r = refineBarycentricSymmetricDisp<F, R, D>(view3(fl, h, wl, f), view3(fr, h, wr, f), view2(idx, h, wi), width);
+	out2(r, out);
+	return 0;
+}
+template<matchingFunctions F, Contiguity::bidimensionalContiguity C, dispDirection D>
+int bary2d(const float* fl, const float* fr, int h, int w, int f, const int32_t* idx, const int* so, int sym, float* out) {
+	searchOffset<2> win(so[0], so[1], so[2], so[3]);
+	MD::Array<int32_t, 3> sel(const_cast<int32_t*>(idx), {h, w, 2}, {w * 2, 2, 1}, false);
+	auto r = sym ? refineBarycentricSymmetric2dDisp<F, C, D>(view3(fl, h, w, f), view3(fr, h, w, f), sel, win)
+				 : refineBarycentric2dDisp<F, C, D>(view3(fl, h, w, f), view3(fr, h, w, f), sel, win);
+	out3(r, out);
+	return 0;
+}
+template<matchingFunctions F, dispDirection D>
+int costsym(const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* idx, const float* cv, int wi, int d, float* out) {
+	auto r = refineCostSymmetricDisp<F, D>(view3(fl, h, wl, f), view3(fr, h, wr, f), view2(idx, h, wi), view3(cv, h, wi, d));
+	out2(r, out);
+	return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+void ref_ibr_set_num_threads(int n) { omp_set_num_threads(n); }
+
+#define IBR_MF(...) \
+	switch (matchfunc) { \
+	case 1: { constexpr auto F = matchingFunctions::NCC; __VA_ARGS__; } \
+	case 5: { constexpr auto F = matchingFunctions::ZNCC; __VA_ARGS__; } \
+	case 2: { constexpr auto F = matchingFunctions::SSD; __VA_ARGS__; } \
+	case 6: { constexpr auto F = matchingFunctions::ZSSD; __VA_ARGS__; } \
+	default: break; }
+#define IBR_MF_L1(...) \
+	switch (matchfunc) { \
+	case 3: { constexpr auto F = matchingFunctions::SAD; __VA_ARGS__; } \
+	case 7: { constexpr auto F = matchingFunctions::ZSAD; __VA_ARGS__; } \
+	default: break; }
+
+// image_based_refinement.h:184-355. matchfunc: the stevi_matchfunc numbering (c_api.h); dir 1 = RightToLeft
+int ref_refine_barycentric_disp(int matchfunc, const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* idx, int dir, float* out) {
+	const int wi = dir ? wr : wl;
+	if (dir) { IBR_MF(return (bary1d<F, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, wi, out))) IBR_MF_L1(return (bary1d<F, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, wi, out))) }
+	else { IBR_MF(return (bary1d<F, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, wi, out))) IBR_MF_L1(return (bary1d<F, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, wi, out))) }
+	return 3;
+}
+
+// image_based_refinement.h:31-105 (refineRadius 1 or 2)
+int ref_refine_barycentric_symmetric_disp(int matchfunc, int radius, const float* fl, const float* fr, int h, int wl, int wr, int f,
+										  const int32_t* idx, int width, int dir, float* out) {
+	const int wi = dir ? wr : wl;
+	if (radius == 1) {
+		if (dir) { IBR_MF(return (barysym1d<F, 1, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, wi, width, out))) }
+		else { IBR_MF(return (barysym1d<F, 1, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, wi, width, out))) }
+	} else if (radius == 2) {
+		if (dir) { IBR_MF(return (barysym1d<F, 2, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, wi, width, out))) }
+		else { IBR_MF(return (barysym1d<F, 2, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, wi, width, out))) }
+	}
+	return 3;
+}
+
+// image_based_refinement.h:675-880 (sym 0) and :1068-1241 (sym 1). contiguity: 0 Queen, 1 Rook, 2 Bishop
+int ref_refine_barycentric_2d_disp(int matchfunc, int contiguity, int sym, const float* fl, const float* fr, int h, int w, int f,
+								   const int32_t* idx, const int* so, int dir, float* out) {
+#define IBR_C(CONT) \
+	if (dir) { IBR_MF(return (bary2d<F, CONT, dispDirection::RightToLeft>(fl, fr, h, w, f, idx, so, sym, out))) } \
+	else { IBR_MF(return (bary2d<F, CONT, dispDirection::LeftToRight>(fl, fr, h, w, f, idx, so, sym, out))) }
+	if (contiguity == 0) { IBR_C(Contiguity::Queen) }
+	else if (contiguity == 1) { IBR_C(Contiguity::Rook) }
+	else if (contiguity == 2) { IBR_C(Contiguity::Bishop) }
+	return 3;
+}
+
+// image_based_refinement.h:1591-1690
+int ref_refine_cost_symmetric_disp(int matchfunc, const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* idx,
+								   const float* cv, int d, int dir, float* out) {
+	const int wi = dir ? wr : wl;
+	if (dir) { IBR_MF(return (costsym<F, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) IBR_MF_L1(return (costsym<F, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) }
+	else { IBR_MF(return (costsym<F, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) IBR_MF_L1(return (costsym<F, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) }
+	return 3;
+}
+
+// refinedBarycentricDisp on images (image_based_refinement.h:2502-2544): unfold, features, cost volume, winner, refinement
+int ref_refined_barycentric_disp_f32(int matchfunc, const float* l, const float* r, int h, int wl, int wr, int hr, int vr, int width,
+									 int prenormalize, float* out) {
+	IBR_MF({ auto res = refinedBarycentricDisp<F, float, float, 2, dispDirection::RightToLeft>(view2(l, h, wl), view2(r, h, wr), uint8_t(hr), uint8_t(vr), width, prenormalize != 0);
+			 out2(res, out); return 0; })
+	return 3;
+}
+
+}

@@ -12,6 +12,7 @@
  * All buffers are dense, C-order (last index fastest). File:line citations are relative to /root/reference.
  * Compiled with -ffp-contract=off: the float operation ORDER below follows the reference's loops.
  */
+#define _GNU_SOURCE /* qsort_r */
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -940,3 +941,259 @@ int NAME(const float* mean, const T* in, int h, int w, int c, int hr, int vr, fl
 }
 ORC_SIGMA_FILTER(orc_sigma_filter_f32, float)
 ORC_SIGMA_FILTER(orc_sigma_filter_u8, uint8_t)
+
+/* ==== correlation/image_based_refinement.h: feature-domain subpixel refinement =================================================
+ * The reference builds F x (K+1) Eigen matrices per pixel and solves with Eigen::FullPivHouseholderQR (Eigen 3.3, absent from this
+ * image); the least-squares solves below go through oracle/small_qr.h, the same published algorithm in float. Everything else —
+ * the affine-space reduction, the spherical fit, the weighted median, the border rules, the score comparisons — follows the
+ * reference line by line in float. Pinned against the reference's own code compiled with the same stand-in solver
+ * (oracle/_ref/libstevi_ref_ibr.so) and against its known-answer tests (tests/test_oracle_pinning.py). */
+#include "small_qr.h"
+
+int orc_qr_lstsq(int m, int n, const float* A, const float* b, float* x) { stevi_qr_lstsq(m, n, A, b, x); return 0; }
+
+#define IBR_MAXC 9 /* columns of the largest system: Queen neighbourhood + centre */
+
+static int ibr_family(int mf) { /* matching_costs.h:435-439, :475-479, :498-502, :538-542, :561-565, :584-588 */
+	if (mf == MF_NCC || mf == MF_ZNCC) return 0;
+	if (mf == MF_SSD || mf == MF_ZSSD) return 1;
+	if (mf == MF_SAD || mf == MF_ZSAD) return 2;
+	return -1;
+}
+
+/* l1optimization.h:33-60 (weighted_median_index) on the one-unknown overload of leastAbsoluteDifferences (:257-283) */
+static int ibr_cmp_key(const void* a, const void* b, void* el) {
+	const float* e = (const float*)el;
+	float x = e[*(const int*)a], y = e[*(const int*)b];
+	return x < y ? -1 : (y < x ? 1 : 0);
+}
+static float ibr_l1_one_unknown(const float* M, const float* rhs, int F) {
+	float* t = (float*)malloc(sizeof(float) * 2 * F + sizeof(int) * F);
+	float* w = t + F;
+	int* key = (int*)(w + F);
+	for (int i = 0; i < F; i++) { t[i] = 0.f; w[i] = 0.f; }
+	for (int i = 0; i < F; i++) {
+		float o = M[i];
+		w[i] = fabsf(o);
+		t[i] = rhs[i] / o;
+		if (isnan(t[F - 1]) || isinf(t[F - 1])) { w[i] = 0.f; t[i] = -INFINITY; } /* (sic) the test reads t_breaks.back(), :273 */
+	}
+	for (int i = 0; i < F; i++) key[i] = i;
+	float sum = 0.f;
+	for (int i = 0; i < F; i++) sum += w[i];
+	qsort_r(key, F, sizeof(int), ibr_cmp_key, t);
+	float partial = 0.f, res = t[key[F - 1]];
+	for (int i = 0; i < F; i++) {
+		float tmp = 2 * w[key[i]];
+		if (partial + tmp > sum) { res = t[key[i]]; break; }
+		partial += tmp;
+	}
+	free(t);
+	return res;
+}
+
+/* barycentricBestApproximation(A, b): A is F x n column-major (A[c + k*F]), origin of the affine space = last column
+ * (affine_utils.h:44-57); coeffs gets n values. Returns 0 when the family has no such system (L1 with more than one unknown). */
+static int ibr_best_approximation(int family, const float* A, const float* b, int F, int n, float* coeffs) {
+	const int K = n - 1;
+	float* M = (float*)malloc(sizeof(float) * (size_t)F * (K + 4));
+	float* rhs = M + (size_t)F * K;
+	float* bperp = rhs + F;
+	float* aperp = bperp + F;
+	const float* aK = A + (size_t)K * F;
+	float alpha[IBR_MAXC], x[IBR_MAXC];
+	for (int k = 0; k < K; k++) for (int c = 0; c < F; c++) M[c + (size_t)k * F] = A[c + (size_t)k * F] - aK[c];
+	if (family == 1) { /* l2optimization.h:48-63 */
+		for (int c = 0; c < F; c++) rhs[c] = b[c] - aK[c];
+		stevi_qr_lstsq(F, K, M, rhs, alpha);
+	} else if (family == 2) { /* l1optimization.h:293-310 */
+		if (K != 1) { free(M); return 0; }
+		for (int c = 0; c < F; c++) rhs[c] = b[c] - aK[c];
+		alpha[0] = ibr_l1_one_unknown(M, rhs, F);
+	} else { /* sphericaloptimization.h:35-63 */
+		stevi_qr_lstsq(F, n, A, b, x);
+		for (int c = 0; c < F; c++) { float s = 0.f; for (int k = 0; k < n; k++) s += A[c + (size_t)k * F] * x[k]; bperp[c] = s; }
+		stevi_qr_lstsq(F, K, M, aK, x);
+		for (int c = 0; c < F; c++) { float s = 0.f; for (int k = 0; k < K; k++) s += M[c + (size_t)k * F] * x[k]; aperp[c] = aK[c] - s; }
+		float aa = 0.f, ab = 0.f;
+		for (int c = 0; c < F; c++) aa += aperp[c] * aperp[c];
+		for (int c = 0; c < F; c++) ab += aperp[c] * bperp[c];
+		float g = aa / ab;
+		for (int c = 0; c < F; c++) rhs[c] = g * bperp[c] - aK[c];
+		stevi_qr_lstsq(F, K, M, rhs, alpha);
+	}
+	float sum = 0.f;
+	for (int k = 0; k < K; k++) { coeffs[k] = alpha[k]; sum += alpha[k]; }
+	coeffs[K] = 1 - sum; /* affine_utils.h:83-97 */
+	free(M);
+	return 1;
+}
+
+static float ibr_norm(const float* v, int F) { float s = 0.f; for (int c = 0; c < F; c++) s += v[c] * v[c]; return sqrtf(s); }
+/* featureComparison of the (normalised when the function is) vectors s and t: image_based_refinement.h:253-306 */
+static float ibr_compare(int mf, const float* s, const float* t, int F, float* tmp) {
+	float* a = tmp; float* b = tmp + F;
+	if (mf_normalized(mf)) {
+		float ns = ibr_norm(s, F), nt = ibr_norm(t, F);
+		for (int c = 0; c < F; c++) { a[c] = s[c] / ns; b[c] = t[c] / nt; }
+	} else { memcpy(a, s, sizeof(float) * F); memcpy(b, t, sizeof(float) * F); }
+	return compare_f32(mf, a, b, F);
+}
+
+/* image_based_refinement.h:184-355 */
+int orc_refine_barycentric_disp(int mf, const float* fl, const float* fr, int h, int wl, int wr, int F, const int32_t* idx, int dir, float* out) {
+	const int family = ibr_family(mf);
+	if (family < 0) return 3;
+	const float* src = dir ? fr : fl; const float* tgt = dir ? fl : fr;
+	const int ws = dir ? wr : wl, wt = dir ? wl : wr, sign = dir ? 1 : -1, score_mode = mf_strategy(mf) == STRAT_SCORE;
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) {
+		float* buf = (float*)malloc(sizeof(float) * F * 5);
+		float* A = buf; float* interp = buf + 2 * F; float* tmp = buf + 3 * F;
+		for (int j = 0; j < ws; j++) {
+			int d = idx[(size_t)i * ws + j], jd = j + sign * d;
+			if (jd < 1 || jd + 1 >= ws) { out[(size_t)i * ws + j] = (float)d; continue; }
+			const float* s = src + ((size_t)i * ws + j) * F;
+			const float* t0 = tgt + ((size_t)i * wt + jd) * F;
+			float cp[2], cm[2];
+			memcpy(A, t0, sizeof(float) * F); memcpy(A + F, t0 + F, sizeof(float) * F);
+			ibr_best_approximation(family, A, s, F, 2, cp);
+			float score = ibr_compare(mf, s, t0, F, tmp), delta = 0.f;
+			float dplus = cp[1];
+			if (dplus > 0 && dplus < 1) {
+				for (int c = 0; c < F; c++) interp[c] = A[c] * cp[0] + A[F + c] * cp[1];
+				float sc = ibr_compare(mf, s, interp, F, tmp);
+				if (score_mode ? sc > score : sc < score) { score = sc; delta = dplus; }
+			}
+			memcpy(A, t0 - F, sizeof(float) * F); memcpy(A + F, t0, sizeof(float) * F);
+			ibr_best_approximation(family, A, s, F, 2, cm);
+			float dminus = cm[0];
+			if (dminus > 0 && dminus < 1) {
+				for (int c = 0; c < F; c++) interp[c] = A[c] * cm[0] + A[F + c] * cm[1];
+				float sc = ibr_compare(mf, s, interp, F, tmp);
+				if (score_mode ? sc > score : sc < score) { score = sc; delta = -dminus; }
+			}
+			out[(size_t)i * ws + j] = d + sign * delta;
+		}
+		free(buf);
+	}
+	return 0;
+}
+
+/* image_based_refinement.h:31-105 */
+int orc_refine_barycentric_symmetric_disp(int mf, int radius, const float* fl, const float* fr, int h, int wl, int wr, int F,
+										  const int32_t* idx, int width, int dir, float* out) {
+	const int family = ibr_family(mf);
+	if (family < 0 || family == 2 || radius < 1 || 2 * radius + 1 > IBR_MAXC) return 3;
+	const float* src = dir ? fr : fl; const float* tgt = dir ? fl : fr;
+	const int ws = dir ? wr : wl, wt = dir ? wl : wr, sign = dir ? 1 : -1, n = 2 * radius + 1;
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) {
+		float* A = (float*)malloc(sizeof(float) * F * n);
+		for (int j = 0; j < ws; j++) {
+			int d = idx[(size_t)i * ws + j], jd = j + sign * d;
+			float res = (float)d;
+			if (!(j < 0 || j + 1 >= ws) && !(jd - radius < 0 || jd + 1 > ws - radius) && !(d == 0 || d + 1 >= width)) {
+				float co[IBR_MAXC];
+				for (int p = -radius; p <= radius; p++) memcpy(A + (size_t)(p + radius) * F, tgt + ((size_t)i * wt + jd + p) * F, sizeof(float) * F);
+				ibr_best_approximation(family, A, src + ((size_t)i * ws + j) * F, F, n, co);
+				float delta = 0.f;
+				for (int p = -radius; p <= radius; p++) delta += co[p + radius] * (float)p;
+				if (fabsf(delta) < 1) res = d + delta;
+			}
+			out[(size_t)i * ws + j] = res;
+		}
+		free(A);
+	}
+	return 0;
+}
+
+/* image_based_refinement.h:675-880 (sym 0) and :1068-1241 (sym 1); contiguity 0 Queen, 1 Rook, 2 Bishop (utils/contiguity.h:98-164) */
+int orc_refine_barycentric_2d_disp(int mf, int contiguity, int sym, const float* fl, const float* fr, int h, int w, int F,
+								   const int32_t* idx, const int* so, int dir, float* out) {
+	static const int corner[3][3][2] = {{{1, 1}, {1, 0}, {0, 1}}, {{1, 0}, {0, 1}, {0, 0}}, {{1, 1}, {0, 0}, {0, 0}}};
+	static const int ncorner[3] = {3, 2, 1};
+	static const int dirs[3][8][2] = {{{1, 1}, {1, 0}, {1, -1}, {0, 1}, {0, -1}, {-1, 1}, {-1, 0}, {-1, -1}},
+									  {{1, 0}, {0, 1}, {0, -1}, {-1, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}},
+									  {{1, 1}, {1, -1}, {-1, 1}, {-1, -1}, {0, 0}, {0, 0}, {0, 0}, {0, 0}}};
+	static const int ndirs[3] = {8, 4, 4};
+	const int family = ibr_family(mf);
+	if (family < 0 || family == 2 || contiguity < 0 || contiguity > 2) return 3;
+	const float* src = dir ? fr : fl; const float* tgt = dir ? fl : fr;
+	const int score_mode = mf_strategy(mf) == STRAT_SCORE, K = sym ? ndirs[contiguity] : ncorner[contiguity], nsys = sym ? 1 : 4;
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) {
+		float* buf = (float*)malloc(sizeof(float) * F * (IBR_MAXC + 3));
+		float* A = buf; float* interp = buf + (size_t)IBR_MAXC * F; float* tmp = interp + F;
+		for (int j = 0; j < w; j++) {
+			int d0 = idx[((size_t)i * w + j) * 2], d1 = idx[((size_t)i * w + j) * 2 + 1], id = i + d0, jd = j + d1;
+			float dd0 = 0.f, dd1 = 0.f;
+			if (!(id < 1 || id + 1 >= h) && !(jd < 1 || jd + 1 >= w) && !(d0 < so[0] || d0 > so[1]) && !(d1 < so[2] || d1 > so[3])) {
+				const float* s = src + ((size_t)i * w + j) * F;
+				const float* t0 = tgt + ((size_t)id * w + jd) * F;
+				float score = ibr_compare(mf, s, t0, F, tmp);
+				for (int q = 0; q < nsys; q++) {
+					int sx = sym ? 1 : (q < 2 ? 1 : -1), sy = sym ? 1 : ((q & 1) ? -1 : 1), di[IBR_MAXC], dj[IBR_MAXC];
+					float co[IBR_MAXC];
+					for (int k = 0; k < K; k++) {
+						di[k] = (sym ? dirs[contiguity][k][0] : corner[contiguity][k][0]) * sx;
+						dj[k] = (sym ? dirs[contiguity][k][1] : corner[contiguity][k][1]) * sy;
+						memcpy(A + (size_t)k * F, tgt + ((size_t)(id + di[k]) * w + jd + dj[k]) * F, sizeof(float) * F);
+					}
+					memcpy(A + (size_t)K * F, t0, sizeof(float) * F);
+					ibr_best_approximation(family, A, s, F, K + 1, co);
+					float e0 = 0.f, e1 = 0.f;
+					for (int k = 0; k < K; k++) { e0 += co[k] * di[k]; e1 += co[k] * dj[k]; }
+					if (fabsf(e0) <= 1. && fabsf(e1) <= 1.) {
+						for (int c = 0; c < F; c++) { float v = 0.f; for (int k = 0; k <= K; k++) v += A[c + (size_t)k * F] * co[k]; interp[c] = v; }
+						float sc = ibr_compare(mf, s, interp, F, tmp);
+						if (score_mode ? sc > score : sc < score) { dd0 = e0; dd1 = e1; score = sc; }
+					}
+				}
+			}
+			out[((size_t)i * w + j) * 2] = d0 + dd0;
+			out[((size_t)i * w + j) * 2 + 1] = d1 + dd1;
+		}
+		free(buf);
+	}
+	return 0;
+}
+
+/* image_based_refinement.h:1591-1690 */
+int orc_refine_cost_symmetric_disp(int mf, const float* fl, const float* fr, int h, int wl, int wr, int F, const int32_t* idx,
+								   const float* cv, int D, int dir, float* out) {
+	const float* src = dir ? fr : fl; const float* tgt = dir ? fl : fr;
+	const int ws = dir ? wr : wl, wt = dir ? wl : wr, sign = dir ? 1 : -1;
+	#pragma omp parallel for
+	for (int i = 0; i < h; i++) {
+		float* buf = (float*)malloc(sizeof(float) * F * 4);
+		float* si = buf; float* tn = buf + F;
+		for (int j = 0; j < ws; j++) {
+			int d = idx[(size_t)i * ws + j], jd = j + sign * d;
+			float delta = 0;
+			if (j > 1 && j + 1 < ws && d > 0 && d + 1 < D) {
+				const float* c = cv + ((size_t)i * ws + j) * D + d;
+				float cm1 = c[-1], c0 = c[0], c1 = c[1];
+				delta = (cm1 - c1) / (2 * (c1 - 2 * c0 + cm1));
+				int sdir = delta > 0 ? -1 : 1;
+				if (jd + 1 < ws && jd > 1) {
+					const float* s = src + ((size_t)i * ws + j) * F;
+					for (int k = 0; k < F; k++) si[k] = (float)(0.5 * s[k] + 0.5 * s[k + sdir * F]);
+					if (mf_normalized(mf)) { float nn = ibr_norm(si, F); for (int k = 0; k < F; k++) si[k] /= nn; }
+					float f[3];
+					for (int q = -1; q <= 1; q++) {
+						const float* t = tgt + ((size_t)i * wt + jd + q) * F;
+						memcpy(tn, t, sizeof(float) * F);
+						if (mf_normalized(mf)) { float nn = ibr_norm(tn, F); for (int k = 0; k < F; k++) tn[k] /= nn; }
+						f[q + 1] = compare_f32(mf, si, tn, F);
+					}
+					float delta2 = (float)((f[0] - f[2]) / (2 * (f[2] - 2 * f[1] + f[0])) - sdir * 0.5);
+					if (fabsf(delta2) < 1.) delta = (delta + delta2) / 2;
+				}
+			}
+			out[(size_t)i * ws + j] = d + delta;
+		}
+		free(buf);
+	}
+	return 0;
+}

@@ -7,6 +7,7 @@
 #include <StereoVision/correlation/sgm.h>
 #include <StereoVision/correlation/cost_based_refinement.h>
 #include <StereoVision/correlation/hierarchical.h>
+#include <StereoVision/correlation/image_based_refinement.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -96,6 +97,14 @@ int main() {
 	auto sigma = sigmaFilter(2, 1, mean, lf);
 	std::printf("mean_filter %.4f\nsigma_filter %.4f\nmean_filter_empty %d\n", checksum(mean), checksum(sigma),
 				int(meanFilter2D(uint8_t(w), 1, lf).empty()));
+	// feature-domain refinement (image_based_refinement.h): image-level and feature-level forms
+	auto bary = refinedBarycentricDisp<matchingFunctions::ZNCC, float, float>(lf, rf, 2, 2, D);
+	auto barysym = refineBarycentricSymmetricDisp<matchingFunctions::SSD>(fvl, fvr, zi, D);
+	Multidim::Array<disp_t, 3> zero2(h, w, 2);
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) { zero2.at<Multidim::AccessCheck::Nocheck>(i, j, 0) = 0; zero2.at<Multidim::AccessCheck::Nocheck>(i, j, 1) = 0; }
+	auto bary2 = refineBarycentric2dDisp<matchingFunctions::ZSSD, Contiguity::Rook>(fvl, fvl, zero2, searchOffset<2>(-1, 1, -1, 1));
+	std::printf("barycentric %.3f\nbarycentric_symmetric %.3f\nbarycentric_2d %.3f\nbarycentric_empty %d\n", checksum(bary), checksum(barysym), checksum(bary2),
+				int(refinedBarycentricDisp<matchingFunctions::ZNCC, float, float>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D).empty()));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);
 	std::printf("mismatch_empty %d\n", int(bad.empty()));
 	auto even = refineDispCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 3>(h, w, 4), zi);

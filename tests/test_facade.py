@@ -35,7 +35,10 @@ def test_facade_headers_carry_the_reference_names():
                  "sgmDirections", "PaddingMargins", "disp_t", "searchOffset", "unfoldBased2dDisparityCostVolume",
                  "extractSelected2dIndex", "selected2dIndexToDisp", "truncatedBidirectionaCostVolume", "refineDisp2dCostInterpolation",
                  "IsotropyHypothesis", "GrPix17R3Filter", "GrPix17R4Filter", "aggregateCost", "featureVolume2CostVolume",
-                 "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid", "meanFilter2D", "sigmaFilter"):
+                 "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid", "meanFilter2D", "sigmaFilter",
+                 "refineBarycentricDisp", "refineBarycentricSymmetricDisp", "refineBarycentric2dDisp", "refineBarycentricSymmetric2dDisp",
+                 "refineCostSymmetricDisp", "refinedBarycentricDisp", "refinedBarycentricDispFeatureVol", "refinedCostSymmetricDisp",
+                 "bidimensionalContiguity"):
         assert name in text, name
 
 
@@ -115,6 +118,16 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
         assert any(abs(float(got[name]) - c) <= 2e-3 * max(1.0, abs(c)) for c in cands), (name, got[name], cands)
     zn = api.unfoldBasedCostVolume(api.ZNCC, lf, rf, 2, 2, D, layout="c", ctx=ctx)
     zi = api.extractSelectedIndex(zn, api.SCORE, ctx=ctx)
+    # feature-domain refinement: the facade's results against the Python mirror's
+    fvl, fvr = api.unfold(2, 2, lf, ctx=ctx), api.unfold(2, 2, rf, ctx=ctx)
+    zero2 = np.zeros((h, w, 2), np.int32)
+    for name, arr in (("barycentric", api.refinedBarycentricDisp(api.ZNCC, lf, rf, 2, 2, D, ctx=ctx)),
+                      ("barycentric_symmetric", api.refineBarycentricSymmetricDisp(api.SSD, fvl, fvr, zi, D, ctx=ctx)),
+                      ("barycentric_2d", api.refineBarycentric2dDisp(api.ZSSD, fvl, fvl, zero2, (-1, 1, -1, 1), api.ROOK, ctx=ctx))):
+        a = np.asarray(arr)
+        cands = {_checksum(a), _checksum(np.transpose(a))}
+        assert any(abs(float(got[name]) - c) <= 1e-4 * max(1.0, abs(c)) for c in cands), (name, got[name], cands)
+    assert int(got["barycentric_empty"]) == 1
     assert abs(float(got["zncc_match"]) - float((zi[4:h - 4, 4:w - 24] == 5).mean())) < 1e-3
     assert float(got["zncc_match"]) > 0.95
     order = os.environ.get("STEVI_FACADE_ORDER", "")
