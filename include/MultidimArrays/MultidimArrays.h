@@ -223,6 +223,9 @@ public:
 				 (std::is_integral<typename std::decay<Is>::type>::value && ...)>::type>
 	T& atUnchecked(Is... is) { return _data[offset(ShapeBlock{static_cast<int>(is)...})]; }
 	T& atUnchecked(ShapeBlock const& idx) { return _data[offset(idx)]; }
+	// flat position in the array's own memory (what io/image_io.h:96,160 use to reach the first element of a dense array)
+	template<int D = nDim, typename = typename std::enable_if<(D > 1)>::type>
+	T& atUnchecked(int flatPosition) { return _data[flatPosition]; }
 
 	template<AccessCheck c = AccessCheck::Check, typename... Is,
 			 typename = typename std::enable_if<(sizeof...(Is) == nDim) &&

@@ -537,6 +537,26 @@ def refineDisp2dCostPatchInterpolation(tcv, rawDisparity, kernel=PARABOLA, ctx=N
     return out
 
 
+def computeAggregationWindows(guide, h_radius, v_radius, spatialWeightFunc, matchWeightFunc):
+    """guided_cost_filtering.h:26-100: weights(i,j,di+v,dj+h) = spatialWeightFunc(di, dj) * matchWeightFunc(guide(i,j,:), guide(i+di,j+dj,:)),
+    0 for window cells outside the image. The two functors are the caller's code and run on the host: ``spatialWeightFunc(di, dj)``
+    returns a number, ``matchWeightFunc(ref, target)`` takes two (..., C) numpy arrays and returns the weights of all pixels at once.
+    The result feeds variableCostVolumeAggregation, which is where the volume-sized work is."""
+    g = np.asarray(guide)
+    if g.ndim == 2:
+        g = g[:, :, None]
+    H, W = g.shape[:2]
+    out = np.zeros((H, W, 2 * v_radius + 1, 2 * h_radius + 1), np.float32)
+    for di in range(-v_radius, v_radius + 1):
+        for dj in range(-h_radius, h_radius + 1):
+            i0, i1, j0, j1 = max(0, -di), min(H, H - di), max(0, -dj), min(W, W - dj)
+            if i0 >= i1 or j0 >= j1:
+                continue
+            w = np.float32(spatialWeightFunc(di, dj)) * np.asarray(matchWeightFunc(g[i0:i1, j0:j1], g[i0 + di:i1 + di, j0 + dj:j1 + dj]), np.float32)
+            out[i0:i1, j0:j1, di + v_radius, dj + h_radius] = w
+    return out
+
+
 def variableCostVolumeAggregation(costVolume, aggregationWindows, layout="c", out=None, ctx=None):
     """guided_cost_filtering.h:102-176. (H, W, D) f32 volume + (H, W, 2v+1, 2h+1) f32 per-pixel weights -> (H, W, D) f32 weighted
     means over each pixel's (image-clipped) window. ``layout`` "ref" gives the result the strides {W*D, 1, W} of the reference's

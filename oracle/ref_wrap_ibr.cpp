@@ -12,6 +12,7 @@
 #include <omp.h>
 
 #include <correlation/image_based_refinement.h>
+#include <io/image_io.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -121,6 +122,29 @@ int ref_refine_cost_symmetric_disp(int matchfunc, const float* fl, const float* 
 	if (dir) { IBR_MF(return (costsym<F, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) IBR_MF_L1(return (costsym<F, dispDirection::RightToLeft>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) }
 	else { IBR_MF(return (costsym<F, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) IBR_MF_L1(return (costsym<F, dispDirection::LeftToRight>(fl, fr, h, wl, wr, f, idx, cv, wi, d, out))) }
 	return 3;
+}
+
+// io/image_io.h:66-165 through the reference's own writer / reader: data is a dense C-order (d0,d1,d2) block; `ref_layout` != 0
+// writes it through an array with the reference's cost-volume strides {d1*d2, 1, d1} (cross_correlations.h:220)
+int ref_write_stevimg_f32(const char* path, const float* data, int d0, int d1, int d2, int ref_layout) {
+	MD::Array<float, 3> a = ref_layout ? MD::Array<float, 3>({d0, d1, d2}, {d1 * d2, 1, d1}) : MD::Array<float, 3>({d0, d1, d2}, {d1 * d2, d2, 1});
+	for (int i = 0; i < d0; i++) for (int j = 0; j < d1; j++) for (int k = 0; k < d2; k++) a.atUnchecked(i, j, k) = data[(size_t(i) * d1 + j) * d2 + k];
+	return IO::writeStevimg<float, float, 3>(path, a) ? 0 : 1;
+}
+int ref_write_stevimg_u8_from_i32(const char* path, const int32_t* data, int d0, int d1) {
+	MD::Array<int32_t, 2> a({d0, d1}, {d1, 1});
+	for (int i = 0; i < d0; i++) for (int j = 0; j < d1; j++) a.atUnchecked(i, j) = data[size_t(i) * d1 + j];
+	return IO::writeStevimg<uint8_t, int32_t, 2>(path, a) ? 0 : 1;
+}
+int ref_read_stevimg_f32(const char* path, float* out, int* shape) {
+	auto a = IO::readStevimg<float, 3>(path);
+	if (a.empty()) return 1;
+	for (int k = 0; k < 3; k++) shape[k] = a.shape()[k];
+	out3(a, out);
+	return 0;
+}
+int ref_stevimg_matches(const char* path, int which) {
+	return which == 0 ? IO::stevImgFileMatchTypeAndDim<float, 3>(path) : (which == 1 ? IO::stevImgFileMatchTypeAndDim<uint8_t, 2>(path) : IO::stevImgFileMatchTypeAndDim<float, 2>(path));
 }
 
 // refinedBarycentricDisp on images (image_based_refinement.h:2502-2544): unfold, features, cost volume, winner, refinement

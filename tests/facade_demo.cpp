@@ -8,6 +8,7 @@
 #include <StereoVision/correlation/cost_based_refinement.h>
 #include <StereoVision/correlation/hierarchical.h>
 #include <StereoVision/correlation/image_based_refinement.h>
+#include <StereoVision/correlation/guided_cost_filtering.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -105,6 +106,12 @@ int main() {
 	auto bary2 = refineBarycentric2dDisp<matchingFunctions::ZSSD, Contiguity::Rook>(fvl, fvl, zero2, searchOffset<2>(-1, 1, -1, 1));
 	std::printf("barycentric %.3f\nbarycentric_symmetric %.3f\nbarycentric_2d %.3f\nbarycentric_empty %d\n", checksum(bary), checksum(barysym), checksum(bary2),
 				int(refinedBarycentricDisp<matchingFunctions::ZNCC, float, float>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D).empty()));
+	// guided aggregation (guided_cost_filtering.h): bilateral weights from the caller's functors, aggregation on the GPU
+	auto windows = computeAggregationWindows<float>(rf, 2, 1, [](int di, int dj) { return std::exp(-float(di * di + dj * dj) / 4.f); },
+		[](Multidim::Array<float, 1> const& a, Multidim::Array<float, 1> const& b) { float d = a.valueUnchecked(0) - b.valueUnchecked(0); return std::exp(-d * d * 8.f); });
+	auto aggregated = variableCostVolumeAggregation(f2c, windows);
+	std::printf("aggregation_windows %.4f\naggregated %.3f\naggregated_empty %d\n", checksum(windows), checksum(aggregated),
+				int(variableCostVolumeAggregation(f2c, Multidim::Array<float, 4>(h, w, 2, 3)).empty()));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);
 	std::printf("mismatch_empty %d\n", int(bad.empty()));
 	auto even = refineDispCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 3>(h, w, 4), zi);

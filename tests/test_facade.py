@@ -38,7 +38,7 @@ def test_facade_headers_carry_the_reference_names():
                  "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid", "meanFilter2D", "sigmaFilter",
                  "refineBarycentricDisp", "refineBarycentricSymmetricDisp", "refineBarycentric2dDisp", "refineBarycentricSymmetric2dDisp",
                  "refineCostSymmetricDisp", "refinedBarycentricDisp", "refinedBarycentricDispFeatureVol", "refinedCostSymmetricDisp",
-                 "bidimensionalContiguity"):
+                 "bidimensionalContiguity", "computeAggregationWindows", "variableCostVolumeAggregation", "readStevimg", "writeStevimg"):
         assert name in text, name
 
 
@@ -128,6 +128,15 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
         cands = {_checksum(a), _checksum(np.transpose(a))}
         assert any(abs(float(got[name]) - c) <= 1e-4 * max(1.0, abs(c)) for c in cands), (name, got[name], cands)
     assert int(got["barycentric_empty"]) == 1
+    # guided aggregation: the caller's functors on the host, the aggregation on the GPU
+    win = api.computeAggregationWindows(rf, 2, 1, lambda di, dj: np.exp(-np.float32(di * di + dj * dj) / np.float32(4)),
+                                        lambda a, b: np.exp(-(a[..., 0] - b[..., 0]) ** 2 * np.float32(8)))
+    f2c_c = np.ascontiguousarray(f2c)
+    for name, arr, tol in (("aggregation_windows", win, 1e-4), ("aggregated", api.variableCostVolumeAggregation(f2c_c, win, ctx=ctx), 2e-3)):
+        a = np.asarray(arr)
+        cands = {_checksum(a), _checksum(np.transpose(a))}
+        assert any(abs(float(got[name]) - c) <= tol * max(1.0, abs(c)) for c in cands), (name, got[name], cands)
+    assert int(got["aggregated_empty"]) == 1
     assert abs(float(got["zncc_match"]) - float((zi[4:h - 4, 4:w - 24] == 5).mean())) < 1e-3
     assert float(got["zncc_match"]) > 0.95
     order = os.environ.get("STEVI_FACADE_ORDER", "")
