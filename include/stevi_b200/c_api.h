@@ -229,6 +229,13 @@ STEVI_API int32_t stevi_index_to_disp(stevi_ctx* ctx, const stevi_array* idx, in
  * image. Float matching functions (CC..ZSAD); sizes that differ or an empty window -> STEVI_E_SHAPE (reference: empty array). */
 STEVI_API int32_t stevi_cost_volume_2d(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
 							 int32_t h_radius, int32_t v_radius, const int32_t search[4], int32_t direction, stevi_array* out);
+/* The same with a semantics word, as stevi_cost_volume has: without STEVI_EXACT_SUMS (what stevi_cost_volume_2d passes) windows up
+ * to 9 columns wide take the O(1)-per-cell box sums, one pass of the 1-D box kernel per row offset (1e-5 of the largest magnitude
+ * against the reference, 1e-4 absolute for the normalised correlations); with it every cell is summed over its F features in the
+ * reference's channel order (2e-6). ZSAD (not a box filter) and wider windows always take the second form. */
+STEVI_API int32_t stevi_cost_volume_2d_ex(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* img_l, const stevi_array* img_r,
+								int32_t h_radius, int32_t v_radius, const int32_t search[4], int32_t direction, int32_t semantics,
+								stevi_array* out);
 
 /* extractSelected2dIndex<strategy, T_CV> (correlation/correlation_base.h:466-508): vol (H,W,D1,D2) f32 -> out (H,W,2) i32;
  * row-major scan of (d1,d2) with `<=` / `>=`: the LAST extremum wins, a NaN at (0,0) sticks. */

@@ -466,16 +466,19 @@ def _search4(search):
     return (ctypes.c_int32 * 4)(lo0, up0, lo1, up1), up0 - lo0 + 1, up1 - lo1 + 1
 
 
-def unfoldBased2dDisparityCostVolume(matchFunc, img_l, img_r, h_radius, v_radius, searchWindows, dDir=RIGHT_TO_LEFT, layout="ref", ctx=None):
+def unfoldBased2dDisparityCostVolume(matchFunc, img_l, img_r, h_radius, v_radius, searchWindows, dDir=RIGHT_TO_LEFT, layout="ref",
+                                     exact_sums=False, ctx=None):
     """cross_correlations.h:794-822. ``searchWindows`` = (lower0, upper0, lower1, upper1), the arguments of searchOffset<2>
     (axis 0 = rows, axis 1 = columns). Returns (H, W, dH, dW) float32; ``layout`` "ref" = the reference's strides
-    {W*dW*dH, 1, W*dW, W}, "c" = C order. Raises SteviError(E_SHAPE) where the reference returns an empty array."""
+    {W*dW*dH, 1, W*dW, W}, "c" = C order. ``exact_sums``: every cell summed over its features in the reference's channel order
+    (2e-6) instead of the O(1) box sums (1e-5). Raises SteviError(E_SHAPE) where the reference returns an empty array."""
     ctx = _ctx_for(ctx, img_l)
     so, dH, dW = _search4(searchWindows)
     H, W = img_l.shape
     out = _empty(img_l, (H, W, max(dH, 0), max(dW, 0)), np.float32, (0, 2, 3, 1) if layout == "ref" else None)
     l, r, o = describe(img_l), describe(img_r), describe(out)
-    ctx.check(lib.stevi_cost_volume_2d(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, so, dDir, ctypes.byref(o)))
+    ctx.check(lib.stevi_cost_volume_2d_ex(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), h_radius, v_radius, so, dDir,
+                                          EXACT_SUMS if exact_sums else COMPAT, ctypes.byref(o)))
     return out
 
 

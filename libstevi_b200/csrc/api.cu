@@ -281,16 +281,21 @@ int32_t stevi_index_to_disp(stevi_ctx* c, const stevi_array* idx, int32_t direct
 	return st.finish();
 }
 
-int32_t stevi_cost_volume_2d(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
-							 const int32_t* search, int32_t direction, stevi_array* out) {
+int32_t stevi_cost_volume_2d_ex(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
+								const int32_t* search, int32_t direction, int32_t semantics, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);
 	View vl, vr_, vo;
 	STEVI_TRY(st.in(l, vl, "img_l"));
 	STEVI_TRY(st.in(r, vr_, "img_r"));
 	STEVI_TRY(st.out(out, vo, "out"));
-	STEVI_TRY(float_cv2d_dev(c, mf, vl, vr_, hr, vr, search, direction, vo));
+	STEVI_TRY(float_cv2d_dev(c, mf, vl, vr_, hr, vr, search, direction, vo, (semantics & STEVI_EXACT_SUMS) != 0));
 	return st.finish();
+}
+
+int32_t stevi_cost_volume_2d(stevi_ctx* c, int32_t mf, const stevi_array* l, const stevi_array* r, int32_t hr, int32_t vr,
+							 const int32_t* search, int32_t direction, stevi_array* out) {
+	return stevi_cost_volume_2d_ex(c, mf, l, r, hr, vr, search, direction, STEVI_COMPAT, out);
 }
 
 int32_t stevi_wta_2d(stevi_ctx* c, const stevi_array* vol, int32_t strategy, stevi_array* out) {

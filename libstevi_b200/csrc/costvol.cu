@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(128) k_cv2d_planes_x4(const Cv2dParams p, int 
 
 } // namespace
 
-int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows) {
+int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows, int extra_rows) {
 	if (l.ndim != 2 || r.ndim != 2) return fail(c, STEVI_E_UNSUPPORTED, "images must be 2-D (H,W)");
 	if (l.dtype != r.dtype || (l.dtype != STEVI_U8 && l.dtype != STEVI_F32))
 		return fail(c, STEVI_E_DTYPE, "images must both be u8 or both f32");
@@ -350,10 +350,10 @@ int32_t PaddedPair::build(stevi_ctx* c, const View& l, const View& r, int hr, in
 	if (H > 65535) return fail(c, STEVI_E_UNSUPPORTED, "more than 65535 rows");
 	const int Wmax = std::max(l.shape[1], r.shape[1]);
 	pad_left = (D + hr + 48 + 7) / 8 * 8;
-	pad_top = vr + 1;
+	pad_top = vr + 1 + extra_rows;
 	pitch = (pad_left + (Wmax + 127) / 128 * 128 + pad_left + 64 + 63) / 64 * 64;
 	half = (int)(pitch / 2);
-	rows = pad_top + (H + band_rows) + vr + 1;
+	rows = pad_top + (H + band_rows) + vr + 1 + extra_rows;
 	plane = (size_t)rows * pitch;
 	float* buf = nullptr;
 	STEVI_TRY(arena_alloc_t(c, plane * 6, &buf));
@@ -409,7 +409,7 @@ int32_t PaddedPair::stats(stevi_ctx* c, int which, int hr, int vr, int mf, int k
 // target image, for both directions (the direction only picks the source image). One launch of the reference-order kernel
 // per row offset; search = {lower0, upper0, lower1, upper1}; out (H, W, dH, dW).
 int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const int32_t* search, int direction,
-					   const View& out) {
+					   const View& out, bool exact) {
 	switch (mf) {
 	case STEVI_MF_CC: case STEVI_MF_NCC: case STEVI_MF_ZCC: case STEVI_MF_ZNCC:
 	case STEVI_MF_SSD: case STEVI_MF_ZSSD: case STEVI_MF_SAD: case STEVI_MF_ZSAD: break;
@@ -432,8 +432,42 @@ int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int h
 	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
 	const int reach = std::max(abs(search[2]), abs(search[3]));   // the padded rows must hold every target column a cell can name
 	PaddedPair pp;
-	STEVI_TRY(pp.build(c, l, r, hr, vr, reach + 1, 1));
 	const int si = r2l ? 1 : 0, ti = 1 - si;
+	if (!exact && mf != STEVI_MF_ZSAD && hr >= 1 && hr <= 4 && BOX_BAND_ROWS + 2 * vr <= BOX_MAX_TILE_ROWS && dW <= 65535 - 8) {
+		// One launch of the 1-D box kernel (§ costvol_box.cuh: O(1) per cell from running window sums) per row offset: row offset a of the
+		// search is the 1-D volume against the target planes read a rows further down, column offsets lower1 .. upper1 are its
+		// "disparities". Rows and columns outside the target image are zero image / zero statistics in the padded planes, which is
+		// how the kernel recognises the reference's zero target vector. The de-interleaved planes can be shifted by whole pairs of
+		// 16-byte units (8 columns) only: the first stored column offset is the d_first-th one the kernel evaluates.
+		const int vreach = std::max(abs(search[0]), abs(search[1]));
+		STEVI_TRY(pp.build(c, l, r, hr, vr, reach + 9, BOX_BAND_ROWS, vreach));
+		const int op = mf_op(mf);
+		STEVI_TRY(pp.stats(c, si, hr, vr, mf, op == BOX_PROD ? STATS_PROD_SRC : STATS_DIFF_SRC));
+		STEVI_TRY(pp.stats(c, ti, hr, vr, mf, op == BOX_PROD ? STATS_PROD_TGT : STATS_DIFF_TGT));
+		const int lo8 = search[2] >= 0 ? search[2] / 8 * 8 : -((-search[2] + 7) / 8 * 8);
+		const int d_first = search[2] - lo8;
+		const int64_t col_shift = (int64_t)(lo8 / 8) * 4;   // 8 columns = two units = 4 floats in the de-interleaved rows
+		for (int a = 0; a < dH; a++) {
+			const int64_t shift = (int64_t)(search[0] + a) * pp.pitch + col_shift;
+			BoxParams p;
+			p.ps = pp.img[si]; p.pt = pp.img[ti] + shift; p.As = pp.A[si]; p.Bs = pp.B[si]; p.At = pp.A[ti] + shift; p.Bt = pp.B[ti] + shift;
+			p.pitch = pp.pitch; p.half = pp.half; p.pad_left = pp.pad_left; p.H = H; p.Ws = W; p.D = dW + d_first; p.vr = vr; p.R = BOX_BAND_ROWS;
+			p.row_shift = ((c->row_origin % BOX_BAND_ROWS) + BOX_BAND_ROWS) % BOX_BAND_ROWS;
+			p.d_first = d_first;
+			p.Ff = (float)((2 * hr + 1) * (2 * vr + 1));
+			p.out = out.as<float>() + (int64_t)a * out.st[2] - (int64_t)d_first * out.st[3];
+			p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[3];
+			p.keys = nullptr;
+			p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0 && out.st[3] % 4 == 0;
+			switch (op) {
+			case BOX_PROD: STEVI_TRY(launch_cv_box_prod(c, p, hr, 1)); break;
+			case BOX_SQ: STEVI_TRY(launch_cv_box_sq(c, p, hr, 1)); break;
+			default: STEVI_TRY(launch_cv_box_abs(c, p, hr, 1)); break;
+			}
+		}
+		return STEVI_OK;
+	}
+	STEVI_TRY(pp.build(c, l, r, hr, vr, reach + 1, 1));
 	STEVI_TRY(pp.stats(c, si, hr, vr, mf, STATS_RAW));
 	STEVI_TRY(pp.stats(c, ti, hr, vr, mf, STATS_RAW));
 	const int F = (2 * hr + 1) * (2 * vr + 1);

@@ -54,6 +54,7 @@ struct BoxParams {
 	int64_t pitch;
 	int half, pad_left;
 	int H, Ws, D, vr, R, row_shift;
+	int d_first = 0;                    // disparities below this one are evaluated but not stored (2-D search: the target planes can only be shifted by whole pairs of units)
 	float Ff;                           // number of features F as float
 	float* out; int64_t o0, o1, o2;
 	int vec_store;                      // o1 == 1, 16-byte aligned rows
@@ -282,6 +283,7 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 #pragma unroll
 		for (int q = 0; q < 4; q++) {
 			if (d0 + q >= p.D) break;
+			if (d0 + q < p.d_first) continue;
 			float o[8];
 			float h = V[q][LH - HR];
 #pragma unroll

@@ -26,7 +26,8 @@ struct PaddedPair {
 	float* img[2] = {nullptr, nullptr};
 	float* A[2] = {nullptr, nullptr};
 	float* B[2] = {nullptr, nullptr};
-	int32_t build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows);
+	// extra_rows: further zero rows above and below (2-D search: the target planes are read shifted by whole rows)
+	int32_t build(stevi_ctx* c, const View& l, const View& r, int hr, int vr, int D, int band_rows, int extra_rows = 0);
 	int32_t stats(stevi_ctx* c, int which, int hr, int vr, int mf, int kind);
 };
 // unfoldBasedCostVolume for CC/NCC/ZCC/ZNCC/SSD/ZSSD/SAD/ZSAD, out (H,Wsource,D) f32
@@ -55,7 +56,9 @@ int32_t sgm_dev(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1, 
 				const WtaSink* wta);
 
 // costvol.cu: 2-D search cost volume, search = {lower0, upper0, lower1, upper1}, out (H,W,dH,dW) f32
-int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const int32_t* search, int direction, const View& out);
+// exact: the reference's O(F) sums in its channel order (2e-6); else the O(1) box sums per row offset (1e-5), where a box kernel exists
+int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const int32_t* search, int direction, const View& out,
+					   bool exact = false);
 
 // features_cv.cu: feature-level forms (caller-supplied float feature volumes)
 int32_t features_for_matchfunc_dev(stevi_ctx* c, int mf, const View& in, const View& out);

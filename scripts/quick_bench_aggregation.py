@@ -43,6 +43,10 @@ if which in ("all", "search2d"):
     n = 5 * 33
     vol = api.unfoldBased2dDisparityCostVolume(api.ZNCC, dl, dr, 4, 4, search, ctx=ctx)
     ms_cv = timed(lambda: api.unfoldBased2dDisparityCostVolume(api.ZNCC, dl, dr, 4, 4, search, ctx=ctx), n=5)
+    ms_cv_exact = timed(lambda: api.unfoldBased2dDisparityCostVolume(api.ZNCC, dl, dr, 4, 4, search, exact_sums=True, ctx=ctx), n=5)
+    print(json.dumps({"stage": "search2d volume, box sums (default) vs the reference's channel-order sums", "box_ms": round(ms_cv, 3),
+                      "exact_sums_ms": round(ms_cv_exact, 3), "cells": H * W * n, "box_store_GBps": round(H * W * n * 4 / ms_cv / 1e6, 1),
+                      "box_frac_of_hbm_peak": round(H * W * n * 4 / ms_cv / 1e6 / PEAK, 3)}))
     idx = api.extractSelected2dIndex(vol, api.SCORE, ctx=ctx)
     ms_wta = timed(lambda: api.extractSelected2dIndex(vol, api.SCORE, ctx=ctx), n=5)
     t = api.truncatedBidirectionaCostVolume(vol, idx, 1, 1, ctx=ctx)

@@ -38,7 +38,7 @@ def close(name, got, want):
 def test_cost_volume_2d_matches_oracle(api, ctx, oracle, name, search):
     L, R = synth.random_image(21, 37, 3), synth.random_image(21, 37, 4)
     for direction in (0, 1):
-        got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, dDir=direction, ctx=ctx)
+        got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, dDir=direction, exact_sums=True, ctx=ctx)
         close(name, np.ascontiguousarray(got), oracle.port.cost_volume_2d(getattr(oracle, name), L, R, 2, 1, search, direction))
 
 
@@ -49,13 +49,13 @@ def test_cost_volume_2d_aligned_rows_match_oracle(api, ctx, oracle, name, W, sea
     """Widths that are multiples of 4 take the kernel with four source pixels x four column offsets per thread; its groups of
     offsets start at a multiple of 4 at or below lower1, so unaligned and negative windows exercise the partial groups."""
     L, R = synth.random_image(13, W, 5), synth.random_image(13, W, 6)
-    got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, ctx=ctx)
+    got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, exact_sums=True, ctx=ctx)
     want = oracle.port.cost_volume_2d(getattr(oracle, name), L, R, 2, 1, search)
     close(name, np.ascontiguousarray(got), want)
-    c_layout = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, layout="c", ctx=ctx)
+    c_layout = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, layout="c", exact_sums=True, ctx=ctx)
     assert np.array_equal(np.ascontiguousarray(got), c_layout, equal_nan=True)
     # the same cells through the four-candidate kernel (odd width: the last column dropped) agree bit for bit
-    narrow = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L[:, :W - 1].copy(), R[:, :W - 1].copy(), 2, 1, search, layout="c", ctx=ctx)
+    narrow = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L[:, :W - 1].copy(), R[:, :W - 1].copy(), 2, 1, search, layout="c", exact_sums=True, ctx=ctx)
     inner = slice(8, W - 12)     # away from the dropped column's reach (window radius 2 + offsets up to 9)
     assert np.array_equal(narrow[:, inner], c_layout[:, inner], equal_nan=True)
 
@@ -65,7 +65,7 @@ def test_cost_volume_2d_golden(api, ctx, oracle, name):
     L, R = synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_l"])), synth.random_image(int(G2["H"]), int(G2["W"]), int(G2["seed_r"]))
     search = tuple(int(v) for v in G2["search"])
     for direction in (0, 1):
-        got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, dDir=direction, ctx=ctx)
+        got = api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, 2, 1, search, dDir=direction, exact_sums=True, ctx=ctx)
         close(name, np.ascontiguousarray(got), G2[f"cv2d_{getattr(oracle, name)}_{direction}"])
 
 
@@ -74,13 +74,13 @@ def test_layouts_windows_and_device_operands(api, ctx, oracle):
     L, R = synth.random_image(33, 150, 8), synth.random_image(33, 150, 9)   # more than one 128-column block
     search = (-1, 1, -6, 9)
     want = oracle.port.cost_volume_2d(oracle.ZNCC, L, R, 4, 3, search)
-    ref_layout = api.unfoldBased2dDisparityCostVolume(api.ZNCC, L, R, 4, 3, search, ctx=ctx)
+    ref_layout = api.unfoldBased2dDisparityCostVolume(api.ZNCC, L, R, 4, 3, search, exact_sums=True, ctx=ctx)
     assert ref_layout.strides == (150 * 16 * 3 * 4, 4, 150 * 16 * 4, 150 * 4)      # {W*dW*dH, 1, W*dW, W} elements
-    c_layout = api.unfoldBased2dDisparityCostVolume(api.ZNCC, L, R, 4, 3, search, layout="c", ctx=ctx)
+    c_layout = api.unfoldBased2dDisparityCostVolume(api.ZNCC, L, R, 4, 3, search, layout="c", exact_sums=True, ctx=ctx)
     close("ZNCC", np.ascontiguousarray(ref_layout), want)
     assert np.array_equal(np.ascontiguousarray(ref_layout), c_layout, equal_nan=True)
     tctx = api.Context(0, torch_stream=True)
-    dev = api.unfoldBased2dDisparityCostVolume(api.ZNCC, torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda(), 4, 3, search, ctx=tctx)
+    dev = api.unfoldBased2dDisparityCostVolume(api.ZNCC, torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda(), 4, 3, search, exact_sums=True, ctx=tctx)
     idx = api.extractSelected2dIndex(dev, api.SCORE, ctx=tctx)
     disp = api.selected2dIndexToDisp(idx, search, ctx=tctx)
     torch.cuda.synchronize()
@@ -89,15 +89,38 @@ def test_layouts_windows_and_device_operands(api, ctx, oracle):
     tctx.close()
     # windows the box kernels do not cover (wider than 9, zero radius) go through the same path
     for hr, vr in ((6, 0), (0, 2)):
-        got = api.unfoldBased2dDisparityCostVolume(api.SAD, L, R, hr, vr, (0, 1, -2, 2), ctx=ctx)
+        got = api.unfoldBased2dDisparityCostVolume(api.SAD, L, R, hr, vr, (0, 1, -2, 2), exact_sums=True, ctx=ctx)
         close("SAD", np.ascontiguousarray(got), oracle.port.cost_volume_2d(oracle.SAD, L, R, hr, vr, (0, 1, -2, 2)))
+
+
+@pytest.mark.parametrize("name", ["CC", "NCC", "ZCC", "ZNCC", "SSD", "ZSSD", "SAD"])
+@pytest.mark.parametrize("hr,vr", [(1, 1), (2, 3), (4, 2)])
+@pytest.mark.parametrize("W", [37, 132, 300])
+@pytest.mark.parametrize("search", [(0, 2, 0, 4), (-3, -1, 2, 6), (-2, 2, -5, 0), (1, 1, -13, -9), (-1, 0, -3, 40), (4, 4, 7, 7)])
+def test_cost_volume_2d_box_sums_match_oracle(api, ctx, oracle, name, hr, vr, W, search):
+    """The default path: the O(1) box sums of the 1-D kernel, one pass per row offset with the target planes read shifted.
+    Tolerance of the box form: 1e-4 absolute for the normalised correlations, 1e-5 of the largest magnitude
+    otherwise; NaNs (flat windows) in the same cells. Column windows that start off a multiple of 8, negative and far offsets,
+    rows and columns of the target outside the image, several 128-column blocks, both layouts."""
+    L, R = synth.random_image(19, W, 3 + W), synth.random_image(19, W, 4 + W)
+    L[5:12, 8:20] = 0.25   # a flat patch: NaN for the normalised zero-mean functions (Q6)
+    want = oracle.port.cost_volume_2d(getattr(oracle, name), L, R, hr, vr, search)
+    for layout in ("ref", "c"):
+        got = np.ascontiguousarray(api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, hr, vr, search, layout=layout, ctx=ctx))
+        assert got.shape == want.shape and np.array_equal(np.isnan(got), np.isnan(want))
+        tol = 1e-4 if name in ("NCC", "ZNCC") else 1e-5 * max(1.0, float(np.nanmax(np.abs(want))))
+        assert np.nanmax(np.abs(got - want)) <= tol
+    l2r = np.ascontiguousarray(api.unfoldBased2dDisparityCostVolume(getattr(api, name), L, R, hr, vr, search, dDir=api.LEFT_TO_RIGHT, ctx=ctx))
+    want = oracle.port.cost_volume_2d(getattr(oracle, name), L, R, hr, vr, search, oracle.L2R)
+    assert np.array_equal(np.isnan(l2r), np.isnan(want))
+    assert np.nanmax(np.abs(l2r - want)) <= (1e-4 if name in ("NCC", "ZNCC") else 1e-5 * max(1.0, float(np.nanmax(np.abs(want)))))
 
 
 def test_row_offset_zero_equals_the_1d_volume(api, ctx):
     """The slice at row offset 0 of a search window starting at column offset 0 is the 1-D right-to-left volume of the
     reference-order kernel, bit for bit (same kernel, same arithmetic)."""
     L, R = synth.random_image(64, 200, 21), synth.random_image(64, 200, 22)
-    cv2 = api.unfoldBased2dDisparityCostVolume(api.ZNCC, L, R, 3, 3, (-2, 2, 0, 11), layout="c", ctx=ctx)
+    cv2 = api.unfoldBased2dDisparityCostVolume(api.ZNCC, L, R, 3, 3, (-2, 2, 0, 11), layout="c", exact_sums=True, ctx=ctx)
     cv1 = api.unfoldBasedCostVolume(api.ZNCC, L, R, 3, 3, 12, exact_sums=True, layout="c", ctx=ctx)
     assert np.array_equal(cv2[:, :, 2, :], cv1, equal_nan=True)
 
@@ -124,13 +147,13 @@ def test_selection_2d(api, ctx, oracle):
 def test_reference_shape_rules(api, ctx):
     a, b = np.zeros((5, 6), np.float32), np.zeros((5, 7), np.float32)
     with pytest.raises(api.SteviError) as e:       # cross_correlations.h:808-810: empty array
-        api.unfoldBased2dDisparityCostVolume(api.ZNCC, a, b, 1, 1, (0, 1, 0, 1), ctx=ctx)
+        api.unfoldBased2dDisparityCostVolume(api.ZNCC, a, b, 1, 1, (0, 1, 0, 1), exact_sums=True, ctx=ctx)
     assert e.value.status == api.E_SHAPE
     with pytest.raises(api.SteviError) as e:       # :336-338: empty search window
-        api.unfoldBased2dDisparityCostVolume(api.ZNCC, a, a, 1, 1, (1, 0, 0, 1), ctx=ctx)
+        api.unfoldBased2dDisparityCostVolume(api.ZNCC, a, a, 1, 1, (1, 0, 0, 1), exact_sums=True, ctx=ctx)
     assert e.value.status == api.E_SHAPE
     with pytest.raises(api.SteviError) as e:
-        api.unfoldBased2dDisparityCostVolume(api.CENSUS, a, a, 1, 1, (0, 1, 0, 1), ctx=ctx)
+        api.unfoldBased2dDisparityCostVolume(api.CENSUS, a, a, 1, 1, (0, 1, 0, 1), exact_sums=True, ctx=ctx)
     assert e.value.status == api.E_UNSUPPORTED
 
 
@@ -139,7 +162,7 @@ def test_reference_shape_rules(api, ctx):
 def test_ref_test2dMatching_and_test2dDisparity(api, ctx, oracle, name, hr, vr, dw, dh):
     """testCorrelation2d.cpp:73-194 run against the CUDA functions."""
     def cv2d(mf, l, r, hr_, vr_, search):
-        return api.unfoldBased2dDisparityCostVolume(mf, l, r, hr_, vr_, search, ctx=ctx)
+        return api.unfoldBased2dDisparityCostVolume(mf, l, r, hr_, vr_, search, exact_sums=True, ctx=ctx)
     mf = getattr(oracle, name)   # oracle and api share the matching-function codes
     assert mf == getattr(api, name)
     check_2d_matching(cv2d, mf, hr, vr, dw, dh, 77)
@@ -246,7 +269,7 @@ def test_refinement_2d_shape_rules_and_device_operands(api, ctx, oracle):
     L, R = synth.random_image(64, 200, 51), synth.random_image(64, 200, 52)
     search = (-2, 2, -3, 3)
     tctx = api.Context(0, torch_stream=True)
-    cv = api.unfoldBased2dDisparityCostVolume(api.ZNCC, torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda(), 2, 2, search, ctx=tctx)
+    cv = api.unfoldBased2dDisparityCostVolume(api.ZNCC, torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda(), 2, 2, search, exact_sums=True, ctx=tctx)
     idx = api.extractSelected2dIndex(cv, api.SCORE, ctx=tctx)
     t = api.truncatedBidirectionaCostVolume(cv, idx, 1, 1, ctx=tctx)
     disp = api.selected2dIndexToDisp(idx, search, ctx=tctx)
