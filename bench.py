@@ -258,6 +258,10 @@ def main_float(args, wl, rank, world, local_rank, dist=None, steps=None, with_cp
         def step_device():
             res["tcv"], res["disp"] = run(dl, dr)
 
+        def step_sharded():   # every rank keeps its band of the result: no collective at all
+            res["tcv_band"], res["disp_band"] = sharding.hierarchical_rows(api, api.ZNCC, wl["depth"], dl, dr, wl["hr"], wl["vr"], D, g0, g1,
+                                                                          wl["radius"], band_row0=lo, full_height=H, ctx=ctx)
+
         hdisp = torch.empty((H, W), dtype=torch.int32).pin_memory()
 
         def step_host():  # host frame in, host disparity map out (the band's rows travel H2D, the gathered map D2H)
@@ -327,6 +331,11 @@ def main_float(args, wl, rank, world, local_rank, dist=None, steps=None, with_cp
         if dist is not None:
             ms_host = sharding.max_over_ranks(ms_host, dist, dev)
         e2e_mode = f"{args.inflight} pairs in flight (HostPairStream: one ctx+stream per slot, stevi_ctx_set_deferred_host)"
+    ms_sharded = None
+    if hier and world > 1:
+        for _ in range(warmup):
+            step_sharded()
+        ms_sharded, _ = timed(step_sharded, steps)
     ctx.set_timing(True)
     per_kernel = {}
     for _ in range(max(3, min(steps, 10))):
@@ -354,6 +363,13 @@ def main_float(args, wl, rank, world, local_rank, dist=None, steps=None, with_cp
                 "gpu_launches": int(launches), "clocks": clocks, "kernels_ms_per_step": {k: round(v, 4) for k, v in kern_ms.items()},
                 "ground_truth_agreement": accuracy}
         config["l2"] = "512 MB memset between timed steps (outside the event pairs)"
+        if ms_sharded is not None:
+            t_rows = 2 * wl["radius"] + 1
+            line["result_sharded"] = {"ms_per_step": ms_sharded / steps, "value": units * steps / (ms_sharded * 1e-3) / 1e9, "unit": "Gdisp/s",
+                                      "note": "same frame, same row bands, every rank keeps its band of (tcv, disp): no collective; the gathered "
+                                              "form in `value` adds one NCCL all_gather of the bands",
+                                      "gathered_bytes": int(H * W * (t_rows + 1) * 4),
+                                      "gather_ms_per_step": (ms_dev - ms_sharded) / steps}
         dom = dom_key if dom_key in kern_ms else max(kern_ms, key=kern_ms.get)
         n_launch = len(per_kernel[dom]) / reps
         if dom_bytes:
@@ -514,6 +530,11 @@ def main_census(args, wl, rank, world, local_rank, dist=None, steps=None, with_c
                      "ms_per_step": ms_sus / n_sus, "clocks": sus_clocks}
 
     # dominant kernel, per launch, CUDA events on the launching stream (second pass with the ctx's event hooks on)
+    ms_sharded = None
+    if hier and world > 1:
+        for _ in range(warmup):
+            step_sharded()
+        ms_sharded, _ = timed(step_sharded, steps)
     ctx.set_timing(True)
     per_kernel = {}
     for _ in range(max(3, min(steps, 10))):
@@ -797,7 +818,7 @@ def main():
             r = main_float(args, WORKLOADS[name], rank, world, local_rank, dist, steps=k, with_cpu=False)
             if r is not None:
                 sec[name] = {q: r[q] for q in ("value", "unit", "ms_per_step", "scaling", "e2e", "roofline", "kernels_ms_per_step",
-                                               "ground_truth_agreement", "gpu_launches") if q in r}
+                                               "ground_truth_agreement", "gpu_launches", "result_sharded", "n_gpus") if q in r}
                 sec[name]["workload"] = r["config"]["workload"]
         r = main_census(args, WORKLOADS["c5"], rank, world, local_rank, dist, steps=k, with_cpu=False)
         if r is not None:
