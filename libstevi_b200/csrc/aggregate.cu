@@ -12,6 +12,7 @@
 // inner, a rounded multiply and a rounded add per cell: its Release build does not contract `acc += w*cv`), so the result is
 // bit-identical.
 #include <cstdlib>
+#include <type_traits>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -167,6 +168,128 @@ __global__ void __launch_bounds__(128) k_var_aggregate_x4(const Agg p) {
 	}
 }
 
+
+// Windows of 5 x 5 and 7 x 7 on volumes with contiguous columns: the d-plane tile a block of 8 rows x 16*CPT columns needs (its
+// pixels plus R on every side, zero outside the image) goes through shared memory, double-buffered along the disparity axis — the
+// plane of d+1 is fetched into registers before the arithmetic of d and stored after it, one barrier per disparity. A thread owns
+// CPT adjacent columns of one row with their CPT x (2R+1)^2 weights in registers and reads each window row of the tile as 16-byte
+// (CPT = 4) or 8-byte (CPT = 2) shared-memory loads. What this removes against k_var_aggregate_x4 / k_var_aggregate: the 5- / 7-fold
+// re-read of every plane row through L2 by the blocks of neighbouring rows (one block per row there) whose latency 12 resident
+// warps could not hide; the tile is read 1.6 - 2.1 times. Weights of window cells outside the image are 0 and their tile
+// values 0: the sum takes the same terms in the same order as the reference's clipped loop plus exact zeros. No border launch.
+template<int R, int CPT, bool VEC>
+__global__ void __launch_bounds__(128, 3) k_var_aggregate_tile(const Agg p) {
+	// VEC (16-byte aligned rows, W % 4 == 0): the tile starts four columns left of the block so that it is made of whole 16-byte
+	// units, fetched and stored as float4 (1 - 2 per thread and plane instead of 5 - 7 scalars)
+	constexpr int N = 2 * R + 1, TXN = 16, TYN = 8;
+	constexpr int ORG = VEC ? 4 : R, SHIFT = ORG - R;
+	constexpr int TC = TXN * CPT, TR = TYN, TW = TC + 2 * ORG, TH = TR + 2 * R;
+	constexpr int PITCH = (TW + 3) / 4 * 4;
+	constexpr int EL = VEC ? TH * (TW / 4) : TH * TW;       // elements (float4 or float) of a plane's tile
+	constexpr int K = (EL + 127) / 128;
+	constexpr int LW = CPT == 4 ? 4 : 2;                     // floats per shared-memory load
+	constexpr int NV = (CPT + 2 * R + SHIFT + LW - 1) / LW * LW;
+	__shared__ __align__(16) float tile[2][TH * PITCH];
+	const int tx = threadIdx.x % TXN, ty = threadIdx.x / TXN;
+	const int j0 = blockIdx.x * TC, i0 = blockIdx.y * TR;
+	const int j = j0 + tx * CPT, i = i0 + ty;
+	const int c_begin = blockIdx.z * p.chunk, c_end = min(p.D, c_begin + p.chunk);
+	// the elements of the tile this thread moves: a pointer into the first plane (nullptr outside the image) and the place in the tile
+	const float* src[K];
+	int sidx[K];
+#pragma unroll
+	for (int k = 0; k < K; k++) {
+		const int e = threadIdx.x + k * 128;
+		constexpr int PER_ROW = VEC ? TW / 4 : TW;
+		const int r = e / PER_ROW, t = (e - r * PER_ROW) * (VEC ? 4 : 1);
+		const int gi = i0 - R + r, gj = j0 - ORG + t;
+		const bool in = e < EL && gi >= 0 && gi < p.H && gj >= 0 && gj + (VEC ? 4 : 1) <= p.W;
+		src[k] = in ? p.cv + (int64_t)gi * p.c0 + gj + (int64_t)c_begin * p.c2 : nullptr;
+		sidx[k] = e < EL ? r * PITCH + t : -1;
+	}
+	float w[CPT][N][N], weight[CPT];
+#pragma unroll
+	for (int q = 0; q < CPT; q++) {
+		const bool pix = i < p.H && j + q < p.W;
+		const float* wp = p.win + (int64_t)(pix ? i : 0) * p.w0 + (int64_t)(pix ? j + q : 0) * p.w1;
+		weight[q] = 0.f;
+#pragma unroll
+		for (int a = 0; a < N; a++)
+#pragma unroll
+			for (int b = 0; b < N; b++) {
+				const int gi = i + a - R, gj = j + q + b - R;
+				const bool in = pix && gi >= 0 && gi < p.H && gj >= 0 && gj < p.W;
+				const float x = in ? wp[a * p.w2 + b * p.w3] : 0.f;
+				w[q][a][b] = x;
+				if (in) weight[q] = __fadd_rn(weight[q], x);
+			}
+	}
+	typedef typename std::conditional<VEC, float4, float>::type El;
+	auto fetch = [](const float* q) -> El {
+		if constexpr (VEC) return q ? __ldg(reinterpret_cast<const float4*>(q)) : make_float4(0.f, 0.f, 0.f, 0.f);
+		else return q ? __ldg(q) : 0.f;
+	};
+#pragma unroll
+	for (int k = 0; k < K; k++)
+		if (sidx[k] >= 0) *reinterpret_cast<El*>(&tile[0][sidx[k]]) = fetch(src[k]);
+	__syncthreads();
+	float* dst = p.out + (int64_t)min(i, p.H - 1) * p.o0 + (int64_t)min(j, p.W - 1) * p.o1 + (int64_t)c_begin * p.o2;
+	const bool vec = p.vec_out && i < p.H && j + CPT <= p.W;
+	for (int c = c_begin; c < c_end; c++) {
+		const int buf = (c - c_begin) & 1;
+		const bool more = c + 1 < c_end;
+		El nx[K];
+#pragma unroll
+		for (int k = 0; k < K; k++) {
+			if (src[k]) src[k] += p.c2;
+			nx[k] = fetch(more ? src[k] : nullptr);
+		}
+		float acc[CPT];
+#pragma unroll
+		for (int q = 0; q < CPT; q++) acc[q] = 0.f;
+		const float* trow = &tile[buf][ty * PITCH + tx * CPT];
+#pragma unroll
+		for (int a = 0; a < N; a++) {
+			float v[NV];
+			if (LW == 4) {
+#pragma unroll
+				for (int u = 0; u < NV / 4; u++) {
+					const float4 x = *reinterpret_cast<const float4*>(trow + a * PITCH + 4 * u);
+					v[4 * u] = x.x; v[4 * u + 1] = x.y; v[4 * u + 2] = x.z; v[4 * u + 3] = x.w;
+				}
+			} else {
+#pragma unroll
+				for (int u = 0; u < NV / 2; u++) {
+					const float2 x = *reinterpret_cast<const float2*>(trow + a * PITCH + 2 * u);
+					v[2 * u] = x.x; v[2 * u + 1] = x.y;
+				}
+			}
+#pragma unroll
+			for (int b = 0; b < N; b++)
+#pragma unroll
+				for (int q = 0; q < CPT; q++) acc[q] = __fadd_rn(acc[q], __fmul_rn(w[q][a][b], v[SHIFT + q + b]));
+		}
+		float res[CPT];
+#pragma unroll
+		for (int q = 0; q < CPT; q++) res[q] = __fdiv_rn(acc[q], weight[q]);
+		if (vec) {
+			if (CPT == 4) *reinterpret_cast<float4*>(dst) = make_float4(res[0], res[1], res[2], res[3]);
+			else *reinterpret_cast<float2*>(dst) = make_float2(res[0], res[1]);
+		} else if (i < p.H) {
+#pragma unroll
+			for (int q = 0; q < CPT; q++)
+				if (j + q < p.W) dst[q * p.o1] = res[q];
+		}
+		dst += p.o2;
+		if (more) {
+#pragma unroll
+			for (int k = 0; k < K; k++)
+				if (sidx[k] >= 0) *reinterpret_cast<El*>(&tile[buf ^ 1][sidx[k]]) = nx[k];
+		}
+		__syncthreads();
+	}
+}
+
 // the frame of pixels k_var_aggregate_x4 skips: rows [0, top) and [bot, H) in full, columns [0, 4) and [W - 4, W) of the rows
 // in between; thread per (pixel, disparity)
 __global__ void __launch_bounds__(128) k_var_aggregate_border(const Agg p, int top, int bot) {
@@ -209,6 +332,21 @@ int32_t var_aggregate_dev(stevi_ctx* c, const View& cv, const View& win, const V
 	static const bool no_x4 = getenv("STEVI_AGG_NO_X4") != nullptr;   // measurement aid: the one-column-per-thread kernels only
 	const bool x4 = !no_x4 && (key == 1 || key == 2) && cv.st[1] == 1 && aligned(cv.p, cv.st[0], cv.st[2]) && W >= 16 && W % 4 == 0;
 	p.vec_out = out.st[1] == 1 && aligned(out.p, out.st[0], out.st[2]) ? 1 : 0;
+	static const bool no_tile = getenv("STEVI_AGG_NO_TILE") != nullptr;   // measurement aid: the kernels without the shared-memory tile
+	if (!no_tile && (key == 2 || key == 3) && cv.st[1] == 1) {
+		const int tc = key == 2 ? 64 : 32;
+		const int tiles = cdiv(W, tc) * cdiv(H, 8);
+		int slices = std::max(1, std::min(cdiv(D, 16), cdiv(c->sm_count * 3 * 4, tiles)));
+		p.chunk = cdiv(D, slices);
+		slices = cdiv(D, p.chunk);
+		// 16-byte (8-byte) stores of a thread's four (two) results
+		p.vec_out = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0 ? 1 : 0;
+		dim3 grid(cdiv(W, tc), cdiv(H, 8), slices);
+		const bool vec_in = aligned(cv.p, cv.st[0], cv.st[2]) && W % 4 == 0;
+		if (key == 2) { if (vec_in) STEVI_LAUNCH(c, (k_var_aggregate_tile<2, 4, true>), grid, 128, 0, p); else STEVI_LAUNCH(c, (k_var_aggregate_tile<2, 4, false>), grid, 128, 0, p); }
+		else { if (vec_in) STEVI_LAUNCH(c, (k_var_aggregate_tile<3, 2, true>), grid, 128, 0, p); else STEVI_LAUNCH(c, (k_var_aggregate_tile<3, 2, false>), grid, 128, 0, p); }
+		return STEVI_OK;
+	}
 	// slices of the disparity axis: enough blocks for a few waves over the SMs, each thread amortising its weight loads
 	const int col_blocks = x4 ? cdiv(cdiv(W, 4), 128) : cdiv(W, 128);
 	const int tiles = col_blocks * H;

@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-N=${NGPU:-2}
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --workload c4 --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_c4_${N}gpu.json 2> gpurun_out/bench_c4_${N}gpu.err
-tail -c 1800 gpurun_out/bench_c4_${N}gpu.json; tail -3 gpurun_out/bench_c4_${N}gpu.err
+timeout 900 python -m pytest tests/test_gpu_aggregation.py -m gpu -q -x 2>&1 | grep -E "^E  |Error|passed|failed|^FAILED" | head -20
+timeout 300 python scripts/quick_bench_aggregation.py aggregation 2>&1 | tee gpurun_out/stage_aggregation.jsonl | tail -6

@@ -16,7 +16,7 @@ G2 = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_output
 
 @pytest.mark.parametrize("H,W,D,vr,hr", [(23, 150, 9, 1, 1), (40, 300, 33, 2, 2), (17, 129, 5, 3, 3), (12, 140, 7, 1, 3), (9, 131, 4, 4, 0),
                                          (5, 4, 3, 3, 3), (1, 1, 2, 2, 2), (11, 512, 6, 2, 2), (9, 516, 35, 1, 1), (8, 20, 3, 2, 2),
-                                         (7, 1030, 4, 2, 2)])
+                                         (7, 1030, 4, 2, 2), (21, 203, 19, 3, 3), (33, 260, 21, 3, 3), (19, 77, 6, 2, 2), (9, 64, 40, 3, 3)])
 def test_aggregation_matches_oracle(api, ctx, oracle, H, W, D, vr, hr):
     rng = np.random.default_rng(H * W)
     cv = rng.uniform(-2, 2, (H, W, D)).astype(np.float32)
@@ -26,6 +26,25 @@ def test_aggregation_matches_oracle(api, ctx, oracle, H, W, D, vr, hr):
     ref_layout = np.ascontiguousarray(cv.transpose(0, 2, 1)).transpose(0, 2, 1)          # {W*D, 1, W}
     got = api.variableCostVolumeAggregation(ref_layout, win, layout="ref", ctx=ctx)
     assert got.transpose(0, 2, 1).flags.c_contiguous and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("r", [1, 2, 3])
+def test_aggregation_on_column_sliced_views(api, ctx, oracle, r):
+    """A column-sliced view of a volume in the reference's layout (pitch wider than the view, width not a multiple of 4): the
+    16-byte paths must not be taken for it, and every column is written."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(70 + r)
+    H, Wfull, W, D = 14, 48, 45, 10
+    full = rng.uniform(-1, 1, (H, D, Wfull)).astype(np.float32)
+    win = rng.uniform(0.01, 1, (H, W, 2 * r + 1, 2 * r + 1)).astype(np.float32)
+    tctx = api.Context(0, torch_stream=True)
+    view = torch.from_numpy(full).cuda().permute(0, 2, 1)[:, 1:1 + W]          # strides {Wfull*D, 1, Wfull}, first column off alignment
+    out = torch.full((H, D, Wfull), float("nan"), device="cuda").permute(0, 2, 1)[:, 1:1 + W]
+    api.variableCostVolumeAggregation(view, torch.from_numpy(win).cuda(), out=out, ctx=tctx)
+    torch.cuda.synchronize()
+    want = oracle.port.variable_cost_volume_aggregation(np.ascontiguousarray(full.transpose(0, 2, 1)[:, 1:1 + W]), win)
+    assert np.array_equal(out.cpu().numpy(), want)
+    tctx.close()
 
 
 def test_aggregation_golden_and_pipeline(api, ctx, oracle):
