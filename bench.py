@@ -530,11 +530,6 @@ def main_census(args, wl, rank, world, local_rank, dist=None, steps=None, with_c
                      "ms_per_step": ms_sus / n_sus, "clocks": sus_clocks}
 
     # dominant kernel, per launch, CUDA events on the launching stream (second pass with the ctx's event hooks on)
-    ms_sharded = None
-    if hier and world > 1:
-        for _ in range(warmup):
-            step_sharded()
-        ms_sharded, _ = timed(step_sharded, steps)
     ctx.set_timing(True)
     per_kernel = {}
     for _ in range(max(3, min(steps, 10))):
