@@ -65,95 +65,105 @@ __device__ __forceinline__ void gram(const float* const (&p)[N], const int64_t (
 		for (int b = a; b < N; b++, e++) { const double s = gsum(acc[e]); G[a][b] = s; G[b][a] = s; }
 }
 
-// P x = r for nr right-hand sides, Gaussian elimination with full pivoting; P and r are destroyed. A pivot that is negligible
-// against the first one ends the elimination: the remaining unknowns stay 0.
-__device__ void solve_small(int n, double (*P)[MAXK + 1], int nr, double (*r)[MAXK + 1], double (*x)[MAXK + 1]) {
-	int perm[MAXK + 1];
-	for (int k = 0; k < n; k++) perm[k] = k;
-	const double thr = (double)FLT_EPSILON * n * (double)FLT_EPSILON * n;
-	double first = 0.0;
-	int rank = n;
-	for (int k = 0; k < n; k++) {
-		int pr = k, pc = k;
-		double big = -1.0;
-		for (int i = k; i < n; i++) for (int j = k; j < n; j++) { const double v = fabs(P[i][j]); if (v > big) { big = v; pr = i; pc = j; } }
-		if (k == 0) first = big;
-		if (!(big > first * thr)) { rank = k; break; }
-		if (pr != k) {
-			for (int j = 0; j < n; j++) { const double t = P[k][j]; P[k][j] = P[pr][j]; P[pr][j] = t; }
-			for (int q = 0; q < nr; q++) { const double t = r[q][k]; r[q][k] = r[q][pr]; r[q][pr] = t; }
-		}
-		if (pc != k) {
-			for (int i = 0; i < n; i++) { const double t = P[i][k]; P[i][k] = P[i][pc]; P[i][pc] = t; }
-			const int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t;
-		}
-		const double inv = 1.0 / P[k][k];
-		for (int i = k + 1; i < n; i++) {
-			const double f = P[i][k] * inv;
-			for (int j = k + 1; j < n; j++) P[i][j] -= f * P[k][j];
-			for (int q = 0; q < nr; q++) r[q][i] -= f * r[q][k];
+// A x = b for a symmetric positive semi-definite A (a Gram matrix), N known at compile time so that everything stays in
+// registers: Gaussian elimination without exchanges (safe on Gram matrices); a pivot that is negligible against the largest
+// diagonal entry marks a dependent column, whose unknown stays 0 — the basic solution a rank-revealing QR gives. A and b are destroyed.
+template<int N>
+__device__ __forceinline__ void solve_gram(double (&A)[N][N], double (&b)[N], double (&x)[N]) {
+	double maxd = 0.0;
+#pragma unroll
+	for (int k = 0; k < N; k++) maxd = fmax(maxd, fabs(A[k][k]));
+	const double thr = maxd * ((double)FLT_EPSILON * N) * ((double)FLT_EPSILON * N);
+	double inv[N];
+#pragma unroll
+	for (int k = 0; k < N; k++) {
+		inv[k] = fabs(A[k][k]) > thr ? 1.0 / A[k][k] : 0.0;
+#pragma unroll
+		for (int i = k + 1; i < N; i++) {
+			const double f = A[i][k] * inv[k];
+#pragma unroll
+			for (int j = k + 1; j < N; j++) A[i][j] -= f * A[k][j];
+			b[i] -= f * b[k];
 		}
 	}
-	for (int q = 0; q < nr; q++) {
-		for (int k = 0; k < n; k++) x[q][k] = 0.0;
-		for (int k = rank - 1; k >= 0; k--) {
-			double s = r[q][k];
-			for (int j = k + 1; j < rank; j++) s -= P[k][j] * r[q][j];
-			r[q][k] = s / P[k][k];
-		}
-		for (int k = 0; k < rank; k++) x[q][perm[k]] = r[q][k];
+#pragma unroll
+	for (int k = N - 1; k >= 0; k--) {
+		double s = b[k];
+#pragma unroll
+		for (int j = k + 1; j < N; j++) s -= A[k][j] * x[j];
+		x[k] = s * inv[k];
 	}
 }
 
 // Coefficients of the best affine combination of the columns cols[0..K] of the Gram matrix (the last one is the origin of the
 // affine space: optimization/affine_utils.h:44-57 with referenceId = -1) to the source vector ib.
 // L2: l2optimization.h:48-63. Spherical: sphericaloptimization.h:35-63, every product it forms expressed through G.
-__device__ void bary_coeffs(int family, int K, const int* cols, int ib, const double (*G)[MAXN], float* coeffs) {
-	double P[MAXK + 1][MAXK + 1], r[2][MAXK + 1], x[2][MAXK + 1], q[MAXK + 1];
-	const int cK = cols[K];
-	const double gKK = G[cK][cK];
-	auto load_P = [&]() {
-		for (int a = 0; a < K; a++) for (int b = 0; b < K; b++) P[a][b] = G[cols[a]][cols[b]] - G[cols[a]][cK] - G[cols[b]][cK] + gKK;
-	};
-	for (int a = 0; a < K; a++) q[a] = G[cols[a]][cK] - gKK; // M^T a_K
-	double alpha[MAXK + 1];
+template<int K>
+__device__ __forceinline__ void bary_coeffs(int family, const int* cols, int ib, const double (*G)[MAXN], float* coeffs) {
+	double g[K + 1][K + 1], gb[K + 1];   // Gram matrix of the K+1 columns, and their products with the source
+#pragma unroll
+	for (int a = 0; a <= K; a++) {
+		gb[a] = G[cols[a]][ib];
+#pragma unroll
+		for (int b = 0; b <= K; b++) g[a][b] = G[cols[a]][cols[b]];
+	}
+	const double gKK = g[K][K];
+	double P[K][K], q[K], r[K], alpha[K];
+#pragma unroll
+	for (int a = 0; a < K; a++) {
+		q[a] = g[a][K] - gKK; // M^T a_K
+#pragma unroll
+		for (int b = 0; b < K; b++) P[a][b] = g[a][b] - g[a][K] - g[b][K] + gKK;
+	}
 	if (family == FAM_L2) {
-		load_P();
-		for (int a = 0; a < K; a++) r[0][a] = (G[cols[a]][ib] - G[cK][ib]) - q[a];
-		solve_small(K, P, 1, r, x);
-		for (int a = 0; a < K; a++) alpha[a] = x[0][a];
+#pragma unroll
+		for (int a = 0; a < K; a++) r[a] = (gb[a] - gb[K]) - q[a];
+		solve_gram<K>(P, r, alpha);
 	} else {
 		// bPerp = A lstsq(A, b)
-		double xa[MAXK + 1];
-		for (int a = 0; a <= K; a++) { for (int b = 0; b <= K; b++) P[a][b] = G[cols[a]][cols[b]]; r[0][a] = G[cols[a]][ib]; }
-		solve_small(K + 1, P, 1, r, x);
-		for (int a = 0; a <= K; a++) xa[a] = x[0][a];
+		double ga[K + 1][K + 1], ra[K + 1], xa[K + 1];
+#pragma unroll
+		for (int a = 0; a <= K; a++) {
+			ra[a] = gb[a];
+#pragma unroll
+			for (int b = 0; b <= K; b++) ga[a][b] = g[a][b];
+		}
+		solve_gram<K + 1>(ga, ra, xa);
 		// aPerp = a_K - M lstsq(M, a_K)
-		load_P();
-		for (int a = 0; a < K; a++) r[0][a] = q[a];
-		solve_small(K, P, 1, r, x);
-		double y[MAXK + 1];
-		for (int a = 0; a < K; a++) y[a] = x[0][a];
-		load_P();
-		double aa = gKK, ab = 0.0;
-		for (int a = 0; a < K; a++) { double s = 0.0; for (int b = 0; b < K; b++) s += P[a][b] * y[b]; aa += y[a] * (s - 2.0 * q[a]); }
-		double w[MAXK + 1];
-		for (int a = 0; a < K; a++) w[a] = 0.0;
+		double P2[K][K], y[K];
+#pragma unroll
+		for (int a = 0; a < K; a++) {
+			r[a] = q[a];
+#pragma unroll
+			for (int b = 0; b < K; b++) P2[a][b] = P[a][b];
+		}
+		solve_gram<K>(P2, r, y);
+		double aa = gKK, ab = 0.0, w[K];
+#pragma unroll
+		for (int a = 0; a < K; a++) {
+			double s = 0.0;
+#pragma unroll
+			for (int b = 0; b < K; b++) s += P[a][b] * y[b];
+			aa += y[a] * (s - 2.0 * q[a]);
+			w[a] = 0.0;
+		}
+#pragma unroll
 		for (int i = 0; i <= K; i++) {
-			double u = G[cK][cols[i]]; // aPerp . a_i
-			for (int a = 0; a < K; a++) { const double m = G[cols[a]][cols[i]] - G[cK][cols[i]]; u -= y[a] * m; w[a] += xa[i] * m; }
+			double u = g[K][i]; // aPerp . a_i
+#pragma unroll
+			for (int a = 0; a < K; a++) { const double m = g[a][i] - g[K][i]; u -= y[a] * m; w[a] += xa[i] * m; }
 			ab += xa[i] * u;
 		}
-		const double g = aa / ab;
-		for (int a = 0; a < K; a++) r[0][a] = g * w[a] - q[a];
-		solve_small(K, P, 1, r, x);
-		for (int a = 0; a < K; a++) alpha[a] = x[0][a];
+		const double gg = aa / ab;
+#pragma unroll
+		for (int a = 0; a < K; a++) r[a] = gg * w[a] - q[a];
+		solve_gram<K>(P, r, alpha);
 	}
 	float sum = 0.f;
+#pragma unroll
 	for (int a = 0; a < K; a++) { coeffs[a] = (float)alpha[a]; sum += coeffs[a]; }
 	coeffs[K] = 1.f - sum; // affine_utils.h:83-97
 }
-
 // featureComparison(source / |source|, A coeffs / |A coeffs|) for the normalised functions, SumSquareDiff(source, A coeffs)
 // otherwise (image_based_refinement.h:293-306), from the Gram matrix
 __device__ double score_of(int family, int K, const int* cols, int ib, const double (*G)[MAXN], const float* coeffs) {
@@ -197,7 +207,7 @@ __global__ void __launch_bounds__(BLOCK) k_bary_1d(const Bary p) {
 	if (work && lane < 2) {
 		const int* cols = lane == 0 ? cp : cm;
 		float k[2];
-		bary_coeffs(p.family, 1, cols, 3, G, k);
+		bary_coeffs<1>(p.family, cols, 3, G, k);
 		frac = lane == 0 ? k[1] : k[0];
 		adm = frac > 0.f && frac < 1.f;
 		if (adm) sc = score_of(p.family, 1, cols, 3, G, k);
@@ -307,7 +317,7 @@ __global__ void __launch_bounds__(BLOCK) k_bary_sym_1d(const Bary p) {
 		int cols[N - 1];
 		float co[N - 1];
 		for (int k = 0; k < N - 1; k++) cols[k] = k;
-		bary_coeffs(p.family, N - 2, cols, N - 1, G, co);
+		bary_coeffs<N - 2>(p.family, cols, N - 1, G, co);
 		float delta = 0.f;
 		for (int k = 0; k < N - 1; k++) delta = __fadd_rn(delta, __fmul_rn(co[k], (float)(k - R))); // :88-91
 		if (fabsf(delta) < 1.f) res = __fadd_rn((float)d, delta);
@@ -324,6 +334,7 @@ __constant__ int c_dirs[3][8][2] = {{{1, 1}, {1, 0}, {1, -1}, {0, 1}, {0, -1}, {
 									 {{1, 1}, {1, -1}, {-1, 1}, {-1, -1}, {0, 0}, {0, 0}, {0, 0}, {0, 0}}};
 __constant__ int c_ndirs[3] = {8, 4, 4};
 
+template<int K>
 __global__ void __launch_bounds__(BLOCK) k_bary_2d(const Bary p) {
 	const int lane = threadIdx.x & (GL - 1);
 	const int j = blockIdx.x * (BLOCK / GL) + threadIdx.x / GL, i = blockIdx.y;
@@ -343,13 +354,12 @@ __global__ void __launch_bounds__(BLOCK) k_bary_2d(const Bary p) {
 	gram<10>(vec, st, work ? p.F : 0, lane, G);
 	// one system per lane (the four quadrants; a single one for the symmetric form); lane 0 takes them in the reference's order
 	const int nsys = p.symmetric ? 1 : 4;
-	const int K = p.symmetric ? c_ndirs[p.contiguity] : c_ncorner[p.contiguity];
 	float t0 = 0.f, t1 = 0.f;
 	double sc = 0.0;
 	bool adm = false;
 	if (work && lane < nsys) {
-		int cols[MAXK + 1];
-		float co[MAXK + 1];
+		int cols[K + 1];
+		float co[K + 1];
 		const int s = lane;
 		const int sx = p.symmetric ? 1 : (s < 2 ? 1 : -1), sy = p.symmetric ? 1 : ((s & 1) ? -1 : 1); // dirShifts = {1,-1}, x outer (:783-790)
 		for (int k = 0; k < K; k++) {
@@ -358,7 +368,7 @@ __global__ void __launch_bounds__(BLOCK) k_bary_2d(const Bary p) {
 			cols[k] = 3 * (di + 1) + (dj + 1);
 		}
 		cols[K] = 4;
-		bary_coeffs(p.family, K, cols, 9, G, co);
+		bary_coeffs<K>(p.family, cols, 9, G, co);
 		for (int k = 0; k < K; k++) {
 			const int di = cols[k] / 3 - 1, dj = cols[k] % 3 - 1;
 			t0 = __fadd_rn(t0, __fmul_rn(co[k], (float)di));
@@ -515,7 +525,14 @@ int32_t refine_barycentric_2d_dev(stevi_ctx* c, int mf, int contiguity, int symm
 	p.contiguity = contiguity; p.symmetric = symmetric ? 1 : 0;
 	if (p.H == 0 || p.W == 0) return STEVI_OK;
 	dim3 grid(cdiv(p.W, BLOCK / GL), p.H);
-	STEVI_LAUNCH(c, k_bary_2d, grid, BLOCK, 0, p);
+	const int K = symmetric ? (contiguity == STEVI_QUEEN ? 8 : 4) : (contiguity == STEVI_QUEEN ? 3 : contiguity == STEVI_ROOK ? 2 : 1);
+	switch (K) {
+	case 1: STEVI_LAUNCH(c, k_bary_2d<1>, grid, BLOCK, 0, p); break;
+	case 2: STEVI_LAUNCH(c, k_bary_2d<2>, grid, BLOCK, 0, p); break;
+	case 3: STEVI_LAUNCH(c, k_bary_2d<3>, grid, BLOCK, 0, p); break;
+	case 4: STEVI_LAUNCH(c, k_bary_2d<4>, grid, BLOCK, 0, p); break;
+	default: STEVI_LAUNCH(c, k_bary_2d<8>, grid, BLOCK, 0, p); break;
+	}
 	return STEVI_OK;
 }
 
