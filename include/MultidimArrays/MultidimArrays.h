@@ -310,6 +310,19 @@ public:
 		return Array<T, nDim - 1, viewConstness>(_data + long(index) * _strides[dim], shape, strides, false);
 	}
 
+	// the 1-D view along dimension `dim` at the position given for the other dimensions, in their order (on-demand cost volumes
+	// read one pixel's feature vector with it: correlation/on_demand_cost_volume.h:164-172)
+	template<typename P>
+	Array<T, 1, ConstView> indexDimView(int dim, P const& otherIdxs) const {
+		long off = 0;
+		int o = 0;
+		for (int k = 0; k < nDim; k++) {
+			if (k == dim) continue;
+			off += long(otherIdxs[o]) * _strides[k]; o++;
+		}
+		return Array<T, 1, ConstView>(_data + off, std::array<int, 1>{_shape[dim]}, std::array<int, 1>{_strides[dim]}, false);
+	}
+
 private:
 	void allocate() {
 		size_t n = span();

@@ -348,6 +348,33 @@ STEVI_API int32_t stevi_refine_barycentric_2d_disp(stevi_ctx* ctx, int32_t match
 STEVI_API int32_t stevi_refine_cost_symmetric_disp(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_l, const stevi_array* feat_r,
 										 const stevi_array* idx, const stevi_array* cv, int32_t direction, stevi_array* out);
 
+/* ---- on-demand costs and PatchMatch ----------------------------------------------------------------
+ * feat_source (H,W,F), feat_target (Ht,Wt,F) f32: raw feature volumes (what unfold gives); the function's processing (zero mean,
+ * normalisation) is applied inside, like the reference does. search_dims = 1: search along the columns, search = {lower, upper},
+ * Ht must equal H; search_dims = 2: search = {lower0, upper0, lower1, upper1} (rows, columns). A cell (pixel, disparity) has no
+ * value when the disparity is outside the search range or the target pixel outside the target image. CC .. ZSAD. */
+
+/* patchMatch<matchFunc, searchSpaceDim>(feature_vol_s, feature_vol_t, searchOffset, nIter, nRandomSearch, initializer)
+ * (correlation/patchmatch.h:498-556 over patchMatchImpl :449-496, patchMatchPropagate :371-446, patchMatchSearch :233-369,
+ * patchMatchTestCost :166-231) -> disp (H,W,search_dims) i32. Per iteration: the reference's row scans and column scans in the
+ * iteration's direction (each pixel tests its predecessor's disparity and keeps it when it compares at least as well), then
+ * n_random_search random candidates per pixel pulled towards its current disparity; an iteration without a change ends the run.
+ * init (nullable): the initial map (the reference's `initializer`); NULL = uniform random disparities in the search range
+ * (randomDispInit, :57-160). With n_random_search = 0 and an init the result equals the reference's bit for bit; the random draws
+ * come from a counter-based generator keyed by `seed` (the reference seeds from std::random_device: its own runs differ). */
+STEVI_API int32_t stevi_patch_match(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_source, const stevi_array* feat_target,
+						  int32_t search_dims, const int32_t* search, int32_t n_iter, int32_t n_random_search, uint64_t seed,
+						  const stevi_array* init, stevi_array* disp);
+
+/* OnDemand*CostVolume::truncatedCostVolume(disp, radius) (correlation/on_demand_cost_volume.h:187-310): the costs of the cells
+ * around each pixel's disparity, evaluated where asked for — no cost volume exists. disp (H,W) or (H,W,1) i32 for a 1-D search,
+ * (H,W,2) for a 2-D one -> out (H,W,2r+1) / (H,W,2r+1,2r+1) f32; cells without a value hold defaultCvValForMatchFunc
+ * (matching_costs.h:706-713: FLT_MAX for costs, FLT_MIN for scores). The features are processed once, as the on-demand volume's
+ * constructor does (:63-68). Like the reference (:224-241) the window is shifted by the lower search offset when that is not 0. */
+STEVI_API int32_t stevi_on_demand_truncated_cost_volume(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_source,
+											  const stevi_array* feat_target, int32_t search_dims, const int32_t* search,
+											  const stevi_array* disp, int32_t radius, stevi_array* out);
+
 /* ---- coarse-to-fine matching ---------------------------------------------------------------------------------- */
 
 /* meanFilter2D(h_radius, v_radius, in_data) (correlation/correlation_base.h:881-938 for (H,W), :941-1004 for (H,W,C) images):

@@ -808,6 +808,44 @@ def refinedCostSymmetricDisp(matchFunc, img_l, img_r, h_radius, v_radius, search
     return refinedCostSymmetricDispFeatureVol(matchFunc, fl, fr, searchRange, preNormalize, dDir, ctx=ctx)
 
 
+def _search_arg(searchOffset):
+    v = [int(x) for x in searchOffset]
+    if len(v) not in (2, 4):
+        raise ValueError("searchOffset: (lower, upper) for a 1-D search, (lower0, upper0, lower1, upper1) for a 2-D one")
+    return (ctypes.c_int32 * len(v))(*v), len(v) // 2
+
+
+def patchMatch(matchFunc, feature_vol_s, feature_vol_t, searchOffset, nIter=5, nRandomSearch=4, initializer=None, seed=0, ctx=None):
+    """patchMatch<matchFunc, searchSpaceDim>, correlation/patchmatch.h:498-556: (H,W,F) f32 RAW feature volumes (source, target),
+    ``searchOffset`` = (lower, upper) or (lower0, upper0, lower1, upper1) -> disparities (H,W,searchSpaceDim) int32. ``initializer``:
+    an (H,W,searchSpaceDim) int32 map to start from (the reference's initializer functor's result); None = uniform random in the
+    range. ``seed`` keys the counter-based generator of the random draws. None where the reference returns an empty array."""
+    ctx = _ctx_for(ctx, feature_vol_s)
+    so, dims = _search_arg(searchOffset)
+    out = _empty(feature_vol_s, tuple(feature_vol_s.shape[:2]) + (dims,), np.int32)
+    s, t, o = describe(feature_vol_s), describe(feature_vol_t), describe(out)
+    i = describe(initializer) if initializer is not None else None
+    rc = lib.stevi_patch_match(ctx.handle, matchFunc, ctypes.byref(s), ctypes.byref(t), dims, so, nIter, nRandomSearch, ctypes.c_uint64(seed),
+                               ctypes.byref(i) if i is not None else None, ctypes.byref(o))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return out
+
+
+def onDemandTruncatedCostVolume(matchFunc, feature_vol_s, feature_vol_t, searchOffset, disp, radius=1, ctx=None):
+    """OnDemand*CostVolume(source, target, searchSpace).truncatedCostVolume(disp, radius), correlation/on_demand_cost_volume.h:187-310:
+    the costs around each pixel's disparity evaluated on demand -> (H,W,2r+1) or (H,W,2r+1,2r+1) float32."""
+    ctx = _ctx_for(ctx, feature_vol_s)
+    so, dims = _search_arg(searchOffset)
+    n = 2 * radius + 1
+    out = _empty(feature_vol_s, tuple(feature_vol_s.shape[:2]) + (n,) * dims, np.float32)
+    s, t, d, o = describe(feature_vol_s), describe(feature_vol_t), describe(disp), describe(out)
+    ctx.check(lib.stevi_on_demand_truncated_cost_volume(ctx.handle, matchFunc, ctypes.byref(s), ctypes.byref(t), dims, so, ctypes.byref(d),
+                                                        radius, ctypes.byref(o)))
+    return out
+
+
 def refineFromCostVolume(cv, idx, h_radius, v_radius, kernel=PARABOLA, return_tcv=False, ctx=None):
     """truncatedCostVolume<Same>(radius 1) + refineDispCostInterpolation fused into one pass over the winners."""
     ctx = _ctx_for(ctx, cv)

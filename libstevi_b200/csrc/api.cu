@@ -478,6 +478,32 @@ int32_t stevi_refine_cost_symmetric_disp(stevi_ctx* c, int32_t mf, const stevi_a
 	return st.finish();
 }
 
+int32_t stevi_patch_match(stevi_ctx* c, int32_t mf, const stevi_array* fs, const stevi_array* ft, int32_t dims, const int32_t* search,
+						  int32_t n_iter, int32_t n_random, uint64_t seed, const stevi_array* init, stevi_array* disp) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vs, vt, vi, vd;
+	STEVI_TRY(st.in(fs, vs, "feat_source"));
+	STEVI_TRY(st.in(ft, vt, "feat_target"));
+	if (init) STEVI_TRY(st.in(init, vi, "init"));
+	STEVI_TRY(st.out(disp, vd, "disp"));
+	STEVI_TRY(patch_match_dev(c, mf, vs, vt, dims, search, n_iter, n_random, seed, init ? &vi : nullptr, vd));
+	return st.finish();
+}
+
+int32_t stevi_on_demand_truncated_cost_volume(stevi_ctx* c, int32_t mf, const stevi_array* fs, const stevi_array* ft, int32_t dims,
+											  const int32_t* search, const stevi_array* disp, int32_t radius, stevi_array* out) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vs, vt, vd, vo;
+	STEVI_TRY(st.in(fs, vs, "feat_source"));
+	STEVI_TRY(st.in(ft, vt, "feat_target"));
+	STEVI_TRY(st.in(disp, vd, "disp"));
+	STEVI_TRY(st.out(out, vo, "out"));
+	STEVI_TRY(on_demand_tcv_dev(c, mf, vs, vt, dims, search, vd, radius, vo));
+	return st.finish();
+}
+
 int32_t stevi_mean_filter_2d(stevi_ctx* c, const stevi_array* img, int32_t hr, int32_t vr, stevi_array* out) {
 	STEVI_TRY(begin_call(c));
 	Stager st(c);

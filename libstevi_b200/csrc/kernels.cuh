@@ -96,6 +96,13 @@ int32_t refine_barycentric_2d_dev(stevi_ctx* c, int mf, int contiguity, int symm
 								  const int32_t* search, int direction, const View& out2);
 int32_t refine_cost_symmetric_dev(stevi_ctx* c, int mf, const View& fl, const View& fr, const View& idx, const View& cv, int direction, const View& out);
 
+// patchmatch.cu: on-demand cost evaluation and PatchMatch (on_demand_cost_volume.h, patchmatch.h); search = {lower, upper} for a
+// 1-D search (columns), {lower0, upper0, lower1, upper1} for a 2-D one; disp (H,W,dims) i32
+int32_t patch_match_dev(stevi_ctx* c, int mf, const View& fs, const View& ft, int dims, const int32_t* search, int n_iter, int n_random,
+						unsigned long long seed, const View* init, const View& disp);
+int32_t on_demand_tcv_dev(stevi_ctx* c, int mf, const View& fs, const View& ft, int dims, const int32_t* search, const View& disp, int radius,
+						  const View& out);
+
 // aggregate.cu: variableCostVolumeAggregation (guided_cost_filtering.h:102-176)
 int32_t var_aggregate_dev(stevi_ctx* c, const View& cv, const View& win, const View& out);
 

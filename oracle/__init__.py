@@ -420,6 +420,27 @@ class _Checker:
                                                    cv.shape[2], direction, _p(out))
         return out if rc == 0 else None
 
+    # --- on-demand cost volumes and PatchMatch (on_demand_cost_volume.h, patchmatch.h) --
+    def patch_match(self, mf, fs, ft, search, n_iter=5, n_random=4, init=None):
+        fs, ft = _c(fs, np.float32), _c(ft, np.float32)
+        so = np.asarray(search, np.int32)
+        dims = len(so) // 2
+        out = np.zeros(fs.shape[:2] + (dims,), np.int32)
+        ini = _c(init, np.int32) if init is not None else None
+        rc = self._f("patch_match")(mf, dims, _p(fs), _p(ft), fs.shape[0], fs.shape[1], ft.shape[0], ft.shape[1], fs.shape[2], _p(so), n_iter, n_random,
+                                    _p(ini) if ini is not None else None, _p(out))
+        return out if rc == 0 else None
+
+    def on_demand_truncated_cost_volume(self, mf, fs, ft, search, disp, radius=1):
+        fs, ft, disp = _c(fs, np.float32), _c(ft, np.float32), _c(disp, np.int32)
+        so = np.asarray(search, np.int32)
+        dims = len(so) // 2
+        n = 2 * radius + 1
+        out = np.zeros(fs.shape[:2] + (n,) * dims, np.float32)
+        rc = self._f("on_demand_truncated_cost_volume")(mf, dims, _p(fs), _p(ft), fs.shape[0], fs.shape[1], ft.shape[0], ft.shape[1], fs.shape[2],
+                                                        _p(so), _p(disp), radius, _p(out))
+        return out if rc == 0 else None
+
     def refined_barycentric_disp(self, mf, left, right, hr, vr, width, prenormalize=False):
         left, right = _c(left, np.float32), _c(right, np.float32)
         out = np.empty(right.shape, np.float32)

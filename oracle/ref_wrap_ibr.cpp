@@ -13,6 +13,8 @@
 
 #include <correlation/image_based_refinement.h>
 #include <io/image_io.h>
+#include <correlation/patchmatch.h>
+#include <correlation/on_demand_cost_volume.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -59,6 +61,53 @@ template<matchingFunctions F, dispDirection D>
 int costsym(const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* idx, const float* cv, int wi, int d, float* out) {
 	auto r = refineCostSymmetricDisp<F, D>(view3(fl, h, wl, f), view3(fr, h, wr, f), view2(idx, h, wi), view3(cv, h, wi, d));
 	out2(r, out);
+	return 0;
+}
+
+// patchMatch<matchFunc, dims>(source, target, searchOffset, nIter, nRandomSearch, initializer) (patchmatch.h:498-556). init
+// (nullable) is returned by the initializer; without it the reference draws the initial map (and, with nRand > 0, the search
+// candidates) from std::random_device: such runs are not repeatable.
+template<matchingFunctions F, int DIMS>
+int pm_run(const float* fs, const float* ft, int h, int w, int ht, int wt, int f, const int* so, int nIter, int nRand, const int32_t* init, int32_t* out) {
+	auto s = view3(fs, h, w, f), t = view3(ft, ht, wt, f);
+	typedef MD::Array<float, 3> FV;
+	std::optional<typename PatchMatchTraits<F, FV, FV, DIMS>::PatchMatchInitializer> initializer = std::nullopt;
+	if (init) initializer = [init, h, w](FV const&, FV const&) {
+		MD::Array<disp_t, 3> d(h, w, DIMS);
+		for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) for (int k = 0; k < DIMS; k++) d.atUnchecked(i, j, k) = init[(size_t(i) * w + j) * DIMS + k];
+		return d;
+	};
+	MD::Array<disp_t, 3> d;
+	if constexpr (DIMS == 1) d = patchMatch<F, 1>(s, t, searchOffset<1>(so[0], so[1]), nIter, nRand, initializer);
+	else d = patchMatch<F, 2>(s, t, searchOffset<2>(so[0], so[1], so[2], so[3]), nIter, nRand, initializer);
+	if (d.empty()) return 1;
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) for (int k = 0; k < DIMS; k++) out[(size_t(i) * w + j) * DIMS + k] = d.valueUnchecked(i, j, k);
+	return 0;
+}
+
+// OnDemandStereoCostVolume / OnDemandImageFlowVolume ::truncatedCostVolume(disp, radius) (on_demand_cost_volume.h:187-310)
+template<matchingFunctions F>
+int od_run(int dims, const float* fs, const float* ft, int h, int w, int ht, int wt, int f, const int* so, const int32_t* disp, int radius, float* out) {
+	typedef MD::Array<float, 3> FV;
+	auto s = view3(fs, h, w, f), t = view3(ft, ht, wt, f);
+	const int n = 2 * radius + 1;
+	if (dims == 1) {
+		typedef OnDemandStereoCostVolume<F, float, FV, FV> CV;
+		typename CV::SearchSpaceType space(SearchSpaceBase::IgnoredDim(), SearchSpaceBase::SearchDim(so[0], so[1]), SearchSpaceBase::FeatureDim());
+		CV cv(s, t, space);
+		auto r = cv.truncatedCostVolume(view2(disp, h, w), radius);
+		if (r.empty()) return 1;
+		for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) for (int k = 0; k < n; k++) out[(size_t(i) * w + j) * n + k] = r.valueUnchecked(i, j, k);
+	} else {
+		typedef OnDemandImageFlowVolume<F, float, FV, FV> CV;
+		typename CV::SearchSpaceType space(SearchSpaceBase::SearchDim(so[0], so[1]), SearchSpaceBase::SearchDim(so[2], so[3]), SearchSpaceBase::FeatureDim());
+		CV cv(s, t, space);
+		MD::Array<int32_t, 3> d(const_cast<int32_t*>(disp), {h, w, 2}, {w * 2, 2, 1}, false);
+		auto r = cv.truncatedCostVolume(d, radius);
+		if (r.empty()) return 1;
+		for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) for (int a = 0; a < n; a++) for (int b = 0; b < n; b++)
+			out[((size_t(i) * w + j) * n + a) * n + b] = r.valueUnchecked(i, j, a, b);
+	}
 	return 0;
 }
 
@@ -145,6 +194,26 @@ int ref_read_stevimg_f32(const char* path, float* out, int* shape) {
 }
 int ref_stevimg_matches(const char* path, int which) {
 	return which == 0 ? IO::stevImgFileMatchTypeAndDim<float, 3>(path) : (which == 1 ? IO::stevImgFileMatchTypeAndDim<uint8_t, 2>(path) : IO::stevImgFileMatchTypeAndDim<float, 2>(path));
+}
+
+int ref_patch_match(int matchfunc, int dims, const float* fs, const float* ft, int h, int w, int ht, int wt, int f, const int* so, int nIter, int nRand,
+					const int32_t* init, int32_t* out) {
+	switch (matchfunc) {
+	case 5: return dims == 1 ? pm_run<matchingFunctions::ZNCC, 1>(fs, ft, h, w, ht, wt, f, so, nIter, nRand, init, out) : pm_run<matchingFunctions::ZNCC, 2>(fs, ft, h, w, ht, wt, f, so, nIter, nRand, init, out);
+	case 2: return dims == 1 ? pm_run<matchingFunctions::SSD, 1>(fs, ft, h, w, ht, wt, f, so, nIter, nRand, init, out) : pm_run<matchingFunctions::SSD, 2>(fs, ft, h, w, ht, wt, f, so, nIter, nRand, init, out);
+	case 7: return dims == 1 ? pm_run<matchingFunctions::ZSAD, 1>(fs, ft, h, w, ht, wt, f, so, nIter, nRand, init, out) : pm_run<matchingFunctions::ZSAD, 2>(fs, ft, h, w, ht, wt, f, so, nIter, nRand, init, out);
+	default: return 3;
+	}
+}
+
+int ref_on_demand_truncated_cost_volume(int matchfunc, int dims, const float* fs, const float* ft, int h, int w, int ht, int wt, int f, const int* so,
+										const int32_t* disp, int radius, float* out) {
+	switch (matchfunc) {
+	case 5: return od_run<matchingFunctions::ZNCC>(dims, fs, ft, h, w, ht, wt, f, so, disp, radius, out);
+	case 2: return od_run<matchingFunctions::SSD>(dims, fs, ft, h, w, ht, wt, f, so, disp, radius, out);
+	case 7: return od_run<matchingFunctions::ZSAD>(dims, fs, ft, h, w, ht, wt, f, so, disp, radius, out);
+	default: return 3;
+	}
 }
 
 // refinedBarycentricDisp on images (image_based_refinement.h:2502-2544): unfold, features, cost volume, winner, refinement

@@ -27,5 +27,7 @@ public:
 private:
 	int _s[N]; bool _on[N];
 };
+template<size_t N> IndexConverter(std::array<int, N> const&) -> IndexConverter<int(N)>;
+template<size_t N> IndexConverter(std::array<int, N> const&, DimsExclusionSet<int(N)> const&) -> IndexConverter<int(N)>;
 }
 #endif

@@ -1197,3 +1197,107 @@ int orc_refine_cost_symmetric_disp(int mf, const float* fl, const float* fr, int
 	}
 	return 0;
 }
+
+/* ==== correlation/on_demand_cost_volume.h + correlation/patchmatch.h ===============================================================
+ * fs (h,w,F), ft (ht,wt,F): feature volumes as the on-demand volume's constructor leaves them (already processed for the function).
+ * search: {lo, up} (dims 1, columns) or {lo0, up0, lo1, up1} (dims 2: rows, columns). */
+typedef struct { const float* fs; const float* ft; int h, w, ht, wt, F, dims, lo0, up0, lo1, up1, mf; } od_volume;
+
+/* costValue, on_demand_cost_volume.h:105-181: 0 when the cell has no value */
+static int od_cost(const od_volume* v, int i, int j, int d0, int d1, float* c) {
+	if (v->dims == 2 && (d0 < v->lo0 || d0 > v->up0)) return 0;
+	if (d1 < v->lo1 || d1 > v->up1) return 0;
+	int ti = i + (v->dims == 2 ? d0 : 0), tj = j + d1;
+	if (ti < 0 || ti >= v->ht || tj < 0 || tj >= v->wt) return 0;
+	*c = compare_f32(v->mf, v->fs + ((size_t)i * v->w + j) * v->F, v->ft + ((size_t)ti * v->wt + tj) * v->F, v->F);
+	return 1;
+}
+
+static void od_setup(od_volume* v, int mf, int dims, const float* fs, const float* ft, int h, int w, int ht, int wt, int F, const int* so) {
+	v->fs = fs; v->ft = ft; v->h = h; v->w = w; v->ht = ht; v->wt = wt; v->F = F; v->dims = dims; v->mf = mf;
+	v->lo0 = v->up0 = 0;
+	if (dims == 1) { v->lo1 = so[0]; v->up1 = so[1]; } else { v->lo0 = so[0]; v->up0 = so[1]; v->lo1 = so[2]; v->up1 = so[3]; }
+}
+
+static float* od_processed(int mf, const float* f, size_t npix, int F, int passes) {
+	float* p = (float*)malloc(sizeof(float) * npix * F);
+	memcpy(p, f, sizeof(float) * npix * F);
+	if (mf_zero_mean(mf) || mf_normalized(mf)) for (int k = 0; k < passes; k++) features_inplace(mf, p, npix, F);
+	return p;
+}
+
+/* truncatedCostVolume(disp, radius), :187-310, incl. the index handed to costValue as a disparity (:224-241) */
+int orc_on_demand_truncated_cost_volume(int mf, int dims, const float* fs, const float* ft, int h, int w, int ht, int wt, int F, const int* so,
+										const int32_t* disp, int radius, float* out) {
+	float* ps = od_processed(mf, fs, (size_t)h * w, F, 1);
+	float* pt = od_processed(mf, ft, (size_t)ht * wt, F, 1);
+	od_volume v;
+	od_setup(&v, mf, dims, ps, pt, h, w, ht, wt, F, so);
+	const int n = 2 * radius + 1;
+	const float missing = mf_strategy(mf) == STRAT_COST ? 3.402823466e+38f : 1.17549435e-38f; /* matching_costs.h:706-713 */
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		if (dims == 1) {
+			int d = disp[(size_t)i * w + j];
+			for (int k = 0; k < n; k++) { float c; out[((size_t)i * w + j) * n + k] = od_cost(&v, i, j, 0, (d - v.lo1) + k - radius, &c) ? c : missing; }
+		} else {
+			int d0 = disp[((size_t)i * w + j) * 2], d1 = disp[((size_t)i * w + j) * 2 + 1];
+			for (int a = 0; a < n; a++) for (int b = 0; b < n; b++) {
+				float c;
+				out[(((size_t)i * w + j) * n + a) * n + b] = od_cost(&v, i, j, (d0 - v.lo0) + a - radius, (d1 - v.lo1) + b - radius, &c) ? c : missing;
+			}
+		}
+	}
+	free(ps); free(pt);
+	return 0;
+}
+
+/* patchMatchTestCost, patchmatch.h:166-231; cur / ok: the cost of the pixel's disparity (an empty optional compares below any value) */
+static int pm_test(const od_volume* v, int32_t* sol, float* cur, unsigned char* ok, int i, int j, int d0, int d1) {
+	float c;
+	if (!od_cost(v, i, j, d0, d1, &c)) return 0;
+	size_t px = (size_t)i * v->w + j;
+	int score = mf_strategy(v->mf) == STRAT_SCORE;
+	int keep = score ? (!ok[px] || c >= cur[px]) : (ok[px] && c <= cur[px]);
+	if (!keep) return 0;
+	if (v->dims == 2) { sol[px * 2] = d0; sol[px * 2 + 1] = d1; } else sol[px] = d1;
+	cur[px] = c; ok[px] = 1;
+	return 1;
+}
+
+/* patchMatch with nRandomSearch = 0 from a given initial map (patchmatch.h:371-446 propagate, :449-496 the loop, :498-556 the entry that
+ * processes the features once more before the on-demand volume does): the deterministic part of the algorithm */
+int orc_patch_match(int mf, int dims, const float* fs, const float* ft, int h, int w, int ht, int wt, int F, const int* so, int n_iter, int n_rand,
+					const int32_t* init, int32_t* out) {
+	if (n_rand != 0 || !init) return 3; /* the random draws are not restated: the reference seeds them from std::random_device */
+	float* ps = od_processed(mf, fs, (size_t)h * w, F, 2);
+	float* pt = od_processed(mf, ft, (size_t)ht * wt, F, 2);
+	od_volume v;
+	od_setup(&v, mf, dims, ps, pt, h, w, ht, wt, F, so);
+	memcpy(out, init, sizeof(int32_t) * (size_t)h * w * dims);
+	float* cur = (float*)malloc(sizeof(float) * (size_t)h * w);
+	unsigned char* ok = (unsigned char*)malloc((size_t)h * w);
+	for (int i = 0; i < h; i++) for (int j = 0; j < w; j++) {
+		size_t px = (size_t)i * w + j;
+		ok[px] = (unsigned char)od_cost(&v, i, j, dims == 2 ? out[px * 2] : 0, dims == 2 ? out[px * 2 + 1] : out[px], &cur[px]);
+	}
+	static const int inc[4][2] = {{1, 1}, {1, -1}, {-1, 1}, {-1, -1}}; /* utils/propagation_direction.h:65-86 */
+	for (int it = 0; it < n_iter; it++) {
+		int n = 0, di = inc[it % 4][0], dj = inc[it % 4][1];
+		/* a backward scan ends before index 0 (initialAndFinalPos<-1> = {size-1, 0}, :45-60) */
+		for (int i = 0; i < h; i++) for (int j = dj > 0 ? 0 : w - 1; dj > 0 ? j < w : j > 0; j += dj) {
+			int pj = j - dj;
+			if (pj < 0 || pj >= w) continue;
+			size_t pp = (size_t)i * w + pj;
+			n += pm_test(&v, out, cur, ok, i, j, dims == 2 ? out[pp * 2] : 0, dims == 2 ? out[pp * 2 + 1] : out[pp]);
+		}
+		for (int j = 0; j < w; j++) for (int i = di > 0 ? 0 : h - 1; di > 0 ? i < h : i > 0; i += di) {
+			int pi = i - di;
+			if (pi < 0 || pi >= h) continue;
+			size_t pp = (size_t)pi * w + j;
+			n += pm_test(&v, out, cur, ok, i, j, dims == 2 ? out[pp * 2] : 0, dims == 2 ? out[pp * 2 + 1] : out[pp]);
+		}
+		if (n == 0) break;
+	}
+	free(cur); free(ok); free(ps); free(pt);
+	return 0;
+}

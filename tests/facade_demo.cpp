@@ -9,6 +9,7 @@
 #include <StereoVision/correlation/hierarchical.h>
 #include <StereoVision/correlation/image_based_refinement.h>
 #include <StereoVision/correlation/guided_cost_filtering.h>
+#include <StereoVision/correlation/patchmatch.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -112,6 +113,14 @@ int main() {
 	auto aggregated = variableCostVolumeAggregation(f2c, windows);
 	std::printf("aggregation_windows %.4f\naggregated %.3f\naggregated_empty %d\n", checksum(windows), checksum(aggregated),
 				int(variableCostVolumeAggregation(f2c, Multidim::Array<float, 4>(h, w, 2, 3)).empty()));
+	// PatchMatch over on-demand costs (patchmatch.h), what examples/stereo-match runs: source = right features, target = left
+	auto pm = patchMatch<matchingFunctions::ZNCC, 1>(fvr, fvl, searchOffset<1>(0, D - 1), 5, 4);
+	int pm_good = 0;
+	for (int i = 4; i < h - 4; i++) for (int j = 4; j < w - 24; j++) pm_good += pm.valueUnchecked(i, j, 0) == 5;
+	OnDemandStereoCostVolume<matchingFunctions::ZNCC> odcv(fvr, fvl, searchOffset<1>(0, D - 1));
+	auto odt = odcv.truncatedCostVolume(pm, 1);
+	std::printf("patchmatch_match %.3f\non_demand_tcv %.3f\npatchmatch_empty %d\n", double(pm_good) / ((h - 8) * (w - 28)), checksum(odt),
+				int(patchMatch<matchingFunctions::ZNCC, 1>(fvr, Multidim::Array<float, 3>(h + 1, w, 25), searchOffset<1>(0, D - 1)).empty()));
 	auto bad = unfoldBasedCostVolume<matchingFunctions::ZNCC>(lf, Multidim::Array<float, 2>(h + 1, w), 2, 2, D);
 	std::printf("mismatch_empty %d\n", int(bad.empty()));
 	auto even = refineDispCostInterpolation<InterpolationKernel::Parabola>(Multidim::Array<float, 3>(h, w, 4), zi);

@@ -38,7 +38,8 @@ def test_facade_headers_carry_the_reference_names():
                  "getFeatureVolumeForMatchFunc", "buildFeaturePyramid", "FeatureVolumePyramid", "meanFilter2D", "sigmaFilter",
                  "refineBarycentricDisp", "refineBarycentricSymmetricDisp", "refineBarycentric2dDisp", "refineBarycentricSymmetric2dDisp",
                  "refineCostSymmetricDisp", "refinedBarycentricDisp", "refinedBarycentricDispFeatureVol", "refinedCostSymmetricDisp",
-                 "bidimensionalContiguity", "computeAggregationWindows", "variableCostVolumeAggregation", "readStevimg", "writeStevimg"):
+                 "bidimensionalContiguity", "computeAggregationWindows", "variableCostVolumeAggregation", "readStevimg", "writeStevimg",
+                 "patchMatch", "cachelessPatchMatch", "OnDemandStereoCostVolume", "OnDemandImageFlowVolume", "truncatedCostVolume"):
         assert name in text, name
 
 
@@ -137,6 +138,13 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
         cands = {_checksum(a), _checksum(np.transpose(a))}
         assert any(abs(float(got[name]) - c) <= tol * max(1.0, abs(c)) for c in cands), (name, got[name], cands)
     assert int(got["aggregated_empty"]) == 1
+    # PatchMatch through the facade (seed 0) = the Python mirror's with the same seed; the on-demand cells around its result
+    pm = api.patchMatch(api.ZNCC, fvr, fvl, (0, D - 1), 5, 4, seed=0, ctx=ctx)
+    assert abs(float(got["patchmatch_match"]) - float((pm[4:h - 4, 4:w - 24, 0] == 5).mean())) < 1e-3 and float(got["patchmatch_match"]) > 0.95
+    odt = np.asarray(api.onDemandTruncatedCostVolume(api.ZNCC, fvr, fvl, (0, D - 1), pm, 1, ctx=ctx))
+    cands = {_checksum(odt), _checksum(np.transpose(odt))}
+    assert any(abs(float(got["on_demand_tcv"]) - c) <= 1e-4 * max(1.0, abs(c)) for c in cands), (got["on_demand_tcv"], cands)
+    assert int(got["patchmatch_empty"]) == 1
     assert abs(float(got["zncc_match"]) - float((zi[4:h - 4, 4:w - 24] == 5).mean())) < 1e-3
     assert float(got["zncc_match"]) > 0.95
     order = os.environ.get("STEVI_FACADE_ORDER", "")

@@ -626,3 +626,45 @@ def test_port_refinements_equal_the_compiled_reference(mf):
         for sym in (0, 1):
             _mostly_equal(O.port.refine_barycentric_2d(mf, cont, sym, fl, fr2, idx2, search),
                           O.ref_ibr.refine_barycentric_2d(mf, cont, sym, fl, fr2, idx2, search), tol=1e-4, frac=0.99)
+
+
+# ---- on-demand cost volumes and PatchMatch (on_demand_cost_volume.h, patchmatch.h) -----------------------------------------------
+
+needs_ref_pm = pytest.mark.skipif(O.ref_ibr is None or not O.ref_ibr.has("patch_match"), reason="oracle/_ref/libstevi_ref_ibr.so was not built")
+
+
+@needs_ref_pm
+@pytest.mark.parametrize("mf", [O.ZNCC, O.SSD, O.ZSAD])
+def test_port_on_demand_and_patch_match_equal_the_compiled_reference(mf):
+    """The C restatement against the reference's own classes: the on-demand truncated volume (incl. cells without a value, a
+    search range that does not start at 0) and the deterministic part of PatchMatch (no random search, given initial map; 1-D and
+    2-D searches, all four scan directions) bit for bit."""
+    L, R, _ = synth.stereo_pair(40, 96, 3, d_bg=3, d_sq=8, d_max=0, dtype=np.float32)
+    fs, ft = port.unfold(R, 2, 1), port.unfold(L, 2, 1)
+    rng = np.random.default_rng(int(mf))
+    for search in ((0, 11), (-2, 9), (3, 12)):
+        d = rng.integers(search[0] - 1, search[1] + 2, fs.shape[:2]).astype(np.int32)
+        for radius in (1, 2):
+            assert same(port.on_demand_truncated_cost_volume(mf, fs, ft, search, d, radius), O.ref_ibr.on_demand_truncated_cost_volume(mf, fs, ft, search, d, radius))
+    init = rng.integers(-1, 14, fs.shape[:2] + (1,)).astype(np.int32)
+    for n_iter in (1, 2, 3, 4, 6):
+        assert same(port.patch_match(mf, fs, ft, (0, 11), n_iter, 0, init), O.ref_ibr.patch_match(mf, fs, ft, (0, 11), n_iter, 0, init))
+    ft2 = port.unfold(np.roll(L, 1, axis=0), 2, 1)
+    init2 = np.stack([rng.integers(-2, 3, fs.shape[:2]), rng.integers(0, 10, fs.shape[:2])], axis=2).astype(np.int32)
+    d2 = np.stack([rng.integers(-3, 4, fs.shape[:2]), rng.integers(-1, 11, fs.shape[:2])], axis=2).astype(np.int32)
+    search2 = (-2, 2, 0, 9)
+    assert same(port.on_demand_truncated_cost_volume(mf, fs, ft2, search2, d2, 1), O.ref_ibr.on_demand_truncated_cost_volume(mf, fs, ft2, search2, d2, 1))
+    assert same(port.patch_match(mf, fs, ft2, search2, 5, 0, init2), O.ref_ibr.patch_match(mf, fs, ft2, search2, 5, 0, init2))
+
+
+def test_on_demand_cells_equal_the_full_cost_volume():
+    """testOnDemandCostVolume.cpp:62-112: every cell the on-demand volume gives equals the cell of the full cost volume."""
+    L, R, _ = synth.stereo_pair(24, 64, 5, d_bg=2, d_sq=6, d_max=0, dtype=np.float32)
+    fs, ft = port.unfold(R, 1, 1), port.unfold(L, 1, 1)
+    for mf in (O.ZNCC, O.SSD, O.SAD):
+        full = port.feature_volume_to_cost_volume(mf, ft, fs, 10, O.R2L)
+        for d in range(10):
+            disp = np.full(fs.shape[:2], d, np.int32)
+            cells = port.on_demand_truncated_cost_volume(mf, fs, ft, (0, 9), disp, 0)[..., 0]
+            ok = np.arange(64)[None, :] + d < 64
+            assert np.array_equal(cells[np.broadcast_to(ok, cells.shape)], full[..., d][np.broadcast_to(ok, cells.shape)])
