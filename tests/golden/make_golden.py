@@ -121,8 +121,48 @@ def main_filters():
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+def main_refinement():
+    """Feature-domain refinement (image_based_refinement.h), on-demand truncated volumes and the deterministic part of PatchMatch
+    (on_demand_cost_volume.h, patchmatch.h) from oracle/_ref/libstevi_ref_ibr.so: the reference's unmodified code; the Eigen calls
+    inside the refinements run on the stand-in solver of oracle/small_qr.h (see oracle/shims/Eigen)."""
+    ref = O.ref_ibr
+    assert ref is not None, "build oracle/_ref first (make -C oracle ref)"
+    H, W = 22, 56
+    rng = np.random.default_rng(401)
+    base = rng.uniform(-1, 1, (H, W + 16)).astype(np.float32)
+    k = np.array([1, 2, 1], np.float32) / 4
+    base = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 1, base).astype(np.float32)
+    left, right = base[:, 4:4 + W].copy(), (0.6 * base[:, 8:8 + W] + 0.4 * base[:, 9:9 + W]).astype(np.float32)
+    out = {"H": H, "W": W, "left": left, "right": right}
+    fl_raw, fr_raw = O.port.unfold(left, 2, 1), O.port.unfold(right, 2, 1)
+    for name in ("NCC", "ZNCC", "SSD", "ZSSD", "SAD", "ZSAD"):
+        mf = getattr(O, name)
+        fl, fr = O.port.features_for_matchfunc(mf, fl_raw), O.port.features_for_matchfunc(mf, fr_raw)
+        cv = O.port.aggregate_cost(mf, fl, fr, 0, 9, O.R2L)
+        idx = O.port.wta(cv, O.strategy_of(mf))
+        out[f"idx_{name}"] = idx
+        out[f"bary_{name}"] = ref.refine_barycentric(mf, fl, fr, idx)
+        out[f"costsym_{name}"] = ref.refine_cost_symmetric(mf, fl, fr, idx, cv)
+        if name not in ("SAD", "ZSAD"):
+            out[f"barysym1_{name}"] = ref.refine_barycentric_symmetric(mf, 1, fl, fr, idx, 10)
+            out[f"barysym2_{name}"] = ref.refine_barycentric_symmetric(mf, 2, fl, fr, idx, 10)
+    init = rng.integers(-1, 12, (H, W, 1)).astype(np.int32)
+    disp = rng.integers(-3, 12, (H, W)).astype(np.int32)
+    out["pm_init"], out["od_disp"] = init, disp
+    for name in ("ZNCC", "SSD", "ZSAD"):
+        mf = getattr(O, name)
+        for n_iter in (1, 2, 4):
+            out[f"pm_{name}_{n_iter}"] = ref.patch_match(mf, fr_raw, fl_raw, (0, 9), n_iter, 0, init)
+        out[f"od_{name}"] = ref.on_demand_truncated_cost_volume(mf, fr_raw, fl_raw, (-2, 9), disp, 1)
+    path = os.path.join(HERE, "reference_outputs_refinement.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
-    if "2d" in sys.argv[1:]:
+    if "refinement" in sys.argv[1:]:
+        main_refinement()
+    elif "2d" in sys.argv[1:]:
         main_2d()
     elif "filters" in sys.argv[1:]:
         main_filters()
@@ -130,3 +170,4 @@ if __name__ == "__main__":
         main()
         main_2d()
         main_filters()
+        main_refinement()

@@ -668,3 +668,29 @@ def test_on_demand_cells_equal_the_full_cost_volume():
             cells = port.on_demand_truncated_cost_volume(mf, fs, ft, (0, 9), disp, 0)[..., 0]
             ok = np.arange(64)[None, :] + d < 64
             assert np.array_equal(cells[np.broadcast_to(ok, cells.shape)], full[..., d][np.broadcast_to(ok, cells.shape)])
+
+
+def test_golden_refinement_patch_match_on_demand():
+    """The C restatement against outputs of the reference's own code stored in tests/golden/reference_outputs_refinement.npz
+    (generator: tests/golden/make_golden.py refinement): runs where neither /root/reference nor oracle/_ref exist."""
+    G3 = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_outputs_refinement.npz"))
+    left, right = G3["left"], G3["right"]
+    fl_raw, fr_raw = port.unfold(left, 2, 1), port.unfold(right, 2, 1)
+    inner = (slice(1, -1), slice(4, -14))
+    for name in ("NCC", "ZNCC", "SSD", "ZSSD", "SAD", "ZSAD"):
+        mf = getattr(O, name)
+        fl, fr = port.features_for_matchfunc(mf, fl_raw), port.features_for_matchfunc(mf, fr_raw)
+        cv = port.aggregate_cost(mf, fl, fr, 0, 9, O.R2L)
+        idx = port.wta(cv, O.strategy_of(mf))
+        assert np.array_equal(idx, G3[f"idx_{name}"])
+        b = port.refine_barycentric(mf, fl, fr, idx)
+        _mostly_equal(b[inner], G3[f"bary_{name}"][inner]) if name in ("SAD", "ZSAD") else _mostly_equal(b, G3[f"bary_{name}"])
+        _mostly_equal(port.refine_cost_symmetric(mf, fl, fr, idx, cv), G3[f"costsym_{name}"])
+        if name not in ("SAD", "ZSAD"):
+            for r in (1, 2):
+                _mostly_equal(port.refine_barycentric_symmetric(mf, r, fl, fr, idx, 10), G3[f"barysym{r}_{name}"])
+    for name in ("ZNCC", "SSD", "ZSAD"):
+        mf = getattr(O, name)
+        for n_iter in (1, 2, 4):
+            assert same(port.patch_match(mf, fr_raw, fl_raw, (0, 9), n_iter, 0, G3["pm_init"]), G3[f"pm_{name}_{n_iter}"])
+        assert same(port.on_demand_truncated_cost_volume(mf, fr_raw, fl_raw, (-2, 9), G3["od_disp"], 1), G3[f"od_{name}"])
