@@ -24,8 +24,8 @@ namespace {
 enum { BOX_PROD = 0, BOX_SQ = 1, BOX_ABS = 2 };   // the comparison: products, squared differences, absolute differences
 
 struct Pm {
-	const float* fs; const float* ft;   // processed feature volumes, dense [H][W][F]
-	int Hs, Ws, Ht, Wt, F;
+	const float* fs; const float* ft;   // processed feature volumes, dense [H][W][Fp]: vectors padded with zeros to a multiple of 4
+	int Hs, Ws, Ht, Wt, F, Fp;          // (16-byte loads; a zero pair adds an exact zero to every sum)
 	int dims;                           // search dimensions: 1 (columns) or 2 (rows, columns)
 	int lo0, up0, lo1, up1;             // dims == 1: lo1 / up1 only
 	int32_t* disp; int64_t d0s, d1s, d2s;
@@ -40,12 +40,29 @@ __device__ __forceinline__ bool pm_cost(const Pm& p, int i, int j, int d0, int d
 	if (d1 < p.lo1 || d1 > p.up1) return false;
 	const int ti = i + (p.dims == 2 ? d0 : 0), tj = j + d1;
 	if (ti < 0 || ti >= p.Ht || tj < 0 || tj >= p.Wt) return false;
-	const float* s = p.fs + ((int64_t)i * p.Ws + j) * p.F;
-	const float* t = p.ft + ((int64_t)ti * p.Wt + tj) * p.F;
+	const float4* s = reinterpret_cast<const float4*>(p.fs + ((int64_t)i * p.Ws + j) * p.Fp);
+	const float4* t = reinterpret_cast<const float4*>(p.ft + ((int64_t)ti * p.Wt + tj) * p.Fp);
 	float acc = 0.f;
-	if (p.op == BOX_PROD) for (int k = 0; k < p.F; k++) acc = __fadd_rn(acc, __fmul_rn(s[k], t[k]));
-	else if (p.op == BOX_SQ) for (int k = 0; k < p.F; k++) { const float e = __fsub_rn(s[k], t[k]); acc = __fadd_rn(acc, __fmul_rn(e, e)); }
-	else for (int k = 0; k < p.F; k++) acc = __fadd_rn(acc, fabsf(__fsub_rn(s[k], t[k])));
+	// the reference's sequential sum over the channels (matching_costs.h:59-156). The loads of a chunk of 32 channels of both
+	// vectors are issued together before any of them is used: a vector spans one or two 128-byte lines, and taken one load at a
+	// time in a rolled loop each line's miss would be waited for in turn
+	const int n4 = p.Fp / 4;
+	for (int k0 = 0; k0 < n4; k0 += 8) {
+		float4 a[8], b[8];
+#pragma unroll
+		for (int k = 0; k < 8; k++) if (k0 + k < n4) { a[k] = __ldg(s + k0 + k); b[k] = __ldg(t + k0 + k); }
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			if (k0 + k >= n4) break;
+			const float sa[4] = {a[k].x, a[k].y, a[k].z, a[k].w}, tb[4] = {b[k].x, b[k].y, b[k].z, b[k].w};
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				if (p.op == BOX_PROD) acc = __fadd_rn(acc, __fmul_rn(sa[q], tb[q]));
+				else if (p.op == BOX_SQ) { const float e = __fsub_rn(sa[q], tb[q]); acc = __fadd_rn(acc, __fmul_rn(e, e)); }
+				else acc = __fadd_rn(acc, fabsf(__fsub_rn(sa[q], tb[q])));
+			}
+		}
+	}
 	c = acc;
 	return true;
 }
@@ -104,6 +121,50 @@ __global__ void __launch_bounds__(128) k_pm_init(const Pm p, unsigned long long 
 	else d[0] = pm_uniform(seed ^ pm_mix(px), p.lo1, p.up1);
 }
 
+// pulls the feature vector that starts at q towards the SM (one request per 128-byte line)
+__device__ __forceinline__ void pm_prefetch(const float* q, int F) {
+	for (int k = 0; k < F; k += 32) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + k));
+	asm volatile("prefetch.global.L1 [%0];" ::"l"(q + F - 1));
+}
+
+// what a scan knows about a pixel before it reaches it: its disparity, the cost of that disparity and whether that cost exists
+struct PmPixel { int d0, d1; float cur; bool ok; };
+__device__ __forceinline__ PmPixel pm_load_pixel(const Pm& p, int i, int j) {
+	PmPixel x;
+	pm_read(p, i, j, x.d0, x.d1);
+	const int64_t px = (int64_t)i * p.Ws + j;
+	x.cur = p.cur[px]; x.ok = p.cur_ok[px] != 0;
+	return x;
+}
+
+// One step of a scan: pixel (i, j), whose state `me` was loaded a step ago, tests the disparity (d0, d1) its predecessor ended
+// with. The step is a dependent chain — the candidate's target vector can only be fetched once the predecessor is settled — so
+// everything that does not depend on it is asked for a step ahead: the next pixel's own state (`next`, loaded here, used by the
+// next step: a warp issues in order, a load consumed in the same step would expose its whole latency), the next pixel's source
+// vector, and the target vector the next pixel will need if this one keeps the disparity it has (after the first sweeps the
+// common case).
+__device__ __forceinline__ int pm_scan_step(const Pm& p, int i, int j, int ni, int nj, const PmPixel& me, PmPixel& next, int& d0, int& d1) {
+	const bool has_next = ni >= 0 && ni < p.Hs && nj >= 0 && nj < p.Ws;
+	if (has_next) {
+		next = pm_load_pixel(p, ni, nj);
+		pm_prefetch(p.fs + ((int64_t)ni * p.Ws + nj) * p.Fp, p.Fp);
+		const int ti = ni + (p.dims == 2 ? me.d0 : 0), tj = nj + me.d1;
+		if (ti >= 0 && ti < p.Ht && tj >= 0 && tj < p.Wt) pm_prefetch(p.ft + ((int64_t)ti * p.Wt + tj) * p.Fp, p.Fp);
+	}
+	float c;
+	bool keep = false;
+	if (pm_cost(p, i, j, d0, d1, c)) keep = p.score ? (!me.ok || c >= me.cur) : (me.ok && c <= me.cur);   // patchmatch.h:211-219
+	if (keep) {
+		int32_t* d = p.disp + i * p.d0s + j * p.d1s;
+		if (p.dims == 2) { d[0] = d0; d[p.d2s] = d1; } else d[0] = d1;
+		const int64_t px = (int64_t)i * p.Ws + j;
+		p.cur[px] = c; p.cur_ok[px] = 1;
+		return 1;
+	}
+	d0 = me.d0; d1 = me.d1;   // the pixel keeps its own disparity: that is what its successor will test
+	return 0;
+}
+
 // line scans of patchMatchPropagate, :391-415: a thread per row, along the columns in the direction inc
 __global__ void __launch_bounds__(64) k_pm_scan_rows(const Pm p, int inc) {
 	if (*p.stop) return;
@@ -112,12 +173,14 @@ __global__ void __launch_bounds__(64) k_pm_scan_rows(const Pm p, int inc) {
 	int n = 0;
 	// backward scans end BEFORE index 0: initialAndFinalPos<-1> gives {size - 1, 0} and the loop runs while j != final
 	// (utils/propagation_direction.h:45-60)
-	for (int j = inc > 0 ? 0 : p.Ws - 1; inc > 0 ? j < p.Ws : j > 0; j += inc) {
-		const int pj = j - inc;
-		if (pj < 0 || pj >= p.Ws) continue;
-		int d0, d1;
-		pm_read(p, i, pj, d0, d1);
-		n += pm_test(p, i, j, d0, d1);
+	const int first = inc > 0 ? 0 : p.Ws - 1;
+	int d0, d1;
+	pm_read(p, i, first, d0, d1);   // the first pixel of the line has no predecessor and is only a source
+	PmPixel me = {0, 0, 0.f, false}, next = me;
+	if (first + inc >= 0 && first + inc < p.Ws) me = pm_load_pixel(p, i, first + inc);
+	for (int j = first + inc; inc > 0 ? j < p.Ws : j > 0; j += inc) {
+		n += pm_scan_step(p, i, j, i, j + inc, me, next, d0, d1);
+		me = next;
 	}
 	if (n) atomicAdd(p.changes, n);
 }
@@ -128,12 +191,14 @@ __global__ void __launch_bounds__(64) k_pm_scan_cols(const Pm p, int inc) {
 	const int j = blockIdx.x * 64 + threadIdx.x;
 	if (j >= p.Ws) return;
 	int n = 0;
-	for (int i = inc > 0 ? 0 : p.Hs - 1; inc > 0 ? i < p.Hs : i > 0; i += inc) {
-		const int pi = i - inc;
-		if (pi < 0 || pi >= p.Hs) continue;
-		int d0, d1;
-		pm_read(p, pi, j, d0, d1);
-		n += pm_test(p, i, j, d0, d1);
+	const int first = inc > 0 ? 0 : p.Hs - 1;
+	int d0, d1;
+	pm_read(p, first, j, d0, d1);
+	PmPixel me = {0, 0, 0.f, false}, next = me;
+	if (first + inc >= 0 && first + inc < p.Hs) me = pm_load_pixel(p, first + inc, j);
+	for (int i = first + inc; inc > 0 ? i < p.Hs : i > 0; i += inc) {
+		n += pm_scan_step(p, i, j, i + inc, j, me, next, d0, d1);
+		me = next;
 	}
 	if (n) atomicAdd(p.changes, n);
 }
@@ -223,7 +288,7 @@ int32_t prepare(stevi_ctx* c, const char* who, int mf, const View& fs, const Vie
 	if (fs.shape[2] != ft.shape[2] || (dims == 1 && fs.shape[0] != ft.shape[0])) return fail(c, STEVI_E_SHAPE, "%s: the feature volumes do not match", who);
 	if (fs.shape[0] > 65535) return fail(c, STEVI_E_UNSUPPORTED, "%s: more than 65535 rows", who);
 	p = Pm{};
-	p.Hs = fs.shape[0]; p.Ws = fs.shape[1]; p.Ht = ft.shape[0]; p.Wt = ft.shape[1]; p.F = fs.shape[2];
+	p.Hs = fs.shape[0]; p.Ws = fs.shape[1]; p.Ht = ft.shape[0]; p.Wt = ft.shape[1]; p.F = fs.shape[2]; p.Fp = (p.F + 3) / 4 * 4;
 	p.dims = dims;
 	if (dims == 1) { p.lo1 = search[0]; p.up1 = search[1]; }
 	else { p.lo0 = search[0]; p.up0 = search[1]; p.lo1 = search[2]; p.up1 = search[3]; }
@@ -238,8 +303,10 @@ int32_t prepare(stevi_ctx* c, const char* who, int mf, const View& fs, const Vie
 		for (int pass = 0; pass < std::max(n, 1); pass++) {
 			View dst = cur;
 			float* buf = nullptr;
-			STEVI_TRY(arena_alloc_t(c, cur.count(), &buf));
-			dst.p = buf; dst.st[0] = (int64_t)cur.shape[1] * cur.shape[2]; dst.st[1] = cur.shape[2]; dst.st[2] = 1;
+			const size_t padded = (size_t)cur.shape[0] * cur.shape[1] * p.Fp;
+			STEVI_TRY(arena_alloc_t(c, padded, &buf));
+			if (p.Fp != p.F) STEVI_CUDA(c, cudaMemsetAsync(buf, 0, padded * sizeof(float), c->stream));
+			dst.p = buf; dst.st[0] = (int64_t)cur.shape[1] * p.Fp; dst.st[1] = p.Fp; dst.st[2] = 1;
 			// CC / SSD / SAD: features_for_matchfunc is the identity, used here as the copy into a dense volume
 			STEVI_TRY(features_for_matchfunc_dev(c, n ? mf : STEVI_MF_CC, cur, dst));
 			cur = dst;

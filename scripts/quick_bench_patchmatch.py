@@ -31,9 +31,30 @@ for name, search, n_iter in (("1-D search of 128", (0, 127), 5), ("2-D search of
     inner = (slice(8, -8), slice(8, W - 136))
     print(json.dumps({"stage": "patchMatch ZNCC 5x5 " + name, "H": H, "W": W, "nIter": n_iter, "nRandomSearch": 4, "ms": round(ms, 2),
                       "equal_to_ground_truth": round(float((d[inner] == gt[inner]).mean()), 4)}))
+ctx.set_timing(True)
+api.patchMatch(api.ZNCC, fr, fl, (0, 127), 5, 4, seed=1, ctx=ctx)
+per = {}
+for name, ms in ctx.timing_report():
+    per.setdefault(name.split("<")[0].strip("()"), []).append(ms)
+ctx.set_timing(False)
+print(json.dumps({"stage": "patchMatch 1-D kernels (ms, summed over the 5 iterations)", **{k: round(sum(v), 3) for k, v in per.items()}}))
 ms_cv = timed(lambda: api.unfoldBasedCostVolume(api.ZNCC, dl, dr, 2, 2, 128, ctx=ctx))
 cv = api.unfoldBasedCostVolume(api.ZNCC, dl, dr, 2, 2, 128, ctx=ctx)
 ms_wta = timed(lambda: api.extractSelectedIndex(cv, api.SCORE, ctx=ctx))
 idx = api.extractSelectedIndex(cv, api.SCORE, ctx=ctx).cpu().numpy()
 print(json.dumps({"stage": "exhaustive: unfoldBasedCostVolume ZNCC 5x5 D=128 + extractSelectedIndex", "ms": round(ms_cv + ms_wta, 3),
                   "equal_to_ground_truth": round(float((idx[8:-8, 8:W - 136] == gt[8:-8, 8:W - 136]).mean()), 4)}))
+
+# the reference's own patchMatch on the host cores of this box (test infrastructure used as the timed CPU baseline, like bench.py's)
+try:
+    import time
+    import oracle as O
+    if O.ref_ibr is not None and O.ref_ibr.has("patch_match"):
+        fs, ft = O.port.unfold(R, 2, 2), O.port.unfold(L, 2, 2)
+        t0 = time.time()
+        out = O.ref_ibr.patch_match(O.ZNCC, fs, ft, (0, 127), 5, 4)
+        dt = time.time() - t0
+        print(json.dumps({"stage": "reference CPU patchMatch ZNCC 5x5 1-D search of 128 (oracle/_ref, all host cores)", "ms": round(dt * 1e3, 1),
+                          "cores": os.cpu_count(), "equal_to_ground_truth": round(float((out[8:-8, 8:W - 136, 0] == gt[8:-8, 8:W - 136]).mean()), 4)}))
+except Exception as e:  # the checker is optional here
+    print(json.dumps({"stage": "reference CPU patchMatch", "skipped": str(e)}))
