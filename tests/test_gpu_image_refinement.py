@@ -204,3 +204,34 @@ def test_unsupported_functions_are_refused(api, ctx):
             api.refineBarycentricDisp(getattr(api, name), f, f, idx, ctx=ctx)
     with pytest.raises(api.SteviError):   # the reference's randomised L1 descent is not provided
         api.refineBarycentricSymmetricDisp(api.SAD, f, f, idx, 4, ctx=ctx)
+
+
+def test_full_size_refinement_properties(api, ctx):
+    """1080p, 9x9 windows (F = 81), device-resident: the refinements move the winners towards the true sub-pixel field, stay
+    within one pixel of them, and host and device operands give the same maps."""
+    torch = pytest.importorskip("torch")
+    left, right, field = smooth_pair(1080, 1920, 9.0, 5)
+    tctx = api.Context(0, torch_stream=True)
+    dl, dr = torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda()
+    fl, fr = api.unfold(4, 4, dl, ctx=tctx), api.unfold(4, 4, dr, ctx=tctx)
+    zl, zr = (api.getFeatureVolumeForMatchFuncFromFeatures(api.ZNCC, f, ctx=tctx) for f in (fl, fr))
+    cv = api.aggregateCost(api.ZNCC, zl, zr, 20, ctx=tctx)
+    idx = api.extractSelectedIndex(cv, api.SCORE, ctx=tctx)
+    inner = (slice(8, -8), slice(16, -40))
+    raw = idx.cpu().numpy().astype(np.float32)
+    base_err = np.abs(raw[inner] - field[inner]).mean()
+    # (the cost-symmetric form averages two parabolas and is unbounded on flat ones: no one-pixel bound for it)
+    for bounded, fn in ((True, lambda: api.refineBarycentricDisp(api.ZNCC, zl, zr, idx, ctx=tctx)),
+                        (True, lambda: api.refineBarycentricSymmetricDisp(api.ZNCC, zl, zr, idx, 20, 1, ctx=tctx)),
+                        (False, lambda: api.refineCostSymmetricDisp(api.ZNCC, zl, zr, idx, cv, ctx=tctx))):
+        out = fn().cpu().numpy()
+        assert np.isfinite(out[inner]).mean() > 0.999
+        ok = np.isfinite(out)
+        if bounded:
+            assert np.abs(out[ok] - raw[ok]).max() <= 1.0 + 1e-5
+        assert np.nanmean(np.abs(out[inner] - field[inner])) < 0.8 * base_err
+    small = (slice(500, 540), slice(900, 1000))
+    host = api.refineBarycentricDisp(api.ZNCC, zl[small].cpu().numpy().copy(), zr[small].cpu().numpy().copy(), raw[small].astype(np.int32), ctx=ctx)
+    dev = api.refineBarycentricDisp(api.ZNCC, zl[small].contiguous(), zr[small].contiguous(), idx[small].contiguous(), ctx=tctx).cpu().numpy()
+    assert np.array_equal(host, dev, equal_nan=True)
+    tctx.close()

@@ -131,3 +131,29 @@ def test_shape_rules(api, ctx):
     assert api.patchMatch(api.SSD, a, b, (-1, 1, 0, 3), 1, 0, ctx=ctx).shape == (5, 8, 2)
     with pytest.raises(api.SteviError):
         api.patchMatch(api.CENSUS, a, a, (0, 3), ctx=ctx)
+
+
+def test_full_size_patch_match_properties(api, ctx, oracle):
+    """1080p, 5x5 windows, device-resident: PatchMatch ends within the search range, agrees with the exhaustive winner on almost
+    all pixels, never ends on a worse cell than it started from, and is repeatable."""
+    torch = pytest.importorskip("torch")
+    L, R, gt = synth.stereo_pair(1080, 1920, 9, d_bg=8, d_sq=32, d_max=60, dtype=np.float32)
+    tctx = api.Context(0, torch_stream=True)
+    dl, dr = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    fl, fr = api.unfold(2, 2, dl, ctx=tctx), api.unfold(2, 2, dr, ctx=tctx)
+    init = torch.randint(0, 128, (1080, 1920, 1), dtype=torch.int32, device="cuda")
+    out = api.patchMatch(api.ZNCC, fr, fl, (0, 127), 5, 4, initializer=init, seed=3, ctx=tctx)
+    again = api.patchMatch(api.ZNCC, fr, fl, (0, 127), 5, 4, initializer=init, seed=3, ctx=tctx)
+    torch.cuda.synchronize()
+    assert torch.equal(out, again)
+    d = out[..., 0].cpu().numpy()
+    assert d.min() >= 0 and d.max() <= 127
+    best = api.extractSelectedIndex(api.unfoldBasedCostVolume(api.ZNCC, dl, dr, 2, 2, 128, ctx=tctx), api.SCORE, ctx=tctx).cpu().numpy()
+    inner = (slice(8, -8), slice(8, 1920 - 136))
+    assert (d[inner] == best[inner]).mean() > 0.97
+    # the cost of the final disparity is at least the cost of the initial one wherever the initial one named a cell
+    c0 = api.onDemandTruncatedCostVolume(api.ZNCC, fr, fl, (0, 127), init, 0, ctx=tctx)[..., 0].cpu().numpy()
+    c1 = api.onDemandTruncatedCostVolume(api.ZNCC, fr, fl, (0, 127), out, 0, ctx=tctx)[..., 0].cpu().numpy()
+    named = c0 != np.float32(1.17549435e-38)
+    assert (c1[named] >= c0[named]).all()
+    tctx.close()
