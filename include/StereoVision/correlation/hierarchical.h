@@ -66,6 +66,21 @@ OffsetedCostVolume<TCV> hiearchicalTruncatedCostVolume(Multidim::Array<T_L, nImD
 	return hiearchicalTruncatedCostVolume<matchFunc, depth, T_L, T_R, nImDim, dDir, TCV>(img_l, img_r, h_radiuses, v_radiuses, disp_width, upscale_disp_radius);
 }
 
+// computeGuidedCV, :73-233: the caller's (processed) feature volumes and the coarser level's disparity estimate
+template<matchingFunctions matchFunc, typename T_L, typename T_R, dispDirection dDir = dispDirection::RightToLeft, typename TCV = float>
+OffsetedCostVolume<TCV> computeGuidedCV(Multidim::Array<T_L, 3> const& feature_vol_l, Multidim::Array<T_R, 3> const& feature_vol_r,
+										Multidim::Array<disp_t, 2> disp_guide, disp_t upscale_disp_radius) {
+	static_assert(std::is_same_v<T_L, float> && std::is_same_v<T_R, float> && std::is_same_v<TCV, float>, "float features and costs");
+	auto sh = (dDir == dispDirection::RightToLeft ? feature_vol_r : feature_vol_l).shape();
+	const int t = 2 * upscale_disp_radius + 1;
+	OffsetedCostVolume<TCV> r{Multidim::Array<TCV, 3>({sh[0], sh[1], t}, {sh[1] * t, t, 1}), Multidim::Array<disp_t, 2>(sh[0], sh[1])};   // strides :107
+	stevi_array l = B200::describe(feature_vol_l), rr = B200::describe(feature_vol_r), g = B200::describe(disp_guide),
+				tc = B200::describe(r.truncated_cost_volume), d = B200::describe(r.disp_estimate);
+	if (!B200::ok(stevi_guided_cost_volume_features(B200::threadContext(), int(matchFunc), &l, &rr, &g, upscale_disp_radius, int(dDir), &tc, &d)))
+		return OffsetedCostVolume<TCV>{Multidim::Array<TCV, 3>(), Multidim::Array<disp_t, 2>()};
+	return r;
+}
+
 // computeGuidedCV on images (unfold + features fused): guide = the coarser level's disp_estimate / selected index
 template<matchingFunctions matchFunc, dispDirection dDir = dispDirection::RightToLeft>
 OffsetedCostVolume<float> computeGuidedCV(Multidim::Array<float, 2> const& img_l, Multidim::Array<float, 2> const& img_r, uint8_t h_radius,

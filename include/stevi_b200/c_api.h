@@ -402,6 +402,14 @@ STEVI_API int32_t stevi_guided_cost_volume(stevi_ctx* ctx, int32_t matchfunc, co
 								 int32_t h_radius, int32_t v_radius, const stevi_array* guide, int32_t upscale_disp_radius,
 								 int32_t direction, stevi_array* tcv, stevi_array* disp);
 
+/* computeGuidedCV<matchFunc, float, float, dDir, float>(feature_vol_l, feature_vol_r, disp_guide, upscale_disp_radius) with the
+ * reference's own operands (correlation/hierarchical.h:73-233): feat_l (H,Wl,F), feat_r (H,Wr,F) f32 feature volumes as the caller
+ * prepared them (getFeatureVolumeForMatchFunc of an unfold, a FeatureVolumePyramid level, ..), guide (h_g,w_g) i32 ->
+ * tcv (H,Wsource,2*radius+1) f32, disp (H,Wsource) i32. Sums in the reference's channel order. */
+STEVI_API int32_t stevi_guided_cost_volume_features(stevi_ctx* ctx, int32_t matchfunc, const stevi_array* feat_l, const stevi_array* feat_r,
+										  const stevi_array* guide, int32_t upscale_disp_radius, int32_t direction,
+										  stevi_array* tcv, stevi_array* disp);
+
 /* Row-band form of stevi_guided_cost_volume for frames split across GPUs: img_l / img_r hold image
  * rows img_row0 .. img_row0 + rows-1 of an image that is img_height rows tall, guide holds guide rows guide_row0 .. of a
  * guide that is guide_height rows tall, and tcv / disp receive the rows out_row0 .. out_row0 + tcv.shape[0]-1. The guide

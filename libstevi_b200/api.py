@@ -909,6 +909,22 @@ def computeGuidedCV(matchFunc, img_l, img_r, h_radius, v_radius, guide, upscale_
     return tcv, disp
 
 
+def computeGuidedCVFromFeatures(matchFunc, feature_vol_l, feature_vol_r, disp_guide, upscale_disp_radius=2, dDir=RIGHT_TO_LEFT, ctx=None):
+    """computeGuidedCV with the reference's own operands, hierarchical.h:73-233: (H,W,F) f32 feature volumes as the caller prepared them
+    and the (h_g,w_g) int32 guide. Returns (truncated_cost_volume, disp_estimate), or None where the reference returns an empty volume."""
+    ctx = _ctx_for(ctx, feature_vol_l)
+    ws = feature_vol_r.shape[1] if dDir == RIGHT_TO_LEFT else feature_vol_l.shape[1]
+    tcv = _empty(feature_vol_l, (feature_vol_l.shape[0], ws, 2 * upscale_disp_radius + 1), np.float32)
+    disp = _empty(feature_vol_l, (feature_vol_l.shape[0], ws), np.int32)
+    l, r, g, t, d = describe(feature_vol_l), describe(feature_vol_r), describe(disp_guide), describe(tcv), describe(disp)
+    rc = lib.stevi_guided_cost_volume_features(ctx.handle, matchFunc, ctypes.byref(l), ctypes.byref(r), ctypes.byref(g), upscale_disp_radius, dDir,
+                                               ctypes.byref(t), ctypes.byref(d))
+    if rc == E_SHAPE:
+        return None
+    ctx.check(rc)
+    return tcv, disp
+
+
 def hiearchicalTruncatedCostVolume(matchFunc, depth, img_l, img_r, h_radius, v_radius, disp_width, upscale_disp_radius=2,
                                    dDir=RIGHT_TO_LEFT, ctx=None):
     """hierarchical.h:235-314 (sic). h_radius / v_radius: scalars, or depth+1 values coarsest level first.

@@ -478,6 +478,20 @@ int32_t stevi_refine_cost_symmetric_disp(stevi_ctx* c, int32_t mf, const stevi_a
 	return st.finish();
 }
 
+int32_t stevi_guided_cost_volume_features(stevi_ctx* c, int32_t mf, const stevi_array* fl, const stevi_array* fr, const stevi_array* guide,
+										  int32_t radius, int32_t direction, stevi_array* tcv, stevi_array* disp) {
+	STEVI_TRY(begin_call(c));
+	Stager st(c);
+	View vl, vr, vg, vt, vd;
+	STEVI_TRY(st.in(fl, vl, "feat_l"));
+	STEVI_TRY(st.in(fr, vr, "feat_r"));
+	STEVI_TRY(st.in(guide, vg, "guide"));
+	STEVI_TRY(st.out(tcv, vt, "tcv"));
+	STEVI_TRY(st.out(disp, vd, "disp"));
+	STEVI_TRY(guided_cv_features_dev(c, mf, vl, vr, vg, radius, direction, vt, vd));
+	return st.finish();
+}
+
 int32_t stevi_patch_match(stevi_ctx* c, int32_t mf, const stevi_array* fs, const stevi_array* ft, int32_t dims, const int32_t* search,
 						  int32_t n_iter, int32_t n_random, uint64_t seed, const stevi_array* init, stevi_array* disp) {
 	STEVI_TRY(begin_call(c));

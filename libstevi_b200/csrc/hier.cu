@@ -188,6 +188,50 @@ __device__ __forceinline__ int guided_d0(const Guided& p, int gi, int j) {
 	return p.sign * (int)roundf(id);
 }
 
+// computeGuidedCV on caller-supplied feature volumes — the reference's own signature (hierarchical.h:73-233): the candidates and
+// the re-centred window are comparisons of the source vector with target vectors (zeros outside the target image, :170),
+// accumulated over the channels in the reference's order.
+struct GuidedFeat {
+	Guided g;
+	const float* fs; int64_t s0, s1, s2;
+	const float* ft; int64_t t0, t1, t2;
+	int F;
+};
+__device__ __forceinline__ float guided_compare(const GuidedFeat& q, const float* s, const float* t, bool inside) {
+	float acc = 0.f;
+	for (int c = 0; c < q.F; c++) {
+		const float sv = s[c * q.s2], tv = inside ? t[c * q.t2] : 0.f;
+		if (q.g.op == BOX_PROD) acc = __fadd_rn(acc, __fmul_rn(sv, tv));
+		else if (q.g.op == BOX_SQ) { const float e = __fsub_rn(sv, tv); acc = __fadd_rn(acc, __fmul_rn(e, e)); }
+		else acc = __fadd_rn(acc, fabsf(__fsub_rn(sv, tv)));
+	}
+	return acc;
+}
+__global__ void __launch_bounds__(128) k_guided_cv_features(const GuidedFeat q) {
+	const Guided& p = q.g;
+	const int j = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+	if (j >= p.Ws) return;
+	const int d0 = guided_d0(p, i, j);
+	const float* s = q.fs + i * q.s0 + j * q.s1;
+	const float* trow = q.ft + i * q.t0;
+	float score = p.cost ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+	int d_r = d0;
+	for (int dd = -p.r; dd <= p.r; dd++) {   // strict compare: the first extremum wins (:179,:184)
+		const int jt = j + d0 + dd;
+		const bool inside = jt >= 0 && jt < p.Wt;
+		const float cmp = guided_compare(q, s, trow + (int64_t)(inside ? jt : 0) * q.t1, inside);
+		if (p.cost ? (cmp < score) : (cmp > score)) { score = cmp; d_r = d0 + dd; }
+	}
+	p.disp[i * p.d0s + j * p.d1s] = p.sign * d_r;
+	// after the reference's shift-and-refill (:194-226) cell dd holds the comparison against target column j + d_r + sign*(dd - r)
+	float* o = p.tcv + i * p.t0 + j * p.t1;
+	for (int dd = 0; dd <= 2 * p.r; dd++) {
+		const int jt = j + d_r + p.sign * (dd - p.r);
+		const bool inside = jt >= 0 && jt < p.Wt;
+		o[dd * p.t2] = guided_compare(q, s, trow + (int64_t)(inside ? jt : 0) * q.t1, inside);
+	}
+}
+
 // Tiled form for windows up to 9 wide and upscale radii 1..2: a block owns 128 consecutive pixels of GT_ROWS consecutive
 // rows. The image rows under those windows (GT_ROWS + 2vr of them) are staged once in shared memory, 16 bytes at a time:
 // 136 source columns and the span of all candidate columns of the block (the guide being smooth). A thread then walks its
@@ -485,6 +529,41 @@ int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr
 	p.disp = disp.as<int32_t>(); p.d0s = disp.st[0]; p.d1s = disp.st[1];
 	dim3 grid(cdiv(Ws, 128), n_rows);
 	return launch_guided(c, p, grid);
+}
+
+int32_t guided_cv_features_dev(stevi_ctx* c, int mf, const View& fl, const View& fr, const View& guide, int radius, int direction,
+							   const View& tcv, const View& disp) {
+	if (!h_known(mf)) return fail(c, STEVI_E_UNSUPPORTED, "guided_cv_features: matching function %d not available", mf);
+	if (radius < 0 || radius > 64) return fail(c, STEVI_E_ARG, "guided_cv_features: upscale radius");
+	if (fl.ndim != 3 || fr.ndim != 3 || fl.dtype != STEVI_F32 || fr.dtype != STEVI_F32) return fail(c, STEVI_E_DTYPE, "guided_cv_features: feature volumes must be (H,W,F) f32");
+	if (guide.ndim != 2 || guide.dtype != STEVI_I32) return fail(c, STEVI_E_DTYPE, "guided_cv_features: guide must be (h_g,w_g) i32");
+	// hierarchical.h:89-91: an empty volume when the heights differ
+	if (fl.shape[0] != fr.shape[0] || fl.shape[2] != fr.shape[2]) return fail(c, STEVI_E_SHAPE, "guided_cv_features: the feature volumes do not match");
+	const bool r2l = direction == STEVI_RIGHT_TO_LEFT;
+	const View& src = r2l ? fr : fl;
+	const View& tgt = r2l ? fl : fr;
+	const int H = src.shape[0], Ws = src.shape[1];
+	if (H < 2 || Ws < 2 || guide.shape[0] < 2 || guide.shape[1] < 2) return fail(c, STEVI_E_SHAPE, "guided_cv_features: every axis needs at least 2 pixels (hierarchical.h:116,132)");
+	if (H > 65535) return fail(c, STEVI_E_UNSUPPORTED, "guided_cv_features: more than 65535 rows");
+	if (tcv.ndim != 3 || tcv.dtype != STEVI_F32 || tcv.shape[0] != H || tcv.shape[1] != Ws || tcv.shape[2] != 2 * radius + 1)
+		return fail(c, STEVI_E_SHAPE, "guided_cv_features: tcv must be (%d,%d,%d) f32", H, Ws, 2 * radius + 1);
+	if (disp.ndim != 2 || disp.dtype != STEVI_I32 || disp.shape[0] != H || disp.shape[1] != Ws)
+		return fail(c, STEVI_E_SHAPE, "guided_cv_features: disp must be (%d,%d) i32", H, Ws);
+	GuidedFeat q;
+	Guided& p = q.g;
+	p = Guided{};
+	p.guide = guide.as<int32_t>(); p.g0 = guide.st[0]; p.g1 = guide.st[1]; p.hg = guide.shape[0]; p.wg = guide.shape[1];
+	p.H = H; p.Ws = Ws; p.Wt = tgt.shape[1]; p.r = radius; p.sign = r2l ? 1 : -1;
+	p.op = h_op(mf); p.cost = h_score(mf) ? 0 : 1;
+	p.n_rows = H;
+	p.tcv = tcv.as<float>(); p.t0 = tcv.st[0]; p.t1 = tcv.st[1]; p.t2 = tcv.st[2];
+	p.disp = disp.as<int32_t>(); p.d0s = disp.st[0]; p.d1s = disp.st[1];
+	q.fs = src.as<float>(); q.s0 = src.st[0]; q.s1 = src.st[1]; q.s2 = src.st[2];
+	q.ft = tgt.as<float>(); q.t0 = tgt.st[0]; q.t1 = tgt.st[1]; q.t2 = tgt.st[2];
+	q.F = src.shape[2];
+	dim3 grid(cdiv(Ws, 128), H);
+	STEVI_LAUNCH(c, k_guided_cv_features, grid, 128, 0, q);
+	return STEVI_OK;
 }
 
 // hierarchical.h:235-314. h_radii / v_radii hold depth+1 entries, coarsest level first (like the reference's arrays).

@@ -114,6 +114,9 @@ int32_t sigma_filter_dev(stevi_ctx* c, const View& mean, const View& img, int hr
 // band == nullptr: whole images; else the images / guide are row bands placed in global coordinates (c_api.h: stevi_band)
 int32_t guided_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr, int vr, const View& guide, int radius, int direction,
 					  const stevi_band* band, const View& tcv, const View& disp);
+// computeGuidedCV on caller-supplied (processed) feature volumes, the reference's own signature (hierarchical.h:73-233)
+int32_t guided_cv_features_dev(stevi_ctx* c, int mf, const View& fl, const View& fr, const View& guide, int radius, int direction,
+							   const View& tcv, const View& disp);
 int32_t hierarchical_dev(stevi_ctx* c, int mf, int depth, const View& l, const View& r, const int32_t* h_radii, const int32_t* v_radii,
 						 int D, int radius, int direction, const View& tcv, const View& disp);
 

@@ -358,6 +358,15 @@ class _Checker:
         assert rc == 0
         return tcv, disp
 
+    def guided_cv_features(self, mf, fl, fr, guide, radius=2, direction=R2L):
+        fl, fr, g = _c(fl, np.float32), _c(fr, np.float32), _c(guide, np.int32)
+        ws = fr.shape[1] if direction == R2L else fl.shape[1]
+        tcv = np.empty((fl.shape[0], ws, 2 * radius + 1), np.float32)
+        disp = np.empty((fl.shape[0], ws), np.int32)
+        rc = self._f("guided_cv_features_f32")(mf, _p(fl), _p(fr), fl.shape[0], fl.shape[1], fr.shape[1], fl.shape[2], _p(g), g.shape[0], g.shape[1],
+                                               radius, direction, _p(tcv), _p(disp))
+        return (tcv, disp) if rc == 0 else None
+
     def hierarchical(self, mf, depth, left, right, hr, vr, D, radius=2, direction=R2L):
         h, w = left.shape
         tcv = np.empty((h, w, 2 * radius + 1), np.float32)

@@ -15,6 +15,7 @@
 #include <io/image_io.h>
 #include <correlation/patchmatch.h>
 #include <correlation/on_demand_cost_volume.h>
+#include <correlation/hierarchical.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -214,6 +215,25 @@ int ref_on_demand_truncated_cost_volume(int matchfunc, int dims, const float* fs
 	case 7: return od_run<matchingFunctions::ZSAD>(dims, fs, ft, h, w, ht, wt, f, so, disp, radius, out);
 	default: return 3;
 	}
+}
+
+// computeGuidedCV<matchFunc, float, float, dDir>(feature_vol_l, feature_vol_r, disp_guide, radius) (hierarchical.h:73-233)
+int ref_guided_cv_features_f32(int matchfunc, const float* fl, const float* fr, int h, int wl, int wr, int f, const int32_t* guide, int hg, int wg,
+							   int radius, int dir, float* tcv, int32_t* disp) {
+	auto L = view3(fl, h, wl, f), R = view3(fr, h, wr, f);
+	auto G = view2(guide, hg, wg);
+	const int ws = dir ? wr : wl, n = 2 * radius + 1;
+#define GCV(F_) { auto r = dir ? computeGuidedCV<F_, float, float, dispDirection::RightToLeft>(L, R, G, radius) : computeGuidedCV<F_, float, float, dispDirection::LeftToRight>(L, R, G, radius); \
+		if (r.truncated_cost_volume.empty()) return 1; \
+		for (int i = 0; i < h; i++) for (int j = 0; j < ws; j++) { disp[size_t(i) * ws + j] = r.disp_estimate.valueUnchecked(i, j); \
+			for (int k = 0; k < n; k++) tcv[(size_t(i) * ws + j) * n + k] = r.truncated_cost_volume.valueUnchecked(i, j, k); } return 0; }
+	switch (matchfunc) {
+	case 5: GCV(matchingFunctions::ZNCC)
+	case 2: GCV(matchingFunctions::SSD)
+	case 7: GCV(matchingFunctions::ZSAD)
+	default: return 3;
+	}
+#undef GCV
 }
 
 // refinedBarycentricDisp on images (image_based_refinement.h:2502-2544): unfold, features, cost volume, winner, refinement

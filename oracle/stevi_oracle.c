@@ -850,6 +850,13 @@ int orc_guided_cv_f32(int mf, const float* l, const float* r, int h, int wl, int
 	return 0;
 }
 
+/* computeGuidedCV on caller-supplied feature volumes, the reference's own signature (hierarchical.h:73-233) */
+int orc_guided_cv_features_f32(int mf, const float* fl, const float* fr, int h, int wl, int wr, int F, const int32_t* guide, int hg, int wg,
+							   int radius, int dir, float* tcv, int32_t* disp) {
+	guided_cv(mf, fl, fr, h, wl, wr, F, guide, hg, wg, radius, dir, tcv, disp);
+	return 0;
+}
+
 /* ---- hierarchical.h:235-314 (same radii at every level). tcv (h,w,2*radius+1), disp (h,w) at full resolution. */
 static int hier_level(int mf, int depth, const float* l, const float* r, int h, int w, int hr, int vr, int D,
 					  int radius, int dir, float* tcv, int32_t* disp) {

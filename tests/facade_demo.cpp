@@ -91,6 +91,10 @@ int main() {
 
 	auto hier = hiearchicalTruncatedCostVolume<matchingFunctions::ZNCC, 2>(lf, rf, 2, 2, D, 2);
 	std::printf("hier_disp %.0f\n", checksum(hier.disp_estimate));
+	// computeGuidedCV in the reference's own form: processed feature volumes + the coarser level's estimate
+	auto gcv = computeGuidedCV<matchingFunctions::ZNCC, float, float>(getFeatureVolumeForMatchFunc<matchingFunctions::ZNCC>(fvl),
+																	  getFeatureVolumeForMatchFunc<matchingFunctions::ZNCC>(fvr), hier.disp_estimate, 2);
+	std::printf("guided_features_disp %.0f\n", checksum(gcv.disp_estimate));
 	auto pyr = buildFeaturePyramid<float>(lf, 1, 1, 3);
 	auto psh = pyr.back().shape();
 	std::printf("pyramid_levels %d\npyramid_last_shape %dx%dx%d\npyramid_empty %d\n", int(pyr.size()), psh[0], psh[1], psh[2],

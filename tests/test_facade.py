@@ -148,8 +148,10 @@ def test_facade_results_equal_the_python_mirror(tmp_path, api, ctx):
     assert abs(float(got["zncc_match"]) - float((zi[4:h - 4, 4:w - 24] == 5).mean())) < 1e-3
     assert float(got["zncc_match"]) > 0.95
     order = os.environ.get("STEVI_FACADE_ORDER", "")
-    sums = {"census_cv": cv, "sgm": sg, "disp": disp, "zncc_idx": zi,
-            "hier_disp": api.hiearchicalTruncatedCostVolume(api.ZNCC, 2, lf, rf, 2, 2, D, 2, ctx=ctx)[1]}
+    hier_disp = api.hiearchicalTruncatedCostVolume(api.ZNCC, 2, lf, rf, 2, 2, D, 2, ctx=ctx)[1]
+    zfl, zfr = (api.getFeatureVolumeForMatchFuncFromFeatures(api.ZNCC, f, ctx=ctx) for f in (fvl, fvr))
+    sums = {"census_cv": cv, "sgm": sg, "disp": disp, "zncc_idx": zi, "hier_disp": hier_disp,
+            "guided_features_disp": api.computeGuidedCVFromFeatures(api.ZNCC, zfl, zfr, hier_disp, 2, ctx=ctx)[1]}
     for name, arr in sums.items():
         a = np.asarray(arr)
         cands = {_checksum(a), _checksum(np.transpose(a))}   # last-index-fastest or first-index-fastest walk

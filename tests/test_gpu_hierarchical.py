@@ -86,3 +86,27 @@ def test_hierarchical_odd_sizes_and_per_level_radii(api, ctx, oracle):
     agree(got, want, 0.995)
     got = api.hiearchicalTruncatedCostVolume(api.ZNCC, 2, L, R, (1, 2, 3), (1, 1, 2), 14, 2, ctx=ctx)
     assert got[0].shape == (45, 71, 5) and np.isfinite(got[0]).mean() > 0.9
+
+
+@pytest.mark.parametrize("name", ["ZNCC", "SSD", "ZSAD", "CC", "SAD"])
+@pytest.mark.parametrize("ddir", ["r2l", "l2r"])
+def test_guided_cv_on_feature_volumes(api, ctx, oracle, name, ddir):
+    """computeGuidedCV with the reference's own operands (hierarchical.h:73-233): caller-supplied feature volumes and a guide of
+    half the size. Disparities equal; volumes equal to 2e-6 of the largest magnitude (sums in the reference's channel order)."""
+    rng = np.random.default_rng(17)
+    L, R = synth.random_image(37, 90, 51), synth.random_image(37, 86, 52)
+    mf = getattr(oracle, name)
+    fl, fr = oracle.port.features_for_matchfunc(mf, oracle.port.unfold(L, 2, 1)), oracle.port.features_for_matchfunc(mf, oracle.port.unfold(R, 2, 1))
+    guide = rng.integers(-3, 9, (19, 45)).astype(np.int32)
+    d_api, d_o = (api.RIGHT_TO_LEFT, oracle.R2L) if ddir == "r2l" else (api.LEFT_TO_RIGHT, oracle.L2R)
+    for radius in (1, 2, 3):
+        tcv, disp = api.computeGuidedCVFromFeatures(getattr(api, name), fl, fr, guide, radius, d_api, ctx=ctx)
+        checkers = [oracle.port]
+        if oracle.ref_ibr is not None and oracle.ref_ibr.has("guided_cv_features_f32") and name in ("ZNCC", "SSD", "ZSAD"):
+            checkers.append(oracle.ref_ibr)
+        for chk in checkers:
+            wt, wd = chk.guided_cv_features(mf, fl, fr, guide, radius, d_o)
+            assert np.array_equal(disp, wd)
+            assert np.array_equal(np.isnan(tcv), np.isnan(wt))
+            assert np.nanmax(np.abs(tcv - wt)) <= 2e-6 * max(1.0, float(np.nanmax(np.abs(wt))))
+    assert api.computeGuidedCVFromFeatures(getattr(api, name), fl[:20], fr, guide, 2, d_api, ctx=ctx) is None   # heights differ: empty volume
