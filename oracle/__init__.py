@@ -326,7 +326,7 @@ class _Checker:
         return out if rc == 0 else None
 
     def refine_2d_patch(self, tcv, raw, kernel=PARABOLA):
-        """refineDisp2dCostPatchInterpolation (port only: the compiled reference needs Eigen for this one)."""
+        """refineDisp2dCostPatchInterpolation (``ref_ibr`` runs the reference's code on the Eigen stand-in's Gauss-Jordan inverse)."""
         h, w, n0, n1 = tcv.shape
         out = np.empty((h, w, 2), np.float32)
         rc = self._f("refine_disp_2d_cost_patch_interp")(_p(_c(tcv, np.float32)), _p(_c(raw, np.int32)), h, w, n0, n1, kernel, _p(out))

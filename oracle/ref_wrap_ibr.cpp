@@ -16,6 +16,7 @@
 #include <correlation/patchmatch.h>
 #include <correlation/on_demand_cost_volume.h>
 #include <correlation/hierarchical.h>
+#include <correlation/cost_based_refinement.h>
 
 using namespace StereoVision;
 using namespace StereoVision::Correlation;
@@ -234,6 +235,17 @@ int ref_guided_cv_features_f32(int matchfunc, const float* fl, const float* fr, 
 	default: return 3;
 	}
 #undef GCV
+}
+
+// refineDisp2dCostPatchInterpolation<kernel> (cost_based_refinement.h:371-433 over refineCostPatch :71-126): the reference's code; its
+// two Eigen inverses (6x6 normal equations, 2x2 Hessian) run on the stand-in's Gauss-Jordan. kernel: 1 Parabola, 2 Gaussian
+int ref_refine_disp_2d_cost_patch_interp(const float* tcv, const int32_t* raw, int h, int w, int n0, int n1, int kernel, float* out) {
+	MD::Array<float, 4> t(const_cast<float*>(tcv), {h, w, n0, n1}, {w * n0 * n1, n0 * n1, n1, 1}, false);
+	MD::Array<int32_t, 3> d(const_cast<int32_t*>(raw), {h, w, 2}, {w * 2, 2, 1}, false);
+	auto r = kernel == 2 ? refineDisp2dCostPatchInterpolation<InterpolationKernel::Gaussian>(t, d) : refineDisp2dCostPatchInterpolation<InterpolationKernel::Parabola>(t, d);
+	if (r.empty()) return 1;
+	out3(r, out);
+	return 0;
 }
 
 // refinedBarycentricDisp on images (image_based_refinement.h:2502-2544): unfold, features, cost volume, winner, refinement

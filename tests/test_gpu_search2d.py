@@ -251,6 +251,10 @@ def test_patch_refinement_matches_oracle(api, ctx, oracle):
         kept = (got != raw) .all(axis=2) & (want != raw).all(axis=2)
         assert kept.mean() > 0.6
         assert np.max(np.abs(got - want)[kept]) <= 1e-4
+        if oracle.ref_ibr is not None:      # the reference's own refineCostPatch (its Eigen inverses on the stand-in's Gauss-Jordan)
+            ref = oracle.ref_ibr.refine_2d_patch(t, raw, kernel)
+            assert np.array_equal((got != raw).all(axis=2), (ref != raw).all(axis=2))
+            assert np.max(np.abs(got - ref)) <= 1e-4
         d = got[0, 0] - raw[0, 0]
         ref64 = lstsq_patch_deltas(np.log(t[0, 0, 1:4]) if kernel == oracle.GAUSSIAN else t[0, 0, 1:4])
         if np.all(np.abs(ref64) < 0.99):

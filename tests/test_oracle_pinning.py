@@ -694,3 +694,22 @@ def test_golden_refinement_patch_match_on_demand():
         for n_iter in (1, 2, 4):
             assert same(port.patch_match(mf, fr_raw, fl_raw, (0, 9), n_iter, 0, G3["pm_init"]), G3[f"pm_{name}_{n_iter}"])
         assert same(port.on_demand_truncated_cost_volume(mf, fr_raw, fl_raw, (-2, 9), G3["od_disp"], 1), G3[f"od_{name}"])
+
+
+def test_patch_refinement_port_matches_compiled_reference(oracle):
+    """refineDisp2dCostPatchInterpolation (cost_based_refinement.h:371-433): the port's closed-form normal equations against the reference's
+    refineCostPatch (:71-126) compiled over the Eigen stand-in (float Gauss-Jordan inverses). Same kept/dropped pixels, deltas within 1e-4."""
+    if oracle.ref_ibr is None:
+        pytest.skip("oracle/_ref/libstevi_ref_ibr.so not built")
+    rng = np.random.default_rng(12)
+    t = rng.uniform(0.5, 2.0, (30, 90, 5, 3)).astype(np.float32)
+    t[:, :, 2, 1] = 0.1
+    t[::7, ::5, 2, 1] = 3.0             # centre is not the extremum: deltas beyond one pixel are dropped
+    raw = rng.integers(-5, 6, (30, 90, 2)).astype(np.int32)
+    for kernel in (oracle.PARABOLA, oracle.GAUSSIAN):
+        a = oracle.port.refine_2d_patch(t, raw, kernel)
+        b = oracle.ref_ibr.refine_2d_patch(t, raw, kernel)
+        assert np.array_equal((a != raw).all(axis=2), (b != raw).all(axis=2))
+        assert np.max(np.abs(a - b)) <= 1e-4
+    for shape in ((3, 3, 4, 3), (3, 3, 3, 1)):
+        assert oracle.ref_ibr.refine_2d_patch(np.zeros(shape, np.float32), np.zeros((3, 3, 2), np.int32), oracle.PARABOLA) is None
