@@ -36,6 +36,15 @@ enum { SW_SCORE = 0, SW_COST_COMPAT = 1, SW_COST = 2 };
 
 template<int MODE> __device__ __forceinline__ float sw_worst() { return MODE == SW_SCORE ? -INFINITY : INFINITY; }
 template<int MODE> __device__ __forceinline__ float sw_better(float a, float b) { return MODE == SW_SCORE ? fmaxf(a, b) : fminf(a, b); }
+// extremum over the warp in ONE instruction (sm_100a: redux.sync on f32, CREDUX in SASS) instead of five dependent shuffle
+// rounds. The operands are never NaN here (non-finite scores have been replaced by the worst value), so this is the value the
+// butterfly of fmaxf / fminf gave. (Measured: no change in kernel time — see the note at k_sgm_sweep_h on what bounds it.)
+template<int MODE> __device__ __forceinline__ float sw_warp_best(float v) {
+	float r;
+	if (MODE == SW_SCORE) asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+	else asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+	return r;
+}
 
 // one cell of one path: `in` = previous score at d (non-finite ones already replaced by the worst value), l / r = at d-1 / d+1,
 // farv = M -/+ P2 with M = extremum of the previous scores, FINITE (the caller handles the other case: actual_cost = c).
@@ -65,6 +74,7 @@ struct HSweep {
 	float* A; int64_t a0, a2;
 	int H, W, D, top, bottom, left, right;
 	float P1, P2, Pout;
+	int pf;   // L2 prefetch distance in tiles (0: none)
 };
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -78,9 +88,11 @@ template<> struct Tile<1> {
 	static __device__ __forceinline__ void st(float* p, const float* v) { p[0] = v[0]; }
 };
 template<> struct Tile<8> {
+	// one 256-bit access per sector (sm_100a: LDG.E.256 / STG.E.256): the lanes of a warp address 32 different rows of the volume, so
+	// every instruction costs 32 tag look-ups whatever its width
 	static __device__ __forceinline__ void f32(const float* p, float* v) {
-		const float4 x = __ldg(reinterpret_cast<const float4*>(p)), y = __ldg(reinterpret_cast<const float4*>(p) + 1);
-		v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w; v[4] = y.x; v[5] = y.y; v[6] = y.z; v[7] = y.w;
+		asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+					 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
 	}
 	static __device__ __forceinline__ void u16(const uint16_t* p, float* v) {
 		const uint4 x = __ldg(reinterpret_cast<const uint4*>(p));
@@ -88,8 +100,8 @@ template<> struct Tile<8> {
 		v[4] = (float)(x.z & 0xffffu); v[5] = (float)(x.z >> 16); v[6] = (float)(x.w & 0xffffu); v[7] = (float)(x.w >> 16);
 	}
 	static __device__ __forceinline__ void st(float* p, const float* v) {
-		reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
-		reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+		asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+					 :: "l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
 	}
 };
 
@@ -128,8 +140,16 @@ __device__ __forceinline__ void sw_path(const float (&c)[DN], float (&st)[DN], f
 
 // warp = one image row; lane l = disparities l*DH .. l*DH+DH-1; columns in aligned tiles of CT. The contributions replace the
 // costs in the tile registers and leave as whole tiles. REVERSE walks right to left and adds to what A already holds.
+// What bounds it (ncu source page, round 2, profiles/ncu_source_r2c_k_sgm_sweep.txt): 65 % of the stall samples are waits for the
+// next tile's loads and for the stores at the tile boundaries, and neither a longer prefetch distance (2, 3, 6 tiles: 1.80, 1.86,
+// 2.36 ms), nor whole-line L2 fetches (ld.global.L2::128B), nor the register budget (168 -> 197, spill gone) moved it: every
+// access of a warp goes to 32 different rows of the volume, i.e. 32 tag look-ups per instruction whatever its width (l1tex 58 %,
+// lts 56 % busy at 0.7 IPC). What did move it is fewer instructions through that stage: 256-bit loads and stores (1.80 -> 1.57
+// ms) and no prefetch instructions at all (-> 1.43 ms; the loads of the next tile are in flight for a whole tile anyway). What
+// is left is a load path that does not go through the L1 tag stage lane by lane (a tensor-map TMA box [DH*32 rows][8 columns]
+// per warp and tile); not built this round.
 template<int DH, int CT, int MODE, bool REVERSE>
-__global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
+__global__ void __launch_bounds__(128, 2) k_sgm_sweep_h(const HSweep p) {
 	const int lane = threadIdx.x & 31;
 	const int i = p.top + blockIdx.x * 4 + (threadIdx.x >> 5);
 	if (i >= p.H - p.bottom) return;
@@ -159,7 +179,7 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 	};
 	// the sectors two tiles ahead are pulled into L2 while the next tile's loads are in flight
 	auto prefetch_tile = [&](int tile) {
-		if (CT == 1 || (REVERSE ? tile < t_last : tile > t_last)) return;
+		if (CT == 1 || p.pf == 0 || (REVERSE ? tile < t_last : tile > t_last)) return;
 #pragma unroll
 		for (int k = 0; k < DH; k++) {
 			if (d0 + k < p.D) {
@@ -170,7 +190,7 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 	};
 	float cn[DH][CT];
 	load_tile(t_first, cn);
-	prefetch_tile(t_first + dt);
+	for (int k = 1; k < p.pf; k++) prefetch_tile(t_first + k * dt);
 	for (int tile = t_first; REVERSE ? tile >= t_last : tile <= t_last; tile += dt) {
 		float c[DH][CT];
 #pragma unroll
@@ -178,7 +198,7 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 #pragma unroll
 			for (int q = 0; q < CT; q++) c[k][q] = cn[k][q];
 		if (tile != t_last) load_tile(tile + dt, cn);   // the next tile's loads fly while this one is worked on
-		prefetch_tile(tile + 2 * dt);
+		prefetch_tile(tile + p.pf * dt);
 		const bool full = tile * CT >= jb && tile * CT + CT <= je;
 		float old[REVERSE ? DH : 1][CT];
 		if (REVERSE) {
@@ -194,8 +214,7 @@ __global__ void __launch_bounds__(128) k_sgm_sweep_h(const HSweep p) {
 			float mx = WORST;
 #pragma unroll
 			for (int k = 0; k < DH; k++) mx = sw_better<MODE>(mx, pf[k]);
-#pragma unroll
-			for (int s = 16; s > 0; s >>= 1) mx = sw_better<MODE>(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+			mx = sw_warp_best<MODE>(mx);
 			float nlo = __shfl_up_sync(0xffffffffu, pf[DH - 1], 1), nhi = __shfl_down_sync(0xffffffffu, pf[0], 1);
 			if (lane == 0) nlo = WORST;
 			if (lane == 31) nhi = WORST;
@@ -600,11 +619,8 @@ __global__ void __launch_bounds__((SW_NWARP + 1 + SW_NIO) * 32, 1) k_sgm_sweep_t
 					for (int m = 0; m < DH; m++) M[k] = sw_better<MODE>(M[k], st[k][m]);
 				}
 #pragma unroll
-				for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-					for (int k = 0; k < 3; k++)
-						if ((DIRS >> k) & 1) M[k] = sw_better<MODE>(M[k], __shfl_xor_sync(0xffffffffu, M[k], o));
-				}
+				for (int k = 0; k < 3; k++)
+					if ((DIRS >> k) & 1) M[k] = sw_warp_best<MODE>(M[k]);
 #pragma unroll
 				for (int k = 0; k < 3; k++) {
 					if (!((DIRS >> k) & 1)) continue;
@@ -749,6 +765,7 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 	h.A = A; h.a0 = (int64_t)D * W4; h.a2 = W4;
 	h.H = H; h.W = W; h.D = D; h.top = mg.top; h.bottom = mg.bottom; h.left = mg.left; h.right = mg.right;
 	h.P1 = P1; h.P2 = P2; h.Pout = Pout;
+	{ static const char* e = getenv("STEVI_SGM_HPF"); h.pf = e ? atoi(e) : 0; }
 	const size_t esz = dtype_size(cv.dtype);
 	const bool vec = (uintptr_t)cv.p % (8 * esz) == 0 && cv.st[0] % 8 == 0 && cv.st[2] % 8 == 0 && W % 8 == 0;
 	if (mode == SW_SCORE) STEVI_TRY((launch_h<SW_SCORE, false>(c, h, vec)));
