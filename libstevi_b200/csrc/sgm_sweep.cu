@@ -322,7 +322,7 @@ __device__ __forceinline__ void sw_path_fast(const float (&c)[DN], float (&st)[D
 }
 
 // One block walks one strip down (or up) the rows. Per row the strip's slab of the volume, [D][16 columns], is brought into
-// shared memory with coalesced 64-byte runs (asynchronous copies, one row ahead; an L2 prefetch several rows ahead) and read
+// shared memory with coalesced 64-byte runs (asynchronous copies, one or two rows ahead) and read
 // back TRANSPOSED: warp w works on column w of the tile, lane l holding the DH consecutive disparities l*DH .. l*DH+DH-1 of
 // each of the three paths through the pixel (previous scores in registers; extremum over d = one warp reduction; the
 // neighbours d-1 / d+1 are in registers except at the lane borders: two shuffles). The tile rows are stored permuted
@@ -466,7 +466,10 @@ __global__ void __launch_bounds__((SW_NWARP + 1 + SW_NIO) * 32, 1) k_sgm_sweep_t
 					if (p.accumulate) { const float* q = p.S + r * p.s0 + (int64_t)d * p.s2; prefetch_l2(q + j0); prefetch_l2(q + j1); }
 				}
 			};
-			for (int u = NB - 1; u < PD; u++) prefetch(t_begin + u);
+			// the L2 prefetch several rows ahead pays for u16 costs only, whose slabs are fetched by ordinary loads (no 2-byte asynchronous
+			// copies); for float costs it costs more than it hides (downward sweep at C2 size 4.12 -> 3.83 ms without it, round 2)
+			const bool use_pf = p.c_u16 || (p.dbg & 128);
+			if (use_pf) for (int u = NB - 1; u < PD; u++) prefetch(t_begin + u);
 #pragma unroll
 			for (int u = 0; u < NB - 1; u++) fill(t_begin + u, u);
 			int b = 0;   // buffer of row t
@@ -478,7 +481,7 @@ __global__ void __launch_bounds__((SW_NWARP + 1 + SW_NIO) * 32, 1) k_sgm_sweep_t
 				const int bp = b == 0 ? NB - 1 : b - 1;                 // buffer of row t - 1 = buffer of row t + NB - 1
 				if (t > t_begin && !(p.dbg & 32)) flush(t - 1, bp);
 				if (!(p.dbg & 64)) fill(t + NB - 1, bp);                // into the buffer just flushed
-				if (!(p.dbg & 128)) prefetch(t + PD);
+				if (use_pf) prefetch(t + PD);
 			}
 			asm volatile("cp.async.wait_all;" ::: "memory");
 			__syncthreads();   // the last row's results are staged
