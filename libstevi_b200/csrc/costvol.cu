@@ -459,6 +459,7 @@ int32_t float_cv2d_dev(stevi_ctx* c, int mf, const View& l, const View& r, int h
 			p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[3];
 			p.keys = nullptr;
 			p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0 && out.st[3] % 4 == 0;
+			if (p.vec_store && (uintptr_t)out.p % 32 == 0 && out.st[0] % 8 == 0 && out.st[2] % 8 == 0 && out.st[3] % 8 == 0) p.vec_store = 2;
 			switch (op) {
 			case BOX_PROD: STEVI_TRY(launch_cv_box_prod(c, p, hr, 1)); break;
 			case BOX_SQ: STEVI_TRY(launch_cv_box_sq(c, p, hr, 1)); break;
@@ -581,6 +582,7 @@ int32_t float_cv_dev(stevi_ctx* c, int mf, const View& l, const View& r, int hr,
 		STEVI_CUDA(c, cudaMemsetAsync(p.keys, 0, (size_t)H * Ws * sizeof(unsigned long long), c->stream));
 	}
 	p.vec_store = out.st[1] == 1 && (uintptr_t)out.p % 16 == 0 && out.st[0] % 4 == 0 && out.st[2] % 4 == 0;
+	if (p.vec_store && (uintptr_t)out.p % 32 == 0 && out.st[0] % 8 == 0 && out.st[2] % 8 == 0) p.vec_store = 2;
 	switch (op) {
 	case BOX_PROD: STEVI_TRY(launch_cv_box_prod(c, p, hr, r2l ? 1 : -1)); break;
 	case BOX_SQ: STEVI_TRY(launch_cv_box_sq(c, p, hr, r2l ? 1 : -1)); break;

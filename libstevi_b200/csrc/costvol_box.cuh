@@ -57,7 +57,7 @@ struct BoxParams {
 	int d_first = 0;                    // disparities below this one are evaluated but not stored (2-D search: the target planes can only be shifted by whole pairs of units)
 	float Ff;                           // number of features F as float
 	float* out; int64_t o0, o1, o2;
-	int vec_store;                      // o1 == 1, 16-byte aligned rows
+	int vec_store;                      // o1 == 1 and rows aligned to 16 bytes (1) or to 32 bytes (2)
 	// optional fused winner-take-all (extractSelectedIndex, correlation_base.h:427-464): dense [H][Ws] keys, cleared to 0
 	// beforehand; key = (order-preserving bits of the score, negated for costs) << 32 | d, merged with atomicMax, so equal
 	// values resolve to the larger d = the reference's `>=` / `<=` (last extremum wins, Q5); a NaN at d = 0 "sticks"
@@ -310,7 +310,10 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 				}
 			}
 			float* dst = p.out + (int64_t)i * p.o0 + (int64_t)(d0 + q) * p.o2;
-			if (p.vec_store && j0 + 8 <= p.Ws) {
+			if (p.vec_store == 2 && j0 + 8 <= p.Ws) {   // 32-byte aligned rows: one 256-bit store per sector (sm_100a, STG.E.256)
+				asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+							 :: "l"(dst + j0), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7]) : "memory");
+			} else if (p.vec_store && j0 + 8 <= p.Ws) {
 				__stcs(reinterpret_cast<float4*>(dst + j0), make_float4(o[0], o[1], o[2], o[3]));
 				__stcs(reinterpret_cast<float4*>(dst + j0 + 4), make_float4(o[4], o[5], o[6], o[7]));
 			} else {

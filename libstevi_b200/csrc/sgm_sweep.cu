@@ -27,6 +27,7 @@
 // bits. Other penalties, 16 directions, D > 512 and volumes with strided columns take sgm_general.cu's line kernels.
 #include "common.cuh"
 #include "kernels.cuh"
+#include <cuda.h>   // CUtensorMap: the type only; cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint (no libcuda link)
 #include <cmath>
 #include <climits>
 
@@ -239,6 +240,104 @@ __global__ void __launch_bounds__(128, 2) k_sgm_sweep_h(const HSweep p) {
 					if (d0 + k < p.D && tile * CT + q >= jb && tile * CT + q < je) arow[(int64_t)k * p.a2 + (int64_t)tile * CT + q] = c[k][q];
 		}
 	}
+}
+
+// ---- horizontal paths, tiles moved by the TMA engine ---------------------------------------------------------------------------
+// The same walk as k_sgm_sweep_h<DH, 8, MODE, false>, but the tile of a warp — DH*32 disparity rows x 8 columns, 32 bytes out of
+// every one of DH*32 rows of the volume — is fetched and written back by ONE tensor-map bulk copy each (UTMALDG / UTMASTG in
+// SASS) instead of DH 256-bit accesses per lane that each cost 32 look-ups in the L1 tag stage (what bounded the kernel above).
+// The volume is described to the TMA unit as a 4-D tensor (column, lane, k, image row) with d = lane*DH + k, so that the box
+// lands in shared memory as [k][lane][8 columns]: lane l reads and writes its own 32 bytes per k with two 16-byte accesses.
+// Per warp a ring of three tiles: one being worked on (contributions replace the costs in place), one arriving, one leaving;
+// a warp and its three mbarriers are self-contained, no block-wide barrier. Requires D == 32*DH, float costs, no left / right
+// margin, 16-byte aligned strides; everything else stays with the kernel above. Measured at C2 size (Score, f32): 1.40 ms with
+// the 256-bit accesses -> 1.19 ms; loads by TMA but stores by STG.256 (the stage then frees at once, three tiles of lookahead):
+// 1.31 ms. What is left is the memory system serving 32-byte pieces of 2 x 2.1 GB at 3.6 TB/s.
+constexpr int SW_HT_STAGES = 3;
+
+__device__ __forceinline__ uint32_t hs_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ bool hs_mbar_try(uint64_t* bar, uint32_t parity) {
+	uint32_t ok;
+	asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+				 : "=r"(ok) : "r"(hs_smem(bar)), "r"(parity) : "memory");
+	return ok != 0;
+}
+
+template<int DH, int MODE>
+__global__ void __launch_bounds__(128, 2) k_sgm_sweep_h_tma(const HSweep p, const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmA) {
+	constexpr int TILE = 32 * DH * 8;   // floats per tile
+	extern __shared__ __align__(1024) float hsm[];
+	__shared__ uint64_t bars[4][SW_HT_STAGES];
+	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+	const int i = p.top + blockIdx.x * 4 + w;
+	if (i >= p.H - p.bottom) return;   // (the warps of a block never meet at a barrier)
+	float* ring = hsm + w * SW_HT_STAGES * TILE;
+	uint64_t* bar = bars[w];
+	if (lane == 0) {
+#pragma unroll
+		for (int s = 0; s < SW_HT_STAGES; s++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(hs_smem(&bar[s])) : "memory");
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncwarp();
+	const float WORST = sw_worst<MODE>();
+	const int d0 = lane * DH;
+	const int n_tiles = p.W / 8;
+	auto issue_load = [&](int tile) {   // lane 0
+		const int s = tile % SW_HT_STAGES;
+		asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(hs_smem(&bar[s])), "r"(TILE * 4) : "memory");
+		asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+					 ::"r"(hs_smem(ring + s * TILE)), "l"(&tmC), "r"(tile * 8), "r"(0), "r"(0), "r"(i), "r"(hs_smem(&bar[s])) : "memory");
+	};
+	if (lane == 0) { issue_load(0); if (n_tiles > 1) issue_load(1); }
+	float pf[DH];
+#pragma unroll
+	for (int k = 0; k < DH; k++) pf[k] = 0.f;   // previous_cost starts at 0 (sgm.h:206-208)
+	for (int tile = 0; tile < n_tiles; tile++) {
+		const int s = tile % SW_HT_STAGES;
+		float* T = ring + s * TILE + lane * 8;
+		while (!hs_mbar_try(&bar[s], (tile / SW_HT_STAGES) & 1)) {}
+		float c[DH][8];
+#pragma unroll
+		for (int k = 0; k < DH; k++) {
+			const float4 x = *reinterpret_cast<const float4*>(T + k * 256), y = *reinterpret_cast<const float4*>(T + k * 256 + 4);
+			c[k][0] = x.x; c[k][1] = x.y; c[k][2] = x.z; c[k][3] = x.w; c[k][4] = y.x; c[k][5] = y.y; c[k][6] = y.z; c[k][7] = y.w;
+		}
+#pragma unroll
+		for (int q = 0; q < 8; q++) {
+			const int j = tile * 8 + q;
+			float mx = WORST;
+#pragma unroll
+			for (int k = 0; k < DH; k++) mx = sw_better<MODE>(mx, pf[k]);
+			mx = sw_warp_best<MODE>(mx);
+			float nlo = __shfl_up_sync(0xffffffffu, pf[DH - 1], 1), nhi = __shfl_down_sync(0xffffffffu, pf[0], 1);
+			if (lane == 0) nlo = WORST;
+			if (lane == 31) nhi = WORST;
+			float cc[DH], acc[DH];
+#pragma unroll
+			for (int k = 0; k < DH; k++) { cc[k] = c[k][q]; acc[k] = 0.f; }
+			// j + d >= W (the Pout term) only concerns the last D columns
+			if (j + p.D <= p.W) sw_path<DH, MODE, false, false>(cc, pf, nlo, nhi, mx, p.P1, p.P2, p.Pout, 0, acc, false);
+			else sw_path<DH, MODE, true, false>(cc, pf, nlo, nhi, mx, p.P1, p.P2, p.Pout, p.W - j - d0, acc, false);
+#pragma unroll
+			for (int k = 0; k < DH; k++) c[k][q] = acc[k];
+		}
+#pragma unroll
+		for (int k = 0; k < DH; k++) {
+			*reinterpret_cast<float4*>(T + k * 256) = make_float4(c[k][0], c[k][1], c[k][2], c[k][3]);
+			*reinterpret_cast<float4*>(T + k * 256 + 4) = make_float4(c[k][4], c[k][5], c[k][6], c[k][7]);
+		}
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the lanes' writes, before the TMA unit reads the tile
+		__syncwarp();
+		if (lane == 0) {
+			asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3, %4}], [%5];"
+						 ::"l"(&tmA), "r"(tile * 8), "r"(0), "r"(0), "r"(i), "r"(hs_smem(ring + s * TILE)) : "memory");
+			asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+			// tile + 2 goes where tile - 1 was: its store (committed one iteration ago) must have read the tile
+			asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+			if (tile + 2 < n_tiles) issue_load(tile + 2);
+		}
+	}
+	if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // ---- vertical and diagonal paths: sheared strips -----------------------------------------------------------------------------
@@ -701,6 +800,49 @@ static int32_t launch_h(stevi_ctx* c, const HSweep& p, bool vec) {
 	return STEVI_OK;
 }
 
+// tensor map of a volume with unit column stride for the tiles of k_sgm_sweep_h_tma: dims (column, lane, k, image row), d = lane*dh + k
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+								  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+	static EncodeTiledFn fn = [] {
+		void* f = nullptr;
+		cudaDriverEntryPointQueryResult qr;
+		if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) f = nullptr;
+		(void)cudaGetLastError();
+		return reinterpret_cast<EncodeTiledFn>(f);
+	}();
+	return fn;
+}
+static bool h_tile_map(CUtensorMap* tm, const float* base, int64_t row_stride, int64_t d_stride, int H, int W, int dh) {
+	EncodeTiledFn fn = encode_tiled_fn();
+	if (!fn) return false;
+	const cuuint64_t dims[4] = {(cuuint64_t)W, 32, (cuuint64_t)dh, (cuuint64_t)H};
+	const cuuint64_t strides[3] = {(cuuint64_t)dh * d_stride * 4, (cuuint64_t)d_stride * 4, (cuuint64_t)row_stride * 4};
+	const cuuint32_t box[4] = {8, 32, (cuuint32_t)dh, 1}, es[4] = {1, 1, 1, 1};
+	// (L2 promotion 64 / 128 / 256 bytes measured: 1.40 / 1.19 / 1.35 ms against 1.21 without, at C2 size: left off)
+	return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+			  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template<int MODE>
+static int32_t launch_h_tma(stevi_ctx* c, const HSweep& p, const CUtensorMap& tmC, const CUtensorMap& tmA) {
+	const int rows = p.H - p.top - p.bottom;
+	dim3 grid(cdiv(rows, 4));
+	const int dh = p.D / 32;
+	const int smem = 4 * SW_HT_STAGES * 32 * dh * 8 * (int)sizeof(float);
+#define STEVI_HT(DH) do { \
+	STEVI_CUDA(c, cudaFuncSetAttribute((k_sgm_sweep_h_tma<DH, MODE>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+	STEVI_LAUNCH(c, (k_sgm_sweep_h_tma<DH, MODE>), grid, 128, smem, p, tmC, tmA); } while (0)
+	switch (dh) {
+	case 1: STEVI_HT(1); break;
+	case 2: STEVI_HT(2); break;
+	case 4: STEVI_HT(4); break;
+	default: STEVI_HT(8); break;
+	}
+#undef STEVI_HT
+	return STEVI_OK;
+}
+
 static size_t sweep_smem(int dh, bool has_a, bool accumulate) {
 	const size_t tile = (size_t)32 * dh * SW_TWP;
 	return ((dh <= 8 ? 3 : 2) * tile * (1 + (has_a ? 1 : 0) + (accumulate ? 1 : 0)) + (size_t)(2 * SW_NWARP + 6) * 32 * dh) * sizeof(float);
@@ -771,7 +913,18 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 	{ static const char* e = getenv("STEVI_SGM_HPF"); h.pf = e ? atoi(e) : 0; }
 	const size_t esz = dtype_size(cv.dtype);
 	const bool vec = (uintptr_t)cv.p % (8 * esz) == 0 && cv.st[0] % 8 == 0 && cv.st[2] % 8 == 0 && W % 8 == 0;
-	if (mode == SW_SCORE) STEVI_TRY((launch_h<SW_SCORE, false>(c, h, vec)));
+	// the forward walk with TMA-moved tiles where the volume allows it (see k_sgm_sweep_h_tma)
+	static const bool no_tma = getenv("STEVI_SGM_NO_TMA") != nullptr;   // measurement aid
+	CUtensorMap tmC, tmA;
+	const bool tma = !no_tma && vec && !h.c_u16 && (D == 32 || D == 64 || D == 128 || D == 256) && mg.left == 0 && mg.right == 0 &&
+					 (uintptr_t)cv.p % 16 == 0 && h_tile_map(&tmC, cv.as<float>(), cv.st[0], cv.st[2], H, W, D / 32) &&
+					 h_tile_map(&tmA, A, h.a0, h.a2, H, W4, D / 32);
+	if (tma) {
+		if (mode == SW_SCORE) STEVI_TRY((launch_h_tma<SW_SCORE>(c, h, tmC, tmA)));
+		else if (mode == SW_COST) STEVI_TRY((launch_h_tma<SW_COST>(c, h, tmC, tmA)));
+		else STEVI_TRY((launch_h_tma<SW_COST_COMPAT>(c, h, tmC, tmA)));
+	}
+	else if (mode == SW_SCORE) STEVI_TRY((launch_h<SW_SCORE, false>(c, h, vec)));
 	else if (mode == SW_COST) STEVI_TRY((launch_h<SW_COST, false>(c, h, vec)));
 	else STEVI_TRY((launch_h<SW_COST_COMPAT, false>(c, h, vec)));
 	if (corrected) {   // Right2Left is live only with the corrected start rule (Q4)

@@ -154,6 +154,29 @@ def test_sweep_non_finite_scores(api, ctx, oracle):
     assert np.array_equal(got, want, equal_nan=True)
 
 
+@pytest.mark.parametrize("shape", [(24, 72, 32), (17, 40, 64), (20, 136, 128), (12, 320, 32), (9, 264, 256)])
+def test_sweep_tma_tiles(api, ctx, oracle, shape):
+    """D == 32 * DH, W % 8 == 0, float costs, no left / right margin: the horizontal tiles travel by tensor-map bulk copies
+    (k_sgm_sweep_h_tma); Pout columns, non-finite scores, every strategy / semantics, row margins."""
+    h, w, D = shape
+    v = zncc_like_volume(h, w, D, 3 * h + w + D)
+    v[2, 5, :] = np.nan
+    v[4, w // 2, D // 3] = np.inf
+    v[5, :, 0] = -np.inf
+    for ndir in (4, 8):
+        got = api.sgmCostVolume(ref_layout(v), 0.02, 0.3, Pout=1.5, nDirections=ndir, strategy=api.SCORE, ctx=ctx)
+        assert np.array_equal(got, oracle.port.sgm(v, ndir, oracle.SCORE, 0.02, 0.3, 1.5), equal_nan=True)
+    c = (np.abs(zncc_like_volume(h, w, D, h)) * 10).astype(np.float32)
+    got = api.sgmCostVolume(ref_layout(c), 0.5, 2.0, Pout=100, nDirections=8, strategy=api.COST, ctx=ctx)
+    assert np.array_equal(got, oracle.port.sgm(c, 8, oracle.COST, 0.5, 2.0, 100))
+    got = api.sgmCostVolume(ref_layout(c), 0.5, 2.0, Pout=100, nDirections=8, strategy=api.COST, semantics=api.CORRECTED, ctx=ctx)
+    want = oracle.port.sgm_corrected(c, 8, oracle.COST, 0.5, 2.0, 100)
+    assert np.allclose(got, want, rtol=0, atol=1e-4 * max(1.0, float(np.abs(want).max())))
+    mg = (0, 2, 0, 1)   # (left, top, right, bottom): rows only
+    got = api.sgmCostVolume(ref_layout(v), 0.5, 2.0, margins=mg, Pout=3.5, nDirections=8, strategy=api.SCORE, ctx=ctx)
+    assert np.array_equal(got, oracle.port.sgm(v, 8, oracle.SCORE, 0.5, 2.0, 3.5, mg), equal_nan=True)
+
+
 def test_sweep_column_slices_and_unaligned_rows(api, ctx, oracle):
     # views whose rows are not 16-byte aligned take the scalar column tiles of the horizontal kernel
     v = zncc_like_volume(20, 64, 24, 9)
