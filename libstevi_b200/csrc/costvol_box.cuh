@@ -233,23 +233,46 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 		for (int c = 0; c < NV; c++) V[q][c] = 0.f;
 	// merge the 8 disparity groups' winners of one column and publish them: one 64-bit atomicMax per column, row and block
 	const int kslot = (threadIdx.x & 7) * BOX_KEY_PITCH + (threadIdx.x >> 3);
+	// The threads leave {best value (raw float bits) << 32 | index q of its disparity among the thread's four, -1: none, -2: the
+	// NaN at d = 0 that sticks}; the merging thread of a column walks the 8 groups in ascending d with the reference's >= / <=
+	// (a later equal value wins, -0 == +0) and converts the one winner into the ordered key.
+	constexpr unsigned long long KEY_NONE = 0x00000000FFFFFFFFull;
 	auto merge_keys = [&](int row, int buf) {
 		if (jb + (int)threadIdx.x >= p.Ws) return;
 		const unsigned long long* src = kb + buf * 8 * BOX_KEY_ROW + kslot;
-		unsigned long long key = src[0];
+		float bv = OP == BOX_PROD ? __int_as_float(0xff800000) : __int_as_float(0x7f800000);
+		int bd = -1;
+		bool stick = false;
 #pragma unroll
-		for (int g = 1; g < 8; g++) { const unsigned long long o = src[g * BOX_KEY_ROW]; key = o > key ? o : key; }
+		for (int g = 0; g < 8; g++) {
+			const unsigned long long e = src[g * BOX_KEY_ROW];
+			const float v = __uint_as_float((unsigned)(e >> 32));
+			const int q = (int)(unsigned)e;
+			if (g == 0) stick = q == -2;
+			if (q >= 0 && (OP == BOX_PROD ? (v >= bv) : (v <= bv))) { bv = v; bd = db + 4 * g + q; }
+		}
+		unsigned long long key = 0;
+		// + 0.f: -0 -> +0, the reference's comparisons see them as equal
+		if (bd >= 0) key = ((unsigned long long)wta_order_bits((OP == BOX_PROD ? bv : -bv) + 0.f) << 32) | (unsigned)bd;
+		if (stick) key = 0xFFFFFFFF00000000ull;
 		if (key) atomicMax(p.keys + (int64_t)row * p.Ws + jb + threadIdx.x, key);
 	};
 	if (WTA && !live) {
 #pragma unroll
-		for (int k = 0; k < 8; k++) { kb[dg * BOX_KEY_ROW + k * BOX_KEY_PITCH + cg] = 0; kb[(8 + dg) * BOX_KEY_ROW + k * BOX_KEY_PITCH + cg] = 0; }
+		for (int k = 0; k < 8; k++) { kb[dg * BOX_KEY_ROW + k * BOX_KEY_PITCH + cg] = KEY_NONE; kb[(8 + dg) * BOX_KEY_ROW + k * BOX_KEY_PITCH + cg] = KEY_NONE; }
 	}
 	mbar_wait(&bar_img, 0);
 	if (live)
 		for (int r = 0; r <= 2 * p.vr; r++)
 			box_accum_row<OP, NV, SIGN, true>(V, tile + r * BOX_ROW_FLOATS, sA, sB, tA, tB);
-	for (int i = i0; i < i_end; i++) {
+	// loop-invariant: which of the thread's four disparities exist and are stored, how its 8 columns leave, where row i0 starts
+	bool qok[4];
+#pragma unroll
+	for (int q = 0; q < 4; q++) qok[q] = d0 + q < p.D && d0 + q >= p.d_first;
+	const int smode = (j0 + 8 <= p.Ws) ? p.vec_store : 0;
+	float* orow = p.out + (int64_t)i0 * p.o0 + (int64_t)d0 * p.o2 + (smode ? j0 : 0);
+	const bool first_d = d0 == 0;   // only these threads can see the NaN-at-d-0 rule
+	for (int i = i0; i < i_end; i++, orow += p.o0) {
 		const int n = i - i0, slot = n % BOX_STAT_SLOTS;
 		// every warp has finished row i-1, so its ring slot can take row i + BOX_STAT_SLOTS - 1
 		__syncthreads();
@@ -280,10 +303,10 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 		unsigned nan0 = 0;
 #pragma unroll
 		for (int k = 0; k < 8; k++) { bestv[k] = OP == BOX_PROD ? __int_as_float(0xff800000) : __int_as_float(0x7f800000); bestq[k] = -1; }
+		float* dst = orow;
 #pragma unroll
-		for (int q = 0; q < 4; q++) {
-			if (d0 + q >= p.D) break;
-			if (d0 + q < p.d_first) continue;
+		for (int q = 0; q < 4; q++, dst += p.o2) {
+			if (!qok[q]) continue;
 			float o[8];
 			float h = V[q][LH - HR];
 #pragma unroll
@@ -306,33 +329,32 @@ __global__ void __launch_bounds__(BOX_THREADS, BOX_BLOCKS_PER_SM) k_cv_box(const
 				o[k] = v;
 				if (WTA) {
 					if (OP == BOX_PROD ? (v >= bestv[k]) : (v <= bestv[k])) { bestv[k] = v; bestq[k] = q; }
-					if (q == 0 && d0 == 0 && v != v) nan0 |= 1u << k;
 				}
 			}
-			float* dst = p.out + (int64_t)i * p.o0 + (int64_t)(d0 + q) * p.o2;
-			if (p.vec_store == 2 && j0 + 8 <= p.Ws) {   // 32-byte aligned rows: one 256-bit store per sector (sm_100a, STG.E.256)
+			if (WTA && q == 0 && first_d) {
+#pragma unroll
+				for (int k = 0; k < 8; k++) if (o[k] != o[k]) nan0 |= 1u << k;
+			}
+			if (smode == 2) {   // 32-byte aligned rows: one 256-bit store per sector (sm_100a, STG.E.256)
 				asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
-							 :: "l"(dst + j0), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7]) : "memory");
-			} else if (p.vec_store && j0 + 8 <= p.Ws) {
-				__stcs(reinterpret_cast<float4*>(dst + j0), make_float4(o[0], o[1], o[2], o[3]));
-				__stcs(reinterpret_cast<float4*>(dst + j0 + 4), make_float4(o[4], o[5], o[6], o[7]));
+							 :: "l"(dst), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7]) : "memory");
+			} else if (smode) {
+				__stcs(reinterpret_cast<float4*>(dst), make_float4(o[0], o[1], o[2], o[3]));
+				__stcs(reinterpret_cast<float4*>(dst + 4), make_float4(o[4], o[5], o[6], o[7]));
 			} else {
 #pragma unroll
 				for (int k = 0; k < 8; k++)
-					if (j0 + k < p.Ws) p.out[(int64_t)i * p.o0 + (int64_t)(j0 + k) * p.o1 + (int64_t)(d0 + q) * p.o2] = o[k];
+					if (j0 + k < p.Ws) dst[(int64_t)(j0 + k) * p.o1] = o[k];
 			}
 		}
 		if (WTA) {
-			unsigned long long* dstk = kb + ((n & 1) * 8 + dg) * BOX_KEY_ROW + cg;
+			if (first_d && nan0) {
 #pragma unroll
-			for (int k = 0; k < 8; k++) {
-				unsigned long long key = 0;
-				// + 0.f: -0 -> +0, the reference's comparisons see them as equal
-				if (bestq[k] >= 0)
-					key = ((unsigned long long)wta_order_bits((OP == BOX_PROD ? bestv[k] : -bestv[k]) + 0.f) << 32) | (unsigned)(d0 + bestq[k]);
-				if ((nan0 >> k) & 1u) key = 0xFFFFFFFF00000000ull;
-				dstk[k * BOX_KEY_PITCH] = key;
+				for (int k = 0; k < 8; k++) if ((nan0 >> k) & 1u) bestq[k] = -2;
 			}
+			uint2* dstk = reinterpret_cast<uint2*>(kb + ((n & 1) * 8 + dg) * BOX_KEY_ROW + cg);
+#pragma unroll
+			for (int k = 0; k < 8; k++) dstk[k * BOX_KEY_PITCH] = make_uint2((unsigned)bestq[k], __float_as_uint(bestv[k]));
 		}
 	}
 	if (WTA) {
