@@ -188,6 +188,33 @@ __device__ __forceinline__ int guided_d0(const Guided& p, int gi, int j) {
 	return p.sign * (int)roundf(id);
 }
 
+// the same split in its column part (once per thread) and its row part (once per pixel): identical operations, identical result
+struct GuideCol { int h0, h1; float ah, bh; };
+__device__ __forceinline__ GuideCol guided_col(const Guided& p, int j) {
+	const float h_pos = __fdiv_rn((float)(j * (p.wg - 1)), (float)(p.Ws - 1));
+	GuideCol c;
+	c.h0 = (int)floorf(h_pos); c.h1 = (int)ceilf(h_pos);
+	if (c.h0 == c.h1) c.h1 += 1;
+	if (c.h1 == p.wg) { c.h0 -= 1; c.h1 -= 1; }
+	c.ah = __fsub_rn(h_pos, (float)c.h0); c.bh = __fsub_rn((float)c.h1, h_pos);
+	return c;
+}
+__device__ __forceinline__ int guided_d0_row(const Guided& p, int gi, const GuideCol& c) {
+	const float v_pos = __fdiv_rn((float)(gi * (p.hg - 1)), (float)(p.H - 1));
+	int v0 = (int)floorf(v_pos), v1 = (int)ceilf(v_pos);
+	if (v0 == v1) v1 += 1;
+	if (v1 == p.hg) { v0 -= 1; v1 -= 1; }
+	const float av = __fsub_rn(v_pos, (float)v0), bv = __fsub_rn((float)v1, v_pos);
+	const int64_t gr0 = (int64_t)(v0 - p.guide_row0) * p.g0, gr1 = (int64_t)(v1 - p.guide_row0) * p.g0;
+	float id = 0.f;
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, c.ah), (float)p.guide[gr1 + c.h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, c.ah), (float)p.guide[gr0 + c.h1 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(av, c.bh), (float)p.guide[gr1 + c.h0 * p.g1]));
+	id = __fadd_rn(id, __fmul_rn(__fmul_rn(bv, c.bh), (float)p.guide[gr0 + c.h0 * p.g1]));
+	id = __fmul_rn(id, 2.f);
+	return p.sign * (int)roundf(id);
+}
+
 // computeGuidedCV on caller-supplied feature volumes — the reference's own signature (hierarchical.h:73-233): the candidates and
 // the re-centred window are comparisons of the source vector with target vectors (zeros outside the target image, :170),
 // accumulated over the channels in the reference's order.
@@ -266,9 +293,10 @@ __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 	// guide disparities of this thread's pixels, and the span of the block's candidate columns
 	int d0r[GT_ROWS];
 	int lo = 0x7fffffff, hi = -0x7fffffff;
+	const GuideCol gcol = guided_col(p, live ? j : 0);
 #pragma unroll
 	for (int rr = 0; rr < GT_ROWS; rr++) {
-		d0r[rr] = (live && rr < n_out) ? guided_d0(p, gi0 + rr, j) : 0;
+		d0r[rr] = (live && rr < n_out) ? guided_d0_row(p, gi0 + rr, gcol) : 0;
 		if (live && rr < n_out) { lo = min(lo, j + d0r[rr] - 2 * R); hi = max(hi, j + d0r[rr] - 2 * R); }
 	}
 #pragma unroll
@@ -362,6 +390,26 @@ __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 				}
 			}
 		}
+		if (OP == BOX_PROD && TILED) {
+			// branch-free: the 4R+1 candidates of a pixel are finished as straight-line code (ncu, round 2: this part was 575 of the
+			// 1420 instructions per pixel, a third of it branches around the IEEE division and the inside / flat-window cases). The
+			// quotient is num * rcp(den) (2 ulp; the volume is tolerance-matched at 1e-4); the cases that decide NaN
+			// and 0 are the same exact tests as before.
+			const float nan = __int_as_float(0x7fc00000);
+			const float Fms = p.zero_mean ? F * ms : 0.f;
+			const bool norm = p.normalized != 0, ns0 = norm && ns == 0.f;
+			const float ns_eff = norm ? ns : 1.f;
+			const float outside_v = ns0 ? nan : 0.f;   // NaN source features times a zero target vector (Q6)
+#pragma unroll
+			for (int e = 0; e < NC; e++) {
+				const float mt = smt[tstat0 + e], nt = snt[tstat0 + e];
+				const float num = fmaf(-Fms, mt, acc[e]);
+				const float den = ns_eff * (norm ? nt : 1.f);
+				float v = __fdividef(num, den);
+				v = (ns0 || (norm && nt == 0.f)) ? nan : v;
+				acc[e] = ((unsigned)(jt0 + e) < (unsigned)p.Wt) ? v : outside_v;
+			}
+		} else {
 #pragma unroll
 		for (int e = 0; e < NC; e++) {
 			const int jt = jt0 + e;
@@ -376,6 +424,7 @@ __global__ void __launch_bounds__(128) k_guided_cv_tile(const Guided p) {
 				} else if (p.normalized && ns == 0.f) v = __int_as_float(0x7fc00000);
 			} else v = inside ? acc[e] : zacc;
 			acc[e] = v;
+		}
 		}
 		float score = p.cost ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
 		int best = R;   // index of the candidate at d0 (hierarchical.h: d_r starts at d0 and moves only on a strict improvement)
