@@ -149,7 +149,10 @@ __global__ void __launch_bounds__(128) k_window_stats(const StatsParams p) {
 	float acc[PX];
 #pragma unroll
 	for (int q = 0; q < PX; q++) acc[q] = 0.f;
-	if (p.op != BOX_PROD || p.normalized) {
+	// the accumulation is decided once, outside the unrolled loops (as per-element selects it was 49 of 270 instructions per pixel);
+	// without zero mean, mean[] is 0 and f - 0 is f, bit for bit
+	const int acc_mode = p.op == BOX_PROD ? (p.normalized ? 1 : 0) : (p.op == BOX_SQ ? 1 : 2);   // 1: squares, 2: absolute values
+	if (acc_mode == 1) {
 		for (int k = 0; k < vs; k++) {
 			float r[16];
 			load_units<4>(r, base + k * p.pitch, oA, oB);
@@ -157,10 +160,18 @@ __global__ void __launch_bounds__(128) k_window_stats(const StatsParams p) {
 			for (int q = 0; q < PX; q++)
 #pragma unroll
 				for (int l = 0; l < HS; l++) {
-					float f = r[4 - HR + q + l];
-					if (p.zero_mean) f = __fsub_rn(f, mean[q]);
-					acc[q] = stats_accum(p.op, p.normalized, acc[q], f);
+					const float f = __fsub_rn(r[4 - HR + q + l], mean[q]);
+					acc[q] = __fmaf_rn(f, f, acc[q]);
 				}
+		}
+	} else if (acc_mode == 2) {
+		for (int k = 0; k < vs; k++) {
+			float r[16];
+			load_units<4>(r, base + k * p.pitch, oA, oB);
+#pragma unroll
+			for (int q = 0; q < PX; q++)
+#pragma unroll
+				for (int l = 0; l < HS; l++) acc[q] = __fadd_rn(acc[q], fabsf(__fsub_rn(r[4 - HR + q + l], mean[q])));
 		}
 	}
 	float a[PX], b[PX];
