@@ -76,6 +76,7 @@ struct HSweep {
 	int H, W, D, top, bottom, left, right;
 	float P1, P2, Pout;
 	int pf;   // L2 prefetch distance in tiles (0: none)
+	int* fault;   // ctx fault flag: raised instead of waiting for ever on a tile that does not arrive
 };
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -254,6 +255,7 @@ __global__ void __launch_bounds__(128, 2) k_sgm_sweep_h(const HSweep p) {
 // the 256-bit accesses -> 1.19 ms; loads by TMA but stores by STG.256 (the stage then frees at once, three tiles of lookahead):
 // 1.31 ms. What is left is the memory system serving 32-byte pieces of 2 x 2.1 GB at 3.6 TB/s.
 constexpr int SW_HT_STAGES = 3;
+constexpr int SW_SPIN_LIMIT = 1 << 22;
 
 __device__ __forceinline__ uint32_t hs_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ bool hs_mbar_try(uint64_t* bar, uint32_t parity) {
@@ -295,7 +297,8 @@ __global__ void __launch_bounds__(128, 2) k_sgm_sweep_h_tma(const HSweep p, cons
 	for (int tile = 0; tile < n_tiles; tile++) {
 		const int s = tile % SW_HT_STAGES;
 		float* T = ring + s * TILE + lane * 8;
-		while (!hs_mbar_try(&bar[s], (tile / SW_HT_STAGES) & 1)) {}
+		for (int spins = 0; !hs_mbar_try(&bar[s], (tile / SW_HT_STAGES) & 1); spins++)
+			if (spins > SW_SPIN_LIMIT) { *p.fault = 1; break; }   // (bounded like the strip hand-over: a flagged wrong result, not a hung device)
 		float c[DH][8];
 #pragma unroll
 		for (int k = 0; k < DH; k++) {
@@ -345,7 +348,6 @@ __global__ void __launch_bounds__(128, 2) k_sgm_sweep_h_tma(const HSweep p, cons
 constexpr int SW_TW = 16;          // columns per strip = warps per block (a warp per column)
 constexpr int SW_NWARP = SW_TW;
 constexpr int SW_TWP = SW_TW + 1;  // tile pitch (odd: a warp reading one column over 32 rows touches 32 banks)
-constexpr int SW_SPIN_LIMIT = 1 << 22;
 
 struct VSweep {
 	const void* C; int64_t c0, c2; int c_u16;
@@ -911,6 +913,7 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 	h.H = H; h.W = W; h.D = D; h.top = mg.top; h.bottom = mg.bottom; h.left = mg.left; h.right = mg.right;
 	h.P1 = P1; h.P2 = P2; h.Pout = Pout;
 	{ static const char* e = getenv("STEVI_SGM_HPF"); h.pf = e ? atoi(e) : 0; }
+	h.fault = c->fault_dev;
 	const size_t esz = dtype_size(cv.dtype);
 	const bool vec = (uintptr_t)cv.p % (8 * esz) == 0 && cv.st[0] % 8 == 0 && cv.st[2] % 8 == 0 && W % 8 == 0;
 	// the forward walk with TMA-moved tiles where the volume allows it (see k_sgm_sweep_h_tma)
