@@ -204,6 +204,7 @@ struct HamParams {
 	void* out; int64_t o0, o1, o2;            // (row, column, disparity) strides of the cost volume
 	int32_t* gmap; int pout;
 	const int32_t* T; const int32_t* R; unsigned long long* keys;   // MODE 2: path sums in, winner keys out
+	uint32_t* kin; uint32_t* kout;            // MODE 4: per pixel min over d of cost * 8192 + (8191 - d), d with j + d < W / >= W
 	int round;                                // Q2: round target words through float
 	int P;                                    // pitch of one of the 8 interleaved shared-memory lanes
 };
@@ -244,6 +245,11 @@ template<> __device__ __forceinline__ void store8<float>(float* p, const uint32_
 // over the disparity chunks through the same 64-bit keys as k_sgm_apply_rows. MODE 3 is MODE 2 with the running arg-min
 // packed in one word, (S + T) * 8192 + (8191 - d), so that a cell costs one multiply-add and one min (the host picks it
 // when |S + T| < 2^17; D <= 8192 on this path; T is constant along d and re-enters at the end).
+// MODE 4 (round 2c) makes the second pass unnecessary: S is, per pixel, an increasing affine map of the cost plus one constant
+// on the disparities with j + d >= W, so its arg-min under `<=` (last minimum wins) is decided by two numbers per pixel — the
+// smallest cost, with its LARGEST disparity, among the d with j + d < W and among those with j + d >= W. One pass keeps both as
+// cost * 8192 + (8191 - d) minima; g follows from them, and after the path sums a thread per pixel picks the winner
+// (sgm.cu: k_keys_to_gmap, k_keys_to_disp).
 template<int NW, int SIGN, typename TO, bool VEC, bool EMIT_G, int MODE = 0>
 __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	extern __shared__ uint32_t sm[];
@@ -299,7 +305,12 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	// the plain minimum of the costs and double it at the end
 	const bool edge = (EMIT_G || MODE >= 2) && (j + 7 + d0 + dn - 1 >= p.Ws);
 	int r1[8], rp[8], tneg[8], best[8], bd[8];
-	if (MODE >= 2) {
+	uint32_t kin[8], kout[8];
+	if (MODE == 4) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) kin[k] = kout[k] = 0xffffffffu;
+	}
+	if (MODE == 2 || MODE == 3) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) {
 			const bool in = j + k < p.Ws;
@@ -342,6 +353,16 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 							int key = r1[k] * (int)cst[k] + inv;
 							if (EDGE) key += (j + k + d >= p.Ws) ? rp[k] : 0;
 							best[k] = min(best[k], key);
+						}
+					}
+					if (MODE == 4) {
+						const int d = d0 + 8 * gr + u;
+						const uint32_t inv = 8191u - (uint32_t)d;
+#pragma unroll
+						for (int k = 0; k < 8; k++) {
+							const uint32_t key = cst[k] * 8192u + inv;
+							if (EDGE) { if (j + k + d >= p.Ws) kout[k] = min(kout[k], key); else kin[k] = min(kin[k], key); }
+							else kin[k] = min(kin[k], key);
 						}
 					}
 					if (MODE == 2) {
@@ -391,7 +412,17 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) { bd[k] = 8191 - (best[k] & 8191); best[k] = (best[k] >> 13) + tneg[k]; }
 	}
-	if (MODE >= 2) {
+	if (MODE == 4) {
+#pragma unroll
+		for (int k = 0; k < 8; k++) if (j + k < p.Ws) {
+			const int64_t o = (int64_t)i * p.Ws + j + k;
+			if (gridDim.z > 1) {   // the host pre-filled both maps with ones
+				atomicMin(p.kin + o, kin[k]);
+				if (kout[k] != 0xffffffffu) atomicMin(p.kout + o, kout[k]);
+			} else { p.kin[o] = kin[k]; p.kout[o] = kout[k]; }
+		}
+	}
+	if (MODE == 2 || MODE == 3) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) if (j + k < p.Ws) {
 			const unsigned long long key = ((unsigned long long)((uint32_t)best[k] ^ 0x80000000u) << 32) | (0xffffffffu - (uint32_t)bd[k]);
@@ -466,6 +497,10 @@ static int32_t hamming_rows_plan(stevi_ctx* c, HamParams& p, dim3& grid, size_t&
 	while ((smem = plan(dchunk, P)) > 48 * 1024 && dchunk > 32) dchunk = std::max(32, (dchunk / 2 + 7) / 8 * 8);
 	if (p.gmap && dchunk < p.D) // chunks merge their minima with atomicMin
 		STEVI_CUDA(c, cudaMemsetAsync(p.gmap, 0x7f, (size_t)p.H * p.Ws * sizeof(int32_t), c->stream));
+	if (p.kin && dchunk < p.D) {
+		STEVI_CUDA(c, cudaMemsetAsync(p.kin, 0xff, (size_t)p.H * p.Ws * sizeof(uint32_t), c->stream));
+		STEVI_CUDA(c, cudaMemsetAsync(p.kout, 0xff, (size_t)p.H * p.Ws * sizeof(uint32_t), c->stream));
+	}
 	p.dchunk = dchunk;
 	p.P = P;
 	grid = dim3(xb, p.H, cdiv(p.D, dchunk));
@@ -508,7 +543,7 @@ static int32_t ham_params(stevi_ctx* c, const HamSource& h, HamParams& p) {
 	p.H = src.shape[0]; p.Ws = src.shape[1]; p.Wt = tgt.shape[1]; p.D = h.D; p.dchunk = h.D;
 	p.n_words = std::min(h.n_cmp, src.shape[2]);
 	p.out = nullptr; p.o0 = p.o2 = 0; p.o1 = 1;
-	p.gmap = nullptr; p.pout = 0; p.T = p.R = nullptr; p.keys = nullptr; p.round = h.round ? 1 : 0; p.P = 0;
+	p.gmap = nullptr; p.pout = 0; p.T = p.R = nullptr; p.keys = nullptr; p.kin = p.kout = nullptr; p.round = h.round ? 1 : 0; p.P = 0;
 	return STEVI_OK;
 }
 
@@ -541,6 +576,13 @@ int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int po
 	return hamming_fused_launch<1>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
 }
 
+int32_t hamming_minkeys_dev(stevi_ctx* c, const HamSource& h, uint32_t* kin, uint32_t* kout) {
+	HamParams p;
+	STEVI_TRY(ham_params(c, h, p));
+	p.kin = kin; p.kout = kout;
+	return hamming_fused_launch<4>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
+}
+
 int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, int r_max,
 							unsigned long long* keys) {
 	HamParams p;
@@ -570,7 +612,7 @@ int32_t hamming_cv_dev(stevi_ctx* c, const View& fl, const View& fr, int n_cmp, 
 	p.n_words = std::min(n_cmp, src.shape[2]);
 	p.out = out.p; p.o0 = out.st[0]; p.o1 = out.st[1]; p.o2 = out.st[2];
 	p.gmap = gmap; p.pout = pout_i; p.round = round_target ? 1 : 0; p.P = 0;
-	p.T = p.R = nullptr; p.keys = nullptr;
+	p.T = p.R = nullptr; p.keys = nullptr; p.kin = p.kout = nullptr;
 	if (out.ndim != 3 || out.shape[0] != p.H || out.shape[1] != p.Ws || out.shape[2] != D)
 		return fail(c, STEVI_E_SHAPE, "hamming: out must be (%d,%d,%d)", p.H, p.Ws, D);
 	if (p.H == 0 || p.Ws == 0 || D == 0) return STEVI_OK;

@@ -403,6 +403,40 @@ __global__ void __launch_bounds__(256) k_wta_decode_keys(const unsigned long lon
 	out[i * o0 + j * o1] = sign * d + offset;
 }
 
+// Disparity-only census + SGM in ONE pass over the costs (round 2c). With the collapsed evaluation S(d) = (1+R)*C(d) + R*pout*[j+d >= W] - T,
+// 1 + R >= 1, so on each side of the column W - j the order of S is the order of C: the winner under the reference's `<=` scan (last
+// minimum wins, correlation_base.h:446) is the largest-d minimum of C on one of the two sides, and a tie between the sides goes
+// to the far side (its disparities are the larger ones). The Hamming pass leaves, per pixel, kin / kout = min over the d of a side of
+// C*8192 + (8191 - d) (0xffffffff: the side is empty); g = min_d (2*C + pout*[j+d >= W]) follows from the same two numbers.
+__global__ void __launch_bounds__(256) k_keys_to_gmap(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ kout, int n, int pout,
+													  int32_t* __restrict__ g) {
+	const int k = blockIdx.x * 256 + threadIdx.x;
+	if (k >= n) return;
+	const uint32_t a = kin[k], b = kout[k];
+	int v = 0x7fffffff;
+	if (a != 0xffffffffu) v = 2 * (int)(a >> 13);
+	if (b != 0xffffffffu) v = min(v, 2 * (int)(b >> 13) + pout);
+	g[k] = v;
+}
+
+__global__ void __launch_bounds__(256) k_keys_to_disp(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ kout,
+													  const int32_t* __restrict__ T, const int32_t* __restrict__ R, int H, int W, int pout,
+													  int sign, int offset, int32_t* __restrict__ out, int64_t o0, int64_t o1) {
+	const int j = blockIdx.x * 256 + threadIdx.x;
+	const int i = blockIdx.y;
+	if (j >= W) return;
+	const int64_t k = (int64_t)i * W + j;
+	const uint32_t a = kin[k], b = kout[k];
+	const int r = R[k], t = T[k];
+	int d = 0;   // (no disparity at all cannot happen: d = 0 always lies on the near side)
+	if (a != 0xffffffffu) d = 8191 - (int)(a & 8191u);
+	if (b != 0xffffffffu) {
+		const int s_out = (1 + r) * (int)(b >> 13) + r * pout - t;
+		if (a == 0xffffffffu || s_out <= (1 + r) * (int)(a >> 13) - t) d = 8191 - (int)(b & 8191u);
+	}
+	out[i * o0 + j * o1] = sign * d + offset;
+}
+
 // any strides: one thread per pixel
 __global__ void __launch_bounds__(128) k_sgm_apply_generic(const uint16_t* __restrict__ cv, int64_t c0, int64_t c1, int64_t cd,
 														   float* __restrict__ S, int64_t s0, int64_t s1, int64_t sd,
@@ -557,9 +591,25 @@ int32_t sgm_census_disparity_dev(stevi_ctx* c, const HamSource& h, int ndir, int
 	const bool r2l = h.direction == STEVI_RIGHT_TO_LEFT;
 	const int H = h.fl.shape[0], W = r2l ? h.fr.shape[1] : h.fl.shape[1];
 	const size_t npix = (size_t)H * W;
-	// pass 1: g(p) = min_d (2*C + pout*[j+d >= W]); the costs live in registers only
+	static const bool two_pass = getenv("STEVI_DISP_TWO_PASS") != nullptr;   // measurement aid: the round-2 form (costs evaluated twice)
 	int32_t* g = nullptr;
 	STEVI_TRY(arena_alloc_t(c, npix, &g));
+	if (!two_pass && npix < (size_t)1 << 31) {
+		// one pass over the costs (in registers only): the two side minima per pixel; g and, after the path sums, the winner follow
+		uint32_t *kin = nullptr, *kout = nullptr;
+		STEVI_TRY(arena_alloc_t(c, npix, &kin));
+		STEVI_TRY(arena_alloc_t(c, npix, &kout));
+		STEVI_TRY(hamming_minkeys_dev(c, h, kin, kout));
+		STEVI_LAUNCH(c, k_keys_to_gmap, dim3(cdiv((int)npix, 256)), 256, 0, kin, kout, (int)npix, pout, g);
+		int32_t *T = nullptr, *R = nullptr;
+		const int32_t s = collapsed_sums(c, g, H, W, ndir, pout, mg, max_cost, &T, &R);
+		if (s == STEVI_FALLBACK) return STEVI_NOT_FUSED;
+		STEVI_TRY(s);
+		dim3 gd(cdiv(W, 256), H);
+		STEVI_LAUNCH(c, k_keys_to_disp, gd, 256, 0, kin, kout, T, R, H, W, pout, wta.sign, wta.offset, wta.out.as<int32_t>(), wta.out.st[0], wta.out.st[1]);
+		return STEVI_OK;
+	}
+	// pass 1: g(p) = min_d (2*C + pout*[j+d >= W]); the costs live in registers only
 	STEVI_TRY(hamming_gmap_dev(c, h, g, pout));
 	int32_t *T = nullptr, *R = nullptr;
 	const int32_t s = collapsed_sums(c, g, H, W, ndir, pout, mg, max_cost, &T, &R);
