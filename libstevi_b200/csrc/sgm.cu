@@ -186,12 +186,13 @@ __device__ __forceinline__ bool sgm_start_live(int start_pos, int corrected) { r
 // segment long (34 rows at 1080p) instead of the image height; integer arithmetic, so the split changes nothing.
 constexpr int SWEEP_SEGS = 32;
 
-__global__ void __launch_bounds__(32 * SWEEP_SEGS) k_sgm_pathsum_sweep(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
-																		int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+// (bx, by: the block's place in the grid of the stand-alone launch; the fused launch below hands them in)
+__device__ __forceinline__ void pathsum_sweep_body(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+												   int32_t* __restrict__ max_abs_m, const SgmGeom& geom, int bx, int by) {
 	__shared__ int seg_sum[SWEEP_SEGS][32];
 	__shared__ int seg_cnt[SWEEP_SEGS][32];
 	const int sweep_dirs[6] = {0, 1, 4, 5, 6, 7};
-	const int dir = sweep_dirs[blockIdx.y];
+	const int dir = sweep_dirs[by];
 	const int sv = c_sgm_steps[dir][0], sh = c_sgm_steps[dir][2];
 	const bool col_live = sgm_start_live(sgm_start_pos(sv, sv), geom.corrected);
 	const bool row_live = sh != 0 && sgm_start_live(sgm_start_pos(sh, sh), geom.corrected);
@@ -199,7 +200,7 @@ __global__ void __launch_bounds__(32 * SWEEP_SEGS) k_sgm_pathsum_sweep(const int
 	if (nrows <= 0 || ncols <= 0 || (!col_live && !row_live)) return;
 	const int nlines = ncols + (sh != 0 ? nrows - 1 : 0);
 	const int lane = threadIdx.x & 31, seg = threadIdx.x >> 5;
-	const int t = blockIdx.x * 32 + lane;
+	const int t = bx * 32 + lane;
 	const int jlo = geom.left, jhi = geom.W - geom.right - 1;
 	// k counts rows in traversal order; the line sits on column j0 + sh*k and lives on rows kf <= k < kl
 	int j0 = 0, kf = 0x7fffffff, kl = 0, w = 0;
@@ -267,14 +268,19 @@ __global__ void __launch_bounds__(32 * SWEEP_SEGS) k_sgm_pathsum_sweep(const int
 	if (lane == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
 }
 
-__global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
-														  int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
-	const int dir = 2 + blockIdx.y; // Left2Right, Right2Left
+__global__ void __launch_bounds__(32 * SWEEP_SEGS) k_sgm_pathsum_sweep(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+																		int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+	pathsum_sweep_body(g, T, R, max_abs_m, geom, blockIdx.x, blockIdx.y);
+}
+
+// row: the warp's row inside the margin rectangle; by: 0 Left2Right, 1 Right2Left
+__device__ __forceinline__ void pathsum_rows_body(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+												  int32_t* __restrict__ max_abs_m, const SgmGeom& geom, int row, int by) {
+	const int dir = 2 + by; // Left2Right, Right2Left
 	const int sh = c_sgm_steps[dir][2];
 	if (!sgm_start_live(sgm_start_pos(sh, sh), geom.corrected)) return;
 	const int nrows = geom.H - geom.top - geom.bottom, ncols = geom.W - geom.left - geom.right;
 	const int lane = threadIdx.x & 31;
-	const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
 	if (row >= nrows || ncols <= 0) return;
 	const int64_t base = (int64_t)(geom.top + row) * geom.W;
 	int carry = 0, mabs = 0;
@@ -307,6 +313,25 @@ __global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restr
 	}
 	mabs = __reduce_max_sync(0xffffffffu, mabs);
 	if (lane == 0 && mabs > 0) atomicMax(max_abs_m, mabs);
+}
+
+__global__ void __launch_bounds__(128) k_sgm_pathsum_rows(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+														  int32_t* __restrict__ max_abs_m, const SgmGeom geom) {
+	pathsum_rows_body(g, T, R, max_abs_m, geom, blockIdx.x * 4 + (threadIdx.x >> 5), blockIdx.y);
+}
+
+// Both in one launch (round 2c): the row walks are latency-bound chains (issue slots 19 % busy, 22 us by themselves at 1080p) and the
+// sweeps are not; side by side the walks hide behind the sweeps. The row blocks come first in the grid so that they start first.
+__global__ void __launch_bounds__(32 * SWEEP_SEGS) k_sgm_pathsum_both(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
+																	   int32_t* __restrict__ max_abs_m, const SgmGeom geom, int n_rows_x, int n_rows_blocks,
+																	   int n_sweep_x) {
+	int b = blockIdx.x;
+	if (b < n_rows_blocks) {   // (warp-uniform; no barrier on this side)
+		pathsum_rows_body(g, T, R, max_abs_m, geom, (b % n_rows_x) * SWEEP_SEGS + (threadIdx.x >> 5), b / n_rows_x);
+		return;
+	}
+	b -= n_rows_blocks;
+	pathsum_sweep_body(g, T, R, max_abs_m, geom, b % n_sweep_x, b / n_sweep_x);
 }
 
 // S = (1+R)*C + R*pout*[j+d >= W] - T on the reference's [H][D][W] layout (column stride 1 in and out): a thread owns 4
@@ -492,10 +517,17 @@ static int32_t collapsed_sums(stevi_ctx* c, const int32_t* g, int H, int W, int 
 	{
 		const int nrows = H - mg.top - mg.bottom;
 		dim3 gsweep(cdiv(H + W, 32), ndir == 4 ? 2 : 6);
-		STEVI_LAUNCH(c, k_sgm_pathsum_sweep, gsweep, 32 * SWEEP_SEGS, 0, g, T, R, d_max, geom);
-		if (nrows > 0) {
-			dim3 grows(cdiv(nrows, 4), 2);
-			STEVI_LAUNCH(c, k_sgm_pathsum_rows, grows, 128, 0, g, T, R, d_max, geom);
+		static const bool separate = getenv("STEVI_PATHSUM_SEPARATE") != nullptr;   // measurement aid: the two launches of round 2
+		if (nrows > 0 && !separate) {
+			const int n_rows_x = cdiv(nrows, SWEEP_SEGS), n_rows_blocks = 2 * n_rows_x;
+			STEVI_LAUNCH(c, k_sgm_pathsum_both, dim3(n_rows_blocks + gsweep.x * gsweep.y), 32 * SWEEP_SEGS, 0, g, T, R, d_max, geom, n_rows_x,
+						 n_rows_blocks, (int)gsweep.x);
+		} else {
+			STEVI_LAUNCH(c, k_sgm_pathsum_sweep, gsweep, 32 * SWEEP_SEGS, 0, g, T, R, d_max, geom);
+			if (nrows > 0) {
+				dim3 grows(cdiv(nrows, 4), 2);
+				STEVI_LAUNCH(c, k_sgm_pathsum_rows, grows, 128, 0, g, T, R, d_max, geom);
+			}
 		}
 		if (ndir == 16) {
 			dim3 gwalk(cdiv(H + W, 128), 8);
