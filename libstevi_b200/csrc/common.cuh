@@ -44,7 +44,10 @@ struct stevi_ctx {
 	// disparity maps going to host memory travel as the narrowest exact type (u8 / u16) and are widened into the caller's
 	// int32 array by the host once the copy has landed (ctx.cu: Stager::out_index): tasks waiting for that, and the
 	// page-locked staging buffers they use (a free list; a buffer is busy from its call to the synchronisation that widens it)
-	struct Widen { void* staged; int32_t* dst; size_t n; int bytes_per; int sign, offset; size_t slot; };
+	// (round 2c: the widening is done by a small pool of worker threads; a task is handed to them by the first API call of the
+	// process that finds its copy landed (an event after the copy, polled on entry to every call), at the latest by the
+	// synchronising call, which only waits for tasks that are not finished yet)
+	struct Widen { void* staged; int32_t* dst; size_t n; int bytes_per; int sign, offset; size_t slot; void* task; };
 	std::vector<Widen> widen;
 	struct Pinned { void* p; size_t cap; bool busy; };
 	std::vector<Pinned> pinned;
@@ -138,10 +141,14 @@ private:
 	bool any_host_ = false;
 };
 
+// narrow maps of ANY context of this device whose copies have landed go to the widening workers (ctx.cu); cheap when none is pending
+void poll_landed_maps(int device);
+
 inline int32_t begin_call(stevi_ctx* c) {
 	if (!c) return STEVI_E_ARG;
 	cudaError_t e = cudaSetDevice(c->device);
 	if (e != cudaSuccess) return fail(c, STEVI_E_CUDA, "cudaSetDevice(%d): %s", c->device, cudaGetErrorString(e));
+	poll_landed_maps(c->device);
 	return arena_reset(c);
 }
 

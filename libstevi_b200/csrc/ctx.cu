@@ -1,6 +1,11 @@
 // Context, workspace arena and host-operand staging for the C ABI (include/stevi_b200/c_api.h).
 #include "common.cuh"
 #include <immintrin.h>
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
 
 namespace stevi {
 
@@ -168,16 +173,92 @@ static void widen_range(const TN* src, int32_t* dst, long n, int sign, int offse
 	_mm_sfence();
 }
 
+// ---- widening off the caller's thread ----------------------------------------------------------------------------------------
+// A process-wide pool of host_threads() workers (they inherit the affinity mask of the thread that makes the first call, i.e. the
+// rank's core slice). A task is one narrow map; it is cut into chunks, one queue entry each. Who makes the entries: see
+// poll_landed_maps below.
+struct WidenTask {
+	const void* staged; int32_t* dst; long n; int bytes_per, sign, offset, chunks;
+	cudaEvent_t landed; int device;   // recorded after the device-to-host copy
+	std::atomic<int> remaining;
+	std::atomic<int> submitted;   // handed to the pool once, by the host function or (if the stream never ran it) by the synchronising call
+};
+
+class WidenPool {
+public:
+	static WidenPool& get() { static WidenPool* p = new WidenPool(); return *p; }   // never destroyed: the workers outlive static teardown
+	void submit(WidenTask* t) {
+		{
+			std::lock_guard<std::mutex> lk(m_);
+			for (int k = 0; k < t->chunks; k++) q_.push_back({t, k});
+		}
+		if (t->chunks > 1) cv_.notify_all(); else cv_.notify_one();
+	}
+private:
+	WidenPool() {
+		const int n = host_threads();
+		for (int k = 0; k < n; k++) std::thread([this] { run(); }).detach();
+	}
+	void run() {
+		for (;;) {
+			std::pair<WidenTask*, int> job;
+			{
+				std::unique_lock<std::mutex> lk(m_);
+				cv_.wait(lk, [this] { return !q_.empty(); });
+				job = q_.front();
+				q_.pop_front();
+			}
+			WidenTask* t = job.first;
+			const long a = t->n * job.second / t->chunks / 8 * 8, b = job.second + 1 == t->chunks ? t->n : t->n * (job.second + 1) / t->chunks / 8 * 8;
+			if (t->bytes_per == 1) widen_range(static_cast<const uint8_t*>(t->staged) + a, t->dst + a, b - a, t->sign, t->offset);
+			else widen_range(static_cast<const uint16_t*>(t->staged) + a, t->dst + a, b - a, t->sign, t->offset);
+			t->remaining.fetch_sub(1, std::memory_order_release);
+		}
+	}
+	std::mutex m_;
+	std::condition_variable cv_;
+	std::deque<std::pair<WidenTask*, int>> q_;
+};
+
+static void hand_over_once(WidenTask* t) { if (t->submitted.exchange(1) == 0) WidenPool::get().submit(t); }
+
+// Who notices that a copy has landed: measured at C2, 4 pairs in flight (ms per pair, same box): OpenMP region in the synchronising
+// call 0.33; a host function in the stream (cudaLaunchHostFunc) 0.52 — the stream stalls around it; the pool fed by the
+// synchronising call 0.28; and, built here, every API call of the process polls the events of the pending maps of its device on
+// entry, so that the workers widen pair k while the calling thread enqueues pair k+1.
+static std::mutex g_pending_m;
+static std::vector<WidenTask*> g_pending;
+static std::atomic<int> g_pending_n{0};
+
+void poll_landed_maps(int device) {
+	if (g_pending_n.load(std::memory_order_relaxed) == 0) return;   // (a miss only delays the hand-over to the next call)
+	std::lock_guard<std::mutex> lk(g_pending_m);
+	for (size_t k = 0; k < g_pending.size();) {
+		WidenTask* t = g_pending[k];
+		if (t->device == device && cudaEventQuery(t->landed) == cudaSuccess) {
+			hand_over_once(t);
+			g_pending[k] = g_pending.back();
+			g_pending.pop_back();
+			g_pending_n.fetch_sub(1, std::memory_order_relaxed);
+		} else k++;
+	}
+	(void)cudaGetLastError();   // cudaErrorNotReady is not an error
+}
+
+// after a stream synchronisation: every host function of the stream has run, i.e. every task has been handed to the pool; wait
+// for the ones still being widened
 void finish_host(stevi_ctx* c) {
 	for (auto& w : c->widen) {
-		const long n = (long)w.n;
-		const int nt = (int)std::max(1L, std::min((long)host_threads(), n / 65536));
-#pragma omp parallel for num_threads(nt) schedule(static)
-		for (int t = 0; t < nt; t++) {
-			const long a = n * t / nt / 8 * 8, b = t + 1 == nt ? n : n * (t + 1) / nt / 8 * 8;
-			if (w.bytes_per == 1) widen_range(static_cast<const uint8_t*>(w.staged) + a, w.dst + a, b - a, w.sign, w.offset);
-			else widen_range(static_cast<const uint16_t*>(w.staged) + a, w.dst + a, b - a, w.sign, w.offset);
+		WidenTask* t = static_cast<WidenTask*>(w.task);
+		{
+			std::lock_guard<std::mutex> lk(g_pending_m);
+			for (size_t k = 0; k < g_pending.size(); k++)
+				if (g_pending[k] == t) { g_pending[k] = g_pending.back(); g_pending.pop_back(); g_pending_n.fetch_sub(1, std::memory_order_relaxed); break; }
 		}
+		hand_over_once(t);
+		while (t->remaining.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+		if (t->landed) cudaEventDestroy(t->landed);
+		delete t;
 		c->pinned[w.slot].busy = false;
 	}
 	c->widen.clear();
@@ -211,7 +292,21 @@ int32_t Stager::finish() {
 		}
 		c_->pinned[slot].busy = true;
 		STEVI_CUDA(c_, cudaMemcpyAsync(c_->pinned[slot].p, dn, bytes, cudaMemcpyDeviceToHost, c_->stream));
-		c_->widen.push_back({c_->pinned[slot].p, nw.host, nw.n, nw.bytes_per, nw.sign, nw.offset, slot});
+		(void)WidenPool::get();   // the workers are started by an API-calling thread (they inherit ITS affinity mask, not the driver's callback thread's)
+		WidenTask* t = new WidenTask();
+		t->staged = c_->pinned[slot].p; t->dst = nw.host; t->n = (long)nw.n; t->bytes_per = nw.bytes_per; t->sign = nw.sign; t->offset = nw.offset;
+		t->chunks = (int)std::max(1L, std::min((long)host_threads(), t->n / 65536));
+		t->remaining.store(t->chunks, std::memory_order_relaxed);
+		t->submitted.store(0, std::memory_order_relaxed);
+		c_->widen.push_back({c_->pinned[slot].p, nw.host, nw.n, nw.bytes_per, nw.sign, nw.offset, slot, t});
+		t->device = c_->device; t->landed = nullptr;
+		static const bool no_poll = getenv("STEVI_WIDEN_NO_POLL") != nullptr;   // measurement aid: hand over at the synchronisation only
+		if (no_poll) {
+		} else if (cudaEventCreateWithFlags(&t->landed, cudaEventDisableTiming) == cudaSuccess && cudaEventRecord(t->landed, c_->stream) == cudaSuccess) {
+			std::lock_guard<std::mutex> lk(g_pending_m);
+			g_pending.push_back(t);
+			g_pending_n.fetch_add(1, std::memory_order_relaxed);
+		} else (void)cudaGetLastError();   // (then the synchronising call hands the task over)
 	}
 	narrow_.clear();
 	if (any_host_ && !c_->deferred_host) {
@@ -274,7 +369,7 @@ int32_t stevi_ctx_destroy(stevi_ctx* c) {
 	if (c->own_stream) cudaStreamDestroy(c->stream);
 	if (c->fault_host) cudaFreeHost(c->fault_host);
 	if (c->sgm_xchg) cudaFree(c->sgm_xchg);
-	c->widen.clear();   // (results nobody synchronised for are dropped: their host arrays may be gone)
+	finish_host(c);   // (the stream has been synchronised: every pending map has been handed to the workers; wait for them)
 	for (auto& pb : c->pinned) cudaFreeHost(pb.p);
 	delete c;
 	return STEVI_OK;
