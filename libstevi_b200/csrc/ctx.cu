@@ -194,10 +194,29 @@ public:
 		}
 		if (t->chunks > 1) cv_.notify_all(); else cv_.notify_one();
 	}
+	// a thread that waits for a task takes chunks itself instead of spinning beside the workers (a rank may own 4 cores)
+	bool run_one() {
+		std::pair<WidenTask*, int> job;
+		{
+			std::lock_guard<std::mutex> lk(m_);
+			if (q_.empty()) return false;
+			job = q_.front();
+			q_.pop_front();
+		}
+		work(job);
+		return true;
+	}
 private:
 	WidenPool() {
 		const int n = host_threads();
 		for (int k = 0; k < n; k++) std::thread([this] { run(); }).detach();
+	}
+	static void work(const std::pair<WidenTask*, int>& job) {
+		WidenTask* t = job.first;
+		const long a = t->n * job.second / t->chunks / 8 * 8, b = job.second + 1 == t->chunks ? t->n : t->n * (job.second + 1) / t->chunks / 8 * 8;
+		if (t->bytes_per == 1) widen_range(static_cast<const uint8_t*>(t->staged) + a, t->dst + a, b - a, t->sign, t->offset);
+		else widen_range(static_cast<const uint16_t*>(t->staged) + a, t->dst + a, b - a, t->sign, t->offset);
+		t->remaining.fetch_sub(1, std::memory_order_release);
 	}
 	void run() {
 		for (;;) {
@@ -208,11 +227,7 @@ private:
 				job = q_.front();
 				q_.pop_front();
 			}
-			WidenTask* t = job.first;
-			const long a = t->n * job.second / t->chunks / 8 * 8, b = job.second + 1 == t->chunks ? t->n : t->n * (job.second + 1) / t->chunks / 8 * 8;
-			if (t->bytes_per == 1) widen_range(static_cast<const uint8_t*>(t->staged) + a, t->dst + a, b - a, t->sign, t->offset);
-			else widen_range(static_cast<const uint16_t*>(t->staged) + a, t->dst + a, b - a, t->sign, t->offset);
-			t->remaining.fetch_sub(1, std::memory_order_release);
+			work(job);
 		}
 	}
 	std::mutex m_;
@@ -256,7 +271,8 @@ void finish_host(stevi_ctx* c) {
 				if (g_pending[k] == t) { g_pending[k] = g_pending.back(); g_pending.pop_back(); g_pending_n.fetch_sub(1, std::memory_order_relaxed); break; }
 		}
 		hand_over_once(t);
-		while (t->remaining.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+		while (t->remaining.load(std::memory_order_acquire) != 0)
+			if (!WidenPool::get().run_one()) std::this_thread::yield();
 		if (t->landed) cudaEventDestroy(t->landed);
 		delete t;
 		c->pinned[w.slot].busy = false;
@@ -295,7 +311,7 @@ int32_t Stager::finish() {
 		(void)WidenPool::get();   // the workers are started by an API-calling thread (they inherit ITS affinity mask, not the driver's callback thread's)
 		WidenTask* t = new WidenTask();
 		t->staged = c_->pinned[slot].p; t->dst = nw.host; t->n = (long)nw.n; t->bytes_per = nw.bytes_per; t->sign = nw.sign; t->offset = nw.offset;
-		t->chunks = (int)std::max(1L, std::min((long)host_threads(), t->n / 65536));
+		t->chunks = (int)std::max(1L, std::min(2L * host_threads(), t->n / 65536));   // (more chunks than workers: the waiting thread takes some)
 		t->remaining.store(t->chunks, std::memory_order_relaxed);
 		t->submitted.store(0, std::memory_order_relaxed);
 		c_->widen.push_back({c_->pinned[slot].p, nw.host, nw.n, nw.bytes_per, nw.sign, nw.offset, slot, t});
