@@ -101,7 +101,12 @@ STEVI_API int32_t stevi_ctx_synchronize(stevi_ctx* ctx);
 /* Disparity / index maps that go back to HOST memory as dense (H,W) int32 arrays (disp_t, correlation_base.h:47) cross PCIe as
  * the narrowest exact type (u8 for up to 256 disparities, u16 up to 65536) and are widened into the caller's int32 array by the
  * host when the copy has landed (inside the call, or inside stevi_ctx_synchronize with deferred host completion): the same
- * values with a quarter / half of the device->host bytes. On by default; 0 sends the int32 map itself. */
+ * values with a quarter / half of the device->host bytes. On by default; 0 sends the int32 map itself. The widening is done by a
+ * process-wide pool of STEVI_HOST_THREADS (default 4) worker threads, started by the first call that needs them (they inherit
+ * that thread's CPU affinity); a map is handed to them by the first library call that finds its copy landed, at the latest by
+ * the synchronising call, which also takes part of the work. Which setting is faster depends on the box: narrow when many
+ * GPUs share the host's PCIe path (8 GPUs: 0.69 vs 0.87 ms per 1080p map), the int32 map itself when host cores / memory
+ * bandwidth are the scarcer resource (1 GPU: 0.27 vs 0.33 ms). Callers that can use a u8 / u16 map pass one and skip both. */
 STEVI_API int32_t stevi_ctx_set_narrow_wire(stevi_ctx* ctx, int32_t enable);
 STEVI_API const char* stevi_last_error(stevi_ctx* ctx);
 /* number of kernels this ctx has launched so far (for the benchmark's gpu_launches claim) */
