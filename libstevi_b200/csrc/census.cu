@@ -415,11 +415,8 @@ __global__ void __launch_bounds__(128) k_hamming_rows(const HamParams p) {
 	if (MODE == 4) {
 #pragma unroll
 		for (int k = 0; k < 8; k++) if (j + k < p.Ws) {
-			const int64_t o = (int64_t)i * p.Ws + j + k;
-			if (gridDim.z > 1) {   // the host pre-filled both maps with ones
-				atomicMin(p.kin + o, kin[k]);
-				if (kout[k] != 0xffffffffu) atomicMin(p.kout + o, kout[k]);
-			} else { p.kin[o] = kin[k]; p.kout[o] = kout[k]; }
+			const int64_t o = ((int64_t)blockIdx.z * p.H + i) * p.Ws + j + k;   // one slice per disparity chunk
+			p.kin[o] = kin[k]; p.kout[o] = kout[k];
 		}
 	}
 	if (MODE == 2 || MODE == 3) {
@@ -497,10 +494,6 @@ static int32_t hamming_rows_plan(stevi_ctx* c, HamParams& p, dim3& grid, size_t&
 	while ((smem = plan(dchunk, P)) > 48 * 1024 && dchunk > 32) dchunk = std::max(32, (dchunk / 2 + 7) / 8 * 8);
 	if (p.gmap && dchunk < p.D) // chunks merge their minima with atomicMin
 		STEVI_CUDA(c, cudaMemsetAsync(p.gmap, 0x7f, (size_t)p.H * p.Ws * sizeof(int32_t), c->stream));
-	if (p.kin && dchunk < p.D) {
-		STEVI_CUDA(c, cudaMemsetAsync(p.kin, 0xff, (size_t)p.H * p.Ws * sizeof(uint32_t), c->stream));
-		STEVI_CUDA(c, cudaMemsetAsync(p.kout, 0xff, (size_t)p.H * p.Ws * sizeof(uint32_t), c->stream));
-	}
 	p.dchunk = dchunk;
 	p.P = P;
 	grid = dim3(xb, p.H, cdiv(p.D, dchunk));
@@ -576,11 +569,28 @@ int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int po
 	return hamming_fused_launch<1>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
 }
 
-int32_t hamming_minkeys_dev(stevi_ctx* c, const HamSource& h, uint32_t* kin, uint32_t* kout) {
+int32_t hamming_minkeys_dev(stevi_ctx* c, const HamSource& h, uint32_t** kin, uint32_t** kout, int* nz) {
 	HamParams p;
 	STEVI_TRY(ham_params(c, h, p));
-	p.kin = kin; p.kout = kout;
-	return hamming_fused_launch<4>(c, p, h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1);
+	dim3 grid;
+	size_t smem = 0;
+	STEVI_TRY(hamming_rows_plan(c, p, grid, smem));   // (no side effects: no map is attached yet)
+	const size_t npix = (size_t)p.H * p.Ws;
+	STEVI_TRY(arena_alloc_t(c, npix * grid.z, kin));
+	STEVI_TRY(arena_alloc_t(c, npix * grid.z, kout));
+	p.kin = *kin; p.kout = *kout;
+	*nz = (int)grid.z;
+	const int sign = h.direction == STEVI_RIGHT_TO_LEFT ? 1 : -1;
+#define STEVI_HAM_CASE(NW)                                                                                   \
+	case NW:                                                                                                 \
+		if (sign > 0) STEVI_LAUNCH(c, (k_hamming_rows<NW, 1, uint16_t, true, false, 4>), grid, 128, smem, p);   \
+		else STEVI_LAUNCH(c, (k_hamming_rows<NW, -1, uint16_t, true, false, 4>), grid, 128, smem, p);           \
+		return STEVI_OK;
+	switch (p.n_words) {
+		STEVI_HAM_CASE(1) STEVI_HAM_CASE(2) STEVI_HAM_CASE(3) STEVI_HAM_CASE(4)
+	}
+#undef STEVI_HAM_CASE
+	return fail(c, STEVI_E_UNSUPPORTED, "hamming: unreachable");
 }
 
 int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, int r_max,

@@ -44,7 +44,8 @@ struct HamSource { View fl, fr; int n_cmp, D, direction; bool round; };
 bool hamming_fused_capable(const HamSource& h);
 int32_t hamming_gmap_dev(stevi_ctx* c, const HamSource& h, int32_t* gmap, int pout_i);
 // one pass: per pixel the minima over d of cost * 8192 + (8191 - d), separately for j + d < W (kin) and j + d >= W (kout)
-int32_t hamming_minkeys_dev(stevi_ctx* c, const HamSource& h, uint32_t* kin, uint32_t* kout);
+// (*nz slices of H*W keys each, one per disparity chunk of the pass, allocated in the ctx workspace: the consumer takes their minimum)
+int32_t hamming_minkeys_dev(stevi_ctx* c, const HamSource& h, uint32_t** kin, uint32_t** kout, int* nz);
 // r_max: upper bound of R (number of passes over a pixel)
 int32_t hamming_sgm_wta_dev(stevi_ctx* c, const HamSource& h, const int32_t* T, const int32_t* R, int pout_i, int r_max,
 							unsigned long long* keys);

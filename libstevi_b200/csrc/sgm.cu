@@ -183,8 +183,8 @@ __device__ __forceinline__ bool sgm_start_live(int start_pos, int corrected) { r
 // SWEEP_SEGS segments (warps). Phase A: every warp forms the alternating sum of its segment with a zero carry-in;
 // phase B: the carry into a segment is folded from the sums of the segments before it (shared memory);
 // phase C: the segment is replayed with the true carry and accumulates T += w*m_prev, R += w. The serial chain is one
-// segment long (34 rows at 1080p) instead of the image height; integer arithmetic, so the split changes nothing.
-constexpr int SWEEP_SEGS = 32;
+// segment long (68 rows at 1080p) instead of the image height; integer arithmetic, so the split changes nothing.
+constexpr int SWEEP_SEGS = 16;   // (measured at 1080p, one launch with the row walks: 32 segments 44 us, 16: 41 us, 8: 42 us)
 
 // (bx, by: the block's place in the grid of the stand-alone launch; the fused launch below hands them in)
 __device__ __forceinline__ void pathsum_sweep_body(const int32_t* __restrict__ g, int32_t* __restrict__ T, int32_t* __restrict__ R,
@@ -433,11 +433,13 @@ __global__ void __launch_bounds__(256) k_wta_decode_keys(const unsigned long lon
 // minimum wins, correlation_base.h:446) is the largest-d minimum of C on one of the two sides, and a tie between the sides goes
 // to the far side (its disparities are the larger ones). The Hamming pass leaves, per pixel, kin / kout = min over the d of a side of
 // C*8192 + (8191 - d) (0xffffffff: the side is empty); g = min_d (2*C + pout*[j+d >= W]) follows from the same two numbers.
-__global__ void __launch_bounds__(256) k_keys_to_gmap(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ kout, int n, int pout,
+// (nz: the disparity chunks of the Hamming pass leave one slice of n keys each; their minimum is taken here: no atomics, no pre-fill)
+__global__ void __launch_bounds__(256) k_keys_to_gmap(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ kout, int n, int nz, int pout,
 													  int32_t* __restrict__ g) {
 	const int k = blockIdx.x * 256 + threadIdx.x;
 	if (k >= n) return;
-	const uint32_t a = kin[k], b = kout[k];
+	uint32_t a = kin[k], b = kout[k];
+	for (int z = 1; z < nz; z++) { a = min(a, kin[(int64_t)z * n + k]); b = min(b, kout[(int64_t)z * n + k]); }
 	int v = 0x7fffffff;
 	if (a != 0xffffffffu) v = 2 * (int)(a >> 13);
 	if (b != 0xffffffffu) v = min(v, 2 * (int)(b >> 13) + pout);
@@ -445,13 +447,14 @@ __global__ void __launch_bounds__(256) k_keys_to_gmap(const uint32_t* __restrict
 }
 
 __global__ void __launch_bounds__(256) k_keys_to_disp(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ kout,
-													  const int32_t* __restrict__ T, const int32_t* __restrict__ R, int H, int W, int pout,
+													  const int32_t* __restrict__ T, const int32_t* __restrict__ R, int H, int W, int nz, int pout,
 													  int sign, int offset, int32_t* __restrict__ out, int64_t o0, int64_t o1) {
 	const int j = blockIdx.x * 256 + threadIdx.x;
 	const int i = blockIdx.y;
 	if (j >= W) return;
-	const int64_t k = (int64_t)i * W + j;
-	const uint32_t a = kin[k], b = kout[k];
+	const int64_t k = (int64_t)i * W + j, n = (int64_t)H * W;
+	uint32_t a = kin[k], b = kout[k];
+	for (int z = 1; z < nz; z++) { a = min(a, kin[z * n + k]); b = min(b, kout[z * n + k]); }
 	const int r = R[k], t = T[k];
 	int d = 0;   // (no disparity at all cannot happen: d = 0 always lies on the near side)
 	if (a != 0xffffffffu) d = 8191 - (int)(a & 8191u);
@@ -629,16 +632,15 @@ int32_t sgm_census_disparity_dev(stevi_ctx* c, const HamSource& h, int ndir, int
 	if (!two_pass && npix < (size_t)1 << 31) {
 		// one pass over the costs (in registers only): the two side minima per pixel; g and, after the path sums, the winner follow
 		uint32_t *kin = nullptr, *kout = nullptr;
-		STEVI_TRY(arena_alloc_t(c, npix, &kin));
-		STEVI_TRY(arena_alloc_t(c, npix, &kout));
-		STEVI_TRY(hamming_minkeys_dev(c, h, kin, kout));
-		STEVI_LAUNCH(c, k_keys_to_gmap, dim3(cdiv((int)npix, 256)), 256, 0, kin, kout, (int)npix, pout, g);
+		int nz = 1;
+		STEVI_TRY(hamming_minkeys_dev(c, h, &kin, &kout, &nz));
+		STEVI_LAUNCH(c, k_keys_to_gmap, dim3(cdiv((int)npix, 256)), 256, 0, kin, kout, (int)npix, nz, pout, g);
 		int32_t *T = nullptr, *R = nullptr;
 		const int32_t s = collapsed_sums(c, g, H, W, ndir, pout, mg, max_cost, &T, &R);
 		if (s == STEVI_FALLBACK) return STEVI_NOT_FUSED;
 		STEVI_TRY(s);
 		dim3 gd(cdiv(W, 256), H);
-		STEVI_LAUNCH(c, k_keys_to_disp, gd, 256, 0, kin, kout, T, R, H, W, pout, wta.sign, wta.offset, wta.out.as<int32_t>(), wta.out.st[0], wta.out.st[1]);
+		STEVI_LAUNCH(c, k_keys_to_disp, gd, 256, 0, kin, kout, T, R, H, W, nz, pout, wta.sign, wta.offset, wta.out.as<int32_t>(), wta.out.st[0], wta.out.st[1]);
 		return STEVI_OK;
 	}
 	// pass 1: g(p) = min_d (2*C + pout*[j+d >= W]); the costs live in registers only
