@@ -345,9 +345,10 @@ __global__ void __launch_bounds__(128, 2) k_sgm_sweep_h_tma(const HSweep p, cons
 
 // ---- vertical and diagonal paths: sheared strips -----------------------------------------------------------------------------
 
-constexpr int SW_TW = 16;          // columns per strip = warps per block (a warp per column)
-constexpr int SW_NWARP = SW_TW;
-constexpr int SW_TWP = SW_TW + 1;  // tile pitch (odd: a warp reading one column over 32 rows touches 32 banks)
+// columns per strip = computing warps per block (a warp per column): a template parameter, 16 or 8. Eight-column strips (round 2c) make
+// twice as many strips, two blocks per SM and half the bytes per block and row: the sweeps are bound by the per-row latency of a
+// block (tile movement, barriers), not by arithmetic. The tile pitch is TW + 1 (odd: a warp reading one column over 32 rows touches
+// 32 banks); TW / 2 warps move tiles.
 
 struct VSweep {
 	const void* C; int64_t c0, c2; int c_u16;
@@ -437,11 +438,9 @@ __device__ __forceinline__ void sw_path_fast(const float (&c)[DN], float (&st)[D
 // reader is a 17th warp that does nothing else: it collects what the strip on the right left for the NEXT row while the 16
 // others work on the current one (its trips to L2 are off their critical path) and joins them at the barrier that opens a row.
 // DIRS: bit k = path k is part of the direction set of this sweep.
-constexpr int SW_NIO = 8;          // warps that only move tiles
-
-template<int DH, int MODE, int DIRS>
-__global__ void __launch_bounds__((SW_NWARP + 1 + SW_NIO) * 32, 1) k_sgm_sweep_t(const VSweep p) {
-	constexpr int TW = SW_TW, TWP = SW_TWP, NWARP = SW_NWARP, DR = 32 * DH, TILE = DR * TWP;
+template<int DH, int MODE, int DIRS, int TWT>
+__global__ void __launch_bounds__((TWT + 1 + TWT / 2) * 32, TWT == 8 ? 2 : 1) k_sgm_sweep_t(const VSweep p) {
+	constexpr int TW = TWT, TWP = TWT + 1, NWARP = TWT, SW_NIO = TWT / 2, DR = 32 * DH, TILE = DR * TWP;
 	constexpr bool EN0 = (DIRS & 1) != 0, EN1 = (DIRS & 2) != 0, EN2 = (DIRS & 4) != 0, XCH = EN1 || EN2;
 	constexpr int NCT = NWARP * 32, NIOT = SW_NIO * 32, NALL = NCT + 32 + NIOT;   // computing threads, tile movers, everyone
 	extern __shared__ float smem[];
@@ -475,8 +474,8 @@ __global__ void __launch_bounds__((SW_NWARP + 1 + SW_NIO) * 32, 1) k_sgm_sweep_t
 		if (w > NWARP) {
 			// ================= tile movers: slab of row t+1 in (asynchronous copies), results of row t out =================
 			// thread = tile column fcol, disparity rows frow + 16 u. (Row d sits at tile row (d % DH) * 32 + d / DH.)
-			constexpr int FR = NIOT / 16;                   // disparity rows the movers cover at a time (16)
-			const int it = tid - NCT - 32, fcol = it & 15, frow = it >> 4;   // frow 0..FR-1
+			constexpr int FR = NIOT / TW;                   // disparity rows the movers cover at a time (16)
+			const int it = tid - NCT - 32, fcol = it % TW, frow = it / TW;   // frow 0..FR-1
 			constexpr int NU = DR / FR;
 			auto tile_row = [&](int u) { return (frow % DH) * 32 + frow / DH + u * (FR / DH); };   // (FR is a multiple of DH)
 			const int nu = min(NU, (p.D - frow + FR - 1) / FR);   // disparity rows of this thread that exist
@@ -845,20 +844,23 @@ static int32_t launch_h_tma(stevi_ctx* c, const HSweep& p, const CUtensorMap& tm
 	return STEVI_OK;
 }
 
-static size_t sweep_smem(int dh, bool has_a, bool accumulate) {
-	const size_t tile = (size_t)32 * dh * SW_TWP;
-	return ((dh <= 8 ? 3 : 2) * tile * (1 + (has_a ? 1 : 0) + (accumulate ? 1 : 0)) + (size_t)(2 * SW_NWARP + 6) * 32 * dh) * sizeof(float);
+static size_t sweep_smem(int dh, bool has_a, bool accumulate, int tw) {
+	const size_t tile = (size_t)32 * dh * (tw + 1);
+	return ((dh <= 8 ? 3 : 2) * tile * (1 + (has_a ? 1 : 0) + (accumulate ? 1 : 0)) + (size_t)(2 * tw + 6) * 32 * dh) * sizeof(float);
 }
 
-template<int MODE, int DIRS>
+template<int MODE, int DIRS, int TWT>
 static int32_t launch_v(stevi_ctx* c, const VSweep& p) {
 	const int dh = p.D <= 32 ? 1 : p.D <= 64 ? 2 : p.D <= 128 ? 4 : p.D <= 256 ? 8 : 16;
-	const size_t smem = sweep_smem(dh, p.A != nullptr, p.accumulate != 0);
+	const size_t smem = sweep_smem(dh, p.A != nullptr, p.accumulate != 0, TWT);
 	if (smem > (227u << 10)) return fail(c, STEVI_E_UNSUPPORTED, "sgm: the sweep tiles do not fit in shared memory");
-	dim3 grid(std::min(p.n_strips, c->sm_count));
+	// persistent blocks: as many as are resident at once (a strip waits for the strip on its right, which must be running)
+	const int want_per_sm = TWT == 8 ? 2 : 1;
+	const int per_sm = std::max(1, std::min(want_per_sm, (int)((227u << 10) / (smem + 1024))));
+	dim3 grid(std::min(p.n_strips, per_sm * c->sm_count));
 #define STEVI_T(DH) do { \
-	STEVI_CUDA(c, cudaFuncSetAttribute((k_sgm_sweep_t<DH, MODE, DIRS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-	STEVI_LAUNCH(c, (k_sgm_sweep_t<DH, MODE, DIRS>), grid, (SW_NWARP + 1 + SW_NIO) * 32, smem, p); } while (0)
+	STEVI_CUDA(c, cudaFuncSetAttribute((k_sgm_sweep_t<DH, MODE, DIRS, TWT>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+	STEVI_LAUNCH(c, (k_sgm_sweep_t<DH, MODE, DIRS, TWT>), grid, (TWT + 1 + TWT / 2) * 32, smem, p); } while (0)
 	switch (dh) {
 	case 1: STEVI_T(1); break;
 	case 2: STEVI_T(2); break;
@@ -871,13 +873,21 @@ static int32_t launch_v(stevi_ctx* c, const VSweep& p) {
 }
 
 template<int MODE>
-static int32_t launch_v_dirs(stevi_ctx* c, const VSweep& p, int dirs) {
-	switch (dirs) {
-	case 7: return launch_v<MODE, 7>(c, p);
-	case 2: return launch_v<MODE, 2>(c, p);
-	case 1: return launch_v<MODE, 1>(c, p);
-	default: return fail(c, STEVI_E_UNSUPPORTED, "sgm: unexpected direction set of a sweep");
+static int32_t launch_v_dirs(stevi_ctx* c, const VSweep& p, int dirs, int tw) {
+	if (tw == 8) {
+		switch (dirs) {
+		case 7: return launch_v<MODE, 7, 8>(c, p);
+		case 2: return launch_v<MODE, 2, 8>(c, p);
+		case 1: return launch_v<MODE, 1, 8>(c, p);
+		}
+	} else {
+		switch (dirs) {
+		case 7: return launch_v<MODE, 7, 16>(c, p);
+		case 2: return launch_v<MODE, 2, 16>(c, p);
+		case 1: return launch_v<MODE, 1, 16>(c, p);
+		}
 	}
+	return fail(c, STEVI_E_UNSUPPORTED, "sgm: unexpected direction set of a sweep");
 }
 
 bool sgm_sweep_capable(const View& cv, int ndir, int strategy, float P1, float P2, int semantics, const View& out) {
@@ -940,16 +950,18 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 	v.S = out.as<float>(); v.s0 = out.st[0]; v.s2 = out.st[2];
 	v.a0 = h.a0; v.a2 = h.a2;
 	v.H = H; v.W = W; v.D = D; v.top = mg.top; v.left = mg.left; v.nrows = nrows; v.ncols = ncols;
-	const int cw = SW_TW;
+	// strip width per sweep: 8 columns when nothing is exchanged between strips (the along-the-shear path alone: the upward sweep of
+	// COMPAT), 16 otherwise (measured at C2 size: upward sweep 1.82 -> 1.29 ms with 8; downward sweep 3.80 -> 5.46 ms: the hand-over
+	// chain is as long as the strips are many). The exchange buffer is sized for 16-column strips: only they exchange.
+	static const int tw_env = [] { const char* e = getenv("STEVI_SGM_TW"); return e ? atoi(e) : 0; }();   // measurement aid: force 8 or 16
+	const int cw = tw_env == 8 ? 8 : 16;   // (the width the exchange buffer is sized for)
 	const int dr = 32 * (D <= 32 ? 1 : D <= 64 ? 2 : D <= 128 ? 4 : D <= 256 ? 8 : 16);   // disparity rows of a tile
 	v.P1 = P1; v.P2 = P2; v.Pout = Pout;
 	v.corner_once = corrected ? 1 : 0;
 	v.fault = c->fault_dev;
 	{ static const char* e = getenv("STEVI_SGM_DBG"); v.dbg = e ? atoi(e) : 0; }
-	v.s_lo = -((nrows - 1 + cw - 1) / cw);
-	const int s_all = (ncols - 1) / cw;
 	// exchange buffer between neighbouring strips: persistent in the ctx (only ever holds this kernel's tagged pairs)
-	const size_t xbytes = (size_t)(s_all - v.s_lo + 1) * nrows * 3 * dr * sizeof(uint2);
+	const size_t xbytes = (size_t)((ncols - 1) / cw + (nrows - 1 + cw - 1) / cw + 1) * nrows * 3 * dr * sizeof(uint2);
 	if (c->sgm_xchg_bytes < xbytes) {
 		STEVI_CUDA(c, cudaStreamSynchronize(c->stream));
 		if (c->sgm_xchg) cudaFree(c->sgm_xchg);
@@ -979,6 +991,9 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 			any_col |= v.collive[k] != 0;
 		}
 		if (!dirs) continue;
+		const int tw = tw_env == 8 || tw_env == 16 ? tw_env : (dirs == 1 ? 8 : 16);   // (4-column strips: 2.66 ms for the upward sweep, half-sector accesses)
+		v.s_lo = -((nrows - 1 + tw - 1) / tw);
+		const int s_all = (ncols - 1) / tw;
 		// strips that hold live pixels: lines started by the column loop reach everywhere, lines started on the left column
 		// (the only row starts of a sweep without live column starts) stay at or left of the diagonal through the corner
 		v.s_hi = any_col ? s_all : 0;
@@ -989,9 +1004,9 @@ int32_t sgm_sweep(stevi_ctx* c, const View& cv, int ndir, int strategy, float P1
 			c->sgm_epoch = 0;
 		}
 		v.tag_base = (unsigned)(++c->sgm_epoch) << 16;
-		if (mode == SW_SCORE) STEVI_TRY(launch_v_dirs<SW_SCORE>(c, v, dirs));
-		else if (mode == SW_COST) STEVI_TRY(launch_v_dirs<SW_COST>(c, v, dirs));
-		else STEVI_TRY(launch_v_dirs<SW_COST_COMPAT>(c, v, dirs));
+		if (mode == SW_SCORE) STEVI_TRY(launch_v_dirs<SW_SCORE>(c, v, dirs, tw));
+		else if (mode == SW_COST) STEVI_TRY(launch_v_dirs<SW_COST>(c, v, dirs, tw));
+		else STEVI_TRY(launch_v_dirs<SW_COST_COMPAT>(c, v, dirs, tw));
 	}
 	return STEVI_OK;
 }
